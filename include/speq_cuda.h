@@ -1,0 +1,196 @@
+/* speq_cuda.h -- C ABI of libspeq_cuda.so: the B200 (sm_100a) replacement for SPeQ's scan hot path.
+ *
+ * SPeQ (ibharvey/speq) has no plugin/FFI layer of its own: the hot path is reached from three C++ entry points called
+ * by main() (reference src/main.cpp:21-35).  Every entry point below names the reference interface it replaces
+ * (paths relative to the reference checkout; S3 = deps/seqan3, SDSL = S3/submodules/sdsl-lite/include/sdsl).
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success and a negative SPEQG_E* code on
+ * failure, with a human-readable message available from speqg_last_error() (thread-local).  No exception crosses the
+ * ABI.  Handles are not thread-safe; use one speqg_scan per host thread / CUDA device.  There is NO CPU fallback:
+ * every compute entry point fails with SPEQG_ECUDA when no CUDA device is usable.
+ */
+#ifndef SPEQ_CUDA_H
+#define SPEQ_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPEQG_ABI_VERSION 1
+
+enum
+{
+    SPEQG_OK = 0,
+    SPEQG_EINVAL = -1,   /* bad argument (message says which) */
+    SPEQG_ECUDA = -2,    /* CUDA runtime error / no device */
+    SPEQG_EIO = -3,      /* file could not be read / written / has the wrong format */
+    SPEQG_ENOMEM = -4,
+    SPEQG_ESTATE = -5    /* call made in the wrong state (e.g. refine without recorded multiplicities) */
+};
+
+typedef struct speqg_index speqg_index;   /* FM index over the variant collection (host copy + per-device copies) */
+typedef struct speqg_scan speqg_scan;     /* one scan stream on one device */
+
+const char * speqg_last_error(void);
+int speqg_abi_version(void);
+int speqg_device_count(int * count);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Index.  Replaces seqan3::fm_index{fnr_ref_seqs} (reference src/fm_indexer.cpp:19-36; construction
+ * S3/include/seqan3/search/fm_index/fm_index.hpp:233-316; sdsl::construct_im SDSL/construct.hpp:110-166) and the
+ * text-position machinery behind locate() (S3/include/seqan3/search/fm_index/fm_index_cursor.hpp:521-538).
+ *
+ * texts[i] / lens[i]: the S texts of the collection, as dna5 RANKS (A0 C1 G2 N3 T4), in the order speq indexes them:
+ *   text 2j = scaffold j, text 2j+1 = reverse complement of scaffold j (src/fm_indexer.cpp:25-33).
+ * group_of_text[i]: variant of text i in [0, V) -- the reference's double_group_scaffolds (src/fm_scanner.cpp:74-77).
+ *   Negative (unassigned) entries are rejected: the reference indexes vectors with -1 in its refinement loop
+ *   (src/fm_scanner.cpp:1102), which is undefined behaviour.
+ * flags: SPEQG_BUILD_KEEP_SA keeps the suffix array for speqg_index_export (tests).
+ * ------------------------------------------------------------------------------------------------------------------ */
+#define SPEQG_BUILD_KEEP_SA 1u
+
+typedef struct speqg_index_info
+{
+    uint64_t n;             /* indexed text length incl. delimiters and sentinel == seqan3 fm_index::size() */
+    uint32_t n_texts;       /* S */
+    uint32_t n_groups;      /* V */
+    uint64_t C[8];          /* cumulative symbol counts: C[c] = #text symbols < c, c = 0 sentinel,1 A,2 C,3 G,4 N,5 T,6 delim */
+    uint64_t n_exceptions;  /* BWT positions holding N / delimiter / sentinel */
+    uint64_t device_bytes;  /* bytes one device copy occupies */
+} speqg_index_info;
+
+int speqg_index_build(const uint8_t * const * texts, const uint64_t * lens, uint32_t n_texts,
+                      const int32_t * group_of_text, uint32_t n_groups, uint32_t flags, speqg_index ** out);
+int speqg_index_save(const speqg_index * idx, const char * path);
+int speqg_index_load(const char * path, speqg_index ** out);
+int speqg_index_get_info(const speqg_index * idx, speqg_index_info * info);
+/* White-box export for parity tests: any pointer may be NULL (n entries each).  sa needs SPEQG_BUILD_KEEP_SA.  bwt holds
+ * text symbols (A1 C2 G3 N4 T5; delimiter and sentinel both 0xFF); lcp is capped at 127. */
+int speqg_index_export(const speqg_index * idx, uint32_t * sa, uint8_t * bwt, uint32_t * group_of_sa, uint8_t * lcp);
+int speqg_index_upload(speqg_index * idx, int device);
+void speqg_index_free(speqg_index * idx);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Packed read batches.  Replaces what seqan3::sequence_file_input hands the reference's workers (vector<dna5> +
+ * vector<phred42> per record, src/fm_scanner.cpp:198-199) by a 2-bit packed, length-prefixed batch.
+ * Read i owns 32-base groups [grp_off[i], grp_off[i+1]):
+ *   bases[g]: 32 x 2-bit codes (A0 C1 G2 T3; N coded 0), base j of the read in bits [2*(j%32), +2) of group j/32
+ *   inv[g]:   1 bit per base: base is N, or (scan) its phred <= phred_cutoff -- a window containing a set bit is not
+ *             counted (src/fm_scanner.cpp:162: min(phred) > cutoff && no 'N')
+ *   qual:     phred (0..41) per base at byte 32*grp_off[i] + j; only for local-error mode, else NULL
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct speqg_batch
+{
+    uint64_t * bases;
+    uint32_t * inv;
+    uint8_t * qual;
+    uint64_t * grp_off;    /* n_reads + 1 entries */
+    uint32_t * len;        /* n_reads entries */
+    uint64_t n_reads;
+    uint64_t n_groups32;   /* == grp_off[n_reads] */
+} speqg_batch;
+
+#define SPEQG_ENC_ASCII 0   /* seq: IUPAC letters (dna5 rules, S3/include/seqan3/alphabet/nucleotide/dna5.hpp:87-119);
+                               qual: phred+33 chars (clamped to 0..41, S3/.../quality/quality_base.hpp:139-160) */
+#define SPEQG_ENC_RANK 1    /* seq: dna5 ranks 0..4; qual: phred values */
+
+/* offsets: n_reads+1 byte offsets into seq/qual (read i = [offsets[i], offsets[i+1])).  qual may be NULL (no quality
+ * filter, e.g. reference scaffolds).  n_only != 0: inv marks N only (back-check / statistics).  The arrays of `out`
+ * must be preallocated: n_groups32 = speqg_pack_groups(offsets, n_reads), bases n_groups32 u64, inv n_groups32 u32,
+ * qual 32*n_groups32 bytes or NULL, grp_off n_reads+1, len n_reads.  Illegal (non-IUPAC) letters -> SPEQG_EINVAL
+ * (the reference throws seqan3::parse_error). */
+uint64_t speqg_pack_groups(const uint64_t * offsets, uint64_t n_reads);
+int speqg_pack_reads(const uint8_t * seq, const uint8_t * qual, const uint64_t * offsets, uint64_t n_reads,
+                     int encoding, uint32_t phred_cutoff, int n_only, int threads, speqg_batch * out);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Scan.  Replaces the worker bodies of speq::scan::_async_{one,two}_with_{global,local}_error_rate
+ * (src/fm_scanner.cpp:145-216, 418-491, 662-732, 911-998): sliding k-mer windows, seqan3::search() with
+ * max_error{total{0}} (S3/include/seqan3/search/algorithm/search.hpp:166-192), and do_a_count.
+ * ------------------------------------------------------------------------------------------------------------------ */
+#define SPEQG_MODE_GLOBAL 0   /* --fixed-accuracy != 0: integer unique tallies (src/fm_scanner.cpp:180) */
+#define SPEQG_MODE_LOCAL 1    /* fp64 tallies weighted by prod 1/(1-10^(-q/10)) (src/fm_scanner.cpp:454-455) */
+
+#define SPEQG_ALGO_ROLLING 0  /* one pass per read: consecutive windows share their search state (default) */
+#define SPEQG_ALGO_DIRECT 1   /* every window searched from the root, k steps, like seqan3's search_trivial (global mode) */
+
+typedef struct speqg_params
+{
+    uint32_t k;                    /* k-mer length, 1..128 (include/arg_parse.h:20) */
+    uint32_t phred_cutoff;         /* include/arg_parse.h:21; used by the device packer of submit_ascii */
+    int32_t mode;                  /* SPEQG_MODE_* */
+    int32_t paired;                /* reads 2i and 2i+1 of every batch are mates sharing one ambiguity state */
+    int32_t record_multiplicity;   /* keep per-k-mer multiplicities so speqg_refine can run without re-reading reads */
+    uint32_t algorithm;            /* SPEQG_ALGO_* */
+    void * stream;                 /* cudaStream_t to launch on; NULL = a stream owned by the handle */
+} speqg_params;
+
+typedef struct speqg_counts
+{
+    uint64_t total_kmers;       /* valid windows (src/fm_scanner.cpp:164) */
+    uint64_t ambiguous_reads;   /* reads / pairs with unique k-mers of >= 2 variants (src/fm_scanner.cpp:183-190,213) */
+    uint64_t lookups;           /* windows presented = sum max(0, L-k+1) */
+    uint64_t reads;
+    uint64_t kernel_launches;   /* kernels launched by this handle since open / reset */
+    /* filled by speqg_scan_stats only (reference-semantics work counters for the roofline): */
+    uint64_t steps_executed;    /* backward_search calls incl. the failing one (fm_index_cursor.hpp:316-324) */
+    uint64_t kmers_hit;         /* k-mers with a non-empty final interval */
+    uint64_t occurrences;       /* sum of final interval sizes */
+    uint64_t occ_sectors;       /* sum ceil(occ/32) */
+} speqg_counts;
+
+int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, speqg_scan ** out);
+/* host packed batch: H2D copy + kernel, asynchronous; the host arrays may be reused after speqg_scan_sync. */
+int speqg_scan_submit_packed(speqg_scan * scan, const speqg_batch * host_batch);
+/* host raw reads (ASCII or ranks): H2D copy of the bytes + device packer + kernel, asynchronous. */
+int speqg_scan_submit_raw(speqg_scan * scan, const uint8_t * seq, const uint8_t * qual, const uint64_t * offsets,
+                          uint64_t n_reads, int encoding);
+/* batch whose arrays already live in device memory of the scan's device (pointers are device pointers). */
+int speqg_scan_submit_device(speqg_scan * scan, const speqg_batch * device_batch);
+int speqg_scan_sync(speqg_scan * scan);
+/* sync, then copy the tallies out.  unique_u64 / unique_f64: n_groups entries each, either may be NULL. */
+int speqg_scan_finish(speqg_scan * scan, uint64_t * unique_u64, double * unique_f64, speqg_counts * counts);
+int speqg_scan_reset(speqg_scan * scan);
+/* Reference-semantics work counters for one device batch (every window searched from the root with no jump table,
+ * N searched as a symbol, stop at the first empty interval).  Not part of the product path; used for the roofline. */
+int speqg_scan_stats(speqg_scan * scan, const speqg_batch * device_batch, speqg_counts * counts);
+void speqg_scan_close(speqg_scan * scan);
+
+/* device-resident copy of a host batch (for speqg_scan_submit_device); free with speqg_batch_free_device. */
+int speqg_batch_to_device(int device, const speqg_batch * host_batch, speqg_batch * device_batch);
+void speqg_batch_free_device(int device, speqg_batch * device_batch);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Back-check.  Replaces speq::scan::_async_count_unique_kmers_per_group (src/fm_scanner.cpp:1476-1576): for every
+ * scaffold (text 2j) and its reverse complement (text 2j+1), every k-mer incl. those containing N; unique iff every
+ * occurrence lies in the scaffold's own group.  unique_ref / total_ref: n_groups entries.
+ * ------------------------------------------------------------------------------------------------------------------ */
+int speqg_backcheck(speqg_index * idx, int device, uint32_t k, uint64_t * unique_ref, uint64_t * total_ref);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Refinement estimate.  Replaces speq::scan::_async_{one,two}_{global,local}_estimate_kmer_per_group
+ * (src/fm_scanner.cpp:1069-1453) WITHOUT re-reading the reads: uses the multiplicities recorded during the scan
+ * (params.record_multiplicity).  percent, group_counts: n_groups entries in; tkpg: n_groups entries out.
+ * The per-k-mer weight of the reference (1/pp-(1-pp), resp. the phred products) multiplies every group of one k-mer
+ * alike and cancels in a[g]/sum(a) (src/fm_scanner.cpp:1099-1119), so it is not needed here.
+ * ------------------------------------------------------------------------------------------------------------------ */
+int speqg_refine(speqg_scan * scan, const double * percent, const int32_t * group_counts, double * tkpg);
+/* export / import the recorded multiplicities (lb, rb, count) so several devices or ranks can be merged. */
+int speqg_scan_multiplicity_count(speqg_scan * scan, uint64_t * n_entries);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Host-side solve (fp64, exact operation order of the reference).
+ * speqg_unique_to_percent: speq::scan::unique_to_percent (src/fm_scanner.cpp:1455-1474).
+ * speqg_solve: the loop of src/fm_scanner.cpp:238-279 driven by speqg_refine; returns the iteration count.
+ * ------------------------------------------------------------------------------------------------------------------ */
+int speqg_unique_to_percent(const double * unique_in_reads, uint64_t total_in_reads, const double * unique_in_refs,
+                            const double * total_in_refs, uint32_t n_groups, double * out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPEQ_CUDA_H */

@@ -1,0 +1,471 @@
+// capi_scan.cu -- scan / back-check / refinement entry points of the C ABI (include/speq_cuda.h).
+//
+// One speqg_scan owns: the tallies in device memory, a compute stream (the caller's or its own), a copy stream, and a
+// ring of device staging slots so the H2D copy of batch i+1 overlaps the kernel of batch i.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "capi_util.h"
+#include "kernels.h"
+
+using namespace speqb;
+
+namespace
+{
+constexpr int kSlots = 3;
+
+template <class T> struct dev_buf
+{
+    T * p = nullptr;
+    size_t cap = 0;
+    void reserve(size_t count)
+    {
+        if (count <= cap) return;
+        if (p) CK(cudaFree(p));
+        p = nullptr;
+        cap = 0;
+        size_t want = count + count / 8 + 64;
+        CK(cudaMalloc(reinterpret_cast<void **>(&p), want * sizeof(T)));
+        cap = want;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct Slot
+{
+    dev_buf<uint64_t> bases, grp_off, raw_off;
+    dev_buf<uint32_t> inv, len;
+    dev_buf<uint8_t> qual, raw_seq, raw_qual;
+    cudaEvent_t copied = nullptr, done = nullptr;
+    bool busy = false;
+    void release()
+    {
+        bases.release(); grp_off.release(); raw_off.release(); inv.release(); len.release();
+        qual.release(); raw_seq.release(); raw_qual.release();
+        if (copied) cudaEventDestroy(copied);
+        if (done) cudaEventDestroy(done);
+        copied = done = nullptr;
+    }
+};
+}   // namespace
+
+struct speqg_scan
+{
+    speqg_index * idx = nullptr;
+    DeviceIndex * di = nullptr;
+    int device = 0;
+    speqg_params p{};
+    int mode = 0;
+    cudaStream_t compute = nullptr, copy = nullptr;
+    bool own_compute = false;
+    unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr;
+    double * d_unique_w = nullptr, * d_qden = nullptr, * d_percent = nullptr, * d_tkpg = nullptr, * d_partial = nullptr;
+    int32_t * d_gc = nullptr;
+    LaunchCfg cfg{}, cfg_direct{}, cfg_stats{};
+    int refine_grid = 0;
+    Slot slots[kSlots];
+    int next_slot = 0;
+    std::vector<uint64_t> h_grp_off;   // scratch for submit_raw
+    std::vector<uint32_t> h_len;
+    uint64_t launches = 0;
+};
+
+namespace speqb
+{
+struct scan_refine_view
+{
+    int device;
+    uint32_t k, V;
+    uint64_t n;
+    DeviceIndex * di;
+    cudaStream_t stream;
+    unsigned long long * mult;
+    double * d_percent, * d_tkpg, * d_partial;
+    int32_t * d_gc;
+    int refine_grid;
+};
+scan_refine_view refine_view(speqg_scan * s)
+{
+    return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->di, s->compute, s->d_mult,
+                            s->d_percent, s->d_tkpg, s->d_partial, s->d_gc, s->refine_grid};
+}
+}   // namespace speqb
+
+namespace
+{
+void scan_release(speqg_scan * s)
+{
+    cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
+    cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
+    cudaFree(s->d_gc);
+    for (auto & sl : s->slots) sl.release();
+    if (s->copy) cudaStreamDestroy(s->copy);
+    if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
+}
+
+ScanArgs scan_args(speqg_scan * s)
+{
+    ScanArgs a{};
+    a.k = s->p.k;
+    a.V = s->idx->host.V;
+    a.unique = s->d_unique;
+    a.total_g = s->d_total_g;
+    a.unique_w = s->d_unique_w;
+    a.scalars = s->d_scalars;
+    a.mult = s->d_mult;
+    a.qden = s->d_qden;
+    a.segs = nullptr;
+    a.n_segs = 0;
+    return a;
+}
+
+void check_batch(speqg_scan * s, speqg_batch const * b)
+{
+    need(b != nullptr, "batch is NULL");
+    if (b->n_reads == 0) return;
+    need(b->bases && b->inv && b->grp_off && b->len, "batch arrays must not be NULL");
+    need(!(s->mode & M_LOCAL) || b->qual != nullptr, "local-error mode needs per-base qualities (batch.qual)");
+    need(!(s->mode & M_PAIRED) || b->n_reads % 2 == 0, "paired mode needs an even number of reads per batch (mates interleaved)");
+    need(b->n_reads < (uint64_t(1) << 32), "more than 2^32 reads in one batch");
+}
+
+void launch_on_view(speqg_scan * s, BatchView const & v)
+{
+    if (v.n_reads == 0) return;
+    ScanArgs a = scan_args(s);
+    if (s->p.algorithm == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->di->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
+    else CK(launch_scan_roll(s->di->view, v, a, s->mode, s->cfg, s->compute));
+    ++s->launches;
+}
+
+Slot & acquire_slot(speqg_scan * s)
+{
+    Slot & sl = s->slots[s->next_slot];
+    s->next_slot = (s->next_slot + 1) % kSlots;
+    if (!sl.copied)
+    {
+        CK(cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    }
+    // the staging buffers may be regrown (cudaFree) or overwritten only after the kernel that read them has finished
+    if (sl.busy) CK(cudaStreamWaitEvent(s->copy, sl.done, 0));
+    return sl;
+}
+}   // namespace
+
+extern "C" {
+
+int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, speqg_scan ** out)
+{
+    SPEQG_TRY
+    need(idx && params && out, "NULL argument");
+    need(params->k >= 1 && params->k <= kMaxK, "k must be in [1, 127]");
+    need(params->mode == SPEQG_MODE_GLOBAL || params->mode == SPEQG_MODE_LOCAL, "unknown mode");
+    need(params->algorithm == SPEQG_ALGO_ROLLING || params->algorithm == SPEQG_ALGO_DIRECT, "unknown algorithm");
+    need(!(params->algorithm == SPEQG_ALGO_DIRECT && params->mode == SPEQG_MODE_LOCAL), "the direct algorithm covers global mode only");
+    DeviceIndex & di = device_index(idx, device);
+    device_guard guard(device);
+    auto * s = new speqg_scan();
+    try
+    {
+        s->idx = idx;
+        s->di = &di;
+        s->device = device;
+        s->p = *params;
+        s->mode = (params->mode == SPEQG_MODE_LOCAL ? M_LOCAL : 0) | (params->record_multiplicity ? M_RECORD : 0) |
+                  (params->paired ? M_PAIRED : 0);
+        uint32_t V = idx->host.V;
+        if (params->stream) s->compute = static_cast<cudaStream_t>(params->stream);
+        else
+        {
+            CK(cudaStreamCreateWithFlags(&s->compute, cudaStreamNonBlocking));
+            s->own_compute = true;
+        }
+        CK(cudaStreamCreateWithFlags(&s->copy, cudaStreamNonBlocking));
+        s->d_unique = dev_alloc<unsigned long long>(V);
+        s->d_total_g = dev_alloc<unsigned long long>(V);
+        s->d_unique_w = dev_alloc<double>(V);
+        s->d_scalars = dev_alloc<unsigned long long>(SC_COUNT);
+        s->d_bad = dev_alloc<unsigned long long>(1);
+        s->d_percent = dev_alloc<double>(V);
+        s->d_tkpg = dev_alloc<double>(V);
+        s->d_gc = dev_alloc<int32_t>(V);
+        if (params->record_multiplicity) s->d_mult = dev_alloc<unsigned long long>(idx->host.n);
+        // local-mode denominators with the host's libm, exactly the reference's expression (src/fm_scanner.cpp:454)
+        double qden[42];
+        for (int q = 0; q < 42; ++q)
+        {
+            double b = q;
+            qden[q] = 1.0 - 1.0 / pow(10.0, b / 10.0);
+        }
+        s->d_qden = dev_upload(qden, 42);
+        CK(scan_launch_cfg(s->mode, 0, V, &s->cfg));
+        CK(scan_launch_cfg(s->mode, 1, V, &s->cfg_direct));
+        CK(scan_launch_cfg(s->mode, 2, V, &s->cfg_stats));
+        int sms = 0;
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        s->refine_grid = sms * 4;
+        s->d_partial = dev_alloc<double>((size_t)s->refine_grid * V);
+    }
+    catch (...)
+    {
+        scan_release(s);
+        delete s;
+        throw;
+    }
+    *out = s;
+    int rc = speqg_scan_reset(s);
+    if (rc != SPEQG_OK)
+    {
+        scan_release(s);
+        delete s;
+        *out = nullptr;
+        return rc;
+    }
+    SPEQG_CATCH
+}
+
+int speqg_scan_reset(speqg_scan * s)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    device_guard guard(s->device);
+    uint32_t V = s->idx->host.V;
+    CK(cudaMemsetAsync(s->d_unique, 0, V * 8, s->compute));
+    CK(cudaMemsetAsync(s->d_total_g, 0, V * 8, s->compute));
+    CK(cudaMemsetAsync(s->d_unique_w, 0, V * 8, s->compute));
+    CK(cudaMemsetAsync(s->d_scalars, 0, SC_COUNT * 8, s->compute));
+    CK(cudaMemsetAsync(s->d_bad, 0, 8, s->compute));
+    if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
+    s->launches = 0;
+    SPEQG_CATCH
+}
+
+int speqg_scan_submit_packed(speqg_scan * s, const speqg_batch * hb)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    check_batch(s, hb);
+    if (hb->n_reads == 0) return SPEQG_OK;
+    device_guard guard(s->device);
+    Slot & sl = acquire_slot(s);
+    uint64_t R = hb->n_reads, G = hb->n_groups32;
+    need(G == hb->grp_off[R], "n_groups32 != grp_off[n_reads]");
+    sl.bases.reserve(G + 1); sl.inv.reserve(G + 1); sl.grp_off.reserve(R + 1); sl.len.reserve(R);
+    CK(cudaMemcpyAsync(sl.bases.p, hb->bases, G * 8, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaMemcpyAsync(sl.inv.p, hb->inv, G * 4, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaMemcpyAsync(sl.grp_off.p, hb->grp_off, (R + 1) * 8, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaMemcpyAsync(sl.len.p, hb->len, R * 4, cudaMemcpyHostToDevice, s->copy));
+    if (s->mode & M_LOCAL)
+    {
+        sl.qual.reserve(G * 32 + 32);
+        CK(cudaMemcpyAsync(sl.qual.p, hb->qual, G * 32, cudaMemcpyHostToDevice, s->copy));
+    }
+    CK(cudaEventRecord(sl.copied, s->copy));
+    CK(cudaStreamWaitEvent(s->compute, sl.copied, 0));
+    BatchView v{};
+    v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = (s->mode & M_LOCAL) ? sl.qual.p : nullptr;
+    v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = R;
+    launch_on_view(s, v);
+    CK(cudaEventRecord(sl.done, s->compute));
+    sl.busy = true;
+    SPEQG_CATCH
+}
+
+int speqg_scan_submit_raw(speqg_scan * s, const uint8_t * seq, const uint8_t * qual, const uint64_t * offsets, uint64_t n_reads,
+                          int encoding)
+{
+    SPEQG_TRY
+    need(s != nullptr && offsets != nullptr, "NULL argument");
+    if (n_reads == 0) return SPEQG_OK;
+    need(seq != nullptr, "seq is NULL");
+    need(encoding == SPEQG_ENC_ASCII || encoding == SPEQG_ENC_RANK, "unknown encoding");
+    need(!(s->mode & M_LOCAL) || qual != nullptr, "local-error mode needs qualities");
+    need(!(s->mode & M_PAIRED) || n_reads % 2 == 0, "paired mode needs an even number of reads per batch (mates interleaved)");
+    need(n_reads < (uint64_t(1) << 32), "more than 2^32 reads in one batch");
+    device_guard guard(s->device);
+    uint64_t R = n_reads, base = offsets[0], bytes = offsets[R] - base;
+    s->h_grp_off.resize(R + 1);
+    uint64_t G = 0;
+    for (uint64_t i = 0; i < R; ++i)
+    {
+        uint64_t L = offsets[i + 1] - offsets[i];
+        need(L < (uint64_t(1) << 32), "read longer than 2^32");
+        s->h_grp_off[i] = G;
+        G += (L + 31) >> 5;
+    }
+    s->h_grp_off[R] = G;
+    Slot & sl = acquire_slot(s);
+    sl.bases.reserve(G + 1); sl.inv.reserve(G + 1); sl.grp_off.reserve(R + 1); sl.len.reserve(R); sl.raw_off.reserve(R + 1);
+    sl.raw_seq.reserve(bytes + 1);
+    if (qual) sl.raw_qual.reserve(bytes + 1);
+    if (s->mode & M_LOCAL) sl.qual.reserve(G * 32 + 32);
+    // the host scratch (h_grp_off) is pageable: cudaMemcpyAsync stages it before returning, so it may be reused at once
+    CK(cudaMemcpyAsync(sl.raw_seq.p, seq + base, bytes, cudaMemcpyHostToDevice, s->copy));
+    if (qual) CK(cudaMemcpyAsync(sl.raw_qual.p, qual + base, bytes, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaMemcpyAsync(sl.raw_off.p, offsets, (R + 1) * 8, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaMemcpyAsync(sl.grp_off.p, s->h_grp_off.data(), (R + 1) * 8, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaEventRecord(sl.copied, s->copy));
+    CK(cudaStreamWaitEvent(s->compute, sl.copied, 0));
+    // offsets are relative to `seq`; the device copy starts at offsets[0]
+    CK(launch_pack(sl.raw_seq.p, qual ? sl.raw_qual.p : nullptr, base, sl.raw_off.p, R, encoding, s->p.phred_cutoff, 0,
+                   sl.bases.p, sl.inv.p, (s->mode & M_LOCAL) ? sl.qual.p : nullptr, sl.grp_off.p, sl.len.p, s->d_bad, s->compute));
+    ++s->launches;
+    BatchView v{};
+    v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = (s->mode & M_LOCAL) ? sl.qual.p : nullptr;
+    v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = R;
+    launch_on_view(s, v);
+    CK(cudaEventRecord(sl.done, s->compute));
+    sl.busy = true;
+    SPEQG_CATCH
+}
+
+int speqg_scan_submit_device(speqg_scan * s, const speqg_batch * db)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    check_batch(s, db);
+    if (db->n_reads == 0) return SPEQG_OK;
+    device_guard guard(s->device);
+    BatchView v{};
+    v.bases = db->bases; v.inv = db->inv; v.qual = (s->mode & M_LOCAL) ? db->qual : nullptr;
+    v.grp_off = db->grp_off; v.len = db->len; v.read_group = nullptr; v.n_reads = db->n_reads;
+    launch_on_view(s, v);
+    SPEQG_CATCH
+}
+
+int speqg_scan_sync(speqg_scan * s)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    device_guard guard(s->device);
+    CK(cudaStreamSynchronize(s->copy));
+    CK(cudaStreamSynchronize(s->compute));
+    for (auto & sl : s->slots) sl.busy = false;
+    SPEQG_CATCH
+}
+
+int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64, speqg_counts * counts)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    device_guard guard(s->device);
+    CK(cudaStreamSynchronize(s->copy));
+    CK(cudaStreamSynchronize(s->compute));
+    for (auto & sl : s->slots) sl.busy = false;
+    uint32_t V = s->idx->host.V;
+    unsigned long long bad = 0;
+    CK(cudaMemcpy(&bad, s->d_bad, 8, cudaMemcpyDeviceToHost));
+    if (bad) throw api_error(SPEQG_EINVAL, "parse_error: illegal (non-IUPAC) sequence character in a read");
+    if (unique_u64) CK(cudaMemcpy(unique_u64, s->d_unique, V * 8, cudaMemcpyDeviceToHost));
+    if (unique_f64) CK(cudaMemcpy(unique_f64, s->d_unique_w, V * 8, cudaMemcpyDeviceToHost));
+    if (counts)
+    {
+        unsigned long long sc[SC_COUNT];
+        CK(cudaMemcpy(sc, s->d_scalars, sizeof sc, cudaMemcpyDeviceToHost));
+        memset(counts, 0, sizeof *counts);
+        counts->total_kmers = sc[SC_TOTAL];
+        counts->ambiguous_reads = sc[SC_AMBIG];
+        counts->lookups = sc[SC_LOOKUPS];
+        counts->reads = sc[SC_READS];
+        counts->kernel_launches = s->launches;
+    }
+    SPEQG_CATCH
+}
+
+int speqg_scan_stats(speqg_scan * s, const speqg_batch * db, speqg_counts * counts)
+{
+    SPEQG_TRY
+    need(s && db && counts, "NULL argument");
+    memset(counts, 0, sizeof *counts);
+    if (db->n_reads == 0) return SPEQG_OK;
+    need(db->bases && db->inv && db->grp_off && db->len, "batch arrays must not be NULL");
+    device_guard guard(s->device);
+    unsigned long long * sc_dev = dev_alloc<unsigned long long>(SC_COUNT);
+    try
+    {
+        CK(cudaMemsetAsync(sc_dev, 0, SC_COUNT * 8, s->compute));
+        ScanArgs a = scan_args(s);
+        a.scalars = sc_dev;
+        BatchView v{};
+        v.bases = db->bases; v.inv = db->inv; v.qual = nullptr; v.grp_off = db->grp_off; v.len = db->len; v.n_reads = db->n_reads;
+        CK(launch_scan_direct(s->di->view, v, a, s->mode & M_PAIRED, 1, s->cfg_stats, s->compute));
+        unsigned long long sc[SC_COUNT];
+        CK(cudaMemcpyAsync(sc, sc_dev, sizeof sc, cudaMemcpyDeviceToHost, s->compute));
+        CK(cudaStreamSynchronize(s->compute));
+        counts->lookups = sc[SC_LOOKUPS];
+        counts->reads = sc[SC_READS];
+        counts->steps_executed = sc[SC_STEPS];
+        counts->kmers_hit = sc[SC_HIT];
+        counts->occurrences = sc[SC_OCC];
+        counts->occ_sectors = sc[SC_OCCSEC];
+    }
+    catch (...)
+    {
+        cudaFree(sc_dev);
+        throw;
+    }
+    cudaFree(sc_dev);
+    SPEQG_CATCH
+}
+
+void speqg_scan_close(speqg_scan * s)
+{
+    if (!s) return;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->copy);
+    cudaStreamSynchronize(s->compute);
+    scan_release(s);
+    if (prev >= 0) cudaSetDevice(prev);
+    delete s;
+}
+
+int speqg_batch_to_device(int device, const speqg_batch * hb, speqg_batch * db)
+{
+    SPEQG_TRY
+    need(hb && db, "NULL argument");
+    need(hb->bases && hb->inv && hb->grp_off && (hb->len || hb->n_reads == 0), "batch arrays must not be NULL");
+    device_guard guard(device);
+    memset(db, 0, sizeof *db);
+    uint64_t R = hb->n_reads, G = hb->n_groups32;
+    try
+    {
+        db->bases = dev_upload(hb->bases, G);
+        db->inv = dev_upload(hb->inv, G);
+        db->grp_off = dev_upload(hb->grp_off, R + 1);
+        db->len = dev_upload(hb->len, R);
+        if (hb->qual) db->qual = dev_upload(hb->qual, G * 32);
+    }
+    catch (...)
+    {
+        cudaFree(db->bases); cudaFree(db->inv); cudaFree(db->grp_off); cudaFree(db->len); cudaFree(db->qual);
+        memset(db, 0, sizeof *db);
+        throw;
+    }
+    db->n_reads = R;
+    db->n_groups32 = G;
+    SPEQG_CATCH
+}
+
+void speqg_batch_free_device(int device, speqg_batch * db)
+{
+    if (!db) return;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    cudaSetDevice(device);
+    cudaFree(db->bases); cudaFree(db->inv); cudaFree(db->grp_off); cudaFree(db->len); cudaFree(db->qual);
+    memset(db, 0, sizeof *db);
+    if (prev >= 0) cudaSetDevice(prev);
+}
+
+}   // extern "C"

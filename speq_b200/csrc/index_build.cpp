@@ -1,0 +1,231 @@
+// index_build.cpp -- host construction of the blocked FM index (see fm_layout.h for the layout).
+//
+// Reference behaviour reproduced (not its code): speq::fm::generate_fm_index (src/fm_indexer.cpp:8-52) hands
+// seqan3::fm_index the collection {scaffold_0, revcomp(scaffold_0), scaffold_1, ...}; seqan3 joins rank+1 symbols with
+// delimiter 6, reverses, and sdsl appends the 0 sentinel and builds SA/BWT/C
+// (deps/seqan3/include/seqan3/search/fm_index/fm_index.hpp:247-316).  locate() maps SA[i] back to a text with
+// loc = (n - k - 1) - SA[i] (fm_index_cursor.hpp:103-107,521-538).  Because an ACGT(N) query can never span a
+// delimiter, the text that owns occurrence i is the text that owns the FIRST symbol of suffix SA[i] in the reversed
+// text -- independent of k -- so the whole locate() walk collapses into the per-suffix group array built here.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "sais.hpp"
+#include "speq_internal.h"
+
+namespace speqb
+{
+static const uint8_t kCodeOfRank[5] = {0, 1, 2, 0, 3};   // dna5 rank -> 2-bit code (N coded 0, flagged in inv)
+
+static void pack_text_as_read(uint8_t const * ranks, uint64_t len, uint64_t * bases, uint32_t * inv)
+{
+    uint64_t groups = (len + 31) / 32;
+    for (uint64_t g = 0; g < groups; ++g)
+    {
+        uint64_t w = 0;
+        uint32_t m = 0;
+        uint64_t lim = std::min<uint64_t>(32, len - g * 32);
+        for (uint64_t j = 0; j < lim; ++j)
+        {
+            uint8_t r = ranks[g * 32 + j];
+            w |= uint64_t(kCodeOfRank[r]) << (2 * j);
+            if (r == 3) m |= 1u << j;
+        }
+        bases[g] = w;
+        inv[g] = m;
+    }
+}
+
+void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint32_t S, int32_t const * group_of_text,
+                      uint32_t V, uint32_t flags, HostIndex & h)
+{
+    if (S == 0) throw api_error(SPEQG_EINVAL, "The text that is indexed cannot be empty.");
+    if (V == 0) throw api_error(SPEQG_EINVAL, "n_groups must be > 0");
+    uint64_t text_size = 0;
+    bool all_empty = true;
+    for (uint32_t i = 0; i < S; ++i)
+    {
+        if (lens[i]) all_empty = false;
+        text_size += 1 + lens[i];
+        if (group_of_text[i] < 0 || (uint32_t)group_of_text[i] >= V)
+            throw api_error(SPEQG_EINVAL, "text " + std::to_string(i) + " has group " + std::to_string(group_of_text[i]) +
+                                              " outside [0, n_groups): every scaffold must be assigned to a variant "
+                                              "(the reference indexes vectors with -1 for unassigned scaffolds)");
+    }
+    if (all_empty) throw api_error(SPEQG_EINVAL, "A text collection that only contains empty texts cannot be indexed.");
+    uint64_t m = text_size - (S > 1 ? 1 : 0);   // fm_index.hpp:283
+    uint64_t n = m + 1;                          // + sentinel
+    if (n >= (uint64_t(1) << 31)) throw api_error(SPEQG_EINVAL, "collection too large: indexed text must be < 2^31 symbols");
+
+    h = HostIndex{};
+    h.n = n; h.S = S; h.V = V;
+    h.group_of_text.assign(group_of_text, group_of_text + S);
+
+    // T = reverse(join(rank+1, 6)) + {0}; owner[p] = group owning T[p] (kNoGroup for delimiter / sentinel)
+    std::vector<uint8_t> T(n);
+    std::vector<uint32_t> owner(n, kNoGroup);
+    {
+        uint64_t f = 0;   // position in the forward concatenation; T position = m-1-f
+        for (uint32_t i = 0; i < S; ++i)
+        {
+            uint8_t const * t = texts[i];
+            uint32_t g = (uint32_t)group_of_text[i];
+            for (uint64_t j = 0; j < lens[i]; ++j, ++f)
+            {
+                if (t[j] > 4) throw api_error(SPEQG_EINVAL, "text symbols must be dna5 ranks 0..4");
+                T[m - 1 - f] = (uint8_t)(t[j] + 1);
+                owner[m - 1 - f] = g;
+            }
+            if (i + 1 < S || S == 1) { T[m - 1 - f] = (uint8_t)kSymDelim; ++f; }   // fm_index.hpp:302,310-311
+        }
+        T[m] = 0;
+    }
+
+    std::vector<int32_t> SA(n);
+    suffix_array(T.data(), SA.data(), (int32_t)n, 7);
+
+    // C[] (deps/seqan3/include/seqan3/search/fm_index/detail/csa_alphabet_strategy.hpp:84-117)
+    uint64_t cnt[8] = {0};
+    for (uint64_t i = 0; i < n; ++i) ++cnt[T[i]];
+    h.C[0] = 0;
+    for (int c = 1; c < 8; ++c) h.C[c] = h.C[c - 1] + cnt[c - 1];
+
+    // BWT -> blocks, exceptions.  bwt[i] = T[SA[i]-1], wrapping (sdsl construct_bwt.hpp:35-73)
+    uint64_t nblocks = n / kBlockSyms + 1;
+    h.blocks.assign(nblocks * 8, 0);
+    static const int8_t code_of_sym[7] = {-1, 0, 1, 2, -1, 3, -1};
+    uint32_t run[4] = {0, 0, 0, 0};
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        uint64_t b = i / kBlockSyms, j = i % kBlockSyms;
+        uint32_t * blk = &h.blocks[b * 8];
+        if (j == 0) { blk[0] |= run[0]; blk[1] = run[1]; blk[2] = run[2]; blk[3] = run[3]; }
+        uint8_t sym = T[SA[i] ? SA[i] - 1 : n - 1];
+        int8_t c2 = code_of_sym[sym];
+        if (c2 < 0)
+        {
+            blk[0] |= kExcFlag;
+            h.exc_pos.push_back((uint32_t)i);
+            if (sym == kSymN) h.n_pos.push_back((uint32_t)i);
+            c2 = 0;
+        }
+        else
+            ++run[c2];
+        blk[4 + j / 32] |= uint32_t(c2 & 1) << (j % 32);
+        blk[6 + j / 32] |= uint32_t((c2 >> 1) & 1) << (j % 32);
+    }
+    if (n % kBlockSyms == 0)
+    {
+        uint32_t * blk = &h.blocks[(nblocks - 1) * 8];
+        blk[0] = run[0]; blk[1] = run[1]; blk[2] = run[2]; blk[3] = run[3];
+    }
+
+    // group runs over SA order
+    h.gr.resize(n);
+    for (uint64_t i = 0; i < n; ++i) h.gr[i].group = owner[SA[i]];
+    h.gr[n - 1].run_end = (uint32_t)(n - 1);
+    for (uint64_t i = n - 1; i-- > 0;)
+        h.gr[i].run_end = (h.gr[i].group == h.gr[i + 1].group) ? h.gr[i + 1].run_end : (uint32_t)i;
+
+    // capped LCP array (Kasai et al. 2001, with the cap folded in: lcp[rank[i+1]] >= lcp[rank[i]] - 1 also holds for
+    // min(cap, lcp)).  The sentinel is unique, so the symbol comparison stops before either suffix runs off the text.
+    {
+        std::vector<int32_t> rank(n);
+        for (uint64_t i = 0; i < n; ++i) rank[SA[i]] = (int32_t)i;
+        h.lcp.assign(((n + 7) / 8) * 8 + 16, 0);
+        uint32_t hh = 0;
+        for (uint64_t i = 0; i < n; ++i)
+        {
+            int32_t r = rank[i];
+            if (r == 0) { hh = 0; continue; }
+            uint64_t j = (uint64_t)SA[r - 1];
+            while (hh < kLcpCap && T[i + hh] == T[j + hh]) ++hh;
+            h.lcp[r] = (uint8_t)hh;
+            if (hh) --hh;
+        }
+    }
+
+    if (flags & SPEQG_BUILD_KEEP_SA)
+    {
+        h.sa.resize(n);
+        for (uint64_t i = 0; i < n; ++i) h.sa[i] = (uint32_t)SA[i];
+    }
+
+    // texts as a packed read batch for the back-check
+    h.t_grp_off.resize(S + 1);
+    h.t_len.resize(S);
+    uint64_t g = 0;
+    for (uint32_t i = 0; i < S; ++i) { h.t_grp_off[i] = g; h.t_len[i] = (uint32_t)lens[i]; g += (lens[i] + 31) / 32; }
+    h.t_grp_off[S] = g;
+    for (uint32_t i = 0; i < S; ++i)
+        if (lens[i] >= (uint64_t(1) << 32)) throw api_error(SPEQG_EINVAL, "text longer than 2^32");
+    h.t_bases.assign(g + 1, 0);
+    h.t_inv.assign(g + 1, 0);
+    for (uint32_t i = 0; i < S; ++i) pack_text_as_read(texts[i], lens[i], &h.t_bases[h.t_grp_off[i]], &h.t_inv[h.t_grp_off[i]]);
+}
+
+// ---- cache file: own binary payload (the reference's .idx is a cereal+sdsl archive; byte compatibility is a later row)
+static const char kMagic[8] = {'S', 'P', 'E', 'Q', 'B', '2', '0', '1'};
+
+template <class T> static void wr(FILE * f, T const & v)
+{
+    if (fwrite(&v, sizeof(T), 1, f) != 1) throw api_error(SPEQG_EIO, "short write");
+}
+template <class T> static void wrv(FILE * f, std::vector<T> const & v)
+{
+    uint64_t n = v.size();
+    wr(f, n);
+    if (n && fwrite(v.data(), sizeof(T), n, f) != n) throw api_error(SPEQG_EIO, "short write");
+}
+template <class T> static void rd(FILE * f, T & v)
+{
+    if (fread(&v, sizeof(T), 1, f) != 1) throw api_error(SPEQG_EIO, "short read (truncated index payload)");
+}
+template <class T> static void rdv(FILE * f, std::vector<T> & v)
+{
+    uint64_t n;
+    rd(f, n);
+    if (n > (uint64_t(1) << 36)) throw api_error(SPEQG_EIO, "corrupt index payload");
+    v.resize(n);
+    if (n && fread(v.data(), sizeof(T), n, f) != n) throw api_error(SPEQG_EIO, "short read (truncated index payload)");
+}
+
+void save_host_index(HostIndex const & h, std::string const & path)
+{
+    FILE * f = fopen(path.c_str(), "wb");
+    if (!f) throw api_error(SPEQG_EIO, "cannot open " + path + " for writing");
+    try
+    {
+        if (fwrite(kMagic, 1, 8, f) != 8) throw api_error(SPEQG_EIO, "short write");
+        wr(f, h.n); wr(f, h.S); wr(f, h.V);
+        for (int c = 0; c < 8; ++c) wr(f, h.C[c]);
+        wrv(f, h.blocks); wrv(f, h.gr); wrv(f, h.lcp); wrv(f, h.exc_pos); wrv(f, h.n_pos); wrv(f, h.group_of_text);
+        wrv(f, h.t_bases); wrv(f, h.t_inv); wrv(f, h.t_grp_off); wrv(f, h.t_len); wrv(f, h.sa);
+    }
+    catch (...) { fclose(f); throw; }
+    if (fclose(f) != 0) throw api_error(SPEQG_EIO, "cannot close " + path);
+}
+
+void load_host_index(std::string const & path, HostIndex & h)
+{
+    FILE * f = fopen(path.c_str(), "rb");
+    if (!f) throw api_error(SPEQG_EIO, "cannot open " + path);
+    try
+    {
+        char mg[8];
+        if (fread(mg, 1, 8, f) != 8 || memcmp(mg, kMagic, 8) != 0) throw api_error(SPEQG_EIO, path + " is not a speq-b200 index payload");
+        h = HostIndex{};
+        rd(f, h.n); rd(f, h.S); rd(f, h.V);
+        for (int c = 0; c < 8; ++c) rd(f, h.C[c]);
+        rdv(f, h.blocks); rdv(f, h.gr); rdv(f, h.lcp); rdv(f, h.exc_pos); rdv(f, h.n_pos); rdv(f, h.group_of_text);
+        rdv(f, h.t_bases); rdv(f, h.t_inv); rdv(f, h.t_grp_off); rdv(f, h.t_len); rdv(f, h.sa);
+        if (h.blocks.size() != (h.n / kBlockSyms + 1) * 8 || h.gr.size() != h.n || h.group_of_text.size() != h.S ||
+            h.lcp.size() != ((h.n + 7) / 8) * 8 + 16)
+            throw api_error(SPEQG_EIO, "inconsistent index payload");
+    }
+    catch (...) { fclose(f); throw; }
+    fclose(f);
+}
+}   // namespace speqb

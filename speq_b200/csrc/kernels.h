@@ -1,0 +1,67 @@
+// kernels.h -- launchers of the sm_100a kernels (kernels.cu), called by the C ABI (capi.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "fm_layout.h"
+
+namespace speqb
+{
+enum : int
+{
+    M_LOCAL = 1,       // fp64 phred-weighted unique tallies
+    M_RECORD = 2,      // record per-k-mer multiplicities for the refinement
+    M_BACKCHECK = 4,   // reads are the index's own texts; N is searched; tallies are unique_ref/total_ref
+    M_PAIRED = 8       // reads 2i, 2i+1 share one ambiguity state
+};
+
+// indices into the u64 scalar counter block
+enum : int { SC_TOTAL = 0, SC_AMBIG = 1, SC_LOOKUPS = 2, SC_STEPS = 3, SC_HIT = 4, SC_OCC = 5, SC_OCCSEC = 6, SC_READS = 7, SC_COUNT = 8 };
+
+// One unit of lane work: windows [start, start + nwin) of read `read` (positions [start, start + nwin + k - 1)).
+struct Segment
+{
+    uint32_t read;
+    uint32_t start;
+    uint32_t nwin;
+};
+
+struct ScanArgs
+{
+    uint32_t k;
+    uint32_t V;
+    unsigned long long * unique;      // [V] (back-check: unique_ref)
+    unsigned long long * total_g;     // [V] back-check: total_ref
+    double * unique_w;                // [V] local mode
+    unsigned long long * scalars;     // [SC_COUNT]
+    unsigned long long * mult;        // [n] multiplicity of the valid k-mer windows whose interval starts at lb
+    const double * qden;              // [42] 1 - 1/pow(10, q/10), host libm values   (local mode)
+    const Segment * segs;             // optional segment table (back-check); null: one segment per read / pair
+    uint64_t n_segs;
+};
+
+struct LaunchCfg
+{
+    int grid;     // CTAs (multiple of the SM count)
+    int block;    // threads per CTA
+};
+
+// rolling-window scan (the product kernel)
+cudaError_t launch_scan_roll(DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg, cudaStream_t st);
+// from-the-root search of every window, one warp per read.  stats != 0: only the reference-semantics work counters
+// (SC_STEPS, SC_HIT, SC_OCC, SC_OCCSEC, SC_LOOKUPS) are produced; else the same tallies as launch_scan_roll (global mode).
+cudaError_t launch_scan_direct(DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, int stats, LaunchCfg cfg, cudaStream_t st);
+cudaError_t scan_launch_cfg(int mode, int direct, uint32_t V, LaunchCfg * cfg);   // occupancy-sized persistent grid
+size_t scan_smem_bytes(uint32_t V);
+
+// refinement estimate: tkpg[g] = sum over recorded k-mers of mult * a[g] / sum(a), a[g] = h[g] * percent[g] / group_counts[g]
+cudaError_t launch_refine(DevIndex const & ix, uint32_t k, const unsigned long long * mult, const double * percent,
+                          const int32_t * group_counts, uint32_t V, double * partial, int grid, int block, cudaStream_t st);
+cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V, double * tkpg, cudaStream_t st);
+// device packer: raw reads (ASCII or dna5 ranks) already in device memory -> packed batch (grp_off / len precomputed).
+// *bad is set to 1 when an illegal sequence character is met.
+// seq / qual hold the bytes [off0, offsets[n_reads]) of the caller's arrays (offsets are relative to the caller's).
+cudaError_t launch_pack(const uint8_t * seq, const uint8_t * qual, uint64_t off0, const uint64_t * offsets, uint64_t n_reads,
+                        int encoding, uint32_t phred_cutoff, int n_only, uint64_t * bases, uint32_t * inv, uint8_t * qual_out,
+                        const uint64_t * grp_off, uint32_t * len, unsigned long long * bad, cudaStream_t st);
+cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
+}   // namespace speqb
