@@ -1,0 +1,215 @@
+"""GPU tier (B200): the CUDA path through the C ABI vs the golden fixtures, vs the CPU oracle on seeded inputs, and
+size-independent properties at BASELINE.json's shapes.  Integer tallies are bit-exact; fp64 results within 1e-12
+relative (the tolerance BASELINE.json:north_star states)."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+import helpers
+from speq_b200 import capi, driver, engine, synth
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+def _reads(seqs, quals):
+    seq, q, offs = helpers.flat_reads(seqs, quals)
+    return driver.Reads(seq, q, offs)
+
+
+def _compare(out: dict, exp: dict, V: int):
+    assert [int(x) for x in out["unique_ref"]] == exp["unique_ref"]
+    assert [int(x) for x in out["total_ref"]] == exp["total_ref"]
+    assert out["total_kmers"] == exp["total_kmers"]
+    assert out["ambiguous"] == exp["ambiguous"]
+    assert out["lookups"] == exp["lookups"]
+    assert out["n"] == exp["n"]
+    if exp["mode"] == "global":
+        assert [int(x) for x in out["unique"]] == exp["unique"]
+        assert list(out["unique_totals"]) == exp["unique_totals"]        # one division per entry: bit-exact
+        assert list(out["percent_initial"]) == exp["percent_initial"]
+    else:
+        assert helpers.rel_close(out["unique_w"], exp["unique_w"], TOL)
+        assert helpers.rel_close(out["percent_initial"], exp["percent_initial"], TOL)
+    assert out["iterations"] == exp["iterations"]
+    assert helpers.rel_close(out["percent_final"], exp["percent_final"], TOL)
+    for a, b in zip(out["iter_tkpg"], exp["iter_tkpg"]):
+        assert helpers.rel_close(a, b, 1e-11)
+
+
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("raw", [True, False])
+def test_golden(lib, name, raw):
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
+                         fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], raw=raw, batch_reads=64)
+    _compare(out, exp, len(counts))
+
+
+@pytest.mark.parametrize("name", ["global_single", "global_paired", "refs_with_n", "short_k"])
+def test_golden_direct_algorithm(lib, name):
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], fixed_accuracy=run["fixed_accuracy"],
+                         paired=run["paired"], algorithm=capi.ALGO_DIRECT)
+    _compare(out, exp, len(counts))
+
+
+def test_reference_work_counters(lib):
+    """speqg_scan_stats reproduces the oracle's reference-semantics counters (steps incl. the failing one, hits, occ)."""
+    fx = helpers.load_golden("global_single")
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    idx = engine.Index.from_scaffolds(scaff, gs, len(counts))
+    seq, q, offs = helpers.flat_reads(seqs, quals)
+    pb = engine.pack_reads(seq, q, offs, n_only=True)
+    db = engine.DeviceBatch(0, pb)
+    sc = engine.Scan(idx, k=run["k"])
+    st = sc.stats(db)
+    assert st["lookups"] == exp["lookups"]
+    assert st["steps_executed"] == exp["steps_executed"]
+    assert st["kmers_hit"] == exp["kmers_hit"]
+    assert st["occ"] == exp["occ"]
+    assert st["occ_sectors"] == exp["occ_sectors"]
+    sc.close(); db.close(); idx.close()
+
+
+@pytest.mark.parametrize("mode", ["global", "local", "global_paired"])
+def test_vs_oracle_c1_like(lib, oracle_bin, tmp_path, mode):
+    """C1-shaped input (2 variants x 3 isolates x 30 kb, 150 bp reads, k=21) at a read count the oracle finishes in seconds."""
+    sh = synth.CONFIGS["C1"]
+    refs = synth.make_refs(sh, synth.SEED0 + 1)
+    R = 6000
+    seq, qual = synth.make_reads(sh, refs, R, synth.SEED0 + 101, local_quals=(mode == "local"), n_rate=0.001)
+    seq, qual = seq.numpy(), qual.numpy()
+    synth.write_fasta(str(tmp_path / "refs.fa"), refs)
+    synth.write_groups(str(tmp_path / "groups.txt"), sh)
+    paired = mode.endswith("paired")
+    if paired:
+        synth.write_fastq(str(tmp_path / "r1.fq"), seq[0::2], qual[0::2])
+        synth.write_fastq(str(tmp_path / "r2.fq"), seq[1::2], qual[1::2])
+    else:
+        synth.write_fastq(str(tmp_path / "r1.fq"), seq, qual)
+    acc = 0.0 if mode == "local" else sh.accuracy
+    cutoff = 19 if mode == "local" else 30
+    exp = helpers.run_oracle(oracle_bin, tmp_path / "refs.fa", tmp_path / "groups.txt", tmp_path / "r1.fq",
+                             reads2=(tmp_path / "r2.fq") if paired else None, k=sh.k, fixed_accuracy=acc, phred_cutoff=cutoff, threads=8)
+    offs = (np.arange(R + 1, dtype=np.uint64) * sh.L)
+    out = driver.run_all(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), [sh.I] * sh.V,
+                         driver.Reads(seq.reshape(-1), qual.reshape(-1), offs), k=sh.k, phred_cutoff=cutoff, fixed_accuracy=acc,
+                         paired=paired, batch_reads=2048)
+    _compare(out, exp, sh.V)
+
+
+def test_edge_cases(lib):
+    scaff = [engine.ascii_to_ranks("ACGTTGCAAGGCTTAACCGGTTAGCATCGA"), engine.ascii_to_ranks("ACGTTGCATGGCTTAACCGGTAAGCATCGA")]
+    idx = engine.Index.from_scaffolds(scaff, [0, 1], 2)
+    sc = engine.Scan(idx, k=8)
+    # no reads at all; then empty reads, reads shorter than k, read exactly k long, all-N read
+    r = sc.finish()
+    assert r.total_kmers == 0 and r.lookups == 0 and r.reads == 0
+    seqs = ["", "ACG", "ACGTTGCA", "NNNNNNNNNNNN", "ACGTTGCANGGCTTAACC"]
+    quals = ["", "III", "IIIIIIII", "IIIIIIIIIIII", "IIIIIIIIIIIIIIIIII"]
+    seq, q, offs = helpers.flat_reads(seqs, quals)
+    sc.submit_raw(seq, q, offs, len(seqs))
+    r = sc.finish()
+    assert r.reads == 5 and r.lookups == 0 + 0 + 1 + 5 + 11
+    assert r.total_kmers == 1 + 0 + (1 + 2)       # windows without N: ACGTTGCA | [0..8) and [9..17),[10..18) of the last read
+    # ACGTTGCA occurs in both variants -> not unique; GGCTTAAC / GCTTAACC occur in both as well
+    assert list(r.unique) == [0, 0]
+    sc.reset()
+    seq, q, offs = helpers.flat_reads(["AAGGCTTAACCGGTTAGC"], ["I" * 18])
+    sc.submit_raw(seq, q, offs, 1)
+    r = sc.finish()
+    assert r.total_kmers == 11 and int(r.unique[0]) > 0 and int(r.unique[1]) == 0
+    # illegal letter -> parse_error surfaced at finish (device packer)
+    sc.reset()
+    seq, q, offs = helpers.flat_reads(["ACGTTGCAXGGCTTAACC"], ["I" * 18])
+    sc.submit_raw(seq, q, offs, 1)
+    with pytest.raises(capi.SpeqError) as ei:
+        sc.finish()
+    assert "parse_error" in ei.value.message
+    # paired mode needs an even number of reads; local mode needs qualities
+    sp = engine.Scan(idx, k=8, paired=True)
+    with pytest.raises(capi.SpeqError):
+        sp.submit_raw(seq, q, offs, 1)
+    sl = engine.Scan(idx, k=8, mode=capi.MODE_LOCAL)
+    with pytest.raises(capi.SpeqError):
+        sl.submit_raw(seq, None, offs, 1)
+    with pytest.raises(capi.SpeqError):
+        engine.Scan(idx, k=0)
+    with pytest.raises(capi.SpeqError):
+        engine.Scan(idx, k=128)
+    with pytest.raises(capi.SpeqError):
+        sc.refine(np.ones(2), np.ones(2, np.int32))     # opened without record_multiplicity -> ESTATE
+    for s in (sc, sp, sl):
+        s.close()
+    idx.close()
+
+
+def _scan_tallies(idx, k, seq, qual, offs, **kw):
+    sc = engine.Scan(idx, k=k, **kw)
+    sc.submit_raw(seq, qual, offs, offs.size - 1)
+    r = sc.finish()
+    sc.close()
+    return r
+
+
+@pytest.mark.parametrize("cfg,R", [("C2", 400_000), ("C3", 200_000), ("C5", 300)])
+def test_properties_at_config_shapes(lib, cfg, R):
+    """Size-independent properties on the full-size indexes of BASELINE.json's configs (read count bounded for test time):
+    rolling == direct; shard additivity; lookups = R (L-k+1); error-free reads from a scaffold always hit."""
+    import torch
+    sh = synth.CONFIGS[cfg]
+    dev = "cuda"
+    refs = synth.make_refs(sh, synth.SEED0 + int(cfg[1]), device=dev)
+    idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V)
+    seq, qual = synth.make_reads(sh, refs, R, 77, n_rate=0.0005)
+    seq, qual = seq.cpu().numpy().reshape(-1), qual.cpu().numpy().reshape(-1)
+    offs = np.arange(R + 1, dtype=np.uint64) * sh.L
+    a = _scan_tallies(idx, sh.k, seq, qual, offs)
+    b = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_DIRECT)
+    assert a.lookups == R * sh.windows_per_read == b.lookups
+    assert a.total_kmers == b.total_kmers and a.ambiguous == b.ambiguous
+    assert np.array_equal(a.unique, b.unique)
+    assert a.unique.sum() > 0
+    h = R // 2
+    p1 = _scan_tallies(idx, sh.k, seq, qual, offs[:h + 1])
+    p2 = _scan_tallies(idx, sh.k, seq, qual, offs[h:])
+    assert np.array_equal(p1.unique + p2.unique, a.unique)
+    assert p1.total_kmers + p2.total_kmers == a.total_kmers and p1.ambiguous + p2.ambiguous == a.ambiguous
+    # error-free reads: every window occurs, so total == lookups and refine's recorded windows == total
+    import dataclasses
+    sh0 = dataclasses.replace(sh, e=0.0)
+    n0 = max(64, R // 8)
+    s0, q0 = synth.make_reads(sh0, refs, n0, 78)
+    sc = engine.Scan(idx, k=sh.k, record=True)
+    sc.submit_raw(s0.cpu().numpy().reshape(-1), q0.cpu().numpy().reshape(-1), np.arange(n0 + 1, dtype=np.uint64) * sh.L, n0)
+    r0 = sc.finish()
+    assert r0.total_kmers == r0.lookups == n0 * sh.windows_per_read
+    # refinement estimate conserves mass: sum_g tkpg[g] == number of recorded (hit) windows
+    tk = sc.refine(np.full(sh.V, 100.0 / sh.V), np.full(sh.V, sh.I, np.int32))
+    assert abs(tk.sum() - r0.total_kmers) <= 1e-9 * r0.total_kmers
+    sc.close()
+    idx.close()
+    del refs
+    torch.cuda.empty_cache()
+
+
+def test_backcheck_idempotent_and_index_roundtrip(lib, tmp_path):
+    sh = synth.CONFIGS["C1"]
+    refs = synth.make_refs(sh, 5)
+    idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V)
+    u1, t1 = engine.backcheck(idx, sh.k)
+    u2, t2 = engine.backcheck(idx, sh.k)
+    assert np.array_equal(u1, u2) and np.array_equal(t1, t2)
+    assert list(t1) == [2 * sh.I * (sh.G - sh.k + 1)] * sh.V
+    idx.save(str(tmp_path / "c1.idx"))
+    idx2 = engine.Index.load(str(tmp_path / "c1.idx"))
+    u3, t3 = engine.backcheck(idx2, sh.k)
+    assert np.array_equal(u1, u3) and np.array_equal(t1, t3)
+    idx.close(); idx2.close()

@@ -1,0 +1,175 @@
+"""CPU tier: the C ABI loads and exports every declared symbol; host packer; host index builder vs the oracle's
+SA/BWT/C; the kernels' per-lane arithmetic (scan_core.h, compiled for the host by tests/sim) vs the golden fixtures;
+compute entry points fail loudly without a CUDA device."""
+from __future__ import annotations
+
+import ctypes as C
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import helpers
+from speq_b200 import capi, engine
+
+
+def _have_gpu():
+    import torch
+    return torch.cuda.is_available()
+
+
+def test_header_symbols_exported(lib):
+    hdr = (helpers.ROOT / "include" / "speq_cuda.h").read_text()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(speqg_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 25
+    assert declared == set(capi.SIGNATURES), declared ^ set(capi.SIGNATURES)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.speqg_abi_version() == 1
+    # the product library must not contain the oracle
+    nm = subprocess.run(["nm", "-D", "--defined-only", str(capi.LIB_PATH)], capture_output=True, text=True).stdout
+    assert "oracle" not in nm.lower()
+
+
+def test_no_cpu_fallback(lib):
+    if _have_gpu():
+        pytest.skip("a CUDA device is present")
+    idx = engine.Index.from_scaffolds([engine.ascii_to_ranks("ACGTACGTTGCA")], [0], 1)
+    with pytest.raises(capi.SpeqError) as ei:
+        engine.Scan(idx, k=3)
+    assert ei.value.code == capi.ECUDA
+    with pytest.raises(capi.SpeqError) as ei:
+        engine.backcheck(idx, 3)
+    assert ei.value.code == capi.ECUDA
+
+
+def test_index_build_errors(lib):
+    with pytest.raises(capi.SpeqError) as ei:
+        engine.Index.from_texts([], [], 1)
+    assert "cannot be empty" in ei.value.message          # seqan3 fm_index.hpp:240
+    with pytest.raises(capi.SpeqError) as ei:
+        engine.Index.from_texts([np.zeros(0, np.uint8)] * 2, [0, 0], 1)
+    assert "only contains empty texts" in ei.value.message  # fm_index.hpp:257
+    with pytest.raises(capi.SpeqError):
+        engine.Index.from_texts([np.array([0, 1, 2], np.uint8)], [-1], 1)
+    with pytest.raises(capi.SpeqError):
+        engine.Index.from_texts([np.array([0, 1, 7], np.uint8)], [0], 1)
+
+
+def test_pack_reads_matches_numpy(lib):
+    rng = np.random.default_rng(3)
+    letters = np.frombuffer(b"ACGTUNRYSWKMBDHVacgtunryswkmbdhv", np.uint8)
+    lens = [0, 1, 31, 32, 33, 64, 150, 7]
+    seqs = [bytes(rng.choice(letters, n)).decode() for n in lens]
+    quals = ["".join(chr(int(x)) for x in rng.integers(33, 90, n)) for n in lens]
+    seq, q, offs = helpers.flat_reads(seqs, quals)
+    cutoff = 30
+    pb = engine.pack_reads(seq, q, offs, phred_cutoff=cutoff, with_qual=True, threads=2)
+    assert pb.n_reads == len(lens) and pb.n_groups32 == sum((n + 31) // 32 for n in lens)
+    code = {"A": 0, "C": 1, "G": 2, "T": 3, "U": 3}
+    for i, (s, ql) in enumerate(zip(seqs, quals)):
+        g0 = int(pb.grp_off[i])
+        assert int(pb.len[i]) == len(s)
+        for j, ch in enumerate(s):
+            c = (int(pb.bases[g0 + j // 32]) >> (2 * (j % 32))) & 3
+            iv = (int(pb.inv[g0 + j // 32]) >> (j % 32)) & 1
+            ph = min(max(ord(ql[j]) - 33, 0), 41)
+            isn = ch.upper() not in code
+            assert c == (0 if isn else code[ch.upper()])
+            assert iv == int(isn or not (ph > cutoff))
+            assert int(pb.qual[(g0 + j // 32) * 32 + j % 32]) == ph
+    with pytest.raises(capi.SpeqError) as ei:
+        s2, q2, o2 = helpers.flat_reads(["ACGTXACGT"], ["IIIIIIIII"])
+        engine.pack_reads(s2, q2, o2)
+    assert "parse_error" in ei.value.message
+
+
+def test_index_matches_oracle_dump(lib, oracle_bin, tmp_path):
+    case = helpers.random_case(21, V=3, I=2, G=300, R=1, n_rate_ref=0.01)
+    helpers.write_fasta(tmp_path / "refs.fa", case["scaffolds"])
+    subprocess.run([str(oracle_bin), "dump", str(tmp_path / "refs.fa"), str(tmp_path / "dump.bin")], check=True)
+    raw = (tmp_path / "dump.bin").read_bytes()
+    n = int(np.frombuffer(raw[:8], np.uint64)[0])
+    Cc = np.frombuffer(raw[8:72], np.uint64)
+    rec = np.frombuffer(raw[72:], np.dtype([("sa", "<u4"), ("bwt", "u1")]))
+    idx = engine.Index.from_scaffolds([engine.ascii_to_ranks(s) for s in case["scaffolds"]], case["group_scaffolds"], case["V"], keep_sa=True)
+    assert idx.n == n and idx.C == [int(x) for x in Cc]
+    ex = idx.export(sa=True)
+    assert np.array_equal(ex["sa"], rec["sa"])
+    bwt = rec["bwt"].copy()
+    bwt[(bwt == 0) | (bwt == 6)] = 0xFF
+    assert np.array_equal(ex["bwt"], bwt)
+    # lcp against a direct comparison of suffixes of the reversed text
+    T = np.zeros(n, np.uint8)
+    f = 0
+    texts = []
+    for s in case["scaffolds"]:
+        r = engine.ascii_to_ranks(s)
+        texts += [r, engine.revcomp_ranks(r)]
+    m = n - 1
+    for i, t in enumerate(texts):
+        T[m - 1 - f - np.arange(t.size)] = t + 1
+        f += t.size
+        if i + 1 < len(texts):
+            T[m - 1 - f] = 6
+            f += 1
+    sa = ex["sa"].astype(np.int64)
+    for i in range(1, n, 17):
+        a, b, h = sa[i - 1], sa[i], 0
+        while h < 127 and T[a + h] == T[b + h]:
+            h += 1
+        assert ex["lcp"][i] == h
+    # save / load round trip
+    idx.save(str(tmp_path / "x.idx"))
+    idx2 = engine.Index.load(str(tmp_path / "x.idx"))
+    ex2 = idx2.export(sa=True)
+    for key in ex:
+        assert np.array_equal(ex[key], ex2[key])
+    with pytest.raises(capi.SpeqError) as ei:
+        (tmp_path / "bad.idx").write_bytes(b"not an index")
+        engine.Index.load(str(tmp_path / "bad.idx"))
+    assert ei.value.code == capi.EIO
+
+
+def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck=False, want_mult=False):
+    texts, grp = [], []
+    for j, s in enumerate(scaff):
+        texts += [np.ascontiguousarray(s), np.ascontiguousarray(engine.revcomp_ranks(s))]
+        grp += [int(gs[j])] * 2
+    S = len(texts)
+    ptrs = (C.c_void_p * S)(*[t.ctypes.data if t.size else None for t in texts])
+    lens = np.array([t.size for t in texts], np.uint64)
+    grp = np.array(grp, np.int32)
+    seq, q, offs = helpers.flat_reads(seqs, quals)
+    pb = engine.pack_reads(seq, q, offs, phred_cutoff=cutoff)
+    out = np.zeros(2 * V + 4, np.uint64)
+    n = int(lens.sum()) + S
+    mult = np.zeros(n + 1, np.uint64) if want_mult else None
+    sim.sim_scan.restype = C.c_int
+    rc = sim.sim_scan(ptrs, C.c_void_p(lens.ctypes.data), C.c_uint32(S), C.c_void_p(grp.ctypes.data), C.c_uint32(V),
+                      C.c_void_p(pb.bases.ctypes.data), C.c_void_p(pb.inv.ctypes.data), C.c_void_p(pb.grp_off.ctypes.data),
+                      C.c_void_p(pb.len.ctypes.data), C.c_uint64(pb.n_reads), C.c_uint32(k), C.c_int(int(paired)), C.c_int(algo),
+                      C.c_int(int(backcheck)), C.c_void_p(out.ctypes.data), C.c_void_p(mult.ctypes.data if want_mult else None))
+    assert rc == 0
+    return out, mult
+
+
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("algo", [0, 1])
+def test_lane_arithmetic_vs_golden(lib, sim, name, algo):
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    V = len(counts)
+    out, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], algo)
+    if exp["mode"] == "global":
+        assert list(out[:V]) == exp["unique"]
+    assert int(out[V]) == exp["total_kmers"]
+    assert int(out[V + 1]) == exp["ambiguous"]
+    assert int(out[V + 2]) == exp["lookups"]
+    if algo == 0:
+        bc, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], 30, False, 0, backcheck=True)
+        assert list(bc[:V]) == exp["unique_ref"]
+        assert list(bc[V:2 * V]) == exp["total_ref"]
