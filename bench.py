@@ -263,7 +263,8 @@ def main() -> None:
     t_pack = time.perf_counter() - t0
     del pb
 
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream: the scan handle launches on it and the events time it
+    torch.cuda.set_stream(stream)
     algo = capi.ALGO_ROLLING if args.algorithm == "rolling" else capi.ALGO_DIRECT
     scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=algo, device=local_rank, stream=stream.cuda_stream)
     V = sh.V
