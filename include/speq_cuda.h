@@ -67,6 +67,10 @@ int speqg_index_build(const uint8_t * const * texts, const uint64_t * lens, uint
                       const int32_t * group_of_text, uint32_t n_groups, uint32_t flags, speqg_index ** out);
 int speqg_index_save(const speqg_index * idx, const char * path);
 int speqg_index_load(const char * path, speqg_index ** out);
+/* same, with the payload starting `offset` bytes into an existing file (the `speq` binary keeps the reference's .idx
+ * metadata -- reference path, mtimes, group names / scaffolds / counts, src/fm_indexer.cpp:39-50 -- in front of it). */
+int speqg_index_save_at(const speqg_index * idx, const char * path, uint64_t offset);
+int speqg_index_load_at(const char * path, uint64_t offset, speqg_index ** out);
 int speqg_index_get_info(const speqg_index * idx, speqg_index_info * info);
 /* White-box export for parity tests: any pointer may be NULL (n entries each).  sa needs SPEQG_BUILD_KEEP_SA.  bwt holds
  * text symbols (A1 C2 G3 N4 T5; delimiter and sentinel both 0xFF); lcp is capped at 127. */
@@ -152,6 +156,8 @@ int speqg_scan_submit_raw(speqg_scan * scan, const uint8_t * seq, const uint8_t 
 /* batch whose arrays already live in device memory of the scan's device (pointers are device pointers). */
 int speqg_scan_submit_device(speqg_scan * scan, const speqg_batch * device_batch);
 int speqg_scan_sync(speqg_scan * scan);
+/* wait only for the host->device copies submitted so far (the host buffers may be refilled; kernels keep running). */
+int speqg_scan_wait_copies(speqg_scan * scan);
 /* sync, then copy the tallies out.  unique_u64 / unique_f64: n_groups entries each, either may be NULL. */
 int speqg_scan_finish(speqg_scan * scan, uint64_t * unique_u64, double * unique_f64, speqg_counts * counts);
 int speqg_scan_reset(speqg_scan * scan);
@@ -159,6 +165,11 @@ int speqg_scan_reset(speqg_scan * scan);
  * N searched as a symbol, stop at the first empty interval).  Not part of the product path; used for the roofline. */
 int speqg_scan_stats(speqg_scan * scan, const speqg_batch * device_batch, speqg_counts * counts);
 void speqg_scan_close(speqg_scan * scan);
+
+/* page-locked host memory for read batches (replaces the heap vectors seqan3's record buffer holds,
+ * deps/seqan3/include/seqan3/range/views/async_input_buffer.hpp:89-116). */
+int speqg_host_alloc(size_t bytes, void ** out);
+void speqg_host_free(void * p);
 
 /* device-resident copy of a host batch (for speqg_scan_submit_device); free with speqg_batch_free_device. */
 int speqg_batch_to_device(int device, const speqg_batch * host_batch, speqg_batch * device_batch);

@@ -62,7 +62,7 @@ def build_cli(force: bool = False) -> Path | None:
         return CLI_BIN
     CLI_BIN.parent.mkdir(exist_ok=True)
     cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-pthread", "-I", str(ROOT.parent / "include"), "-o", str(CLI_BIN)] + \
-          [str(s) for s in srcs] + ["-L", str(LIB_DIR), "-lspeq_cuda", "-Wl,-rpath,$ORIGIN/../lib"]
+          [str(s) for s in srcs] + ["-L", str(LIB_DIR), "-lspeq_cuda", "-lz", "-Wl,-rpath,$ORIGIN/../lib"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("g++ failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)

@@ -57,6 +57,11 @@ SIGNATURES = {
                                     C.POINTER(C.c_void_p)]),
     "speqg_index_save": (C.c_int, [C.c_void_p, C.c_char_p]),
     "speqg_index_load": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "speqg_index_save_at": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64]),
+    "speqg_index_load_at": (C.c_int, [C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "speqg_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    "speqg_host_free": (None, [C.c_void_p]),
+    "speqg_scan_wait_copies": (C.c_int, [C.c_void_p]),
     "speqg_index_get_info": (C.c_int, [C.c_void_p, C.POINTER(IndexInfo)]),
     "speqg_index_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "speqg_index_upload": (C.c_int, [C.c_void_p, C.c_int]),

@@ -78,7 +78,7 @@ int speqg_device_count(int * count)
     if (e != cudaSuccess)
     {
         *count = 0;
-        throw api_error(SPEQG_ECUDA, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+        throw api_error(SPEQG_ECUDA, std::string("no usable CUDA device (there is no CPU path): cudaGetDeviceCount: ") + cudaGetErrorString(e));
     }
     SPEQG_CATCH
 }
@@ -108,6 +108,48 @@ int speqg_index_save(const speqg_index * idx, const char * path)
     need(idx && path, "NULL argument");
     save_host_index(idx->host, path);
     SPEQG_CATCH
+}
+
+int speqg_index_save_at(const speqg_index * idx, const char * path, uint64_t offset)
+{
+    SPEQG_TRY
+    need(idx && path, "NULL argument");
+    save_host_index(idx->host, path, offset);
+    SPEQG_CATCH
+}
+
+int speqg_index_load_at(const char * path, uint64_t offset, speqg_index ** out)
+{
+    SPEQG_TRY
+    need(path && out, "NULL argument");
+    auto * idx = new speqg_index();
+    try
+    {
+        load_host_index(path, idx->host, offset);
+    }
+    catch (...)
+    {
+        delete idx;
+        throw;
+    }
+    *out = idx;
+    SPEQG_CATCH
+}
+
+int speqg_host_alloc(size_t bytes, void ** out)
+{
+    SPEQG_TRY
+    need(out != nullptr, "NULL argument");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) throw api_error(SPEQG_ECUDA, "no usable CUDA device (there is no CPU path)");
+    CK(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable));
+    SPEQG_CATCH
+}
+
+void speqg_host_free(void * p)
+{
+    if (p) cudaFreeHost(p);
 }
 
 int speqg_index_load(const char * path, speqg_index ** out)

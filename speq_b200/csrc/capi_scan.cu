@@ -353,6 +353,15 @@ int speqg_scan_sync(speqg_scan * s)
     SPEQG_CATCH
 }
 
+int speqg_scan_wait_copies(speqg_scan * s)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    device_guard guard(s->device);
+    CK(cudaStreamSynchronize(s->copy));
+    SPEQG_CATCH
+}
+
 int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64, speqg_counts * counts)
 {
     SPEQG_TRY

@@ -192,12 +192,13 @@ template <class T> static void rdv(FILE * f, std::vector<T> & v)
     if (n && fread(v.data(), sizeof(T), n, f) != n) throw api_error(SPEQG_EIO, "short read (truncated index payload)");
 }
 
-void save_host_index(HostIndex const & h, std::string const & path)
+void save_host_index(HostIndex const & h, std::string const & path, uint64_t offset)
 {
-    FILE * f = fopen(path.c_str(), "wb");
+    FILE * f = fopen(path.c_str(), offset ? "r+b" : "wb");
     if (!f) throw api_error(SPEQG_EIO, "cannot open " + path + " for writing");
     try
     {
+        if (offset && fseek(f, (long)offset, SEEK_SET) != 0) throw api_error(SPEQG_EIO, "cannot seek in " + path);
         if (fwrite(kMagic, 1, 8, f) != 8) throw api_error(SPEQG_EIO, "short write");
         wr(f, h.n); wr(f, h.S); wr(f, h.V);
         for (int c = 0; c < 8; ++c) wr(f, h.C[c]);
@@ -208,12 +209,13 @@ void save_host_index(HostIndex const & h, std::string const & path)
     if (fclose(f) != 0) throw api_error(SPEQG_EIO, "cannot close " + path);
 }
 
-void load_host_index(std::string const & path, HostIndex & h)
+void load_host_index(std::string const & path, HostIndex & h, uint64_t offset)
 {
     FILE * f = fopen(path.c_str(), "rb");
     if (!f) throw api_error(SPEQG_EIO, "cannot open " + path);
     try
     {
+        if (offset && fseek(f, (long)offset, SEEK_SET) != 0) throw api_error(SPEQG_EIO, "cannot seek in " + path);
         char mg[8];
         if (fread(mg, 1, 8, f) != 8 || memcmp(mg, kMagic, 8) != 0) throw api_error(SPEQG_EIO, path + " is not a speq-b200 index payload");
         h = HostIndex{};

@@ -57,8 +57,8 @@ struct DeviceIndex
 
 void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint32_t S, int32_t const * group_of_text,
                       uint32_t V, uint32_t flags, HostIndex & out);
-void save_host_index(HostIndex const & h, std::string const & path);
-void load_host_index(std::string const & path, HostIndex & h);
+void save_host_index(HostIndex const & h, std::string const & path, uint64_t offset = 0);
+void load_host_index(std::string const & path, HostIndex & h, uint64_t offset = 0);
 
 // packer (pack.cpp)
 uint64_t pack_groups(uint64_t const * offsets, uint64_t n_reads);

@@ -1,0 +1,485 @@
+// speq.cpp -- the `speq index | scan | all` host binary of the B200 build.
+//
+// Keeps the reference's surface for the scan hot path -- sub-commands, flags, `.idx` / `<stem>_<k>mer.dat` caching with
+// the same staleness rules, and the stderr report -- and calls libspeq_cuda.so (include/speq_cuda.h) for everything that
+// computes.  Reference entry points mirrored (paths relative to the reference checkout):
+//   main                      src/main.cpp:15-40
+//   speq::fm::index           src/fm_indexer.cpp:55-110   (generate_fm_index :8-52)
+//   speq::scan::async_one/two src/fm_scanner.cpp:5-33, with the four _async_* bodies :35-279, 310-545, 548-792, 795-1065
+//   back-check                src/fm_scanner.cpp:1476-1576
+// There is no CPU path: without a CUDA device every compute call fails and the message is printed.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/speq_cuda.h"
+#include "args.h"
+#include "groups.h"
+#include "seqio.h"
+
+namespace fs = std::filesystem;
+using speq::args::cmd_arguments;
+
+namespace
+{
+void ck(int rc, const char * what)
+{
+    if (rc != SPEQG_OK) throw std::runtime_error(std::string(what) + ": " + speqg_last_error());
+}
+
+// seqan3::debug_stream prints ranges as [a,b,c] and arithmetic values with the ostream defaults
+template <class T> std::ostream & operator<<(std::ostream & os, std::vector<T> const & v)
+{
+    os << '[';
+    for (size_t i = 0; i < v.size(); ++i) os << (i ? "," : "") << v[i];
+    return os << ']';
+}
+
+int64_t mtime_of(fs::path const & p)
+{
+    return static_cast<int64_t>(fs::last_write_time(p).time_since_epoch().count());
+}
+
+// ---- .idx container: metadata the reference archives in front of the index (src/fm_indexer.cpp:39-50), then our payload
+const char kIdxMagic[8] = {'S', 'P', 'Q', 'I', 'D', 'X', '0', '2'};
+const char kDatMagic[8] = {'S', 'P', 'Q', 'D', 'A', 'T', '0', '1'};
+
+struct idx_meta
+{
+    std::string scaffold_file;
+    int64_t scaffold_time = 0, group_time = 0;
+    std::vector<std::string> group_names;
+    std::vector<int> group_scaffolds, group_counts;
+    uint64_t payload_offset = 0;
+};
+
+void put_u64(std::ostream & os, uint64_t v) { os.write(reinterpret_cast<const char *>(&v), 8); }
+uint64_t get_u64(std::istream & is)
+{
+    uint64_t v = 0;
+    is.read(reinterpret_cast<char *>(&v), 8);
+    if (!is) throw std::runtime_error("truncated index file");
+    return v;
+}
+void put_str(std::ostream & os, std::string const & s) { put_u64(os, s.size()); os.write(s.data(), static_cast<std::streamsize>(s.size())); }
+std::string get_str(std::istream & is)
+{
+    uint64_t n = get_u64(is);
+    if (n > (1u << 20)) throw std::runtime_error("corrupt index file");
+    std::string s(n, '\0');
+    is.read(s.data(), static_cast<std::streamsize>(n));
+    if (!is) throw std::runtime_error("truncated index file");
+    return s;
+}
+void put_ints(std::ostream & os, std::vector<int> const & v)
+{
+    put_u64(os, v.size());
+    os.write(reinterpret_cast<const char *>(v.data()), static_cast<std::streamsize>(v.size() * sizeof(int)));
+}
+std::vector<int> get_ints(std::istream & is)
+{
+    uint64_t n = get_u64(is);
+    if (n > (1u << 28)) throw std::runtime_error("corrupt index file");
+    std::vector<int> v(n);
+    is.read(reinterpret_cast<char *>(v.data()), static_cast<std::streamsize>(n * sizeof(int)));
+    if (!is) throw std::runtime_error("truncated index file");
+    return v;
+}
+
+uint64_t write_meta(fs::path const & p, idx_meta const & m)
+{
+    std::ofstream os(p, std::ios::binary | std::ios::trunc);
+    if (!os) throw std::runtime_error("cannot write " + p.string());
+    os.write(kIdxMagic, 8);
+    put_str(os, m.scaffold_file);
+    put_u64(os, static_cast<uint64_t>(m.scaffold_time));
+    put_u64(os, static_cast<uint64_t>(m.group_time));
+    put_u64(os, m.group_names.size());
+    for (auto const & s : m.group_names) put_str(os, s);
+    put_ints(os, m.group_scaffolds);
+    put_ints(os, m.group_counts);
+    uint64_t off = static_cast<uint64_t>(os.tellp());
+    off = (off + 8 + 63) / 64 * 64;   // payload starts 64-byte aligned; its offset is stored just before the padding
+    put_u64(os, off);
+    while (static_cast<uint64_t>(os.tellp()) < off) os.put('\0');
+    return off;
+}
+
+idx_meta read_meta(fs::path const & p)
+{
+    std::ifstream is(p, std::ios::binary);
+    if (!is) throw std::runtime_error("cannot open index file " + p.string());
+    char mg[8];
+    is.read(mg, 8);
+    if (!is || memcmp(mg, kIdxMagic, 8) != 0)
+        throw std::runtime_error(p.string() + " is not an index written by this build (the reference's cereal archive is not readable yet)");
+    idx_meta m;
+    m.scaffold_file = get_str(is);
+    m.scaffold_time = static_cast<int64_t>(get_u64(is));
+    m.group_time = static_cast<int64_t>(get_u64(is));
+    uint64_t n = get_u64(is);
+    for (uint64_t i = 0; i < n; ++i) m.group_names.push_back(get_str(is));
+    m.group_scaffolds = get_ints(is);
+    m.group_counts = get_ints(is);
+    m.payload_offset = get_u64(is);
+    return m;
+}
+
+struct index_handle
+{
+    speqg_index * h = nullptr;
+    ~index_handle() { speqg_index_free(h); }
+};
+
+// ---- speq::fm::generate_fm_index (src/fm_indexer.cpp:8-52)
+void generate_fm_index(cmd_arguments & args, int64_t scaffold_time, int64_t group_time, std::vector<std::string> const & group_names,
+                       std::vector<int> const & group_scaffolds, std::vector<int> const & group_counts)
+{
+    auto scaffolds = speq::io::read_reference_ranks(args.in_file_references);
+    // every sequence twice; odd copies <- complement(reverse)  (src/fm_indexer.cpp:19-33)
+    static const uint8_t comp[5] = {4, 2, 1, 3, 0};
+    std::vector<std::vector<uint8_t>> texts;
+    std::vector<int32_t> group_of_text;
+    for (size_t j = 0; j < scaffolds.size(); ++j)
+    {
+        std::vector<uint8_t> rc(scaffolds[j].rbegin(), scaffolds[j].rend());
+        for (auto & c : rc) c = comp[c];
+        int g = j < group_scaffolds.size() ? group_scaffolds[j] : -1;
+        texts.push_back(std::move(scaffolds[j]));
+        texts.push_back(std::move(rc));
+        group_of_text.push_back(g);
+        group_of_text.push_back(g);
+    }
+    std::vector<const uint8_t *> ptrs;
+    std::vector<uint64_t> lens;
+    for (auto const & t : texts) { ptrs.push_back(t.data()); lens.push_back(t.size()); }
+    index_handle idx;
+    ck(speqg_index_build(ptrs.data(), lens.data(), static_cast<uint32_t>(texts.size()), group_of_text.data(),
+                         static_cast<uint32_t>(group_names.size()), 0, &idx.h), "speqg_index_build");
+    args.io_file_index.replace_extension(".idx");
+    idx_meta m{args.in_file_references.string(), scaffold_time, group_time, group_names, group_scaffolds, group_counts, 0};
+    uint64_t off = write_meta(args.io_file_index, m);
+    ck(speqg_index_save_at(idx.h, args.io_file_index.c_str(), off), "speqg_index_save_at");
+}
+
+// ---- speq::fm::index (src/fm_indexer.cpp:55-110)
+int do_index(cmd_arguments & args)
+{
+    int64_t scaffold_time = mtime_of(args.in_file_references);
+    int64_t group_time = mtime_of(args.in_file_references_groups);
+    std::vector<int> group_scaffolds, group_counts;
+    std::vector<std::string> group_names;
+    speq::file_to_map(args.in_file_references_groups, group_names, group_scaffolds, group_counts);
+    bool rebuild = true;
+    if (fs::exists(args.io_file_index) && !args.is_force)
+    {
+        args.io_file_index.replace_extension(".idx");
+        idx_meta old = read_meta(args.io_file_index);
+        rebuild = fs::path(old.scaffold_file) != args.in_file_references || old.group_time != group_time || old.scaffold_time != scaffold_time;
+    }
+    if (rebuild) generate_fm_index(args, scaffold_time, group_time, group_names, group_scaffolds, group_counts);
+    return 0;
+}
+
+// ---- pinned double buffers per device
+struct host_batch
+{
+    uint8_t * seq = nullptr;
+    uint8_t * qual = nullptr;
+    uint64_t * offsets = nullptr;
+    uint64_t cap_bytes = 0, cap_reads = 0, n_reads = 0, n_bytes = 0;
+    void alloc(uint64_t bytes, uint64_t reads)
+    {
+        release();
+        void * p = nullptr;
+        ck(speqg_host_alloc(bytes, &p), "speqg_host_alloc"); seq = static_cast<uint8_t *>(p);
+        ck(speqg_host_alloc(bytes, &p), "speqg_host_alloc"); qual = static_cast<uint8_t *>(p);
+        ck(speqg_host_alloc((reads + 1) * 8, &p), "speqg_host_alloc"); offsets = static_cast<uint64_t *>(p);
+        cap_bytes = bytes; cap_reads = reads; n_reads = 0; n_bytes = 0; offsets[0] = 0;
+    }
+    void release()
+    {
+        speqg_host_free(seq); speqg_host_free(qual); speqg_host_free(offsets);
+        seq = qual = nullptr; offsets = nullptr;
+    }
+    bool fits(uint64_t len, uint64_t n) const { return n_reads + n <= cap_reads && n_bytes + len <= cap_bytes; }
+    void push(std::string const & s, std::string const & q)
+    {
+        memcpy(seq + n_bytes, s.data(), s.size());
+        memcpy(qual + n_bytes, q.data(), q.size());
+        n_bytes += s.size();
+        offsets[++n_reads] = n_bytes;
+    }
+    void clear() { n_reads = 0; n_bytes = 0; offsets[0] = 0; }
+};
+
+struct device_lane
+{
+    speqg_scan * scan = nullptr;
+    host_batch buf[2];
+    int cur = 0;
+};
+
+struct scan_out
+{
+    std::vector<uint64_t> unique_int;
+    std::vector<double> unique_w;
+    uint64_t total_kmers = 0, ambiguous = 0, lookups = 0, reads = 0;
+    double seconds = 0;
+};
+
+// worker bodies + reduction of the futures (src/fm_scanner.cpp:138-236 and the three sibling functions)
+scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, uint32_t V, bool paired)
+{
+    auto t0 = std::chrono::steady_clock::now();
+    speq::io::sequence_reader r1(args.in_file_reads_path_1);
+    std::unique_ptr<speq::io::sequence_reader> r2;
+    if (paired) r2 = std::make_unique<speq::io::sequence_reader>(args.in_file_reads_path_2);
+    const uint64_t per = paired ? 2 : 1;
+    size_t dev = 0;
+    std::string s1, q1, s2, q2;
+    auto flush = [&](device_lane & L)
+    {
+        host_batch & b = L.buf[L.cur];
+        if (b.n_reads == 0) return;
+        ck(speqg_scan_submit_raw(L.scan, b.seq, b.qual, b.offsets, b.n_reads, SPEQG_ENC_ASCII), "speqg_scan_submit_raw");
+        L.cur ^= 1;
+        ck(speqg_scan_wait_copies(L.scan), "speqg_scan_wait_copies");   // the other buffer's copy (submitted earlier) is done
+        L.buf[L.cur].clear();
+    };
+    while (r1.next(s1, q1))
+    {
+        if (paired && !r2->next(s2, q2)) break;   // views::zip stops at the shorter file (src/fm_scanner.cpp:651)
+        uint64_t need = s1.size() + (paired ? s2.size() : 0);
+        device_lane * L = &lanes[dev];
+        if (!L->buf[L->cur].fits(need, per))
+        {
+            flush(*L);
+            dev = (dev + 1) % lanes.size();
+            L = &lanes[dev];
+            if (!L->buf[L->cur].fits(need, per))
+            {
+                if (L->buf[L->cur].n_reads) flush(*L);
+                if (need > L->buf[L->cur].cap_bytes)
+                {
+                    ck(speqg_scan_sync(L->scan), "speqg_scan_sync");
+                    L->buf[L->cur].alloc(need * 2, L->buf[L->cur].cap_reads);
+                }
+            }
+        }
+        L->buf[L->cur].push(s1, q1);
+        if (paired) L->buf[L->cur].push(s2, q2);
+    }
+    for (auto & L : lanes) flush(L);
+    scan_out out;
+    out.unique_int.assign(V, 0);
+    out.unique_w.assign(V, 0.0);
+    for (auto & L : lanes)   // the per-device tallies are summed like the reference sums its futures (src/fm_scanner.cpp:224-233)
+    {
+        std::vector<uint64_t> u(V);
+        std::vector<double> w(V);
+        speqg_counts c{};
+        ck(speqg_scan_finish(L.scan, u.data(), w.data(), &c), "speqg_scan_finish");
+        for (uint32_t g = 0; g < V; ++g) { out.unique_int[g] += u[g]; out.unique_w[g] += w[g]; }
+        out.total_kmers += c.total_kmers; out.ambiguous += c.ambiguous_reads; out.lookups += c.lookups; out.reads += c.reads;
+    }
+    out.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return out;
+}
+
+std::vector<double> unique_to_percent(std::vector<double> const & unique_in_reads, uint64_t total_in_reads,
+                                      std::vector<double> const & unique_in_refs, std::vector<double> const & total_in_refs)
+{
+    std::vector<double> out(unique_in_refs.size(), 0.0);
+    ck(speqg_unique_to_percent(unique_in_reads.data(), total_in_reads, unique_in_refs.data(), total_in_refs.data(),
+                               static_cast<uint32_t>(out.size()), out.data()), "speqg_unique_to_percent");
+    return out;
+}
+
+void write_json(fs::path const & p, cmd_arguments const & args, bool local, bool paired, std::vector<uint64_t> const & uref,
+                std::vector<uint64_t> const & tref, scan_out const & so, std::vector<double> const & unique_totals,
+                std::vector<double> const & initial, std::vector<double> const & fin, size_t iters, double t_backcheck, double t_refine)
+{
+    FILE * f = fopen(p.c_str(), "w");
+    if (!f) throw std::runtime_error("cannot write " + p.string());
+    auto vu = [&](const char * k, std::vector<uint64_t> const & v)
+    {
+        fprintf(f, "\"%s\":[", k);
+        for (size_t i = 0; i < v.size(); ++i) fprintf(f, "%s%llu", i ? "," : "", static_cast<unsigned long long>(v[i]));
+        fprintf(f, "],");
+    };
+    auto vd = [&](const char * k, std::vector<double> const & v)
+    {
+        fprintf(f, "\"%s\":[", k);
+        for (size_t i = 0; i < v.size(); ++i) fprintf(f, "%s%.17g", i ? "," : "", v[i]);
+        fprintf(f, "],");
+    };
+    fprintf(f, "{\"k\":%u,\"mode\":\"%s\",\"paired\":%s,\"gpus\":%u,", args.kmer, local ? "local" : "global", paired ? "true" : "false", args.gpus);
+    vu("unique_ref", uref); vu("total_ref", tref); vu("unique", so.unique_int); vd("unique_w", so.unique_w); vd("unique_totals", unique_totals);
+    vd("percent_initial", initial); vd("percent_final", fin);
+    fprintf(f, "\"total_kmers\":%llu,\"ambiguous\":%llu,\"lookups\":%llu,\"reads\":%llu,\"iterations\":%zu,",
+            (unsigned long long)so.total_kmers, (unsigned long long)so.ambiguous, (unsigned long long)so.lookups, (unsigned long long)so.reads, iters);
+    fprintf(f, "\"t_backcheck_s\":%.6f,\"t_scan_s\":%.6f,\"t_refine_s\":%.6f}\n", t_backcheck, so.seconds, t_refine);
+    fclose(f);
+}
+
+// ---- speq::scan::async_one / async_two
+int do_scan(cmd_arguments & args)
+{
+    const bool paired = !args.in_file_reads_path_2.empty();
+    const bool local = (args.fixed_accuracy == 0.0);                                 // src/fm_scanner.cpp:8-17
+    const double percent_perfect = local ? 0.0 : pow(args.fixed_accuracy, args.kmer);
+    // import the index (src/fm_scanner.cpp:37-58)
+    args.io_file_index.replace_extension(".idx");
+    idx_meta meta = read_meta(args.io_file_index);
+    index_handle idx;
+    ck(speqg_index_load_at(args.io_file_index.c_str(), meta.payload_offset, &idx.h), "speqg_index_load_at");
+    if (args.in_file_references != fs::path(meta.scaffold_file))                      // src/fm_scanner.cpp:60-72
+    {
+        if (fs::exists(meta.scaffold_file)) args.in_file_references = meta.scaffold_file;
+        else throw std::logic_error{"SPeQ could not find the sequence file used to make the specified index file."};
+    }
+    const uint32_t V = static_cast<uint32_t>(meta.group_names.size());
+    int ndev = 0;
+    ck(speqg_device_count(&ndev), "speqg_device_count");
+    if (ndev <= 0) throw std::runtime_error("no CUDA device: speq scan has no CPU path");
+    const unsigned gpus = std::min<unsigned>(args.gpus, static_cast<unsigned>(ndev));
+
+    // <stem>_<k>mer.dat: back-check counts, cached per k, keyed by the .idx mtime (src/fm_scanner.cpp:79-135)
+    int64_t idx_time = mtime_of(args.io_file_index);
+    fs::path dat = args.io_file_index;
+    dat.replace_filename(args.io_file_index.stem().string() + "_" + std::to_string(args.kmer) + "mer.dat");
+    std::vector<uint64_t> unique_ref(V, 0), total_ref(V, 0);
+    bool have_dat = false;
+    double t_backcheck = 0;
+    if (fs::exists(dat))
+    {
+        std::ifstream is(dat, std::ios::binary);
+        char mg[8];
+        is.read(mg, 8);
+        if (is && memcmp(mg, kDatMagic, 8) == 0 && static_cast<int64_t>(get_u64(is)) == idx_time && get_u64(is) == V)
+        {
+            is.read(reinterpret_cast<char *>(unique_ref.data()), V * 8);
+            is.read(reinterpret_cast<char *>(total_ref.data()), V * 8);
+            have_dat = static_cast<bool>(is);
+        }
+    }
+    if (!have_dat)
+    {
+        auto t0 = std::chrono::steady_clock::now();
+        ck(speqg_backcheck(idx.h, 0, args.kmer, unique_ref.data(), total_ref.data()), "speqg_backcheck");
+        t_backcheck = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        std::ofstream os(dat, std::ios::binary | std::ios::trunc);
+        os.write(kDatMagic, 8);
+        put_u64(os, static_cast<uint64_t>(idx_time));
+        put_u64(os, V);
+        os.write(reinterpret_cast<const char *>(unique_ref.data()), V * 8);
+        os.write(reinterpret_cast<const char *>(total_ref.data()), V * 8);
+        std::cerr << unique_ref << "\n";                                              // src/fm_scanner.cpp:1572-1573
+        std::cerr << total_ref << "\n";
+    }
+
+    // one scan handle per device, index replicated
+    std::vector<device_lane> lanes(gpus);
+    speqg_params prm{};
+    prm.k = args.kmer;
+    prm.phred_cutoff = args.phred_cutoff;
+    prm.mode = local ? SPEQG_MODE_LOCAL : SPEQG_MODE_GLOBAL;
+    prm.paired = paired ? 1 : 0;
+    prm.record_multiplicity = 1;
+    prm.algorithm = SPEQG_ALGO_ROLLING;
+    uint64_t cap_reads = std::max<uint64_t>(2, args.batch_reads & ~1u);
+    uint64_t cap_bytes = std::min<uint64_t>(cap_reads * 320, uint64_t(512) << 20);
+    for (unsigned d = 0; d < gpus; ++d)
+    {
+        ck(speqg_scan_open(idx.h, static_cast<int>(d), &prm, &lanes[d].scan), "speqg_scan_open");
+        lanes[d].buf[0].alloc(cap_bytes, cap_reads);
+        lanes[d].buf[1].alloc(cap_bytes, cap_reads);
+    }
+    int rc = 1;
+    try
+    {
+        scan_out so = run_scan(args, lanes, V, paired);
+        std::vector<double> unique_totals(V, 0.0);
+        if (local) unique_totals = so.unique_w;
+        else for (uint32_t i = 0; i < V; ++i) unique_totals[i] += static_cast<double>(so.unique_int[i]) / percent_perfect;   // :234-236
+        std::vector<double> d_uref(unique_ref.begin(), unique_ref.end()), d_tref(total_ref.begin(), total_ref.end());
+        auto percent = unique_to_percent(unique_totals, so.total_kmers, d_uref, d_tref);                                    // :238-243
+        auto initial = percent;
+        // report (global single :245-247, local single :513-514, global paired :757-759, local paired :1030-1033)
+        std::cerr << percent << "\n";
+        if (!(local && !paired)) std::cerr << unique_totals << "\n";
+        std::cerr << so.total_kmers << "\t" << so.ambiguous << "\n";
+        if (local && paired)
+        {
+            // the reference's fusion map only ever holds the empty-set key (set_groups is passed by value, :916)
+            if (so.ambiguous) std::cerr << "[([]," << so.ambiguous << ")]\n";
+            else std::cerr << "[]\n";
+        }
+        // refinement loop (src/fm_scanner.cpp:248-279): the estimate runs on the recorded k-mer multiplicities
+        auto t0 = std::chrono::steady_clock::now();
+        std::vector<double> diff(V, 1.0);
+        size_t iters = 0;
+        while (V > 0 && *std::max_element(diff.begin(), diff.end()) > args.precision)
+        {
+            std::vector<double> next_tkpg(V, 0.0), part(V);
+            for (auto & L : lanes)
+            {
+                ck(speqg_refine(L.scan, percent.data(), meta.group_counts.data(), part.data()), "speqg_refine");
+                for (uint32_t g = 0; g < V; ++g) next_tkpg[g] += part[g];
+            }
+            if (local && !paired) std::cerr << "1: " << unique_totals << "\n2: " << so.total_kmers << "\n3: " << next_tkpg << "\n";   // :530
+            auto next_percent = unique_to_percent(unique_totals, so.total_kmers, unique_totals, next_tkpg);
+            for (uint32_t i = 0; i < V; ++i) diff[i] = std::abs(next_percent[i] - percent[i]);
+            percent = next_percent;
+            if (local && !paired)
+            {
+                std::cerr << "Percent of each group: " << percent << "\n";                                                  // :543-544
+                std::cerr << "Total Kmers per group: " << next_tkpg << "\n\n";
+            }
+            else
+            {
+                std::cerr << percent << "\n";                                                                               // :277-278
+                std::cerr << next_tkpg << "\n\n";
+            }
+            ++iters;
+        }
+        double t_refine = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (!args.json_path.empty())
+            write_json(args.json_path, args, local, paired, unique_ref, total_ref, so, unique_totals, initial, percent, iters, t_backcheck, t_refine);
+    }
+    catch (...)
+    {
+        for (auto & L : lanes) { speqg_scan_close(L.scan); L.buf[0].release(); L.buf[1].release(); }
+        throw;
+    }
+    for (auto & L : lanes) { speqg_scan_close(L.scan); L.buf[0].release(); L.buf[1].release(); }
+    return rc;
+}
+}   // namespace
+
+int main(int argc, char ** argv)
+{
+    auto args = speq::args::initialize_argument_parser(argc, argv);
+    if (!args.is_parsed) return 0;   // the reference returns 0 after printing the parse error (src/main.cpp:17-40)
+    try
+    {
+        if (args.is_indexer) do_index(args);
+        if (args.is_scanner) do_scan(args);
+    }
+    catch (std::exception const & e)
+    {
+        // the reference lets exceptions escape (terminate); we print the same message and exit non-zero
+        std::cerr << "terminate called after throwing an instance of an exception\n  what():  " << e.what() << "\n";
+        return 134;
+    }
+    return 0;
+}

@@ -1,0 +1,135 @@
+"""The `speq index|scan|all` host binary (speq_b200/host): reference flags, .idx/.dat caching rules, stderr report.
+CPU tier: argument handling, groups grammar via `speq index`, staleness rules, and that `scan` refuses to run without a
+CUDA device.  GPU tier: `speq all` on the golden fixtures, compared with the sdsl-backed expectations."""
+from __future__ import annotations
+
+import json
+import os
+import subprocess
+import time
+
+import numpy as np
+import pytest
+
+import helpers
+
+
+@pytest.fixture(scope="module")
+def speq_bin(lib):
+    from speq_b200 import build
+    b = build.build_cli()
+    assert b is not None and b.exists()
+    return b
+
+
+def run(speq_bin, *a, cwd=None):
+    return subprocess.run([str(speq_bin), *map(str, a)], capture_output=True, text=True, cwd=cwd)
+
+
+def test_argument_errors(speq_bin, tmp_path):
+    r = run(speq_bin)
+    assert r.returncode == 0 and r.stderr.startswith("SPeQ Error: ")
+    r = run(speq_bin, "scan", "-t", "1")
+    assert "speq scan | argument parsing error:  Validation failed for option -t/--threads" in r.stderr
+    r = run(speq_bin, "all", "--fixed-accuracy", "1.5")
+    assert "speq all | argument parsing error:  Validation failed for option --fixed-accuracy" in r.stderr
+    r = run(speq_bin, "index", "-r", "missing.fa", cwd=tmp_path)
+    assert 'The relative-path file "missing.fa" was not found.' in r.stderr
+    r = run(speq_bin, "index", "-r", "/nonexistent/dir/x.fa")
+    assert 'The full-path file "/nonexistent/dir/x.fa" was not found.' in r.stderr
+    (tmp_path / "output.txt").write_text("x")
+    r = run(speq_bin, "all", cwd=tmp_path)
+    assert "Cowardly refusing to use an existing output file. Use '-f' to overwrite." in r.stderr
+    r = run(speq_bin, "index", "--kmer", "5")
+    assert "Unknown option --kmer" in r.stderr          # speq index takes no -k (src/arg_parse.cpp:91-126)
+
+
+def test_index_cache_rules(speq_bin, tmp_path):
+    fx = helpers.load_golden("global_single")
+    refs, groups, r1, _ = helpers.golden_files(tmp_path, fx)
+    idx = tmp_path / "cache.idx"
+    r = run(speq_bin, "index", "-r", refs, "-g", groups, "-x", idx, cwd=tmp_path)
+    assert r.returncode == 0 and idx.exists(), r.stderr
+    m0 = idx.stat().st_mtime_ns
+    time.sleep(0.05)
+    run(speq_bin, "index", "-r", refs, "-g", groups, "-x", idx, cwd=tmp_path)
+    assert idx.stat().st_mtime_ns == m0                  # inputs unchanged: not rebuilt (src/fm_indexer.cpp:68-97)
+    run(speq_bin, "index", "-r", refs, "-g", groups, "-x", idx, "-f", cwd=tmp_path)
+    m1 = idx.stat().st_mtime_ns
+    assert m1 != m0                                      # -f forces a rebuild
+    time.sleep(0.05)
+    os.utime(groups)                                     # groups file touched: rebuilt
+    run(speq_bin, "index", "-r", refs, "-g", groups, "-x", idx, cwd=tmp_path)
+    assert idx.stat().st_mtime_ns != m1
+    # the payload is loadable by the library at the recorded offset
+    from speq_b200 import engine
+    raw = idx.read_bytes()
+    assert raw[:8] == b"SPQIDX02"
+
+
+def test_groups_grammar_through_index(speq_bin, tmp_path):
+    helpers.write_fasta(tmp_path / "r.fa", ["ACGTACGTAA", "ACGTTCGTAA", "TTGTACGTAA", "ACGAACGTCC"])
+    (tmp_path / "g.txt").write_text("# comment line\nalpha (2) : 0 - 1 # trailing comment\nno colon here\nbeta(2):\t3 , x, 2\n")
+    r = run(speq_bin, "index", "-r", "r.fa", "-g", "g.txt", "-x", "g.idx", cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    assert "A non-integer index was detected and ignored at: x" in r.stderr
+    raw = (tmp_path / "g.idx").read_bytes()
+    assert b"alpha " in raw and b"beta" in raw           # names are kept untrimmed, as the reference does
+    # a groups line without (count) makes std::stoi throw, as in the reference (src/file_to_map.cpp:42-43)
+    (tmp_path / "bad.txt").write_text("MCV-1p: 0-3\n")
+    r = run(speq_bin, "index", "-r", "r.fa", "-g", "bad.txt", "-x", "bad.idx", cwd=tmp_path)
+    assert r.returncode != 0 and "stoi" in r.stderr
+    # an unassigned scaffold is rejected loudly (reference: undefined behaviour in the refinement loop)
+    (tmp_path / "part.txt").write_text("a(1): 0\nb(1): 2-3\n")
+    r = run(speq_bin, "index", "-r", "r.fa", "-g", "part.txt", "-x", "part.idx", cwd=tmp_path)
+    assert r.returncode != 0 and "every scaffold must be assigned" in r.stderr
+
+
+def test_scan_needs_gpu(speq_bin, tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    fx = helpers.load_golden("global_single")
+    refs, groups, r1, _ = helpers.golden_files(tmp_path, fx)
+    r = run(speq_bin, "all", "-r", refs, "-g", groups, "-1", r1, "-x", tmp_path / "i.idx", "-k", 13, "--fixed-accuracy", 0.99, cwd=tmp_path)
+    assert r.returncode != 0 and ("no usable CUDA device" in r.stderr or "no CUDA device" in r.stderr)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+def test_speq_all_matches_golden(speq_bin, tmp_path, name):
+    fx = helpers.load_golden(name)
+    exp, runp = fx["expected"], fx["run"]
+    refs, groups, r1, r2 = helpers.golden_files(tmp_path, fx)
+    cmd = ["all", "-r", refs, "-g", groups, "-1", r1, "-x", tmp_path / "i.idx", "-k", runp["k"], "--fixed-accuracy", runp["fixed_accuracy"],
+           "--phred-cutoff", runp.get("phred_cutoff", 30), "--json", tmp_path / "out.json", "--batch-reads", 64]
+    if r2 is not None:
+        cmd += ["-2", r2]
+    r = run(speq_bin, *cmd, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    out = json.loads((tmp_path / "out.json").read_text())
+    assert out["unique_ref"] == exp["unique_ref"] and out["total_ref"] == exp["total_ref"]
+    assert out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"] and out["lookups"] == exp["lookups"]
+    if exp["mode"] == "global":
+        assert out["unique"] == exp["unique"]
+        assert out["percent_initial"] == exp["percent_initial"]
+    else:
+        assert helpers.rel_close(out["unique_w"], exp["unique_w"])
+    assert out["iterations"] == exp["iterations"]
+    assert helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
+    # stderr shape: first the back-check vectors (the .dat was built), then percent / totals lines, then the iterations
+    lines = r.stderr.strip().split("\n")
+    assert lines[0] == "[" + ",".join(map(str, exp["unique_ref"])) + "]"
+    assert lines[1] == "[" + ",".join(map(str, exp["total_ref"])) + "]"
+    assert f"{exp['total_kmers']}\t{exp['ambiguous']}" in lines
+    dat = tmp_path / f"i_{runp['k']}mer.dat"
+    assert dat.exists()
+    # second run: .dat is fresh, so the back-check vectors are not printed again (src/fm_scanner.cpp:101-119)
+    cmd[0] = "scan"
+    cmd2 = [c for i, c in enumerate(cmd) if not (i > 0 and str(cmd[i - 1]) in ("-r", "-g")) and str(c) not in ("-r", "-g")]
+    r2nd = run(speq_bin, *cmd2, "-f", cwd=tmp_path)
+    assert r2nd.returncode == 0, r2nd.stderr
+    assert r2nd.stderr.strip().split("\n")[0] != lines[0] or exp["unique_ref"] == exp["total_ref"]
+    # sharded over 2 "GPUs" requested on a 1-GPU box clamps to the devices present; result unchanged
+    out2 = json.loads((tmp_path / "out.json").read_text())
+    assert out2["total_kmers"] == exp["total_kmers"]
