@@ -27,11 +27,19 @@ DeviceIndex & device_index(speqg_index * idx, int device)
     d.device = device;
     try
     {
+        // query code -> text symbol: A1 C2 G3 T5, N4 (fm_index.hpp:302: rank + 1; dna5 ranks A0 C1 G2 N3 T4)
+        static const uint32_t sym_of_code[5] = {1, 2, 3, 5, 4};
+        uint32_t ctab[16] = {0};
+        for (int c = 0; c < 5; ++c)
+        {
+            ctab[c] = (uint32_t)h.C[sym_of_code[c]];
+            ctab[kCtabEnd + c] = (uint32_t)h.C[sym_of_code[c] + 1];
+        }
         d.blocks = dev_upload(h.blocks.data(), h.blocks.size(), &d.bytes);
-        d.gr = dev_upload(h.gr.data(), h.gr.size(), &d.bytes);
+        d.grp = dev_upload(h.grp.data(), h.grp.size(), &d.bytes);
         d.lcp = dev_upload(h.lcp.data(), h.lcp.size(), &d.bytes);
-        d.exc_pos = dev_upload(h.exc_pos.data(), h.exc_pos.size(), &d.bytes);
         d.n_pos = dev_upload(h.n_pos.data(), h.n_pos.size(), &d.bytes);
+        d.ctab = dev_upload(ctab, 16, &d.bytes);
         d.t_bases = dev_upload(h.t_bases.data(), h.t_bases.size(), &d.bytes);
         d.t_inv = dev_upload(h.t_inv.data(), h.t_inv.size(), &d.bytes);
         d.t_grp_off = dev_upload(h.t_grp_off.data(), h.t_grp_off.size(), &d.bytes);
@@ -44,22 +52,13 @@ DeviceIndex & device_index(speqg_index * idx, int device)
         throw;
     }
     DevIndex & v = d.view;
-    v.blocks = reinterpret_cast<const RankBlock *>(d.blocks);
+    v.blocks = d.blocks;
     v.lcp = d.lcp;
-    v.gr = d.gr;
-    v.exc_pos = d.exc_pos;
+    v.grp = d.grp;
     v.n_pos = d.n_pos;
-    v.n_exc = (uint32_t)h.exc_pos.size();
+    v.ctab = d.ctab;
     v.n_npos = (uint32_t)h.n_pos.size();
     v.n = (uint32_t)h.n;
-    // query code -> text symbol: A1 C2 G3 T5, N4 (fm_index.hpp:302: rank + 1; dna5 ranks A0 C1 G2 N3 T4)
-    static const uint32_t sym_of_code[5] = {1, 2, 3, 5, 4};
-    for (int c = 0; c < 16; ++c) v.ctab[c] = 0;
-    for (int c = 0; c < 5; ++c)
-    {
-        v.ctab[c] = (uint32_t)h.C[sym_of_code[c]];
-        v.ctab[kCtabEnd + c] = (uint32_t)h.C[sym_of_code[c] + 1];
-    }
     return idx->dev.emplace(device, d).first->second;
 }
 }   // namespace speqb
@@ -179,8 +178,8 @@ int speqg_index_get_info(const speqg_index * idx, speqg_index_info * info)
     info->n_texts = h.S;
     info->n_groups = h.V;
     for (int c = 0; c < 8; ++c) info->C[c] = h.C[c];
-    info->n_exceptions = h.exc_pos.size();
-    info->device_bytes = h.blocks.size() * 4 + h.gr.size() * sizeof(GroupRun) + h.lcp.size() + h.exc_pos.size() * 4 +
+    info->n_exceptions = h.n_exc;
+    info->device_bytes = h.blocks.size() * sizeof(KBlock) + h.grp.size() * 2 + h.lcp.size() + 64 +
                          h.n_pos.size() * 4 + h.t_bases.size() * 8 + h.t_inv.size() * 4 + h.t_grp_off.size() * 8 +
                          h.t_len.size() * 4 + h.group_of_text.size() * 4;
     SPEQG_CATCH
@@ -203,16 +202,15 @@ int speqg_index_export(const speqg_index * idx, uint32_t * sa, uint8_t * bwt, ui
         static const uint8_t sym_of_code[4] = {1, 2, 3, 5};
         for (uint64_t i = 0; i < h.n; ++i)
         {
-            uint32_t const * blk = &h.blocks[(i / kBlockSyms) * 8];
+            KBlock const & blk = h.blocks[i / kBlockSyms];
             uint32_t j = (uint32_t)(i % kBlockSyms);
-            uint32_t c = ((blk[4 + j / 32] >> (j % 32)) & 1u) | (((blk[6 + j / 32] >> (j % 32)) & 1u) << 1);
-            bwt[i] = sym_of_code[c];
+            uint32_t c = ((blk.lo[j / 32] >> (j % 32)) & 1u) | (((blk.hi[j / 32] >> (j % 32)) & 1u) << 1);
+            bwt[i] = ((blk.exc[j / 32] >> (j % 32)) & 1u) ? 0xFF : sym_of_code[c];
         }
-        for (uint32_t p : h.exc_pos) bwt[p] = 0xFF;
         for (uint32_t p : h.n_pos) bwt[p] = (uint8_t)kSymN;
     }
     if (group_of_sa)
-        for (uint64_t i = 0; i < h.n; ++i) group_of_sa[i] = h.gr[i].group;
+        for (uint64_t i = 0; i < h.n; ++i) group_of_sa[i] = h.grp[i] == kNoGroup16 ? kNoGroup : h.grp[i];
     if (lcp) std::copy(h.lcp.begin(), h.lcp.begin() + h.n, lcp);
     SPEQG_CATCH
 }

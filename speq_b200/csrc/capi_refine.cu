@@ -17,7 +17,7 @@ struct scan_refine_view
     int device;
     uint32_t k, V;
     uint64_t n;
-    DeviceIndex * di;
+    DevIndex view;
     cudaStream_t stream;
     unsigned long long * mult;
     double * d_percent, * d_tkpg, * d_partial;
@@ -50,22 +50,34 @@ int speqg_backcheck(speqg_index * idx, int device, uint32_t k, uint64_t * unique
     uint64_t lanes = (uint64_t)cfg.grid * cfg.block;
     uint64_t seg = total_windows / (8 * lanes);
     seg = std::min<uint64_t>(std::max<uint64_t>(seg, 32), 8192);
-    std::vector<Segment> segs;
+    std::vector<SegmentX> segs;
     segs.reserve(total_windows / seg + h.S);
     for (uint32_t i = 0; i < h.S; ++i)
     {
         if (h.t_len[i] < k) continue;
         uint32_t nw = h.t_len[i] - k + 1;
         for (uint32_t st = 0; st < nw; st += (uint32_t)seg)
-            segs.push_back(Segment{i, st, (uint32_t)std::min<uint64_t>(seg, nw - st)});
+        {
+            SegmentX sx{};
+            sx.g0 = h.t_grp_off[i];
+            sx.start = st;
+            sx.nwin = (uint32_t)std::min<uint64_t>(seg, nw - st);
+            sx.group = (uint32_t)h.group_of_text[i];
+            segs.push_back(sx);
+        }
     }
-    Segment * d_segs = nullptr;
+    SegmentX * d_segs = nullptr;
+    KBlock * d_blocks_k = nullptr;
     unsigned long long * d_cnt = nullptr;
     cudaStream_t st = nullptr;
     try
     {
         CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         d_segs = dev_upload(segs.data(), segs.size());
+        d_blocks_k = dev_alloc<KBlock>(h.blocks.size());
+        CK(launch_fill_e(di.blocks, d_blocks_k, di.lcp, (uint32_t)h.n, k, st));
+        DevIndex view = di.view;
+        view.blocks = d_blocks_k;
         d_cnt = dev_alloc<unsigned long long>(2 * (size_t)V + SC_COUNT);
         CK(cudaMemsetAsync(d_cnt, 0, (2 * (size_t)V + SC_COUNT) * 8, st));
         ScanArgs a{};
@@ -79,7 +91,7 @@ int speqg_backcheck(speqg_index * idx, int device, uint32_t k, uint64_t * unique
         BatchView v{};
         v.bases = di.t_bases; v.inv = di.t_inv; v.qual = nullptr; v.grp_off = di.t_grp_off; v.len = di.t_len;
         v.read_group = di.t_group; v.n_reads = h.S;
-        CK(launch_scan_roll(di.view, v, a, M_BACKCHECK, cfg, st));
+        CK(launch_scan_roll(view, v, a, M_BACKCHECK, cfg, st));
         std::vector<unsigned long long> out(2 * (size_t)V);
         CK(cudaMemcpyAsync(out.data(), d_cnt, out.size() * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -91,11 +103,11 @@ int speqg_backcheck(speqg_index * idx, int device, uint32_t k, uint64_t * unique
     }
     catch (...)
     {
-        cudaFree(d_segs); cudaFree(d_cnt);
+        cudaFree(d_segs); cudaFree(d_cnt); cudaFree(d_blocks_k);
         if (st) cudaStreamDestroy(st);
         throw;
     }
-    cudaFree(d_segs); cudaFree(d_cnt);
+    cudaFree(d_segs); cudaFree(d_cnt); cudaFree(d_blocks_k);
     cudaStreamDestroy(st);
     SPEQG_CATCH
 }
@@ -110,7 +122,7 @@ int speqg_refine(speqg_scan * scan, const double * percent, const int32_t * grou
     // pageable host sources: cudaMemcpyAsync stages them before returning
     CK(cudaMemcpyAsync(r.d_percent, percent, r.V * 8, cudaMemcpyHostToDevice, r.stream));
     CK(cudaMemcpyAsync(r.d_gc, group_counts, r.V * 4, cudaMemcpyHostToDevice, r.stream));
-    CK(launch_refine(r.di->view, r.k, r.mult, r.d_percent, r.d_gc, r.V, r.d_partial, r.refine_grid, 256, r.stream));
+    CK(launch_refine(r.view, r.k, r.mult, r.d_percent, r.d_gc, r.V, r.d_partial, r.refine_grid, 256, r.stream));
     CK(launch_refine_reduce(r.d_partial, r.refine_grid, r.V, r.d_tkpg, r.stream));
     CK(cudaMemcpyAsync(tkpg, r.d_tkpg, r.V * 8, cudaMemcpyDeviceToHost, r.stream));
     CK(cudaStreamSynchronize(r.stream));

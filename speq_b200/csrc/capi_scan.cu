@@ -61,6 +61,8 @@ struct speqg_scan
 {
     speqg_index * idx = nullptr;
     DeviceIndex * di = nullptr;
+    DevIndex view{};               // di->view with `blocks` replaced by this scan's k-specialised copy
+    KBlock * d_blocks_k = nullptr;
     int device = 0;
     speqg_params p{};
     int mode = 0;
@@ -85,7 +87,7 @@ struct scan_refine_view
     int device;
     uint32_t k, V;
     uint64_t n;
-    DeviceIndex * di;
+    DevIndex view;
     cudaStream_t stream;
     unsigned long long * mult;
     double * d_percent, * d_tkpg, * d_partial;
@@ -94,7 +96,7 @@ struct scan_refine_view
 };
 scan_refine_view refine_view(speqg_scan * s)
 {
-    return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->di, s->compute, s->d_mult,
+    return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult,
                             s->d_percent, s->d_tkpg, s->d_partial, s->d_gc, s->refine_grid};
 }
 }   // namespace speqb
@@ -105,7 +107,7 @@ void scan_release(speqg_scan * s)
 {
     cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
     cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
-    cudaFree(s->d_gc);
+    cudaFree(s->d_gc); cudaFree(s->d_blocks_k);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -141,8 +143,8 @@ void launch_on_view(speqg_scan * s, BatchView const & v)
 {
     if (v.n_reads == 0) return;
     ScanArgs a = scan_args(s);
-    if (s->p.algorithm == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->di->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
-    else CK(launch_scan_roll(s->di->view, v, a, s->mode, s->cfg, s->compute));
+    if (s->p.algorithm == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
+    else CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg, s->compute));
     ++s->launches;
 }
 
@@ -207,6 +209,11 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             qden[q] = 1.0 - 1.0 / pow(10.0, b / 10.0);
         }
         s->d_qden = dev_upload(qden, 42);
+        // rank blocks specialised for this k (e bits = lcp >= k-1): one pass over the index, once per scan handle
+        s->d_blocks_k = dev_alloc<KBlock>(idx->host.blocks.size());
+        CK(launch_fill_e(di.blocks, s->d_blocks_k, di.lcp, (uint32_t)idx->host.n, params->k, s->compute));
+        s->view = di.view;
+        s->view.blocks = s->d_blocks_k;
         CK(scan_launch_cfg(s->mode, 0, V, &s->cfg));
         CK(scan_launch_cfg(s->mode, 1, V, &s->cfg_direct));
         CK(scan_launch_cfg(s->mode, 2, V, &s->cfg_stats));
@@ -406,7 +413,7 @@ int speqg_scan_stats(speqg_scan * s, const speqg_batch * db, speqg_counts * coun
         a.scalars = sc_dev;
         BatchView v{};
         v.bases = db->bases; v.inv = db->inv; v.qual = nullptr; v.grp_off = db->grp_off; v.len = db->len; v.n_reads = db->n_reads;
-        CK(launch_scan_direct(s->di->view, v, a, s->mode & M_PAIRED, 1, s->cfg_stats, s->compute));
+        CK(launch_scan_direct(s->view, v, a, s->mode & M_PAIRED, 1, s->cfg_stats, s->compute));
         unsigned long long sc[SC_COUNT];
         CK(cudaMemcpyAsync(sc, sc_dev, sizeof sc, cudaMemcpyDeviceToHost, s->compute));
         CK(cudaStreamSynchronize(s->compute));

@@ -5,23 +5,24 @@
 // reversed, sentinel appended.  The suffix array of that text is unique, so SA intervals here are identical to the
 // reference's at every backward-search step.
 //
-// Rank structure ("blocks"): the BWT is cut into blocks of 64 symbols; each block is ONE 32-byte sector:
-//     u32 cnt[4]   occurrences of A,C,G,T in bwt[0, 64*b)          (bit 31 of cnt[0] = block holds an exception)
-//     u32 lo[2]    bit plane 0 of the 2-bit codes (A0 C1 G2 T3): symbol j at bit j%32 of lo[j/32]
-//     u32 hi[2]    bit plane 1
-// so rank(i, c) costs exactly one sector load (one LDG.256) and the in-block count is two LOP3 + POPC per word.
-// BWT positions that hold N / delimiter / sentinel ("exceptions") are coded as 0 and listed in `exc_pos` (sorted);
-// only blocks with the flag bit need the correction, and only for c = A.
+// KBlock: everything one rolling-search iteration needs about 64 consecutive suffixes, in ONE 64-byte half cache line
+// (two 32-byte sectors, fetched by two LDG.256):
+//   sector 0  cnt[4]   occurrences of A,C,G,T in bwt[0, 64*b)
+//             lo, hi   the two bit planes of the 2-bit BWT codes (A0 C1 G2 T3), symbol j at bit j
+//   sector 1  e        bit j: lcp[64b+j] >= k-1      (filled per scan for the scan's k; zero in the stored index)
+//             chg      bit j: group of suffix 64b+j differs from the group of suffix 64b+j-1
+//             exc      bit j: bwt[64b+j] is N / delimiter / sentinel (coded 0 in the planes, never counted)
+//             chgcum   number of chg bits in [0, 64*b)
+// rank(i, c) = cnt[c] + popc(match_c & ~exc & below(i % 64)) -- one block, no exception list.
+// "The pattern shortened by its first symbol has the same SA interval" (the common case of a sliding k-mer window) is
+// e[lb] == 0 && e[rb+1] == 0, and otherwise the widened interval is found by a bit scan in the very same two blocks the
+// next rank step needs.  "All occurrences lie in one variant" (reference: src/fm_scanner.cpp:166-177 after locate())
+// is "no chg bit in (lb, rb]" = chgcum/popc arithmetic on those same two blocks.  So a window costs one round trip to
+// two half lines, plus one 2-byte group load when (and only when) the k-mer is unique to a variant.
 //
-// LCP structure: lcp[i] = min(127, longest common prefix of suffixes SA[i-1] and SA[i]) (lcp[0] = 0).  The SA interval
-// of a pattern shortened by its FIRST query symbol (= last symbol of the reversed pattern) is the maximal range around
-// the old interval whose inner lcp values are >= the new depth; this is what lets consecutive, overlapping k-mer
-// windows of a read share their search work (scan_core.h) while producing the very same intervals as k independent
-// backward-search steps per window.
-//
-// Group structure: gr[i] = {run_end, group}: group of the text that owns suffix SA[i] (kNoGroup for delimiter /
-// sentinel suffixes) and the last index of the maximal run of equal groups starting at i.  "All occurrences of a
-// k-mer lie in one variant" (reference: src/fm_scanner.cpp:166-177 after locate()) becomes gr[lb].run_end >= rb.
+// lcp[i] = min(127, longest common prefix of suffixes SA[i-1] and SA[i]) (lcp[0] = 0), one byte per suffix, is kept for
+// the uncommon contractions (after a mismatch, or when the widened interval leaves the two blocks).
+// grp[i]  = variant of the text that owns suffix SA[i] (u16; kNoGroup16 for delimiter / sentinel suffixes).
 #pragma once
 #include <cstdint>
 
@@ -34,42 +35,43 @@
 namespace speqb
 {
 constexpr uint32_t kBlockSyms = 64;
-constexpr uint32_t kExcFlag = 0x80000000u;
 constexpr uint32_t kNoGroup = 0xFFFFFFFFu;
+constexpr uint16_t kNoGroup16 = 0xFFFFu;
+constexpr uint32_t kMaxGroups = 65535;
 constexpr uint32_t kSymN = 4;       // text symbol of N
 constexpr uint32_t kSymDelim = 6;   // text symbol of the delimiter (sigma + 1, fm_index.hpp:285)
 constexpr uint32_t kMaxK = 127;     // lcp is stored in 7 bits; depth k-1 <= 126 must be representable
 constexpr uint32_t kLcpCap = 127;
 constexpr uint32_t kCodeN = 4;      // query code of N (back-check only); A0 C1 G2 T3
+constexpr uint32_t kLcpChunk = 32;  // the lcp array is read in 32-byte chunks (one LDG.256)
 
-struct __attribute__((aligned(32))) RankBlock
+struct __attribute__((aligned(64))) KBlock
 {
     uint32_t cnt[4];
     uint32_t lo[2];
     uint32_t hi[2];
+    uint32_t e[2];
+    uint32_t chg[2];
+    uint32_t exc[2];
+    uint32_t chgcum;
+    uint32_t pad;
 };
+static_assert(sizeof(KBlock) == 64, "KBlock must be 64 bytes");
 
-struct GroupRun
-{
-    uint32_t run_end;
-    uint32_t group;
-};
+constexpr uint32_t kCtabEnd = 8;
 
 // Device view of the index (passed to kernels by value).
 struct DevIndex
 {
-    const RankBlock * blocks;     // n/64 + 1 blocks
-    const uint8_t * lcp;          // n entries, padded to a multiple of 8 bytes (+8) with zeros
-    const GroupRun * gr;          // n entries
-    const uint32_t * exc_pos;     // sorted BWT positions holding a non-ACGT symbol
-    const uint32_t * n_pos;       // sorted BWT positions holding N
-    uint32_t n_exc;
+    const KBlock * blocks;        // n/64 + 1 blocks (for a scan: the copy whose e bits are filled for the scan's k)
+    const uint8_t * lcp;          // n entries, zero padded to a multiple of 32 bytes + 32, 32-byte aligned
+    const uint16_t * grp;         // n entries
+    const uint32_t * n_pos;       // sorted BWT positions holding N (rank of the symbol N; back-check only)
+    const uint32_t * ctab;        // 16 entries: [c] = C of query code c (A,C,G,T,N) = #text symbols smaller;
+                                  //             [kCtabEnd + c] = C of the next text symbol (exclusive end of the range)
     uint32_t n_npos;
     uint32_t n;                   // text length including the sentinel
-    uint32_t ctab[16];            // [c]: C of query code c (A,C,G,T,N) = #text symbols smaller; [kCtabEnd + c]: C of the
-                                  // next text symbol (exclusive end of the symbol's SA range)
 };
-constexpr uint32_t kCtabEnd = 8;
 
 // Device/host view of one packed batch of reads.  Read i owns 32-base groups [grp_off[i], grp_off[i+1]).
 //   bases[g]  u64: 32 x 2-bit codes     inv[g] u32: 1 bit per base (scan: N or phred <= cutoff; back-check: N)
@@ -83,5 +85,13 @@ struct BatchView
     const uint32_t * len;         // n_reads
     const int32_t * read_group;   // back-check only: group of the scaffold the read came from
     uint64_t n_reads;
+};
+
+// One unit of lane work in the back-check: windows [start, start + nwin) of text `read`.
+struct Segment
+{
+    uint32_t read;
+    uint32_t start;
+    uint32_t nwin;
 };
 }   // namespace speqb

@@ -42,7 +42,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
                       uint32_t V, uint32_t flags, HostIndex & h)
 {
     if (S == 0) throw api_error(SPEQG_EINVAL, "The text that is indexed cannot be empty.");
-    if (V == 0) throw api_error(SPEQG_EINVAL, "n_groups must be > 0");
+    if (V == 0 || V > kMaxGroups) throw api_error(SPEQG_EINVAL, "n_groups must be in [1, 65535]");
     uint64_t text_size = 0;
     bool all_empty = true;
     for (uint32_t i = 0; i < S; ++i)
@@ -92,49 +92,55 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
     h.C[0] = 0;
     for (int c = 1; c < 8; ++c) h.C[c] = h.C[c - 1] + cnt[c - 1];
 
-    // BWT -> blocks, exceptions.  bwt[i] = T[SA[i]-1], wrapping (sdsl construct_bwt.hpp:35-73)
+    // BWT -> KBlocks.  bwt[i] = T[SA[i]-1], wrapping (sdsl construct_bwt.hpp:35-73).  N / delimiter / sentinel are coded 0
+    // in the planes and flagged in the block's exc bits; cnt[] counts A,C,G,T only.
+    // Group of every suffix + change bits: chg[i] = group(i) != group(i-1), chg[0] = 1.
     uint64_t nblocks = n / kBlockSyms + 1;
-    h.blocks.assign(nblocks * 8, 0);
+    h.blocks.assign(nblocks, KBlock{});
+    h.grp.resize(n);
     static const int8_t code_of_sym[7] = {-1, 0, 1, 2, -1, 3, -1};
     uint32_t run[4] = {0, 0, 0, 0};
+    uint32_t chgcum = 0;
+    uint32_t prev_group = 0;
     for (uint64_t i = 0; i < n; ++i)
     {
         uint64_t b = i / kBlockSyms, j = i % kBlockSyms;
-        uint32_t * blk = &h.blocks[b * 8];
-        if (j == 0) { blk[0] |= run[0]; blk[1] = run[1]; blk[2] = run[2]; blk[3] = run[3]; }
+        KBlock & blk = h.blocks[b];
+        if (j == 0) { blk.cnt[0] = run[0]; blk.cnt[1] = run[1]; blk.cnt[2] = run[2]; blk.cnt[3] = run[3]; blk.chgcum = chgcum; }
         uint8_t sym = T[SA[i] ? SA[i] - 1 : n - 1];
         int8_t c2 = code_of_sym[sym];
         if (c2 < 0)
         {
-            blk[0] |= kExcFlag;
-            h.exc_pos.push_back((uint32_t)i);
+            blk.exc[j / 32] |= 1u << (j % 32);
+            ++h.n_exc;
             if (sym == kSymN) h.n_pos.push_back((uint32_t)i);
             c2 = 0;
         }
         else
             ++run[c2];
-        blk[4 + j / 32] |= uint32_t(c2 & 1) << (j % 32);
-        blk[6 + j / 32] |= uint32_t((c2 >> 1) & 1) << (j % 32);
+        blk.lo[j / 32] |= uint32_t(c2 & 1) << (j % 32);
+        blk.hi[j / 32] |= uint32_t((c2 >> 1) & 1) << (j % 32);
+        uint32_t g = owner[SA[i]];
+        h.grp[i] = g == kNoGroup ? kNoGroup16 : (uint16_t)g;
+        if (i == 0 || g != prev_group)
+        {
+            blk.chg[j / 32] |= 1u << (j % 32);
+            ++chgcum;
+        }
+        prev_group = g;
     }
     if (n % kBlockSyms == 0)
     {
-        uint32_t * blk = &h.blocks[(nblocks - 1) * 8];
-        blk[0] = run[0]; blk[1] = run[1]; blk[2] = run[2]; blk[3] = run[3];
+        KBlock & blk = h.blocks[nblocks - 1];
+        blk.cnt[0] = run[0]; blk.cnt[1] = run[1]; blk.cnt[2] = run[2]; blk.cnt[3] = run[3]; blk.chgcum = chgcum;
     }
-
-    // group runs over SA order
-    h.gr.resize(n);
-    for (uint64_t i = 0; i < n; ++i) h.gr[i].group = owner[SA[i]];
-    h.gr[n - 1].run_end = (uint32_t)(n - 1);
-    for (uint64_t i = n - 1; i-- > 0;)
-        h.gr[i].run_end = (h.gr[i].group == h.gr[i + 1].group) ? h.gr[i + 1].run_end : (uint32_t)i;
 
     // capped LCP array (Kasai et al. 2001, with the cap folded in: lcp[rank[i+1]] >= lcp[rank[i]] - 1 also holds for
     // min(cap, lcp)).  The sentinel is unique, so the symbol comparison stops before either suffix runs off the text.
     {
         std::vector<int32_t> rank(n);
         for (uint64_t i = 0; i < n; ++i) rank[SA[i]] = (int32_t)i;
-        h.lcp.assign(((n + 7) / 8) * 8 + 16, 0);
+        h.lcp.assign(lcp_padded_size(n), 0);
         uint32_t hh = 0;
         for (uint64_t i = 0; i < n; ++i)
         {
@@ -167,7 +173,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
 }
 
 // ---- cache file: own binary payload (the reference's .idx is a cereal+sdsl archive; byte compatibility is a later row)
-static const char kMagic[8] = {'S', 'P', 'E', 'Q', 'B', '2', '0', '1'};
+static const char kMagic[8] = {'S', 'P', 'E', 'Q', 'B', '2', '0', '2'};
 
 template <class T> static void wr(FILE * f, T const & v)
 {
@@ -202,7 +208,7 @@ void save_host_index(HostIndex const & h, std::string const & path, uint64_t off
         if (fwrite(kMagic, 1, 8, f) != 8) throw api_error(SPEQG_EIO, "short write");
         wr(f, h.n); wr(f, h.S); wr(f, h.V);
         for (int c = 0; c < 8; ++c) wr(f, h.C[c]);
-        wrv(f, h.blocks); wrv(f, h.gr); wrv(f, h.lcp); wrv(f, h.exc_pos); wrv(f, h.n_pos); wrv(f, h.group_of_text);
+        wr(f, h.n_exc); wrv(f, h.blocks); wrv(f, h.grp); wrv(f, h.lcp); wrv(f, h.n_pos); wrv(f, h.group_of_text);
         wrv(f, h.t_bases); wrv(f, h.t_inv); wrv(f, h.t_grp_off); wrv(f, h.t_len); wrv(f, h.sa);
     }
     catch (...) { fclose(f); throw; }
@@ -221,10 +227,10 @@ void load_host_index(std::string const & path, HostIndex & h, uint64_t offset)
         h = HostIndex{};
         rd(f, h.n); rd(f, h.S); rd(f, h.V);
         for (int c = 0; c < 8; ++c) rd(f, h.C[c]);
-        rdv(f, h.blocks); rdv(f, h.gr); rdv(f, h.lcp); rdv(f, h.exc_pos); rdv(f, h.n_pos); rdv(f, h.group_of_text);
+        rd(f, h.n_exc); rdv(f, h.blocks); rdv(f, h.grp); rdv(f, h.lcp); rdv(f, h.n_pos); rdv(f, h.group_of_text);
         rdv(f, h.t_bases); rdv(f, h.t_inv); rdv(f, h.t_grp_off); rdv(f, h.t_len); rdv(f, h.sa);
-        if (h.blocks.size() != (h.n / kBlockSyms + 1) * 8 || h.gr.size() != h.n || h.group_of_text.size() != h.S ||
-            h.lcp.size() != ((h.n + 7) / 8) * 8 + 16)
+        if (h.blocks.size() != h.n / kBlockSyms + 1 || h.grp.size() != h.n || h.group_of_text.size() != h.S ||
+            h.lcp.size() != lcp_padded_size(h.n))
             throw api_error(SPEQG_EIO, "inconsistent index payload");
     }
     catch (...) { fclose(f); throw; }

@@ -45,10 +45,58 @@ __device__ __forceinline__ SmemView smem_view(unsigned char * raw, uint32_t V)
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Rolling scan.  A lane owns one unit (read, read pair or text segment) at a time and runs a flat state machine: every
-// trip of the loop feeds ONE read position to roll_advance (at most one LCP contraction + one rank step), so lanes of
-// a warp stay convergent whatever their reads look like; a lane that finishes its unit fetches the next one.
+// Rolling scan.  A lane owns one unit (read, read pair or text segment) at a time and runs the flat state machine of
+// scan_core.h: every trip of the loop is ONE iteration of lane_plan -> loads -> lane_consume.  All loads of an
+// iteration are issued back to back before anything is consumed, so an iteration costs one round trip to L2 / HBM
+// whatever phase each lane is in, and the warp is re-converged at the top of every trip.
 // ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ld256_if(uint32_t * w, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %9, 0;\n\t@q ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]), "+r"(w[6]), "+r"(w[7])
+                 : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld64_if(uint64_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u64 %0, [%1];\n\t}" : "+l"(v) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld32_if(uint32_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
+}
+
+template <int MODE> struct DevEnv
+{
+    static constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
+    DevIndex const & ix;
+    BatchView const & b;
+    ScanArgs const & a;
+    SmemView sm;
+    __device__ __forceinline__ uint32_t load_grp(uint32_t i) const
+    {
+        uint32_t v;
+        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(v) : "l"(ix.grp + i));
+        return v;
+    }
+    __device__ __forceinline__ uint32_t npos_rank(uint32_t i) const { return lower_bound_u32(ix.n_pos, ix.n_npos, i); }
+    __device__ __forceinline__ double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
+    {
+        // window = positions [t_end-k, t_end); the left fold of src/fm_scanner.cpp:454, a / (1 - 1/pow(10, q/10)), with
+        // the denominators tabulated by the host's libm: IEEE division keeps every weight bit-exact
+        const uint8_t * q = b.qual + 32u * g0 + (t_end - k);
+        double w = 1.0;
+        for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
+        return w;
+    }
+    __device__ __forceinline__ void unique(uint32_t g, uint32_t n, double w) const
+    {
+        if (LOCAL) atomicAdd(&sm.w[g], w);
+        else atomicAdd(&sm.cnt[g], n);
+    }
+    __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(a.mult + lb, 1ull); }
+    __device__ __forceinline__ void backtotal(uint32_t g, uint32_t n) const { atomicAdd(&sm.tot[g], n); }
+};
+
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) scan_roll_kernel(const DevIndex ix, const BatchView b, const ScanArgs a, const int paired)
 {
@@ -67,126 +115,58 @@ __global__ void __launch_bounds__(kBlock) scan_roll_kernel(const DevIndex ix, co
     }
     __syncthreads();
 
-    const uint32_t k = a.k;
-    const uint64_t units = a.segs ? a.n_segs : (paired ? b.n_reads / 2 : b.n_reads);
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    ScanCfg cfg;
+    cfg.k = a.k;
+    cfg.units = BACK ? a.n_segs : (paired ? b.n_reads / 2 : b.n_reads);
+    cfg.stride = (uint64_t)gridDim.x * blockDim.x;
+    cfg.paired = BACK ? 0 : paired;
+    cfg.local = LOCAL;
+    cfg.record = RECORD;
+    cfg.back = BACK;
+    DevEnv<MODE> env{ix, b, a, sm};
 
-    unsigned long long c_total = 0, c_look = 0;
-    uint32_t c_amb = 0, c_reads = 0;
-    uint32_t agg_g = kNone, agg_n = 0;   // run-length aggregation of this lane's unique tallies
-    double agg_w = 0.0;
-
-    // unit state
-    bool active = false;
-    uint32_t mate = 0, gmin = kNone, gmax = 0;
-    // read state
-    uint64_t g0 = 0;
-    uint32_t t = 0, pend = 0, cw = kNone, winv = 0;
-    uint64_t wbase = 0;
-    RollState s;
-    roll_reset(ix, s);
+    Lane s;
+    lane_init(s, (uint64_t)blockIdx.x * blockDim.x + threadIdx.x);
+    Loads ld;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) ld.A.w[i] = ld.B.w[i] = 0u;
+    ld.rdw = 0; ld.rdi = 0; ld.flen = ld.fstart = ld.fgroup = 0; ld.fg0 = 0;
+    uint32_t seg[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
     while (true)
     {
-        if (!active)
+        __syncwarp();
+        if (!__any_sync(0xFFFFFFFFu, s.phase != PH_DONE)) break;
+        Plan p;
+        lane_plan(s, ix, b, cfg, p);
+        // ---- every load of this iteration, issued before anything is consumed
+        const void * a0 = p.blocks ? (const void *)p.pa : (const void *)p.pl;
+        const void * b0 = p.blocks ? (const void *)p.pb : (const void *)p.pr;
+        ld256_if(ld.A.w, a0, p.blocks || p.lcp_l);
+        ld256_if(ld.B.w, b0, p.blocks || p.lcp_r);
+        ld256_if(ld.A.w + 8, reinterpret_cast<const char *>(p.pa) + 32, p.blocks);
+        ld256_if(ld.B.w + 8, reinterpret_cast<const char *>(p.pb) + 32, p.blocks);
+        ld64_if(ld.rdw, p.pw, p.word);
+        ld32_if(ld.rdi, p.pi, p.word);
+        if (BACK)
         {
-            if (u >= units) break;
-            uint64_t r;
-            if (a.segs)
-            {
-                Segment sg = a.segs[u];
-                r = sg.read;
-                t = sg.start;
-                pend = sg.start + sg.nwin + k - 1u;
-                if (BACK) atomicAdd(&sm.tot[b.read_group[r]], sg.nwin);
-            }
-            else
-            {
-                r = paired ? 2 * u + mate : u;
-                uint32_t L = b.len[r];
-                t = 0;
-                pend = L >= k ? L : 0u;   // L < k: no windows (sliding view is empty)
-                ++c_reads;
-                if (L >= k) c_look += L - k + 1u;
-            }
-            g0 = b.grp_off[r];
-            cw = kNone;
-            roll_reset(ix, s);
-            active = true;
-        }
-        if (t < pend)
-        {
-            if ((t >> 5) != cw)
-            {
-                cw = t >> 5;
-                wbase = load_ro(b.bases + g0 + cw);
-                winv = load_ro(b.inv + g0 + cw);
-            }
-            uint32_t c = (uint32_t)(wbase >> (2u * (t & 31u))) & 3u;
-            bool ib = (winv >> (t & 31u)) & 1u;
-            if (BACK && ib) c = kCodeN;
-            uint32_t res = roll_advance(ix, ctab, k, s, c, BACK ? false : ib);
-            if (res & ROLL_CONSUMED) ++t;
-            if (res & ROLL_WINDOW) ++c_total;
-            if (res & ROLL_HIT)
-            {
-                if (RECORD) atomicAdd(a.mult + s.lb, 1ull);
-                GroupRun g = load_gr(ix.gr + s.lb);
-                if (g.run_end >= s.rb)
-                {
-                    gmin = min(gmin, g.group);
-                    gmax = max(gmax, g.group);
-                    if (LOCAL)
-                    {
-                        // window = positions [t-k, t); the left fold of src/fm_scanner.cpp:454, a / (1 - 1/pow(10, q/10)),
-                        // with the denominators tabulated by the host's libm: IEEE division keeps every weight bit-exact
-                        const uint8_t * q = b.qual + 32u * g0 + (t - k);
-                        double w = 1.0;
-                        for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
-                        if (g.group != agg_g)
-                        {
-                            if (agg_g != kNone) atomicAdd(&sm.w[agg_g], agg_w);
-                            agg_g = g.group;
-                            agg_w = 0.0;
-                        }
-                        agg_w += w;
-                    }
-                    else
-                    {
-                        if (g.group != agg_g)
-                        {
-                            if (agg_g != kNone) atomicAdd(&sm.cnt[agg_g], agg_n);
-                            agg_g = g.group;
-                            agg_n = 0;
-                        }
-                        ++agg_n;
-                    }
-                }
-            }
+            ld256_if(seg, a.segs + (p.fetch ? p.fr : 0), p.fetch);
+            ld.fg0 = u64of(seg[0], seg[1]);
+            ld.fstart = seg[2];
+            ld.flen = seg[3];
+            ld.fgroup = seg[4];
         }
         else
         {
-            // read finished
-            if (!a.segs && paired && mate == 0) mate = 1;
-            else
-            {
-                if (!BACK && gmin != kNone && gmin != gmax) ++c_amb;
-                gmin = kNone;
-                gmax = 0;
-                mate = 0;
-                u += stride;
-            }
-            active = false;
+            ld32_if(ld.flen, b.len + p.fr, p.fetch);
+            ld64_if(ld.fg0, b.grp_off + p.fr, p.fetch);
         }
+        // ---- consume
+        lane_consume(s, ld, ix, ctab, cfg, env);
     }
-    if (agg_g != kNone)
-    {
-        if (LOCAL) atomicAdd(&sm.w[agg_g], agg_w);
-        else atomicAdd(&sm.cnt[agg_g], agg_n);
-    }
+    lane_flush_agg(s, cfg, env);
     __syncwarp();
-    unsigned long long v0 = warp_sum(c_total), v1 = warp_sum(c_amb), v2 = warp_sum(c_look), v3 = warp_sum(c_reads);
+    unsigned long long v0 = warp_sum(s.c_total), v1 = warp_sum(s.c_amb), v2 = warp_sum(s.c_look), v3 = warp_sum(s.c_reads);
     if ((threadIdx.x & 31) == 0 && !BACK)
     {
         if (v0) atomicAdd(a.scalars + SC_TOTAL, v0);
@@ -276,12 +256,12 @@ __global__ void __launch_bounds__(kBlock) scan_direct_kernel(const DevIndex ix, 
                     ++c_total;
                     if (!direct_window(ix, ctab, b.bases, b.inv, g0, s, k, lb, rb, steps)) continue;
                     if (record) atomicAdd(a.mult + lb, 1ull);
-                    GroupRun g = load_gr(ix.gr + lb);
-                    if (g.run_end >= rb)
+                    uint32_t grp = interval_group(ix, lb, rb);
+                    if (grp != kNoGroup)
                     {
-                        gmin = min(gmin, g.group);
-                        gmax = max(gmax, g.group);
-                        atomicAdd(&sm.cnt[g.group], 1u);
+                        gmin = min(gmin, grp);
+                        gmax = max(gmax, grp);
+                        atomicAdd(&sm.cnt[grp], 1u);
                     }
                 }
             }
@@ -327,6 +307,20 @@ __global__ void __launch_bounds__(kBlock) scan_direct_kernel(const DevIndex ix, 
 // reference multiplies h by is the same for every g of one window and cancels in a[g]/s.  Windows with the same
 // k-mer share one SA interval, so the sum over windows is a sum over recorded interval starts times multiplicity.
 // ---------------------------------------------------------------------------------------------------------------
+// smallest p' > p with a group change at p' (chg bit), capped at `limit` (exclusive upper bound of the search)
+__device__ __forceinline__ uint32_t next_change(const KBlock * blocks, uint32_t p, uint32_t limit)
+{
+    uint32_t q = p + 1u;
+    while (q < limit)
+    {
+        const KBlock * kb = blocks + (q >> 6);
+        uint64_t m = u64of(load_ro(&kb->chg[0]), load_ro(&kb->chg[1])) & from64(q & 63u);
+        if (m) return min(limit, (q & ~63u) + ctz64(m));
+        q = (q & ~63u) + 64u;
+    }
+    return limit;
+}
+
 __global__ void __launch_bounds__(kBlock) refine_kernel(const DevIndex ix, const uint32_t k, const unsigned long long * __restrict__ mult,
                                                         const double * __restrict__ percent, const int32_t * __restrict__ group_counts,
                                                         const uint32_t V, double * __restrict__ partial)
@@ -347,28 +341,54 @@ __global__ void __launch_bounds__(kBlock) refine_kernel(const DevIndex ix, const
     {
         unsigned long long m = mult[i];
         if (m == 0ull) continue;
+        // the k-mer's interval [i, rb]: it ends before the first lcp < k
         uint32_t rb = (uint32_t)i;
         while (rb + 1u < ix.n && load_ro(ix.lcp + rb + 1u) >= k) ++rb;
         double s = 0.0;
         for (uint32_t p = (uint32_t)i; p <= rb;)
         {
-            GroupRun g = load_gr(ix.gr + p);
-            uint32_t e = min(g.run_end, rb);
-            s += (double)(e - p + 1u) * s_p[g.group] / s_c[g.group];
-            p = e + 1u;
+            uint32_t e = next_change(ix.blocks, p, rb + 1u);   // run of one group = [p, e)
+            uint32_t g = load_ro(ix.grp + p);
+            s += (double)(e - p) * s_p[g] / s_c[g];
+            p = e;
         }
         if (!(s > 0.0)) continue;
         for (uint32_t p = (uint32_t)i; p <= rb;)
         {
-            GroupRun g = load_gr(ix.gr + p);
-            uint32_t e = min(g.run_end, rb);
-            double av = (double)(e - p + 1u) * s_p[g.group] / s_c[g.group];
-            atomicAdd(&s_t[g.group], (double)m * (av / s));
-            p = e + 1u;
+            uint32_t e = next_change(ix.blocks, p, rb + 1u);
+            uint32_t g = load_ro(ix.grp + p);
+            double av = (double)(e - p) * s_p[g] / s_c[g];
+            atomicAdd(&s_t[g], (double)m * (av / s));
+            p = e;
         }
     }
     __syncthreads();
     for (uint32_t g = threadIdx.x; g < V; g += blockDim.x) partial[(size_t)blockIdx.x * V + g] = s_t[g];
+}
+
+// copy the rank blocks and fill the e bits for one k: bit j of block b = (lcp[64b+j] >= k-1)
+__global__ void __launch_bounds__(kBlock) fill_e_kernel(const KBlock * __restrict__ src, KBlock * __restrict__ dst, const uint8_t * __restrict__ lcp,
+                                                        const uint32_t n, const uint32_t k)
+{
+    const uint32_t nblocks = n / kBlockSyms + 1u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; blk < nblocks; blk += nwarps)
+    {
+        const uint32_t * s32 = reinterpret_cast<const uint32_t *>(src + blk);
+        uint32_t * d32 = reinterpret_cast<uint32_t *>(dst + blk);
+        uint32_t i0 = blk * 64u + lane, i1 = i0 + 32u;
+        bool e0 = i0 < n && (uint32_t)lcp[i0] + 1u >= k;
+        bool e1 = i1 < n && (uint32_t)lcp[i1] + 1u >= k;
+        uint32_t w0 = __ballot_sync(0xFFFFFFFFu, e0), w1 = __ballot_sync(0xFFFFFFFFu, e1);
+        if (lane < 16)
+        {
+            uint32_t v = s32[lane];
+            if (lane == 8) v = w0;
+            if (lane == 9) v = w1;
+            d32[lane] = v;
+        }
+    }
 }
 
 __global__ void refine_reduce_kernel(const double * __restrict__ partial, int nparts, uint32_t V, double * __restrict__ tkpg)
@@ -558,6 +578,12 @@ cudaError_t launch_pack(const uint8_t * seq, const uint8_t * qual, uint64_t off0
     uint64_t want = (n_reads * 32 + kBlock - 1) / kBlock;
     int grid = (int)std::min<uint64_t>(want, (uint64_t)sm_count() * 16);
     pack_kernel<<<grid, kBlock, 0, st>>>(seq, qual, off0, offsets, n_reads, encoding, phred_cutoff, n_only, bases, inv, qual_out, grp_off, len, bad);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fill_e(const KBlock * src, KBlock * dst, const uint8_t * lcp, uint32_t n, uint32_t k, cudaStream_t st)
+{
+    fill_e_kernel<<<sm_count() * 8, kBlock, 0, st>>>(src, dst, lcp, n, k);
     return cudaGetLastError();
 }
 

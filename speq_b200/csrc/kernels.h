@@ -17,12 +17,15 @@ enum : int
 // indices into the u64 scalar counter block
 enum : int { SC_TOTAL = 0, SC_AMBIG = 1, SC_LOOKUPS = 2, SC_STEPS = 3, SC_HIT = 4, SC_OCC = 5, SC_OCCSEC = 6, SC_READS = 7, SC_COUNT = 8 };
 
-// One unit of lane work: windows [start, start + nwin) of read `read` (positions [start, start + nwin + k - 1)).
-struct Segment
+// One unit of lane work in the back-check, as the kernel fetches it (one 32-byte load): windows [start, start + nwin) of the
+// text whose packed bases start at 32-base group g0 and whose variant is `group`.
+struct __attribute__((aligned(32))) SegmentX
 {
-    uint32_t read;
+    uint64_t g0;
     uint32_t start;
     uint32_t nwin;
+    uint32_t group;
+    uint32_t pad[3];
 };
 
 struct ScanArgs
@@ -35,7 +38,7 @@ struct ScanArgs
     unsigned long long * scalars;     // [SC_COUNT]
     unsigned long long * mult;        // [n] multiplicity of the valid k-mer windows whose interval starts at lb
     const double * qden;              // [42] 1 - 1/pow(10, q/10), host libm values   (local mode)
-    const Segment * segs;             // optional segment table (back-check); null: one segment per read / pair
+    const SegmentX * segs;             // optional segment table (back-check); null: one segment per read / pair
     uint64_t n_segs;
 };
 
@@ -63,5 +66,7 @@ cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V,
 cudaError_t launch_pack(const uint8_t * seq, const uint8_t * qual, uint64_t off0, const uint64_t * offsets, uint64_t n_reads,
                         int encoding, uint32_t phred_cutoff, int n_only, uint64_t * bases, uint32_t * inv, uint8_t * qual_out,
                         const uint64_t * grp_off, uint32_t * len, unsigned long long * bad, cudaStream_t st);
+// per-scan specialisation of the rank blocks: copy `src` to `dst` and fill the e bits (lcp >= k-1) for this k
+cudaError_t launch_fill_e(const KBlock * src, KBlock * dst, const uint8_t * lcp, uint32_t n, uint32_t k, cudaStream_t st);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

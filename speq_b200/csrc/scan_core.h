@@ -1,5 +1,5 @@
 // scan_core.h -- per-lane arithmetic of the scan hot path: rank on the blocked BWT, one backward-search step, the
-// LCP contraction, the rolling k-mer window and the from-the-root ("direct") window search.
+// LCP contraction, and the rolling k-mer window as a flat, one-round-trip-per-iteration state machine.
 //
 // Everything here is __host__ __device__: kernels.cu runs it on the GPU (the product path); tests/sim compiles the same
 // header with g++ as a white-box debugging aid (never shipped, never linked into libspeq_cuda.so).
@@ -19,35 +19,63 @@
 namespace speqb
 {
 #if defined(__CUDA_ARCH__)
-SPEQB_HD uint32_t popc32(uint32_t x) { return (uint32_t)__popc(x); }
+SPEQB_HD uint32_t popc64(uint64_t x) { return (uint32_t)__popcll(x); }
 SPEQB_HD uint32_t clz64(uint64_t x) { return (uint32_t)__clzll((long long)x); }
 SPEQB_HD uint32_t ctz64(uint64_t x) { return (uint32_t)__ffsll((long long)x) - 1u; }
-SPEQB_HD RankBlock load_block(const RankBlock * p)
-{
-    RankBlock b;
-    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(b.cnt[0]), "=r"(b.cnt[1]), "=r"(b.cnt[2]), "=r"(b.cnt[3]), "=r"(b.lo[0]), "=r"(b.lo[1]),
-                   "=r"(b.hi[0]), "=r"(b.hi[1])
-                 : "l"(p));
-    return b;
-}
+SPEQB_HD uint32_t clz32(uint32_t x) { return (uint32_t)__clz((int)x); }
+SPEQB_HD uint32_t ctz32(uint32_t x) { return (uint32_t)__ffs((int)x) - 1u; }
 template <class T> SPEQB_HD T load_ro(const T * p) { return __ldg(p); }
-SPEQB_HD GroupRun load_gr(const GroupRun * p)
-{
-    uint2 v = __ldg(reinterpret_cast<const uint2 *>(p));
-    GroupRun g;
-    g.run_end = v.x;
-    g.group = v.y;
-    return g;
-}
 #else
-SPEQB_HD uint32_t popc32(uint32_t x) { return (uint32_t)__builtin_popcount(x); }
+SPEQB_HD uint32_t popc64(uint64_t x) { return (uint32_t)__builtin_popcountll(x); }
 SPEQB_HD uint32_t clz64(uint64_t x) { return (uint32_t)__builtin_clzll(x); }
 SPEQB_HD uint32_t ctz64(uint64_t x) { return (uint32_t)__builtin_ctzll(x); }
-SPEQB_HD RankBlock load_block(const RankBlock * p) { return *p; }
+SPEQB_HD uint32_t clz32(uint32_t x) { return (uint32_t)__builtin_clz(x); }
+SPEQB_HD uint32_t ctz32(uint32_t x) { return (uint32_t)__builtin_ctz(x); }
 template <class T> SPEQB_HD T load_ro(const T * p) { return *p; }
-SPEQB_HD GroupRun load_gr(const GroupRun * p) { return *p; }
 #endif
+
+SPEQB_HD uint64_t u64of(uint32_t lo, uint32_t hi) { return (uint64_t)lo | ((uint64_t)hi << 32); }
+SPEQB_HD uint64_t below64(uint32_t j) { return (1ull << j) - 1ull; }   // bits [0, j), j in [0, 63]
+SPEQB_HD uint64_t upto64(uint32_t j) { return (2ull << j) - 1ull; }    // bits [0, j], j in [0, 63]
+SPEQB_HD uint64_t from64(uint32_t j) { return ~0ull << j; }            // bits [j, 63]
+
+// One KBlock in registers: w[0..3] cnt, w[4..5] lo, w[6..7] hi, w[8..9] e, w[10..11] chg, w[12..13] exc, w[14] chgcum.
+// (Indexed with compile-time constants only, so it stays in registers.)
+struct BlkRegs
+{
+    uint32_t w[16];
+};
+
+SPEQB_HD BlkRegs load_kblock(const KBlock * p)
+{
+    BlkRegs b;
+#if defined(__CUDA_ARCH__)
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(b.w[0]), "=r"(b.w[1]), "=r"(b.w[2]), "=r"(b.w[3]), "=r"(b.w[4]), "=r"(b.w[5]), "=r"(b.w[6]), "=r"(b.w[7])
+                 : "l"(p));
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(b.w[8]), "=r"(b.w[9]), "=r"(b.w[10]), "=r"(b.w[11]), "=r"(b.w[12]), "=r"(b.w[13]), "=r"(b.w[14]), "=r"(b.w[15])
+                 : "l"(reinterpret_cast<const char *>(p) + 32));
+#else
+    const uint32_t * s = reinterpret_cast<const uint32_t *>(p);
+    for (int i = 0; i < 16; ++i) b.w[i] = s[i];
+#endif
+    return b;
+}
+
+// occurrences of query code c (A0 C1 G2 T3) in bwt[0, 64*block + j), j in [0, 63]
+SPEQB_HD uint32_t blk_rank(BlkRegs const & b, uint32_t c, uint32_t j)
+{
+    uint64_t lo = u64of(b.w[4], b.w[5]), hi = u64of(b.w[6], b.w[7]), exc = u64of(b.w[12], b.w[13]);
+    uint64_t xl = (c & 1u) ? 0ull : ~0ull, xh = (c & 2u) ? 0ull : ~0ull;
+    uint64_t m = (lo ^ xl) & (hi ^ xh) & ~exc & below64(j);
+    uint32_t base = c == 0u ? b.w[0] : (c == 1u ? b.w[1] : (c == 2u ? b.w[2] : b.w[3]));
+    return base + popc64(m);
+}
+// number of group changes in [0, 64*block + j), j in [0, 63]
+SPEQB_HD uint32_t blk_chg_before(BlkRegs const & b, uint32_t j) { return b.w[14] + popc64(u64of(b.w[10], b.w[11]) & below64(j)); }
+// number of group changes in [0, 64*block + j], j in [0, 63]
+SPEQB_HD uint32_t blk_chg_upto(BlkRegs const & b, uint32_t j) { return b.w[14] + popc64(u64of(b.w[10], b.w[11]) & upto64(j)); }
 
 // first index in sorted a[0, n) whose value is >= x
 SPEQB_HD uint32_t lower_bound_u32(const uint32_t * a, uint32_t n, uint32_t x)
@@ -61,40 +89,8 @@ SPEQB_HD uint32_t lower_bound_u32(const uint32_t * a, uint32_t n, uint32_t x)
     return lo;
 }
 
-// symbols with 2-bit code c among the first j (0..63) symbols of a block; exceptions are coded 0 and counted as A here
-SPEQB_HD uint32_t block_count(RankBlock const & b, uint32_t c, uint32_t j)
-{
-    uint32_t m0 = j >= 32u ? 0xFFFFFFFFu : ((1u << j) - 1u);
-    uint32_t m1 = j <= 32u ? 0u : ((1u << (j - 32u)) - 1u);
-    uint32_t xl = (c & 1u) ? 0u : 0xFFFFFFFFu;
-    uint32_t xh = (c & 2u) ? 0u : 0xFFFFFFFFu;
-    uint32_t w0 = (b.lo[0] ^ xl) & (b.hi[0] ^ xh) & m0;
-    uint32_t w1 = (b.lo[1] ^ xl) & (b.hi[1] ^ xh) & m1;
-    return popc32(w0) + popc32(w1);
-}
-
-// rank(i, c): occurrences of query code c (A0 C1 G2 T3) in bwt[0, i), 0 <= i <= n, given the block that holds i
-SPEQB_HD uint32_t rank_in(DevIndex const & ix, RankBlock const & b, uint32_t i, uint32_t c)
-{
-    uint32_t base = b.cnt[c];
-    uint32_t r = block_count(b, c, i & (kBlockSyms - 1u));
-    if (c == 0u)
-    {
-        if (base & kExcFlag)
-        {
-            base &= ~kExcFlag;
-            uint32_t start = i & ~(kBlockSyms - 1u);
-            if (i != start)
-                r -= lower_bound_u32(ix.exc_pos, ix.n_exc, i) - lower_bound_u32(ix.exc_pos, ix.n_exc, start);
-        }
-    }
-    return base + r;
-}
-
-// One backward-search step with query code c (0..3, or kCodeN).  Returns false (interval untouched) when the extended
-// pattern does not occur.
-// ctab: C[c] at ctab[c], Cend[c] at ctab[kCtabEnd + c] (a shared-memory copy on the device: indexing the kernel
-// parameter struct dynamically would spill it to local memory).
+// One backward-search step with query code c (0..3, or kCodeN), loading its blocks itself (direct search, host tools).
+// Returns false (interval untouched) when the extended pattern does not occur.
 SPEQB_HD bool fm_step(DevIndex const & ix, const uint32_t * ctab, uint32_t & lb, uint32_t & rb, uint32_t c)
 {
     uint32_t nl, nr;   // nr exclusive
@@ -112,10 +108,10 @@ SPEQB_HD bool fm_step(DevIndex const & ix, const uint32_t * ctab, uint32_t & lb,
     else
     {
         uint32_t bl = lb >> 6, br = (rb + 1u) >> 6;
-        RankBlock B = load_block(ix.blocks + bl);
-        nl = cc + rank_in(ix, B, lb, c);
-        if (br != bl) B = load_block(ix.blocks + br);
-        nr = cc + rank_in(ix, B, rb + 1u, c);
+        BlkRegs B = load_kblock(ix.blocks + bl);
+        nl = cc + blk_rank(B, c, lb & 63u);
+        if (br != bl) B = load_kblock(ix.blocks + br);
+        nr = cc + blk_rank(B, c, (rb + 1u) & 63u);
     }
     if (nr <= nl) return false;
     lb = nl;
@@ -123,102 +119,19 @@ SPEQB_HD bool fm_step(DevIndex const & ix, const uint32_t * ctab, uint32_t & lb,
     return true;
 }
 
-// high bit of each byte set iff that byte < dd (bytes <= 127, 1 <= dd <= 127)
-SPEQB_HD uint64_t lcp_lt_mask(uint64_t w, uint32_t dd)
+// bit i set iff byte i of the 32-byte chunk (8 words) is < dd (bytes <= 127, 1 <= dd <= 127)
+SPEQB_HD uint32_t lcp_lt_bits(const uint32_t * w, uint32_t dd)
 {
-    const uint64_t H = 0x8080808080808080ull, L = 0x0101010101010101ull;
-    return ~((w | H) - (uint64_t)dd * L) & H;
-}
-
-// Shorten the pattern of interval [lb, rb] to depth dd (drop query symbols from the LEFT of the window): the result is
-// the maximal range around [lb, rb] whose inner lcp values are all >= dd.
-SPEQB_HD void fm_contract(DevIndex const & ix, uint32_t & lb, uint32_t & rb, uint32_t dd)
-{
-    if (dd == 0u)
+    uint32_t out = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
     {
-        lb = 0u;
-        rb = ix.n - 1u;
-        return;
+        const uint64_t H = 0x8080808080808080ull, L = 0x0101010101010101ull;
+        uint64_t x = u64of(w[2 * i], w[2 * i + 1]);
+        uint64_t m = (~((x | H) - (uint64_t)dd * L) & H) >> 7;            // bit 0 of byte b set iff byte b < dd
+        out |= (uint32_t)((m * 0x0102040810204080ull) >> 56) << (8 * i);   // gather the 8 byte flags into 8 bits
     }
-    const uint64_t * lw = reinterpret_cast<const uint64_t *>(ix.lcp);
-    uint32_t wl = lb >> 3, wr = (rb + 1u) >> 3;
-    uint64_t first = load_ro(lw + wl);
-    uint64_t second = (wr == wl) ? first : load_ro(lw + wr);
-    // left boundary: largest i <= lb with lcp[i] < dd (lcp[0] = 0 stops the scan)
-    uint64_t m = lcp_lt_mask(first, dd) & (~0ull >> (8u * (7u - (lb & 7u))));
-    while (m == 0ull)
-    {
-        --wl;
-        m = lcp_lt_mask(load_ro(lw + wl), dd);
-    }
-    lb = wl * 8u + ((63u - clz64(m)) >> 3);
-    // right boundary: smallest j > rb with lcp[j] < dd (zero padding behind n stops the scan)
-    m = lcp_lt_mask(second, dd) & (~0ull << (8u * ((rb + 1u) & 7u)));
-    while (m == 0ull)
-    {
-        ++wr;
-        m = lcp_lt_mask(load_ro(lw + wr), dd);
-    }
-    rb = wr * 8u + (ctz64(m) >> 3) - 1u;
-}
-
-// ---- rolling window --------------------------------------------------------------------------------------------
-struct RollState
-{
-    uint32_t lb, rb;      // SA interval of the current pattern
-    uint32_t d;           // its length (<= k)
-    uint32_t run;         // consecutive searchable positions ending at the previous position (window validity)
-    uint32_t retry;       // last extension failed: contract before trying the same position again
-};
-
-SPEQB_HD void roll_reset(DevIndex const & ix, RollState & s)
-{
-    s.lb = 0u;
-    s.rb = ix.n - 1u;
-    s.d = 0u;
-    s.run = 0u;
-    s.retry = 0u;
-}
-
-// Result of one roll_advance call
-enum : uint32_t
-{
-    ROLL_CONSUMED = 1u,   // the position was consumed (advance t)
-    ROLL_WINDOW = 2u,     // a valid window [t-k+1, t] ends at this position (counts towards total_kmers)
-    ROLL_HIT = 4u         // ... and it occurs in the text: s.lb, s.rb is its SA interval
-};
-
-// Feed read position t (query code c, `inv` = position cannot be part of a counted window and resets the search).
-// One call performs at most one contraction and one step, so lanes of a warp stay convergent; a failed extension
-// returns 0 and must be called again with the same position.
-SPEQB_HD uint32_t roll_advance(DevIndex const & ix, const uint32_t * ctab, uint32_t k, RollState & s, uint32_t c, bool inv)
-{
-    if (inv)
-    {
-        roll_reset(ix, s);
-        return ROLL_CONSUMED;
-    }
-    if (s.retry || s.d == k)
-    {
-        s.d -= 1u;
-        fm_contract(ix, s.lb, s.rb, s.d);
-        s.retry = 0u;
-    }
-    bool ok = fm_step(ix, ctab, s.lb, s.rb, c);
-    if (ok) s.d += 1u;
-    else if (s.d != 0u)
-    {
-        s.retry = 1u;
-        return 0u;
-    }
-    s.run += 1u;
-    uint32_t r = ROLL_CONSUMED;
-    if (s.run >= k)
-    {
-        r |= ROLL_WINDOW;
-        if (s.d == k) r |= ROLL_HIT;
-    }
-    return r;
+    return out;
 }
 
 // ---- packed read access ----------------------------------------------------------------------------------------
@@ -248,5 +161,311 @@ SPEQB_HD bool direct_window(DevIndex const & ix, const uint32_t * ctab, const ui
         if (!fm_step(ix, ctab, lb, rb, c)) return false;
     }
     return true;
+}
+
+// "every occurrence in [lb, rb] belongs to one variant" + that variant (kNoGroup when not)
+SPEQB_HD uint32_t interval_group(DevIndex const & ix, uint32_t lb, uint32_t rb)
+{
+    BlkRegs A = load_kblock(ix.blocks + (lb >> 6));
+    uint32_t cl = blk_chg_upto(A, lb & 63u);
+    BlkRegs B = load_kblock(ix.blocks + ((rb + 1u) >> 6));
+    uint32_t cr = blk_chg_before(B, (rb + 1u) & 63u);
+    return cl == cr ? (uint32_t)load_ro(ix.grp + lb) : kNoGroup;
+}
+
+// ================================================================================================================
+// Rolling window as a flat state machine.  One call of lane_plan + (loads) + lane_consume = one ITERATION; every
+// iteration needs at most ONE round trip to memory, whatever the lane is doing, so the 32 lanes of a warp run it in
+// lock step (the kernel re-converges them with __syncwarp at the top of the loop):
+//   PH_FETCH  pick the next unit (read, pair or text segment): loads its length / first group
+//   PH_STEP   loads the two KBlocks at lb and rb+1; resolves the uniqueness of the previous window's hit; contracts
+//             d == k to k-1 with the e bits; performs the rank step for the next base
+//   PH_LCP    general contraction (after a failed extension, or when the e-bit scan leaves the two blocks): scans one
+//             32-byte lcp chunk per side per iteration until both boundaries are found
+// ================================================================================================================
+enum : uint32_t { PH_FETCH = 0, PH_STEP = 1, PH_LCP = 2, PH_DONE = 3 };
+enum : uint32_t
+{
+    LF_PENDING = 1u,   // the last step produced a hit whose group uniqueness is not yet known
+    LF_HAVE_G = 2u,    // a group load is in flight / waiting in `gval`
+    LF_MATE2 = 4u,     // paired: the second mate of the unit is being scanned
+    LF_LFOUND = 8u,    // PH_LCP: left boundary found
+    LF_RFOUND = 16u    // PH_LCP: right boundary found
+};
+
+struct Lane
+{
+    uint32_t phase, flags;
+    uint32_t lb, rb, d, run;
+    uint32_t t, pend;
+    uint32_t cw, winv;
+    uint64_t wbase, g0;
+    uint64_t u;
+    uint32_t rgroup;        // back-check: variant of the text being scanned
+    uint32_t cl, cr;        // PH_LCP: chunk indices still to scan; then the boundaries found
+    uint32_t nlb, nrb1;
+    uint32_t gval, gt;      // group of the last unique hit (load result) and the window end it belongs to
+    uint32_t gmin, gmax;    // unit-level ambiguity state
+    uint32_t agg_g, agg_n;  // run-length aggregation of this lane's unique tallies
+    double agg_w;
+    unsigned long long c_total, c_look;
+    uint32_t c_amb, c_reads;
+};
+
+struct Plan
+{
+    bool blocks, word, lcp_l, lcp_r, fetch;
+    const KBlock * pa;
+    const KBlock * pb;
+    const uint64_t * pw;
+    const uint32_t * pi;
+    const uint8_t * pl;
+    const uint8_t * pr;
+    uint64_t fr;   // read (or segment) index to fetch
+};
+
+struct Loads
+{
+    BlkRegs A, B;           // KBlocks at lb / rb+1; in PH_LCP A.w[0..7] / B.w[0..7] hold the left / right lcp chunk
+    uint64_t rdw;
+    uint32_t rdi;
+    uint32_t flen, fstart, fgroup;
+    uint64_t fg0;
+};
+
+struct ScanCfg
+{
+    uint32_t k;
+    uint64_t units, stride;   // units to process, distance between two units of one lane
+    int paired, local, record, back;
+};
+
+SPEQB_HD void lane_init(Lane & s, uint64_t first_unit)
+{
+    s.phase = PH_FETCH; s.flags = 0; s.lb = 0; s.rb = 0; s.d = 0; s.run = 0; s.t = 0; s.pend = 0; s.cw = 0xFFFFFFFFu; s.winv = 0;
+    s.wbase = 0; s.g0 = 0; s.u = first_unit; s.rgroup = 0; s.cl = s.cr = s.nlb = s.nrb1 = 0; s.gval = 0; s.gt = 0;
+    s.gmin = kNoGroup; s.gmax = 0; s.agg_g = kNoGroup; s.agg_n = 0; s.agg_w = 0.0; s.c_total = s.c_look = 0; s.c_amb = s.c_reads = 0;
+}
+
+SPEQB_HD void lane_plan(Lane const & s, DevIndex const & ix, BatchView const & b, ScanCfg const & cfg, Plan & p)
+{
+    p.blocks = p.word = p.lcp_l = p.lcp_r = p.fetch = false;
+    p.pa = p.pb = ix.blocks; p.pw = b.bases; p.pi = b.inv; p.pl = p.pr = ix.lcp; p.fr = 0;
+    if (s.phase == PH_STEP)
+    {
+        bool stepping = s.t < s.pend;
+        p.blocks = (s.flags & LF_PENDING) || (stepping && s.d != 0u);
+        p.pa = ix.blocks + (s.lb >> 6);
+        p.pb = ix.blocks + ((s.rb + 1u) >> 6);
+        p.word = stepping && (s.t >> 5) != s.cw;
+        p.pw = b.bases + s.g0 + (s.t >> 5);
+        p.pi = b.inv + s.g0 + (s.t >> 5);
+    }
+    else if (s.phase == PH_LCP)
+    {
+        p.lcp_l = !(s.flags & LF_LFOUND);
+        p.lcp_r = !(s.flags & LF_RFOUND);
+        p.pl = ix.lcp + (size_t)s.cl * kLcpChunk;
+        p.pr = ix.lcp + (size_t)s.cr * kLcpChunk;
+    }
+    else if (s.phase == PH_FETCH)
+    {
+        p.fetch = s.u < cfg.units;
+        p.fr = cfg.back ? s.u : (cfg.paired ? 2 * s.u + ((s.flags & LF_MATE2) ? 1u : 0u) : s.u);
+    }
+}
+
+// Env supplies the side effects: group / quality loads, tallies, multiplicity recording.
+//   uint32_t env.load_grp(i)                      group of suffix i
+//   uint32_t env.npos_rank(i)                     # N in bwt[0, i)
+//   double   env.weight(g0, t_end, k)             local-mode weight of the window ending (exclusive) at t_end
+//   void     env.unique(group, n, w)              add n (global / back-check) or w (local) to the variant's tally
+//   void     env.record(lb)                       one more valid window whose k-mer interval starts at lb
+//   void     env.backtotal(group, nwin)           back-check: windows presented for a variant
+template <class Env>
+SPEQB_HD void lane_flush_agg(Lane & s, ScanCfg const & cfg, Env & env)
+{
+    if (s.agg_g != kNoGroup) env.unique(s.agg_g, s.agg_n, s.agg_w);
+    s.agg_g = kNoGroup;
+    s.agg_n = 0;
+    s.agg_w = 0.0;
+}
+
+template <class Env>
+SPEQB_HD void lane_take_group(Lane & s, ScanCfg const & cfg, Env & env)
+{
+    // consume the group of the last unique hit (src/fm_scanner.cpp:178-191: ++unique_kmers[which_hit]; ambiguity state)
+    uint32_t g = s.gval;
+    s.flags &= ~LF_HAVE_G;
+    s.gmin = g < s.gmin ? g : s.gmin;
+    s.gmax = g > s.gmax ? g : s.gmax;
+    if (g != s.agg_g)
+    {
+        lane_flush_agg(s, cfg, env);
+        s.agg_g = g;
+    }
+    if (cfg.local) s.agg_w += env.weight(s.g0, s.gt, cfg.k);
+    else s.agg_n += 1u;
+}
+
+template <class Env>
+SPEQB_HD void lane_consume(Lane & s, Loads const & ld, DevIndex const & ix, const uint32_t * ctab, ScanCfg const & cfg, Env & env)
+{
+    const uint32_t k = cfg.k;
+    if (s.phase == PH_STEP)
+    {
+        if (s.flags & LF_HAVE_G) lane_take_group(s, cfg, env);
+        if (s.flags & LF_PENDING)
+        {
+            // every occurrence in one variant <=> no group change in (lb, rb]
+            s.flags &= ~LF_PENDING;
+            if (blk_chg_upto(ld.A, s.lb & 63u) == blk_chg_before(ld.B, (s.rb + 1u) & 63u))
+            {
+                s.gval = env.load_grp(s.lb);
+                s.gt = s.t;
+                s.flags |= LF_HAVE_G;
+            }
+        }
+        if (s.t < s.pend)
+        {
+            if ((s.t >> 5) != s.cw)
+            {
+                s.cw = s.t >> 5;
+                s.wbase = ld.rdw;
+                s.winv = ld.rdi;
+            }
+            uint32_t c = (uint32_t)(s.wbase >> (2u * (s.t & 31u))) & 3u;
+            bool ib = (s.winv >> (s.t & 31u)) & 1u;
+            if (cfg.back) { if (ib) c = kCodeN; ib = false; }
+            if (ib)
+            {
+                // N / low quality: no window may contain this base; the search restarts behind it
+                s.lb = 0u; s.rb = ix.n - 1u; s.d = 0u; s.run = 0u;
+                s.t += 1u;
+                return;
+            }
+            uint32_t jl = s.lb & 63u, jr = (s.rb + 1u) & 63u;
+            if (s.d == k)
+            {
+                // the window slides: drop its first base = contract the interval to depth k-1
+                if (k == 1u) { s.lb = 0u; s.rb = ix.n - 1u; s.d = 0u; }
+                else
+                {
+                    uint64_t zl = ~u64of(ld.A.w[8], ld.A.w[9]) & upto64(jl);
+                    uint64_t zr = ~u64of(ld.B.w[8], ld.B.w[9]) & from64(jr);
+                    s.d = k - 1u;
+                    if (zl == 0ull || zr == 0ull)
+                    {
+                        // the widened interval leaves the two blocks: general contraction, then come back
+                        s.phase = PH_LCP; s.flags &= ~(LF_LFOUND | LF_RFOUND);
+                        s.cl = s.lb >> 5; s.cr = (s.rb + 1u) >> 5;
+                        return;
+                    }
+                    jl = 63u - clz64(zl);
+                    jr = ctz64(zr);
+                    s.lb = (s.lb & ~63u) + jl;
+                    s.rb = ((s.rb + 1u) & ~63u) + jr - 1u;
+                }
+            }
+            uint32_t nl, nr;
+            const uint32_t cc = ctab[c];
+            if (s.d == 0u) { nl = cc; nr = ctab[kCtabEnd + c]; }
+            else if (c == kCodeN) { nl = cc + env.npos_rank(s.lb); nr = cc + env.npos_rank(s.rb + 1u); }
+            else { nl = cc + blk_rank(ld.A, c, jl); nr = cc + blk_rank(ld.B, c, jr); }
+            if (nr > nl)
+            {
+                s.lb = nl; s.rb = nr - 1u; s.d += 1u;
+            }
+            else if (s.d != 0u)
+            {
+                // read[t-d..t] does not occur: shorten from the left and try the same base again
+                s.d -= 1u;
+                if (s.d == 0u) { s.lb = 0u; s.rb = ix.n - 1u; }
+                else
+                {
+                    s.phase = PH_LCP; s.flags &= ~(LF_LFOUND | LF_RFOUND);
+                    s.cl = s.lb >> 5; s.cr = (s.rb + 1u) >> 5;
+                }
+                return;
+            }
+            s.run += 1u;
+            s.t += 1u;
+            if (s.run >= k)
+            {
+                s.c_total += 1ull;                       // ++total_kmers (src/fm_scanner.cpp:164)
+                if (s.d == k)
+                {
+                    s.flags |= LF_PENDING;
+                    if (cfg.record) env.record(s.lb);
+                }
+            }
+            return;
+        }
+        // the read is finished (its last hit, if any, was resolved above)
+        if (s.flags & LF_HAVE_G) lane_take_group(s, cfg, env);
+        if (!cfg.back && cfg.paired && !(s.flags & LF_MATE2)) s.flags |= LF_MATE2;
+        else
+        {
+            if (!cfg.back && s.gmin != kNoGroup && s.gmin != s.gmax) s.c_amb += 1u;   // is_ambiguous (src/fm_scanner.cpp:183-190,213)
+            s.gmin = kNoGroup; s.gmax = 0u;
+            s.flags &= ~LF_MATE2;
+            s.u += cfg.stride;
+        }
+        s.phase = PH_FETCH;
+        return;
+    }
+    if (s.phase == PH_LCP)
+    {
+        // maximal range around [lb, rb] whose inner lcp values are all >= d
+        if (!(s.flags & LF_LFOUND))
+        {
+            uint32_t lt = lcp_lt_bits(ld.A.w, s.d);
+            if (s.cl == (s.lb >> 5)) lt &= (2u << (s.lb & 31u)) - 1u;      // first chunk: only bytes at or below lb
+            if (lt) { s.nlb = s.cl * kLcpChunk + 31u - clz32(lt); s.flags |= LF_LFOUND; }
+            else s.cl -= 1u;                                                // lcp[0] = 0 stops the scan
+        }
+        if (!(s.flags & LF_RFOUND))
+        {
+            uint32_t lt = lcp_lt_bits(ld.B.w, s.d);
+            if (s.cr == ((s.rb + 1u) >> 5)) lt &= ~0u << ((s.rb + 1u) & 31u);   // first chunk: only bytes above rb
+            if (lt) { s.nrb1 = s.cr * kLcpChunk + ctz32(lt); s.flags |= LF_RFOUND; }
+            else s.cr += 1u;                                                // the zero padding behind n stops the scan
+        }
+        if ((s.flags & (LF_LFOUND | LF_RFOUND)) == (LF_LFOUND | LF_RFOUND))
+        {
+            s.lb = s.nlb; s.rb = s.nrb1 - 1u;
+            s.phase = PH_STEP;
+        }
+        return;
+    }
+    if (s.phase == PH_FETCH)
+    {
+        if (s.u >= cfg.units)
+        {
+            s.phase = PH_DONE;
+            return;
+        }
+        uint32_t L = ld.flen;
+        s.g0 = ld.fg0;
+        s.cw = 0xFFFFFFFFu;
+        s.lb = 0u; s.rb = ix.n - 1u; s.d = 0u; s.run = 0u;
+        if (cfg.back)
+        {
+            // a segment of a text: windows [start, start + nwin)
+            s.t = ld.fstart;
+            s.pend = ld.fstart + L + k - 1u;
+            s.rgroup = ld.fgroup;
+            env.backtotal(ld.fgroup, L);
+        }
+        else
+        {
+            s.t = 0u;
+            s.pend = L >= k ? L : 0u;                   // L < k: the sliding view is empty
+            s.c_reads += 1u;
+            if (L >= k) s.c_look += L - k + 1u;
+        }
+        s.phase = PH_STEP;
+        return;
+    }
 }
 }   // namespace speqb

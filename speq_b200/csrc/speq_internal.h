@@ -23,10 +23,11 @@ struct HostIndex
     uint64_t n = 0;
     uint32_t S = 0, V = 0;
     uint64_t C[8] = {0};
-    std::vector<uint32_t> blocks;          // 8 u32 per block, (n/64 + 1) blocks
-    std::vector<GroupRun> gr;              // n
-    std::vector<uint8_t> lcp;              // n + 16 (zero padded), capped at kLcpCap
-    std::vector<uint32_t> exc_pos, n_pos;  // sorted BWT positions
+    std::vector<KBlock> blocks;            // n/64 + 1 blocks; e bits zero (they are filled per scan, for the scan's k)
+    std::vector<uint16_t> grp;             // n: variant of the text owning suffix SA[i] (kNoGroup16: delimiter / sentinel)
+    std::vector<uint8_t> lcp;              // lcp_padded_size(n) entries (zero padded), capped at kLcpCap
+    std::vector<uint32_t> n_pos;           // sorted BWT positions holding N
+    uint64_t n_exc = 0;                    // BWT positions holding N / delimiter / sentinel
     std::vector<int32_t> group_of_text;    // S
     // the S texts packed as a read batch (inv = N) for the back-check
     std::vector<uint64_t> t_bases;
@@ -40,11 +41,11 @@ struct HostIndex
 struct DeviceIndex
 {
     int device = -1;
-    uint32_t * blocks = nullptr;
-    GroupRun * gr = nullptr;
+    KBlock * blocks = nullptr;
+    uint16_t * grp = nullptr;
     uint8_t * lcp = nullptr;
-    uint32_t * exc_pos = nullptr;
     uint32_t * n_pos = nullptr;
+    uint32_t * ctab = nullptr;
     // texts batch
     uint64_t * t_bases = nullptr;
     uint32_t * t_inv = nullptr;
@@ -54,6 +55,8 @@ struct DeviceIndex
     uint64_t bytes = 0;
     DevIndex view{};
 };
+
+inline uint64_t lcp_padded_size(uint64_t n) { return ((n + kLcpChunk) / kLcpChunk + 1) * kLcpChunk; }
 
 void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint32_t S, int32_t const * group_of_text,
                       uint32_t V, uint32_t flags, HostIndex & out);

@@ -1,7 +1,8 @@
-// roll_sim.cpp -- TEST-ONLY white-box harness: runs the per-lane arithmetic of speq_b200/csrc/scan_core.h (the very
-// header the CUDA kernels compile) on the host, one "lane" at a time, so that index layout / rolling-window logic can be
+// roll_sim.cpp -- TEST-ONLY white-box harness: runs the per-lane state machine of speq_b200/csrc/scan_core.h (the very
+// header the CUDA kernels compile) on the host, lane by lane, so that index layout / rolling-window logic can be
 // checked against the oracle in the CPU-only test tier.  It is never linked into libspeq_cuda.so and is not a product
-// path: the product has no CPU fallback.  Built by tests/conftest.py with g++.
+// path: the product has no CPU fallback.  Built by tests/helpers.py with g++.
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <vector>
@@ -11,108 +12,198 @@
 
 using namespace speqb;
 
-static DevIndex host_view(HostIndex const & h)
+namespace
 {
-    DevIndex v{};
-    v.blocks = reinterpret_cast<const RankBlock *>(h.blocks.data());
-    v.lcp = h.lcp.data();
-    v.gr = h.gr.data();
-    v.exc_pos = h.exc_pos.data();
-    v.n_pos = h.n_pos.data();
-    v.n_exc = (uint32_t)h.exc_pos.size();
-    v.n_npos = (uint32_t)h.n_pos.size();
-    v.n = (uint32_t)h.n;
+struct HostView
+{
+    std::vector<KBlock> blocks_k;
+    uint32_t ctab[16];
+    DevIndex ix;
+};
+
+void make_view(HostIndex const & h, uint32_t k, HostView & hv)
+{
+    hv.blocks_k = h.blocks;
+    for (uint64_t i = 0; i < h.n; ++i)
+        if ((uint32_t)h.lcp[i] + 1u >= k) hv.blocks_k[i / 64].e[(i % 64) / 32] |= 1u << (i % 32);
     static const uint32_t sym_of_code[5] = {1, 2, 3, 5, 4};
+    memset(hv.ctab, 0, sizeof hv.ctab);
     for (int c = 0; c < 5; ++c)
     {
-        v.ctab[c] = (uint32_t)h.C[sym_of_code[c]];
-        v.ctab[kCtabEnd + c] = (uint32_t)h.C[sym_of_code[c] + 1];
+        hv.ctab[c] = (uint32_t)h.C[sym_of_code[c]];
+        hv.ctab[kCtabEnd + c] = (uint32_t)h.C[sym_of_code[c] + 1];
     }
-    return v;
+    hv.ix.blocks = hv.blocks_k.data();
+    hv.ix.lcp = h.lcp.data();
+    hv.ix.grp = h.grp.data();
+    hv.ix.n_pos = h.n_pos.data();
+    hv.ix.ctab = hv.ctab;
+    hv.ix.n_npos = (uint32_t)h.n_pos.size();
+    hv.ix.n = (uint32_t)h.n;
 }
 
+struct HostEnv
+{
+    DevIndex const & ix;
+    const uint8_t * qual;
+    const double * qden;
+    std::vector<uint64_t> & uniq;
+    std::vector<double> & uniq_w;
+    std::vector<uint64_t> & totg;
+    uint64_t * mult;
+    bool local;
+    uint32_t load_grp(uint32_t i) const { return ix.grp[i]; }
+    uint32_t npos_rank(uint32_t i) const { return lower_bound_u32(ix.n_pos, ix.n_npos, i); }
+    double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
+    {
+        const uint8_t * q = qual + 32u * g0 + (t_end - k);
+        double w = 1.0;
+        for (uint32_t i = 0; i < k; ++i) w = w / qden[q[i]];
+        return w;
+    }
+    void unique(uint32_t g, uint32_t n, double w) const
+    {
+        if (local) uniq_w[g] += w;
+        else uniq[g] += n;
+    }
+    void record(uint32_t lb) const { if (mult) ++mult[lb]; }
+    void backtotal(uint32_t g, uint32_t n) const { totg[g] += n; }
+};
+
+void do_loads(Plan const & p, Loads & ld, BatchView const & b, std::vector<uint32_t> const & seg_tab, bool back)
+{
+    if (p.blocks)
+    {
+        memcpy(ld.A.w, p.pa, 64);
+        memcpy(ld.B.w, p.pb, 64);
+    }
+    if (p.lcp_l) memcpy(ld.A.w, p.pl, 32);
+    if (p.lcp_r) memcpy(ld.B.w, p.pr, 32);
+    if (p.word) { ld.rdw = *p.pw; ld.rdi = *p.pi; }
+    if (p.fetch)
+    {
+        if (back)
+        {
+            const uint32_t * sg = &seg_tab[p.fr * 8];
+            ld.fg0 = u64of(sg[0], sg[1]); ld.fstart = sg[2]; ld.flen = sg[3]; ld.fgroup = sg[4];
+        }
+        else { ld.flen = b.len[p.fr]; ld.fg0 = b.grp_off[p.fr]; }
+    }
+}
+}   // namespace
+
 extern "C" {
-// out: unique[V], then total, ambiguous, lookups.  mult (n entries, may be NULL) receives window multiplicities per lb.
-// algo 0 = rolling, 1 = direct.  backcheck != 0: batch = the index's own texts, out = unique_ref[V], total_ref[V].
+// out: unique[V], then total, ambiguous, lookups (back-check: unique_ref[V], total_ref[V]).  out_w (may be NULL): local
+// mode weighted tallies.  mult (n entries, may be NULL) receives window multiplicities per lb.
+// algo 0 = rolling state machine (nlanes lanes striding over the units), 1 = direct.  qual: per-base phred at 32*g0+j.
 int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, const int32_t * group_of_text, uint32_t V,
-             const uint64_t * bases, const uint32_t * inv, const uint64_t * grp_off, const uint32_t * len, uint64_t n_reads,
-             uint32_t k, int paired, int algo, int backcheck, uint64_t * out, uint64_t * mult)
+             const uint64_t * bases, const uint32_t * inv, const uint8_t * qual, const uint64_t * grp_off, const uint32_t * len,
+             uint64_t n_reads, uint32_t k, int paired, int algo, int backcheck, int local, uint32_t nlanes, uint32_t seg_len,
+             uint64_t * out, double * out_w, uint64_t * mult)
 {
     try
     {
         HostIndex h;
         build_host_index(texts, lens, S, group_of_text, V, 0, h);
-        DevIndex ix = host_view(h);
-        const uint32_t * ctab = ix.ctab;
+        HostView hv;
+        make_view(h, k, hv);
+        DevIndex const & ix = hv.ix;
         std::vector<uint64_t> uniq(V, 0), totg(V, 0);
+        std::vector<double> uniq_w(V, 0.0);
         uint64_t total = 0, amb = 0, look = 0;
+        double qden[42];
+        for (int q = 0; q < 42; ++q) { double b = q; qden[q] = 1.0 - 1.0 / pow(10.0, b / 10.0); }
+        BatchView bv{};
+        bv.bases = bases; bv.inv = inv; bv.qual = qual; bv.grp_off = grp_off; bv.len = len; bv.n_reads = n_reads;
+        std::vector<uint32_t> seg_tab;
+        uint64_t n_segs = 0;
         if (backcheck)
         {
-            bases = h.t_bases.data(); inv = h.t_inv.data(); grp_off = h.t_grp_off.data(); len = h.t_len.data(); n_reads = S;
+            bv.bases = h.t_bases.data(); bv.inv = h.t_inv.data(); bv.grp_off = h.t_grp_off.data(); bv.len = h.t_len.data(); bv.n_reads = S;
             paired = 0;
-        }
-        uint64_t units = paired ? n_reads / 2 : n_reads;
-        for (uint64_t u = 0; u < units; ++u)
-        {
-            uint32_t gmin = 0xFFFFFFFFu, gmax = 0;
-            for (int mate = 0; mate < (paired ? 2 : 1); ++mate)
+            for (uint32_t i = 0; i < S; ++i)
             {
-                uint64_t r = paired ? 2 * u + mate : u;
-                uint32_t L = len[r];
-                uint64_t g0 = grp_off[r];
-                if (L < k) continue;
-                look += L - k + 1;
-                if (backcheck) totg[group_of_text[r]] += L - k + 1;
-                if (algo == 0)
+                if (h.t_len[i] < k) continue;
+                uint32_t nw = h.t_len[i] - k + 1;
+                for (uint32_t st = 0; st < nw; st += seg_len)
                 {
-                    RollState s;
-                    roll_reset(ix, s);
-                    uint32_t t = 0;
-                    while (t < L)
-                    {
-                        uint32_t c = code_at(bases, g0, t);
-                        bool ib = inv_at(inv, g0, t);
-                        if (backcheck && ib) c = kCodeN;
-                        uint32_t res = roll_advance(ix, ctab, k, s, c, backcheck ? false : ib);
-                        if (res & ROLL_CONSUMED) ++t;
-                        if (res & ROLL_WINDOW) ++total;
-                        if (res & ROLL_HIT)
-                        {
-                            if (mult) ++mult[s.lb];
-                            GroupRun g = ix.gr[s.lb];
-                            if (g.run_end >= s.rb)
-                            {
-                                ++uniq[g.group];
-                                gmin = gmin < g.group ? gmin : g.group;
-                                gmax = gmax > g.group ? gmax : g.group;
-                            }
-                        }
-                    }
+                    uint32_t e[8] = {(uint32_t)h.t_grp_off[i], (uint32_t)(h.t_grp_off[i] >> 32), st, nw - st < seg_len ? nw - st : seg_len,
+                                     (uint32_t)group_of_text[i], 0, 0, 0};
+                    seg_tab.insert(seg_tab.end(), e, e + 8);
+                    ++n_segs;
                 }
-                else
+            }
+        }
+        if (algo == 0)
+        {
+            ScanCfg cfg;
+            cfg.k = k;
+            cfg.units = backcheck ? n_segs : (paired ? n_reads / 2 : n_reads);
+            cfg.stride = nlanes;
+            cfg.paired = paired; cfg.local = local; cfg.record = mult != nullptr; cfg.back = backcheck;
+            HostEnv env{ix, qual, qden, uniq, uniq_w, totg, mult, local != 0};
+            std::vector<Lane> lanes(nlanes);
+            std::vector<Loads> loads(nlanes);
+            for (uint32_t l = 0; l < nlanes; ++l) { lane_init(lanes[l], l); memset(&loads[l], 0, sizeof(Loads)); }
+            bool any = true;
+            uint64_t guard = 0;
+            while (any)
+            {
+                any = false;
+                for (uint32_t l = 0; l < nlanes; ++l)
                 {
+                    Lane & s = lanes[l];
+                    if (s.phase == PH_DONE) continue;
+                    any = true;
+                    Plan p;
+                    lane_plan(s, ix, bv, cfg, p);
+                    do_loads(p, loads[l], bv, seg_tab, backcheck != 0);
+                    lane_consume(s, loads[l], ix, hv.ctab, cfg, env);
+                }
+                if (++guard > (1ull << 40)) return -2;
+            }
+            for (auto & s : lanes)
+            {
+                lane_flush_agg(s, cfg, env);
+                total += s.c_total; amb += s.c_amb; look += s.c_look;
+            }
+        }
+        else
+        {
+            uint64_t units = paired ? n_reads / 2 : n_reads;
+            for (uint64_t u = 0; u < units; ++u)
+            {
+                uint32_t gmin = 0xFFFFFFFFu, gmax = 0;
+                for (int mate = 0; mate < (paired ? 2 : 1); ++mate)
+                {
+                    uint64_t r = paired ? 2 * u + mate : u;
+                    uint32_t L = len[r];
+                    uint64_t g0 = grp_off[r];
+                    if (L < k) continue;
+                    look += L - k + 1;
                     for (uint32_t s0 = 0; s0 + k <= L; ++s0)
                     {
                         bool bad = false;
                         for (uint32_t i = 0; i < k; ++i) bad |= inv_at(inv, g0, s0 + i) != 0;
-                        if (bad && !backcheck) continue;
+                        if (bad) continue;
                         ++total;
                         uint32_t lb, rb, steps = 0;
-                        if (!direct_window(ix, ctab, bases, inv, g0, s0, k, lb, rb, steps)) continue;
+                        if (!direct_window(ix, hv.ctab, bases, inv, g0, s0, k, lb, rb, steps)) continue;
                         if (mult) ++mult[lb];
-                        GroupRun g = ix.gr[lb];
-                        if (g.run_end >= rb)
+                        uint32_t g = interval_group(ix, lb, rb);
+                        if (g != kNoGroup)
                         {
-                            ++uniq[g.group];
-                            gmin = gmin < g.group ? gmin : g.group;
-                            gmax = gmax > g.group ? gmax : g.group;
+                            ++uniq[g];
+                            gmin = gmin < g ? gmin : g;
+                            gmax = gmax > g ? gmax : g;
                         }
                     }
                 }
+                if (gmin != 0xFFFFFFFFu && gmin != gmax) ++amb;
             }
-            if (gmin != 0xFFFFFFFFu && gmin != gmax) ++amb;
         }
         for (uint32_t g = 0; g < V; ++g) out[g] = uniq[g];
+        if (out_w) for (uint32_t g = 0; g < V; ++g) out_w[g] = uniq_w[g];
         if (backcheck)
             for (uint32_t g = 0; g < V; ++g) out[V + g] = totg[g];
         else

@@ -133,7 +133,8 @@ def test_index_matches_oracle_dump(lib, oracle_bin, tmp_path):
     assert ei.value.code == capi.EIO
 
 
-def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck=False, want_mult=False):
+def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck=False, want_mult=False, local=False, nlanes=7,
+              seg_len=37):
     texts, grp = [], []
     for j, s in enumerate(scaff):
         texts += [np.ascontiguousarray(s), np.ascontiguousarray(engine.revcomp_ranks(s))]
@@ -143,17 +144,20 @@ def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck
     lens = np.array([t.size for t in texts], np.uint64)
     grp = np.array(grp, np.int32)
     seq, q, offs = helpers.flat_reads(seqs, quals)
-    pb = engine.pack_reads(seq, q, offs, phred_cutoff=cutoff)
+    pb = engine.pack_reads(seq, q, offs, phred_cutoff=cutoff, with_qual=True)
     out = np.zeros(2 * V + 4, np.uint64)
+    out_w = np.zeros(V, np.float64)
     n = int(lens.sum()) + S
     mult = np.zeros(n + 1, np.uint64) if want_mult else None
     sim.sim_scan.restype = C.c_int
     rc = sim.sim_scan(ptrs, C.c_void_p(lens.ctypes.data), C.c_uint32(S), C.c_void_p(grp.ctypes.data), C.c_uint32(V),
-                      C.c_void_p(pb.bases.ctypes.data), C.c_void_p(pb.inv.ctypes.data), C.c_void_p(pb.grp_off.ctypes.data),
-                      C.c_void_p(pb.len.ctypes.data), C.c_uint64(pb.n_reads), C.c_uint32(k), C.c_int(int(paired)), C.c_int(algo),
-                      C.c_int(int(backcheck)), C.c_void_p(out.ctypes.data), C.c_void_p(mult.ctypes.data if want_mult else None))
+                      C.c_void_p(pb.bases.ctypes.data), C.c_void_p(pb.inv.ctypes.data), C.c_void_p(pb.qual.ctypes.data),
+                      C.c_void_p(pb.grp_off.ctypes.data), C.c_void_p(pb.len.ctypes.data), C.c_uint64(pb.n_reads), C.c_uint32(k),
+                      C.c_int(int(paired)), C.c_int(algo), C.c_int(int(backcheck)), C.c_int(int(local)), C.c_uint32(nlanes),
+                      C.c_uint32(seg_len), C.c_void_p(out.ctypes.data), C.c_void_p(out_w.ctypes.data),
+                      C.c_void_p(mult.ctypes.data if want_mult else None))
     assert rc == 0
-    return out, mult
+    return out, out_w, mult
 
 
 @pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
@@ -163,13 +167,67 @@ def test_lane_arithmetic_vs_golden(lib, sim, name, algo):
     exp, run = fx["expected"], fx["run"]
     scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
     V = len(counts)
-    out, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], algo)
-    if exp["mode"] == "global":
+    local = exp["mode"] == "local"
+    out, out_w, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], algo,
+                              local=(local and algo == 0))
+    if not local:
         assert list(out[:V]) == exp["unique"]
+    elif algo == 0:
+        assert helpers.rel_close(out_w, exp["unique_w"], 1e-12)
     assert int(out[V]) == exp["total_kmers"]
     assert int(out[V + 1]) == exp["ambiguous"]
     assert int(out[V + 2]) == exp["lookups"]
     if algo == 0:
-        bc, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], 30, False, 0, backcheck=True)
-        assert list(bc[:V]) == exp["unique_ref"]
-        assert list(bc[V:2 * V]) == exp["total_ref"]
+        for nlanes, seg_len in ((1, 5), (7, 37), (64, 100000)):
+            bc, _, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], 30, False, 0, backcheck=True, nlanes=nlanes, seg_len=seg_len)
+            assert list(bc[:V]) == exp["unique_ref"]
+            assert list(bc[V:2 * V]) == exp["total_ref"]
+        one, _, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], 0, nlanes=1, local=local)
+        assert np.array_equal(one, out)
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 31, 64, 127])
+def test_lane_arithmetic_k_extremes(lib, sim, k):
+    """rolling == direct for k from 1 to the maximum (long, repetitive texts so that deep intervals stay wide)."""
+    rng = np.random.default_rng(k)
+    unit = "".join(rng.choice(list("ACGT"), 90))
+    scaff_s = [unit * 4 + "ACGTN" + unit[:50], unit[:70] + "T" + unit[70:] + unit * 2, unit[::-1] * 3]
+    scaff = [engine.ascii_to_ranks(s) for s in scaff_s]
+    seqs = [scaff_s[i % 3][j:j + 200] for i, j in enumerate(rng.integers(0, 100, 40))]
+    seqs = ["".join(ch if rng.random() > 0.01 else "ACGT"[int(rng.integers(0, 4))] for ch in s) for s in seqs]
+    quals = ["I" * len(s) for s in seqs]
+    a, _, ma = _sim_scan(sim, scaff, [0, 1, 2], 3, seqs, quals, k, 30, False, 0, want_mult=True)
+    b, _, mb = _sim_scan(sim, scaff, [0, 1, 2], 3, seqs, quals, k, 30, False, 1, want_mult=True)
+    assert np.array_equal(a, b)
+    assert np.array_equal(ma, mb)
+    assert a[3] > 0
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_lane_arithmetic_low_complexity(lib, sim, seed):
+    """Wide SA intervals (poly-A, short tandem repeats, near-identical copies): the e-bit contraction has to leave its two
+    blocks and the general lcp scan has to cross many 32-byte chunks.  rolling == direct, tallies and multiplicities."""
+    rng = np.random.default_rng(seed)
+    parts = ["A" * 300, "AC" * 200, "ACG" * 150, "".join(rng.choice(list("ACGT"), 200))]
+    base = "".join(parts[i] for i in rng.permutation(4))
+    scaff_s = []
+    for v in range(4):
+        s = list(base)
+        for p in rng.integers(0, len(s), 6):
+            s[p] = "ACGTN"[int(rng.integers(0, 5))]
+        scaff_s.append("".join(s))
+    scaff = [engine.ascii_to_ranks(s) for s in scaff_s]
+    seqs = []
+    for _ in range(60):
+        s = scaff_s[int(rng.integers(0, 4))]
+        j = int(rng.integers(0, len(s) - 120))
+        r = list(s[j:j + 120])
+        for p in rng.integers(0, 120, 2):
+            r[p] = "ACGT"[int(rng.integers(0, 4))]
+        seqs.append("".join(r))
+    quals = ["I" * len(s) for s in seqs]
+    for k in (4, 9, 17, 40):
+        a, _, ma = _sim_scan(sim, scaff, [0, 1, 2, 3], 4, seqs, quals, k, 30, False, 0, want_mult=True, nlanes=5)
+        b, _, mb = _sim_scan(sim, scaff, [0, 1, 2, 3], 4, seqs, quals, k, 30, False, 1, want_mult=True)
+        assert np.array_equal(a, b), k
+        assert np.array_equal(ma, mb), k
