@@ -20,8 +20,9 @@
 // is "no chg bit in (lb, rb]" = chgcum/popc arithmetic on those same two blocks.  So a window costs one round trip to
 // two half lines, plus one 2-byte group load when (and only when) the k-mer is unique to a variant.
 //
-// lcp[i] = min(127, longest common prefix of suffixes SA[i-1] and SA[i]) (lcp[0] = 0), one byte per suffix, is kept for
-// the uncommon contractions (after a mismatch, or when the widened interval leaves the two blocks).
+// lcp[i] = min(127, longest common prefix of suffixes SA[i-1] and SA[i]) (lcp[0] = lcp[n] = 0), one byte per suffix, and
+// pn[i] = {largest j < i with lcp[j] < lcp[i], smallest j > i with lcp[j] < lcp[i]} serve the uncommon moves (after a
+// mismatch, or when the widened interval leaves the two blocks): the parent lcp interval in one round trip.
 // grp[i]  = variant of the text that owns suffix SA[i] (u16; kNoGroup16 for delimiter / sentinel suffixes).
 #pragma once
 #include <cstdint>
@@ -45,6 +46,11 @@ constexpr uint32_t kLcpCap = 127;
 constexpr uint32_t kCodeN = 4;      // query code of N (back-check only); A0 C1 G2 T3
 constexpr uint32_t kLcpChunk = 32;  // the lcp array is read in 32-byte chunks (one LDG.256)
 
+struct __attribute__((aligned(8))) uint2x
+{
+    uint32_t x, y;
+};
+
 struct __attribute__((aligned(64))) KBlock
 {
     uint32_t cnt[4];
@@ -64,7 +70,8 @@ constexpr uint32_t kCtabEnd = 8;
 struct DevIndex
 {
     const KBlock * blocks;        // n/64 + 1 blocks (for a scan: the copy whose e bits are filled for the scan's k)
-    const uint8_t * lcp;          // n entries, zero padded to a multiple of 32 bytes + 32, 32-byte aligned
+    const uint8_t * lcp;          // n + 1 entries (lcp[n] = 0), zero padded
+    const uint2x * pn;            // n + 1 entries: {previous smaller, next smaller} lcp positions
     const uint16_t * grp;         // n entries
     const uint32_t * n_pos;       // sorted BWT positions holding N (rank of the symbol N; back-check only)
     const uint32_t * ctab;        // 16 entries: [c] = C of query code c (A,C,G,T,N) = #text symbols smaller;

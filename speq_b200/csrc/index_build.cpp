@@ -153,6 +153,27 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         }
     }
 
+    // previous / next smaller value links over the capped lcp array (lcp[n] = 0 closes every interval)
+    {
+        h.pn.assign(n + 1, uint2x{0u, (uint32_t)n});
+        std::vector<uint32_t> stack;
+        stack.reserve(256);
+        for (uint64_t i = 0; i <= n; ++i)
+        {
+            uint8_t v = h.lcp[i];   // the padding makes lcp[n] = 0
+            while (!stack.empty() && h.lcp[stack.back()] > v)
+            {
+                h.pn[stack.back()].y = (uint32_t)i;   // first position to the right with a smaller value
+                stack.pop_back();
+            }
+            // stack top now holds a value <= v; an equal value shares its previous STRICTLY smaller position with i
+            if (stack.empty()) h.pn[i].x = 0u;
+            else if (h.lcp[stack.back()] == v) h.pn[i].x = h.pn[stack.back()].x;
+            else h.pn[i].x = stack.back();
+            stack.push_back((uint32_t)i);
+        }
+    }
+
     if (flags & SPEQG_BUILD_KEEP_SA)
     {
         h.sa.resize(n);
@@ -173,7 +194,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
 }
 
 // ---- cache file: own binary payload (the reference's .idx is a cereal+sdsl archive; byte compatibility is a later row)
-static const char kMagic[8] = {'S', 'P', 'E', 'Q', 'B', '2', '0', '2'};
+static const char kMagic[8] = {'S', 'P', 'E', 'Q', 'B', '2', '0', '3'};
 
 template <class T> static void wr(FILE * f, T const & v)
 {
@@ -208,7 +229,7 @@ void save_host_index(HostIndex const & h, std::string const & path, uint64_t off
         if (fwrite(kMagic, 1, 8, f) != 8) throw api_error(SPEQG_EIO, "short write");
         wr(f, h.n); wr(f, h.S); wr(f, h.V);
         for (int c = 0; c < 8; ++c) wr(f, h.C[c]);
-        wr(f, h.n_exc); wrv(f, h.blocks); wrv(f, h.grp); wrv(f, h.lcp); wrv(f, h.n_pos); wrv(f, h.group_of_text);
+        wr(f, h.n_exc); wrv(f, h.blocks); wrv(f, h.grp); wrv(f, h.lcp); wrv(f, h.pn); wrv(f, h.n_pos); wrv(f, h.group_of_text);
         wrv(f, h.t_bases); wrv(f, h.t_inv); wrv(f, h.t_grp_off); wrv(f, h.t_len); wrv(f, h.sa);
     }
     catch (...) { fclose(f); throw; }
@@ -227,10 +248,10 @@ void load_host_index(std::string const & path, HostIndex & h, uint64_t offset)
         h = HostIndex{};
         rd(f, h.n); rd(f, h.S); rd(f, h.V);
         for (int c = 0; c < 8; ++c) rd(f, h.C[c]);
-        rd(f, h.n_exc); rdv(f, h.blocks); rdv(f, h.grp); rdv(f, h.lcp); rdv(f, h.n_pos); rdv(f, h.group_of_text);
+        rd(f, h.n_exc); rdv(f, h.blocks); rdv(f, h.grp); rdv(f, h.lcp); rdv(f, h.pn); rdv(f, h.n_pos); rdv(f, h.group_of_text);
         rdv(f, h.t_bases); rdv(f, h.t_inv); rdv(f, h.t_grp_off); rdv(f, h.t_len); rdv(f, h.sa);
         if (h.blocks.size() != h.n / kBlockSyms + 1 || h.grp.size() != h.n || h.group_of_text.size() != h.S ||
-            h.lcp.size() != lcp_padded_size(h.n))
+            h.lcp.size() != lcp_padded_size(h.n) || h.pn.size() != h.n + 1)
             throw api_error(SPEQG_EIO, "inconsistent index payload");
     }
     catch (...) { fclose(f); throw; }

@@ -65,6 +65,15 @@ __device__ __forceinline__ void ld32_if(uint32_t & v, const void * p, bool pred)
     asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
 }
 
+__device__ __forceinline__ void ld8_if(uint32_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u8 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld64x2_if(uint32_t & x, uint32_t & y, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %3, 0;\n\t@q ld.global.nc.v2.u32 {%0,%1}, [%2];\n\t}" : "+r"(x), "+r"(y) : "l"(p), "r"((int)pred));
+}
+
 template <int MODE> struct DevEnv
 {
     static constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
@@ -140,12 +149,14 @@ __global__ void __launch_bounds__(kBlock) scan_roll_kernel(const DevIndex ix, co
         Plan p;
         lane_plan(s, ix, b, cfg, p);
         // ---- every load of this iteration, issued before anything is consumed
-        const void * a0 = p.blocks ? (const void *)p.pa : (const void *)p.pl;
-        const void * b0 = p.blocks ? (const void *)p.pb : (const void *)p.pr;
-        ld256_if(ld.A.w, a0, p.blocks || p.lcp_l);
-        ld256_if(ld.B.w, b0, p.blocks || p.lcp_r);
+        ld256_if(ld.A.w, p.pa, p.blocks);
+        ld256_if(ld.B.w, p.pb, p.blocks);
         ld256_if(ld.A.w + 8, reinterpret_cast<const char *>(p.pa) + 32, p.blocks);
         ld256_if(ld.B.w + 8, reinterpret_cast<const char *>(p.pb) + 32, p.blocks);
+        ld8_if(ld.A.w[0], ix.lcp + s.lb, p.up);
+        ld8_if(ld.B.w[0], ix.lcp + s.rb + 1u, p.up);
+        ld64x2_if(ld.A.w[2], ld.A.w[3], ix.pn + s.lb, p.up);
+        ld64x2_if(ld.B.w[2], ld.B.w[3], ix.pn + s.rb + 1u, p.up);
         ld64_if(ld.rdw, p.pw, p.word);
         ld32_if(ld.rdi, p.pi, p.word);
         if (BACK)

@@ -119,21 +119,6 @@ SPEQB_HD bool fm_step(DevIndex const & ix, const uint32_t * ctab, uint32_t & lb,
     return true;
 }
 
-// bit i set iff byte i of the 32-byte chunk (8 words) is < dd (bytes <= 127, 1 <= dd <= 127)
-SPEQB_HD uint32_t lcp_lt_bits(const uint32_t * w, uint32_t dd)
-{
-    uint32_t out = 0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-    {
-        const uint64_t H = 0x8080808080808080ull, L = 0x0101010101010101ull;
-        uint64_t x = u64of(w[2 * i], w[2 * i + 1]);
-        uint64_t m = (~((x | H) - (uint64_t)dd * L) & H) >> 7;            // bit 0 of byte b set iff byte b < dd
-        out |= (uint32_t)((m * 0x0102040810204080ull) >> 56) << (8 * i);   // gather the 8 byte flags into 8 bits
-    }
-    return out;
-}
-
 // ---- packed read access ----------------------------------------------------------------------------------------
 SPEQB_HD uint32_t code_at(const uint64_t * bases, uint64_t g0, uint32_t t)
 {
@@ -180,17 +165,18 @@ SPEQB_HD uint32_t interval_group(DevIndex const & ix, uint32_t lb, uint32_t rb)
 //   PH_FETCH  pick the next unit (read, pair or text segment): loads its length / first group
 //   PH_STEP   loads the two KBlocks at lb and rb+1; resolves the uniqueness of the previous window's hit; contracts
 //             d == k to k-1 with the e bits; performs the rank step for the next base
-//   PH_LCP    general contraction (after a failed extension, or when the e-bit scan leaves the two blocks): scans one
-//             32-byte lcp chunk per side per iteration until both boundaries are found
+//   PH_UP     parent jump (after a failed extension, or when the e-bit scan leaves the two blocks): loads lcp and the
+//             previous/next-smaller-value links at lb and rb+1 and moves to the enclosing lcp interval in one iteration.
+//             Shortening the pattern to any depth above the parent's leaves the interval -- and therefore the outcome of
+//             the failed extension -- unchanged, so jumping straight to the parent's depth max(lcp[lb], lcp[rb+1]) visits
+//             exactly the intervals that matter and ends in the same state as shortening one symbol at a time.
 // ================================================================================================================
-enum : uint32_t { PH_FETCH = 0, PH_STEP = 1, PH_LCP = 2, PH_DONE = 3 };
+enum : uint32_t { PH_FETCH = 0, PH_STEP = 1, PH_UP = 2, PH_DONE = 3 };
 enum : uint32_t
 {
     LF_PENDING = 1u,   // the last step produced a hit whose group uniqueness is not yet known
     LF_HAVE_G = 2u,    // a group load is in flight / waiting in `gval`
-    LF_MATE2 = 4u,     // paired: the second mate of the unit is being scanned
-    LF_LFOUND = 8u,    // PH_LCP: left boundary found
-    LF_RFOUND = 16u    // PH_LCP: right boundary found
+    LF_MATE2 = 4u      // paired: the second mate of the unit is being scanned
 };
 
 struct Lane
@@ -202,8 +188,6 @@ struct Lane
     uint64_t wbase, g0;
     uint64_t u;
     uint32_t rgroup;        // back-check: variant of the text being scanned
-    uint32_t cl, cr;        // PH_LCP: chunk indices still to scan; then the boundaries found
-    uint32_t nlb, nrb1;
     uint32_t gval, gt;      // group of the last unique hit (load result) and the window end it belongs to
     uint32_t gmin, gmax;    // unit-level ambiguity state
     uint32_t agg_g, agg_n;  // run-length aggregation of this lane's unique tallies
@@ -214,19 +198,17 @@ struct Lane
 
 struct Plan
 {
-    bool blocks, word, lcp_l, lcp_r, fetch;
+    bool blocks, word, up, fetch;
     const KBlock * pa;
     const KBlock * pb;
     const uint64_t * pw;
     const uint32_t * pi;
-    const uint8_t * pl;
-    const uint8_t * pr;
     uint64_t fr;   // read (or segment) index to fetch
 };
 
 struct Loads
 {
-    BlkRegs A, B;           // KBlocks at lb / rb+1; in PH_LCP A.w[0..7] / B.w[0..7] hold the left / right lcp chunk
+    BlkRegs A, B;           // KBlocks at lb / rb+1; in PH_UP: A.w[0] = lcp[lb], A.w[2] = psv[lb]; B.w[0] = lcp[rb+1], B.w[3] = nsv[rb+1]
     uint64_t rdw;
     uint32_t rdi;
     uint32_t flen, fstart, fgroup;
@@ -243,14 +225,14 @@ struct ScanCfg
 SPEQB_HD void lane_init(Lane & s, uint64_t first_unit)
 {
     s.phase = PH_FETCH; s.flags = 0; s.lb = 0; s.rb = 0; s.d = 0; s.run = 0; s.t = 0; s.pend = 0; s.cw = 0xFFFFFFFFu; s.winv = 0;
-    s.wbase = 0; s.g0 = 0; s.u = first_unit; s.rgroup = 0; s.cl = s.cr = s.nlb = s.nrb1 = 0; s.gval = 0; s.gt = 0;
+    s.wbase = 0; s.g0 = 0; s.u = first_unit; s.rgroup = 0; s.gval = 0; s.gt = 0;
     s.gmin = kNoGroup; s.gmax = 0; s.agg_g = kNoGroup; s.agg_n = 0; s.agg_w = 0.0; s.c_total = s.c_look = 0; s.c_amb = s.c_reads = 0;
 }
 
 SPEQB_HD void lane_plan(Lane const & s, DevIndex const & ix, BatchView const & b, ScanCfg const & cfg, Plan & p)
 {
-    p.blocks = p.word = p.lcp_l = p.lcp_r = p.fetch = false;
-    p.pa = p.pb = ix.blocks; p.pw = b.bases; p.pi = b.inv; p.pl = p.pr = ix.lcp; p.fr = 0;
+    p.blocks = p.word = p.up = p.fetch = false;
+    p.pa = p.pb = ix.blocks; p.pw = b.bases; p.pi = b.inv; p.fr = 0;
     if (s.phase == PH_STEP)
     {
         bool stepping = s.t < s.pend;
@@ -261,13 +243,8 @@ SPEQB_HD void lane_plan(Lane const & s, DevIndex const & ix, BatchView const & b
         p.pw = b.bases + s.g0 + (s.t >> 5);
         p.pi = b.inv + s.g0 + (s.t >> 5);
     }
-    else if (s.phase == PH_LCP)
-    {
-        p.lcp_l = !(s.flags & LF_LFOUND);
-        p.lcp_r = !(s.flags & LF_RFOUND);
-        p.pl = ix.lcp + (size_t)s.cl * kLcpChunk;
-        p.pr = ix.lcp + (size_t)s.cr * kLcpChunk;
-    }
+    else if (s.phase == PH_UP)
+        p.up = true;   // lcp[lb], lcp[rb+1], pn[lb], pn[rb+1]: addressed from s.lb / s.rb by the caller
     else if (s.phase == PH_FETCH)
     {
         p.fetch = s.u < cfg.units;
@@ -356,9 +333,8 @@ SPEQB_HD void lane_consume(Lane & s, Loads const & ld, DevIndex const & ix, cons
                     s.d = k - 1u;
                     if (zl == 0ull || zr == 0ull)
                     {
-                        // the widened interval leaves the two blocks: general contraction, then come back
-                        s.phase = PH_LCP; s.flags &= ~(LF_LFOUND | LF_RFOUND);
-                        s.cl = s.lb >> 5; s.cr = (s.rb + 1u) >> 5;
+                        // the widened interval leaves the two blocks: it is the parent lcp interval (depth k-1); jump there
+                        s.phase = PH_UP;
                         return;
                     }
                     jl = 63u - clz64(zl);
@@ -378,14 +354,9 @@ SPEQB_HD void lane_consume(Lane & s, Loads const & ld, DevIndex const & ix, cons
             }
             else if (s.d != 0u)
             {
-                // read[t-d..t] does not occur: shorten from the left and try the same base again
-                s.d -= 1u;
-                if (s.d == 0u) { s.lb = 0u; s.rb = ix.n - 1u; }
-                else
-                {
-                    s.phase = PH_LCP; s.flags &= ~(LF_LFOUND | LF_RFOUND);
-                    s.cl = s.lb >> 5; s.cr = (s.rb + 1u) >> 5;
-                }
+                // read[t-d..t] does not occur: shorten it from the left (to the parent interval) and try the same base again
+                if (s.d == 1u) { s.lb = 0u; s.rb = ix.n - 1u; s.d = 0u; }
+                else s.phase = PH_UP;
                 return;
             }
             s.run += 1u;
@@ -414,28 +385,20 @@ SPEQB_HD void lane_consume(Lane & s, Loads const & ld, DevIndex const & ix, cons
         s.phase = PH_FETCH;
         return;
     }
-    if (s.phase == PH_LCP)
+    if (s.phase == PH_UP)
     {
-        // maximal range around [lb, rb] whose inner lcp values are all >= d
-        if (!(s.flags & LF_LFOUND))
+        // parent of the lcp interval [lb, rb]: string depth l = max(lcp[lb], lcp[rb+1]); the side(s) whose lcp equals l move to
+        // the previous / next position with a smaller lcp value
+        uint32_t ll = ld.A.w[0], lr = ld.B.w[0];
+        uint32_t l = ll > lr ? ll : lr;
+        if (l == 0u) { s.lb = 0u; s.rb = ix.n - 1u; }
+        else
         {
-            uint32_t lt = lcp_lt_bits(ld.A.w, s.d);
-            if (s.cl == (s.lb >> 5)) lt &= (2u << (s.lb & 31u)) - 1u;      // first chunk: only bytes at or below lb
-            if (lt) { s.nlb = s.cl * kLcpChunk + 31u - clz32(lt); s.flags |= LF_LFOUND; }
-            else s.cl -= 1u;                                                // lcp[0] = 0 stops the scan
+            if (ll == l) s.lb = ld.A.w[2];
+            if (lr == l) s.rb = ld.B.w[3] - 1u;
         }
-        if (!(s.flags & LF_RFOUND))
-        {
-            uint32_t lt = lcp_lt_bits(ld.B.w, s.d);
-            if (s.cr == ((s.rb + 1u) >> 5)) lt &= ~0u << ((s.rb + 1u) & 31u);   // first chunk: only bytes above rb
-            if (lt) { s.nrb1 = s.cr * kLcpChunk + ctz32(lt); s.flags |= LF_RFOUND; }
-            else s.cr += 1u;                                                // the zero padding behind n stops the scan
-        }
-        if ((s.flags & (LF_LFOUND | LF_RFOUND)) == (LF_LFOUND | LF_RFOUND))
-        {
-            s.lb = s.nlb; s.rb = s.nrb1 - 1u;
-            s.phase = PH_STEP;
-        }
+        s.d = l;
+        s.phase = PH_STEP;
         return;
     }
     if (s.phase == PH_FETCH)

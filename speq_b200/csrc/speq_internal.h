@@ -26,6 +26,7 @@ struct HostIndex
     std::vector<KBlock> blocks;            // n/64 + 1 blocks; e bits zero (they are filled per scan, for the scan's k)
     std::vector<uint16_t> grp;             // n: variant of the text owning suffix SA[i] (kNoGroup16: delimiter / sentinel)
     std::vector<uint8_t> lcp;              // lcp_padded_size(n) entries (zero padded), capped at kLcpCap
+    std::vector<uint2x> pn;                // n + 1: previous / next smaller lcp value positions (fm_layout.h)
     std::vector<uint32_t> n_pos;           // sorted BWT positions holding N
     uint64_t n_exc = 0;                    // BWT positions holding N / delimiter / sentinel
     std::vector<int32_t> group_of_text;    // S
@@ -44,6 +45,7 @@ struct DeviceIndex
     KBlock * blocks = nullptr;
     uint16_t * grp = nullptr;
     uint8_t * lcp = nullptr;
+    uint2x * pn = nullptr;
     uint32_t * n_pos = nullptr;
     uint32_t * ctab = nullptr;
     // texts batch

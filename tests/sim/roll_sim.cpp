@@ -35,6 +35,7 @@ void make_view(HostIndex const & h, uint32_t k, HostView & hv)
     }
     hv.ix.blocks = hv.blocks_k.data();
     hv.ix.lcp = h.lcp.data();
+    hv.ix.pn = h.pn.data();
     hv.ix.grp = h.grp.data();
     hv.ix.n_pos = h.n_pos.data();
     hv.ix.ctab = hv.ctab;
@@ -70,15 +71,19 @@ struct HostEnv
     void backtotal(uint32_t g, uint32_t n) const { totg[g] += n; }
 };
 
-void do_loads(Plan const & p, Loads & ld, BatchView const & b, std::vector<uint32_t> const & seg_tab, bool back)
+void do_loads(Plan const & p, Loads & ld, Lane const & s, DevIndex const & ix, BatchView const & b, std::vector<uint32_t> const & seg_tab, bool back)
 {
     if (p.blocks)
     {
         memcpy(ld.A.w, p.pa, 64);
         memcpy(ld.B.w, p.pb, 64);
     }
-    if (p.lcp_l) memcpy(ld.A.w, p.pl, 32);
-    if (p.lcp_r) memcpy(ld.B.w, p.pr, 32);
+    if (p.up)
+    {
+        ld.A.w[0] = ix.lcp[s.lb]; ld.B.w[0] = ix.lcp[s.rb + 1u];
+        ld.A.w[2] = ix.pn[s.lb].x; ld.A.w[3] = ix.pn[s.lb].y;
+        ld.B.w[2] = ix.pn[s.rb + 1u].x; ld.B.w[3] = ix.pn[s.rb + 1u].y;
+    }
     if (p.word) { ld.rdw = *p.pw; ld.rdi = *p.pi; }
     if (p.fetch)
     {
@@ -99,7 +104,7 @@ extern "C" {
 int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, const int32_t * group_of_text, uint32_t V,
              const uint64_t * bases, const uint32_t * inv, const uint8_t * qual, const uint64_t * grp_off, const uint32_t * len,
              uint64_t n_reads, uint32_t k, int paired, int algo, int backcheck, int local, uint32_t nlanes, uint32_t seg_len,
-             uint64_t * out, double * out_w, uint64_t * mult)
+             uint64_t * out, double * out_w, uint64_t * mult, uint64_t * phase_counts)
 {
     try
     {
@@ -155,9 +160,10 @@ int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, c
                     Lane & s = lanes[l];
                     if (s.phase == PH_DONE) continue;
                     any = true;
+                    if (phase_counts) ++phase_counts[s.phase];
                     Plan p;
                     lane_plan(s, ix, bv, cfg, p);
-                    do_loads(p, loads[l], bv, seg_tab, backcheck != 0);
+                    do_loads(p, loads[l], s, ix, bv, seg_tab, backcheck != 0);
                     lane_consume(s, loads[l], ix, hv.ctab, cfg, env);
                 }
                 if (++guard > (1ull << 40)) return -2;

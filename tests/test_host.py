@@ -134,7 +134,7 @@ def test_index_matches_oracle_dump(lib, oracle_bin, tmp_path):
 
 
 def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck=False, want_mult=False, local=False, nlanes=7,
-              seg_len=37):
+              seg_len=37, phases=None):
     texts, grp = [], []
     for j, s in enumerate(scaff):
         texts += [np.ascontiguousarray(s), np.ascontiguousarray(engine.revcomp_ranks(s))]
@@ -155,7 +155,7 @@ def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck
                       C.c_void_p(pb.grp_off.ctypes.data), C.c_void_p(pb.len.ctypes.data), C.c_uint64(pb.n_reads), C.c_uint32(k),
                       C.c_int(int(paired)), C.c_int(algo), C.c_int(int(backcheck)), C.c_int(int(local)), C.c_uint32(nlanes),
                       C.c_uint32(seg_len), C.c_void_p(out.ctypes.data), C.c_void_p(out_w.ctypes.data),
-                      C.c_void_p(mult.ctypes.data if want_mult else None))
+                      C.c_void_p(mult.ctypes.data if want_mult else None), C.c_void_p(phases.ctypes.data if phases is not None else None))
     assert rc == 0
     return out, out_w, mult
 
