@@ -107,7 +107,7 @@ template <int MODE> struct DevEnv
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(kBlock) scan_roll_kernel(const DevIndex ix, const BatchView b, const ScanArgs a, const int paired)
+__global__ void __launch_bounds__(kBlock, 3) scan_roll_kernel(const DevIndex ix, const BatchView b, const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
     constexpr bool RECORD = (MODE & M_RECORD) != 0;

@@ -68,7 +68,7 @@ class Reducer:
             return a
         import torch
         import torch.distributed as dist
-        t = torch.from_numpy(np.ascontiguousarray(a, np.float64)).to(self.device or "cpu")
+        t = torch.from_numpy(np.array(a, dtype=np.float64, copy=True)).to(self.device or "cpu")   # never alias the caller's array
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t.cpu().numpy()
 
