@@ -16,10 +16,11 @@ ROOT = Path(__file__).resolve().parent
 CSRC = ROOT / "csrc"
 LIB_DIR = ROOT / "lib"
 LIB = LIB_DIR / "libspeq_cuda.so"
+OBJ_DIR = ROOT / "build"
 CLI_SRC = ROOT / "host"
 CLI_BIN = ROOT / "bin" / "speq"
 
-LIB_SOURCES = ["capi.cu", "capi_scan.cu", "capi_refine.cu", "kernels.cu", "index_build.cpp", "pack.cpp"]
+LIB_SOURCES = ["capi.cu", "capi_scan.cu", "capi_refine.cu", "kernels.cu", "scan32.cu", "index_build.cpp", "pack.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall,-pthread"]
 
 
@@ -42,14 +43,30 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
     if not force and not _stale(LIB, deps):
         return LIB
     LIB_DIR.mkdir(exist_ok=True)
-    cmd = [nvcc(), *NVCC_FLAGS, "-shared", "-o", str(LIB)] + [str(CSRC / s) for s in LIB_SOURCES]
-    if verbose:
-        cmd.insert(1, "-Xptxas=-v")
+    OBJ_DIR.mkdir(exist_ok=True)
+    headers = [d for d in deps if d.suffix in (".h", ".hpp")]
+
+    def compile_one(src: str) -> Path:
+        obj = OBJ_DIR / (src + ".o")
+        if not force and not _stale(obj, [CSRC / src] + headers):
+            return obj
+        cmd = [nvcc(), *NVCC_FLAGS, "-c", str(CSRC / src), "-o", str(obj)]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+        if verbose:
+            print(r.stderr)
+        return obj
+
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(len(LIB_SOURCES), os.cpu_count() or 2)) as ex:
+        objs = list(ex.map(compile_one, LIB_SOURCES))
+    cmd = [nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC", "-o", str(LIB)] + [str(o) for o in objs]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
+        raise RuntimeError("link failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
     return LIB
 
 

@@ -62,21 +62,20 @@ struct speqg_scan
     speqg_index * idx = nullptr;
     DeviceIndex * di = nullptr;
     DevIndex view{};               // di->view with `blocks` replaced by this scan's k-specialised copy
-    KBlock * d_blocks_k = nullptr;
+    KBlock * d_blocks_k = nullptr;   // SPEQG_ALGO_ROLLING64 only
+    SBlock * d_sblk = nullptr;       // per-k 32-byte blocks of the product kernel
     int device = 0;
     speqg_params p{};
     int mode = 0;
     cudaStream_t compute = nullptr, copy = nullptr;
     bool own_compute = false;
-    unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr;
+    unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
     double * d_unique_w = nullptr, * d_qden = nullptr, * d_percent = nullptr, * d_tkpg = nullptr, * d_partial = nullptr;
     int32_t * d_gc = nullptr;
-    LaunchCfg cfg{}, cfg_direct{}, cfg_stats{};
+    LaunchCfg cfg{}, cfg64{}, cfg_direct{}, cfg_stats{};
     int refine_grid = 0;
     Slot slots[kSlots];
     int next_slot = 0;
-    std::vector<uint64_t> h_grp_off;   // scratch for submit_raw
-    std::vector<uint32_t> h_len;
     uint64_t launches = 0;
 };
 
@@ -107,7 +106,7 @@ void scan_release(speqg_scan * s)
 {
     cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
     cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
-    cudaFree(s->d_gc); cudaFree(s->d_blocks_k);
+    cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk); cudaFree(s->d_work);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -126,6 +125,13 @@ ScanArgs scan_args(speqg_scan * s)
     a.qden = s->d_qden;
     a.segs = nullptr;
     a.n_segs = 0;
+    a.work = s->d_work;
+    static const uint32_t sym_of_code[4] = {1, 2, 3, 5};   // text symbols of A,C,G,T (N = 4 sits between G and T)
+    for (int c = 0; c < 4; ++c)
+    {
+        a.cbeg[c] = (uint32_t)s->idx->host.C[sym_of_code[c]];
+        a.cend[c] = (uint32_t)s->idx->host.C[sym_of_code[c] + 1];
+    }
     return a;
 }
 
@@ -144,7 +150,8 @@ void launch_on_view(speqg_scan * s, BatchView const & v)
     if (v.n_reads == 0) return;
     ScanArgs a = scan_args(s);
     if (s->p.algorithm == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
-    else CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg, s->compute));
+    else if (s->p.algorithm == SPEQG_ALGO_ROLLING64) CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg64, s->compute));
+    else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
     ++s->launches;
 }
 
@@ -171,7 +178,9 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
     need(idx && params && out, "NULL argument");
     need(params->k >= 1 && params->k <= kMaxK, "k must be in [1, 127]");
     need(params->mode == SPEQG_MODE_GLOBAL || params->mode == SPEQG_MODE_LOCAL, "unknown mode");
-    need(params->algorithm == SPEQG_ALGO_ROLLING || params->algorithm == SPEQG_ALGO_DIRECT, "unknown algorithm");
+    need(params->algorithm == SPEQG_ALGO_ROLLING || params->algorithm == SPEQG_ALGO_DIRECT ||
+         params->algorithm == SPEQG_ALGO_ROLLING64, "unknown algorithm");
+    need(idx->host.n <= kMaxN32, "index too large: the indexed text must be shorter than 2^31 symbols");
     need(!(params->algorithm == SPEQG_ALGO_DIRECT && params->mode == SPEQG_MODE_LOCAL), "the direct algorithm covers global mode only");
     DeviceIndex & di = device_index(idx, device);
     device_guard guard(device);
@@ -197,6 +206,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->d_unique_w = dev_alloc<double>(V);
         s->d_scalars = dev_alloc<unsigned long long>(SC_COUNT);
         s->d_bad = dev_alloc<unsigned long long>(1);
+        s->d_work = dev_alloc<unsigned long long>(1);
         s->d_percent = dev_alloc<double>(V);
         s->d_tkpg = dev_alloc<double>(V);
         s->d_gc = dev_alloc<int32_t>(V);
@@ -209,12 +219,21 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             qden[q] = 1.0 - 1.0 / pow(10.0, b / 10.0);
         }
         s->d_qden = dev_upload(qden, 42);
-        // rank blocks specialised for this k (e bits = lcp >= k-1): one pass over the index, once per scan handle
-        s->d_blocks_k = dev_alloc<KBlock>(idx->host.blocks.size());
-        CK(launch_fill_e(di.blocks, s->d_blocks_k, di.lcp, (uint32_t)idx->host.n, params->k, s->compute));
+        // rank blocks specialised for this k: one pass over the index, once per scan handle
         s->view = di.view;
-        s->view.blocks = s->d_blocks_k;
-        CK(scan_launch_cfg(s->mode, 0, V, &s->cfg));
+        if (params->algorithm == SPEQG_ALGO_ROLLING64)
+        {
+            s->d_blocks_k = dev_alloc<KBlock>(idx->host.blocks.size());
+            CK(launch_fill_e(di.blocks, s->d_blocks_k, di.lcp, (uint32_t)idx->host.n, params->k, s->compute));
+            s->view.blocks = s->d_blocks_k;
+            CK(scan_launch_cfg(s->mode, 0, V, &s->cfg64));
+        }
+        else
+        {
+            s->d_sblk = dev_alloc<SBlock>(idx->host.n / 32 + 1);
+            CK(launch_fill32(di.blocks, di.lcp, di.pn, s->d_sblk, (uint32_t)idx->host.n, params->k, s->compute));
+        }
+        CK(scan32_launch_cfg(s->mode, V, &s->cfg));
         CK(scan_launch_cfg(s->mode, 1, V, &s->cfg_direct));
         CK(scan_launch_cfg(s->mode, 2, V, &s->cfg_stats));
         int sms = 0;
@@ -300,31 +319,22 @@ int speqg_scan_submit_raw(speqg_scan * s, const uint8_t * seq, const uint8_t * q
     need(n_reads < (uint64_t(1) << 32), "more than 2^32 reads in one batch");
     device_guard guard(s->device);
     uint64_t R = n_reads, base = offsets[0], bytes = offsets[R] - base;
-    s->h_grp_off.resize(R + 1);
-    uint64_t G = 0;
-    for (uint64_t i = 0; i < R; ++i)
-    {
-        uint64_t L = offsets[i + 1] - offsets[i];
-        need(L < (uint64_t(1) << 32), "read longer than 2^32");
-        s->h_grp_off[i] = G;
-        G += (L + 31) >> 5;
-    }
-    s->h_grp_off[R] = G;
+    need(offsets[R] >= base, "offsets must be non-decreasing");
+    // the device packer lays the reads out itself (group floor(o / 32) + r): no pass over the reads on the host
+    uint64_t G = (bytes >> 5) + R + 1;
     Slot & sl = acquire_slot(s);
     sl.bases.reserve(G + 1); sl.inv.reserve(G + 1); sl.grp_off.reserve(R + 1); sl.len.reserve(R); sl.raw_off.reserve(R + 1);
     sl.raw_seq.reserve(bytes + 1);
     if (qual) sl.raw_qual.reserve(bytes + 1);
     if (s->mode & M_LOCAL) sl.qual.reserve(G * 32 + 32);
-    // the host scratch (h_grp_off) is pageable: cudaMemcpyAsync stages it before returning, so it may be reused at once
     CK(cudaMemcpyAsync(sl.raw_seq.p, seq + base, bytes, cudaMemcpyHostToDevice, s->copy));
     if (qual) CK(cudaMemcpyAsync(sl.raw_qual.p, qual + base, bytes, cudaMemcpyHostToDevice, s->copy));
     CK(cudaMemcpyAsync(sl.raw_off.p, offsets, (R + 1) * 8, cudaMemcpyHostToDevice, s->copy));
-    CK(cudaMemcpyAsync(sl.grp_off.p, s->h_grp_off.data(), (R + 1) * 8, cudaMemcpyHostToDevice, s->copy));
     CK(cudaEventRecord(sl.copied, s->copy));
     CK(cudaStreamWaitEvent(s->compute, sl.copied, 0));
     // offsets are relative to `seq`; the device copy starts at offsets[0]
     CK(launch_pack(sl.raw_seq.p, qual ? sl.raw_qual.p : nullptr, base, sl.raw_off.p, R, encoding, s->p.phred_cutoff, 0,
-                   sl.bases.p, sl.inv.p, (s->mode & M_LOCAL) ? sl.qual.p : nullptr, sl.grp_off.p, sl.len.p, s->d_bad, s->compute));
+                   sl.bases.p, sl.inv.p, (s->mode & M_LOCAL) ? sl.qual.p : nullptr, sl.grp_off.p, 1, sl.len.p, s->d_bad, s->compute));
     ++s->launches;
     BatchView v{};
     v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = (s->mode & M_LOCAL) ? sl.qual.p : nullptr;
@@ -380,6 +390,7 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
     uint32_t V = s->idx->host.V;
     unsigned long long bad = 0;
     CK(cudaMemcpy(&bad, s->d_bad, 8, cudaMemcpyDeviceToHost));
+    if (bad & 2ull) throw api_error(SPEQG_EINVAL, "read longer than 2^32 bases");
     if (bad) throw api_error(SPEQG_EINVAL, "parse_error: illegal (non-IUPAC) sequence character in a read");
     if (unique_u64) CK(cudaMemcpy(unique_u64, s->d_unique, V * 8, cudaMemcpyDeviceToHost));
     if (unique_f64) CK(cudaMemcpy(unique_f64, s->d_unique_w, V * 8, cudaMemcpyDeviceToHost));

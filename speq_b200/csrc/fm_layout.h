@@ -64,6 +64,23 @@ struct __attribute__((aligned(64))) KBlock
 };
 static_assert(sizeof(KBlock) == 64, "KBlock must be 64 bytes");
 
+// SBlock: the scan kernel's per-k view of 32 consecutive suffixes in ONE 32-byte sector (one LDG.256 per lane):
+//   cnt[4]  occurrences of A,C,G,T in bwt[0, 32*b); bit 31 of cnt[0] = the block holds an exception (N / delimiter /
+//           sentinel in the BWT): the lane then fetches the exception mask from the KBlock array (rare slow path)
+//   lo, hi  the two bit planes of the 2-bit BWT codes, symbol j at bit j
+//   e       bit j: lcp[32b+j] >= k-1
+//   uq      bit j: every suffix of the depth-k lcp interval that contains suffix 32b+j belongs to one variant
+// Built on the device from the KBlocks + lcp + pn for the scan's k (fill32_kernel).  A window then costs two sector
+// loads (the blocks at lb and rb+1) and, when the k-mer is unique to a variant, one 2-byte group load.
+struct __attribute__((aligned(32))) SBlock
+{
+    uint32_t cnt[4];
+    uint32_t lo, hi, e, uq;
+};
+static_assert(sizeof(SBlock) == 32, "SBlock must be 32 bytes");
+constexpr uint32_t kSFlagExc = 0x80000000u;
+constexpr uint64_t kMaxN32 = 0x7FFFFFFFull;   // cnt[0] keeps bit 31 for the exception flag
+
 constexpr uint32_t kCtabEnd = 8;
 
 // Device view of the index (passed to kernels by value).

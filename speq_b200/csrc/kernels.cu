@@ -426,7 +426,7 @@ __global__ void __launch_bounds__(kBlock) pack_kernel(const uint8_t * __restrict
                                                       const uint64_t * __restrict__ offsets, const uint64_t n_reads, const int encoding,
                                                       const uint32_t cutoff, const int n_only, uint64_t * __restrict__ bases,
                                                       uint32_t * __restrict__ inv, uint8_t * __restrict__ qual_out,
-                                                      const uint64_t * __restrict__ grp_off, uint32_t * __restrict__ len,
+                                                      uint64_t * __restrict__ grp_off, const int make_grp_off, uint32_t * __restrict__ len,
                                                       unsigned long long * bad)
 {
     __shared__ uint8_t code[256];
@@ -454,12 +454,20 @@ __global__ void __launch_bounds__(kBlock) pack_kernel(const uint8_t * __restrict
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    bool any_bad = false;
+    bool any_bad = false, any_long = false;
     for (uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n_reads; r += nwarps)
     {
-        const uint64_t o = offsets[r] - off0, L = offsets[r + 1] - offsets[r], g0 = grp_off[r];
-        const uint64_t ng = (L + 31) >> 5;
-        if (lane == 0) len[r] = (uint32_t)L;
+        // make_grp_off: read r starts at 32-base group floor(o / 32) + r -- monotone, never overlapping (at most one group
+        // of slack per read), and computable without a prefix sum over the read lengths
+        const uint64_t o = offsets[r] - off0, L = offsets[r + 1] - offsets[r];
+        const uint64_t g0 = make_grp_off ? (o >> 5) + r : grp_off[r];
+        const uint64_t ng = (L >> 32) ? 0 : (L + 31) >> 5;
+        if (L >> 32) any_long = true;            // reported at finish; the read is presented as empty
+        if (lane == 0)
+        {
+            len[r] = (L >> 32) ? 0u : (uint32_t)L;
+            if (make_grp_off) grp_off[r] = g0;
+        }
         for (uint64_t g = lane; g < ng; g += 32u)
         {
             uint64_t w = 0;
@@ -486,7 +494,8 @@ __global__ void __launch_bounds__(kBlock) pack_kernel(const uint8_t * __restrict
             inv[g0 + g] = m;
         }
     }
-    if (any_bad) atomicExch(bad, 1ull);
+    if (any_bad) atomicOr(bad, 1ull);
+    if (any_long) atomicOr(bad, 2ull);
 }
 
 int g_sm_count = 0;
@@ -583,12 +592,12 @@ cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V,
 
 cudaError_t launch_pack(const uint8_t * seq, const uint8_t * qual, uint64_t off0, const uint64_t * offsets, uint64_t n_reads,
                         int encoding, uint32_t phred_cutoff, int n_only, uint64_t * bases, uint32_t * inv, uint8_t * qual_out,
-                        const uint64_t * grp_off, uint32_t * len, unsigned long long * bad, cudaStream_t st)
+                        uint64_t * grp_off, int make_grp_off, uint32_t * len, unsigned long long * bad, cudaStream_t st)
 {
     if (n_reads == 0) return cudaSuccess;
     uint64_t want = (n_reads * 32 + kBlock - 1) / kBlock;
     int grid = (int)std::min<uint64_t>(want, (uint64_t)sm_count() * 16);
-    pack_kernel<<<grid, kBlock, 0, st>>>(seq, qual, off0, offsets, n_reads, encoding, phred_cutoff, n_only, bases, inv, qual_out, grp_off, len, bad);
+    pack_kernel<<<grid, kBlock, 0, st>>>(seq, qual, off0, offsets, n_reads, encoding, phred_cutoff, n_only, bases, inv, qual_out, grp_off, make_grp_off, len, bad);
     return cudaGetLastError();
 }
 

@@ -40,6 +40,8 @@ struct ScanArgs
     const double * qden;              // [42] 1 - 1/pow(10, q/10), host libm values   (local mode)
     const SegmentX * segs;             // optional segment table (back-check); null: one segment per read / pair
     uint64_t n_segs;
+    uint32_t cbeg[4], cend[4];        // scan32: SA ranges of the 1-mers A,C,G,T (C table)
+    unsigned long long * work;        // scan32: next unclaimed unit minus the number of threads (zero at launch)
 };
 
 struct LaunchCfg
@@ -60,13 +62,22 @@ size_t scan_smem_bytes(uint32_t V);
 cudaError_t launch_refine(DevIndex const & ix, uint32_t k, const unsigned long long * mult, const double * percent,
                           const int32_t * group_counts, uint32_t V, double * partial, int grid, int block, cudaStream_t st);
 cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V, double * tkpg, cudaStream_t st);
-// device packer: raw reads (ASCII or dna5 ranks) already in device memory -> packed batch (grp_off / len precomputed).
+// device packer: raw reads (ASCII or dna5 ranks) already in device memory -> packed batch.  make_grp_off != 0: the kernel
+// lays read r out at 32-base group floor((offsets[r] - off0) / 32) + r and writes grp_off[r] itself (the batch then needs
+// (offsets[n_reads] - off0) / 32 + n_reads + 1 groups); else grp_off is an input.
 // *bad is set to 1 when an illegal sequence character is met.
 // seq / qual hold the bytes [off0, offsets[n_reads]) of the caller's arrays (offsets are relative to the caller's).
 cudaError_t launch_pack(const uint8_t * seq, const uint8_t * qual, uint64_t off0, const uint64_t * offsets, uint64_t n_reads,
                         int encoding, uint32_t phred_cutoff, int n_only, uint64_t * bases, uint32_t * inv, uint8_t * qual_out,
-                        const uint64_t * grp_off, uint32_t * len, unsigned long long * bad, cudaStream_t st);
+                        uint64_t * grp_off, int make_grp_off, uint32_t * len, unsigned long long * bad, cudaStream_t st);
 // per-scan specialisation of the rank blocks: copy `src` to `dst` and fill the e bits (lcp >= k-1) for this k
 cudaError_t launch_fill_e(const KBlock * src, KBlock * dst, const uint8_t * lcp, uint32_t n, uint32_t k, cudaStream_t st);
+// the product scan kernel (scan32.cu): rolling window over the per-k 32-byte SBlocks; a.work must point to one u64
+cudaError_t launch_scan32(const SBlock * sblk, DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg,
+                          cudaStream_t st);
+cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
+size_t scan32_smem_bytes(uint32_t V);
+// per-scan specialisation: SBlocks (rank counts, bit planes, e = lcp >= k-1, uq = depth-k interval in one variant) for this k
+cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, SBlock * out, uint32_t n, uint32_t k, cudaStream_t st);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

@@ -1,0 +1,325 @@
+// scan32.cu -- the product scan kernel for sm_100a and the per-k index specialisation it runs on.
+//
+//   fill32_kernel   builds the 32-byte SBlocks (fm_layout.h) for one k from the stored index: rank counts and bit planes
+//                   from the KBlocks, e bits (lcp >= k-1) and uq bits (the depth-k lcp interval of the suffix lies in one
+//                   variant) from lcp, the previous/next-smaller links and the group-change counts.
+//   scan32_kernel   one lane per read (pair): the flat state machine of scan32_core.h.  Every trip of the loop issues
+//                   all loads of the iteration back to back (two LDG.256 for the blocks at lb and rb1; the read group,
+//                   parent-jump and fetch loads only in the iterations that need them) and then consumes them, so a
+//                   window costs one round trip to L2 / HBM.  Units are claimed with one warp-aggregated atomic, tallies
+//                   live in shared memory and reach global memory with one atomic per variant and CTA.
+//
+// Reference behaviour covered: worker / do_a_count of speq::scan::_async_{one,two}_with_{global,local}_error_rate
+// (src/fm_scanner.cpp:145-216, 418-491, 662-732, 911-998).
+#include <algorithm>
+
+#include "kernels.h"
+#include "scan32_core.h"
+
+namespace speqb
+{
+namespace
+{
+constexpr int kBlock32 = 256;
+constexpr uint32_t kFull = 0xFFFFFFFFu;
+
+__device__ __forceinline__ void ld256_if(uint32_t * w, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %9, 0;\n\t@q ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]), "+r"(w[6]), "+r"(w[7])
+                 : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld64_if(uint64_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u64 %0, [%1];\n\t}" : "+l"(v) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld32x2_if(uint32_t & x, uint32_t & y, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %3, 0;\n\t@q ld.global.nc.v2.u32 {%0,%1}, [%2];\n\t}" : "+r"(x), "+r"(y) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld32_if(uint32_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld8_if(uint32_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u8 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
+}
+
+// shared-memory tallies of one CTA
+struct Smem32
+{
+    double * w;                   // [V] local-mode weighted unique tallies
+    uint32_t * cnt;               // [V] unique tallies (global mode)
+    unsigned long long * scal;    // [4] total, ambiguous, lookups, reads
+};
+__device__ __forceinline__ Smem32 smem32_view(unsigned char * raw, uint32_t V)
+{
+    Smem32 s;
+    s.scal = reinterpret_cast<unsigned long long *>(raw);
+    s.w = reinterpret_cast<double *>(raw + 32);
+    s.cnt = reinterpret_cast<uint32_t *>(raw + 32 + (size_t)V * 8);
+    return s;
+}
+
+template <int MODE> struct Env32
+{
+    static constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
+    DevIndex const & ix;
+    BatchView const & b;
+    ScanArgs const & a;
+    Smem32 sm;
+    __device__ __forceinline__ uint32_t load_grp(uint32_t i) const
+    {
+        uint32_t v;
+        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(v) : "l"(ix.grp + i));
+        return v;
+    }
+    __device__ __forceinline__ uint32_t exc_word(uint32_t blk) const { return load_ro(&ix.blocks[blk >> 1].exc[blk & 1u]); }
+    __device__ __forceinline__ double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
+    {
+        // window = positions [t_end-k, t_end); the left fold of src/fm_scanner.cpp:454, a / (1 - 1/pow(10, q/10)), with
+        // the denominators tabulated by the host's libm: IEEE division keeps every weight bit-exact
+        const uint8_t * q = b.qual + 32u * g0 + (t_end - k);
+        double w = 1.0;
+        for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
+        return w;
+    }
+    __device__ __forceinline__ void unique(uint32_t g, uint32_t n, double w) const
+    {
+        if (LOCAL) atomicAdd(&sm.w[g], w);
+        else atomicAdd(&sm.cnt[g], n);
+    }
+    __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(a.mult + lb, 1ull); }
+    __device__ __forceinline__ void count_fetch(uint32_t nwin) const
+    {
+        atomicAdd(&sm.scal[2], (unsigned long long)nwin);
+        atomicAdd(&sm.scal[3], 1ull);
+    }
+    __device__ __forceinline__ void count_unit(uint32_t total, bool amb) const
+    {
+        if (total) atomicAdd(&sm.scal[0], (unsigned long long)total);
+        if (amb) atomicAdd(&sm.scal[1], 1ull);
+    }
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const SBlock * __restrict__ sblk, const DevIndex ix, const BatchView b,
+                                                             const ScanArgs a, const int paired)
+{
+    constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
+    constexpr bool RECORD = (MODE & M_RECORD) != 0;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem32 sm = smem32_view(smem_raw, a.V);
+    if (threadIdx.x < 4) sm.scal[threadIdx.x] = 0ull;
+    for (uint32_t g = threadIdx.x; g < a.V; g += blockDim.x)
+    {
+        sm.w[g] = 0.0;
+        sm.cnt[g] = 0u;
+    }
+    __syncthreads();
+
+    Cfg32 cfg;
+    cfg.k = a.k;
+    cfg.n = ix.n;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+    {
+        cfg.cbeg[c] = a.cbeg[c];
+        cfg.cend[c] = a.cend[c];
+    }
+    cfg.units = paired ? b.n_reads / 2 : b.n_reads;
+    cfg.paired = paired;
+    cfg.local = LOCAL;
+    cfg.record = RECORD;
+    Env32<MODE> env{ix, b, a, sm};
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+
+    Lane32 s;
+    lane32_init(s, (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, ix.n);
+    Loads32 ld;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ld.A[i] = ld.B[i] = 0u;
+
+    while (true)
+    {
+        __syncwarp();
+        const uint32_t ph = s.phase;
+        const uint32_t m_up = __ballot_sync(kFull, ph == P_UP);
+        const uint32_t m_fe = __ballot_sync(kFull, ph == P_FETCH);
+        if (!__any_sync(kFull, ph != P_DONE)) break;
+        // ---- every load of this iteration, issued before anything is consumed
+        const bool stp = ph == P_STEP;
+        ld256_if(ld.A, sblk + (s.lb >> 5), stp);
+        ld256_if(ld.B, sblk + (s.rb1 >> 5), stp);
+        {
+            // the next 32 bases of the read: straight into the lane's window registers (all 32 old bases are consumed)
+            const bool needw = stp && s.t < s.pend && (s.t & 31u) == 0u;
+            ld32x2_if(s.wlo, s.whi, b.bases + s.g0 + (s.t >> 5), needw);
+            ld32_if(s.winv, b.inv + s.g0 + (s.t >> 5), needw);
+        }
+        if (m_up)
+        {
+            const bool up = ph == P_UP;
+            ld8_if(ld.B[0], ix.lcp + s.lb, up);
+            ld8_if(ld.B[1], ix.lcp + s.rb1, up);
+            ld32_if(ld.B[2], &ix.pn[s.lb].x, up);
+            ld32_if(ld.B[3], &ix.pn[s.rb1].y, up);
+        }
+        if (m_fe)
+        {
+            const bool fetch = ph == P_FETCH && s.u < cfg.units;
+            const uint64_t fr = lane32_fetch_read(s, cfg);
+            ld32_if(ld.B[4], b.len + fr, fetch);
+            ld32x2_if(ld.B[5], ld.B[6], b.grp_off + fr, fetch);
+            // claim the unit after this one: one atomic per warp and iteration
+            const bool claim = fetch && !(s.flags & F_MATE2);
+            const uint32_t mc = __ballot_sync(kFull, claim);
+            if (mc)
+            {
+                const int leader = __ffs((int)mc) - 1;
+                unsigned long long base = 0ull;
+                if ((int)lane == leader) base = atomicAdd(a.work, (unsigned long long)__popc(mc));
+                base = __shfl_sync(kFull, base, leader);
+                if (claim) s.unext = nthreads + base + (uint64_t)__popc(mc & ((1u << lane) - 1u));
+            }
+        }
+        // ---- consume
+        if (stp) lane32_step(s, ld, cfg, env);
+        else if (ph == P_UP) lane32_up(s, ld, cfg);
+        else if (ph == P_FETCH) lane32_fetch(s, ld, cfg, env);
+    }
+    lane32_flush_agg(s, env);
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        if (sm.scal[0]) atomicAdd(a.scalars + SC_TOTAL, sm.scal[0]);
+        if (sm.scal[1]) atomicAdd(a.scalars + SC_AMBIG, sm.scal[1]);
+        if (sm.scal[2]) atomicAdd(a.scalars + SC_LOOKUPS, sm.scal[2]);
+        if (sm.scal[3]) atomicAdd(a.scalars + SC_READS, sm.scal[3]);
+    }
+    for (uint32_t g = threadIdx.x; g < a.V; g += blockDim.x)
+    {
+        if (LOCAL) { if (sm.w[g] != 0.0) atomicAdd(a.unique_w + g, sm.w[g]); }
+        else if (sm.cnt[g]) atomicAdd(a.unique + g, (unsigned long long)sm.cnt[g]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Per-k specialisation: one warp per SBlock, one lane per suffix.
+//   e bit   lcp[i] >= k-1
+//   uq bit  the maximal run of suffixes around i whose neighbours share >= k symbols (the SA interval of the k-mer that
+//           prefixes suffix i) holds no group change.  Its ends are found by hopping over the previous / next-smaller
+//           links (every hop lowers the lcp value, so at most kLcpCap hops), the changes are counted with the KBlocks'
+//           chg bits and cumulative counts.  Suffixes shorter than k are never the lb of a depth-k hit.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t chg_upto(const KBlock * kb, uint32_t j)
+{
+    const KBlock * p = kb + (j >> 6);
+    return load_ro(&p->chgcum) + popc64(u64of(load_ro(&p->chg[0]), load_ro(&p->chg[1])) & upto64(j & 63u));
+}
+
+__global__ void __launch_bounds__(kBlock32) fill32_kernel(const KBlock * __restrict__ kb, const uint8_t * __restrict__ lcp,
+                                                          const uint2x * __restrict__ pn, SBlock * __restrict__ out, const uint32_t n,
+                                                          const uint32_t k)
+{
+    const uint32_t nblocks = n / 32u + 1u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; blk < nblocks; blk += nwarps)
+    {
+        const uint32_t i = blk * 32u + lane;
+        bool e = false, uq = false;
+        if (i < n)
+        {
+            e = (uint32_t)lcp[i] + 1u >= k;
+            uint32_t s = i;
+            while ((uint32_t)lcp[s] >= k) s = pn[s].x;
+            uint32_t t = i + 1u;
+            while ((uint32_t)lcp[t] >= k) t = pn[t].y;
+            uq = chg_upto(kb, t - 1u) == chg_upto(kb, s);
+        }
+        const uint32_t we = __ballot_sync(kFull, e), wu = __ballot_sync(kFull, uq);
+        const KBlock * p = kb + (blk >> 1);
+        const uint32_t half = blk & 1u;
+        uint32_t v = 0u;
+        if (lane < 4u)
+        {
+            v = p->cnt[lane];
+            if (half)
+            {
+                const uint32_t xl = (lane & 1u) ? 0u : ~0u, xh = (lane & 2u) ? 0u : ~0u;
+                v += popc32((p->lo[0] ^ xl) & (p->hi[0] ^ xh) & ~p->exc[0]);
+            }
+            if (lane == 0u && p->exc[half] != 0u) v |= kSFlagExc;
+        }
+        else if (lane == 4u) v = p->lo[half];
+        else if (lane == 5u) v = p->hi[half];
+        else if (lane == 6u) v = we;
+        else if (lane == 7u) v = wu;
+        if (lane < 8u) reinterpret_cast<uint32_t *>(out + blk)[lane] = v;
+    }
+}
+
+int g_sm_count32 = 0;
+int sm_count32()
+{
+    if (g_sm_count32 == 0)
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count32, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count32 <= 0) g_sm_count32 = 148;
+    }
+    return g_sm_count32;
+}
+}   // namespace
+
+size_t scan32_smem_bytes(uint32_t V) { return 32 + (size_t)V * 12; }
+
+#define SPEQB_SCAN32_DISPATCH(M, EXPR)                                                             \
+    switch (M)                                                                                     \
+    {                                                                                              \
+        case 0: { auto kern = scan32_kernel<0>; EXPR; break; }                                     \
+        case M_RECORD: { auto kern = scan32_kernel<M_RECORD>; EXPR; break; }                       \
+        case M_LOCAL: { auto kern = scan32_kernel<M_LOCAL>; EXPR; break; }                         \
+        case M_LOCAL | M_RECORD: { auto kern = scan32_kernel<M_LOCAL | M_RECORD>; EXPR; break; }   \
+        default: return cudaErrorInvalidValue;                                                     \
+    }
+
+cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
+{
+    const size_t smem = scan32_smem_bytes(V);
+    int bps = 0;
+    cudaError_t e = cudaSuccess;
+    const int m = mode & (M_LOCAL | M_RECORD);
+    SPEQB_SCAN32_DISPATCH(m, {
+        if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlock32, smem);
+    })
+    if (e != cudaSuccess) return e;
+    if (bps <= 0) return cudaErrorLaunchOutOfResources;
+    cfg->block = kBlock32;
+    cfg->grid = sm_count32() * bps;
+    return cudaSuccess;
+}
+
+cudaError_t launch_scan32(const SBlock * sblk, DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg,
+                          cudaStream_t st)
+{
+    const size_t smem = scan32_smem_bytes(a.V);
+    const int paired = (mode & M_PAIRED) ? 1 : 0;
+    const int m = mode & (M_LOCAL | M_RECORD);
+    cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    SPEQB_SCAN32_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(sblk, ix, b, a, paired)))
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, SBlock * out, uint32_t n, uint32_t k, cudaStream_t st)
+{
+    fill32_kernel<<<sm_count32() * 8, kBlock32, 0, st>>>(kb, lcp, pn, out, n, k);
+    return cudaGetLastError();
+}
+}   // namespace speqb

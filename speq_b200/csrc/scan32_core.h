@@ -1,0 +1,266 @@
+// scan32_core.h -- per-lane arithmetic of the product scan kernel (scan32.cu): the rolling k-mer window over the
+// 32-byte SBlocks (fm_layout.h), as a flat state machine in which every iteration costs one round trip to memory.
+//
+// __host__ __device__ like scan_core.h: scan32.cu runs it on the GPU; tests/sim compiles the same header with g++ as a
+// white-box check of the state machine against the oracle in the CPU-only test tier (never shipped, never linked into
+// libspeq_cuda.so).
+//
+// Reference arithmetic reproduced (S3 = deps/seqan3 of the reference checkout):
+//   step        fm_index_cursor::backward_search, S3/include/seqan3/search/fm_index/fm_index_cursor.hpp:110-146
+//   window rule ranges::views::sliding(k) (range-v3 view/sliding.hpp:129-142); valid iff no base of the window is N or
+//               has phred <= cutoff (src/fm_scanner.cpp:162)
+//   tallies     do_a_count, src/fm_scanner.cpp:153-196 (global), :426-471 (local), :665-708 / :916-962 (paired)
+// State of a lane: the SA interval [lb, rb1) of the longest suffix of read[0..t) that occurs in the text, capped at k
+// symbols (depth d).  The SA interval of a pattern is unique, so the interval reported for a window is bit-identical to
+// the one k backward-search steps from the root produce.
+//   P_STEP   loads the SBlocks at lb and rb1.  Resolves the previous window's hit (uq bit at lb -> group load), slides
+//            the window (d == k: contract to depth k-1 with the e bits), and extends by the next base (rank step).
+//   P_UP     parent jump (failed extension, or the e-bit scan left the two blocks): loads lcp + previous/next-smaller
+//            links at lb and rb1 and moves to the enclosing lcp interval.
+//   P_FETCH  next unit (read or pair): loads its length and first 32-base group.
+#pragma once
+#include "scan_core.h"
+
+namespace speqb
+{
+enum : uint32_t { P_FETCH = 0, P_STEP = 1, P_UP = 2, P_DONE = 3 };
+enum : uint32_t { F_PENDING = 1u, F_HAVE_G = 2u, F_MATE2 = 4u };
+
+struct Lane32
+{
+    uint32_t phase, flags;
+    uint32_t lb, rb1, d, run;     // interval [lb, rb1), depth, length of the current run of valid bases
+    uint32_t t, pend;             // next base, end of the read (0 when the read is shorter than k)
+    uint32_t wlo, whi, winv;      // the current 32-base group, shifted so that base t is in the low bits
+    uint64_t g0;                  // first 32-base group of the read
+    uint64_t u, unext;            // unit being scanned / claimed for afterwards
+    uint32_t gval, gt;            // group of the last unique hit and the window end it belongs to
+    uint32_t gmin, gmax;          // unit-level ambiguity state
+    uint32_t agg_g, agg_n;        // run-length aggregation of the lane's unique tallies
+    double agg_w;
+    uint32_t c_total;             // valid windows of the current unit
+};
+
+// What one iteration loads.  A lane is in exactly one phase, so the phases share registers:
+//   P_STEP   A, B = SBlocks at lb / rb1   (the read group goes straight into Lane32::wlo / whi / winv)
+//   P_UP     B[0] = lcp[lb], B[1] = lcp[rb1], B[2] = psv[lb], B[3] = nsv[rb1]
+//   P_FETCH  B[4] = length of the read, B[5], B[6] = its first 32-base group (low, high word)
+struct Loads32
+{
+    uint32_t A[8], B[8];
+};
+
+struct Cfg32
+{
+    uint32_t k, n;
+    uint32_t cbeg[4], cend[4];    // C of the query codes A,C,G,T and of the next text symbol (SA range of the 1-mers)
+    uint64_t units;
+    int paired, local, record;
+};
+
+SPEQB_HD void lane32_init(Lane32 & s, uint64_t first_unit, uint32_t n)
+{
+    s.phase = P_FETCH; s.flags = 0; s.lb = 0; s.rb1 = n; s.d = 0; s.run = 0; s.t = 0; s.pend = 0; s.wlo = s.whi = s.winv = 0;
+    s.g0 = 0; s.u = first_unit; s.unext = first_unit; s.gval = 0; s.gt = 0; s.gmin = kNoGroup; s.gmax = 0;
+    s.agg_g = kNoGroup; s.agg_n = 0; s.agg_w = 0.0; s.c_total = 0;
+}
+
+// Env supplies the side effects:
+//   uint32_t env.load_grp(i)               group of suffix i
+//   uint32_t env.exc_word(blk)             exception mask of SBlock blk (slow path)
+//   double   env.weight(g0, t_end, k)      local-mode weight of the window ending (exclusive) at t_end
+//   void     env.unique(group, n, w)       add n (global) or w (local) to the variant's tally
+//   void     env.record(lb)                one more valid window whose k-mer interval starts at lb
+//   void     env.count_fetch(nwin)         a read with nwin windows was presented
+//   void     env.count_unit(total, amb)    a unit ended with `total` valid windows; amb: it was ambiguous
+template <class Env>
+SPEQB_HD void lane32_flush_agg(Lane32 & s, Env & env)
+{
+    if (s.agg_g != kNoGroup) env.unique(s.agg_g, s.agg_n, s.agg_w);
+    s.agg_g = kNoGroup;
+    s.agg_n = 0;
+    s.agg_w = 0.0;
+}
+
+template <class Env>
+SPEQB_HD void lane32_take_group(Lane32 & s, Cfg32 const & cfg, Env & env)
+{
+    // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191)
+    const uint32_t g = s.gval;
+    s.flags &= ~F_HAVE_G;
+    s.gmin = g < s.gmin ? g : s.gmin;
+    s.gmax = g > s.gmax ? g : s.gmax;
+    if (g != s.agg_g)
+    {
+        lane32_flush_agg(s, env);
+        s.agg_g = g;
+    }
+    if (cfg.local) s.agg_w += env.weight(s.g0, s.gt, cfg.k);
+    else s.agg_n += 1u;
+}
+
+#if defined(__CUDA_ARCH__)
+SPEQB_HD uint32_t popc32(uint32_t x) { return (uint32_t)__popc(x); }
+#else
+SPEQB_HD uint32_t popc32(uint32_t x) { return (uint32_t)__builtin_popcount(x); }
+#endif
+SPEQB_HD uint32_t below32(uint32_t j) { return (1u << j) - 1u; }   // bits [0, j), j in [0, 31]
+SPEQB_HD uint32_t upto32(uint32_t j) { return (2u << j) - 1u; }    // bits [0, j], j in [0, 31]
+SPEQB_HD uint32_t from32(uint32_t j) { return ~0u << j; }          // bits [j, 31]
+
+// index of the read a lane in P_FETCH loads
+SPEQB_HD uint64_t lane32_fetch_read(Lane32 const & s, Cfg32 const & cfg)
+{
+    return cfg.paired ? 2 * s.u + ((s.flags & F_MATE2) ? 1u : 0u) : s.u;
+}
+
+SPEQB_HD void lane32_advance(Lane32 & s)
+{
+    s.t += 1u;
+    s.wlo = (s.wlo >> 2) | (s.whi << 30);
+    s.whi >>= 2;
+    s.winv >>= 1;
+}
+
+// P_STEP.  ld.A / ld.B: the SBlocks at lb / rb1.  The read group of base t has been loaded into s.wlo / s.whi / s.winv by
+// the caller when t is a multiple of 32.  Written select-style so that the common case is one straight run of code.
+template <class Env>
+SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env & env)
+{
+    const uint32_t k = cfg.k;
+    if (s.flags & F_HAVE_G) lane32_take_group(s, cfg, env);
+    if (s.flags & F_PENDING)
+    {
+        // every occurrence of the window's k-mer in one variant <=> uq bit of any suffix of its interval
+        s.flags &= ~F_PENDING;
+        if ((ld.A[7] >> (s.lb & 31u)) & 1u)
+        {
+            s.gval = env.load_grp(s.lb);
+            s.gt = s.t;
+            s.flags |= F_HAVE_G;
+        }
+    }
+    if (s.t >= s.pend)
+    {
+        // the read is finished (its last hit, if any, was resolved above)
+        if (s.flags & F_HAVE_G) lane32_take_group(s, cfg, env);
+        if (cfg.paired && !(s.flags & F_MATE2)) s.flags |= F_MATE2;
+        else
+        {
+            // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
+            env.count_unit(s.c_total, s.gmin != kNoGroup && s.gmin != s.gmax);
+            s.c_total = 0u;
+            s.gmin = kNoGroup; s.gmax = 0u;
+            s.flags &= ~F_MATE2;
+            s.u = s.unext;
+        }
+        s.phase = P_FETCH;
+        return;
+    }
+    const uint32_t c = s.wlo & 3u;
+    const bool c1 = (c & 1u) != 0u, c2 = (c & 2u) != 0u;
+    if (s.winv & 1u)
+    {
+        // N / low quality: no window may contain this base; the search restarts behind it
+        s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; s.run = 0u;
+        lane32_advance(s);
+        return;
+    }
+    // the window slides (d == k): drop its first base = contract the interval to depth k-1 with the e bits
+    const bool slide = s.d == k;
+    uint32_t jl = s.lb & 31u, jr = s.rb1 & 31u;
+    const uint32_t zl = ~ld.A[6] & upto32(jl);
+    const uint32_t zr = ~ld.B[6] & from32(jr);
+    if (slide && k != 1u && (zl == 0u || zr == 0u))
+    {
+        // the widened interval leaves the two blocks: it is the parent lcp interval (depth k-1); jump there
+        s.d = k - 1u;
+        s.phase = P_UP;
+        return;
+    }
+    if (slide)
+    {
+        jl = 31u - clz32(zl | 1u);    // (| 1, | 2^31: only reached with k == 1, where the values are unused)
+        jr = ctz32(zr | 0x80000000u);
+    }
+    const uint32_t lbc = (s.lb & ~31u) + jl, rbc = (s.rb1 & ~31u) + jr;
+    const uint32_t dd = slide ? k - 1u : s.d;
+    // rank step (fm_index_cursor.hpp:110-146)
+    uint32_t ml = below32(jl), mr = below32(jr);
+    uint32_t a0 = ld.A[0], b0 = ld.B[0];
+    if ((a0 | b0) & kSFlagExc)
+    {
+        // N / delimiter / sentinel in the BWT of one of the blocks: they match no query symbol
+        if (a0 & kSFlagExc) ml &= ~env.exc_word(s.lb >> 5);
+        if (b0 & kSFlagExc) mr &= ~env.exc_word(s.rb1 >> 5);
+        a0 &= ~kSFlagExc;
+        b0 &= ~kSFlagExc;
+    }
+    const uint32_t xl = c1 ? 0u : ~0u, xh = c2 ? 0u : ~0u;
+    const uint32_t ca = c2 ? (c1 ? ld.A[3] : ld.A[2]) : (c1 ? ld.A[1] : a0);
+    const uint32_t cb = c2 ? (c1 ? ld.B[3] : ld.B[2]) : (c1 ? ld.B[1] : b0);
+    const uint32_t cc = c2 ? (c1 ? cfg.cbeg[3] : cfg.cbeg[2]) : (c1 ? cfg.cbeg[1] : cfg.cbeg[0]);
+    uint32_t nl = cc + ca + popc32((ld.A[4] ^ xl) & (ld.A[5] ^ xh) & ml);
+    uint32_t nr = cc + cb + popc32((ld.B[4] ^ xl) & (ld.B[5] ^ xh) & mr);   // exclusive
+    if (dd == 0u)
+    {
+        nl = cc;
+        nr = c2 ? (c1 ? cfg.cend[3] : cfg.cend[2]) : (c1 ? cfg.cend[1] : cfg.cend[0]);
+    }
+    if (nr <= nl && dd != 0u)
+    {
+        // read[t-d..t] does not occur: shorten it from the left (to the parent interval) and try the same base again
+        if (dd == 1u) { s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; }
+        else { s.lb = lbc; s.rb1 = rbc; s.d = dd; s.phase = P_UP; }
+        return;
+    }
+    const bool ok = nr > nl;
+    s.lb = ok ? nl : 0u;
+    s.rb1 = ok ? nr : cfg.n;
+    s.d = ok ? dd + 1u : 0u;
+    s.run += 1u;
+    lane32_advance(s);
+    if (s.run >= k)
+    {
+        s.c_total += 1u;                         // ++total_kmers (src/fm_scanner.cpp:164)
+        if (s.d == k)
+        {
+            s.flags |= F_PENDING;
+            if (cfg.record) env.record(s.lb);
+        }
+    }
+}
+
+// P_UP: parent of the lcp interval [lb, rb1): string depth l = max(lcp[lb], lcp[rb1]); the side(s) whose lcp equals l move
+// to the previous / next position with a smaller lcp value.
+SPEQB_HD void lane32_up(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg)
+{
+    const uint32_t ul = ld.B[0], ur = ld.B[1];
+    const uint32_t l = ul > ur ? ul : ur;
+    if (l == 0u) { s.lb = 0u; s.rb1 = cfg.n; }
+    else
+    {
+        if (ul == l) s.lb = ld.B[2];
+        if (ur == l) s.rb1 = ld.B[3];
+    }
+    s.d = l;
+    s.phase = P_STEP;
+}
+
+// P_FETCH.  The caller has set s.unext (the unit after s.u) when this is the first mate of the unit.
+template <class Env>
+SPEQB_HD void lane32_fetch(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env & env)
+{
+    if (s.u >= cfg.units)
+    {
+        s.phase = P_DONE;
+        return;
+    }
+    const uint32_t L = ld.B[4];
+    s.g0 = u64of(ld.B[5], ld.B[6]);
+    s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; s.run = 0u; s.t = 0u;
+    s.pend = L >= cfg.k ? L : 0u;                  // L < k: the sliding view is empty
+    env.count_fetch(L >= cfg.k ? L - cfg.k + 1u : 0u);
+    s.phase = P_STEP;
+}
+}   // namespace speqb

@@ -39,7 +39,7 @@ def sim_library() -> C.CDLL:
     src = ROOT / "tests" / "sim" / "roll_sim.cpp"
     so = ROOT / "tests" / "sim" / "roll_sim.so"
     csrc = ROOT / "speq_b200" / "csrc"
-    deps = [src, csrc / "scan_core.h", csrc / "fm_layout.h", csrc / "index_build.cpp", csrc / "sais.hpp", csrc / "speq_internal.h"]
+    deps = [src, csrc / "scan_core.h", csrc / "scan32_core.h", csrc / "fm_layout.h", csrc / "index_build.cpp", csrc / "sais.hpp", csrc / "speq_internal.h"]
     if not so.exists() or any(d.stat().st_mtime > so.stat().st_mtime for d in deps):
         subprocess.run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-pthread", "-o", str(so), str(src),
                         str(csrc / "index_build.cpp")], check=True, capture_output=True)

@@ -7,7 +7,7 @@
 #include <cstring>
 #include <vector>
 
-#include "../../speq_b200/csrc/scan_core.h"
+#include "../../speq_b200/csrc/scan32_core.h"
 #include "../../speq_b200/csrc/speq_internal.h"
 
 using namespace speqb;
@@ -42,6 +42,73 @@ void make_view(HostIndex const & h, uint32_t k, HostView & hv)
     hv.ix.n_npos = (uint32_t)h.n_pos.size();
     hv.ix.n = (uint32_t)h.n;
 }
+
+// Host restatement of fill32_kernel (scan32.cu): the per-k 32-byte blocks of the product kernel.
+uint32_t chg_upto_host(HostIndex const & h, uint32_t j)
+{
+    KBlock const & b = h.blocks[j >> 6];
+    return b.chgcum + popc64(u64of(b.chg[0], b.chg[1]) & upto64(j & 63u));
+}
+void make_sblocks(HostIndex const & h, uint32_t k, std::vector<SBlock> & out)
+{
+    const uint32_t n = (uint32_t)h.n;
+    out.assign(n / 32 + 1, SBlock{});
+    for (uint32_t blk = 0; blk < out.size(); ++blk)
+    {
+        KBlock const & p = h.blocks[blk >> 1];
+        const uint32_t half = blk & 1u;
+        SBlock & o = out[blk];
+        for (uint32_t c = 0; c < 4; ++c)
+        {
+            o.cnt[c] = p.cnt[c];
+            const uint32_t xl = (c & 1u) ? 0u : ~0u, xh = (c & 2u) ? 0u : ~0u;
+            if (half) o.cnt[c] += popc32((p.lo[0] ^ xl) & (p.hi[0] ^ xh) & ~p.exc[0]);
+        }
+        if (p.exc[half]) o.cnt[0] |= kSFlagExc;
+        o.lo = p.lo[half];
+        o.hi = p.hi[half];
+        for (uint32_t j = 0; j < 32; ++j)
+        {
+            const uint32_t i = blk * 32 + j;
+            if (i >= n) break;
+            if ((uint32_t)h.lcp[i] + 1u >= k) o.e |= 1u << j;
+            uint32_t s0 = i;
+            while ((uint32_t)h.lcp[s0] >= k) s0 = h.pn[s0].x;
+            uint32_t t0 = i + 1;
+            while ((uint32_t)h.lcp[t0] >= k) t0 = h.pn[t0].y;
+            if (chg_upto_host(h, t0 - 1) == chg_upto_host(h, s0)) o.uq |= 1u << j;
+        }
+    }
+}
+
+struct HostEnv32
+{
+    HostIndex const & h;
+    const uint8_t * qual;
+    const double * qden;
+    std::vector<uint64_t> & uniq;
+    std::vector<double> & uniq_w;
+    uint64_t * mult;
+    bool local;
+    uint64_t & total, & amb, & look;
+    uint32_t load_grp(uint32_t i) const { return h.grp[i]; }
+    uint32_t exc_word(uint32_t blk) const { return h.blocks[blk >> 1].exc[blk & 1u]; }
+    double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
+    {
+        const uint8_t * q = qual + 32u * g0 + (t_end - k);
+        double w = 1.0;
+        for (uint32_t i = 0; i < k; ++i) w = w / qden[q[i]];
+        return w;
+    }
+    void unique(uint32_t g, uint32_t n, double w) const
+    {
+        if (local) uniq_w[g] += w;
+        else uniq[g] += n;
+    }
+    void record(uint32_t lb) const { if (mult) ++mult[lb]; }
+    void count_fetch(uint32_t nwin) const { look += nwin; }
+    void count_unit(uint32_t t, bool a) const { total += t; amb += a ? 1 : 0; }
+};
 
 struct HostEnv
 {
@@ -173,6 +240,66 @@ int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, c
                 lane_flush_agg(s, cfg, env);
                 total += s.c_total; amb += s.c_amb; look += s.c_look;
             }
+        }
+        else if (algo == 2)
+        {
+            // the product kernel's state machine (scan32_core.h) over host-built SBlocks; lanes claim units in turn
+            if (backcheck) return -3;
+            std::vector<SBlock> sb;
+            make_sblocks(h, k, sb);
+            Cfg32 cfg;
+            cfg.k = k; cfg.n = (uint32_t)h.n; cfg.units = paired ? n_reads / 2 : n_reads;
+            cfg.paired = paired; cfg.local = local; cfg.record = mult != nullptr;
+            for (int c = 0; c < 4; ++c) { cfg.cbeg[c] = hv.ctab[c]; cfg.cend[c] = hv.ctab[kCtabEnd + c]; }
+            HostEnv32 env{h, qual, qden, uniq, uniq_w, mult, local != 0, total, amb, look};
+            std::vector<Lane32> lanes(nlanes);
+            std::vector<Loads32> loads(nlanes);
+            uint64_t work = nlanes;
+            for (uint32_t l = 0; l < nlanes; ++l) { lane32_init(lanes[l], l, cfg.n); memset(&loads[l], 0, sizeof(Loads32)); }
+            bool any = true;
+            uint64_t guard = 0;
+            while (any)
+            {
+                any = false;
+                for (uint32_t l = 0; l < nlanes; ++l)
+                {
+                    Lane32 & s = lanes[l];
+                    Loads32 & ld = loads[l];
+                    if (s.phase == P_DONE) continue;
+                    any = true;
+                    if (phase_counts) ++phase_counts[s.phase];
+                    if (s.phase == P_STEP)
+                    {
+                        memcpy(ld.A, &sb[s.lb >> 5], 32);
+                        memcpy(ld.B, &sb[s.rb1 >> 5], 32);
+                        if (s.t < s.pend && (s.t & 31u) == 0u)
+                        {
+                            uint64_t w = bases[s.g0 + (s.t >> 5)];
+                            s.wlo = (uint32_t)w; s.whi = (uint32_t)(w >> 32);
+                            s.winv = inv[s.g0 + (s.t >> 5)];
+                        }
+                        lane32_step(s, ld, cfg, env);
+                    }
+                    else if (s.phase == P_UP)
+                    {
+                        ld.B[0] = h.lcp[s.lb]; ld.B[1] = h.lcp[s.rb1];
+                        ld.B[2] = h.pn[s.lb].x; ld.B[3] = h.pn[s.rb1].y;
+                        lane32_up(s, ld, cfg);
+                    }
+                    else
+                    {
+                        if (s.u < cfg.units)
+                        {
+                            uint64_t fr = lane32_fetch_read(s, cfg);
+                            ld.B[4] = len[fr]; ld.B[5] = (uint32_t)grp_off[fr]; ld.B[6] = (uint32_t)(grp_off[fr] >> 32);
+                            if (!(s.flags & F_MATE2)) s.unext = work++;
+                        }
+                        lane32_fetch(s, ld, cfg, env);
+                    }
+                }
+                if (++guard > (1ull << 40)) return -2;
+            }
+            for (auto & s : lanes) lane32_flush_agg(s, env);
         }
         else
         {

@@ -177,6 +177,8 @@ def test_properties_at_config_shapes(lib, cfg, R):
     assert a.total_kmers == b.total_kmers and a.ambiguous == b.ambiguous
     assert np.array_equal(a.unique, b.unique)
     assert a.unique.sum() > 0
+    c = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
+    assert np.array_equal(a.unique, c.unique) and a.total_kmers == c.total_kmers and a.ambiguous == c.ambiguous
     h = R // 2
     p1 = _scan_tallies(idx, sh.k, seq, qual, offs[:h + 1])
     p2 = _scan_tallies(idx, sh.k, seq, qual, offs[h:])

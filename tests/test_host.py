@@ -161,7 +161,7 @@ def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck
 
 
 @pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
-@pytest.mark.parametrize("algo", [0, 1])
+@pytest.mark.parametrize("algo", [0, 1, 2])
 def test_lane_arithmetic_vs_golden(lib, sim, name, algo):
     fx = helpers.load_golden(name)
     exp, run = fx["expected"], fx["run"]
@@ -169,10 +169,10 @@ def test_lane_arithmetic_vs_golden(lib, sim, name, algo):
     V = len(counts)
     local = exp["mode"] == "local"
     out, out_w, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], algo,
-                              local=(local and algo == 0))
+                              local=(local and algo != 1))
     if not local:
         assert list(out[:V]) == exp["unique"]
-    elif algo == 0:
+    elif algo != 1:
         assert helpers.rel_close(out_w, exp["unique_w"], 1e-12)
     assert int(out[V]) == exp["total_kmers"]
     assert int(out[V + 1]) == exp["ambiguous"]
@@ -182,8 +182,11 @@ def test_lane_arithmetic_vs_golden(lib, sim, name, algo):
             bc, _, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], 30, False, 0, backcheck=True, nlanes=nlanes, seg_len=seg_len)
             assert list(bc[:V]) == exp["unique_ref"]
             assert list(bc[V:2 * V]) == exp["total_ref"]
-        one, _, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], 0, nlanes=1, local=local)
+    if algo != 1:
+        one, _, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], algo, nlanes=1, local=local)
         assert np.array_equal(one, out)
+        many, _, _ = _sim_scan(sim, scaff, gs, V, seqs, quals, run["k"], run.get("phred_cutoff", 30), run["paired"], algo, nlanes=64, local=local)
+        assert np.array_equal(many, out)
 
 
 @pytest.mark.parametrize("k", [1, 2, 3, 31, 64, 127])
@@ -198,8 +201,11 @@ def test_lane_arithmetic_k_extremes(lib, sim, k):
     quals = ["I" * len(s) for s in seqs]
     a, _, ma = _sim_scan(sim, scaff, [0, 1, 2], 3, seqs, quals, k, 30, False, 0, want_mult=True)
     b, _, mb = _sim_scan(sim, scaff, [0, 1, 2], 3, seqs, quals, k, 30, False, 1, want_mult=True)
+    c, _, mc = _sim_scan(sim, scaff, [0, 1, 2], 3, seqs, quals, k, 30, False, 2, want_mult=True)
     assert np.array_equal(a, b)
     assert np.array_equal(ma, mb)
+    assert np.array_equal(c, b)
+    assert np.array_equal(mc, mb)
     assert a[3] > 0
 
 
@@ -229,5 +235,8 @@ def test_lane_arithmetic_low_complexity(lib, sim, seed):
     for k in (4, 9, 17, 40):
         a, _, ma = _sim_scan(sim, scaff, [0, 1, 2, 3], 4, seqs, quals, k, 30, False, 0, want_mult=True, nlanes=5)
         b, _, mb = _sim_scan(sim, scaff, [0, 1, 2, 3], 4, seqs, quals, k, 30, False, 1, want_mult=True)
+        c, _, mc = _sim_scan(sim, scaff, [0, 1, 2, 3], 4, seqs, quals, k, 30, False, 2, want_mult=True, nlanes=5)
         assert np.array_equal(a, b), k
         assert np.array_equal(ma, mb), k
+        assert np.array_equal(c, b), k
+        assert np.array_equal(mc, mb), k
