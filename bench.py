@@ -245,7 +245,15 @@ def main() -> None:
     R, L = seq.shape
     t_gen = time.perf_counter() - t_gen
     t0 = time.perf_counter()
-    idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V)
+    cache = os.environ.get("SPEQ_BENCH_INDEX_CACHE")   # optional: reuse the (deterministic) synthetic index between runs
+    cpath = Path(cache) / f"{args.config}.speqidx" if cache else None
+    if cpath is not None and cpath.exists():
+        idx = engine.Index.load(str(cpath))
+    else:
+        idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V)
+        if cpath is not None and rank == 0:
+            cpath.parent.mkdir(parents=True, exist_ok=True)
+            idx.save(str(cpath))
     t_index = time.perf_counter() - t0
     idx.upload(local_rank)
     log(f"[rank {rank}] workload {R} reads generated in {t_gen:.1f}s; index n={idx.n} built in {t_index:.1f}s, {idx.device_bytes/1e6:.1f} MB on device")

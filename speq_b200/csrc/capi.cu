@@ -39,6 +39,10 @@ DeviceIndex & device_index(speqg_index * idx, int device)
         d.grp = dev_upload(h.grp.data(), h.grp.size(), &d.bytes);
         d.lcp = dev_upload(h.lcp.data(), h.lcp.size(), &d.bytes);
         d.pn = dev_upload(h.pn.data(), h.pn.size(), &d.bytes);
+        d.up = dev_alloc<UpRec>(h.pn.size());
+        d.bytes += h.pn.size() * sizeof(UpRec);
+        CK(launch_build_up(d.lcp, d.pn, d.up, h.pn.size(), nullptr));
+        CK(cudaStreamSynchronize(nullptr));
         d.n_pos = dev_upload(h.n_pos.data(), h.n_pos.size(), &d.bytes);
         d.ctab = dev_upload(ctab, 16, &d.bytes);
         d.t_bases = dev_upload(h.t_bases.data(), h.t_bases.size(), &d.bytes);
@@ -56,6 +60,7 @@ DeviceIndex & device_index(speqg_index * idx, int device)
     v.blocks = d.blocks;
     v.lcp = d.lcp;
     v.pn = d.pn;
+    v.up = d.up;
     v.grp = d.grp;
     v.n_pos = d.n_pos;
     v.ctab = d.ctab;
@@ -181,7 +186,7 @@ int speqg_index_get_info(const speqg_index * idx, speqg_index_info * info)
     info->n_groups = h.V;
     for (int c = 0; c < 8; ++c) info->C[c] = h.C[c];
     info->n_exceptions = h.n_exc;
-    info->device_bytes = h.blocks.size() * sizeof(KBlock) + h.grp.size() * 2 + h.lcp.size() + h.pn.size() * 8 + 64 +
+    info->device_bytes = h.blocks.size() * sizeof(KBlock) + h.grp.size() * 2 + h.lcp.size() + h.pn.size() * 24 + 64 +
                          h.n_pos.size() * 4 + h.t_bases.size() * 8 + h.t_inv.size() * 4 + h.t_grp_off.size() * 8 +
                          h.t_len.size() * 4 + h.group_of_text.size() * 4;
     SPEQG_CATCH

@@ -63,7 +63,7 @@ struct speqg_scan
     DeviceIndex * di = nullptr;
     DevIndex view{};               // di->view with `blocks` replaced by this scan's k-specialised copy
     KBlock * d_blocks_k = nullptr;   // SPEQG_ALGO_ROLLING64 only
-    SBlock * d_sblk = nullptr;       // per-k 32-byte blocks of the product kernel
+    FBlock * d_sblk = nullptr;       // per-k blocks of the product kernel (SBlock + variant bytes)
     int device = 0;
     speqg_params p{};
     int mode = 0;
@@ -230,8 +230,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         }
         else
         {
-            s->d_sblk = dev_alloc<SBlock>(idx->host.n / 32 + 1);
-            CK(launch_fill32(di.blocks, di.lcp, di.pn, s->d_sblk, (uint32_t)idx->host.n, params->k, s->compute));
+            s->d_sblk = dev_alloc<FBlock>(idx->host.n / 32 + 1);
+            CK(launch_fill32(di.blocks, di.lcp, di.pn, di.grp, s->d_sblk, (uint32_t)idx->host.n, params->k, s->compute));
         }
         CK(scan32_launch_cfg(s->mode, V, &s->cfg));
         CK(scan_launch_cfg(s->mode, 1, V, &s->cfg_direct));

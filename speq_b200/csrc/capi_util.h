@@ -76,7 +76,7 @@ template <class T> T * dev_upload(T const * src, size_t count, uint64_t * bytes 
 
 inline void free_device_index(DeviceIndex & d)
 {
-    cudaFree(d.blocks); cudaFree(d.grp); cudaFree(d.lcp); cudaFree(d.pn); cudaFree(d.n_pos); cudaFree(d.ctab);
+    cudaFree(d.blocks); cudaFree(d.grp); cudaFree(d.lcp); cudaFree(d.pn); cudaFree(d.up); cudaFree(d.n_pos); cudaFree(d.ctab);
     cudaFree(d.t_bases); cudaFree(d.t_inv); cudaFree(d.t_grp_off); cudaFree(d.t_len); cudaFree(d.t_group);
     d = DeviceIndex{};
 }

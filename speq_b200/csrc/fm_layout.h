@@ -78,6 +78,24 @@ struct __attribute__((aligned(32))) SBlock
     uint32_t lo, hi, e, uq;
 };
 static_assert(sizeof(SBlock) == 32, "SBlock must be 32 bytes");
+// FBlock: what the scan kernel actually addresses -- the SBlock of 32 suffixes and, in the other sector of the same
+// 64-byte DRAM burst, their variants as bytes (used when the index has <= 255 variants; 0xFF = delimiter / sentinel
+// suffix).  On indexes larger than L2 the group load of a unique hit then rides on the burst that brought the SBlock.
+struct __attribute__((aligned(64))) FBlock
+{
+    SBlock s;
+    uint8_t g[32];
+};
+static_assert(sizeof(FBlock) == 64, "FBlock must be 64 bytes");
+constexpr uint32_t kMaxGroups8 = 255;
+// UpRec: everything a parent jump needs about one suffix position in ONE 16-byte load.
+struct __attribute__((aligned(16))) UpRec
+{
+    uint32_t psv, nsv;   // previous / next position with a smaller lcp value
+    uint32_t lcp;        // min(127, lcp)
+    uint32_t pad;
+};
+static_assert(sizeof(UpRec) == 16, "UpRec must be 16 bytes");
 constexpr uint32_t kSFlagExc = 0x80000000u;
 constexpr uint64_t kMaxN32 = 0x7FFFFFFFull;   // cnt[0] keeps bit 31 for the exception flag
 
@@ -89,6 +107,7 @@ struct DevIndex
     const KBlock * blocks;        // n/64 + 1 blocks (for a scan: the copy whose e bits are filled for the scan's k)
     const uint8_t * lcp;          // n + 1 entries (lcp[n] = 0), zero padded
     const uint2x * pn;            // n + 1 entries: {previous smaller, next smaller} lcp positions
+    const UpRec * up;             // n + 1 entries: pn + lcp in one record (built on the device at upload)
     const uint16_t * grp;         // n entries
     const uint32_t * n_pos;       // sorted BWT positions holding N (rank of the symbol N; back-check only)
     const uint32_t * ctab;        // 16 entries: [c] = C of query code c (A,C,G,T,N) = #text symbols smaller;

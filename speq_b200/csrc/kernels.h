@@ -73,11 +73,14 @@ cudaError_t launch_pack(const uint8_t * seq, const uint8_t * qual, uint64_t off0
 // per-scan specialisation of the rank blocks: copy `src` to `dst` and fill the e bits (lcp >= k-1) for this k
 cudaError_t launch_fill_e(const KBlock * src, KBlock * dst, const uint8_t * lcp, uint32_t n, uint32_t k, cudaStream_t st);
 // the product scan kernel (scan32.cu): rolling window over the per-k 32-byte SBlocks; a.work must point to one u64
-cudaError_t launch_scan32(const SBlock * sblk, DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg,
+cudaError_t launch_scan32(const FBlock * fblk, DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg,
                           cudaStream_t st);
 cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 size_t scan32_smem_bytes(uint32_t V);
 // per-scan specialisation: SBlocks (rank counts, bit planes, e = lcp >= k-1, uq = depth-k interval in one variant) for this k
-cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, SBlock * out, uint32_t n, uint32_t k, cudaStream_t st);
+cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, const uint16_t * grp, FBlock * out, uint32_t n,
+                          uint32_t k, cudaStream_t st);
+// parent-jump records {psv, nsv, lcp} (one 16-byte load per side) from the stored lcp and pn arrays; once per device copy
+cudaError_t launch_build_up(const uint8_t * lcp, const uint2x * pn, UpRec * out, uint64_t count, cudaStream_t st);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

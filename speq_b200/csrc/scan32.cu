@@ -41,9 +41,11 @@ __device__ __forceinline__ void ld32_if(uint32_t & v, const void * p, bool pred)
 {
     asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
 }
-__device__ __forceinline__ void ld8_if(uint32_t & v, const void * p, bool pred)
+__device__ __forceinline__ void ld128_if(uint32_t * w, const void * p, bool pred)
 {
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u8 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %5, 0;\n\t@q ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
+                 : "l"(p), "r"((int)pred));
 }
 
 // shared-memory tallies of one CTA
@@ -62,17 +64,20 @@ __device__ __forceinline__ Smem32 smem32_view(unsigned char * raw, uint32_t V)
     return s;
 }
 
-template <int MODE> struct Env32
+template <int MODE, bool G8> struct Env32
 {
     static constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
+    const FBlock * fblk;
     DevIndex const & ix;
     BatchView const & b;
     ScanArgs const & a;
     Smem32 sm;
     __device__ __forceinline__ uint32_t load_grp(uint32_t i) const
     {
+        // G8: the variant byte sits in the 64-byte burst of the suffix's own block
         uint32_t v;
-        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(v) : "l"(ix.grp + i));
+        if (G8) asm volatile("ld.global.nc.u8 %0, [%1];" : "=r"(v) : "l"(&fblk[i >> 5].g[i & 31u]));
+        else asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(v) : "l"(ix.grp + i));
         return v;
     }
     __device__ __forceinline__ uint32_t exc_word(uint32_t blk) const { return load_ro(&ix.blocks[blk >> 1].exc[blk & 1u]); }
@@ -103,8 +108,8 @@ template <int MODE> struct Env32
     }
 };
 
-template <int MODE>
-__global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const SBlock * __restrict__ sblk, const DevIndex ix, const BatchView b,
+template <int MODE, bool G8>
+__global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __restrict__ fblk, const DevIndex ix, const BatchView b,
                                                              const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
@@ -132,7 +137,7 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const SBlock * __re
     cfg.paired = paired;
     cfg.local = LOCAL;
     cfg.record = RECORD;
-    Env32<MODE> env{ix, b, a, sm};
+    Env32<MODE, G8> env{fblk, ix, b, a, sm};
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
 
@@ -151,8 +156,8 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const SBlock * __re
         if (!__any_sync(kFull, ph != P_DONE)) break;
         // ---- every load of this iteration, issued before anything is consumed
         const bool stp = ph == P_STEP;
-        ld256_if(ld.A, sblk + (s.lb >> 5), stp);
-        ld256_if(ld.B, sblk + (s.rb1 >> 5), stp);
+        ld256_if(ld.A, fblk + (s.lb >> 5), stp);
+        ld256_if(ld.B, fblk + (s.rb1 >> 5), stp);
         {
             // the next 32 bases of the read: straight into the lane's window registers (all 32 old bases are consumed)
             const bool needw = stp && s.t < s.pend && (s.t & 31u) == 0u;
@@ -162,10 +167,8 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const SBlock * __re
         if (m_up)
         {
             const bool up = ph == P_UP;
-            ld8_if(ld.B[0], ix.lcp + s.lb, up);
-            ld8_if(ld.B[1], ix.lcp + s.rb1, up);
-            ld32_if(ld.B[2], &ix.pn[s.lb].x, up);
-            ld32_if(ld.B[3], &ix.pn[s.rb1].y, up);
+            ld128_if(ld.A, ix.up + s.lb, up);
+            ld128_if(ld.B, ix.up + s.rb1, up);
         }
         if (m_fe)
         {
@@ -221,8 +224,8 @@ __device__ __forceinline__ uint32_t chg_upto(const KBlock * kb, uint32_t j)
 }
 
 __global__ void __launch_bounds__(kBlock32) fill32_kernel(const KBlock * __restrict__ kb, const uint8_t * __restrict__ lcp,
-                                                          const uint2x * __restrict__ pn, SBlock * __restrict__ out, const uint32_t n,
-                                                          const uint32_t k)
+                                                          const uint2x * __restrict__ pn, const uint16_t * __restrict__ grp,
+                                                          FBlock * __restrict__ out, const uint32_t n, const uint32_t k)
 {
     const uint32_t nblocks = n / 32u + 1u;
     const uint32_t lane = threadIdx.x & 31u;
@@ -259,6 +262,20 @@ __global__ void __launch_bounds__(kBlock32) fill32_kernel(const KBlock * __restr
         else if (lane == 6u) v = we;
         else if (lane == 7u) v = wu;
         if (lane < 8u) reinterpret_cast<uint32_t *>(out + blk)[lane] = v;
+        // variants as bytes (meaningful when the index has <= 255 variants; 0xFFFF -> 0xFF)
+        out[blk].g[lane] = i < n ? (uint8_t)grp[i] : (uint8_t)0xFF;
+    }
+}
+
+__global__ void __launch_bounds__(kBlock32) build_up_kernel(const uint8_t * __restrict__ lcp, const uint2x * __restrict__ pn,
+                                                            UpRec * __restrict__ out, const uint64_t count)
+{
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const uint2x v = pn[i];
+        UpRec r;
+        r.psv = v.x; r.nsv = v.y; r.lcp = lcp[i]; r.pad = 0u;
+        out[i] = r;
     }
 }
 
@@ -278,14 +295,19 @@ int sm_count32()
 
 size_t scan32_smem_bytes(uint32_t V) { return 32 + (size_t)V * 12; }
 
-#define SPEQB_SCAN32_DISPATCH(M, EXPR)                                                             \
-    switch (M)                                                                                     \
-    {                                                                                              \
-        case 0: { auto kern = scan32_kernel<0>; EXPR; break; }                                     \
-        case M_RECORD: { auto kern = scan32_kernel<M_RECORD>; EXPR; break; }                       \
-        case M_LOCAL: { auto kern = scan32_kernel<M_LOCAL>; EXPR; break; }                         \
-        case M_LOCAL | M_RECORD: { auto kern = scan32_kernel<M_LOCAL | M_RECORD>; EXPR; break; }   \
-        default: return cudaErrorInvalidValue;                                                     \
+#define SPEQB_SCAN32_CASE(M, G, EXPR) { auto kern = scan32_kernel<M, G>; EXPR; break; }
+#define SPEQB_SCAN32_DISPATCH(M, G8, EXPR)                                                        \
+    switch ((M) | ((G8) ? 16 : 0))                                                                \
+    {                                                                                             \
+        case 0: SPEQB_SCAN32_CASE(0, false, EXPR)                                                 \
+        case M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, false, EXPR)                                   \
+        case M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, false, EXPR)                                     \
+        case M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, false, EXPR)               \
+        case 16: SPEQB_SCAN32_CASE(0, true, EXPR)                                                 \
+        case 16 | M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, true, EXPR)                               \
+        case 16 | M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, true, EXPR)                                 \
+        case 16 | M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, true, EXPR)           \
+        default: return cudaErrorInvalidValue;                                                    \
     }
 
 cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
@@ -294,7 +316,8 @@ cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     int bps = 0;
     cudaError_t e = cudaSuccess;
     const int m = mode & (M_LOCAL | M_RECORD);
-    SPEQB_SCAN32_DISPATCH(m, {
+    const bool g8 = V <= kMaxGroups8;
+    SPEQB_SCAN32_DISPATCH(m, g8, {
         if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlock32, smem);
     })
@@ -305,7 +328,7 @@ cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     return cudaSuccess;
 }
 
-cudaError_t launch_scan32(const SBlock * sblk, DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg,
+cudaError_t launch_scan32(const FBlock * fblk, DevIndex const & ix, BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg,
                           cudaStream_t st)
 {
     const size_t smem = scan32_smem_bytes(a.V);
@@ -313,13 +336,21 @@ cudaError_t launch_scan32(const SBlock * sblk, DevIndex const & ix, BatchView co
     const int m = mode & (M_LOCAL | M_RECORD);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
-    SPEQB_SCAN32_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(sblk, ix, b, a, paired)))
+    const bool g8 = a.V <= kMaxGroups8;
+    SPEQB_SCAN32_DISPATCH(m, g8, (kern<<<cfg.grid, cfg.block, smem, st>>>(fblk, ix, b, a, paired)))
     return cudaGetLastError();
 }
 
-cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, SBlock * out, uint32_t n, uint32_t k, cudaStream_t st)
+cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, const uint16_t * grp, FBlock * out, uint32_t n,
+                          uint32_t k, cudaStream_t st)
 {
-    fill32_kernel<<<sm_count32() * 8, kBlock32, 0, st>>>(kb, lcp, pn, out, n, k);
+    fill32_kernel<<<sm_count32() * 8, kBlock32, 0, st>>>(kb, lcp, pn, grp, out, n, k);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_build_up(const uint8_t * lcp, const uint2x * pn, UpRec * out, uint64_t count, cudaStream_t st)
+{
+    build_up_kernel<<<sm_count32() * 8, kBlock32, 0, st>>>(lcp, pn, out, count);
     return cudaGetLastError();
 }
 }   // namespace speqb

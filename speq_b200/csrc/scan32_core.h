@@ -43,7 +43,7 @@ struct Lane32
 
 // What one iteration loads.  A lane is in exactly one phase, so the phases share registers:
 //   P_STEP   A, B = SBlocks at lb / rb1   (the read group goes straight into Lane32::wlo / whi / winv)
-//   P_UP     B[0] = lcp[lb], B[1] = lcp[rb1], B[2] = psv[lb], B[3] = nsv[rb1]
+//   P_UP     A[0..3] = UpRec of lb, B[0..3] = UpRec of rb1 ({psv, nsv, lcp, -})
 //   P_FETCH  B[4] = length of the read, B[5], B[6] = its first 32-base group (low, high word)
 struct Loads32
 {
@@ -235,13 +235,13 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
 // to the previous / next position with a smaller lcp value.
 SPEQB_HD void lane32_up(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg)
 {
-    const uint32_t ul = ld.B[0], ur = ld.B[1];
+    const uint32_t ul = ld.A[2], ur = ld.B[2];
     const uint32_t l = ul > ur ? ul : ur;
     if (l == 0u) { s.lb = 0u; s.rb1 = cfg.n; }
     else
     {
-        if (ul == l) s.lb = ld.B[2];
-        if (ur == l) s.rb1 = ld.B[3];
+        if (ul == l) s.lb = ld.A[0];
+        if (ur == l) s.rb1 = ld.B[1];
     }
     s.d = l;
     s.phase = P_STEP;

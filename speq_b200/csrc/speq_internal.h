@@ -46,6 +46,7 @@ struct DeviceIndex
     uint16_t * grp = nullptr;
     uint8_t * lcp = nullptr;
     uint2x * pn = nullptr;
+    UpRec * up = nullptr;
     uint32_t * n_pos = nullptr;
     uint32_t * ctab = nullptr;
     // texts batch

@@ -282,8 +282,8 @@ int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, c
                     }
                     else if (s.phase == P_UP)
                     {
-                        ld.B[0] = h.lcp[s.lb]; ld.B[1] = h.lcp[s.rb1];
-                        ld.B[2] = h.pn[s.lb].x; ld.B[3] = h.pn[s.rb1].y;
+                        ld.A[0] = h.pn[s.lb].x; ld.A[1] = h.pn[s.lb].y; ld.A[2] = h.lcp[s.lb];
+                        ld.B[0] = h.pn[s.rb1].x; ld.B[1] = h.pn[s.rb1].y; ld.B[2] = h.lcp[s.rb1];
                         lane32_up(s, ld, cfg);
                     }
                     else

@@ -215,3 +215,35 @@ def test_backcheck_idempotent_and_index_roundtrip(lib, tmp_path):
     u3, t3 = engine.backcheck(idx2, sh.k)
     assert np.array_equal(u1, u3) and np.array_equal(t1, t3)
     idx.close(); idx2.close()
+
+
+@pytest.mark.gpu
+def test_many_variants_u16_groups(lib):
+    """More than 255 variants: the scan kernel reads u16 groups from the separate array instead of the bytes inside its
+    blocks.  rolling == direct == rolling64."""
+    rng = np.random.default_rng(5)
+    V = 300
+    anc = rng.integers(0, 4, 400)
+    scaff = []
+    for v in range(V):
+        s = anc.copy()
+        pos = rng.integers(0, s.size, 12)
+        s[pos] = rng.integers(0, 4, 12)
+        scaff.append(np.where(s == 3, 4, s).astype(np.uint8))     # dna5 ranks: A0 C1 G2 N3 T4
+    idx = engine.Index.from_scaffolds(scaff, list(range(V)), V)
+    R, L = 3000, 80
+    src = rng.integers(0, V, R)
+    st = rng.integers(0, anc.size - L, R)
+    letters = np.frombuffer(b"ACGNT", np.uint8)
+    seq = np.concatenate([letters[scaff[int(v)][int(p):int(p) + L]] for v, p in zip(src, st)])
+    flip = rng.random(seq.size) < 0.01
+    seq[flip] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(flip.sum()))]
+    qual = np.full(seq.size, ord("I"), np.uint8)
+    offs = np.arange(R + 1, dtype=np.uint64) * L
+    a = _scan_tallies(idx, 15, seq, qual, offs)
+    b = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_DIRECT)
+    c = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
+    assert a.unique.sum() > 0
+    for o in (b, c):
+        assert np.array_equal(a.unique, o.unique) and a.total_kmers == o.total_kmers and a.ambiguous == o.ambiguous
+    idx.close()
