@@ -188,7 +188,20 @@ def measured_peak() -> tuple[float, str]:
 
 
 # ---------------------------------------------------------------------------------------------------------------
+def emit(line: dict) -> None:
+    """The ONE JSON line goes to the process's real stdout; everything else a library prints (NCCL's version banner ...)
+    was sent to stderr by main()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main() -> None:
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -227,7 +240,7 @@ def main() -> None:
                 "data": "synthetic", "config": config, "reads_per_sec": out["reads"] / t,
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": T, "kind": kind, "sample": sample},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     # ---------------------------------------------------------------------------------------------------- native arm
@@ -434,7 +447,7 @@ def main() -> None:
                 "clocks": clk, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu,
                 "tallies": {"unique": [int(x) for x in tall[:V]], "total_kmers": int(tall[V]), "ambiguous": int(tall[V + 1])},
                 "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     scan.close()
     db.close()
     idx.close()
