@@ -126,12 +126,7 @@ ScanArgs scan_args(speqg_scan * s)
     a.segs = nullptr;
     a.n_segs = 0;
     a.work = s->d_work;
-    static const uint32_t sym_of_code[4] = {1, 2, 3, 5};   // text symbols of A,C,G,T (N = 4 sits between G and T)
-    for (int c = 0; c < 4; ++c)
-    {
-        a.cbeg[c] = (uint32_t)s->idx->host.C[sym_of_code[c]];
-        a.cend[c] = (uint32_t)s->idx->host.C[sym_of_code[c] + 1];
-    }
+
     return a;
 }
 
@@ -231,7 +226,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         else
         {
             s->d_sblk = dev_alloc<FBlock>(idx->host.n / 32 + 1);
-            CK(launch_fill32(di.blocks, di.lcp, di.pn, di.grp, s->d_sblk, (uint32_t)idx->host.n, params->k, s->compute));
+            CK(launch_fill32(di.blocks, di.lcp, di.pn, di.grp, di.ctab, s->d_sblk, (uint32_t)idx->host.n, params->k, s->compute));
         }
         CK(scan32_launch_cfg(s->mode, V, &s->cfg));
         CK(scan_launch_cfg(s->mode, 1, V, &s->cfg_direct));

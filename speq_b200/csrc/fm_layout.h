@@ -65,8 +65,10 @@ struct __attribute__((aligned(64))) KBlock
 static_assert(sizeof(KBlock) == 64, "KBlock must be 64 bytes");
 
 // SBlock: the scan kernel's per-k view of 32 consecutive suffixes in ONE 32-byte sector (one LDG.256 per lane):
-//   cnt[4]  occurrences of A,C,G,T in bwt[0, 32*b); bit 31 of cnt[0] = the block holds an exception (N / delimiter /
-//           sentinel in the BWT): the lane then fetches the exception mask from the KBlock array (rare slow path)
+//   cnt[4]  C[c] + occurrences of c = A,C,G,T in bwt[0, 32*b) -- the LF value of the block's first suffix, so a rank step
+//           is cnt[c] + popc and the root interval [0, n) needs no special case; bit 31 of cnt[0] = the block holds an
+//           exception (N / delimiter / sentinel in the BWT): the lane then fetches the exception mask from the KBlock
+//           array (rare slow path)
 //   lo, hi  the two bit planes of the 2-bit BWT codes, symbol j at bit j
 //   e       bit j: lcp[32b+j] >= k-1
 //   uq      bit j: every suffix of the depth-k lcp interval that contains suffix 32b+j belongs to one variant

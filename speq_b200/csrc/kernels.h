@@ -40,7 +40,6 @@ struct ScanArgs
     const double * qden;              // [42] 1 - 1/pow(10, q/10), host libm values   (local mode)
     const SegmentX * segs;             // optional segment table (back-check); null: one segment per read / pair
     uint64_t n_segs;
-    uint32_t cbeg[4], cend[4];        // scan32: SA ranges of the 1-mers A,C,G,T (C table)
     unsigned long long * work;        // scan32: next unclaimed unit minus the number of threads (zero at launch)
 };
 
@@ -78,8 +77,8 @@ cudaError_t launch_scan32(const FBlock * fblk, DevIndex const & ix, BatchView co
 cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 size_t scan32_smem_bytes(uint32_t V);
 // per-scan specialisation: SBlocks (rank counts, bit planes, e = lcp >= k-1, uq = depth-k interval in one variant) for this k
-cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, const uint16_t * grp, FBlock * out, uint32_t n,
-                          uint32_t k, cudaStream_t st);
+cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, const uint16_t * grp, const uint32_t * ctab,
+                          FBlock * out, uint32_t n, uint32_t k, cudaStream_t st);
 // parent-jump records {psv, nsv, lcp} (one 16-byte load per side) from the stored lcp and pn arrays; once per device copy
 cudaError_t launch_build_up(const uint8_t * lcp, const uint2x * pn, UpRec * out, uint64_t count, cudaStream_t st);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);

@@ -96,15 +96,22 @@ template <int MODE, bool G8> struct Env32
         else atomicAdd(&sm.cnt[g], n);
     }
     __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(a.mult + lb, 1ull); }
+    // 64-bit shared counters as two native 32-bit atomics (a 64-bit shared atomicAdd is a CAS loop)
+    __device__ __forceinline__ void add64(int i, uint32_t v) const
+    {
+        uint32_t * w = reinterpret_cast<uint32_t *>(sm.scal + i);
+        const uint32_t old = atomicAdd(w, v);
+        if (old + v < old) atomicAdd(w + 1, 1u);
+    }
     __device__ __forceinline__ void count_fetch(uint32_t nwin) const
     {
-        atomicAdd(&sm.scal[2], (unsigned long long)nwin);
-        atomicAdd(&sm.scal[3], 1ull);
+        add64(2, nwin);
+        add64(3, 1u);
     }
     __device__ __forceinline__ void count_unit(uint32_t total, bool amb) const
     {
-        if (total) atomicAdd(&sm.scal[0], (unsigned long long)total);
-        if (amb) atomicAdd(&sm.scal[1], 1ull);
+        if (total) add64(0, total);
+        if (amb) add64(1, 1u);
     }
 };
 
@@ -127,12 +134,6 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
     Cfg32 cfg;
     cfg.k = a.k;
     cfg.n = ix.n;
-#pragma unroll
-    for (int c = 0; c < 4; ++c)
-    {
-        cfg.cbeg[c] = a.cbeg[c];
-        cfg.cend[c] = a.cend[c];
-    }
     cfg.units = paired ? b.n_reads / 2 : b.n_reads;
     cfg.paired = paired;
     cfg.local = LOCAL;
@@ -225,7 +226,8 @@ __device__ __forceinline__ uint32_t chg_upto(const KBlock * kb, uint32_t j)
 
 __global__ void __launch_bounds__(kBlock32) fill32_kernel(const KBlock * __restrict__ kb, const uint8_t * __restrict__ lcp,
                                                           const uint2x * __restrict__ pn, const uint16_t * __restrict__ grp,
-                                                          FBlock * __restrict__ out, const uint32_t n, const uint32_t k)
+                                                          const uint32_t * __restrict__ ctab, FBlock * __restrict__ out,
+                                                          const uint32_t n, const uint32_t k)
 {
     const uint32_t nblocks = n / 32u + 1u;
     const uint32_t lane = threadIdx.x & 31u;
@@ -249,7 +251,7 @@ __global__ void __launch_bounds__(kBlock32) fill32_kernel(const KBlock * __restr
         uint32_t v = 0u;
         if (lane < 4u)
         {
-            v = p->cnt[lane];
+            v = ctab[lane] + p->cnt[lane];     // C[c] folded into the counts
             if (half)
             {
                 const uint32_t xl = (lane & 1u) ? 0u : ~0u, xh = (lane & 2u) ? 0u : ~0u;
@@ -341,10 +343,10 @@ cudaError_t launch_scan32(const FBlock * fblk, DevIndex const & ix, BatchView co
     return cudaGetLastError();
 }
 
-cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, const uint16_t * grp, FBlock * out, uint32_t n,
-                          uint32_t k, cudaStream_t st)
+cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x * pn, const uint16_t * grp, const uint32_t * ctab,
+                          FBlock * out, uint32_t n, uint32_t k, cudaStream_t st)
 {
-    fill32_kernel<<<sm_count32() * 8, kBlock32, 0, st>>>(kb, lcp, pn, grp, out, n, k);
+    fill32_kernel<<<sm_count32() * 8, kBlock32, 0, st>>>(kb, lcp, pn, grp, ctab, out, n, k);
     return cudaGetLastError();
 }
 

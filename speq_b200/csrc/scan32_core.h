@@ -53,7 +53,6 @@ struct Loads32
 struct Cfg32
 {
     uint32_t k, n;
-    uint32_t cbeg[4], cend[4];    // C of the query codes A,C,G,T and of the next text symbol (SA range of the 1-mers)
     uint64_t units;
     int paired, local, record;
 };
@@ -159,33 +158,30 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
     }
     const uint32_t c = s.wlo & 3u;
     const bool c1 = (c & 1u) != 0u, c2 = (c & 2u) != 0u;
-    if (s.winv & 1u)
-    {
-        // N / low quality: no window may contain this base; the search restarts behind it
-        s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; s.run = 0u;
-        lane32_advance(s);
-        return;
-    }
+    // N / low quality: no window may contain this base; the search restarts behind it (root interval, run = 0)
+    const bool inv = (s.winv & 1u) != 0u;
     // the window slides (d == k): drop its first base = contract the interval to depth k-1 with the e bits
     const bool slide = s.d == k;
     uint32_t jl = s.lb & 31u, jr = s.rb1 & 31u;
     const uint32_t zl = ~ld.A[6] & upto32(jl);
     const uint32_t zr = ~ld.B[6] & from32(jr);
-    if (slide && k != 1u && (zl == 0u || zr == 0u))
+    if (slide && !inv && (zl == 0u || zr == 0u))
     {
         // the widened interval leaves the two blocks: it is the parent lcp interval (depth k-1); jump there
+        // (k == 1: every e bit is set, so each base takes this jump to the root)
         s.d = k - 1u;
         s.phase = P_UP;
         return;
     }
     if (slide)
     {
-        jl = 31u - clz32(zl | 1u);    // (| 1, | 2^31: only reached with k == 1, where the values are unused)
+        jl = 31u - clz32(zl | 1u);            // (| 1, | 2^31 only matter on an invalid base, whose values are unused)
         jr = ctz32(zr | 0x80000000u);
     }
     const uint32_t lbc = (s.lb & ~31u) + jl, rbc = (s.rb1 & ~31u) + jr;
     const uint32_t dd = slide ? k - 1u : s.d;
-    // rank step (fm_index_cursor.hpp:110-146)
+    // rank step (fm_index_cursor.hpp:110-146); the blocks' counts include C[c], and the root interval [0, n) needs no
+    // special case: rank(0, c) = 0 and rank(n, c) = #c give [C[c], C[c+1])
     uint32_t ml = below32(jl), mr = below32(jr);
     uint32_t a0 = ld.A[0], b0 = ld.B[0];
     if ((a0 | b0) & kSFlagExc)
@@ -199,26 +195,21 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
     const uint32_t xl = c1 ? 0u : ~0u, xh = c2 ? 0u : ~0u;
     const uint32_t ca = c2 ? (c1 ? ld.A[3] : ld.A[2]) : (c1 ? ld.A[1] : a0);
     const uint32_t cb = c2 ? (c1 ? ld.B[3] : ld.B[2]) : (c1 ? ld.B[1] : b0);
-    const uint32_t cc = c2 ? (c1 ? cfg.cbeg[3] : cfg.cbeg[2]) : (c1 ? cfg.cbeg[1] : cfg.cbeg[0]);
-    uint32_t nl = cc + ca + popc32((ld.A[4] ^ xl) & (ld.A[5] ^ xh) & ml);
-    uint32_t nr = cc + cb + popc32((ld.B[4] ^ xl) & (ld.B[5] ^ xh) & mr);   // exclusive
-    if (dd == 0u)
-    {
-        nl = cc;
-        nr = c2 ? (c1 ? cfg.cend[3] : cfg.cend[2]) : (c1 ? cfg.cend[1] : cfg.cend[0]);
-    }
-    if (nr <= nl && dd != 0u)
+    const uint32_t nl = ca + popc32((ld.A[4] ^ xl) & (ld.A[5] ^ xh) & ml);
+    const uint32_t nr = cb + popc32((ld.B[4] ^ xl) & (ld.B[5] ^ xh) & mr);   // exclusive
+    const bool ok = nr > nl;
+    if (!ok && !inv && dd != 0u)
     {
         // read[t-d..t] does not occur: shorten it from the left (to the parent interval) and try the same base again
         if (dd == 1u) { s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; }
         else { s.lb = lbc; s.rb1 = rbc; s.d = dd; s.phase = P_UP; }
         return;
     }
-    const bool ok = nr > nl;
-    s.lb = ok ? nl : 0u;
-    s.rb1 = ok ? nr : cfg.n;
-    s.d = ok ? dd + 1u : 0u;
-    s.run += 1u;
+    const bool keep = ok && !inv;
+    s.lb = keep ? nl : 0u;
+    s.rb1 = keep ? nr : cfg.n;
+    s.d = keep ? dd + 1u : 0u;
+    s.run = inv ? 0u : s.run + 1u;
     lane32_advance(s);
     if (s.run >= k)
     {

@@ -49,7 +49,7 @@ uint32_t chg_upto_host(HostIndex const & h, uint32_t j)
     KBlock const & b = h.blocks[j >> 6];
     return b.chgcum + popc64(u64of(b.chg[0], b.chg[1]) & upto64(j & 63u));
 }
-void make_sblocks(HostIndex const & h, uint32_t k, std::vector<SBlock> & out)
+void make_sblocks(HostIndex const & h, uint32_t k, const uint32_t * ctab, std::vector<SBlock> & out)
 {
     const uint32_t n = (uint32_t)h.n;
     out.assign(n / 32 + 1, SBlock{});
@@ -60,7 +60,7 @@ void make_sblocks(HostIndex const & h, uint32_t k, std::vector<SBlock> & out)
         SBlock & o = out[blk];
         for (uint32_t c = 0; c < 4; ++c)
         {
-            o.cnt[c] = p.cnt[c];
+            o.cnt[c] = ctab[c] + p.cnt[c];
             const uint32_t xl = (c & 1u) ? 0u : ~0u, xh = (c & 2u) ? 0u : ~0u;
             if (half) o.cnt[c] += popc32((p.lo[0] ^ xl) & (p.hi[0] ^ xh) & ~p.exc[0]);
         }
@@ -246,11 +246,10 @@ int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, c
             // the product kernel's state machine (scan32_core.h) over host-built SBlocks; lanes claim units in turn
             if (backcheck) return -3;
             std::vector<SBlock> sb;
-            make_sblocks(h, k, sb);
+            make_sblocks(h, k, hv.ctab, sb);
             Cfg32 cfg;
             cfg.k = k; cfg.n = (uint32_t)h.n; cfg.units = paired ? n_reads / 2 : n_reads;
             cfg.paired = paired; cfg.local = local; cfg.record = mult != nullptr;
-            for (int c = 0; c < 4; ++c) { cfg.cbeg[c] = hv.ctab[c]; cfg.cend[c] = hv.ctab[kCtabEnd + c]; }
             HostEnv32 env{h, qual, qden, uniq, uniq_w, mult, local != 0, total, amb, look};
             std::vector<Lane32> lanes(nlanes);
             std::vector<Loads32> loads(nlanes);
