@@ -213,7 +213,7 @@ def main() -> None:
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--algorithm", default="rolling", choices=["rolling", "direct"])
+    ap.add_argument("--algorithm", default="rolling", choices=["rolling", "direct", "ktable", "auto"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -286,8 +286,12 @@ def main() -> None:
 
     stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream: the scan handle launches on it and the events time it
     torch.cuda.set_stream(stream)
-    algo = capi.ALGO_ROLLING if args.algorithm == "rolling" else capi.ALGO_DIRECT
+    algo = {"rolling": capi.ALGO_ROLLING, "direct": capi.ALGO_DIRECT, "ktable": capi.ALGO_KTABLE,
+            "auto": capi.ALGO_KTABLE if sh.k <= 31 else capi.ALGO_ROLLING}[args.algorithm]
+    t0 = time.perf_counter()
     scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=algo, device=local_rank, stream=stream.cuda_stream)
+    torch.cuda.synchronize()
+    t_scan_open = time.perf_counter() - t0     # per-(index, k) specialisation: rank blocks or the k-mer table
     V = sh.V
 
     def barrier():
@@ -352,6 +356,19 @@ def main() -> None:
     torch.cuda.synchronize()
     kern_ms = k0.elapsed_time(k1) / args.steps
     scan.finish()
+
+    # ---- cross-check outside every timed region: the k-mer table scan must reproduce the rolling FM search bit for bit
+    cross = None
+    if algo == capi.ALGO_KTABLE:
+        ref_scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=capi.ALGO_ROLLING, device=local_rank,
+                               stream=stream.cuda_stream)
+        ref_scan.submit_device(db)
+        rr = ref_scan.finish()
+        scan.reset(); scan.submit_device(db); rm = scan.finish()
+        assert np.array_equal(rr.unique, rm.unique) and rr.total_kmers == rm.total_kmers and rr.ambiguous == rm.ambiguous, \
+            "k-mer table tallies differ from the rolling FM search"
+        cross = "ktable tallies == rolling FM-search tallies on this rank's reads (unique[V], total, ambiguous)"
+        ref_scan.close()
 
     # ---- e2e: pinned host buffers through the C ABI ----
     e2e = None
@@ -421,13 +438,18 @@ def main() -> None:
         peak, how = measured_peak()
         ach = alg / (kern_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                "kernel": "scan32_kernel<0>" if algo == capi.ALGO_ROLLING else "scan_direct_kernel<0>", "kernel_ms": kern_ms,
+                "kernel": {capi.ALGO_ROLLING: "scan32_kernel<0>", capi.ALGO_KTABLE: "scanh_kernel<0>"}.get(algo, "scan_direct_kernel<0>"),
+                "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_launch": alg, "peak_source": how,
                 "work": {"steps_executed": st["steps_executed"], "lookups": st["lookups"], "kmers_hit": st["kmers_hit"],
                          "occ": st["occ"], "occ_sectors": st["occ_sectors"], "input_bytes": input_bytes},
                 "note": "algorithmic bytes follow the reference's per-window search (k steps from the root); the rolling kernel "
-                        "shares search state between overlapping windows, so its real traffic is lower; index footprint "
-                        f"{idx.device_bytes/1e6:.0f} MB is L2-resident when < 126 MB"}
+                        "shares search state between overlapping windows and the k-mer table kernel memoises the search, so their "
+                        f"real traffic is lower (own_sectors); index footprint {idx.device_bytes/1e6:.0f} MB"}
+        # what the kernel itself must move: one 32-byte sector per valid window (ktable) / two per read base (rolling), plus
+        # the packed input stream; against the HBM peak when the structure misses L2, else informative only
+        own = (32 * int(tall[V]) // world if algo == capi.ALGO_KTABLE else 64 * R * L) + packed_bytes
+        roof["own_sectors"] = {"bytes_per_launch": own, "GB/s": own / (kern_ms * 1e-3) / 1e9, "frac_of_hbm_peak": own / (kern_ms * 1e-3) / 1e9 / peak}
 
     # ---- cpu baseline (rank 0, N = 1 only) ----
     cpu = None
@@ -446,7 +468,8 @@ def main() -> None:
                 "reads_per_sec": reads_step * args.steps / (ms_total * 1e-3),
                 "clocks": clk, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu,
                 "tallies": {"unique": [int(x) for x in tall[:V]], "total_kmers": int(tall[V]), "ambiguous": int(tall[V + 1])},
-                "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack}}
+                "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack, "scan_open_s": t_scan_open},
+                "cross_check": cross}
         emit(line)
     scan.close()
     db.close()

@@ -122,6 +122,9 @@ int speqg_pack_reads(const uint8_t * seq, const uint8_t * qual, const uint64_t *
 #define SPEQG_ALGO_ROLLING 0  /* one pass per read: consecutive windows share their search state (default) */
 #define SPEQG_ALGO_DIRECT 1   /* every window searched from the root, k steps, like seqan3's search_trivial (global mode) */
 #define SPEQG_ALGO_ROLLING64 2 /* the rolling search on the generic 64-byte blocks (the back-check's kernel); cross-checks */
+#define SPEQG_ALGO_KTABLE 3   /* k <= 31: the search memoised per (index, k) as a k-mer table built from the index's own texts;
+                                 one 32-byte probe per window.  Same tallies, bit for bit */
+#define SPEQG_ALGO_AUTO 4     /* KTABLE when k <= 31, else ROLLING */
 
 typedef struct speqg_params
 {

@@ -20,7 +20,7 @@ OBJ_DIR = ROOT / "build"
 CLI_SRC = ROOT / "host"
 CLI_BIN = ROOT / "bin" / "speq"
 
-LIB_SOURCES = ["capi.cu", "capi_scan.cu", "capi_refine.cu", "kernels.cu", "scan32.cu", "index_build.cpp", "pack.cpp"]
+LIB_SOURCES = ["capi.cu", "capi_scan.cu", "capi_refine.cu", "kernels.cu", "scan32.cu", "scanh.cu", "index_build.cpp", "pack.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall,-pthread"]
 
 
@@ -39,12 +39,12 @@ def _stale(target: Path, deps: list[Path]) -> bool:
 
 
 def build_lib(force: bool = False, verbose: bool = False) -> Path:
-    deps = [p for p in CSRC.iterdir() if p.suffix in (".cu", ".cpp", ".h", ".hpp")] + [ROOT.parent / "include" / "speq_cuda.h"]
+    deps = [p for p in CSRC.iterdir() if p.suffix in (".cu", ".cpp", ".h", ".hpp", ".cuh")] + [ROOT.parent / "include" / "speq_cuda.h"]
     if not force and not _stale(LIB, deps):
         return LIB
     LIB_DIR.mkdir(exist_ok=True)
     OBJ_DIR.mkdir(exist_ok=True)
-    headers = [d for d in deps if d.suffix in (".h", ".hpp")]
+    headers = [d for d in deps if d.suffix in (".h", ".hpp", ".cuh")]
 
     def compile_one(src: str) -> Path:
         obj = OBJ_DIR / (src + ".o")

@@ -64,6 +64,14 @@ struct speqg_scan
     DevIndex view{};               // di->view with `blocks` replaced by this scan's k-specialised copy
     KBlock * d_blocks_k = nullptr;   // SPEQG_ALGO_ROLLING64 only
     FBlock * d_sblk = nullptr;       // per-k blocks of the product kernel (SBlock + variant bytes)
+    // SPEQG_ALGO_KTABLE: the per-(index, k) k-mer table and, with record_multiplicity, per-slot counts + interval starts
+    HSlot * d_ktab = nullptr;
+    uint32_t n_buckets = 0;
+    unsigned long long * d_slot_mult = nullptr;
+    uint32_t * d_slot_lb = nullptr;
+    bool slot_mult_dirty = false;
+    uint64_t ktab_keys = 0;
+    uint32_t algo = SPEQG_ALGO_ROLLING;   // resolved algorithm (AUTO -> KTABLE / ROLLING)
     int device = 0;
     speqg_params p{};
     int mode = 0;
@@ -72,7 +80,7 @@ struct speqg_scan
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
     double * d_unique_w = nullptr, * d_qden = nullptr, * d_percent = nullptr, * d_tkpg = nullptr, * d_partial = nullptr;
     int32_t * d_gc = nullptr;
-    LaunchCfg cfg{}, cfg64{}, cfg_direct{}, cfg_stats{};
+    LaunchCfg cfg{}, cfg64{}, cfg_direct{}, cfg_stats{}, cfg_h{};
     int refine_grid = 0;
     Slot slots[kSlots];
     int next_slot = 0;
@@ -95,6 +103,13 @@ struct scan_refine_view
 };
 scan_refine_view refine_view(speqg_scan * s)
 {
+    // k-mer table scan: multiplicities were recorded per table slot; move them to mult[lb] (what the rolling scan records)
+    if (s->slot_mult_dirty && s->d_mult)
+    {
+        device_guard guard(s->device);
+        CK(launch_ktable_fold_mult(s->d_slot_mult, s->d_slot_lb, 2ull * s->n_buckets, s->d_mult, s->compute));
+        s->slot_mult_dirty = false;
+    }
     return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult,
                             s->d_percent, s->d_tkpg, s->d_partial, s->d_gc, s->refine_grid};
 }
@@ -107,6 +122,7 @@ void scan_release(speqg_scan * s)
     cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
     cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk); cudaFree(s->d_work);
+    cudaFree(s->d_ktab); cudaFree(s->d_slot_mult); cudaFree(s->d_slot_lb);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -144,8 +160,13 @@ void launch_on_view(speqg_scan * s, BatchView const & v)
 {
     if (v.n_reads == 0) return;
     ScanArgs a = scan_args(s);
-    if (s->p.algorithm == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
-    else if (s->p.algorithm == SPEQG_ALGO_ROLLING64) CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg64, s->compute));
+    if (s->algo == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
+    else if (s->algo == SPEQG_ALGO_ROLLING64) CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg64, s->compute));
+    else if (s->algo == SPEQG_ALGO_KTABLE)
+    {
+        CK(launch_scanh(s->d_ktab, s->n_buckets, s->d_slot_mult, v, a, s->mode, s->cfg_h, s->compute));
+        if (s->mode & M_RECORD) s->slot_mult_dirty = true;
+    }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
     ++s->launches;
 }
@@ -173,8 +194,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
     need(idx && params && out, "NULL argument");
     need(params->k >= 1 && params->k <= kMaxK, "k must be in [1, 127]");
     need(params->mode == SPEQG_MODE_GLOBAL || params->mode == SPEQG_MODE_LOCAL, "unknown mode");
-    need(params->algorithm == SPEQG_ALGO_ROLLING || params->algorithm == SPEQG_ALGO_DIRECT ||
-         params->algorithm == SPEQG_ALGO_ROLLING64, "unknown algorithm");
+    need(params->algorithm <= SPEQG_ALGO_AUTO, "unknown algorithm");
+    need(!(params->algorithm == SPEQG_ALGO_KTABLE && params->k > kMaxKTable), "the k-mer table algorithm needs k <= 31");
     need(idx->host.n <= kMaxN32, "index too large: the indexed text must be shorter than 2^31 symbols");
     need(!(params->algorithm == SPEQG_ALGO_DIRECT && params->mode == SPEQG_MODE_LOCAL), "the direct algorithm covers global mode only");
     DeviceIndex & di = device_index(idx, device);
@@ -186,6 +207,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->di = &di;
         s->device = device;
         s->p = *params;
+        s->algo = params->algorithm == SPEQG_ALGO_AUTO ? (params->k <= kMaxKTable ? SPEQG_ALGO_KTABLE : SPEQG_ALGO_ROLLING)
+                                                        : params->algorithm;
         s->mode = (params->mode == SPEQG_MODE_LOCAL ? M_LOCAL : 0) | (params->record_multiplicity ? M_RECORD : 0) |
                   (params->paired ? M_PAIRED : 0);
         uint32_t V = idx->host.V;
@@ -216,7 +239,35 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->d_qden = dev_upload(qden, 42);
         // rank blocks specialised for this k: one pass over the index, once per scan handle
         s->view = di.view;
-        if (params->algorithm == SPEQG_ALGO_ROLLING64)
+        if (s->algo == SPEQG_ALGO_KTABLE)
+        {
+            // distinct k-mers of the index <= suffixes that start a depth-k lcp interval; load factor <= 0.4
+            HostIndex const & h = idx->host;
+            uint64_t ub = 0;
+            for (uint64_t i = 0; i < h.n; ++i) ub += h.lcp[i] < params->k ? 1u : 0u;
+            uint64_t nb = ub + ub / 4 + 16;
+            need(nb < (uint64_t(1) << 32), "k-mer table too large");
+            s->n_buckets = (uint32_t)nb;
+            s->d_ktab = dev_alloc<HSlot>(2 * nb);
+            uint32_t max_len = 0;
+            for (uint32_t L : h.t_len) max_len = L > max_len ? L : max_len;
+            CK(cudaMemsetAsync(s->d_work, 0, 8, s->compute));
+            CK(launch_ktable_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, di.t_group, h.S, max_len, s->d_ktab, s->n_buckets,
+                                   params->k, s->d_work, s->compute));
+            unsigned long long nk = 0;
+            CK(cudaMemcpyAsync(&nk, s->d_work, 8, cudaMemcpyDeviceToHost, s->compute));
+            CK(cudaStreamSynchronize(s->compute));
+            s->ktab_keys = nk;
+            if (params->record_multiplicity)
+            {
+                s->d_slot_mult = dev_alloc<unsigned long long>(2 * nb);
+                s->d_slot_lb = dev_alloc<uint32_t>(2 * nb);
+                CK(cudaMemsetAsync(s->d_slot_mult, 0, 2 * nb * 8, s->compute));
+                CK(launch_ktable_lb(s->d_ktab, 2 * nb, s->view, params->k, s->d_slot_lb, s->compute));
+            }
+            CK(scanh_launch_cfg(s->mode, V, &s->cfg_h));
+        }
+        else if (s->algo == SPEQG_ALGO_ROLLING64)
         {
             s->d_blocks_k = dev_alloc<KBlock>(idx->host.blocks.size());
             CK(launch_fill_e(di.blocks, s->d_blocks_k, di.lcp, (uint32_t)idx->host.n, params->k, s->compute));
@@ -266,6 +317,8 @@ int speqg_scan_reset(speqg_scan * s)
     CK(cudaMemsetAsync(s->d_scalars, 0, SC_COUNT * 8, s->compute));
     CK(cudaMemsetAsync(s->d_bad, 0, 8, s->compute));
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
+    if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 2ull * s->n_buckets * 8, s->compute));
+    s->slot_mult_dirty = false;
     s->launches = 0;
     SPEQG_CATCH
 }

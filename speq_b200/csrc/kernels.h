@@ -81,5 +81,15 @@ cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x *
                           FBlock * out, uint32_t n, uint32_t k, cudaStream_t st);
 // parent-jump records {psv, nsv, lcp} (one 16-byte load per side) from the stored lcp and pn arrays; once per device copy
 cudaError_t launch_build_up(const uint8_t * lcp, const uint2x * pn, UpRec * out, uint64_t count, cudaStream_t st);
+// k-mer table scan (scanh.cu): the search memoised per (index, k), k <= kMaxKTable
+cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
+                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, HSlot * tab, uint32_t n_buckets, uint32_t k,
+                                unsigned long long * n_keys, cudaStream_t st);
+cudaError_t launch_ktable_lb(const HSlot * tab, uint64_t n_slots, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st);
+cudaError_t launch_ktable_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
+                                    cudaStream_t st);
+cudaError_t launch_scanh(const HSlot * tab, uint32_t n_buckets, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a,
+                         int mode, LaunchCfg cfg, cudaStream_t st);
+cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

@@ -15,6 +15,7 @@
 
 #include "kernels.h"
 #include "scan32_core.h"
+#include "scan_dev.cuh"
 
 namespace speqb
 {
@@ -23,55 +24,12 @@ namespace
 constexpr int kBlock32 = 256;
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 
-__device__ __forceinline__ void ld256_if(uint32_t * w, const void * p, bool pred)
+template <int MODE, bool G8> struct Env32 : Tally32<MODE>
 {
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %9, 0;\n\t@q ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t}"
-                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]), "+r"(w[6]), "+r"(w[7])
-                 : "l"(p), "r"((int)pred));
-}
-__device__ __forceinline__ void ld64_if(uint64_t & v, const void * p, bool pred)
-{
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u64 %0, [%1];\n\t}" : "+l"(v) : "l"(p), "r"((int)pred));
-}
-__device__ __forceinline__ void ld32x2_if(uint32_t & x, uint32_t & y, const void * p, bool pred)
-{
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %3, 0;\n\t@q ld.global.nc.v2.u32 {%0,%1}, [%2];\n\t}" : "+r"(x), "+r"(y) : "l"(p), "r"((int)pred));
-}
-__device__ __forceinline__ void ld32_if(uint32_t & v, const void * p, bool pred)
-{
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
-}
-__device__ __forceinline__ void ld128_if(uint32_t * w, const void * p, bool pred)
-{
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %5, 0;\n\t@q ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
-                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
-                 : "l"(p), "r"((int)pred));
-}
-
-// shared-memory tallies of one CTA
-struct Smem32
-{
-    double * w;                   // [V] local-mode weighted unique tallies
-    uint32_t * cnt;               // [V] unique tallies (global mode)
-    unsigned long long * scal;    // [4] total, ambiguous, lookups, reads
-};
-__device__ __forceinline__ Smem32 smem32_view(unsigned char * raw, uint32_t V)
-{
-    Smem32 s;
-    s.scal = reinterpret_cast<unsigned long long *>(raw);
-    s.w = reinterpret_cast<double *>(raw + 32);
-    s.cnt = reinterpret_cast<uint32_t *>(raw + 32 + (size_t)V * 8);
-    return s;
-}
-
-template <int MODE, bool G8> struct Env32
-{
-    static constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
     const FBlock * fblk;
     DevIndex const & ix;
-    BatchView const & b;
-    ScanArgs const & a;
-    Smem32 sm;
+    __device__ __forceinline__ Env32(const FBlock * f, DevIndex const & i, BatchView const & b_, ScanArgs const & a_, Smem32 s)
+        : Tally32<MODE>{b_, a_, s}, fblk(f), ix(i) {}
     __device__ __forceinline__ uint32_t load_grp(uint32_t i) const
     {
         // G8: the variant byte sits in the 64-byte burst of the suffix's own block
@@ -81,38 +39,7 @@ template <int MODE, bool G8> struct Env32
         return v;
     }
     __device__ __forceinline__ uint32_t exc_word(uint32_t blk) const { return load_ro(&ix.blocks[blk >> 1].exc[blk & 1u]); }
-    __device__ __forceinline__ double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
-    {
-        // window = positions [t_end-k, t_end); the left fold of src/fm_scanner.cpp:454, a / (1 - 1/pow(10, q/10)), with
-        // the denominators tabulated by the host's libm: IEEE division keeps every weight bit-exact
-        const uint8_t * q = b.qual + 32u * g0 + (t_end - k);
-        double w = 1.0;
-        for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
-        return w;
-    }
-    __device__ __forceinline__ void unique(uint32_t g, uint32_t n, double w) const
-    {
-        if (LOCAL) atomicAdd(&sm.w[g], w);
-        else atomicAdd(&sm.cnt[g], n);
-    }
-    __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(a.mult + lb, 1ull); }
-    // 64-bit shared counters as two native 32-bit atomics (a 64-bit shared atomicAdd is a CAS loop)
-    __device__ __forceinline__ void add64(int i, uint32_t v) const
-    {
-        uint32_t * w = reinterpret_cast<uint32_t *>(sm.scal + i);
-        const uint32_t old = atomicAdd(w, v);
-        if (old + v < old) atomicAdd(w + 1, 1u);
-    }
-    __device__ __forceinline__ void count_fetch(uint32_t nwin) const
-    {
-        add64(2, nwin);
-        add64(3, 1u);
-    }
-    __device__ __forceinline__ void count_unit(uint32_t total, bool amb) const
-    {
-        if (total) add64(0, total);
-        if (amb) add64(1, 1u);
-    }
+    __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(this->a.mult + lb, 1ull); }
 };
 
 template <int MODE, bool G8>
@@ -123,13 +50,7 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
     constexpr bool RECORD = (MODE & M_RECORD) != 0;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem32 sm = smem32_view(smem_raw, a.V);
-    if (threadIdx.x < 4) sm.scal[threadIdx.x] = 0ull;
-    for (uint32_t g = threadIdx.x; g < a.V; g += blockDim.x)
-    {
-        sm.w[g] = 0.0;
-        sm.cnt[g] = 0u;
-    }
-    __syncthreads();
+    smem32_clear(sm, a.V);
 
     Cfg32 cfg;
     cfg.k = a.k;
@@ -138,7 +59,7 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
     cfg.paired = paired;
     cfg.local = LOCAL;
     cfg.record = RECORD;
-    Env32<MODE, G8> env{fblk, ix, b, a, sm};
+    Env32<MODE, G8> env(fblk, ix, b, a, sm);
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
 
@@ -195,19 +116,7 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
         else if (ph == P_FETCH) lane32_fetch(s, ld, cfg, env);
     }
     lane32_flush_agg(s, env);
-    __syncthreads();
-    if (threadIdx.x == 0)
-    {
-        if (sm.scal[0]) atomicAdd(a.scalars + SC_TOTAL, sm.scal[0]);
-        if (sm.scal[1]) atomicAdd(a.scalars + SC_AMBIG, sm.scal[1]);
-        if (sm.scal[2]) atomicAdd(a.scalars + SC_LOOKUPS, sm.scal[2]);
-        if (sm.scal[3]) atomicAdd(a.scalars + SC_READS, sm.scal[3]);
-    }
-    for (uint32_t g = threadIdx.x; g < a.V; g += blockDim.x)
-    {
-        if (LOCAL) { if (sm.w[g] != 0.0) atomicAdd(a.unique_w + g, sm.w[g]); }
-        else if (sm.cnt[g]) atomicAdd(a.unique + g, (unsigned long long)sm.cnt[g]);
-    }
+    smem32_flush<LOCAL>(sm, a);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

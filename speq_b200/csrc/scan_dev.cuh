@@ -1,0 +1,122 @@
+// scan_dev.cuh -- device helpers shared by the scan kernels (scan32.cu, scanh.cu): predicated read-only loads and the
+// CTA's shared-memory tallies (do_a_count's counters, src/fm_scanner.cpp:153-196 / :426-471 of the reference).
+#pragma once
+#include "kernels.h"
+#include "scan_core.h"
+
+namespace speqb
+{
+namespace
+{
+__device__ __forceinline__ void ld256_if(uint32_t * w, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %9, 0;\n\t@q ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]), "+r"(w[6]), "+r"(w[7])
+                 : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld64_if(uint64_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u64 %0, [%1];\n\t}" : "+l"(v) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld32x2_if(uint32_t & x, uint32_t & y, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %3, 0;\n\t@q ld.global.nc.v2.u32 {%0,%1}, [%2];\n\t}" : "+r"(x), "+r"(y) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld32_if(uint32_t & v, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(p), "r"((int)pred));
+}
+__device__ __forceinline__ void ld128_if(uint32_t * w, const void * p, bool pred)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %5, 0;\n\t@q ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
+                 : "l"(p), "r"((int)pred));
+}
+
+// shared-memory tallies of one CTA
+struct Smem32
+{
+    double * w;                   // [V] local-mode weighted unique tallies
+    uint32_t * cnt;               // [V] unique tallies (global mode)
+    unsigned long long * scal;    // [4] total, ambiguous, lookups, reads
+};
+__device__ __forceinline__ Smem32 smem32_view(unsigned char * raw, uint32_t V)
+{
+    Smem32 s;
+    s.scal = reinterpret_cast<unsigned long long *>(raw);
+    s.w = reinterpret_cast<double *>(raw + 32);
+    s.cnt = reinterpret_cast<uint32_t *>(raw + 32 + (size_t)V * 8);
+    return s;
+}
+
+
+// The tally side of a scan kernel's Env: weighted / counted unique hits per variant, total / ambiguous / lookups / reads.
+template <int MODE> struct Tally32
+{
+    static constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
+    BatchView const & b;
+    ScanArgs const & a;
+    Smem32 sm;
+    __device__ __forceinline__ double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
+    {
+        // window = positions [t_end-k, t_end); the left fold of src/fm_scanner.cpp:454, a / (1 - 1/pow(10, q/10)), with
+        // the denominators tabulated by the host's libm: IEEE division keeps every weight bit-exact
+        const uint8_t * q = b.qual + 32u * g0 + (t_end - k);
+        double w = 1.0;
+        for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
+        return w;
+    }
+    __device__ __forceinline__ void unique(uint32_t g, uint32_t n, double w) const
+    {
+        if (LOCAL) atomicAdd(&sm.w[g], w);
+        else atomicAdd(&sm.cnt[g], n);
+    }
+    // 64-bit shared counters as two native 32-bit atomics (a 64-bit shared atomicAdd is a CAS loop)
+    __device__ __forceinline__ void add64(int i, uint32_t v) const
+    {
+        uint32_t * w = reinterpret_cast<uint32_t *>(sm.scal + i);
+        const uint32_t old = atomicAdd(w, v);
+        if (old + v < old) atomicAdd(w + 1, 1u);
+    }
+    __device__ __forceinline__ void count_fetch(uint32_t nwin) const
+    {
+        add64(2, nwin);
+        add64(3, 1u);
+    }
+    __device__ __forceinline__ void count_unit(uint32_t total, bool amb) const
+    {
+        if (total) add64(0, total);
+        if (amb) add64(1, 1u);
+    }
+};
+
+__device__ __forceinline__ void smem32_clear(Smem32 const & sm, uint32_t V)
+{
+    if (threadIdx.x < 4) sm.scal[threadIdx.x] = 0ull;
+    for (uint32_t g = threadIdx.x; g < V; g += blockDim.x)
+    {
+        sm.w[g] = 0.0;
+        sm.cnt[g] = 0u;
+    }
+    __syncthreads();
+}
+
+template <bool LOCAL>
+__device__ __forceinline__ void smem32_flush(Smem32 const & sm, ScanArgs const & a)
+{
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        if (sm.scal[0]) atomicAdd(a.scalars + SC_TOTAL, sm.scal[0]);
+        if (sm.scal[1]) atomicAdd(a.scalars + SC_AMBIG, sm.scal[1]);
+        if (sm.scal[2]) atomicAdd(a.scalars + SC_LOOKUPS, sm.scal[2]);
+        if (sm.scal[3]) atomicAdd(a.scalars + SC_READS, sm.scal[3]);
+    }
+    for (uint32_t g = threadIdx.x; g < a.V; g += blockDim.x)
+    {
+        if (LOCAL) { if (sm.w[g] != 0.0) atomicAdd(a.unique_w + g, sm.w[g]); }
+        else if (sm.cnt[g]) atomicAdd(a.unique + g, (unsigned long long)sm.cnt[g]);
+    }
+}
+}   // namespace
+}   // namespace speqb

@@ -49,6 +49,20 @@ def test_golden(lib, name, raw):
     _compare(out, exp, len(counts))
 
 
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("raw", [True, False])
+def test_golden_ktable_algorithm(lib, name, raw):
+    """The k-mer table scan (one probe per window) against the same fixtures, all modes, with the refinement running on
+    multiplicities recorded per table slot."""
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
+                         fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], raw=raw, batch_reads=64,
+                         algorithm=capi.ALGO_KTABLE)
+    _compare(out, exp, len(counts))
+
+
 @pytest.mark.parametrize("name", ["global_single", "global_paired", "refs_with_n", "short_k"])
 def test_golden_direct_algorithm(lib, name):
     fx = helpers.load_golden(name)
@@ -78,8 +92,9 @@ def test_reference_work_counters(lib):
     sc.close(); db.close(); idx.close()
 
 
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE])
 @pytest.mark.parametrize("mode", ["global", "local", "global_paired"])
-def test_vs_oracle_c1_like(lib, oracle_bin, tmp_path, mode):
+def test_vs_oracle_c1_like(lib, oracle_bin, tmp_path, mode, algorithm):
     """C1-shaped input (2 variants x 3 isolates x 30 kb, 150 bp reads, k=21) at a read count the oracle finishes in seconds."""
     sh = synth.CONFIGS["C1"]
     refs = synth.make_refs(sh, synth.SEED0 + 1)
@@ -101,14 +116,15 @@ def test_vs_oracle_c1_like(lib, oracle_bin, tmp_path, mode):
     offs = (np.arange(R + 1, dtype=np.uint64) * sh.L)
     out = driver.run_all(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), [sh.I] * sh.V,
                          driver.Reads(seq.reshape(-1), qual.reshape(-1), offs), k=sh.k, phred_cutoff=cutoff, fixed_accuracy=acc,
-                         paired=paired, batch_reads=2048)
+                         paired=paired, batch_reads=2048, algorithm=algorithm)
     _compare(out, exp, sh.V)
 
 
-def test_edge_cases(lib):
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE])
+def test_edge_cases(lib, algorithm):
     scaff = [engine.ascii_to_ranks("ACGTTGCAAGGCTTAACCGGTTAGCATCGA"), engine.ascii_to_ranks("ACGTTGCATGGCTTAACCGGTAAGCATCGA")]
     idx = engine.Index.from_scaffolds(scaff, [0, 1], 2)
-    sc = engine.Scan(idx, k=8)
+    sc = engine.Scan(idx, k=8, algorithm=algorithm)
     # no reads at all; then empty reads, reads shorter than k, read exactly k long, all-N read
     r = sc.finish()
     assert r.total_kmers == 0 and r.lookups == 0 and r.reads == 0
@@ -134,16 +150,19 @@ def test_edge_cases(lib):
         sc.finish()
     assert "parse_error" in ei.value.message
     # paired mode needs an even number of reads; local mode needs qualities
-    sp = engine.Scan(idx, k=8, paired=True)
+    sp = engine.Scan(idx, k=8, paired=True, algorithm=algorithm)
     with pytest.raises(capi.SpeqError):
         sp.submit_raw(seq, q, offs, 1)
-    sl = engine.Scan(idx, k=8, mode=capi.MODE_LOCAL)
+    sl = engine.Scan(idx, k=8, mode=capi.MODE_LOCAL, algorithm=algorithm)
     with pytest.raises(capi.SpeqError):
         sl.submit_raw(seq, None, offs, 1)
     with pytest.raises(capi.SpeqError):
         engine.Scan(idx, k=0)
     with pytest.raises(capi.SpeqError):
         engine.Scan(idx, k=128)
+    with pytest.raises(capi.SpeqError):
+        engine.Scan(idx, k=32, algorithm=capi.ALGO_KTABLE)      # the table covers k <= 31; AUTO falls back to rolling
+    engine.Scan(idx, k=32, algorithm=capi.ALGO_AUTO).close()
     with pytest.raises(capi.SpeqError):
         sc.refine(np.ones(2), np.ones(2, np.int32))     # opened without record_multiplicity -> ESTATE
     for s in (sc, sp, sl):
@@ -179,6 +198,9 @@ def test_properties_at_config_shapes(lib, cfg, R):
     assert a.unique.sum() > 0
     c = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
     assert np.array_equal(a.unique, c.unique) and a.total_kmers == c.total_kmers and a.ambiguous == c.ambiguous
+    d = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_KTABLE)
+    assert np.array_equal(a.unique, d.unique) and a.total_kmers == d.total_kmers and a.ambiguous == d.ambiguous
+    assert d.lookups == a.lookups and d.reads == a.reads
     h = R // 2
     p1 = _scan_tallies(idx, sh.k, seq, qual, offs[:h + 1])
     p2 = _scan_tallies(idx, sh.k, seq, qual, offs[h:])
@@ -196,6 +218,14 @@ def test_properties_at_config_shapes(lib, cfg, R):
     # refinement estimate conserves mass: sum_g tkpg[g] == number of recorded (hit) windows
     tk = sc.refine(np.full(sh.V, 100.0 / sh.V), np.full(sh.V, sh.I, np.int32))
     assert abs(tk.sum() - r0.total_kmers) <= 1e-9 * r0.total_kmers
+    # the same through the k-mer table: multiplicities recorded per slot, folded to interval starts before the estimate
+    sk = engine.Scan(idx, k=sh.k, record=True, algorithm=capi.ALGO_KTABLE)
+    sk.submit_raw(s0.cpu().numpy().reshape(-1), q0.cpu().numpy().reshape(-1), np.arange(n0 + 1, dtype=np.uint64) * sh.L, n0)
+    rk = sk.finish()
+    assert rk.total_kmers == r0.total_kmers and np.array_equal(rk.unique, r0.unique)
+    tkk = sk.refine(np.full(sh.V, 100.0 / sh.V), np.full(sh.V, sh.I, np.int32))
+    assert helpers.rel_close(tkk, tk, 1e-11)
+    sk.close()
     sc.close()
     idx.close()
     del refs
@@ -243,7 +273,8 @@ def test_many_variants_u16_groups(lib):
     a = _scan_tallies(idx, 15, seq, qual, offs)
     b = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_DIRECT)
     c = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
+    d = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_KTABLE)
     assert a.unique.sum() > 0
-    for o in (b, c):
+    for o in (b, c, d):
         assert np.array_equal(a.unique, o.unique) and a.total_kmers == o.total_kmers and a.ambiguous == o.ambiguous
     idx.close()
