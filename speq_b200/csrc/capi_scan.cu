@@ -65,8 +65,8 @@ struct speqg_scan
     KBlock * d_blocks_k = nullptr;   // SPEQG_ALGO_ROLLING64 only
     FBlock * d_sblk = nullptr;       // per-k blocks of the product kernel (SBlock + variant bytes)
     // SPEQG_ALGO_KTABLE: the per-(index, k) k-mer table and, with record_multiplicity, per-slot counts + interval starts
-    HSlot * d_ktab = nullptr;
-    uint32_t n_buckets = 0;
+    KTabView kt{};
+    unsigned long long * d_kstat = nullptr;   // [2]: keys stored, placement failure flag
     unsigned long long * d_slot_mult = nullptr;
     uint32_t * d_slot_lb = nullptr;
     bool slot_mult_dirty = false;
@@ -107,7 +107,7 @@ scan_refine_view refine_view(speqg_scan * s)
     if (s->slot_mult_dirty && s->d_mult)
     {
         device_guard guard(s->device);
-        CK(launch_ktable_fold_mult(s->d_slot_mult, s->d_slot_lb, 2ull * s->n_buckets, s->d_mult, s->compute));
+        CK(launch_ktable_fold_mult(s->d_slot_mult, s->d_slot_lb, 4ull * ((uint64_t)s->kt.nbmask + 1), s->d_mult, s->compute));
         s->slot_mult_dirty = false;
     }
     return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult,
@@ -122,7 +122,7 @@ void scan_release(speqg_scan * s)
     cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
     cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk); cudaFree(s->d_work);
-    cudaFree(s->d_ktab); cudaFree(s->d_slot_mult); cudaFree(s->d_slot_lb);
+    cudaFree(s->kt.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_slot_lb); cudaFree(s->d_kstat);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -164,7 +164,7 @@ void launch_on_view(speqg_scan * s, BatchView const & v)
     else if (s->algo == SPEQG_ALGO_ROLLING64) CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg64, s->compute));
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
-        CK(launch_scanh(s->d_ktab, s->n_buckets, s->d_slot_mult, v, a, s->mode, s->cfg_h, s->compute));
+        CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, s->cfg_h, s->compute));
         if (s->mode & M_RECORD) s->slot_mult_dirty = true;
     }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
@@ -241,29 +241,35 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->view = di.view;
         if (s->algo == SPEQG_ALGO_KTABLE)
         {
-            // distinct k-mers of the index <= suffixes that start a depth-k lcp interval; load factor <= 0.4
+            // distinct k-mers of the index <= suffixes that start a depth-k lcp interval; load factor in (0.2, 0.4]
             HostIndex const & h = idx->host;
             uint64_t ub = 0;
             for (uint64_t i = 0; i < h.n; ++i) ub += h.lcp[i] < params->k ? 1u : 0u;
-            uint64_t nb = ub + ub / 4 + 16;
-            need(nb < (uint64_t(1) << 32), "k-mer table too large");
-            s->n_buckets = (uint32_t)nb;
-            s->d_ktab = dev_alloc<HSlot>(2 * nb);
             uint32_t max_len = 0;
             for (uint32_t L : h.t_len) max_len = L > max_len ? L : max_len;
-            CK(cudaMemsetAsync(s->d_work, 0, 8, s->compute));
-            CK(launch_ktable_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, di.t_group, h.S, max_len, s->d_ktab, s->n_buckets,
-                                   params->k, s->d_work, s->compute));
-            unsigned long long nk = 0;
-            CK(cudaMemcpyAsync(&nk, s->d_work, 8, cudaMemcpyDeviceToHost, s->compute));
-            CK(cudaStreamSynchronize(s->compute));
-            s->ktab_keys = nk;
+            s->d_kstat = dev_alloc<unsigned long long>(2);
+            for (uint32_t grow = 0;; ++grow)
+            {
+                need(grow < 4 && ktable_geometry(params->k, ub, grow, &s->kt), "k-mer table too large");
+                s->kt.slots = dev_alloc<uint64_t>(4ull * ((uint64_t)s->kt.nbmask + 1));
+                CK(launch_ktable_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, di.t_group, h.S, max_len, s->kt, params->k,
+                                       s->d_kstat, s->compute));
+                unsigned long long st[2] = {0, 0};
+                CK(cudaMemcpyAsync(st, s->d_kstat, 16, cudaMemcpyDeviceToHost, s->compute));
+                CK(cudaStreamSynchronize(s->compute));
+                s->ktab_keys = st[0];
+                if (!st[1]) break;
+                // a k-mer ended up more than 6 buckets from its home (very unlikely below load 0.4): double the table
+                CK(cudaFree(s->kt.slots));
+                s->kt.slots = nullptr;
+            }
             if (params->record_multiplicity)
             {
-                s->d_slot_mult = dev_alloc<unsigned long long>(2 * nb);
-                s->d_slot_lb = dev_alloc<uint32_t>(2 * nb);
-                CK(cudaMemsetAsync(s->d_slot_mult, 0, 2 * nb * 8, s->compute));
-                CK(launch_ktable_lb(s->d_ktab, 2 * nb, s->view, params->k, s->d_slot_lb, s->compute));
+                const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
+                s->d_slot_mult = dev_alloc<unsigned long long>(n_slots);
+                s->d_slot_lb = dev_alloc<uint32_t>(n_slots);
+                CK(cudaMemsetAsync(s->d_slot_mult, 0, n_slots * 8, s->compute));
+                CK(launch_ktable_lb(s->kt, s->view, params->k, s->d_slot_lb, s->compute));
             }
             CK(scanh_launch_cfg(s->mode, V, &s->cfg_h));
         }
@@ -317,7 +323,7 @@ int speqg_scan_reset(speqg_scan * s)
     CK(cudaMemsetAsync(s->d_scalars, 0, SC_COUNT * 8, s->compute));
     CK(cudaMemsetAsync(s->d_bad, 0, 8, s->compute));
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
-    if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 2ull * s->n_buckets * 8, s->compute));
+    if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
     s->slot_mult_dirty = false;
     s->launches = 0;
     SPEQG_CATCH

@@ -98,15 +98,7 @@ struct __attribute__((aligned(16))) UpRec
     uint32_t pad;
 };
 static_assert(sizeof(UpRec) == 16, "UpRec must be 16 bytes");
-// HSlot: one entry of the per-(index, k) k-mer table (scanh.cu): key = the k-mer's 2-bit code (base i at bits [2i, 2i+2),
-// all ones = empty; k <= 31 keeps real keys below that), val = the variant every occurrence belongs to, or 0xFFFFFFFE when
-// the k-mer occurs in texts of several variants.  Two slots make one 32-byte bucket = one sector per probe.
-struct __attribute__((aligned(16))) HSlot
-{
-    uint64_t key;
-    uint64_t val;
-};
-static_assert(sizeof(HSlot) == 16, "HSlot must be 16 bytes");
+// the k-mer table scan (scanh.cu) memoises the search per (index, k) for k up to:
 constexpr uint32_t kMaxKTable = 31;
 constexpr uint32_t kSFlagExc = 0x80000000u;
 constexpr uint64_t kMaxN32 = 0x7FFFFFFFull;   // cnt[0] keeps bit 31 for the exception flag

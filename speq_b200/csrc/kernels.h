@@ -82,14 +82,22 @@ cudaError_t launch_fill32(const KBlock * kb, const uint8_t * lcp, const uint2x *
 // parent-jump records {psv, nsv, lcp} (one 16-byte load per side) from the stored lcp and pn arrays; once per device copy
 cudaError_t launch_build_up(const uint8_t * lcp, const uint2x * pn, UpRec * out, uint64_t count, cudaStream_t st);
 // k-mer table scan (scanh.cu): the search memoised per (index, k), k <= kMaxKTable
+struct KTabView
+{
+    uint64_t * slots;             // 4 << q slots: value << 48 | displacement << rbits | remainder; all ones = free
+    uint32_t q, rbits, nbmask;    // 2^q buckets of 4 slots; rbits = 2k - q stored key bits; nbmask = 2^q - 1
+    uint64_t mask_b, rmask;       // 4^k - 1, 2^rbits - 1
+    uint64_t mul, mul_inv;        // invertible multiplicative hash mod 4^k and its inverse
+};
+bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt);
 cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
-                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, HSlot * tab, uint32_t n_buckets, uint32_t k,
+                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
                                 unsigned long long * n_keys, cudaStream_t st);
-cudaError_t launch_ktable_lb(const HSlot * tab, uint64_t n_slots, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st);
+cudaError_t launch_ktable_lb(KTabView const & kt, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st);
 cudaError_t launch_ktable_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
                                     cudaStream_t st);
-cudaError_t launch_scanh(const HSlot * tab, uint32_t n_buckets, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a,
-                         int mode, LaunchCfg cfg, cudaStream_t st);
+cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
+                         LaunchCfg cfg, cudaStream_t st);
 cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

@@ -5,19 +5,23 @@
 // which (src/fm_scanner.cpp:166-177).  For k <= 31 that function is materialised once per scan handle:
 //
 //   ktable_build_kernel   walks the index's own texts (both strands of every scaffold, already resident as a packed batch)
-//                         and inserts every N-free k-mer into an open-addressing table keyed by its 2-bit code:
-//                         value = the variant of the text, or kValMulti once two variants have been seen.
+//                         and inserts every N-free k-mer: value = the variant of the text, or kValMulti once texts of two
+//                         variants hold it.
 //   ktable_lb_kernel      (record_multiplicity only) resolves each stored k-mer to the start of its SA interval with k
 //                         rank steps on the blocked BWT, so multiplicities recorded per slot reach the refinement kernel
 //                         as mult[lb] exactly as the rolling kernel records them.
 //   scanh_kernel          one lane per read (pair): rolls the 2-bit k-mer of the window (one shift per base) and probes
 //                         ONE 32-byte bucket per valid window -- one sector per window instead of two per base and no
 //                         instruction spent on interval arithmetic.  A k-mer is absent from the index iff the probe
-//                         reaches an empty slot, which is "the backward search failed" of the reference.
+//                         reaches a bucket with a free slot, which is "the backward search failed" of the reference.
 //
-// Buckets are 32 bytes = 2 slots of {key, value}; a probe loads the bucket with one LDG.256 and moves to the next
-// bucket only when both slots hold other keys.  Units are claimed in chunks of kClaimChunk per warp (one global atomic
-// per chunk), tallies are the shared-memory ones of scan_dev.cuh.
+// Table layout (KTabView, kernels.h): 2^q buckets of four 8-byte slots = one 32-byte sector per probe.  The key is hashed
+// with an invertible multiplication mod 4^k; the top q bits choose the home bucket and only the remaining rbits are
+// stored (quotienting), next to the displacement d <= 6 from the home bucket and the 16-bit value:
+//     slot = value << 48 | d << rbits | remainder,   all ones = free.
+// Insertion takes the first free slot from the home bucket on, so a lookup stops at the first bucket whose last slot is
+// free.  Units are claimed in chunks of kClaimChunk per warp (one global atomic per chunk); tallies go to the shared-memory
+// counters of scan_dev.cuh, per-read scalars through per-lane registers.
 #include <algorithm>
 
 #include "kernels.h"
@@ -30,23 +34,55 @@ namespace
 constexpr int kBlockH = 256;
 constexpr uint32_t kFullH = 0xFFFFFFFFu;
 constexpr uint32_t kClaimChunk = 64;
-constexpr uint64_t kKeyEmpty = ~0ull;
-constexpr uint64_t kValEmpty = ~0ull;
-constexpr uint64_t kValMulti = 0xFFFFFFFEull;      // low word; a group is < 65535
-constexpr uint64_t kHashMul = 0x9E3779B97F4A7C15ull;
-
-__device__ __forceinline__ uint32_t hbucket(uint64_t key, uint32_t nb)
-{
-    return __umulhi((uint32_t)((key * kHashMul) >> 32), nb);
-}
+constexpr uint64_t kSlotFree = ~0ull;
+constexpr uint32_t kValMulti = 0xFFFFu;            // a group is < 65535
+constexpr uint32_t kMaxDisp = 6;
 
 // ---------------------------------------------------------------------------------------------------------------
 // build: one thread per 32-base group of a text; the 32 windows that start in the group
 // ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool ktable_insert(KTabView const & kt, uint64_t key, uint32_t grp, unsigned long long * n_keys)
+{
+    const uint64_t h = (key * kt.mul) & kt.mask_b;
+    const uint32_t home = (uint32_t)(h >> kt.rbits);
+    const uint64_t r = h & kt.rmask;
+    const uint64_t kmask = (kt.rmask << 3) | 7ull;        // remainder + displacement
+    for (uint32_t d = 0; d <= kMaxDisp; ++d)
+    {
+        const uint32_t bk = (home + d) & kt.nbmask;
+        const uint64_t want = r | ((uint64_t)d << kt.rbits);
+        for (int j = 0; j < 4; ++j)
+        {
+            unsigned long long * p = reinterpret_cast<unsigned long long *>(kt.slots + 4ull * bk + j);
+            unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(p);
+            while (true)
+            {
+                if (old == kSlotFree)
+                {
+                    const unsigned long long prev = atomicCAS(p, kSlotFree, want | ((unsigned long long)grp << 48));
+                    if (prev == kSlotFree)
+                    {
+                        atomicAdd(n_keys, 1ull);
+                        return true;
+                    }
+                    old = prev;
+                }
+                if ((old & kmask) != want) break;              // another k-mer lives here: next slot
+                const uint32_t v = (uint32_t)(old >> 48);
+                if (v == grp || v == kValMulti) return true;
+                const unsigned long long prev = atomicCAS(p, old, old | ((unsigned long long)kValMulti << 48));
+                if (prev == old) return true;
+                old = prev;
+            }
+        }
+    }
+    return false;
+}
+
 __global__ void __launch_bounds__(kBlockH) ktable_build_kernel(const uint64_t * __restrict__ bases, const uint32_t * __restrict__ inv,
                                                                const uint64_t * __restrict__ grp_off, const uint32_t * __restrict__ len,
-                                                               const int32_t * __restrict__ text_group, HSlot * __restrict__ tab,
-                                                               const uint32_t nb, const uint32_t k, unsigned long long * __restrict__ n_keys)
+                                                               const int32_t * __restrict__ text_group, const KTabView kt, const uint32_t k,
+                                                               unsigned long long * __restrict__ n_keys)
 {
     const uint32_t text = blockIdx.y;
     const uint32_t L = len[text];
@@ -54,11 +90,10 @@ __global__ void __launch_bounds__(kBlockH) ktable_build_kernel(const uint64_t * 
     const uint32_t nwin = L - k + 1u;
     const uint64_t g0 = grp_off[text];
     const uint32_t grp = (uint32_t)text_group[text];
-    const uint64_t mask = (k == 32u) ? ~0ull : ((1ull << (2u * k)) - 1ull);
     const uint64_t vmask = (1ull << k) - 1ull;
-    for (uint32_t gi = blockIdx.x * blockDim.x + threadIdx.x; gi * 32u < nwin; gi += gridDim.x * blockDim.x)
+    for (uint32_t gi = blockIdx.x * blockDim.x + threadIdx.x; (uint64_t)gi * 32u < nwin; gi += gridDim.x * blockDim.x)
     {
-        // bases [32 gi, 32 gi + 64): every window that starts in this group (k <= 32)
+        // bases [32 gi, 32 gi + 64): every window that starts in this group (k <= 31)
         const uint32_t ngroups = (L + 31u) >> 5;
         const uint64_t b0 = bases[g0 + gi], b1 = gi + 1u < ngroups ? bases[g0 + gi + 1u] : 0ull;
         const uint64_t v = (uint64_t)inv[g0 + gi] | ((gi + 1u < ngroups ? (uint64_t)inv[g0 + gi + 1u] : 0ull) << 32);
@@ -67,46 +102,26 @@ __global__ void __launch_bounds__(kBlockH) ktable_build_kernel(const uint64_t * 
             const uint32_t p = gi * 32u + j;
             if (p >= nwin) break;
             if ((v >> j) & vmask) continue;                       // the window holds an N: no ACGT query matches it
-            const uint64_t key = (j == 0u ? b0 : (b0 >> (2u * j)) | (b1 << (64u - 2u * j))) & mask;
-            uint32_t bk = hbucket(key, nb);
-            while (true)
-            {
-                HSlot * s = tab + 2ull * bk;
-                bool placed = false;
-                for (int w = 0; w < 2 && !placed; ++w)
-                {
-                    unsigned long long * kp = reinterpret_cast<unsigned long long *>(&s[w].key);
-                    unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(kp);
-                    if (old == kKeyEmpty)
-                    {
-                        old = atomicCAS(kp, kKeyEmpty, key);
-                        if (old == kKeyEmpty) atomicAdd(n_keys, 1ull);
-                    }
-                    if (old == kKeyEmpty || old == key)
-                    {
-                        unsigned long long * vp = reinterpret_cast<unsigned long long *>(&s[w].val);
-                        const unsigned long long was = atomicCAS(vp, kValEmpty, (unsigned long long)grp);
-                        if (was != kValEmpty && was != grp && was != kValMulti) atomicExch(vp, kValMulti);
-                        placed = true;
-                    }
-                }
-                if (placed) break;
-                bk = bk + 1u == nb ? 0u : bk + 1u;
-            }
+            const uint64_t key = (j == 0u ? b0 : (b0 >> (2u * j)) | (b1 << (64u - 2u * j))) & kt.mask_b;
+            if (!ktable_insert(kt, key, grp, n_keys)) atomicExch(n_keys + 1, 1ull);   // displacement > kMaxDisp: the host regrows
         }
     }
 }
 
-// slot -> start of the k-mer's SA interval (k rank steps from the root); kNoGroup for empty slots
-__global__ void __launch_bounds__(kBlockH) ktable_lb_kernel(const HSlot * __restrict__ tab, const uint64_t n_slots, const DevIndex ix,
-                                                            const uint32_t k, uint32_t * __restrict__ slot_lb)
+// slot -> start of the k-mer's SA interval (k rank steps from the root); kNoGroup for free slots
+__global__ void __launch_bounds__(kBlockH) ktable_lb_kernel(const KTabView kt, const DevIndex ix, const uint32_t k, uint32_t * __restrict__ slot_lb)
 {
+    const uint64_t n_slots = 4ull * ((uint64_t)kt.nbmask + 1ull);
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
     {
-        const uint64_t key = tab[i].key;
+        const uint64_t w = kt.slots[i];
         uint32_t out = kNoGroup;
-        if (key != kKeyEmpty)
+        if (w != kSlotFree)
         {
+            const uint32_t d = (uint32_t)(w >> kt.rbits) & 7u;
+            const uint32_t home = ((uint32_t)(i >> 2) - d) & kt.nbmask;
+            const uint64_t h = ((uint64_t)home << kt.rbits) | (w & kt.rmask);
+            const uint64_t key = (h * kt.mul_inv) & kt.mask_b;
             uint32_t lb = 0u, rb = ix.n - 1u;
             bool ok = true;
             for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * j)) & 3u);
@@ -133,11 +148,12 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(unsigned long
 // ---------------------------------------------------------------------------------------------------------------
 // scan
 // ---------------------------------------------------------------------------------------------------------------
-enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_PROBE = 3, H_DONE = 4 };
+enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_DONE = 3 };
+constexpr int kWin = 4;     // windows per lane and loop trip: their probes are independent, so all loads are issued together
 
 template <int MODE>
-__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 4 : 6) scanh_kernel(const HSlot * __restrict__ tab, const uint32_t nb, unsigned long long * __restrict__ slot_mult,
-                                                           const BatchView b, const ScanArgs a, const int paired)
+__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : 3) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
+                                                                                  const BatchView b, const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
     constexpr bool RECORD = (MODE & M_RECORD) != 0;
@@ -150,6 +166,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 4 : 6) scanh_kerne
     const uint32_t sh = 2u * (k - 1u);
     const uint32_t units = (uint32_t)(paired ? b.n_reads / 2 : b.n_reads);
     const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t kmask = (kt.rmask << 3) | 7ull;
+    const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
 
     // lane state
     uint32_t phase = H_FETCH;
@@ -160,12 +178,28 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 4 : 6) scanh_kerne
     uint64_t key = 0ull;                         // the last k bases, base i of the window at bits [2i, 2i+2)
     uint32_t wlo = 0u, whi = 0u, winv = 0u;      // current 32-base group, base t in the low bits
     uint32_t nlo = 0u, nhi = 0u, ninv = 0u;      // the following group (prefetched)
-    uint32_t pb = 0u;                            // bucket being probed
     uint32_t gmin = kNoGroup, gmax = 0u, c_total = 0u;
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
+    // per-lane scalars (flushed at the end, or before they could wrap)
+    uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u;
     // warp-uniform chunk of claimed units
     uint32_t wcur = 0u, wend = 0u;
+
+    // one base: shift it into the k-mer, keep the count of valid bases, move the window registers on
+    auto roll = [&]() {
+        if ((t & 31u) == 0u && ((t >> 5) + 1u) * 32u < pend)
+        {
+            const uint64_t v = load_ro(b.bases + g0 + (t >> 5) + 1u);
+            nlo = (uint32_t)v; nhi = (uint32_t)(v >> 32);
+            ninv = load_ro(b.inv + g0 + (t >> 5) + 1u);
+        }
+        key = (key >> 2) | ((uint64_t)(wlo & 3u) << sh);
+        run = (winv & 1u) ? 0u : run + 1u;                        // N / low quality: no window may contain this base
+        t += 1u;
+        wlo = (wlo >> 2) | (whi << 30); whi >>= 2; winv >>= 1;
+        if ((t & 31u) == 0u) { wlo = nlo; whi = nhi; winv = ninv; }
+    };
 
     while (true)
     {
@@ -205,99 +239,118 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 4 : 6) scanh_kerne
                 }
             }
         }
-        if (ph != H_FETCH && ph != H_DONE)
+        if (ph == H_FIRST)
         {
-            // ---- loads of this iteration
-            uint32_t w[8];
-            bool look = false;
-            if (ph == H_FIRST)
+            const uint32_t L = pend;
+            pend = L >= k ? L : 0u;                               // L < k: the sliding view is empty (sliding.hpp:129-142)
+            n_look += L >= k ? L - k + 1u : 0u;
+            n_reads += 1u;
+            t = 0u; run = 0u; key = 0ull;
+            if (pend)
             {
-                const uint32_t L = pend;
-                pend = L >= k ? L : 0u;                           // L < k: the sliding view is empty (sliding.hpp:129-142)
-                env.count_fetch(L >= k ? L - k + 1u : 0u);
-                t = 0u; run = 0u; key = 0ull;
-                if (pend)
-                {
-                    const uint64_t v = load_ro(b.bases + g0);
-                    wlo = (uint32_t)v; whi = (uint32_t)(v >> 32);
-                    winv = load_ro(b.inv + g0);
-                }
-                phase = H_RUN;
+                const uint64_t v = load_ro(b.bases + g0);
+                wlo = (uint32_t)v; whi = (uint32_t)(v >> 32);
+                winv = load_ro(b.inv + g0);
             }
-            else if (ph == H_RUN)
+            phase = H_RUN;
+        }
+        else if (ph == H_RUN)
+        {
+            // ---- up to kWin windows: roll to each, issue every probe, then consume them in window order
+            while (run + 1u < k && t < pend) roll();              // start of a read / behind an N: no window is due yet
+            uint32_t w[kWin][8];
+            uint32_t pb[kWin], want_lo[kWin], want_hi[kWin];
+            bool due[kWin];
+            const uint32_t t0 = t;
+#pragma unroll
+            for (int j = 0; j < kWin; ++j)
             {
-                if ((t & 31u) == 0u && ((t >> 5) + 1u) * 32u < pend)
-                {
-                    const uint64_t v = load_ro(b.bases + g0 + (t >> 5) + 1u);
-                    nlo = (uint32_t)v; nhi = (uint32_t)(v >> 32);
-                    ninv = load_ro(b.inv + g0 + (t >> 5) + 1u);
-                }
+                due[j] = false;
                 if (t < pend)
                 {
-                    const uint32_t c = wlo & 3u;
-                    key = (key >> 2) | ((uint64_t)c << sh);
-                    run = (winv & 1u) ? 0u : run + 1u;            // N / low quality: no window may contain this base
-                    t += 1u;
-                    wlo = (wlo >> 2) | (whi << 30); whi >>= 2; winv >>= 1;
-                    if ((t & 31u) == 0u) { wlo = nlo; whi = nhi; winv = ninv; }
-                    if (run >= k)
-                    {
-                        c_total += 1u;                            // ++total_kmers (src/fm_scanner.cpp:164)
-                        pb = hbucket(key, nb);
-                        look = true;
-                    }
+                    roll();
+                    due[j] = run >= k;
+                }
+                if (due[j])
+                {
+                    const uint64_t h = (key * kt.mul) & kt.mask_b;
+                    pb[j] = (uint32_t)(h >> kt.rbits);
+                    const uint64_t want = h & kt.rmask;
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                 : "l"(kt.slots + 4ull * pb[j]));
                 }
             }
-            else if (ph == H_PROBE) look = true;
-            if (look)
+#pragma unroll
+            for (int j = 0; j < kWin; ++j)
             {
-                const uint32_t * p = reinterpret_cast<const uint32_t *>(tab + 2ull * pb);
-                asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                             : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p));
-                const uint64_t k0 = u64of(w[0], w[1]), k1 = u64of(w[4], w[5]);
-                const bool h0 = k0 == key, h1 = k1 == key;
-                if (h0 || h1)
+                if (!due[j]) continue;
+                c_total += 1u;                                    // ++total_kmers (src/fm_scanner.cpp:164)
+                uint32_t d = 0u;
+                while (true)
                 {
-                    const uint32_t g = h0 ? w[2] : w[6];
-                    if (RECORD) atomicAdd(slot_mult + 2ull * pb + (h0 ? 0u : 1u), 1ull);
-                    if (g != (uint32_t)kValMulti)
+                    const bool h0 = (((w[j][0] ^ want_lo[j]) & kmask_lo) | ((w[j][1] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    const bool h1 = (((w[j][2] ^ want_lo[j]) & kmask_lo) | ((w[j][3] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    const bool h2 = (((w[j][4] ^ want_lo[j]) & kmask_lo) | ((w[j][5] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    const bool h3 = (((w[j][6] ^ want_lo[j]) & kmask_lo) | ((w[j][7] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    if (h0 || h1 || h2 || h3)
                     {
-                        // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191)
-                        gmin = g < gmin ? g : gmin;
-                        gmax = g > gmax ? g : gmax;
-                        if (g != agg_g)
+                        const uint32_t g = (h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7]) >> 16;
+                        if (RECORD) atomicAdd(slot_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
+                        if (g != kValMulti)
                         {
-                            if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
-                            agg_g = g; agg_n = 0u; agg_w = 0.0;
+                            // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191)
+                            gmin = g < gmin ? g : gmin;
+                            gmax = g > gmax ? g : gmax;
+                            if (g != agg_g)
+                            {
+                                if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+                                agg_g = g; agg_n = 0u; agg_w = 0.0;
+                            }
+                            if (LOCAL) agg_w += env.weight(g0, t0 + (uint32_t)j + 1u, k);
+                            else agg_n += 1u;
                         }
-                        if (LOCAL) agg_w += env.weight(g0, t, k);
-                        else agg_n += 1u;
+                        break;
                     }
-                    phase = H_RUN;
-                }
-                else if (k0 == kKeyEmpty || k1 == kKeyEmpty) phase = H_RUN;      // the k-mer does not occur in the index
-                else
-                {
-                    pb = pb + 1u == nb ? 0u : pb + 1u;
-                    phase = H_PROBE;
+                    // a free last slot ends the probe sequence: the k-mer does not occur in the index
+                    if ((w[j][6] & w[j][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;
+                    // rare: the home bucket is full of other k-mers; the k-mer may sit in the next bucket
+                    d += 1u;
+                    pb[j] = (pb[j] + 1u) & kt.nbmask;
+                    const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kt.rbits);
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                 : "l"(kt.slots + 4ull * pb[j]));
                 }
             }
-            if (phase == H_RUN && t >= pend)
+        }
+        if (phase == H_RUN && t >= pend)
+        {
+            // the read is finished
+            if (paired && !mate2) mate2 = true;
+            else
             {
-                // the read is finished
-                if (paired && !mate2) mate2 = true;
-                else
+                // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
+                n_total += c_total;
+                n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
+                c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                mate2 = false;
+                if ((n_total | n_look) & 0x80000000u)
                 {
-                    // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
-                    env.count_unit(c_total, gmin != kNoGroup && gmin != gmax);
-                    c_total = 0u; gmin = kNoGroup; gmax = 0u;
-                    mate2 = false;
+                    env.add64(0, n_total); env.add64(2, n_look);
+                    n_total = 0u; n_look = 0u;
                 }
-                phase = H_FETCH;
             }
+            phase = H_FETCH;
         }
     }
     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+    if (n_total) env.add64(0, n_total);
+    if (n_amb) env.add64(1, n_amb);
+    if (n_look) env.add64(2, n_look);
+    if (n_reads) env.add64(3, n_reads);
     smem32_flush<LOCAL>(sm, a);
 }
 
@@ -342,23 +395,47 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     return cudaSuccess;
 }
 
-cudaError_t launch_scanh(const HSlot * tab, uint32_t n_buckets, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a,
-                         int mode, LaunchCfg cfg, cudaStream_t st)
+// Geometry of the table for `keys` distinct k-mers (an upper bound is fine): load factor in (0.2, 0.4], grown by `grow`
+// doublings; the remainder must fit below the displacement and value fields.
+bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
+{
+    const uint32_t B = 2u * k;
+    uint32_t q = 1u;
+    while (q < B && (1ull << q) * 8ull < keys * 5ull) ++q;       // 4 * 2^q * 0.4 >= keys
+    q = std::min(B, q + grow);
+    if (B > 45u && q < B - 45u) q = B - 45u;
+    if (q > 31u) return false;
+    kt->q = q;
+    kt->rbits = B - q;
+    kt->nbmask = (1u << q) - 1u;
+    kt->mask_b = B == 64u ? ~0ull : (1ull << B) - 1ull;
+    kt->rmask = kt->rbits == 0u ? 0ull : (1ull << kt->rbits) - 1ull;
+    kt->mul = 0x9E3779B97F4A7C15ull;
+    uint64_t x = kt->mul;                                         // Newton: the inverse mod 2^64 (and so mod 2^B)
+    for (int i = 0; i < 6; ++i) x *= 2ull - kt->mul * x;
+    kt->mul_inv = x;
+    return true;
+}
+
+cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
+                         LaunchCfg cfg, cudaStream_t st)
 {
     const size_t smem = scan32_smem_bytes(a.V);
     const int paired = (mode & M_PAIRED) ? 1 : 0;
     const int m = mode & (M_LOCAL | M_RECORD);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
-    SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(tab, n_buckets, slot_mult, b, a, paired)))
+    SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, slot_mult, b, a, paired)))
     return cudaGetLastError();
 }
 
+// n_keys: two u64 -- [0] distinct k-mers stored, [1] set when a k-mer could not be placed within kMaxDisp buckets
 cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
-                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, HSlot * tab, uint32_t n_buckets, uint32_t k,
+                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
                                 unsigned long long * n_keys, cudaStream_t st)
 {
-    cudaError_t e = cudaMemsetAsync(tab, 0xFF, (size_t)n_buckets * 2 * sizeof(HSlot), st);
+    cudaError_t e = cudaMemsetAsync(kt.slots, 0xFF, ((size_t)kt.nbmask + 1) * 32, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(n_keys, 0, 16, st);
     if (e != cudaSuccess) return e;
     if (n_texts == 0 || max_len < k) return cudaSuccess;
     const uint32_t groups = (max_len + 31u) / 32u;
@@ -367,14 +444,14 @@ cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv
     for (uint32_t t0 = 0; t0 < n_texts; t0 += 65535u)
     {
         const uint32_t nt = std::min<uint32_t>(65535u, n_texts - t0);
-        ktable_build_kernel<<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, t_group + t0, tab, n_buckets, k, n_keys);
+        ktable_build_kernel<<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, t_group + t0, kt, k, n_keys);
     }
     return cudaGetLastError();
 }
 
-cudaError_t launch_ktable_lb(const HSlot * tab, uint64_t n_slots, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st)
+cudaError_t launch_ktable_lb(KTabView const & kt, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st)
 {
-    ktable_lb_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(tab, n_slots, ix, k, slot_lb);
+    ktable_lb_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt, ix, k, slot_lb);
     return cudaGetLastError();
 }
 
