@@ -177,6 +177,17 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# independent random 32-byte sector loads, G sectors/s, by table size (profiles/r1_gather_probe.txt, measured on this pool)
+RANDOM_SECTOR_PEAKS = [
+    (0.12e9, 235.8, "L2-resident table (0.1 GB probe)"),
+    (0.4e9, 72.4, "0.3 GB table probe"),
+    (0.8e9, 48.7, "0.5 GB table probe"),
+    (1.6e9, 42.7, "1.1 GB table probe"),
+    (3.2e9, 39.6, "2.1 GB table probe"),
+    (float("inf"), 37.9, "4.3 GB table probe"),
+]
+
+
 def measured_peak() -> tuple[float, str]:
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -213,7 +224,8 @@ def main() -> None:
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--algorithm", default="rolling", choices=["rolling", "direct", "ktable", "auto"])
+    ap.add_argument("--algorithm", default="auto", choices=["auto", "ktable", "rolling", "direct"],
+                    help="auto = the library's default: k-mer table scan for k <= 31, else the rolling FM search")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -450,6 +462,15 @@ def main() -> None:
         # the packed input stream; against the HBM peak when the structure misses L2, else informative only
         own = (32 * int(tall[V]) // world if algo == capi.ALGO_KTABLE else 64 * R * L) + packed_bytes
         roof["own_sectors"] = {"bytes_per_launch": own, "GB/s": own / (kern_ms * 1e-3) / 1e9, "frac_of_hbm_peak": own / (kern_ms * 1e-3) / 1e9 / peak}
+        # the roofline this access pattern really has: independent random 32-byte sectors.  Peaks measured on this pool's B200
+        # by profiles/gather_probe.cu (profiles/r1_gather_probe.txt), chosen by the size of the structure the kernel probes.
+        info = scan.info()
+        sb = info["structure_bytes"]
+        ra_peak, ra_src = next((p_, s_) for lim, p_, s_ in RANDOM_SECTOR_PEAKS if sb <= lim)
+        sectors = (int(tall[V]) // world) if algo == capi.ALGO_KTABLE else 2 * R * L
+        roof["random_access"] = {"sectors_per_launch": sectors, "achieved_Gsectors_per_s": sectors / (kern_ms * 1e-3) / 1e9,
+                                 "peak_Gsectors_per_s": ra_peak, "frac": sectors / (kern_ms * 1e-3) / 1e9 / ra_peak,
+                                 "structure_bytes": sb, "keys": info["keys"], "peak_source": ra_src}
 
     # ---- cpu baseline (rank 0, N = 1 only) ----
     cpu = None

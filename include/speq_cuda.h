@@ -168,6 +168,9 @@ int speqg_scan_reset(speqg_scan * scan);
 /* Reference-semantics work counters for one device batch (every window searched from the root with no jump table,
  * N searched as a symbol, stop at the first empty interval).  Not part of the product path; used for the roofline. */
 int speqg_scan_stats(speqg_scan * scan, const speqg_batch * device_batch, speqg_counts * counts);
+/* What the handle resolved SPEQG_ALGO_AUTO to, and the size of its per-(index, k) structure: the k-mer table
+ * (algorithm == SPEQG_ALGO_KTABLE: bytes, distinct k-mers stored) or the rank blocks of the rolling search (keys = 0). */
+int speqg_scan_info(speqg_scan * scan, uint32_t * algorithm, uint64_t * structure_bytes, uint64_t * keys);
 void speqg_scan_close(speqg_scan * scan);
 
 /* page-locked host memory for read batches (replaces the heap vectors seqan3's record buffer holds,

@@ -498,6 +498,21 @@ int speqg_scan_stats(speqg_scan * s, const speqg_batch * db, speqg_counts * coun
     SPEQG_CATCH
 }
 
+int speqg_scan_info(speqg_scan * s, uint32_t * algorithm, uint64_t * structure_bytes, uint64_t * keys)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    if (algorithm) *algorithm = s->algo;
+    if (structure_bytes)
+    {
+        if (s->algo == SPEQG_ALGO_KTABLE) *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1);
+        else if (s->algo == SPEQG_ALGO_ROLLING) *structure_bytes = sizeof(FBlock) * (s->idx->host.n / 32 + 1);
+        else *structure_bytes = sizeof(KBlock) * s->idx->host.blocks.size();
+    }
+    if (keys) *keys = s->algo == SPEQG_ALGO_KTABLE ? s->ktab_keys : 0;
+    SPEQG_CATCH
+}
+
 void speqg_scan_close(speqg_scan * s)
 {
     if (!s) return;

@@ -103,7 +103,7 @@ def scan_reads(scan: engine.Scan, reads: Reads, lo: int, hi: int, *, paired: boo
 
 def run_all(scaffolds: list[np.ndarray], group_scaffolds, group_counts, reads: Reads, *, k: int, phred_cutoff: int = 30,
             fixed_accuracy: float = 0.0, precision: float = 1e-6, paired: bool = False, device: int = 0,
-            group=None, reduce_device=None, algorithm: int = capi.ALGO_ROLLING, raw: bool = True,
+            group=None, reduce_device=None, algorithm: int = capi.ALGO_AUTO, raw: bool = True,
             batch_reads: int = 1 << 20, refine: bool = True, max_iters: int = 100000, index: engine.Index | None = None) -> dict:
     """scaffolds: dna5-rank arrays in FASTA order.  Returns the same keys the oracle's `run` mode prints."""
     V = len(group_counts)

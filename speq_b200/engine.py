@@ -197,7 +197,7 @@ class ScanResult:
 
 class Scan:
     def __init__(self, index: Index, *, k: int, phred_cutoff: int = 30, mode: int = capi.MODE_GLOBAL, paired: bool = False,
-                 record: bool = False, algorithm: int = capi.ALGO_ROLLING, device: int = 0, stream: int | None = None):
+                 record: bool = False, algorithm: int = capi.ALGO_AUTO, device: int = 0, stream: int | None = None):
         self.index = index
         self.V = index.n_groups
         self.mode = mode
@@ -233,6 +233,12 @@ class Scan:
         capi.check(capi.lib().speqg_scan_stats(self.h, C.byref(b.s), C.byref(c)))
         return {"lookups": int(c.lookups), "reads": int(c.reads), "steps_executed": int(c.steps_executed),
                 "kmers_hit": int(c.kmers_hit), "occ": int(c.occurrences), "occ_sectors": int(c.occ_sectors)}
+
+    def info(self) -> dict:
+        """Resolved algorithm (AUTO -> KTABLE / ROLLING) and the size of the per-(index, k) structure it scans."""
+        a, nb, nk = C.c_uint32(), C.c_uint64(), C.c_uint64()
+        capi.check(capi.lib().speqg_scan_info(self.h, C.byref(a), C.byref(nb), C.byref(nk)))
+        return {"algorithm": int(a.value), "structure_bytes": int(nb.value), "keys": int(nk.value)}
 
     def refine(self, percent: np.ndarray, group_counts: np.ndarray) -> np.ndarray:
         p = np.ascontiguousarray(percent, np.float64)

@@ -395,7 +395,7 @@ int do_scan(cmd_arguments & args)
     prm.mode = local ? SPEQG_MODE_LOCAL : SPEQG_MODE_GLOBAL;
     prm.paired = paired ? 1 : 0;
     prm.record_multiplicity = 1;
-    prm.algorithm = SPEQG_ALGO_ROLLING;
+    prm.algorithm = SPEQG_ALGO_AUTO;   // k <= 31: k-mer table scan; else the rolling FM search
     uint64_t cap_reads = std::max<uint64_t>(2, args.batch_reads & ~1u);
     uint64_t cap_bytes = std::min<uint64_t>(cap_reads * 320, uint64_t(512) << 20);
     for (unsigned d = 0; d < gpus; ++d)

@@ -41,11 +41,13 @@ def _compare(out: dict, exp: dict, V: int):
 @pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
 @pytest.mark.parametrize("raw", [True, False])
 def test_golden(lib, name, raw):
+    """The rolling FM search (the path for every k) against the fixtures."""
     fx = helpers.load_golden(name)
     exp, run = fx["expected"], fx["run"]
     scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
     out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
-                         fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], raw=raw, batch_reads=64)
+                         fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], raw=raw, batch_reads=64,
+                         algorithm=capi.ALGO_ROLLING)
     _compare(out, exp, len(counts))
 
 
@@ -198,9 +200,11 @@ def test_properties_at_config_shapes(lib, cfg, R):
     assert a.unique.sum() > 0
     c = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
     assert np.array_equal(a.unique, c.unique) and a.total_kmers == c.total_kmers and a.ambiguous == c.ambiguous
-    d = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_KTABLE)
-    assert np.array_equal(a.unique, d.unique) and a.total_kmers == d.total_kmers and a.ambiguous == d.ambiguous
-    assert d.lookups == a.lookups and d.reads == a.reads
+    # a ran the default (AUTO: the k-mer table for k <= 31); the rolling FM search and the explicit table must agree
+    for alg in (capi.ALGO_ROLLING, capi.ALGO_KTABLE):
+        d = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=alg)
+        assert np.array_equal(a.unique, d.unique) and a.total_kmers == d.total_kmers and a.ambiguous == d.ambiguous
+        assert d.lookups == a.lookups and d.reads == a.reads
     h = R // 2
     p1 = _scan_tallies(idx, sh.k, seq, qual, offs[:h + 1])
     p2 = _scan_tallies(idx, sh.k, seq, qual, offs[h:])
@@ -211,7 +215,7 @@ def test_properties_at_config_shapes(lib, cfg, R):
     sh0 = dataclasses.replace(sh, e=0.0)
     n0 = max(64, R // 8)
     s0, q0 = synth.make_reads(sh0, refs, n0, 78)
-    sc = engine.Scan(idx, k=sh.k, record=True)
+    sc = engine.Scan(idx, k=sh.k, record=True, algorithm=capi.ALGO_ROLLING)
     sc.submit_raw(s0.cpu().numpy().reshape(-1), q0.cpu().numpy().reshape(-1), np.arange(n0 + 1, dtype=np.uint64) * sh.L, n0)
     r0 = sc.finish()
     assert r0.total_kmers == r0.lookups == n0 * sh.windows_per_read
@@ -274,7 +278,44 @@ def test_many_variants_u16_groups(lib):
     b = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_DIRECT)
     c = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
     d = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_KTABLE)
+    e = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_ROLLING)
     assert a.unique.sum() > 0
-    for o in (b, c, d):
+    for o in (b, c, d, e):
         assert np.array_equal(a.unique, o.unique) and a.total_kmers == o.total_kmers and a.ambiguous == o.ambiguous
+    idx.close()
+
+
+@pytest.mark.parametrize("k", [1, 2, 16, 24, 31])
+def test_ktable_k_range(lib, k):
+    """The k-mer table at the ends of its k range (k = 31 stores 45 remainder bits in a table of >= 2^17 buckets; k = 1, 2
+    have fewer k-mers than one bucket has slots) against the rolling FM search and the from-the-root search, with Ns in
+    the references and in the reads, in single and paired mode."""
+    rng = np.random.default_rng(100 + k)
+    V, G = 4, 3000
+    anc = rng.integers(0, 4, G)
+    scaff = []
+    for v in range(V):
+        s = anc.copy()
+        pos = rng.integers(0, G, 60)
+        s[pos] = rng.integers(0, 4, 60)
+        s = np.where(s == 3, 4, s).astype(np.uint8)              # dna5 ranks: A0 C1 G2 N3 T4
+        s[rng.integers(0, G, 3)] = 3
+        scaff.append(s)
+    idx = engine.Index.from_scaffolds(scaff, list(range(V)), V)
+    R, L = 4000, 100
+    src, st = rng.integers(0, V, R), rng.integers(0, G - L, R)
+    letters = np.frombuffer(b"ACGNT", np.uint8)
+    seq = np.concatenate([letters[scaff[int(v)][int(p):int(p) + L]] for v, p in zip(src, st)])
+    flip = rng.random(seq.size) < 0.01
+    seq[flip] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(flip.sum()))]
+    qual = np.where(rng.random(seq.size) < 0.01, ord("#"), ord("I")).astype(np.uint8)
+    offs = np.arange(R + 1, dtype=np.uint64) * L
+    for paired in (False, True):
+        a = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_KTABLE, paired=paired)
+        b = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_ROLLING, paired=paired)
+        c = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_DIRECT, paired=paired)
+        assert a.total_kmers > 0
+        for o in (b, c):
+            assert np.array_equal(a.unique, o.unique) and a.total_kmers == o.total_kmers and a.ambiguous == o.ambiguous
+            assert a.lookups == o.lookups
     idx.close()
