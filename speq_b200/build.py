@@ -50,7 +50,7 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
         obj = OBJ_DIR / (src + ".o")
         if not force and not _stale(obj, [CSRC / src] + headers):
             return obj
-        cmd = [nvcc(), *NVCC_FLAGS, "-c", str(CSRC / src), "-o", str(obj)]
+        cmd = [nvcc(), *NVCC_FLAGS, *os.environ.get("SPEQB_NVCC_EXTRA", "").split(), "-c", str(CSRC / src), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

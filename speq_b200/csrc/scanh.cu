@@ -149,10 +149,17 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(unsigned long
 // scan
 // ---------------------------------------------------------------------------------------------------------------
 enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_DONE = 3 };
-constexpr int kWin = 4;     // windows per lane and loop trip: their probes are independent, so all loads are issued together
+// windows per lane and loop trip (their probes are independent, so all loads are issued together) and resident CTAs per SM
+#ifndef SPEQB_KWIN
+#define SPEQB_KWIN 2
+#endif
+#ifndef SPEQB_HMINB
+#define SPEQB_HMINB 4
+#endif
+constexpr int kWin = SPEQB_KWIN;
 
 template <int MODE>
-__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : 3) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
+__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
                                                                                   const BatchView b, const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;

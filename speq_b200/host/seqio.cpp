@@ -1,11 +1,16 @@
 #include "seqio.h"
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
 #include <algorithm>
 #include <cctype>
 #include <cstring>
 #include <stdexcept>
+#include <thread>
 
 namespace speq::io
 {
@@ -22,7 +27,7 @@ bool has_ext(std::string const & name, std::initializer_list<const char *> exts)
 }
 }   // namespace
 
-sequence_reader::sequence_reader(std::filesystem::path const & p) : buf_(1 << 20), path_(p.string())
+sequence_reader::sequence_reader(std::filesystem::path const & p, uint64_t start_offset) : buf_(1 << 20), path_(p.string())
 {
     std::string name = p.filename().string();
     std::transform(name.begin(), name.end(), name.begin(), [](unsigned char c) { return std::tolower(c); });
@@ -33,6 +38,8 @@ sequence_reader::sequence_reader(std::filesystem::path const & p) : buf_(1 << 20
     gz_ = gzopen(path_.c_str(), "rb");   // zlib reads plain files transparently
     if (!gz_) throw std::runtime_error("Could not open file " + path_ + " for reading.");
     gzbuffer(static_cast<gzFile>(gz_), 1 << 20);
+    if (start_offset && gzseek(static_cast<gzFile>(gz_), static_cast<z_off_t>(start_offset), SEEK_SET) < 0)
+        throw std::runtime_error("Could not seek in " + path_);
 }
 
 sequence_reader::~sequence_reader()
@@ -109,6 +116,165 @@ bool sequence_reader::next(std::string & seq, std::string & qual)
         qual.assign(seq.size(), 'J');
     }
     return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// parallel FASTQ
+// ---------------------------------------------------------------------------------------------------------------
+bool fastq_map::eligible(std::filesystem::path const & p)
+{
+    std::string name = p.filename().string();
+    std::transform(name.begin(), name.end(), name.begin(), [](unsigned char c) { return std::tolower(c); });
+    if (!has_ext(name, {".fq", ".fastq"})) return false;
+    // a gzip stream under a plain name is still handled by zlib in the serial reader
+    FILE * f = fopen(p.c_str(), "rb");
+    if (!f) return false;
+    unsigned char m[2] = {0, 0};
+    size_t got = fread(m, 1, 2, f);
+    fclose(f);
+    return !(got == 2 && m[0] == 0x1f && m[1] == 0x8b);
+}
+
+fastq_map::fastq_map(std::filesystem::path const & p)
+{
+    fd_ = open(p.c_str(), O_RDONLY);
+    if (fd_ < 0) throw std::runtime_error("Could not open file " + p.string() + " for reading.");
+    struct stat st;
+    if (fstat(fd_, &st) != 0) { close(fd_); throw std::runtime_error("Could not stat " + p.string()); }
+    size_ = static_cast<uint64_t>(st.st_size);
+    if (size_)
+    {
+        void * m = mmap(nullptr, size_, PROT_READ, MAP_PRIVATE, fd_, 0);
+        if (m == MAP_FAILED) { close(fd_); throw std::runtime_error("Could not map " + p.string()); }
+        madvise(m, size_, MADV_SEQUENTIAL);
+        data_ = static_cast<const char *>(m);
+    }
+}
+
+fastq_map::~fastq_map()
+{
+    if (data_) munmap(const_cast<char *>(data_), size_);
+    if (fd_ >= 0) close(fd_);
+}
+
+namespace
+{
+// end of the line that starts at p (position of '\n', or size when the last line is unterminated)
+inline uint64_t line_end(const char * d, uint64_t size, uint64_t p)
+{
+    const void * nl = memchr(d + p, '\n', size - p);
+    return nl ? static_cast<uint64_t>(static_cast<const char *>(nl) - d) : size;
+}
+}   // namespace
+
+uint64_t fastq_map::find_start(uint64_t p) const
+{
+    if (p == 0) return 0;
+    // first line start at or after p
+    uint64_t q = data_[p - 1] == '\n' ? p : line_end(data_, size_, p) + 1;
+    while (q < size_)
+    {
+        uint64_t e0 = line_end(data_, size_, q);
+        if (data_[q] == '@' && e0 < size_)
+        {
+            uint64_t e1 = line_end(data_, size_, e0 + 1);
+            if (e1 < size_ && e1 + 1 < size_ && data_[e1 + 1] == '+') return q;
+        }
+        q = e0 + 1;
+    }
+    return size_;
+}
+
+bool fastq_map::index(uint64_t pos, uint64_t max_bytes, int threads, std::vector<fq_rec> & out) const
+{
+    out.clear();
+    if (pos >= size_) return true;
+    const uint64_t end = std::min(size_, pos + max_bytes);
+    threads = std::max(1, threads);
+    // piece boundaries at record starts
+    std::vector<uint64_t> cut(static_cast<size_t>(threads) + 1);
+    cut[0] = pos;
+    for (int i = 1; i < threads; ++i)
+    {
+        uint64_t want = pos + (end - pos) / static_cast<uint64_t>(threads) * static_cast<uint64_t>(i);
+        cut[static_cast<size_t>(i)] = std::max(cut[static_cast<size_t>(i) - 1], find_start(want));
+    }
+    cut[static_cast<size_t>(threads)] = end == size_ ? size_ : std::max(cut[static_cast<size_t>(threads) - 1], find_start(end));
+    std::vector<std::vector<fq_rec>> part(static_cast<size_t>(threads));
+    std::vector<char> bad(static_cast<size_t>(threads), 0);
+    auto work = [&](int ti)
+    {
+        const char * d = data_;
+        uint64_t p = cut[static_cast<size_t>(ti)], stop = cut[static_cast<size_t>(ti) + 1];
+        auto & v = part[static_cast<size_t>(ti)];
+        v.reserve((stop - p) / 200 + 16);
+        while (p < stop)
+        {
+            if (d[p] == '\n') { ++p; continue; }                 // blank line between records
+            if (d[p] == '\r' && p + 1 < size_ && d[p + 1] == '\n') { p += 2; continue; }
+            fq_rec r;
+            r.start = p;
+            if (d[p] != '@') { bad[static_cast<size_t>(ti)] = 1; return; }
+            uint64_t e0 = line_end(d, size_, p);
+            if (e0 >= size_) { bad[static_cast<size_t>(ti)] = 1; return; }
+            r.seq = e0 + 1;
+            uint64_t e1 = line_end(d, size_, r.seq);
+            if (e1 >= size_ || e1 + 1 >= size_ || d[e1 + 1] != '+') { bad[static_cast<size_t>(ti)] = 1; return; }
+            uint64_t e2 = line_end(d, size_, e1 + 1);
+            if (e2 >= size_) { bad[static_cast<size_t>(ti)] = 1; return; }
+            r.qual = e2 + 1;
+            uint64_t e3 = line_end(d, size_, r.qual);
+            uint64_t ls = e1 - r.seq, lq = e3 - r.qual;
+            if (ls && d[e1 - 1] == '\r') --ls;
+            if (lq && e3 > r.qual && d[e3 - 1] == '\r') --lq;
+            // the strict form: equal lengths, no blanks inside the sequence or quality line
+            if (ls != lq || ls > 0xFFFFFFFFull || memchr(d + r.seq, ' ', ls) || memchr(d + r.seq, '\t', ls) ||
+                memchr(d + r.qual, ' ', lq) || memchr(d + r.qual, '\t', lq))
+            {
+                bad[static_cast<size_t>(ti)] = 1;
+                return;
+            }
+            r.len = static_cast<uint32_t>(ls);
+            r.next = std::min(size_, e3 + 1);
+            v.push_back(r);
+            p = r.next;
+        }
+    };
+    if (threads == 1) work(0);
+    else
+    {
+        std::vector<std::thread> th;
+        for (int i = 0; i < threads; ++i) th.emplace_back(work, i);
+        for (auto & t : th) t.join();
+    }
+    for (int i = 0; i < threads; ++i)
+    {
+        auto & v = part[static_cast<size_t>(i)];
+        out.insert(out.end(), v.begin(), v.end());
+        if (bad[static_cast<size_t>(i)]) return false;             // records of later pieces are dropped: the caller resumes serially
+    }
+    return true;
+}
+
+void copy_records(const char * data, std::vector<fq_rec> const & recs, uint64_t n, uint8_t * seq, uint8_t * qual,
+                  uint64_t const * offsets, uint64_t stride, uint64_t slot, int threads)
+{
+    threads = std::max(1, threads);
+    auto work = [&](int ti)
+    {
+        uint64_t a = n * static_cast<uint64_t>(ti) / static_cast<uint64_t>(threads), b = n * (static_cast<uint64_t>(ti) + 1) / static_cast<uint64_t>(threads);
+        for (uint64_t i = a; i < b; ++i)
+        {
+            fq_rec const & r = recs[i];
+            uint64_t o = offsets[i * stride + slot];
+            memcpy(seq + o, data + r.seq, r.len);
+            memcpy(qual + o, data + r.qual, r.len);
+        }
+    };
+    if (threads == 1 || n < 4096) { for (int i = 0; i < threads; ++i) work(i); return; }
+    std::vector<std::thread> th;
+    for (int i = 0; i < threads; ++i) th.emplace_back(work, i);
+    for (auto & t : th) t.join();
 }
 
 std::vector<std::vector<uint8_t>> read_reference_ranks(std::filesystem::path const & p)

@@ -25,7 +25,8 @@ struct read_batch
 class sequence_reader
 {
 public:
-    explicit sequence_reader(std::filesystem::path const & p);
+    // start_offset: byte offset of a record start (plain files; used when the parallel FASTQ indexer hands over)
+    explicit sequence_reader(std::filesystem::path const & p, uint64_t start_offset = 0);
     ~sequence_reader();
     sequence_reader(sequence_reader const &) = delete;
     // next record: returns false at end of file.  qual is filled with 'J' (phred 41) for FASTA records.
@@ -41,6 +42,47 @@ private:
     std::string peek_;
     std::string path_;
 };
+
+// ---- parallel ingest of plain (uncompressed) FASTQ in the strict 4-line form -------------------------------------
+// The file is mapped; a region is cut into one piece per thread at record starts (a line that begins with '@' whose
+// second successor begins with '+' -- a quality line can begin with '@', but then that line is a sequence line and
+// cannot begin with '+'), every piece is indexed independently (memchr per line), and the records are then copied into
+// the caller's pinned batch by the same threads.  Anything that is not the strict form (multi-line records, blanks
+// inside a sequence line, length mismatch) stops the indexer in front of that record: the caller continues with the
+// serial sequence_reader from that offset, which implements the full seqan3 grammar.
+struct fq_rec
+{
+    uint64_t start;   // file offset of the '@'
+    uint64_t seq;     // file offset of the sequence line
+    uint64_t qual;    // file offset of the quality line
+    uint64_t next;    // file offset of the following record
+    uint32_t len;
+};
+
+class fastq_map
+{
+public:
+    static bool eligible(std::filesystem::path const & p);     // .fq / .fastq, not compressed
+    explicit fastq_map(std::filesystem::path const & p);
+    ~fastq_map();
+    fastq_map(fastq_map const &) = delete;
+    // index records starting at `pos` (a record start) within about max_bytes; returns false when one is irregular
+    // (out then holds the regular records before it).  out[i].next of the last record is where to go on.
+    bool index(uint64_t pos, uint64_t max_bytes, int threads, std::vector<fq_rec> & out) const;
+    const char * data() const { return data_; }
+    uint64_t size() const { return size_; }
+
+private:
+    uint64_t find_start(uint64_t p) const;
+    const char * data_ = nullptr;
+    uint64_t size_ = 0;
+    int fd_ = -1;
+};
+
+// copy records [r0, r1) of `recs` (step `stride`, slot offset `slot`: mates of a pair interleave with stride 2) into the
+// flat arrays; dst offsets come from `offsets` (already filled for every slot)
+void copy_records(const char * data, std::vector<fq_rec> const & recs, uint64_t n, uint8_t * seq, uint8_t * qual,
+                  uint64_t const * offsets, uint64_t stride, uint64_t slot, int threads);
 
 // whole FASTA file -> dna5 rank arrays (A0 C1 G2 N3 T4), one per record (the reference index input)
 std::vector<std::vector<uint8_t>> read_reference_ranks(std::filesystem::path const & p);

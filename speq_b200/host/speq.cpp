@@ -240,12 +240,8 @@ struct scan_out
 scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, uint32_t V, bool paired)
 {
     auto t0 = std::chrono::steady_clock::now();
-    speq::io::sequence_reader r1(args.in_file_reads_path_1);
-    std::unique_ptr<speq::io::sequence_reader> r2;
-    if (paired) r2 = std::make_unique<speq::io::sequence_reader>(args.in_file_reads_path_2);
     const uint64_t per = paired ? 2 : 1;
     size_t dev = 0;
-    std::string s1, q1, s2, q2;
     auto flush = [&](device_lane & L)
     {
         host_batch & b = L.buf[L.cur];
@@ -255,6 +251,66 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
         ck(speqg_scan_wait_copies(L.scan), "speqg_scan_wait_copies");   // the other buffer's copy (submitted earlier) is done
         L.buf[L.cur].clear();
     };
+    // ---- plain 4-line FASTQ: mapped file, indexed and copied into the pinned batches by the parser pool (-t); anything
+    //      irregular hands over to the serial reader (full seqan3 grammar) at the offset of the first irregular record
+    uint64_t off1 = 0, off2 = 0;
+    bool serial = true;
+    if (speq::io::fastq_map::eligible(args.in_file_reads_path_1) && (!paired || speq::io::fastq_map::eligible(args.in_file_reads_path_2)))
+    {
+        serial = false;
+        const int T = std::max(1, static_cast<int>(args.threads) - 1);
+        speq::io::fastq_map m1(args.in_file_reads_path_1);
+        std::unique_ptr<speq::io::fastq_map> m2;
+        if (paired) m2 = std::make_unique<speq::io::fastq_map>(args.in_file_reads_path_2);
+        std::vector<speq::io::fq_rec> v1, v2;
+        while (off1 < m1.size() && (!paired || off2 < m2->size()))
+        {
+            device_lane & L = lanes[dev];
+            host_batch & b = L.buf[L.cur];
+            // a region whose sequence bytes fit the batch: sequence <= half of the record bytes
+            const uint64_t region = b.cap_bytes / per;
+            bool ok = m1.index(off1, region, T, v1);
+            if (paired) ok = m2->index(off2, region, T, v2) && ok;
+            uint64_t n = paired ? std::min(v1.size(), v2.size()) : v1.size();
+            n = std::min<uint64_t>(n, b.cap_reads / per);
+            uint64_t bytes = 0, m = 0;
+            for (; m < n; ++m)
+            {
+                uint64_t add = v1[m].len + (paired ? v2[m].len : 0u);
+                if (bytes + add > b.cap_bytes) break;
+                b.offsets[per * m] = bytes;
+                if (paired) b.offsets[per * m + 1] = bytes + v1[m].len;
+                bytes += add;
+            }
+            n = m;
+            if (n == 0)
+            {
+                serial = true;            // an irregular (or oversized) record is next: the serial reader takes over
+                break;
+            }
+            b.offsets[per * n] = bytes;
+            speq::io::copy_records(m1.data(), v1, n, b.seq, b.qual, b.offsets, per, 0, T);
+            if (paired) speq::io::copy_records(m2->data(), v2, n, b.seq, b.qual, b.offsets, per, 1, T);
+            b.n_reads = per * n;
+            b.n_bytes = bytes;
+            off1 = v1[n - 1].next;
+            if (paired) off2 = v2[n - 1].next;
+            flush(L);
+            dev = (dev + 1) % lanes.size();
+            if (!ok && n == (paired ? std::min(v1.size(), v2.size()) : v1.size()))
+            {
+                serial = true;
+                break;
+            }
+        }
+        if (serial && (off1 >= m1.size() || (paired && off2 >= m2->size()))) serial = false;   // nothing left
+    }
+    if (serial)
+    {
+    speq::io::sequence_reader r1(args.in_file_reads_path_1, off1);
+    std::unique_ptr<speq::io::sequence_reader> r2;
+    if (paired) r2 = std::make_unique<speq::io::sequence_reader>(args.in_file_reads_path_2, off2);
+    std::string s1, q1, s2, q2;
     while (r1.next(s1, q1))
     {
         if (paired && !r2->next(s2, q2)) break;   // views::zip stops at the shorter file (src/fm_scanner.cpp:651)
@@ -277,6 +333,7 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
         }
         L->buf[L->cur].push(s1, q1);
         if (paired) L->buf[L->cur].push(s2, q2);
+    }
     }
     for (auto & L : lanes) flush(L);
     scan_out out;
@@ -466,8 +523,67 @@ int do_scan(cmd_arguments & args)
 }
 }   // namespace
 
+// `speq ingest-check <reads.fq> [threads]`: host-only self-check of the parallel FASTQ indexer against the serial reader
+// (reads, bases, FNV-1a of all sequence and quality bytes in record order).  Not a reference sub-command.
+int ingest_check(int argc, char ** argv)
+{
+    if (argc < 3) { std::cerr << "usage: speq ingest-check <reads.fq> [threads] [region_bytes]\n"; return 2; }
+    fs::path p = argv[2];
+    int T = argc > 3 ? std::max(1, atoi(argv[3])) : 4;
+    uint64_t region = argc > 4 ? strtoull(argv[4], nullptr, 10) : (uint64_t(8) << 20);
+    auto fnv = [](uint64_t h, const char * d, size_t n) { for (size_t i = 0; i < n; ++i) { h ^= static_cast<unsigned char>(d[i]); h *= 1099511628211ull; } return h; };
+    uint64_t n_ser = 0, b_ser = 0, h_ser = 1469598103934665603ull;
+    auto c0 = std::chrono::steady_clock::now();
+    {
+        speq::io::sequence_reader rd(p);
+        std::string s, q;
+        while (rd.next(s, q)) { ++n_ser; b_ser += s.size(); h_ser = fnv(fnv(h_ser, s.data(), s.size()), q.data(), q.size()); }
+    }
+    auto c1 = std::chrono::steady_clock::now();
+    double t_copy = 0;
+    uint64_t n_par = 0, b_par = 0, h_par = 1469598103934665603ull, off = 0, handed = 0;
+    if (speq::io::fastq_map::eligible(p))
+    {
+        speq::io::fastq_map m(p);
+        std::vector<speq::io::fq_rec> v;
+        bool ok = true;
+        while (ok && off < m.size())
+        {
+            auto k0 = std::chrono::steady_clock::now();
+            ok = m.index(off, region, T, v);
+            if (v.empty()) { ok = false; break; }
+            std::vector<uint64_t> offs(v.size() + 1, 0);
+            for (size_t i = 0; i < v.size(); ++i) offs[i + 1] = offs[i] + v[i].len;
+            std::vector<uint8_t> sq(offs.back() + 1), ql(offs.back() + 1);
+            speq::io::copy_records(m.data(), v, v.size(), sq.data(), ql.data(), offs.data(), 1, 0, T);
+            t_copy += std::chrono::duration<double>(std::chrono::steady_clock::now() - k0).count();
+            for (size_t i = 0; i < v.size(); ++i)
+                h_par = fnv(fnv(h_par, reinterpret_cast<const char *>(sq.data()) + offs[i], v[i].len), reinterpret_cast<const char *>(ql.data()) + offs[i], v[i].len);
+            n_par += v.size(); b_par += offs.back();
+            off = v.back().next;
+        }
+        if (!ok && off < m.size())
+        {
+            handed = off;
+            speq::io::sequence_reader rd(p, off);
+            std::string s, q;
+            while (rd.next(s, q)) { ++n_par; b_par += s.size(); h_par = fnv(fnv(h_par, s.data(), s.size()), q.data(), q.size()); }
+        }
+    }
+    std::cerr << "serial reader " << std::chrono::duration<double>(c1 - c0).count() << " s (incl. hashing); parallel index + copy "
+              << t_copy << " s with " << T << " threads\n";
+    std::cout << "serial " << n_ser << " " << b_ser << " " << h_ser << "\nparallel " << n_par << " " << b_par << " " << h_par
+              << " handover " << handed << "\n";
+    return (n_ser == n_par && b_ser == b_par && h_ser == h_par) ? 0 : 1;
+}
+
 int main(int argc, char ** argv)
 {
+    if (argc > 1 && std::string(argv[1]) == "ingest-check")
+    {
+        try { return ingest_check(argc, argv); }
+        catch (std::exception const & e) { std::cerr << e.what() << "\n"; return 3; }
+    }
     auto args = speq::args::initialize_argument_parser(argc, argv);
     if (!args.is_parsed) return 0;   // the reference returns 0 after printing the parse error (src/main.cpp:17-40)
     try

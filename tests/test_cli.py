@@ -133,3 +133,40 @@ def test_speq_all_matches_golden(speq_bin, tmp_path, name):
     # sharded over 2 "GPUs" requested on a 1-GPU box clamps to the devices present; result unchanged
     out2 = json.loads((tmp_path / "out.json").read_text())
     assert out2["total_kmers"] == exp["total_kmers"]
+
+
+def _write_fq(path, recs, newline="\n", trailing=True):
+    txt = newline.join(newline.join(["@" + h, s, "+", q]) for h, s, q in recs)
+    path.write_text(txt + (newline if trailing else ""), newline="")
+
+
+@pytest.mark.parametrize("threads,region", [(1, 1 << 20), (4, 4096), (7, 700), (3, 64)])
+def test_parallel_fastq_indexer_matches_serial_reader(speq_bin, tmp_path, threads, region):
+    """Host-only: the mapped, multi-threaded 4-line FASTQ indexer hands out exactly the records (order, bytes) the serial
+    seqan3-grammar reader does -- quality lines that start with '@' or '+', CRLF, no trailing newline, ragged lengths,
+    empty reads -- and hands over to the serial reader in front of a multi-line record."""
+    import random
+    rnd = random.Random(threads * 1000 + region)
+    qchars = "@+!#IJ5?"
+
+    def rec(i, L):
+        s = "".join(rnd.choice("ACGTN") for _ in range(L))
+        q = "".join(rnd.choice(qchars) for _ in range(L))
+        return (f"r{i} desc @+ x", s, q)
+    recs = [rec(i, rnd.choice([0, 1, 5, 36, 150, 151, 400])) for i in range(600)]
+    for name, nl, trailing in (("a.fq", "\n", True), ("b.fastq", "\r\n", True), ("c.fq", "\n", False)):
+        p = tmp_path / name
+        _write_fq(p, recs, nl, trailing)
+        r = run(speq_bin, "ingest-check", p, threads, region)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert r.stdout.split("\n")[0].split()[1] == "600" and "handover 0" in r.stdout
+    # a multi-line record in the middle: regular records before it go through the indexer, the rest through the serial reader
+    p = tmp_path / "d.fq"
+    head = "".join(f"@{h}\n{s}\n+\n{q}\n" for h, s, q in recs[:300])
+    multi = "@m\nACGT\nACGT\n+\nIIII\nIIII\n"
+    tail = "".join(f"@{h}\n{s}\n+\n{q}\n" for h, s, q in recs[300:])
+    p.write_text(head + multi + tail)
+    r = run(speq_bin, "ingest-check", p, threads, region)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.split("\n")[0].split()[1] == "601"
+    assert int(r.stdout.split("handover")[1]) > 0
