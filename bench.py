@@ -96,6 +96,25 @@ def oracle_choice():
     return helpers.oracle_binary(), "port"
 
 
+def bind_near_gpu(index: int):
+    """One process per GPU: run on (and so first-touch / pin host memory on) the CPUs of the GPU's NUMA node."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(index)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        base = Path("/sys/bus/pci/devices") / bdf
+        cpus = set()
+        for part in (base / "local_cpulist").read_text().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return {"bdf": bdf, "numa_node": int((base / "numa_node").read_text()), "cpus": len(cpus)}
+    except Exception as ex:   # affinity is an optimisation only
+        return {"error": str(ex)[:80]}
+
+
 def host_threads() -> int:
     try:
         return max(1, len(os.sched_getaffinity(0)))
@@ -261,6 +280,7 @@ def main() -> None:
     assert torch.cuda.is_available(), "bench.py --impl native needs a CUDA device: the scan path has no CPU fallback"
     torch.cuda.set_device(local_rank)
     dev = f"cuda:{local_rank}"
+    numa = bind_near_gpu(local_rank) if world > 1 else None   # pinned staging buffers on the GPU's own NUMA node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(dev))
     from speq_b200 import capi, engine
@@ -489,7 +509,7 @@ def main() -> None:
                 "reads_per_sec": reads_step * args.steps / (ms_total * 1e-3),
                 "clocks": clk, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu,
                 "tallies": {"unique": [int(x) for x in tall[:V]], "total_kmers": int(tall[V]), "ambiguous": int(tall[V + 1])},
-                "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack, "scan_open_s": t_scan_open},
+                "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack, "scan_open_s": t_scan_open, "numa": numa},
                 "cross_check": cross}
         emit(line)
     scan.close()
