@@ -12,6 +12,10 @@
 #include <cstring>
 #include <thread>
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
 #include "sais.hpp"
 #include "speq_internal.h"
 
@@ -83,8 +87,16 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         T[m] = 0;
     }
 
+    const bool timing = getenv("SPEQB_TIMING") != nullptr;
+    auto tick = std::chrono::steady_clock::now();
+    auto lap = [&](const char * what) {
+        auto now = std::chrono::steady_clock::now();
+        if (timing) fprintf(stderr, "[index build] %-10s %.3f s\n", what, std::chrono::duration<double>(now - tick).count());
+        tick = now;
+    };
     std::vector<int32_t> SA(n);
     suffix_array(T.data(), SA.data(), (int32_t)n, 7);
+    lap("sa-is");
 
     // C[] (deps/seqan3/include/seqan3/search/fm_index/detail/csa_alphabet_strategy.hpp:84-117)
     uint64_t cnt[8] = {0};
@@ -135,6 +147,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         blk.cnt[0] = run[0]; blk.cnt[1] = run[1]; blk.cnt[2] = run[2]; blk.cnt[3] = run[3]; blk.chgcum = chgcum;
     }
 
+    lap("bwt+grp");
     // capped LCP array (Kasai et al. 2001, with the cap folded in: lcp[rank[i+1]] >= lcp[rank[i]] - 1 also holds for
     // min(cap, lcp)).  The sentinel is unique, so the symbol comparison stops before either suffix runs off the text.
     {
@@ -153,6 +166,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         }
     }
 
+    lap("lcp");
     // previous / next smaller value links over the capped lcp array (lcp[n] = 0 closes every interval)
     {
         h.pn.assign(n + 1, uint2x{0u, (uint32_t)n});
@@ -174,6 +188,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         }
     }
 
+    lap("psv/nsv");
     if (flags & SPEQG_BUILD_KEEP_SA)
     {
         h.sa.resize(n);

@@ -90,20 +90,24 @@ __global__ void __launch_bounds__(kBlockH) ktable_build_kernel(const uint64_t * 
     const uint32_t nwin = L - k + 1u;
     const uint64_t g0 = grp_off[text];
     const uint32_t grp = (uint32_t)text_group[text];
-    const uint64_t vmask = (1ull << k) - 1ull;
     for (uint32_t gi = blockIdx.x * blockDim.x + threadIdx.x; (uint64_t)gi * 32u < nwin; gi += gridDim.x * blockDim.x)
     {
-        // bases [32 gi, 32 gi + 64): every window that starts in this group (k <= 31)
+        // bases [32 gi, 32 gi + 64): every window that starts in this group (k <= 31).  The k-mer code is rolled exactly as
+        // the scan rolls it: key = key << 2 | base, i.e. the first base of the window in the highest of its k digits.
         const uint32_t ngroups = (L + 31u) >> 5;
         const uint64_t b0 = bases[g0 + gi], b1 = gi + 1u < ngroups ? bases[g0 + gi + 1u] : 0ull;
         const uint64_t v = (uint64_t)inv[g0 + gi] | ((gi + 1u < ngroups ? (uint64_t)inv[g0 + gi + 1u] : 0ull) << 32);
-        for (uint32_t j = 0; j < 32u; ++j)
+        uint64_t key = 0ull;
+        uint32_t run = 0u;
+        for (uint32_t j = 0; j < 31u + k; ++j)
         {
-            const uint32_t p = gi * 32u + j;
-            if (p >= nwin) break;
-            if ((v >> j) & vmask) continue;                       // the window holds an N: no ACGT query matches it
-            const uint64_t key = (j == 0u ? b0 : (b0 >> (2u * j)) | (b1 << (64u - 2u * j))) & kt.mask_b;
-            if (!ktable_insert(kt, key, grp, n_keys)) atomicExch(n_keys + 1, 1ull);   // displacement > kMaxDisp: the host regrows
+            const uint32_t pos = gi * 32u + j;
+            if (pos >= L) break;
+            const uint32_t c = (uint32_t)((j < 32u ? b0 >> (2u * j) : b1 >> (2u * (j - 32u))) & 3ull);
+            key = (key << 2) | c;
+            run = ((v >> j) & 1ull) ? 0u : run + 1u;              // an N: no ACGT query matches a window that holds it
+            if (j + 1u >= k && run >= k && !ktable_insert(kt, key & kt.mask_b, grp, n_keys))
+                atomicExch(n_keys + 1, 1ull);                     // displacement > kMaxDisp: the host regrows
         }
     }
 }
@@ -124,7 +128,7 @@ __global__ void __launch_bounds__(kBlockH) ktable_lb_kernel(const KTabView kt, c
             const uint64_t key = (h * kt.mul_inv) & kt.mask_b;
             uint32_t lb = 0u, rb = ix.n - 1u;
             bool ok = true;
-            for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * j)) & 3u);
+            for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - 1u - j))) & 3u);
             if (ok) out = lb;
         }
         slot_lb[i] = out;
@@ -151,7 +155,7 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(unsigned long
 enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_DONE = 3 };
 // windows per lane and loop trip (their probes are independent, so all loads are issued together) and resident CTAs per SM
 #ifndef SPEQB_KWIN
-#define SPEQB_KWIN 2
+#define SPEQB_KWIN 3
 #endif
 #ifndef SPEQB_HMINB
 #define SPEQB_HMINB 4
@@ -170,7 +174,6 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     Tally32<MODE> env{b, a, sm};
 
     const uint32_t k = a.k;
-    const uint32_t sh = 2u * (k - 1u);
     const uint32_t units = (uint32_t)(paired ? b.n_reads / 2 : b.n_reads);
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t kmask = (kt.rmask << 3) | 7ull;
@@ -182,9 +185,10 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     uint32_t u = 0u;                             // unit (read or pair)
     uint64_t g0 = 0ull;                          // first 32-base group of the current read
     uint32_t t = 0u, pend = 0u, run = 0u;        // next base, end of the read, valid bases behind t
-    uint64_t key = 0ull;                         // the last k bases, base i of the window at bits [2i, 2i+2)
-    uint32_t wlo = 0u, whi = 0u, winv = 0u;      // current 32-base group, base t in the low bits
-    uint32_t nlo = 0u, nhi = 0u, ninv = 0u;      // the following group (prefetched)
+    uint64_t key = 0ull;                         // key << 2 | base per base: the low 2k bits are the window (first base highest);
+                                                 // the bits above are stale bases -- the hash is taken mod 4^k, which ignores them
+    uint64_t cb = 0ull, nb = 0ull;               // the 32-base group that holds base t, and the following one (prefetched)
+    uint32_t ci = 0u, ni = 0u;                   // their invalid-base bits
     uint32_t gmin = kNoGroup, gmax = 0u, c_total = 0u;
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
@@ -193,19 +197,22 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     // warp-uniform chunk of claimed units
     uint32_t wcur = 0u, wend = 0u;
 
-    // one base: shift it into the k-mer, keep the count of valid bases, move the window registers on
-    auto roll = [&]() {
-        if ((t & 31u) == 0u && ((t >> 5) + 1u) * 32u < pend)
+    // t has reached a multiple of 32: the prefetched group becomes the current one and the one after it is requested
+    auto next_group = [&]() {
+        cb = nb; ci = ni;
+        if (((t >> 5) + 1u) * 32u < pend)
         {
-            const uint64_t v = load_ro(b.bases + g0 + (t >> 5) + 1u);
-            nlo = (uint32_t)v; nhi = (uint32_t)(v >> 32);
-            ninv = load_ro(b.inv + g0 + (t >> 5) + 1u);
+            nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
+            ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
         }
-        key = (key >> 2) | ((uint64_t)(wlo & 3u) << sh);
-        run = (winv & 1u) ? 0u : run + 1u;                        // N / low quality: no window may contain this base
+    };
+    // one base (start of a read / behind an N, where no window is due)
+    auto roll1 = [&]() {
+        const uint32_t o = t & 31u;
+        key = (key << 2) | ((uint32_t)(cb >> (2u * o)) & 3u);
+        run = ((ci >> o) & 1u) ? 0u : run + 1u;                   // N / low quality: no window may contain this base
         t += 1u;
-        wlo = (wlo >> 2) | (whi << 30); whi >>= 2; winv >>= 1;
-        if ((t & 31u) == 0u) { wlo = nlo; whi = nhi; winv = ninv; }
+        if ((t & 31u) == 0u) next_group();
     };
 
     while (true)
@@ -255,27 +262,40 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
             t = 0u; run = 0u; key = 0ull;
             if (pend)
             {
-                const uint64_t v = load_ro(b.bases + g0);
-                wlo = (uint32_t)v; whi = (uint32_t)(v >> 32);
-                winv = load_ro(b.inv + g0);
+                cb = load_ro(b.bases + g0);
+                ci = load_ro(b.inv + g0);
+                if (pend > 32u)
+                {
+                    nb = load_ro(b.bases + g0 + 1u);
+                    ni = load_ro(b.inv + g0 + 1u);
+                }
             }
             phase = H_RUN;
         }
         else if (ph == H_RUN)
         {
             // ---- up to kWin windows: roll to each, issue every probe, then consume them in window order
-            while (run + 1u < k && t < pend) roll();              // start of a read / behind an N: no window is due yet
+            while (run + 1u < k && t < pend) roll1();             // start of a read / behind an N: no window is due yet
             uint32_t w[kWin][8];
             uint32_t pb[kWin], want_lo[kWin], want_hi[kWin];
             bool due[kWin];
-            const uint32_t t0 = t;
+            const uint32_t t0 = t, o = t & 31u;
+            const uint32_t nbase = pend - t < (uint32_t)kWin ? pend - t : (uint32_t)kWin;
+            // the next kWin bases in one register each (they may straddle into the prefetched group)
+            uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
+            if (o + (uint32_t)kWin > 32u)
+            {
+                bits |= (uint32_t)nb << (2u * (32u - o));
+                ibits |= ni << (32u - o);
+            }
 #pragma unroll
             for (int j = 0; j < kWin; ++j)
             {
                 due[j] = false;
-                if (t < pend)
+                if ((uint32_t)j < nbase)
                 {
-                    roll();
+                    key = (key << 2) | ((bits >> (2 * j)) & 3u);
+                    run = ((ibits >> j) & 1u) ? 0u : run + 1u;    // N / low quality: no window may contain this base
                     due[j] = run >= k;
                 }
                 if (due[j])
@@ -289,6 +309,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                                  : "l"(kt.slots + 4ull * pb[j]));
                 }
             }
+            t += nbase;
+            if (o + nbase >= 32u) next_group();
 #pragma unroll
             for (int j = 0; j < kWin; ++j)
             {
@@ -307,13 +329,15 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                         if (RECORD) atomicAdd(slot_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
                         if (g != kValMulti)
                         {
-                            // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191)
-                            gmin = g < gmin ? g : gmin;
-                            gmax = g > gmax ? g : gmax;
+                            // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191).  The
+                            // run-length tally is closed at the end of every unit, so the variant of an open run is already
+                            // inside [gmin, gmax] of this unit.
                             if (g != agg_g)
                             {
                                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                                 agg_g = g; agg_n = 0u; agg_w = 0.0;
+                                gmin = g < gmin ? g : gmin;
+                                gmax = g > gmax ? g : gmax;
                             }
                             if (LOCAL) agg_w += env.weight(g0, t0 + (uint32_t)j + 1u, k);
                             else agg_n += 1u;
@@ -343,6 +367,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 n_total += c_total;
                 n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
                 c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+                agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
                 mate2 = false;
                 if ((n_total | n_look) & 0x80000000u)
                 {

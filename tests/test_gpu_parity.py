@@ -180,7 +180,7 @@ def _scan_tallies(idx, k, seq, qual, offs, **kw):
     return r
 
 
-@pytest.mark.parametrize("cfg,R", [("C2", 400_000), ("C3", 200_000), ("C5", 300)])
+@pytest.mark.parametrize("cfg,R", [("C1", 100_000), ("C2", 400_000), ("C3", 200_000), ("C4", 200_000), ("C5", 300)])
 def test_properties_at_config_shapes(lib, cfg, R):
     """Size-independent properties on the full-size indexes of BASELINE.json's configs (read count bounded for test time):
     rolling == direct; shard additivity; lookups = R (L-k+1); error-free reads from a scaffold always hit."""
