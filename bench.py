@@ -243,8 +243,8 @@ def main() -> None:
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--algorithm", default="auto", choices=["auto", "ktable", "rolling", "direct"],
-                    help="auto = the library's default: k-mer table scan for k <= 31, else the rolling FM search")
+    ap.add_argument("--algorithm", default="auto", choices=["auto", "kpair", "ktable", "rolling", "direct"],
+                    help="auto = the library's default: pair / k-mer table scan for k <= 31, else the rolling FM search")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -318,10 +318,13 @@ def main() -> None:
 
     stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream: the scan handle launches on it and the events time it
     torch.cuda.set_stream(stream)
-    algo = {"rolling": capi.ALGO_ROLLING, "direct": capi.ALGO_DIRECT, "ktable": capi.ALGO_KTABLE,
-            "auto": capi.ALGO_KTABLE if sh.k <= 31 else capi.ALGO_ROLLING}[args.algorithm]
+    algo_req = {"rolling": capi.ALGO_ROLLING, "direct": capi.ALGO_DIRECT, "ktable": capi.ALGO_KTABLE, "kpair": capi.ALGO_KPAIR,
+                "auto": capi.ALGO_AUTO}[args.algorithm]
     t0 = time.perf_counter()
-    scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=algo, device=local_rank, stream=stream.cuda_stream)
+    scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=algo_req, device=local_rank, stream=stream.cuda_stream)
+    algo = scan.info()["algorithm"]           # what AUTO resolved to
+    config["algorithm"] = {capi.ALGO_ROLLING: "rolling", capi.ALGO_DIRECT: "direct", capi.ALGO_KTABLE: "ktable",
+                           capi.ALGO_KPAIR: "kpair"}[algo] + (" (auto)" if args.algorithm == "auto" else "")
     torch.cuda.synchronize()
     t_scan_open = time.perf_counter() - t0     # per-(index, k) specialisation: rank blocks or the k-mer table
     V = sh.V
@@ -391,7 +394,7 @@ def main() -> None:
 
     # ---- cross-check outside every timed region: the k-mer table scan must reproduce the rolling FM search bit for bit
     cross = None
-    if algo == capi.ALGO_KTABLE:
+    if algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR):
         ref_scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=capi.ALGO_ROLLING, device=local_rank,
                                stream=stream.cuda_stream)
         ref_scan.submit_device(db)
@@ -399,7 +402,8 @@ def main() -> None:
         scan.reset(); scan.submit_device(db); rm = scan.finish()
         assert np.array_equal(rr.unique, rm.unique) and rr.total_kmers == rm.total_kmers and rr.ambiguous == rm.ambiguous, \
             "k-mer table tallies differ from the rolling FM search"
-        cross = "ktable tallies == rolling FM-search tallies on this rank's reads (unique[V], total, ambiguous)"
+        cross = "table-scan tallies == rolling FM-search tallies on this rank's reads (unique[V], total, ambiguous)"
+        probes_rank = rm.probes
         ref_scan.close()
 
     # ---- e2e: pinned host buffers through the C ABI ----
@@ -470,7 +474,8 @@ def main() -> None:
         peak, how = measured_peak()
         ach = alg / (kern_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                "kernel": {capi.ALGO_ROLLING: "scan32_kernel<0>", capi.ALGO_KTABLE: "scanh_kernel<0>"}.get(algo, "scan_direct_kernel<0>"),
+                "kernel": {capi.ALGO_ROLLING: "scan32_kernel<0>", capi.ALGO_KTABLE: "scanh_kernel<0>",
+                           capi.ALGO_KPAIR: "scanp_kernel<0>"}.get(algo, "scan_direct_kernel<0>"),
                 "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_launch": alg, "peak_source": how,
                 "work": {"steps_executed": st["steps_executed"], "lookups": st["lookups"], "kmers_hit": st["kmers_hit"],
@@ -480,14 +485,15 @@ def main() -> None:
                         f"real traffic is lower (own_sectors); index footprint {idx.device_bytes/1e6:.0f} MB"}
         # what the kernel itself must move: one 32-byte sector per valid window (ktable) / two per read base (rolling), plus
         # the packed input stream; against the HBM peak when the structure misses L2, else informative only
-        own = (32 * int(tall[V]) // world if algo == capi.ALGO_KTABLE else 64 * R * L) + packed_bytes
+        table = algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR)
+        own = (32 * probes_rank if table else 64 * R * L) + packed_bytes
         roof["own_sectors"] = {"bytes_per_launch": own, "GB/s": own / (kern_ms * 1e-3) / 1e9, "frac_of_hbm_peak": own / (kern_ms * 1e-3) / 1e9 / peak}
         # the roofline this access pattern really has: independent random 32-byte sectors.  Peaks measured on this pool's B200
         # by profiles/gather_probe.cu (profiles/r1_gather_probe.txt), chosen by the size of the structure the kernel probes.
         info = scan.info()
         sb = info["structure_bytes"]
         ra_peak, ra_src = next((p_, s_) for lim, p_, s_ in RANDOM_SECTOR_PEAKS if sb <= lim)
-        sectors = (int(tall[V]) // world) if algo == capi.ALGO_KTABLE else 2 * R * L
+        sectors = probes_rank if table else 2 * R * L     # table scans count the probes they issue
         roof["random_access"] = {"sectors_per_launch": sectors, "achieved_Gsectors_per_s": sectors / (kern_ms * 1e-3) / 1e9,
                                  "peak_Gsectors_per_s": ra_peak, "frac": sectors / (kern_ms * 1e-3) / 1e9 / ra_peak,
                                  "structure_bytes": sb, "keys": info["keys"], "peak_source": ra_src}

@@ -124,7 +124,10 @@ int speqg_pack_reads(const uint8_t * seq, const uint8_t * qual, const uint64_t *
 #define SPEQG_ALGO_ROLLING64 2 /* the rolling search on the generic 64-byte blocks (the back-check's kernel); cross-checks */
 #define SPEQG_ALGO_KTABLE 3   /* k <= 31: the search memoised per (index, k) as a k-mer table built from the index's own texts;
                                  one 32-byte probe per window.  Same tallies, bit for bit */
-#define SPEQG_ALGO_AUTO 4     /* KTABLE when k <= 31, else ROLLING */
+#define SPEQG_ALGO_AUTO 4     /* k <= 31: KTABLE, or KPAIR when the k-mer table is larger than 3/4 of L2 and the index has <= 254
+                                 variants; else ROLLING */
+#define SPEQG_ALGO_KPAIR 5    /* KTABLE plus a table over the (k+1)-mers of the texts: one probe answers two consecutive
+                                 windows; a miss falls back to two k-mer probes.  k <= 31, <= 254 variants */
 
 typedef struct speqg_params
 {
@@ -145,7 +148,8 @@ typedef struct speqg_counts
     uint64_t reads;
     uint64_t kernel_launches;   /* kernels launched by this handle since open / reset */
     /* filled by speqg_scan_stats only (reference-semantics work counters for the roofline): */
-    uint64_t steps_executed;    /* backward_search calls incl. the failing one (fm_index_cursor.hpp:316-324) */
+    uint64_t steps_executed;    /* backward_search calls incl. the failing one (fm_index_cursor.hpp:316-324); from
+                                   speqg_scan_finish with a table algorithm: 32-byte table probes issued */
     uint64_t kmers_hit;         /* k-mers with a non-empty final interval */
     uint64_t occurrences;       /* sum of final interval sizes */
     uint64_t occ_sectors;       /* sum ceil(occ/32) */

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Tuning sweep of scanh_kernel: windows per trip (SPEQB_KWIN) x resident CTAs per SM (SPEQB_HMINB); rebuilds the library on the box.
 O=${1:-gpurun_out/sweep}; mkdir -p $O
-for v in ${SWEEP:-"2 4" "4 3" "3 4" "2 5" "4 2"}; do
+for v in ${SWEEP:-3:4 2:4 4:3 2:5 4:2}; do
   set -- ${v/:/ }
   SPEQB_NVCC_EXTRA="-DSPEQB_KWIN=$1 -DSPEQB_HMINB=$2" python -m speq_b200.build --force > /dev/null 2>&1
   for c in C2 C3; do

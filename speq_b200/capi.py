@@ -18,7 +18,7 @@ OK, EINVAL, ECUDA, EIO, ENOMEM, ESTATE = 0, -1, -2, -3, -4, -5
 BUILD_KEEP_SA = 1
 ENC_ASCII, ENC_RANK = 0, 1
 MODE_GLOBAL, MODE_LOCAL = 0, 1
-ALGO_ROLLING, ALGO_DIRECT, ALGO_ROLLING64, ALGO_KTABLE, ALGO_AUTO = 0, 1, 2, 3, 4
+ALGO_ROLLING, ALGO_DIRECT, ALGO_ROLLING64, ALGO_KTABLE, ALGO_AUTO, ALGO_KPAIR = 0, 1, 2, 3, 4, 5
 
 u8p = C.POINTER(C.c_uint8)
 u32p = C.POINTER(C.c_uint32)

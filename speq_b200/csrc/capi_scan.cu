@@ -71,6 +71,12 @@ struct speqg_scan
     uint32_t * d_slot_lb = nullptr;
     bool slot_mult_dirty = false;
     uint64_t ktab_keys = 0;
+    // SPEQG_ALGO_KPAIR: the table over the (k+1)-mers (two windows per probe) next to the k-mer table
+    KTabView kp{};
+    unsigned long long * d_pair_mult = nullptr;
+    uint32_t * d_pair_lb = nullptr;
+    uint64_t kpair_keys = 0;
+    LaunchCfg cfg_p{};
     uint32_t algo = SPEQG_ALGO_ROLLING;   // resolved algorithm (AUTO -> KTABLE / ROLLING)
     int device = 0;
     speqg_params p{};
@@ -108,6 +114,8 @@ scan_refine_view refine_view(speqg_scan * s)
     {
         device_guard guard(s->device);
         CK(launch_ktable_fold_mult(s->d_slot_mult, s->d_slot_lb, 4ull * ((uint64_t)s->kt.nbmask + 1), s->d_mult, s->compute));
+        if (s->d_pair_mult)
+            CK(launch_kpair_fold_mult(s->d_pair_mult, s->d_pair_lb, 4ull * ((uint64_t)s->kp.nbmask + 1), s->d_mult, s->compute));
         s->slot_mult_dirty = false;
     }
     return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult,
@@ -123,6 +131,7 @@ void scan_release(speqg_scan * s)
     cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk); cudaFree(s->d_work);
     cudaFree(s->kt.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_slot_lb); cudaFree(s->d_kstat);
+    cudaFree(s->kp.slots); cudaFree(s->d_pair_mult); cudaFree(s->d_pair_lb);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -162,6 +171,11 @@ void launch_on_view(speqg_scan * s, BatchView const & v)
     ScanArgs a = scan_args(s);
     if (s->algo == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
     else if (s->algo == SPEQG_ALGO_ROLLING64) CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg64, s->compute));
+    else if (s->algo == SPEQG_ALGO_KPAIR)
+    {
+        CK(launch_scanp(s->kt, s->kp, s->d_slot_mult, s->d_pair_mult, v, a, s->mode, s->cfg_p, s->compute));
+        if (s->mode & M_RECORD) s->slot_mult_dirty = true;
+    }
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
         CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, s->cfg_h, s->compute));
@@ -194,7 +208,9 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
     need(idx && params && out, "NULL argument");
     need(params->k >= 1 && params->k <= kMaxK, "k must be in [1, 127]");
     need(params->mode == SPEQG_MODE_GLOBAL || params->mode == SPEQG_MODE_LOCAL, "unknown mode");
-    need(params->algorithm <= SPEQG_ALGO_AUTO, "unknown algorithm");
+    need(params->algorithm <= SPEQG_ALGO_KPAIR, "unknown algorithm");
+    need(!(params->algorithm == SPEQG_ALGO_KPAIR && (params->k > kMaxKTable || idx->host.V > kMaxGroupsPair)),
+         "the pair-table algorithm needs k <= 31 and at most 254 variants");
     need(!(params->algorithm == SPEQG_ALGO_KTABLE && params->k > kMaxKTable), "the k-mer table algorithm needs k <= 31");
     need(idx->host.n <= kMaxN32, "index too large: the indexed text must be shorter than 2^31 symbols");
     need(!(params->algorithm == SPEQG_ALGO_DIRECT && params->mode == SPEQG_MODE_LOCAL), "the direct algorithm covers global mode only");
@@ -207,8 +223,10 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->di = &di;
         s->device = device;
         s->p = *params;
-        s->algo = params->algorithm == SPEQG_ALGO_AUTO ? (params->k <= kMaxKTable ? SPEQG_ALGO_KTABLE : SPEQG_ALGO_ROLLING)
-                                                        : params->algorithm;
+        s->algo = params->algorithm != SPEQG_ALGO_AUTO ? params->algorithm
+                  : params->k > kMaxKTable             ? SPEQG_ALGO_ROLLING
+                                                       : SPEQG_ALGO_KTABLE;   // upgraded to KPAIR below when the table misses L2
+        const bool auto_algo = params->algorithm == SPEQG_ALGO_AUTO;
         s->mode = (params->mode == SPEQG_MODE_LOCAL ? M_LOCAL : 0) | (params->record_multiplicity ? M_RECORD : 0) |
                   (params->paired ? M_PAIRED : 0);
         uint32_t V = idx->host.V;
@@ -239,7 +257,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->d_qden = dev_upload(qden, 42);
         // rank blocks specialised for this k: one pass over the index, once per scan handle
         s->view = di.view;
-        if (s->algo == SPEQG_ALGO_KTABLE)
+        if (s->algo == SPEQG_ALGO_KTABLE || s->algo == SPEQG_ALGO_KPAIR)
         {
             // distinct k-mers of the index <= suffixes that start a depth-k lcp interval; load factor in (0.2, 0.4]
             HostIndex const & h = idx->host;
@@ -272,6 +290,43 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 CK(launch_ktable_lb(s->kt, s->view, params->k, s->d_slot_lb, s->compute));
             }
             CK(scanh_launch_cfg(s->mode, V, &s->cfg_h));
+            if (auto_algo && idx->host.V <= kMaxGroupsPair)
+            {
+                // A table that does not stay in L2 is bound by the HBM random-sector rate: halving the probes (two windows
+                // per probe) pays there (C4: +43 %), while on an L2-resident table the single-window kernel is faster.
+                int l2 = 0;
+                CK(cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device));
+                if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3) s->algo = SPEQG_ALGO_KPAIR;
+            }
+            if (s->algo == SPEQG_ALGO_KPAIR)
+            {
+                uint64_t ub2 = 0;
+                for (uint64_t i = 0; i < h.n; ++i) ub2 += h.lcp[i] < params->k + 1 ? 1u : 0u;
+                for (uint32_t grow = 0;; ++grow)
+                {
+                    need(grow < 4 && ktable_geometry(params->k + 1, ub2, grow, &s->kp), "pair table too large");
+                    s->kp.slots = dev_alloc<uint64_t>(4ull * ((uint64_t)s->kp.nbmask + 1));
+                    CK(launch_kpair_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, h.S, max_len, s->kt, s->kp, params->k,
+                                          s->d_kstat, s->compute));
+                    unsigned long long st[2] = {0, 0};
+                    CK(cudaMemcpyAsync(st, s->d_kstat, 16, cudaMemcpyDeviceToHost, s->compute));
+                    CK(cudaStreamSynchronize(s->compute));
+                    s->kpair_keys = st[0];
+                    need(st[1] != 2, "internal error: a k-mer of the texts is missing from the k-mer table");
+                    if (!st[1]) break;
+                    CK(cudaFree(s->kp.slots));
+                    s->kp.slots = nullptr;
+                }
+                if (params->record_multiplicity)
+                {
+                    const uint64_t n_slots = 4ull * ((uint64_t)s->kp.nbmask + 1);
+                    s->d_pair_mult = dev_alloc<unsigned long long>(n_slots);
+                    s->d_pair_lb = dev_alloc<uint32_t>(2 * n_slots);
+                    CK(cudaMemsetAsync(s->d_pair_mult, 0, n_slots * 8, s->compute));
+                    CK(launch_kpair_lb(s->kp, s->view, params->k, s->d_pair_lb, s->compute));
+                }
+                CK(scanp_launch_cfg(s->mode, V, &s->cfg_p));
+            }
         }
         else if (s->algo == SPEQG_ALGO_ROLLING64)
         {
@@ -324,6 +379,7 @@ int speqg_scan_reset(speqg_scan * s)
     CK(cudaMemsetAsync(s->d_bad, 0, 8, s->compute));
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
     if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
+    if (s->d_pair_mult) CK(cudaMemsetAsync(s->d_pair_mult, 0, 4ull * ((uint64_t)s->kp.nbmask + 1) * 8, s->compute));
     s->slot_mult_dirty = false;
     s->launches = 0;
     SPEQG_CATCH
@@ -458,6 +514,7 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
         counts->lookups = sc[SC_LOOKUPS];
         counts->reads = sc[SC_READS];
         counts->kernel_launches = s->launches;
+        counts->steps_executed = sc[SC_STEPS];   // table algorithms: 32-byte table probes issued (0 otherwise)
     }
     SPEQG_CATCH
 }
@@ -506,10 +563,11 @@ int speqg_scan_info(speqg_scan * s, uint32_t * algorithm, uint64_t * structure_b
     if (structure_bytes)
     {
         if (s->algo == SPEQG_ALGO_KTABLE) *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1);
+        else if (s->algo == SPEQG_ALGO_KPAIR) *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1) + 32ull * ((uint64_t)s->kp.nbmask + 1);
         else if (s->algo == SPEQG_ALGO_ROLLING) *structure_bytes = sizeof(FBlock) * (s->idx->host.n / 32 + 1);
         else *structure_bytes = sizeof(KBlock) * s->idx->host.blocks.size();
     }
-    if (keys) *keys = s->algo == SPEQG_ALGO_KTABLE ? s->ktab_keys : 0;
+    if (keys) *keys = s->algo == SPEQG_ALGO_KTABLE ? s->ktab_keys : s->algo == SPEQG_ALGO_KPAIR ? s->ktab_keys + s->kpair_keys : 0;
     SPEQG_CATCH
 }
 

@@ -100,6 +100,7 @@ struct __attribute__((aligned(16))) UpRec
 static_assert(sizeof(UpRec) == 16, "UpRec must be 16 bytes");
 // the k-mer table scan (scanh.cu) memoises the search per (index, k) for k up to:
 constexpr uint32_t kMaxKTable = 31;
+constexpr uint32_t kMaxGroupsPair = 254;   // the pair table stores one byte per k-mer: variant, or 0xFF
 constexpr uint32_t kSFlagExc = 0x80000000u;
 constexpr uint64_t kMaxN32 = 0x7FFFFFFFull;   // cnt[0] keeps bit 31 for the exception flag
 

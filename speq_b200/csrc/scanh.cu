@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
     // per-lane scalars (flushed at the end, or before they could wrap)
-    uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u;
+    uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
     // warp-uniform chunk of claimed units
     uint32_t wcur = 0u, wend = 0u;
 
@@ -316,6 +316,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
             {
                 if (!due[j]) continue;
                 c_total += 1u;                                    // ++total_kmers (src/fm_scanner.cpp:164)
+                n_probe += 1u;
                 uint32_t d = 0u;
                 while (true)
                 {
@@ -348,6 +349,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                     if ((w[j][6] & w[j][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;
                     // rare: the home bucket is full of other k-mers; the k-mer may sit in the next bucket
                     d += 1u;
+                    n_probe += 1u;
                     pb[j] = (pb[j] + 1u) & kt.nbmask;
                     const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kt.rbits);
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
@@ -384,6 +386,420 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     if (n_amb) env.add64(1, n_amb);
     if (n_look) env.add64(2, n_look);
     if (n_reads) env.add64(3, n_reads);
+    {
+        // sectors probed (table loads issued): one global atomic per warp
+        const uint32_t wp = __reduce_add_sync(kFullH, n_probe);
+        if (lane == 0u && wp) atomicAdd(a.scalars + SC_STEPS, (unsigned long long)wp);
+    }
+    smem32_flush<LOCAL>(sm, a);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Two windows per probe (SPEQG_ALGO_KPAIR).  A second table holds every N-free (k+1)-mer of the texts with the values of
+// its two k-mers (one byte each: variant < 255, 0xFF = several variants); a (k+1)-mer of the index contains two k-mers of
+// the index, so a hit answers two consecutive windows with one sector.  A miss (a sequencing error somewhere in the k+1
+// bases, or a junction the index does not have) says nothing about the two k-mers: they are then looked up one by one in
+// the k-mer table, exactly as scanh_kernel does.  Windows that cannot be paired (odd one at the end of a read, next to an
+// N) take the same single-window path.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t kAbsent = 0x10000u;
+
+// value of `key` in a table (synchronous probe sequence), kAbsent when it is not stored; bucket / j = where it is stored
+struct KFound
+{
+    uint32_t val, bucket, j, probes;
+};
+__device__ __forceinline__ KFound ktable_find(KTabView const & kt, uint64_t key)
+{
+    KFound f;
+    f.val = kAbsent; f.bucket = 0u; f.j = 0u; f.probes = 0u;
+    const uint64_t h = (key * kt.mul) & kt.mask_b;
+    uint32_t bk = (uint32_t)(h >> kt.rbits);
+    uint64_t want = h & kt.rmask;
+    const uint64_t kmask = (kt.rmask << 3) | 7ull;
+    for (uint32_t d = 0; d <= kMaxDisp; ++d)
+    {
+        uint32_t w[8];
+        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                     : "l"(kt.slots + 4ull * bk));
+        f.probes += 1u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (f.val == kAbsent && ((u64of(w[2 * j], w[2 * j + 1]) ^ want) & kmask) == 0ull)
+            {
+                f.val = w[2 * j + 1] >> 16; f.bucket = bk; f.j = (uint32_t)j;
+            }
+        if (f.val != kAbsent || (w[6] & w[7]) == 0xFFFFFFFFu) break;
+        bk = (bk + 1u) & kt.nbmask;
+        want += 1ull << kt.rbits;
+    }
+    return f;
+}
+
+// value byte of a k-mer for the pair table: variant (< 255) or 0xFF
+__device__ __forceinline__ uint32_t pair_byte(uint32_t v) { return v == kValMulti ? 0xFFu : v; }
+
+__global__ void __launch_bounds__(kBlockH) kpair_build_kernel(const uint64_t * __restrict__ bases, const uint32_t * __restrict__ inv,
+                                                              const uint64_t * __restrict__ grp_off, const uint32_t * __restrict__ len,
+                                                              const KTabView kt, const KTabView kp, const uint32_t k,
+                                                              unsigned long long * __restrict__ n_keys)
+{
+    const uint32_t text = blockIdx.y;
+    const uint32_t L = len[text];
+    const uint32_t k2 = k + 1u;
+    if (L < k2) return;
+    const uint32_t nwin = L - k2 + 1u;
+    const uint64_t g0 = grp_off[text];
+    for (uint32_t gi = blockIdx.x * blockDim.x + threadIdx.x; (uint64_t)gi * 32u < nwin; gi += gridDim.x * blockDim.x)
+    {
+        const uint32_t ngroups = (L + 31u) >> 5;
+        const uint64_t b0 = bases[g0 + gi], b1 = gi + 1u < ngroups ? bases[g0 + gi + 1u] : 0ull;
+        const uint64_t v = (uint64_t)inv[g0 + gi] | ((gi + 1u < ngroups ? (uint64_t)inv[g0 + gi + 1u] : 0ull) << 32);
+        uint64_t key = 0ull;
+        uint32_t run = 0u;
+        for (uint32_t j = 0; j < 31u + k2; ++j)
+        {
+            const uint32_t pos = gi * 32u + j;
+            if (pos >= L) break;
+            const uint32_t c = (uint32_t)((j < 32u ? b0 >> (2u * j) : b1 >> (2u * (j - 32u))) & 3ull);
+            key = (key << 2) | c;
+            run = ((v >> j) & 1ull) ? 0u : run + 1u;
+            if (run < k2) continue;
+            // both k-mers are in the k-mer table (it was built from the same windows)
+            const uint32_t v1 = ktable_find(kt, (key >> 2) & kt.mask_b).val, v2 = ktable_find(kt, key & kt.mask_b).val;
+            if (v1 == kAbsent || v2 == kAbsent) { atomicExch(n_keys + 1, 2ull); continue; }
+            if (!ktable_insert(kp, key & kp.mask_b, pair_byte(v1) | (pair_byte(v2) << 8), n_keys)) atomicExch(n_keys + 1, 1ull);
+        }
+    }
+}
+
+// pair slot -> interval starts of its two k-mers
+__global__ void __launch_bounds__(kBlockH) kpair_lb_kernel(const KTabView kp, const DevIndex ix, const uint32_t k, uint32_t * __restrict__ slot_lb)
+{
+    const uint64_t n_slots = 4ull * ((uint64_t)kp.nbmask + 1ull);
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const uint64_t w = kp.slots[i];
+        uint32_t out[2] = {kNoGroup, kNoGroup};
+        if (w != kSlotFree)
+        {
+            const uint32_t d = (uint32_t)(w >> kp.rbits) & 7u;
+            const uint32_t home = ((uint32_t)(i >> 2) - d) & kp.nbmask;
+            const uint64_t h = ((uint64_t)home << kp.rbits) | (w & kp.rmask);
+            const uint64_t key = (h * kp.mul_inv) & kp.mask_b;      // k+1 bases, the first in the highest digit
+            for (uint32_t which = 0; which < 2u; ++which)
+            {
+                uint32_t lb = 0u, rb = ix.n - 1u;
+                bool ok = true;
+                for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - (j + which)))) & 3u);
+                if (ok) out[which] = lb;
+            }
+        }
+        slot_lb[2 * i] = out[0];
+        slot_lb[2 * i + 1] = out[1];
+    }
+}
+
+__global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(unsigned long long * __restrict__ slot_mult, const uint32_t * __restrict__ slot_lb,
+                                                                  const uint64_t n_slots, unsigned long long * __restrict__ mult)
+{
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const unsigned long long m = slot_mult[i];
+        if (m == 0ull) continue;
+        slot_mult[i] = 0ull;
+        if (slot_lb[2 * i] != kNoGroup) atomicAdd(mult + slot_lb[2 * i], m);
+        if (slot_lb[2 * i + 1] != kNoGroup) atomicAdd(mult + slot_lb[2 * i + 1], m);
+    }
+}
+
+#ifndef SPEQB_PWIN
+#define SPEQB_PWIN 1
+#endif
+#ifndef SPEQB_PMINB
+#define SPEQB_PMINB 4
+#endif
+constexpr int kPair = SPEQB_PWIN;     // pairs of windows per lane and loop trip
+
+template <int MODE>
+__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) scanp_kernel(const KTabView kt, const KTabView kp, unsigned long long * __restrict__ slot_mult,
+                                                                                  unsigned long long * __restrict__ pair_mult, const BatchView b, const ScanArgs a,
+                                                                                  const int paired)
+{
+    constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
+    constexpr bool RECORD = (MODE & M_RECORD) != 0;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem32 sm = smem32_view(smem_raw, a.V);
+    smem32_clear(sm, a.V);
+    Tally32<MODE> env{b, a, sm};
+
+    const uint32_t k = a.k;
+    const uint32_t units = (uint32_t)(paired ? b.n_reads / 2 : b.n_reads);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t pmask = (kp.rmask << 3) | 7ull;
+    const uint32_t pmask_lo = (uint32_t)pmask, pmask_hi = (uint32_t)(pmask >> 32);
+    const uint64_t tmask = (kt.rmask << 3) | 7ull;
+    const uint32_t tmask_lo = (uint32_t)tmask, tmask_hi = (uint32_t)(tmask >> 32);
+
+    uint32_t phase = H_FETCH;
+    bool mate2 = false;
+    uint32_t u = 0u;
+    uint64_t g0 = 0ull;
+    uint32_t t = 0u, pend = 0u, run = 0u;
+    uint64_t key = 0ull;                         // key << 2 | base per base (see scanh_kernel)
+    uint64_t cb = 0ull, nb = 0ull;
+    uint32_t ci = 0u, ni = 0u;
+    uint32_t gmin = kNoGroup, gmax = 0u, c_total = 0u;
+    uint32_t agg_g = kNoGroup, agg_n = 0u;
+    double agg_w = 0.0;
+    uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
+    uint32_t wcur = 0u, wend = 0u;
+
+    auto next_group = [&]() {
+        cb = nb; ci = ni;
+        if (((t >> 5) + 1u) * 32u < pend)
+        {
+            nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
+            ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
+        }
+    };
+    auto roll1 = [&]() {
+        const uint32_t o = t & 31u;
+        key = (key << 2) | ((uint32_t)(cb >> (2u * o)) & 3u);
+        run = ((ci >> o) & 1u) ? 0u : run + 1u;
+        t += 1u;
+        if ((t & 31u) == 0u) next_group();
+    };
+    // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191) for a window whose k-mer
+    // lies in variant g only; t_end: end of the window (local mode weight)
+    auto tally = [&](uint32_t g, uint32_t t_end) {
+        if (g != agg_g)
+        {
+            if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+            agg_g = g; agg_n = 0u; agg_w = 0.0;
+            gmin = g < gmin ? g : gmin;
+            gmax = g > gmax ? g : gmax;
+        }
+        if (LOCAL) agg_w += env.weight(g0, t_end, k);
+        else agg_n += 1u;
+    };
+    while (true)
+    {
+        __syncwarp();
+        const uint32_t ph = phase;
+        if (!__any_sync(kFullH, ph != H_DONE)) break;
+        const uint32_t m_fe = __ballot_sync(kFullH, ph == H_FETCH);
+        if (m_fe)
+        {
+            const bool claim = ph == H_FETCH && !mate2;
+            const uint32_t mc = __ballot_sync(kFullH, claim);
+            if (mc)
+            {
+                const uint32_t cnt = (uint32_t)__popc(mc), left = wend - wcur;
+                uint32_t cbase = 0u;
+                if (cnt > left)
+                {
+                    if (lane == 0u) cbase = (uint32_t)atomicAdd(a.work, (unsigned long long)kClaimChunk);
+                    cbase = __shfl_sync(kFullH, cbase, 0);
+                }
+                const uint32_t r = (uint32_t)__popc(mc & ((1u << lane) - 1u));
+                if (claim) u = r < left ? wcur + r : cbase + (r - left);
+                if (cnt > left) { wcur = cbase + (cnt - left); wend = cbase + kClaimChunk; }
+                else wcur += cnt;
+            }
+            if (ph == H_FETCH)
+            {
+                if (u >= units) phase = H_DONE;
+                else
+                {
+                    const uint64_t fr = paired ? 2ull * u + (mate2 ? 1u : 0u) : (uint64_t)u;
+                    pend = load_ro(b.len + fr);
+                    g0 = load_ro(b.grp_off + fr);
+                    phase = H_FIRST;
+                }
+            }
+        }
+        if (ph == H_FIRST)
+        {
+            const uint32_t L = pend;
+            pend = L >= k ? L : 0u;                               // L < k: the sliding view is empty (sliding.hpp:129-142)
+            n_look += L >= k ? L - k + 1u : 0u;
+            n_reads += 1u;
+            t = 0u; run = 0u; key = 0ull;
+            if (pend)
+            {
+                cb = load_ro(b.bases + g0);
+                ci = load_ro(b.inv + g0);
+                if (pend > 32u)
+                {
+                    nb = load_ro(b.bases + g0 + 1u);
+                    ni = load_ro(b.inv + g0 + 1u);
+                }
+            }
+            phase = H_RUN;
+        }
+        else if (ph == H_RUN)
+        {
+            while (run + 1u < k && t < pend) roll1();             // start of a read / behind an N: no window is due yet
+            uint32_t w[kPair][8];
+            uint32_t pb[kPair], want_lo[kPair], want_hi[kPair];
+            uint64_t key_a[kPair], key_b[kPair];                  // the k-mer register after the first / second base of each pair
+            uint32_t mode[kPair];                                 // bit 0: first window due, bit 1: second window due
+            const uint32_t t0 = t, o = t & 31u;
+            const uint32_t nbase = pend - t < 2u * (uint32_t)kPair ? pend - t : 2u * (uint32_t)kPair;
+            uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
+            if (o + 2u * (uint32_t)kPair > 32u && o != 0u)
+            {
+                bits |= (uint32_t)nb << (2u * (32u - o));
+                ibits |= ni << (32u - o);
+            }
+#pragma unroll
+            for (int j = 0; j < kPair; ++j)
+            {
+                mode[j] = 0u;
+                if ((uint32_t)(2 * j) < nbase)
+                {
+                    key = (key << 2) | ((bits >> (4 * j)) & 3u);
+                    run = ((ibits >> (2 * j)) & 1u) ? 0u : run + 1u;
+                    mode[j] = run >= k ? 1u : 0u;
+                }
+                key_a[j] = key;
+                if ((uint32_t)(2 * j + 1) < nbase)
+                {
+                    key = (key << 2) | ((bits >> (4 * j + 2)) & 3u);
+                    run = ((ibits >> (2 * j + 1)) & 1u) ? 0u : run + 1u;
+                    mode[j] |= run >= k ? 2u : 0u;
+                }
+                key_b[j] = key;
+                if (mode[j] == 3u)
+                {
+                    const uint64_t h = (key * kp.mul) & kp.mask_b;
+                    pb[j] = (uint32_t)(h >> kp.rbits);
+                    const uint64_t want = h & kp.rmask;
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                 : "l"(kp.slots + 4ull * pb[j]));
+                }
+            }
+            t += nbase;
+            if (o + nbase >= 32u) next_group();
+            // ---- pairs: one probe answers both windows
+#pragma unroll
+            for (int j = 0; j < kPair; ++j)
+            {
+                c_total += (mode[j] & 1u) + (mode[j] >> 1);       // ++total_kmers (src/fm_scanner.cpp:164)
+                if (mode[j] != 3u) continue;
+                n_probe += 1u;
+                uint32_t d = 0u;
+                while (true)
+                {
+                    const bool h0 = (((w[j][0] ^ want_lo[j]) & pmask_lo) | ((w[j][1] ^ want_hi[j]) & pmask_hi)) == 0u;
+                    const bool h1 = (((w[j][2] ^ want_lo[j]) & pmask_lo) | ((w[j][3] ^ want_hi[j]) & pmask_hi)) == 0u;
+                    const bool h2 = (((w[j][4] ^ want_lo[j]) & pmask_lo) | ((w[j][5] ^ want_hi[j]) & pmask_hi)) == 0u;
+                    const bool h3 = (((w[j][6] ^ want_lo[j]) & pmask_lo) | ((w[j][7] ^ want_hi[j]) & pmask_hi)) == 0u;
+                    if (h0 || h1 || h2 || h3)
+                    {
+                        const uint32_t vv = (h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7]) >> 16;
+                        if (RECORD) atomicAdd(pair_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
+                        const uint32_t v1 = vv & 0xFFu, v2 = vv >> 8;
+                        if (v1 != 0xFFu) tally(v1, t0 + 2u * (uint32_t)j + 1u);
+                        if (v2 != 0xFFu) tally(v2, t0 + 2u * (uint32_t)j + 2u);
+                        mode[j] = 0u;                             // answered
+                        break;
+                    }
+                    if ((w[j][6] & w[j][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;   // not a (k+1)-mer of the index
+                    d += 1u;
+                    n_probe += 1u;
+                    pb[j] = (pb[j] + 1u) & kp.nbmask;
+                    const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kp.rbits);
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                 : "l"(kp.slots + 4ull * pb[j]));
+                }
+            }
+            // ---- what is left: unpaired windows and the halves of missed pairs go through the k-mer table, all first probes
+            //      issued together (w[] of the pairs is dead by now)
+            {
+                uint32_t sw[2 * kPair][8];
+                uint32_t sb[2 * kPair], sl[2 * kPair], sh_[2 * kPair];
+#pragma unroll
+                for (int i = 0; i < 2 * kPair; ++i)
+                {
+                    if (!((mode[i >> 1] >> (i & 1)) & 1u)) continue;
+                    const uint64_t h = (((i & 1) ? key_b[i >> 1] : key_a[i >> 1]) * kt.mul) & kt.mask_b;
+                    sb[i] = (uint32_t)(h >> kt.rbits);
+                    const uint64_t want = h & kt.rmask;
+                    sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(sw[i][0]), "=r"(sw[i][1]), "=r"(sw[i][2]), "=r"(sw[i][3]), "=r"(sw[i][4]), "=r"(sw[i][5]), "=r"(sw[i][6]), "=r"(sw[i][7])
+                                 : "l"(kt.slots + 4ull * sb[i]));
+                }
+#pragma unroll
+                for (int i = 0; i < 2 * kPair; ++i)
+                {
+                    if (!((mode[i >> 1] >> (i & 1)) & 1u)) continue;
+                    n_probe += 1u;
+                    uint32_t d = 0u;
+                    while (true)
+                    {
+                        const bool h0 = (((sw[i][0] ^ sl[i]) & tmask_lo) | ((sw[i][1] ^ sh_[i]) & tmask_hi)) == 0u;
+                        const bool h1 = (((sw[i][2] ^ sl[i]) & tmask_lo) | ((sw[i][3] ^ sh_[i]) & tmask_hi)) == 0u;
+                        const bool h2 = (((sw[i][4] ^ sl[i]) & tmask_lo) | ((sw[i][5] ^ sh_[i]) & tmask_hi)) == 0u;
+                        const bool h3 = (((sw[i][6] ^ sl[i]) & tmask_lo) | ((sw[i][7] ^ sh_[i]) & tmask_hi)) == 0u;
+                        if (h0 || h1 || h2 || h3)
+                        {
+                            const uint32_t g = (h0 ? sw[i][1] : h1 ? sw[i][3] : h2 ? sw[i][5] : sw[i][7]) >> 16;
+                            if (RECORD) atomicAdd(slot_mult + 4ull * sb[i] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
+                            if (g != kValMulti) tally(g, t0 + (uint32_t)i + 1u);
+                            break;
+                        }
+                        if ((sw[i][6] & sw[i][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;   // the k-mer does not occur in the index
+                        d += 1u;
+                        n_probe += 1u;
+                        sb[i] = (sb[i] + 1u) & kt.nbmask;
+                        const uint64_t want = u64of(sl[i], sh_[i]) + (1ull << kt.rbits);
+                        sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
+                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(sw[i][0]), "=r"(sw[i][1]), "=r"(sw[i][2]), "=r"(sw[i][3]), "=r"(sw[i][4]), "=r"(sw[i][5]), "=r"(sw[i][6]), "=r"(sw[i][7])
+                                     : "l"(kt.slots + 4ull * sb[i]));
+                    }
+                }
+            }
+        }
+        if (phase == H_RUN && t >= pend)
+        {
+            if (paired && !mate2) mate2 = true;
+            else
+            {
+                // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
+                n_total += c_total;
+                n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
+                c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+                agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
+                mate2 = false;
+                if ((n_total | n_look) & 0x80000000u)
+                {
+                    env.add64(0, n_total); env.add64(2, n_look);
+                    n_total = 0u; n_look = 0u;
+                }
+            }
+            phase = H_FETCH;
+        }
+    }
+    if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+    if (n_total) env.add64(0, n_total);
+    if (n_amb) env.add64(1, n_amb);
+    if (n_look) env.add64(2, n_look);
+    if (n_reads) env.add64(3, n_reads);
+    {
+        // sectors probed (table loads issued): one global atomic per warp
+        const uint32_t wp = __reduce_add_sync(kFullH, n_probe);
+        if (lane == 0u && wp) atomicAdd(a.scalars + SC_STEPS, (unsigned long long)wp);
+    }
     smem32_flush<LOCAL>(sm, a);
 }
 
@@ -459,6 +875,77 @@ cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, Ba
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, slot_mult, b, a, paired)))
+    return cudaGetLastError();
+}
+
+#define SPEQB_SCANP_DISPATCH(M, EXPR)                                                   \
+    switch (M)                                                                          \
+    {                                                                                   \
+        case 0: { auto kern = scanp_kernel<0>; EXPR; break; }                           \
+        case M_RECORD: { auto kern = scanp_kernel<M_RECORD>; EXPR; break; }             \
+        case M_LOCAL: { auto kern = scanp_kernel<M_LOCAL>; EXPR; break; }               \
+        case M_LOCAL | M_RECORD: { auto kern = scanp_kernel<M_LOCAL | M_RECORD>; EXPR; break; } \
+        default: return cudaErrorInvalidValue;                                          \
+    }
+
+cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
+{
+    const size_t smem = scan32_smem_bytes(V);
+    int bps = 0;
+    cudaError_t e = cudaSuccess;
+    const int m = mode & (M_LOCAL | M_RECORD);
+    SPEQB_SCANP_DISPATCH(m, {
+        if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlockH, smem);
+    })
+    if (e != cudaSuccess) return e;
+    if (bps <= 0) return cudaErrorLaunchOutOfResources;
+    cfg->block = kBlockH;
+    cfg->grid = sm_count_h() * bps;
+    return cudaSuccess;
+}
+
+cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long long * slot_mult, unsigned long long * pair_mult,
+                         BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg, cudaStream_t st)
+{
+    const size_t smem = scan32_smem_bytes(a.V);
+    const int paired = (mode & M_PAIRED) ? 1 : 0;
+    const int m = mode & (M_LOCAL | M_RECORD);
+    cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    SPEQB_SCANP_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, kp, slot_mult, pair_mult, b, a, paired)))
+    return cudaGetLastError();
+}
+
+// the pair table: every N-free (k+1)-mer of the texts -> the values of its two k-mers (looked up in the k-mer table kt)
+cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
+                               uint32_t n_texts, uint32_t max_len, KTabView const & kt, KTabView const & kp, uint32_t k,
+                               unsigned long long * n_keys, cudaStream_t st)
+{
+    cudaError_t e = cudaMemsetAsync(kp.slots, 0xFF, ((size_t)kp.nbmask + 1) * 32, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(n_keys, 0, 16, st);
+    if (e != cudaSuccess) return e;
+    if (n_texts == 0 || max_len < k + 1) return cudaSuccess;
+    const uint32_t groups = (max_len + 31u) / 32u;
+    const uint32_t gx = std::min<uint32_t>((groups + kBlockH - 1) / kBlockH, (uint32_t)sm_count_h() * 8u);
+    for (uint32_t t0 = 0; t0 < n_texts; t0 += 65535u)
+    {
+        const uint32_t nt = std::min<uint32_t>(65535u, n_texts - t0);
+        kpair_build_kernel<<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, kt, kp, k, n_keys);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_kpair_lb(KTabView const & kp, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st)
+{
+    kpair_lb_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kp, ix, k, slot_lb);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_kpair_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
+                                   cudaStream_t st)
+{
+    kpair_fold_mult_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(slot_mult, slot_lb, n_slots, mult);
     return cudaGetLastError();
 }
 

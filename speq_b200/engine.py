@@ -193,6 +193,7 @@ class ScanResult:
     lookups: int
     reads: int
     kernel_launches: int
+    probes: int = 0           # table algorithms: 32-byte table probes issued
 
 
 class Scan:
@@ -226,7 +227,7 @@ class Scan:
         w = np.zeros(self.V, np.float64)
         c = capi.Counts()
         capi.check(capi.lib().speqg_scan_finish(self.h, u.ctypes.data, w.ctypes.data, C.byref(c)))
-        return ScanResult(u, w, int(c.total_kmers), int(c.ambiguous_reads), int(c.lookups), int(c.reads), int(c.kernel_launches))
+        return ScanResult(u, w, int(c.total_kmers), int(c.ambiguous_reads), int(c.lookups), int(c.reads), int(c.kernel_launches), int(c.steps_executed))
 
     def stats(self, b: DeviceBatch) -> dict:
         c = capi.Counts()

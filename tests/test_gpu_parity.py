@@ -53,7 +53,8 @@ def test_golden(lib, name, raw):
 
 @pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
 @pytest.mark.parametrize("raw", [True, False])
-def test_golden_ktable_algorithm(lib, name, raw):
+@pytest.mark.parametrize("algorithm", [capi.ALGO_KTABLE, capi.ALGO_KPAIR])
+def test_golden_ktable_algorithm(lib, name, raw, algorithm):
     """The k-mer table scan (one probe per window) against the same fixtures, all modes, with the refinement running on
     multiplicities recorded per table slot."""
     fx = helpers.load_golden(name)
@@ -61,7 +62,7 @@ def test_golden_ktable_algorithm(lib, name, raw):
     scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
     out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
                          fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], raw=raw, batch_reads=64,
-                         algorithm=capi.ALGO_KTABLE)
+                         algorithm=algorithm)
     _compare(out, exp, len(counts))
 
 
@@ -94,7 +95,7 @@ def test_reference_work_counters(lib):
     sc.close(); db.close(); idx.close()
 
 
-@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE])
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR])
 @pytest.mark.parametrize("mode", ["global", "local", "global_paired"])
 def test_vs_oracle_c1_like(lib, oracle_bin, tmp_path, mode, algorithm):
     """C1-shaped input (2 variants x 3 isolates x 30 kb, 150 bp reads, k=21) at a read count the oracle finishes in seconds."""
@@ -122,7 +123,7 @@ def test_vs_oracle_c1_like(lib, oracle_bin, tmp_path, mode, algorithm):
     _compare(out, exp, sh.V)
 
 
-@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE])
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR])
 def test_edge_cases(lib, algorithm):
     scaff = [engine.ascii_to_ranks("ACGTTGCAAGGCTTAACCGGTTAGCATCGA"), engine.ascii_to_ranks("ACGTTGCATGGCTTAACCGGTAAGCATCGA")]
     idx = engine.Index.from_scaffolds(scaff, [0, 1], 2)
@@ -201,7 +202,7 @@ def test_properties_at_config_shapes(lib, cfg, R):
     c = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
     assert np.array_equal(a.unique, c.unique) and a.total_kmers == c.total_kmers and a.ambiguous == c.ambiguous
     # a ran the default (AUTO: the k-mer table for k <= 31); the rolling FM search and the explicit table must agree
-    for alg in (capi.ALGO_ROLLING, capi.ALGO_KTABLE):
+    for alg in (capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR):
         d = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=alg)
         assert np.array_equal(a.unique, d.unique) and a.total_kmers == d.total_kmers and a.ambiguous == d.ambiguous
         assert d.lookups == a.lookups and d.reads == a.reads
@@ -223,13 +224,15 @@ def test_properties_at_config_shapes(lib, cfg, R):
     tk = sc.refine(np.full(sh.V, 100.0 / sh.V), np.full(sh.V, sh.I, np.int32))
     assert abs(tk.sum() - r0.total_kmers) <= 1e-9 * r0.total_kmers
     # the same through the k-mer table: multiplicities recorded per slot, folded to interval starts before the estimate
-    sk = engine.Scan(idx, k=sh.k, record=True, algorithm=capi.ALGO_KTABLE)
-    sk.submit_raw(s0.cpu().numpy().reshape(-1), q0.cpu().numpy().reshape(-1), np.arange(n0 + 1, dtype=np.uint64) * sh.L, n0)
-    rk = sk.finish()
-    assert rk.total_kmers == r0.total_kmers and np.array_equal(rk.unique, r0.unique)
-    tkk = sk.refine(np.full(sh.V, 100.0 / sh.V), np.full(sh.V, sh.I, np.int32))
-    assert helpers.rel_close(tkk, tk, 1e-11)
-    sk.close()
+    for alg in (capi.ALGO_KTABLE, capi.ALGO_KPAIR):
+        sk = engine.Scan(idx, k=sh.k, record=True, algorithm=alg)
+        sk.submit_raw(s0.cpu().numpy().reshape(-1), q0.cpu().numpy().reshape(-1), np.arange(n0 + 1, dtype=np.uint64) * sh.L, n0)
+        rk = sk.finish()
+        assert rk.total_kmers == r0.total_kmers and np.array_equal(rk.unique, r0.unique)
+        tkk = sk.refine(np.full(sh.V, 100.0 / sh.V), np.full(sh.V, sh.I, np.int32))
+        assert helpers.rel_close(tkk, tk, 1e-11)
+        assert sk.multiplicity_count() == sc.multiplicity_count()       # the same set of SA intervals was recorded
+        sk.close()
     sc.close()
     idx.close()
     del refs
@@ -279,6 +282,8 @@ def test_many_variants_u16_groups(lib):
     c = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_ROLLING64)
     d = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_KTABLE)
     e = _scan_tallies(idx, 15, seq, qual, offs, algorithm=capi.ALGO_ROLLING)
+    with pytest.raises(capi.SpeqError):
+        engine.Scan(idx, k=15, algorithm=capi.ALGO_KPAIR)          # one byte per k-mer: at most 254 variants
     assert a.unique.sum() > 0
     for o in (b, c, d, e):
         assert np.array_equal(a.unique, o.unique) and a.total_kmers == o.total_kmers and a.ambiguous == o.ambiguous
@@ -311,7 +316,10 @@ def test_ktable_k_range(lib, k):
     qual = np.where(rng.random(seq.size) < 0.01, ord("#"), ord("I")).astype(np.uint8)
     offs = np.arange(R + 1, dtype=np.uint64) * L
     for paired in (False, True):
+        p = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_KPAIR, paired=paired)
         a = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_KTABLE, paired=paired)
+        assert np.array_equal(a.unique, p.unique) and a.total_kmers == p.total_kmers and a.ambiguous == p.ambiguous
+        assert 0 < p.probes <= a.probes
         b = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_ROLLING, paired=paired)
         c = _scan_tallies(idx, k, seq, qual, offs, algorithm=capi.ALGO_DIRECT, paired=paired)
         assert a.total_kmers > 0
