@@ -392,6 +392,27 @@ def main() -> None:
     kern_ms = k0.elapsed_time(k1) / args.steps
     scan.finish()
 
+    # ---- the same resident step with record_multiplicity = 1 (what `speq scan` runs: per-k-mer counts for the refinement) ----
+    rec = None
+    if rank == 0 and algo != capi.ALGO_DIRECT:
+        rscan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, record=True, algorithm=algo_req, device=local_rank,
+                            stream=stream.cuda_stream)
+        for _ in range(2):
+            rscan.reset(); rscan.submit_device(db)
+        torch.cuda.synchronize()
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        rscan.reset()
+        r0.record(stream)
+        for _ in range(args.steps):
+            rscan.submit_device(db)
+        r1.record(stream)
+        torch.cuda.synchronize()
+        rr_ = rscan.finish()
+        rec_ms = r0.elapsed_time(r1) / args.steps
+        rec = {"kernel_ms": rec_ms, "value": rr_.lookups / args.steps / (rec_ms * 1e-3), "unit": UNIT,
+               "note": "one GPU, resident batch, scan kernel with one 8-byte atomic per hit window on top"}
+        rscan.close()
+
     # ---- cross-check outside every timed region: the k-mer table scan must reproduce the rolling FM search bit for bit
     cross = None
     if algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR):
@@ -483,6 +504,15 @@ def main() -> None:
                 "note": "algorithmic bytes follow the reference's per-window search (k steps from the root); the rolling kernel "
                         "shares search state between overlapping windows and the k-mer table kernel memoises the search, so their "
                         f"real traffic is lower (own_sectors); index footprint {idx.device_bytes/1e6:.0f} MB"}
+        # dram__bytes_read + write of this kernel from the committed `ncu --set full` capture, scaled from the captured launch to
+        # this launch by the number of reads (per-read traffic does not depend on the launch size: input stream + table misses)
+        try:
+            tj = json.loads((ROOT / "profiles" / "r1_traffic.json").read_text()).get(f"{args.config}:{roof['kernel']}")
+            if tj:
+                roof["traffic"] = tj["dram_bytes_per_read"] * R
+                roof["traffic_source"] = tj["source"]
+        except Exception:
+            pass
         # what the kernel itself must move: one 32-byte sector per valid window (ktable) / two per read base (rolling), plus
         # the packed input stream; against the HBM peak when the structure misses L2, else informative only
         table = algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR)
@@ -513,7 +543,7 @@ def main() -> None:
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u64", "data": "synthetic", "config": dict(config, l2="inputs larger than L2: %d MB of packed reads per step" % (packed_bytes >> 20)),
                 "reads_per_sec": reads_step * args.steps / (ms_total * 1e-3),
-                "clocks": clk, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu,
+                "clocks": clk, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu, "record_mode": rec,
                 "tallies": {"unique": [int(x) for x in tall[:V]], "total_kmers": int(tall[V]), "ambiguous": int(tall[V + 1])},
                 "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack, "scan_open_s": t_scan_open, "numa": numa},
                 "cross_check": cross}
