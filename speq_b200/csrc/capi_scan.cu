@@ -64,17 +64,15 @@ struct speqg_scan
     DevIndex view{};               // di->view with `blocks` replaced by this scan's k-specialised copy
     KBlock * d_blocks_k = nullptr;   // SPEQG_ALGO_ROLLING64 only
     FBlock * d_sblk = nullptr;       // per-k blocks of the product kernel (SBlock + variant bytes)
-    // SPEQG_ALGO_KTABLE: the per-(index, k) k-mer table and, with record_multiplicity, per-slot counts + interval starts
+    // SPEQG_ALGO_KTABLE: the per-(index, k) k-mer table and, with record_multiplicity, per-slot counts
     KTabView kt{};
     unsigned long long * d_kstat = nullptr;   // [2]: keys stored, placement failure flag
     unsigned long long * d_slot_mult = nullptr;
-    uint32_t * d_slot_lb = nullptr;
     bool slot_mult_dirty = false;
     uint64_t ktab_keys = 0;
     // SPEQG_ALGO_KPAIR: the table over the (k+1)-mers (two windows per probe) next to the k-mer table
     KTabView kp{};
     unsigned long long * d_pair_mult = nullptr;
-    uint32_t * d_pair_lb = nullptr;
     uint64_t kpair_keys = 0;
     LaunchCfg cfg_p{};
     uint32_t algo = SPEQG_ALGO_ROLLING;   // resolved algorithm (AUTO -> KTABLE / ROLLING)
@@ -113,9 +111,8 @@ scan_refine_view refine_view(speqg_scan * s)
     if (s->slot_mult_dirty && s->d_mult)
     {
         device_guard guard(s->device);
-        CK(launch_ktable_fold_mult(s->d_slot_mult, s->d_slot_lb, 4ull * ((uint64_t)s->kt.nbmask + 1), s->d_mult, s->compute));
-        if (s->d_pair_mult)
-            CK(launch_kpair_fold_mult(s->d_pair_mult, s->d_pair_lb, 4ull * ((uint64_t)s->kp.nbmask + 1), s->d_mult, s->compute));
+        CK(launch_ktable_fold_mult(s->kt, s->view, s->p.k, s->d_slot_mult, s->d_mult, s->compute));
+        if (s->d_pair_mult) CK(launch_kpair_fold_mult(s->kp, s->view, s->p.k, s->d_pair_mult, s->d_mult, s->compute));
         s->slot_mult_dirty = false;
     }
     return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult,
@@ -130,8 +127,8 @@ void scan_release(speqg_scan * s)
     cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
     cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk); cudaFree(s->d_work);
-    cudaFree(s->kt.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_slot_lb); cudaFree(s->d_kstat);
-    cudaFree(s->kp.slots); cudaFree(s->d_pair_mult); cudaFree(s->d_pair_lb);
+    cudaFree(s->kt.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
+    cudaFree(s->kp.slots); cudaFree(s->d_pair_mult);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -285,9 +282,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             {
                 const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
                 s->d_slot_mult = dev_alloc<unsigned long long>(n_slots);
-                s->d_slot_lb = dev_alloc<uint32_t>(n_slots);
                 CK(cudaMemsetAsync(s->d_slot_mult, 0, n_slots * 8, s->compute));
-                CK(launch_ktable_lb(s->kt, s->view, params->k, s->d_slot_lb, s->compute));
             }
             CK(scanh_launch_cfg(s->mode, V, &s->cfg_h));
             if (auto_algo && idx->host.V <= kMaxGroupsPair)
@@ -321,9 +316,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 {
                     const uint64_t n_slots = 4ull * ((uint64_t)s->kp.nbmask + 1);
                     s->d_pair_mult = dev_alloc<unsigned long long>(n_slots);
-                    s->d_pair_lb = dev_alloc<uint32_t>(2 * n_slots);
                     CK(cudaMemsetAsync(s->d_pair_mult, 0, n_slots * 8, s->compute));
-                    CK(launch_kpair_lb(s->kp, s->view, params->k, s->d_pair_lb, s->compute));
                 }
                 CK(scanp_launch_cfg(s->mode, V, &s->cfg_p));
             }

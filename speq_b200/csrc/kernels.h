@@ -93,9 +93,8 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt);
 cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                 const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
                                 unsigned long long * n_keys, cudaStream_t st);
-cudaError_t launch_ktable_lb(KTabView const & kt, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st);
-cudaError_t launch_ktable_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
-                                    cudaStream_t st);
+cudaError_t launch_ktable_fold_mult(KTabView const & kt, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,
+                                    unsigned long long * mult, cudaStream_t st);
 cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
                          LaunchCfg cfg, cudaStream_t st);
 cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
@@ -103,9 +102,8 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, KTabView const & kp, uint32_t k,
                                unsigned long long * n_keys, cudaStream_t st);
-cudaError_t launch_kpair_lb(KTabView const & kp, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st);
-cudaError_t launch_kpair_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
-                                   cudaStream_t st);
+cudaError_t launch_kpair_fold_mult(KTabView const & kp, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,
+                                   unsigned long long * mult, cudaStream_t st);
 cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long long * slot_mult, unsigned long long * pair_mult,
                          BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg, cudaStream_t st);
 cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);

@@ -7,7 +7,7 @@
 //   ktable_build_kernel   walks the index's own texts (both strands of every scaffold, already resident as a packed batch)
 //                         and inserts every N-free k-mer: value = the variant of the text, or kValMulti once texts of two
 //                         variants hold it.
-//   ktable_lb_kernel      (record_multiplicity only) resolves each stored k-mer to the start of its SA interval with k
+//   ktable_fold_mult_kernel (record_multiplicity only) resolves every k-mer that was hit to the start of its SA interval with k
 //                         rank steps on the blocked BWT, so multiplicities recorded per slot reach the refinement kernel
 //                         as mult[lb] exactly as the rolling kernel records them.
 //   scanh_kernel          one lane per read (pair): rolls the 2-bit k-mer of the window (one shift per base) and probes
@@ -112,40 +112,27 @@ __global__ void __launch_bounds__(kBlockH) ktable_build_kernel(const uint64_t * 
     }
 }
 
-// slot -> start of the k-mer's SA interval (k rank steps from the root); kNoGroup for free slots
-__global__ void __launch_bounds__(kBlockH) ktable_lb_kernel(const KTabView kt, const DevIndex ix, const uint32_t k, uint32_t * __restrict__ slot_lb)
+// Multiplicities are recorded per table slot.  Before the refinement reads mult[] they are moved to the start of each
+// k-mer's SA interval -- what the rolling scan records: the hash is inverted to get the k-mer back, k rank steps from the root
+// give the interval (only slots that were hit pay for the search), and the slot counter is cleared.
+__global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(const KTabView kt, const DevIndex ix, const uint32_t k,
+                                                                   unsigned long long * __restrict__ slot_mult, unsigned long long * __restrict__ mult)
 {
     const uint64_t n_slots = 4ull * ((uint64_t)kt.nbmask + 1ull);
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
-    {
-        const uint64_t w = kt.slots[i];
-        uint32_t out = kNoGroup;
-        if (w != kSlotFree)
-        {
-            const uint32_t d = (uint32_t)(w >> kt.rbits) & 7u;
-            const uint32_t home = ((uint32_t)(i >> 2) - d) & kt.nbmask;
-            const uint64_t h = ((uint64_t)home << kt.rbits) | (w & kt.rmask);
-            const uint64_t key = (h * kt.mul_inv) & kt.mask_b;
-            uint32_t lb = 0u, rb = ix.n - 1u;
-            bool ok = true;
-            for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - 1u - j))) & 3u);
-            if (ok) out = lb;
-        }
-        slot_lb[i] = out;
-    }
-}
-
-// mult[lb] += per-slot multiplicities (and clear them): the refinement kernel reads mult[] as the rolling scan leaves it
-__global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(unsigned long long * __restrict__ slot_mult, const uint32_t * __restrict__ slot_lb,
-                                                                   const uint64_t n_slots, unsigned long long * __restrict__ mult)
-{
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
     {
         const unsigned long long m = slot_mult[i];
         if (m == 0ull) continue;
         slot_mult[i] = 0ull;
-        const uint32_t lb = slot_lb[i];
-        if (lb != kNoGroup) atomicAdd(mult + lb, m);
+        const uint64_t w = kt.slots[i];
+        const uint32_t d = (uint32_t)(w >> kt.rbits) & 7u;
+        const uint32_t home = ((uint32_t)(i >> 2) - d) & kt.nbmask;
+        const uint64_t h = ((uint64_t)home << kt.rbits) | (w & kt.rmask);
+        const uint64_t key = (h * kt.mul_inv) & kt.mask_b;          // k bases, the first in the highest digit
+        uint32_t lb = 0u, rb = ix.n - 1u;
+        bool ok = true;
+        for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - 1u - j))) & 3u);
+        if (ok) atomicAdd(mult + lb, m);
     }
 }
 
@@ -474,43 +461,28 @@ __global__ void __launch_bounds__(kBlockH) kpair_build_kernel(const uint64_t * _
     }
 }
 
-// pair slot -> interval starts of its two k-mers
-__global__ void __launch_bounds__(kBlockH) kpair_lb_kernel(const KTabView kp, const DevIndex ix, const uint32_t k, uint32_t * __restrict__ slot_lb)
+// the same for the pair table: a hit counted both k-mers of the stored (k+1)-mer
+__global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(const KTabView kp, const DevIndex ix, const uint32_t k,
+                                                                  unsigned long long * __restrict__ slot_mult, unsigned long long * __restrict__ mult)
 {
     const uint64_t n_slots = 4ull * ((uint64_t)kp.nbmask + 1ull);
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
-    {
-        const uint64_t w = kp.slots[i];
-        uint32_t out[2] = {kNoGroup, kNoGroup};
-        if (w != kSlotFree)
-        {
-            const uint32_t d = (uint32_t)(w >> kp.rbits) & 7u;
-            const uint32_t home = ((uint32_t)(i >> 2) - d) & kp.nbmask;
-            const uint64_t h = ((uint64_t)home << kp.rbits) | (w & kp.rmask);
-            const uint64_t key = (h * kp.mul_inv) & kp.mask_b;      // k+1 bases, the first in the highest digit
-            for (uint32_t which = 0; which < 2u; ++which)
-            {
-                uint32_t lb = 0u, rb = ix.n - 1u;
-                bool ok = true;
-                for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - (j + which)))) & 3u);
-                if (ok) out[which] = lb;
-            }
-        }
-        slot_lb[2 * i] = out[0];
-        slot_lb[2 * i + 1] = out[1];
-    }
-}
-
-__global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(unsigned long long * __restrict__ slot_mult, const uint32_t * __restrict__ slot_lb,
-                                                                  const uint64_t n_slots, unsigned long long * __restrict__ mult)
-{
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
     {
         const unsigned long long m = slot_mult[i];
         if (m == 0ull) continue;
         slot_mult[i] = 0ull;
-        if (slot_lb[2 * i] != kNoGroup) atomicAdd(mult + slot_lb[2 * i], m);
-        if (slot_lb[2 * i + 1] != kNoGroup) atomicAdd(mult + slot_lb[2 * i + 1], m);
+        const uint64_t w = kp.slots[i];
+        const uint32_t d = (uint32_t)(w >> kp.rbits) & 7u;
+        const uint32_t home = ((uint32_t)(i >> 2) - d) & kp.nbmask;
+        const uint64_t h = ((uint64_t)home << kp.rbits) | (w & kp.rmask);
+        const uint64_t key = (h * kp.mul_inv) & kp.mask_b;          // k+1 bases, the first in the highest digit
+        for (uint32_t which = 0; which < 2u; ++which)
+        {
+            uint32_t lb = 0u, rb = ix.n - 1u;
+            bool ok = true;
+            for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - (j + which)))) & 3u);
+            if (ok) atomicAdd(mult + lb, m);
+        }
     }
 }
 
@@ -936,16 +908,10 @@ cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv,
     return cudaGetLastError();
 }
 
-cudaError_t launch_kpair_lb(KTabView const & kp, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st)
+cudaError_t launch_kpair_fold_mult(KTabView const & kp, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,
+                                   unsigned long long * mult, cudaStream_t st)
 {
-    kpair_lb_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kp, ix, k, slot_lb);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_kpair_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
-                                   cudaStream_t st)
-{
-    kpair_fold_mult_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(slot_mult, slot_lb, n_slots, mult);
+    kpair_fold_mult_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kp, ix, k, slot_mult, mult);
     return cudaGetLastError();
 }
 
@@ -969,16 +935,10 @@ cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv
     return cudaGetLastError();
 }
 
-cudaError_t launch_ktable_lb(KTabView const & kt, DevIndex const & ix, uint32_t k, uint32_t * slot_lb, cudaStream_t st)
+cudaError_t launch_ktable_fold_mult(KTabView const & kt, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,
+                                    unsigned long long * mult, cudaStream_t st)
 {
-    ktable_lb_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt, ix, k, slot_lb);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_ktable_fold_mult(unsigned long long * slot_mult, const uint32_t * slot_lb, uint64_t n_slots, unsigned long long * mult,
-                                    cudaStream_t st)
-{
-    ktable_fold_mult_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(slot_mult, slot_lb, n_slots, mult);
+    ktable_fold_mult_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt, ix, k, slot_mult, mult);
     return cudaGetLastError();
 }
 }   // namespace speqb

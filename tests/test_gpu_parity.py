@@ -194,6 +194,10 @@ def test_properties_at_config_shapes(lib, cfg, R):
     seq, qual = seq.cpu().numpy().reshape(-1), qual.cpu().numpy().reshape(-1)
     offs = np.arange(R + 1, dtype=np.uint64) * sh.L
     a = _scan_tallies(idx, sh.k, seq, qual, offs)
+    probe = engine.Scan(idx, k=sh.k)
+    # AUTO: the pair table only where the k-mer table cannot stay in L2 (C4)
+    assert probe.info()["algorithm"] == (capi.ALGO_KPAIR if cfg == "C4" else capi.ALGO_KTABLE)
+    probe.close()
     b = _scan_tallies(idx, sh.k, seq, qual, offs, algorithm=capi.ALGO_DIRECT)
     assert a.lookups == R * sh.windows_per_read == b.lookups
     assert a.total_kmers == b.total_kmers and a.ambiguous == b.ambiguous
