@@ -52,6 +52,8 @@ int speqg_device_count(int * count);
  * flags: SPEQG_BUILD_KEEP_SA keeps the suffix array for speqg_index_export (tests).
  * ------------------------------------------------------------------------------------------------------------------ */
 #define SPEQG_BUILD_KEEP_SA 1u
+#define SPEQG_BUILD_DEVICE_SA 2u   /* sort the suffixes on the current CUDA device (prefix doubling) instead of SA-IS on one
+                                      host core; same suffix array, SPEQG_ECUDA without a device */
 
 typedef struct speqg_index_info
 {

@@ -16,6 +16,7 @@ LIB_PATH = ROOT / "lib" / "libspeq_cuda.so"
 
 OK, EINVAL, ECUDA, EIO, ENOMEM, ESTATE = 0, -1, -2, -3, -4, -5
 BUILD_KEEP_SA = 1
+BUILD_DEVICE_SA = 2
 ENC_ASCII, ENC_RANK = 0, 1
 MODE_GLOBAL, MODE_LOCAL = 0, 1
 ALGO_ROLLING, ALGO_DIRECT, ALGO_ROLLING64, ALGO_KTABLE, ALGO_AUTO, ALGO_KPAIR = 0, 1, 2, 3, 4, 5

@@ -21,6 +21,11 @@
 
 namespace speqb
 {
+// suffix array of T[0, n) (symbols < 8, unique smallest sentinel last) by prefix doubling on the current device
+// (sa_device.cu); 0 or a CUDA error code, *msg its text.  Weak: this file is also compiled on its own by the CPU-tier
+// white-box tests (tests/sim), which have no CUDA objects to link.
+extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const char ** msg) __attribute__((weak));
+
 static const uint8_t kCodeOfRank[5] = {0, 1, 2, 0, 3};   // dna5 rank -> 2-bit code (N coded 0, flagged in inv)
 
 static void pack_text_as_read(uint8_t const * ranks, uint64_t len, uint64_t * bases, uint32_t * inv)
@@ -95,7 +100,15 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         tick = now;
     };
     std::vector<int32_t> SA(n);
-    suffix_array(T.data(), SA.data(), (int32_t)n, 7);
+    if (flags & SPEQG_BUILD_DEVICE_SA)
+    {
+        // prefix doubling on the current CUDA device (sa_device.cu); the suffix array is unique, so it equals SA-IS's
+        if (!speqb_device_suffix_array) throw api_error(SPEQG_ECUDA, "SPEQG_BUILD_DEVICE_SA: built without the device suffix sorter");
+        const char * msg = "";
+        if (speqb_device_suffix_array(T.data(), n, SA.data(), &msg) != 0)
+            throw api_error(SPEQG_ECUDA, std::string("suffix array on the device failed: ") + msg);
+    }
+    else suffix_array(T.data(), SA.data(), (int32_t)n, 7);
     lap("sa-is");
 
     // C[] (deps/seqan3/include/seqan3/search/fm_index/detail/csa_alphabet_strategy.hpp:84-117)

@@ -1,0 +1,155 @@
+// sa_device.cu -- suffix array of the indexed text on the GPU (SPEQG_BUILD_DEVICE_SA): prefix doubling.
+//
+// The reference sorts suffixes with divsufsort on one core (sdsl construct_sa.hpp:80-130); on the 2e8-symbol
+// text of the bacterial config the host SA-IS here needs ~19 s of the 38 s index build.  The suffix array of a text is
+// unique (the sentinel is the smallest symbol and occurs once), so any correct construction yields the array the
+// reference's index is built on; tests compare this one with the host SA-IS element by element.
+//
+// Round 0 sorts the suffixes by their first 21 symbols (3 bits each in one 63-bit key).  Round h sorts by the pair
+// (rank of suffix i, rank of suffix i + h), which orders by the first 2h symbols, and re-ranks; the depth doubles until
+// every rank is unique.  The sort and the scans are the CUDA toolkit's library primitives (cub::DeviceRadixSort,
+// cub::DeviceScan, cub::DeviceReduce -- a plain sort, like calling cuBLAS for a plain GEMM); the key building and
+// ranking kernels are below.  This is index construction, not the timed scan path.
+#include <cub/cub.cuh>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace speqb
+{
+namespace
+{
+constexpr int kBlk = 256;
+constexpr uint32_t kSyms0 = 21;   // symbols in the round-0 key (3 bits each)
+
+__global__ void sa_key0_kernel(const uint8_t * __restrict__ T, uint32_t n, uint64_t * __restrict__ key, uint32_t * __restrict__ sa)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        uint64_t k = 0;
+        for (uint32_t j = 0; j < kSyms0; ++j) k = (k << 3) | (i + j < n ? (uint64_t)T[i + j] : 0ull);
+        key[i] = k;
+        sa[i] = i;
+    }
+}
+
+// head[p] = p when the sorted key at p differs from its predecessor (a new group starts), else 0
+__global__ void sa_heads_kernel(const uint64_t * __restrict__ key, uint32_t n, uint32_t * __restrict__ head)
+{
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x)
+        head[p] = (p == 0 || key[p] != key[p - 1]) ? p : 0u;
+}
+
+// after the inclusive max-scan head[p] is the first position of p's group: that is the rank of suffix sa[p];
+// singles counts the positions that start a group (all n of them once the order is total)
+__global__ void sa_rank_kernel(const uint32_t * __restrict__ sa, const uint32_t * __restrict__ head, uint32_t n, uint32_t * __restrict__ rank)
+{
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) rank[sa[p]] = head[p];
+}
+
+__global__ void sa_count_heads_kernel(const uint32_t * __restrict__ head, uint32_t n, unsigned long long * __restrict__ out)
+{
+    unsigned long long c = 0;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) c += (p == 0 || head[p] != 0u) ? 1u : 0u;
+    c = __reduce_add_sync(0xFFFFFFFFu, (unsigned)c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// key of round h for the suffix at sorted position p: (rank[i], rank[i + h] + 1), 0 when i + h runs off the text
+__global__ void sa_keyh_kernel(const uint32_t * __restrict__ sa, const uint32_t * __restrict__ rank, uint32_t n, uint32_t h,
+                               uint64_t * __restrict__ key)
+{
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x)
+    {
+        const uint32_t i = sa[p];
+        const uint64_t hi = rank[i];
+        const uint64_t lo = (uint64_t)i + h < n ? (uint64_t)rank[i + h] + 1ull : 0ull;
+        key[p] = (hi << 32) | lo;
+    }
+}
+}   // namespace
+
+#define SA_CK(x)                                     \
+    do                                               \
+    {                                                \
+        err = (x);                                   \
+        if (err != cudaSuccess) goto done;           \
+    } while (0)
+
+// T: n symbols on the host (values < 8, T[n-1] = 0 the unique smallest); SA: n entries on the host
+cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA)
+{
+    const uint32_t n = (uint32_t)n64;
+    cudaError_t err = cudaSuccess;
+    uint8_t * d_T = nullptr;
+    uint64_t * d_key = nullptr, * d_key2 = nullptr;
+    uint32_t * d_sa = nullptr, * d_sa2 = nullptr, * d_rank = nullptr, * d_head = nullptr;
+    unsigned long long * d_cnt = nullptr;
+    void * d_tmp = nullptr;
+    size_t tmp_sort = 0, tmp_scan = 0, tmp_bytes = 0;
+    int sms = 148, dev = 0;
+    cudaStream_t st = nullptr;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = sms * 8;
+    int rank_bits = 1;
+    while ((1ull << rank_bits) < (uint64_t)n + 1) ++rank_bits;
+
+    SA_CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    SA_CK(cudaMalloc(&d_T, n));
+    SA_CK(cudaMalloc(&d_key, (size_t)n * 8));
+    SA_CK(cudaMalloc(&d_key2, (size_t)n * 8));
+    SA_CK(cudaMalloc(&d_sa, (size_t)n * 4));
+    SA_CK(cudaMalloc(&d_sa2, (size_t)n * 4));
+    SA_CK(cudaMalloc(&d_rank, (size_t)n * 4));
+    SA_CK(cudaMalloc(&d_head, (size_t)n * 4));
+    SA_CK(cudaMalloc(&d_cnt, 8));
+    SA_CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, d_key, d_key2, d_sa, d_sa2, (int)n, 0, 64, st));
+    SA_CK(cub::DeviceScan::InclusiveScan(nullptr, tmp_scan, d_head, d_head, cub::Max(), (int)n, st));
+    tmp_bytes = tmp_sort > tmp_scan ? tmp_sort : tmp_scan;
+    SA_CK(cudaMalloc(&d_tmp, tmp_bytes));
+    SA_CK(cudaMemcpyAsync(d_T, T, n, cudaMemcpyHostToDevice, st));
+
+    sa_key0_kernel<<<grid, kBlk, 0, st>>>(d_T, n, d_key, d_sa);
+    for (uint32_t h = kSyms0, round = 0;; ++round)
+    {
+        // sort (key, suffix); round 0 keys use 63 bits, later keys (rank, rank + 1) use rank_bits + 1 bits in each half
+        const int end_bit = round == 0 ? 63 : 32 + rank_bits;
+        SA_CK(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_key, d_key2, d_sa, d_sa2, (int)n, 0, end_bit, st));
+        {
+            uint64_t * tk = d_key; d_key = d_key2; d_key2 = tk;
+            uint32_t * ts = d_sa; d_sa = d_sa2; d_sa2 = ts;
+        }
+        sa_heads_kernel<<<grid, kBlk, 0, st>>>(d_key, n, d_head);
+        SA_CK(cudaMemsetAsync(d_cnt, 0, 8, st));
+        sa_count_heads_kernel<<<grid, kBlk, 0, st>>>(d_head, n, d_cnt);
+        unsigned long long groups = 0;
+        SA_CK(cudaMemcpyAsync(&groups, d_cnt, 8, cudaMemcpyDeviceToHost, st));
+        SA_CK(cudaStreamSynchronize(st));
+        if (groups == n) break;                                   // every suffix has its own rank: the order is total
+        if (round > 40 || (uint64_t)h >= 2ull * n) { err = cudaErrorUnknown; goto done; }
+        SA_CK(cub::DeviceScan::InclusiveScan(d_tmp, tmp_bytes, d_head, d_head, cub::Max(), (int)n, st));
+        sa_rank_kernel<<<grid, kBlk, 0, st>>>(d_sa, d_head, n, d_rank);
+        sa_keyh_kernel<<<grid, kBlk, 0, st>>>(d_sa, d_rank, n, h, d_key);
+        h = h > 0x40000000u ? 0x80000000u : h * 2u;
+    }
+    SA_CK(cudaGetLastError());
+    SA_CK(cudaMemcpyAsync(SA, d_sa, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    SA_CK(cudaStreamSynchronize(st));
+done:
+    cudaFree(d_T); cudaFree(d_key); cudaFree(d_key2); cudaFree(d_sa); cudaFree(d_sa2); cudaFree(d_rank); cudaFree(d_head);
+    cudaFree(d_cnt); cudaFree(d_tmp);
+    if (st) cudaStreamDestroy(st);
+    return err;
+}
+}   // namespace speqb
+
+extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const char ** msg)
+{
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e == cudaSuccess && count == 0) e = cudaErrorNoDevice;
+    if (e == cudaSuccess) e = speqb::device_suffix_array(T, n, SA);
+    if (msg) *msg = cudaGetErrorString(e);
+    return (int)e;
+}

@@ -53,7 +53,7 @@ class Index:
         self.device_bytes = int(info.device_bytes)
 
     @classmethod
-    def from_texts(cls, texts: list[np.ndarray], group_of_text, n_groups: int, keep_sa: bool = False) -> "Index":
+    def from_texts(cls, texts: list[np.ndarray], group_of_text, n_groups: int, keep_sa: bool = False, device_sa: bool = False) -> "Index":
         S = len(texts)
         arrs = [np.ascontiguousarray(t, dtype=np.uint8) for t in texts]
         ptrs = (C.c_void_p * max(S, 1))(*[a.ctypes.data if a.size else None for a in arrs])
@@ -62,11 +62,13 @@ class Index:
         assert grp.size == S
         out = C.c_void_p()
         capi.check(capi.lib().speqg_index_build(ptrs, lens.ctypes.data_as(capi.u64p), S, grp.ctypes.data_as(capi.i32p),
-                                                n_groups, capi.BUILD_KEEP_SA if keep_sa else 0, C.byref(out)))
+                                                n_groups, (capi.BUILD_KEEP_SA if keep_sa else 0) | (capi.BUILD_DEVICE_SA if device_sa else 0),
+                                                C.byref(out)))
         return cls(out.value)
 
     @classmethod
-    def from_scaffolds(cls, scaffolds: list[np.ndarray], group_scaffolds, n_groups: int, keep_sa: bool = False) -> "Index":
+    def from_scaffolds(cls, scaffolds: list[np.ndarray], group_scaffolds, n_groups: int, keep_sa: bool = False,
+                       device_sa: bool = False) -> "Index":
         """scaffolds: dna5-rank arrays in FASTA order; group_scaffolds[j]: variant of scaffold j (file_to_map)."""
         texts, grp = [], []
         for j, s in enumerate(scaffolds):
@@ -74,7 +76,7 @@ class Index:
             texts.append(s)
             texts.append(revcomp_ranks(s))
             grp += [int(group_scaffolds[j])] * 2   # double_group_scaffolds, src/fm_scanner.cpp:74-77
-        return cls.from_texts(texts, grp, n_groups, keep_sa)
+        return cls.from_texts(texts, grp, n_groups, keep_sa, device_sa)
 
     @classmethod
     def load(cls, path: str) -> "Index":

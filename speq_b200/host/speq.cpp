@@ -162,8 +162,11 @@ void generate_fm_index(cmd_arguments & args, int64_t scaffold_time, int64_t grou
     std::vector<uint64_t> lens;
     for (auto const & t : texts) { ptrs.push_back(t.data()); lens.push_back(t.size()); }
     index_handle idx;
+    // with a CUDA device the suffixes are sorted there (prefix doubling); without one SA-IS runs on the host -- same index
+    int ndev = 0;
+    if (speqg_device_count(&ndev) != SPEQG_OK) ndev = 0;
     ck(speqg_index_build(ptrs.data(), lens.data(), static_cast<uint32_t>(texts.size()), group_of_text.data(),
-                         static_cast<uint32_t>(group_names.size()), 0, &idx.h), "speqg_index_build");
+                         static_cast<uint32_t>(group_names.size()), ndev > 0 ? SPEQG_BUILD_DEVICE_SA : 0u, &idx.h), "speqg_index_build");
     args.io_file_index.replace_extension(".idx");
     idx_meta m{args.in_file_references.string(), scaffold_time, group_time, group_names, group_scaffolds, group_counts, 0};
     uint64_t off = write_meta(args.io_file_index, m);

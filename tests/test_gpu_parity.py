@@ -331,3 +331,28 @@ def test_ktable_k_range(lib, k):
             assert np.array_equal(a.unique, o.unique) and a.total_kmers == o.total_kmers and a.ambiguous == o.ambiguous
             assert a.lookups == o.lookups
     idx.close()
+
+
+@pytest.mark.parametrize("case", ["random", "repeats", "collection"])
+def test_device_suffix_array_matches_host(lib, case):
+    """SPEQG_BUILD_DEVICE_SA: prefix doubling on the GPU yields the suffix array SA-IS builds on the host (it is unique), hence
+    the same index arrays; inputs with long repeats need many doubling rounds."""
+    rng = np.random.default_rng(7)
+    if case == "random":
+        texts = [rng.integers(0, 5, 5000).astype(np.uint8), rng.integers(0, 5, 1).astype(np.uint8), np.zeros(0, np.uint8)]
+    elif case == "repeats":
+        unit = rng.integers(0, 5, 37).astype(np.uint8)
+        texts = [np.tile(unit, 300), np.zeros(4000, np.uint8), np.tile(unit, 150)[5:]]
+    else:
+        sh = synth.CONFIGS["C1"]
+        refs = synth.make_refs(sh, 9)
+        texts = []
+        for s in synth.refs_to_ranks(refs):
+            texts += [s, engine.revcomp_ranks(s)]
+    grp = [i % 3 for i in range(len(texts))]
+    a = engine.Index.from_texts(texts, grp, 3, keep_sa=True)
+    b = engine.Index.from_texts(texts, grp, 3, keep_sa=True, device_sa=True)
+    ea, eb = a.export(sa=True), b.export(sa=True)
+    for key in ea:
+        assert np.array_equal(ea[key], eb[key]), key
+    a.close(); b.close()
