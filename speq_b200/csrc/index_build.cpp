@@ -24,7 +24,9 @@ namespace speqb
 // suffix array of T[0, n) (symbols < 8, unique smallest sentinel last) by prefix doubling on the current device
 // (sa_device.cu); 0 or a CUDA error code, *msg its text.  Weak: this file is also compiled on its own by the CPU-tier
 // white-box tests (tests/sim), which have no CUDA objects to link.
-extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const char ** msg) __attribute__((weak));
+// With owner != null it also returns bwt[i] = T[SA[i]-1], own[i] = owner[SA[i]] and lcp[i] = min(cap, lcp(SA[i-1], SA[i])).
+extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const uint16_t * owner, uint32_t lcp_cap,
+                                         uint8_t * bwt, uint16_t * own, uint8_t * lcp, const char ** msg) __attribute__((weak));
 
 static const uint8_t kCodeOfRank[5] = {0, 1, 2, 0, 3};   // dna5 rank -> 2-bit code (N coded 0, flagged in inv)
 
@@ -100,12 +102,18 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         tick = now;
     };
     std::vector<int32_t> SA(n);
+    // filled by the device path: the gathers through SA and the suffix comparisons (random accesses on the host)
+    std::vector<uint8_t> d_bwt, d_lcp;
+    std::vector<uint16_t> d_own;
     if (flags & SPEQG_BUILD_DEVICE_SA)
     {
         // prefix doubling on the current CUDA device (sa_device.cu); the suffix array is unique, so it equals SA-IS's
         if (!speqb_device_suffix_array) throw api_error(SPEQG_ECUDA, "SPEQG_BUILD_DEVICE_SA: built without the device suffix sorter");
         const char * msg = "";
-        if (speqb_device_suffix_array(T.data(), n, SA.data(), &msg) != 0)
+        std::vector<uint16_t> owner16(n);
+        for (uint64_t i = 0; i < n; ++i) owner16[i] = owner[i] == kNoGroup ? kNoGroup16 : (uint16_t)owner[i];
+        d_bwt.resize(n); d_own.resize(n); d_lcp.resize(n);
+        if (speqb_device_suffix_array(T.data(), n, SA.data(), owner16.data(), kLcpCap, d_bwt.data(), d_own.data(), d_lcp.data(), &msg) != 0)
             throw api_error(SPEQG_ECUDA, std::string("suffix array on the device failed: ") + msg);
     }
     else suffix_array(T.data(), SA.data(), (int32_t)n, 7);
@@ -132,7 +140,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         uint64_t b = i / kBlockSyms, j = i % kBlockSyms;
         KBlock & blk = h.blocks[b];
         if (j == 0) { blk.cnt[0] = run[0]; blk.cnt[1] = run[1]; blk.cnt[2] = run[2]; blk.cnt[3] = run[3]; blk.chgcum = chgcum; }
-        uint8_t sym = T[SA[i] ? SA[i] - 1 : n - 1];
+        uint8_t sym = !d_bwt.empty() ? d_bwt[i] : T[SA[i] ? SA[i] - 1 : n - 1];
         int8_t c2 = code_of_sym[sym];
         if (c2 < 0)
         {
@@ -145,7 +153,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
             ++run[c2];
         blk.lo[j / 32] |= uint32_t(c2 & 1) << (j % 32);
         blk.hi[j / 32] |= uint32_t((c2 >> 1) & 1) << (j % 32);
-        uint32_t g = owner[SA[i]];
+        uint32_t g = !d_own.empty() ? (d_own[i] == kNoGroup16 ? kNoGroup : (uint32_t)d_own[i]) : owner[SA[i]];
         h.grp[i] = g == kNoGroup ? kNoGroup16 : (uint16_t)g;
         if (i == 0 || g != prev_group)
         {
@@ -163,6 +171,12 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
     lap("bwt+grp");
     // capped LCP array (Kasai et al. 2001, with the cap folded in: lcp[rank[i+1]] >= lcp[rank[i]] - 1 also holds for
     // min(cap, lcp)).  The sentinel is unique, so the symbol comparison stops before either suffix runs off the text.
+    if (!d_lcp.empty())
+    {
+        h.lcp.assign(lcp_padded_size(n), 0);
+        memcpy(h.lcp.data(), d_lcp.data(), n);
+    }
+    else
     {
         std::vector<int32_t> rank(n);
         for (uint64_t i = 0; i < n; ++i) rank[SA[i]] = (int32_t)i;

@@ -67,6 +67,56 @@ __global__ void sa_keyh_kernel(const uint32_t * __restrict__ sa, const uint32_t 
         key[p] = (hi << 32) | lo;
     }
 }
+// ---- arrays derived from the suffix array: the random gathers and the suffix comparisons the host would do one by one
+// text as 4-bit symbols, 16 per word (symbol j of a word at bits [4j, 4j+4)), zero padded
+__global__ void sa_nibbles_kernel(const uint8_t * __restrict__ T, uint32_t n, uint64_t * __restrict__ nib, uint32_t n_words)
+{
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += gridDim.x * blockDim.x)
+    {
+        uint64_t v = 0;
+        for (uint32_t j = 0; j < 16u; ++j)
+        {
+            const uint64_t p = (uint64_t)w * 16u + j;
+            if (p < n) v |= (uint64_t)(T[p] & 15u) << (4u * j);
+        }
+        nib[w] = v;
+    }
+}
+
+__device__ __forceinline__ uint64_t nib16(const uint64_t * __restrict__ nib, uint32_t pos)
+{
+    const uint32_t w = pos >> 4, off = pos & 15u;
+    const uint64_t lo = nib[w] >> (4u * off);
+    return off ? lo | (nib[w + 1] << (64u - 4u * off)) : lo;
+}
+
+// bwt[i] = T[SA[i] - 1] (wrapping), own[i] = owner of text position SA[i], lcp[i] = min(cap, lcp(SA[i-1], SA[i])), lcp[0] = 0.
+// The sentinel is unique, so two different suffixes differ at or before the sentinel of the shorter one: the zero padding
+// behind the text is never compared as equal.
+__global__ void sa_derive_kernel(const uint8_t * __restrict__ T, const uint16_t * __restrict__ owner, const uint64_t * __restrict__ nib,
+                                 const uint32_t * __restrict__ sa, uint32_t n, uint32_t cap, uint8_t * __restrict__ bwt,
+                                 uint16_t * __restrict__ own, uint8_t * __restrict__ lcp)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        const uint32_t b = sa[i];
+        bwt[i] = T[b ? b - 1u : n - 1u];
+        own[i] = owner[b];
+        uint32_t l = 0;
+        if (i)
+        {
+            const uint32_t a = sa[i - 1];
+            while (l < cap)
+            {
+                const uint64_t x = nib16(nib, a + l) ^ nib16(nib, b + l);
+                if (x) { l += (uint32_t)(__ffsll((long long)x) - 1) >> 2; break; }
+                l += 16u;
+            }
+            l = l < cap ? l : cap;
+        }
+        lcp[i] = (uint8_t)l;
+    }
+}
 }   // namespace
 
 #define SA_CK(x)                                     \
@@ -77,7 +127,9 @@ __global__ void sa_keyh_kernel(const uint32_t * __restrict__ sa, const uint32_t 
     } while (0)
 
 // T: n symbols on the host (values < 8, T[n-1] = 0 the unique smallest); SA: n entries on the host
-cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA)
+// owner / bwt / own / lcp: optional (all or none) -- owner[p] = u16 group of text position p on the host; outputs n entries each
+cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA, const uint16_t * owner, uint32_t lcp_cap, uint8_t * bwt,
+                                uint16_t * own, uint8_t * lcp)
 {
     const uint32_t n = (uint32_t)n64;
     cudaError_t err = cudaSuccess;
@@ -85,6 +137,8 @@ cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA)
     uint64_t * d_key = nullptr, * d_key2 = nullptr;
     uint32_t * d_sa = nullptr, * d_sa2 = nullptr, * d_rank = nullptr, * d_head = nullptr;
     unsigned long long * d_cnt = nullptr;
+    uint16_t * d_owner = nullptr;
+    uint64_t * d_nib = nullptr;
     void * d_tmp = nullptr;
     size_t tmp_sort = 0, tmp_scan = 0, tmp_bytes = 0;
     int sms = 148, dev = 0;
@@ -136,7 +190,26 @@ cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA)
     SA_CK(cudaGetLastError());
     SA_CK(cudaMemcpyAsync(SA, d_sa, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     SA_CK(cudaStreamSynchronize(st));
+    if (owner)
+    {
+        // the sort buffers are free now: d_key holds the three output arrays (4 n + 1 bytes <= 8 n)
+        const uint32_t n_words = n / 16u + 10u;                    // + padding read by the last comparisons (cap + 16 symbols)
+        uint8_t * d_bwt = reinterpret_cast<uint8_t *>(d_key);
+        uint8_t * d_lcp = d_bwt + n;
+        uint16_t * d_own = reinterpret_cast<uint16_t *>(d_bwt + 2 * (size_t)n + (n & 1u));
+        SA_CK(cudaMalloc(&d_nib, (size_t)n_words * 8));
+        SA_CK(cudaMalloc(&d_owner, (size_t)n * 2));
+        SA_CK(cudaMemcpyAsync(d_owner, owner, (size_t)n * 2, cudaMemcpyHostToDevice, st));
+        sa_nibbles_kernel<<<grid, kBlk, 0, st>>>(d_T, n, d_nib, n_words);
+        sa_derive_kernel<<<grid, kBlk, 0, st>>>(d_T, d_owner, d_nib, d_sa, n, lcp_cap, d_bwt, d_own, d_lcp);
+        SA_CK(cudaGetLastError());
+        SA_CK(cudaMemcpyAsync(bwt, d_bwt, n, cudaMemcpyDeviceToHost, st));
+        SA_CK(cudaMemcpyAsync(lcp, d_lcp, n, cudaMemcpyDeviceToHost, st));
+        SA_CK(cudaMemcpyAsync(own, d_own, (size_t)n * 2, cudaMemcpyDeviceToHost, st));
+        SA_CK(cudaStreamSynchronize(st));
+    }
 done:
+    cudaFree(d_owner); cudaFree(d_nib);
     cudaFree(d_T); cudaFree(d_key); cudaFree(d_key2); cudaFree(d_sa); cudaFree(d_sa2); cudaFree(d_rank); cudaFree(d_head);
     cudaFree(d_cnt); cudaFree(d_tmp);
     if (st) cudaStreamDestroy(st);
@@ -144,12 +217,13 @@ done:
 }
 }   // namespace speqb
 
-extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const char ** msg)
+extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const uint16_t * owner, uint32_t lcp_cap,
+                                         uint8_t * bwt, uint16_t * own, uint8_t * lcp, const char ** msg)
 {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e == cudaSuccess && count == 0) e = cudaErrorNoDevice;
-    if (e == cudaSuccess) e = speqb::device_suffix_array(T, n, SA);
+    if (e == cudaSuccess) e = speqb::device_suffix_array(T, n, SA, owner, lcp_cap, bwt, own, lcp);
     if (msg) *msg = cudaGetErrorString(e);
     return (int)e;
 }
