@@ -26,7 +26,7 @@ namespace speqb
 // white-box tests (tests/sim), which have no CUDA objects to link.
 // With owner != null it also returns bwt[i] = T[SA[i]-1], own[i] = owner[SA[i]] and lcp[i] = min(cap, lcp(SA[i-1], SA[i])).
 extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const uint16_t * owner, uint32_t lcp_cap,
-                                         uint8_t * bwt, uint16_t * own, uint8_t * lcp, const char ** msg) __attribute__((weak));
+                                         uint8_t * bwt, uint16_t * own, uint8_t * lcp, uint32_t * pn, const char ** msg) __attribute__((weak));
 
 static const uint8_t kCodeOfRank[5] = {0, 1, 2, 0, 3};   // dna5 rank -> 2-bit code (N coded 0, flagged in inv)
 
@@ -113,7 +113,10 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
         std::vector<uint16_t> owner16(n);
         for (uint64_t i = 0; i < n; ++i) owner16[i] = owner[i] == kNoGroup ? kNoGroup16 : (uint16_t)owner[i];
         d_bwt.resize(n); d_own.resize(n); d_lcp.resize(n);
-        if (speqb_device_suffix_array(T.data(), n, SA.data(), owner16.data(), kLcpCap, d_bwt.data(), d_own.data(), d_lcp.data(), &msg) != 0)
+        h.pn.resize(n + 1);
+        static_assert(sizeof(uint2x) == 8, "pn entries are two u32");
+        if (speqb_device_suffix_array(T.data(), n, SA.data(), owner16.data(), kLcpCap, d_bwt.data(), d_own.data(), d_lcp.data(),
+                                      reinterpret_cast<uint32_t *>(h.pn.data()), &msg) != 0)
             throw api_error(SPEQG_ECUDA, std::string("suffix array on the device failed: ") + msg);
     }
     else suffix_array(T.data(), SA.data(), (int32_t)n, 7);
@@ -195,6 +198,7 @@ void build_host_index(uint8_t const * const * texts, uint64_t const * lens, uint
 
     lap("lcp");
     // previous / next smaller value links over the capped lcp array (lcp[n] = 0 closes every interval)
+    if (d_lcp.empty())
     {
         h.pn.assign(n + 1, uint2x{0u, (uint32_t)n});
         std::vector<uint32_t> stack;

@@ -117,6 +117,85 @@ __global__ void sa_derive_kernel(const uint8_t * __restrict__ T, const uint16_t 
         lcp[i] = (uint8_t)l;
     }
 }
+// ---- previous / next strictly smaller value over lcp[0, n] (lcp[n] = 0): two levels of block minima, so a search walks
+// at most one block of values, one superblock of block minima and the superblock minima
+constexpr uint32_t kPnB = 256;    // values per block, blocks per superblock
+
+__global__ void sa_blockmin_kernel(const uint8_t * __restrict__ v, uint32_t count, uint8_t * __restrict__ out, uint32_t n_out)
+{
+    for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < n_out; b += gridDim.x * blockDim.x)
+    {
+        uint32_t m = 255u;
+        const uint64_t lo = (uint64_t)b * kPnB, hi = lo + kPnB < count ? lo + kPnB : count;
+        for (uint64_t i = lo; i < hi; ++i) m = v[i] < m ? v[i] : m;
+        out[b] = (uint8_t)m;
+    }
+}
+
+// pn[i] = {largest j < i with lcp[j] < lcp[i] (0 when there is none), smallest j > i with lcp[j] < lcp[i] (n when none)}
+__global__ void sa_pn_kernel(const uint8_t * __restrict__ lcp, const uint8_t * __restrict__ bmin, const uint8_t * __restrict__ smin,
+                             uint32_t n, uint2 * __restrict__ pn)
+{
+    const uint32_t count = n + 1u;                                 // positions 0..n
+    const uint32_t nb = (count + kPnB - 1u) / kPnB, ns = (nb + kPnB - 1u) / kPnB;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    {
+        const uint32_t v = lcp[i];
+        uint32_t x = 0u, y = n;
+        if (v)
+        {
+            // ---- to the left
+            int64_t j = (int64_t)i - 1;
+            const int64_t blo = (int64_t)(i / kPnB) * kPnB;
+            while (j >= blo && lcp[j] >= v) --j;
+            if (j < blo && blo > 0)
+            {
+                int64_t b = (int64_t)(i / kPnB) - 1;                // blocks of the same superblock
+                const int64_t slo = (b + 1) / kPnB * kPnB;
+                while (b >= slo && bmin[b] >= v) --b;
+                if (b < slo)
+                {
+                    int64_t sb = slo / kPnB - 1;                    // superblocks
+                    while (sb >= 0 && smin[sb] >= v) --sb;
+                    b = -1;
+                    if (sb >= 0)
+                    {
+                        b = (sb + 1) * kPnB - 1;
+                        while (bmin[b] >= v) --b;
+                    }
+                }
+                j = -1;
+                if (b >= 0)
+                {
+                    j = (b + 1) * (int64_t)kPnB - 1;
+                    while (lcp[j] >= v) --j;
+                }
+            }
+            x = j >= 0 ? (uint32_t)j : 0u;
+            // ---- to the right (lcp[n] = 0 < v ends every search)
+            uint64_t r = (uint64_t)i + 1u;
+            const uint64_t bhi = ((uint64_t)(i / kPnB) + 1u) * kPnB < count ? ((uint64_t)(i / kPnB) + 1u) * kPnB : count;
+            while (r < bhi && lcp[r] >= v) ++r;
+            if (r == bhi && r < count)
+            {
+                uint64_t b = i / kPnB + 1u;
+                const uint64_t shi = (b / kPnB + 1u) * kPnB < nb ? (b / kPnB + 1u) * kPnB : nb;
+                while (b < shi && bmin[b] >= v) ++b;
+                if (b == shi)
+                {
+                    uint64_t sb = shi / kPnB;
+                    while (sb < ns && smin[sb] >= v) ++sb;
+                    b = sb * kPnB;
+                    while (bmin[b] >= v) ++b;
+                }
+                r = b * kPnB;
+                while (lcp[r] >= v) ++r;
+            }
+            y = (uint32_t)r;
+        }
+        pn[i] = make_uint2(x, y);
+    }
+}
 }   // namespace
 
 #define SA_CK(x)                                     \
@@ -128,8 +207,9 @@ __global__ void sa_derive_kernel(const uint8_t * __restrict__ T, const uint16_t 
 
 // T: n symbols on the host (values < 8, T[n-1] = 0 the unique smallest); SA: n entries on the host
 // owner / bwt / own / lcp: optional (all or none) -- owner[p] = u16 group of text position p on the host; outputs n entries each
+// pn: n + 1 pairs {previous, next strictly smaller lcp position}
 cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA, const uint16_t * owner, uint32_t lcp_cap, uint8_t * bwt,
-                                uint16_t * own, uint8_t * lcp)
+                                uint16_t * own, uint8_t * lcp, uint32_t * pn)
 {
     const uint32_t n = (uint32_t)n64;
     cudaError_t err = cudaSuccess;
@@ -139,6 +219,8 @@ cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA, c
     unsigned long long * d_cnt = nullptr;
     uint16_t * d_owner = nullptr;
     uint64_t * d_nib = nullptr;
+    uint8_t * d_min = nullptr;
+    uint2 * d_pn = nullptr;
     void * d_tmp = nullptr;
     size_t tmp_sort = 0, tmp_scan = 0, tmp_bytes = 0;
     int sms = 148, dev = 0;
@@ -207,9 +289,26 @@ cudaError_t device_suffix_array(const uint8_t * T, uint64_t n64, int32_t * SA, c
         SA_CK(cudaMemcpyAsync(lcp, d_lcp, n, cudaMemcpyDeviceToHost, st));
         SA_CK(cudaMemcpyAsync(own, d_own, (size_t)n * 2, cudaMemcpyDeviceToHost, st));
         SA_CK(cudaStreamSynchronize(st));
+        if (pn)
+        {
+            // lcp[0, n] with lcp[n] = 0 in d_key2 (free), minima behind it; the links go to d_key ((n + 1) * 8 bytes needs its
+            // own buffer: the outputs above have been copied out, d_key has n * 8)
+            const uint32_t count = n + 1u, nb = (count + kPnB - 1u) / kPnB, ns = (nb + kPnB - 1u) / kPnB;
+            uint8_t * d_l = reinterpret_cast<uint8_t *>(d_key2);
+            SA_CK(cudaMalloc(&d_min, (size_t)nb + ns + 16));
+            SA_CK(cudaMalloc(&d_pn, (size_t)count * 8));
+            SA_CK(cudaMemcpyAsync(d_l, d_lcp, n, cudaMemcpyDeviceToDevice, st));
+            SA_CK(cudaMemsetAsync(d_l + n, 0, 1, st));
+            sa_blockmin_kernel<<<grid, kBlk, 0, st>>>(d_l, count, d_min, nb);
+            sa_blockmin_kernel<<<grid, kBlk, 0, st>>>(d_min, nb, d_min + nb, ns);
+            sa_pn_kernel<<<grid, kBlk, 0, st>>>(d_l, d_min, d_min + nb, n, d_pn);
+            SA_CK(cudaGetLastError());
+            SA_CK(cudaMemcpyAsync(pn, d_pn, (size_t)count * 8, cudaMemcpyDeviceToHost, st));
+            SA_CK(cudaStreamSynchronize(st));
+        }
     }
 done:
-    cudaFree(d_owner); cudaFree(d_nib);
+    cudaFree(d_owner); cudaFree(d_nib); cudaFree(d_min); cudaFree(d_pn);
     cudaFree(d_T); cudaFree(d_key); cudaFree(d_key2); cudaFree(d_sa); cudaFree(d_sa2); cudaFree(d_rank); cudaFree(d_head);
     cudaFree(d_cnt); cudaFree(d_tmp);
     if (st) cudaStreamDestroy(st);
@@ -218,12 +317,12 @@ done:
 }   // namespace speqb
 
 extern "C" int speqb_device_suffix_array(const uint8_t * T, uint64_t n, int32_t * SA, const uint16_t * owner, uint32_t lcp_cap,
-                                         uint8_t * bwt, uint16_t * own, uint8_t * lcp, const char ** msg)
+                                         uint8_t * bwt, uint16_t * own, uint8_t * lcp, uint32_t * pn, const char ** msg)
 {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e == cudaSuccess && count == 0) e = cudaErrorNoDevice;
-    if (e == cudaSuccess) e = speqb::device_suffix_array(T, n, SA, owner, lcp_cap, bwt, own, lcp);
+    if (e == cudaSuccess) e = speqb::device_suffix_array(T, n, SA, owner, lcp_cap, bwt, own, lcp, pn);
     if (msg) *msg = cudaGetErrorString(e);
     return (int)e;
 }

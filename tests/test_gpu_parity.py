@@ -334,7 +334,7 @@ def test_ktable_k_range(lib, k):
 
 
 @pytest.mark.parametrize("case", ["random", "repeats", "collection"])
-def test_device_suffix_array_matches_host(lib, case):
+def test_device_suffix_array_matches_host(lib, case, tmp_path):
     """SPEQG_BUILD_DEVICE_SA: prefix doubling on the GPU yields the suffix array SA-IS builds on the host (it is unique), hence
     the same index arrays; inputs with long repeats need many doubling rounds."""
     rng = np.random.default_rng(7)
@@ -355,4 +355,7 @@ def test_device_suffix_array_matches_host(lib, case):
     ea, eb = a.export(sa=True), b.export(sa=True)
     for key in ea:
         assert np.array_equal(ea[key], eb[key]), key
+    # everything else the index stores (rank blocks, previous / next-smaller links, packed texts): the files are identical
+    a.save(str(tmp_path / "host.idx")); b.save(str(tmp_path / "device.idx"))
+    assert (tmp_path / "host.idx").read_bytes() == (tmp_path / "device.idx").read_bytes()
     a.close(); b.close()
