@@ -295,7 +295,7 @@ def main() -> None:
     if cpath is not None and cpath.exists():
         idx = engine.Index.load(str(cpath))
     else:
-        idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V)
+        idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V, device_sa=True)   # suffix sort etc. on the GPU
         if cpath is not None and rank == 0:
             cpath.parent.mkdir(parents=True, exist_ok=True)
             idx.save(str(cpath))
