@@ -27,7 +27,7 @@ struct cmd_arguments
     bool is_parsed{false};
     // additions of the B200 build (absent from the reference)
     unsigned int gpus{1};                 // --gpus N: devices the reads are sharded over (index replicated)
-    unsigned int batch_reads{1u << 20};   // --batch-reads: reads per C-ABI submit
+    unsigned int batch_reads{1u << 18};   // --batch-reads: reads per C-ABI submit (2 x 2 pinned buffers of 80 MB per device)
     std::filesystem::path json_path{};    // --json FILE: full-precision results for parity checks
 };
 
