@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -81,6 +82,10 @@ struct speqg_scan
     int mode = 0;
     cudaStream_t compute = nullptr, copy = nullptr;
     bool own_compute = false;
+    // the scan's counters live in one device block (one memset per reset, one copy per finish):
+    // unique[V] total_g[V] unique_w[V] scalars[SC_COUNT] bad[1] work[1]; h_state is its pinned host mirror
+    unsigned long long * d_state = nullptr, * h_state = nullptr;
+    size_t state_words = 0;
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
     double * d_unique_w = nullptr, * d_qden = nullptr, * d_percent = nullptr, * d_tkpg = nullptr, * d_partial = nullptr;
     int32_t * d_gc = nullptr;
@@ -124,9 +129,9 @@ namespace
 {
 void scan_release(speqg_scan * s)
 {
-    cudaFree(s->d_unique); cudaFree(s->d_total_g); cudaFree(s->d_scalars); cudaFree(s->d_mult); cudaFree(s->d_bad);
-    cudaFree(s->d_unique_w); cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
-    cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk); cudaFree(s->d_work);
+    cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_mult);
+    cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
+    cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
     cudaFree(s->kt.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
     cudaFree(s->kp.slots); cudaFree(s->d_pair_mult);
     for (auto & sl : s->slots) sl.release();
@@ -162,7 +167,11 @@ void check_batch(speqg_scan * s, speqg_batch const * b)
     need(b->n_reads < (uint64_t(1) << 32), "more than 2^32 reads in one batch");
 }
 
-void launch_on_view(speqg_scan * s, BatchView const & v)
+// reads at least this long on average are scanned by a warp each (scanh.cu, WPR) instead of by a lane each
+constexpr uint64_t kWarpPerReadBases = 1024;
+
+// groups: 32-base groups of the batch (an upper bound is fine: only the average read length is taken from it)
+void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
 {
     if (v.n_reads == 0) return;
     ScanArgs a = scan_args(s);
@@ -175,7 +184,9 @@ void launch_on_view(speqg_scan * s, BatchView const & v)
     }
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
-        CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, s->cfg_h, s->compute));
+        static const uint64_t wpr_bases = getenv("SPEQB_WPR_BASES") ? strtoull(getenv("SPEQB_WPR_BASES"), nullptr, 10) : kWarpPerReadBases;
+        const int wpr = groups * 32u >= v.n_reads * wpr_bases;
+        CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, wpr, s->cfg_h, s->compute));
         if (s->mode & M_RECORD) s->slot_mult_dirty = true;
     }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
@@ -234,12 +245,15 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             s->own_compute = true;
         }
         CK(cudaStreamCreateWithFlags(&s->copy, cudaStreamNonBlocking));
-        s->d_unique = dev_alloc<unsigned long long>(V);
-        s->d_total_g = dev_alloc<unsigned long long>(V);
-        s->d_unique_w = dev_alloc<double>(V);
-        s->d_scalars = dev_alloc<unsigned long long>(SC_COUNT);
-        s->d_bad = dev_alloc<unsigned long long>(1);
-        s->d_work = dev_alloc<unsigned long long>(1);
+        s->state_words = 3 * (size_t)V + SC_COUNT + 2;
+        s->d_state = dev_alloc<unsigned long long>(s->state_words);
+        CK(cudaMallocHost(&s->h_state, s->state_words * 8));
+        s->d_unique = s->d_state;
+        s->d_total_g = s->d_unique + V;
+        s->d_unique_w = reinterpret_cast<double *>(s->d_total_g + V);
+        s->d_scalars = s->d_total_g + 2 * (size_t)V;
+        s->d_bad = s->d_scalars + SC_COUNT;
+        s->d_work = s->d_bad + 1;
         s->d_percent = dev_alloc<double>(V);
         s->d_tkpg = dev_alloc<double>(V);
         s->d_gc = dev_alloc<int32_t>(V);
@@ -364,12 +378,7 @@ int speqg_scan_reset(speqg_scan * s)
     SPEQG_TRY
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
-    uint32_t V = s->idx->host.V;
-    CK(cudaMemsetAsync(s->d_unique, 0, V * 8, s->compute));
-    CK(cudaMemsetAsync(s->d_total_g, 0, V * 8, s->compute));
-    CK(cudaMemsetAsync(s->d_unique_w, 0, V * 8, s->compute));
-    CK(cudaMemsetAsync(s->d_scalars, 0, SC_COUNT * 8, s->compute));
-    CK(cudaMemsetAsync(s->d_bad, 0, 8, s->compute));
+    CK(cudaMemsetAsync(s->d_state, 0, s->state_words * 8, s->compute));
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
     if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
     if (s->d_pair_mult) CK(cudaMemsetAsync(s->d_pair_mult, 0, 4ull * ((uint64_t)s->kp.nbmask + 1) * 8, s->compute));
@@ -403,7 +412,7 @@ int speqg_scan_submit_packed(speqg_scan * s, const speqg_batch * hb)
     BatchView v{};
     v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = (s->mode & M_LOCAL) ? sl.qual.p : nullptr;
     v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = R;
-    launch_on_view(s, v);
+    launch_on_view(s, v, G);
     CK(cudaEventRecord(sl.done, s->compute));
     sl.busy = true;
     SPEQG_CATCH
@@ -442,7 +451,7 @@ int speqg_scan_submit_raw(speqg_scan * s, const uint8_t * seq, const uint8_t * q
     BatchView v{};
     v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = (s->mode & M_LOCAL) ? sl.qual.p : nullptr;
     v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = R;
-    launch_on_view(s, v);
+    launch_on_view(s, v, G);
     CK(cudaEventRecord(sl.done, s->compute));
     sl.busy = true;
     SPEQG_CATCH
@@ -458,7 +467,7 @@ int speqg_scan_submit_device(speqg_scan * s, const speqg_batch * db)
     BatchView v{};
     v.bases = db->bases; v.inv = db->inv; v.qual = (s->mode & M_LOCAL) ? db->qual : nullptr;
     v.grp_off = db->grp_off; v.len = db->len; v.read_group = nullptr; v.n_reads = db->n_reads;
-    launch_on_view(s, v);
+    launch_on_view(s, v, db->n_groups32);
     SPEQG_CATCH
 }
 
@@ -487,20 +496,20 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
     SPEQG_TRY
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
-    CK(cudaStreamSynchronize(s->copy));
+    // every kernel of the scan runs on the compute stream, behind the copies it waits for: one copy + one sync ends the job
+    uint32_t V = s->idx->host.V;
+    CK(cudaMemcpyAsync(s->h_state, s->d_state, s->state_words * 8, cudaMemcpyDeviceToHost, s->compute));
     CK(cudaStreamSynchronize(s->compute));
     for (auto & sl : s->slots) sl.busy = false;
-    uint32_t V = s->idx->host.V;
-    unsigned long long bad = 0;
-    CK(cudaMemcpy(&bad, s->d_bad, 8, cudaMemcpyDeviceToHost));
+    const unsigned long long * hs = s->h_state;
+    const unsigned long long bad = hs[2 * (size_t)V + V + SC_COUNT];
     if (bad & 2ull) throw api_error(SPEQG_EINVAL, "read longer than 2^32 bases");
     if (bad) throw api_error(SPEQG_EINVAL, "parse_error: illegal (non-IUPAC) sequence character in a read");
-    if (unique_u64) CK(cudaMemcpy(unique_u64, s->d_unique, V * 8, cudaMemcpyDeviceToHost));
-    if (unique_f64) CK(cudaMemcpy(unique_f64, s->d_unique_w, V * 8, cudaMemcpyDeviceToHost));
+    if (unique_u64) memcpy(unique_u64, hs, V * 8);
+    if (unique_f64) memcpy(unique_f64, hs + 2 * (size_t)V, V * 8);
     if (counts)
     {
-        unsigned long long sc[SC_COUNT];
-        CK(cudaMemcpy(sc, s->d_scalars, sizeof sc, cudaMemcpyDeviceToHost));
+        const unsigned long long * sc = hs + 3 * (size_t)V;
         memset(counts, 0, sizeof *counts);
         counts->total_kmers = sc[SC_TOTAL];
         counts->ambiguous_reads = sc[SC_AMBIG];

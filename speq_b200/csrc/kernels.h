@@ -95,8 +95,9 @@ cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv
                                 unsigned long long * n_keys, cudaStream_t st);
 cudaError_t launch_ktable_fold_mult(KTabView const & kt, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,
                                     unsigned long long * mult, cudaStream_t st);
+// warp_per_read != 0: the 32 lanes of a warp split the windows of one read (long reads); else one read / pair per lane
 cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
-                         LaunchCfg cfg, cudaStream_t st);
+                         int warp_per_read, LaunchCfg cfg, cudaStream_t st);
 cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 // two windows per probe (SPEQG_ALGO_KPAIR): a second table over the (k+1)-mers of the texts, values = one byte per k-mer
 cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,

@@ -139,7 +139,8 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(const KTabVie
 // ---------------------------------------------------------------------------------------------------------------
 // scan
 // ---------------------------------------------------------------------------------------------------------------
-enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_DONE = 3 };
+enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_DONE = 3, H_WAIT = 4 };
+constexpr uint32_t kClaimChunkW = 4;   // reads a warp claims at a time when it works on one read together
 // windows per lane and loop trip (their probes are independent, so all loads are issued together) and resident CTAs per SM
 #ifndef SPEQB_KWIN
 #define SPEQB_KWIN 3
@@ -149,7 +150,9 @@ enum : uint32_t { H_FETCH = 0, H_FIRST = 1, H_RUN = 2, H_DONE = 3 };
 #endif
 constexpr int kWin = SPEQB_KWIN;
 
-template <int MODE>
+// WPR (long reads): the 32 lanes of a warp share one read -- lane l takes windows [l * per, (l + 1) * per), per = ceil(nwin / 32),
+// pre-rolling the k-1 bases before its first window; the ambiguity state of the read is the warp's min / max variant.
+template <int MODE, bool WPR>
 __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
                                                                                   const BatchView b, const ScanArgs a, const int paired)
 {
@@ -213,7 +216,22 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
             // ---- next read: claim (first mate only), then length + first group offset
             const bool claim = ph == H_FETCH && !mate2;
             const uint32_t mc = __ballot_sync(kFullH, claim);
-            if (mc)
+            if (WPR)
+            {
+                if (mc)
+                {
+                    if (wcur == wend)
+                    {
+                        uint32_t nbase = 0u;
+                        if (lane == 0u) nbase = (uint32_t)atomicAdd(a.work, (unsigned long long)kClaimChunkW);
+                        wcur = __shfl_sync(kFullH, nbase, 0);
+                        wend = wcur + kClaimChunkW;
+                    }
+                    u = wcur;
+                    wcur += 1u;
+                }
+            }
+            else if (mc)
             {
                 const uint32_t cnt = (uint32_t)__popc(mc), left = wend - wcur;
                 uint32_t nbase = 0u;
@@ -243,18 +261,30 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
         if (ph == H_FIRST)
         {
             const uint32_t L = pend;
-            pend = L >= k ? L : 0u;                               // L < k: the sliding view is empty (sliding.hpp:129-142)
-            n_look += L >= k ? L - k + 1u : 0u;
-            n_reads += 1u;
-            t = 0u; run = 0u; key = 0ull;
-            if (pend)
+            run = 0u; key = 0ull;
+            if (WPR)
             {
-                cb = load_ro(b.bases + g0);
-                ci = load_ro(b.inv + g0);
-                if (pend > 32u)
+                const uint32_t nwin = L >= k ? L - k + 1u : 0u, per = (nwin + 31u) >> 5;
+                const uint32_t s0 = lane * per < nwin ? lane * per : nwin, s1 = nwin - s0 < per ? nwin : s0 + per;
+                if (lane == 0u) { n_look += nwin; n_reads += 1u; }
+                t = s0;
+                pend = s1 > s0 ? s1 + k - 1u : s0;                // this lane's bases: its windows and the k-1 bases before
+            }
+            else
+            {
+                pend = L >= k ? L : 0u;                           // L < k: the sliding view is empty (sliding.hpp:129-142)
+                n_look += L >= k ? L - k + 1u : 0u;
+                n_reads += 1u;
+                t = 0u;
+            }
+            if (t < pend)
+            {
+                cb = load_ro(b.bases + g0 + (t >> 5));
+                ci = load_ro(b.inv + g0 + (t >> 5));
+                if (((t >> 5) + 1u) * 32u < pend)
                 {
-                    nb = load_ro(b.bases + g0 + 1u);
-                    ni = load_ro(b.inv + g0 + 1u);
+                    nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
+                    ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
                 }
             }
             phase = H_RUN;
@@ -346,7 +376,33 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 }
             }
         }
-        if (phase == H_RUN && t >= pend)
+        if (WPR)
+        {
+            // the lane's share of the read is finished: wait for the warp, then merge the read's ambiguity state
+            if (phase == H_RUN && t >= pend) phase = H_WAIT;
+            if (__all_sync(kFullH, phase == H_WAIT))
+            {
+                if (paired && !mate2) mate2 = true;
+                else
+                {
+                    gmin = __reduce_min_sync(kFullH, gmin);
+                    gmax = __reduce_max_sync(kFullH, gmax);
+                    n_total += c_total;
+                    if (lane == 0u) n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
+                    c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                    if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+                    agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
+                    mate2 = false;
+                    if ((n_total | n_look) & 0x80000000u)
+                    {
+                        env.add64(0, n_total); env.add64(2, n_look);
+                        n_total = 0u; n_look = 0u;
+                    }
+                }
+                phase = H_FETCH;
+            }
+        }
+        else if (phase == H_RUN && t >= pend)
         {
             // the read is finished
             if (paired && !mate2) mate2 = true;
@@ -789,13 +845,18 @@ int sm_count_h()
 }
 }   // namespace
 
+constexpr int kWprBit = 16;   // dispatch selector: the warp-per-read instantiation
 #define SPEQB_SCANH_DISPATCH(M, EXPR)                                                   \
     switch (M)                                                                          \
     {                                                                                   \
-        case 0: { auto kern = scanh_kernel<0>; EXPR; break; }                           \
-        case M_RECORD: { auto kern = scanh_kernel<M_RECORD>; EXPR; break; }             \
-        case M_LOCAL: { auto kern = scanh_kernel<M_LOCAL>; EXPR; break; }               \
-        case M_LOCAL | M_RECORD: { auto kern = scanh_kernel<M_LOCAL | M_RECORD>; EXPR; break; } \
+        case 0: { auto kern = scanh_kernel<0, false>; EXPR; break; }                    \
+        case M_RECORD: { auto kern = scanh_kernel<M_RECORD, false>; EXPR; break; }      \
+        case M_LOCAL: { auto kern = scanh_kernel<M_LOCAL, false>; EXPR; break; }        \
+        case M_LOCAL | M_RECORD: { auto kern = scanh_kernel<M_LOCAL | M_RECORD, false>; EXPR; break; } \
+        case kWprBit: { auto kern = scanh_kernel<0, true>; EXPR; break; }               \
+        case kWprBit | M_RECORD: { auto kern = scanh_kernel<M_RECORD, true>; EXPR; break; } \
+        case kWprBit | M_LOCAL: { auto kern = scanh_kernel<M_LOCAL, true>; EXPR; break; } \
+        case kWprBit | M_LOCAL | M_RECORD: { auto kern = scanh_kernel<M_LOCAL | M_RECORD, true>; EXPR; break; } \
         default: return cudaErrorInvalidValue;                                          \
     }
 
@@ -804,25 +865,35 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     const size_t smem = scan32_smem_bytes(V);
     int bps = 0;
     cudaError_t e = cudaSuccess;
-    const int m = mode & (M_LOCAL | M_RECORD);
-    SPEQB_SCANH_DISPATCH(m, {
-        if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlockH, smem);
-    })
-    if (e != cudaSuccess) return e;
-    if (bps <= 0) return cudaErrorLaunchOutOfResources;
+    // both instantiations (lane per read, warp per read) are launched with one grid: the smaller occupancy
+    for (int wpr = 0; wpr <= kWprBit; wpr += kWprBit)
+    {
+        const int m = (mode & (M_LOCAL | M_RECORD)) | wpr;
+        int bw = 0;
+        SPEQB_SCANH_DISPATCH(m, {
+            if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, kern, kBlockH, smem);
+        })
+        if (e != cudaSuccess) return e;
+        if (bw <= 0) return cudaErrorLaunchOutOfResources;
+        bps = wpr == 0 || bw < bps ? bw : bps;
+    }
     cfg->block = kBlockH;
     cfg->grid = sm_count_h() * bps;
     return cudaSuccess;
 }
 
-// Geometry of the table for `keys` distinct k-mers (an upper bound is fine): load factor in (0.2, 0.4], grown by `grow`
-// doublings; the remainder must fit below the displacement and value fields.
+// Geometry of the table for `keys` distinct k-mers (an upper bound is fine): load factor in (0.2, 0.4] (down to 0.1 for tables
+// of at most kSmallTableBytes), grown by `grow` doublings; the remainder must fit below the displacement and value fields.
+constexpr uint64_t kSmallTableBytes = 32ull << 20;
 bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
 {
     const uint32_t B = 2u * k;
     uint32_t q = 1u;
     while (q < B && (1ull << q) * 8ull < keys * 5ull) ++q;       // 4 * 2^q * 0.4 >= keys
+    // while the table stays far below L2 anyway, spend memory on a load factor <= 0.1: a k-mer displaced from a full home
+    // bucket costs a second, dependent round trip, and one such lane holds up its whole warp
+    while (q < B && (64ull << q) <= kSmallTableBytes && (4ull << q) < keys * 10ull) ++q;
     q = std::min(B, q + grow);
     if (B > 45u && q < B - 45u) q = B - 45u;
     if (q > 31u) return false;
@@ -839,11 +910,11 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
 }
 
 cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
-                         LaunchCfg cfg, cudaStream_t st)
+                         int warp_per_read, LaunchCfg cfg, cudaStream_t st)
 {
     const size_t smem = scan32_smem_bytes(a.V);
     const int paired = (mode & M_PAIRED) ? 1 : 0;
-    const int m = mode & (M_LOCAL | M_RECORD);
+    const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, slot_mult, b, a, paired)))

@@ -333,6 +333,71 @@ def test_ktable_k_range(lib, k):
     idx.close()
 
 
+@pytest.mark.parametrize("mode", ["global", "local", "record"])
+def test_long_reads_warp_per_read(lib, mode):
+    """Batches whose reads average >= 1024 bases are scanned by a warp per read (scanh.cu, WPR): each lane takes a share of
+    the windows and the read's ambiguity state is merged across the warp.  Against the rolling FM search (a lane per read),
+    with Ns, low qualities, reads shorter than k and reads of fewer windows than a warp has lanes mixed in, single and
+    paired."""
+    rng = np.random.default_rng(41)
+    V, G, k = 5, 40_000, 15
+    anc = rng.integers(0, 4, G)
+    scaff = []
+    for v in range(V):
+        s = anc.copy()
+        pos = rng.integers(0, G, 400)
+        s[pos] = rng.integers(0, 4, 400)
+        s = np.where(s == 3, 4, s).astype(np.uint8)              # dna5 ranks: A0 C1 G2 N3 T4
+        s[rng.integers(0, G, 5)] = 3
+        scaff.append(s)
+    idx = engine.Index.from_scaffolds(scaff, list(range(V)), V)
+    R = 600
+    lens = rng.integers(1500, 9000, R)
+    lens[rng.integers(0, R, 20)] = rng.integers(0, 40, 20)       # empty reads, reads below k, reads of a few windows
+    lens[5] = k; lens[6] = k + 31; lens[7] = k + 32
+    assert lens.sum() >= 1024 * R
+    src, st = rng.integers(0, V, R), np.array([rng.integers(0, G - int(n) + 1) for n in lens])
+    letters = np.frombuffer(b"ACGNT", np.uint8)
+    # odd reads are chimeras of two variants: ambiguity has to be seen across lanes
+    parts = []
+    for i, (v, p, n) in enumerate(zip(src, st, lens)):
+        r = scaff[int(v)][int(p):int(p) + int(n)].copy()
+        if i % 2 and n > 200:
+            w = scaff[int((v + 1) % V)]
+            r[int(n) // 2:] = w[int(p) + int(n) // 2:int(p) + int(n)]
+        parts.append(letters[r])
+    seq = np.concatenate(parts)
+    flip = rng.random(seq.size) < 0.005
+    seq[flip] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(flip.sum()))]
+    qual = np.where(rng.random(seq.size) < 0.003, ord("#"), ord("I")).astype(np.uint8)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    kw = dict(mode=capi.MODE_LOCAL if mode == "local" else capi.MODE_GLOBAL, record=mode == "record")
+    pct, cnt = np.full(V, 100.0 / V), np.full(V, 1, np.int32)
+
+    def run(algorithm, paired):
+        sc = engine.Scan(idx, k=k, algorithm=algorithm, paired=paired, **kw)
+        sc.submit_raw(seq, qual, offs, R)
+        r = sc.finish()
+        extra = (sc.multiplicity_count(), sc.refine(pct, cnt)) if mode == "record" else None
+        sc.close()
+        return r, extra
+
+    for paired in (False, True):
+        a, ea = run(capi.ALGO_KTABLE, paired)
+        b, eb = run(capi.ALGO_ROLLING, paired)
+        assert a.total_kmers > 0 and 0 < a.ambiguous < (R // 2 if paired else R)
+        assert a.total_kmers == b.total_kmers and a.ambiguous == b.ambiguous and a.lookups == b.lookups
+        assert a.reads == b.reads
+        if mode == "local":
+            assert helpers.rel_close(a.unique_w, b.unique_w, 1e-12)
+        else:
+            assert np.array_equal(a.unique, b.unique)
+        if mode == "record":
+            assert ea[0] == eb[0]
+            assert helpers.rel_close(ea[1], eb[1], 1e-11)
+    idx.close()
+
+
 @pytest.mark.parametrize("case", ["random", "repeats", "collection"])
 def test_device_suffix_array_matches_host(lib, case, tmp_path):
     """SPEQG_BUILD_DEVICE_SA: prefix doubling on the GPU yields the suffix array SA-IS builds on the host (it is unique), hence
