@@ -29,11 +29,12 @@ struct option
 const std::vector<option> kAll = {{'1', "forward", false}, {'2', "reverse", false}, {'r', "reference", false}, {'g', "groups", false},
                                   {'x', "index", false}, {'o', "output", false}, {'f', "force", true}, {'k', "kmer", false},
                                   {0, "precision-cutoff", false}, {0, "phred-cutoff", false}, {0, "fixed-accuracy", false},
-                                  {'t', "threads", false}, {0, "gpus", false}, {0, "batch-reads", false}, {0, "json", false}};
+                                  {'t', "threads", false}, {0, "gpus", false}, {0, "batch-reads", false}, {0, "json", false},
+                                  {0, "write-output", true}};
 const std::vector<option> kScan = {{'1', "forward", false}, {'2', "reverse", false}, {'x', "index", false}, {'o', "output", false},
                                    {'f', "force", true}, {'k', "kmer", false}, {0, "precision-cutoff", false},
                                    {0, "phred-cutoff", false}, {0, "fixed-accuracy", false}, {'t', "threads", false},
-                                   {0, "gpus", false}, {0, "batch-reads", false}, {0, "json", false}};
+                                   {0, "gpus", false}, {0, "batch-reads", false}, {0, "json", false}, {0, "write-output", true}};
 const std::vector<option> kIndex = {{'r', "reference", false}, {'g', "groups", false}, {'x', "index", false}, {'f', "force", true},
                                     {'t', "threads", false}};
 
@@ -93,6 +94,7 @@ void assign(cmd_arguments & a, option const & o, std::string const & v)
         range_check(a.batch_reads, 2, 1u << 28, o);
     }
     else if (n == "json") a.json_path = v;
+    else if (n == "write-output") a.write_output = true;
 }
 
 void parse_options(cmd_arguments & a, std::vector<option> const & opts, std::vector<std::string> const & argv)
@@ -134,7 +136,7 @@ void help(std::string const & sub)
     std::cerr << "speq " << sub << " [options]    (B200 build of SPeQ's scan hot path; flags as in the reference, version 0.1.0)\n"
                  "  -1/--forward FILE  -2/--reverse FILE  -r/--reference FASTA  -g/--groups FILE  -x/--index PREFIX  -o/--output FILE  -f/--force\n"
                  "  -k/--kmer N (70)  --precision-cutoff X (1e-06)  --phred-cutoff N (30)  --fixed-accuracy X (0 = use phred)  -t/--threads N (2)\n"
-                 "  --gpus N (1)  --batch-reads N  --json FILE\n";
+                 "  --gpus N (1)  --batch-reads N  --json FILE  --write-output (write the per-variant table to -o FILE)\n";
 }
 }   // namespace
 

@@ -29,6 +29,8 @@ struct cmd_arguments
     unsigned int gpus{1};                 // --gpus N: devices the reads are sharded over (index replicated)
     unsigned int batch_reads{1u << 18};   // --batch-reads: reads per C-ABI submit (2 x 2 pinned buffers of 80 MB per device)
     std::filesystem::path json_path{};    // --json FILE: full-precision results for parity checks
+    bool write_output{false};             // --write-output: write the per-variant table to -o/--output (the reference parses -o,
+                                          // src/arg_parse.cpp:20, and never writes it; off by default for that reason)
 };
 
 cmd_arguments initialize_argument_parser(int argc, char ** argv);

@@ -364,6 +364,21 @@ std::vector<double> unique_to_percent(std::vector<double> const & unique_in_read
     return out;
 }
 
+// --write-output: the per-variant result table as tab-separated text in -o/--output.  The reference declares the option
+// (src/arg_parse.cpp:20) and reports on stderr only; this is the fix-forward of SURVEY.md 8f-4, off by default.
+void write_table(fs::path const & p, idx_meta const & meta, scan_out const & so, std::vector<double> const & unique_totals,
+                 std::vector<double> const & initial, std::vector<double> const & fin)
+{
+    FILE * f = fopen(p.c_str(), "w");
+    if (!f) throw std::runtime_error("cannot write " + p.string());
+    fprintf(f, "# total_kmers\t%llu\n# ambiguous_reads\t%llu\n", static_cast<unsigned long long>(so.total_kmers),
+            static_cast<unsigned long long>(so.ambiguous));
+    fprintf(f, "group\tisolates\tunique_kmers\tpercent_initial\tpercent_final\n");
+    for (size_t g = 0; g < fin.size(); ++g)
+        fprintf(f, "%s\t%d\t%.17g\t%.17g\t%.17g\n", meta.group_names[g].c_str(), meta.group_counts[g], unique_totals[g], initial[g], fin[g]);
+    fclose(f);
+}
+
 void write_json(fs::path const & p, cmd_arguments const & args, bool local, bool paired, std::vector<uint64_t> const & uref,
                 std::vector<uint64_t> const & tref, scan_out const & so, std::vector<double> const & unique_totals,
                 std::vector<double> const & initial, std::vector<double> const & fin, size_t iters, double t_backcheck, double t_refine)
@@ -513,6 +528,7 @@ int do_scan(cmd_arguments & args)
             ++iters;
         }
         double t_refine = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (args.write_output) write_table(args.out_file_path, meta, so, unique_totals, initial, percent);
         if (!args.json_path.empty())
             write_json(args.json_path, args, local, paired, unique_ref, total_ref, so, unique_totals, initial, percent, iters, t_backcheck, t_refine);
     }

@@ -124,8 +124,11 @@ def test_speq_all_matches_golden(speq_bin, tmp_path, name):
     assert f"{exp['total_kmers']}\t{exp['ambiguous']}" in lines
     dat = tmp_path / f"i_{runp['k']}mer.dat"
     assert dat.exists()
+    # -o is parsed and, like in the reference, not written unless --write-output asks for it
+    assert not (tmp_path / "output.txt").exists()
     # second run: .dat is fresh, so the back-check vectors are not printed again (src/fm_scanner.cpp:101-119)
     cmd[0] = "scan"
+    cmd += ["-o", tmp_path / "table.tsv", "--write-output"]
     cmd2 = [c for i, c in enumerate(cmd) if not (i > 0 and str(cmd[i - 1]) in ("-r", "-g")) and str(c) not in ("-r", "-g")]
     r2nd = run(speq_bin, *cmd2, "-f", cwd=tmp_path)
     assert r2nd.returncode == 0, r2nd.stderr
@@ -133,6 +136,12 @@ def test_speq_all_matches_golden(speq_bin, tmp_path, name):
     # sharded over 2 "GPUs" requested on a 1-GPU box clamps to the devices present; result unchanged
     out2 = json.loads((tmp_path / "out.json").read_text())
     assert out2["total_kmers"] == exp["total_kmers"]
+    # the per-variant table of --write-output carries the same numbers at full precision
+    rows = [ln.split("\t") for ln in (tmp_path / "table.tsv").read_text().strip().split("\n")]
+    assert rows[0] == ["# total_kmers", str(exp["total_kmers"])] and rows[1] == ["# ambiguous_reads", str(exp["ambiguous"])]
+    assert rows[2] == ["group", "isolates", "unique_kmers", "percent_initial", "percent_final"]
+    assert [float(r[4]) for r in rows[3:]] == out2["percent_final"]
+    assert [float(r[3]) for r in rows[3:]] == out2["percent_initial"]
 
 
 def _write_fq(path, recs, newline="\n", trailing=True):
