@@ -71,6 +71,7 @@ struct speqg_scan
     unsigned long long * d_slot_mult = nullptr;
     bool slot_mult_dirty = false;
     uint64_t ktab_keys = 0;
+    uint32_t filt_bits = 0;       // presence filter of the k-mer table (pair-table scan): 2^filt_bits bits
     // SPEQG_ALGO_KPAIR: the table over the (k+1)-mers (two windows per probe) next to the k-mer table
     KTabView kp{};
     unsigned long long * d_pair_mult = nullptr;
@@ -132,7 +133,7 @@ void scan_release(speqg_scan * s)
     cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_mult);
     cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
-    cudaFree(s->kt.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
+    cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
     cudaFree(s->kp.slots); cudaFree(s->d_pair_mult);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
@@ -333,6 +334,14 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                     CK(cudaMemsetAsync(s->d_pair_mult, 0, n_slots * 8, s->compute));
                 }
                 CK(scanp_launch_cfg(s->mode, V, &s->cfg_p));
+                // presence filter of the k-mer table: answers the windows with a sequencing error out of L2
+                if (!getenv("SPEQB_NO_FILTER"))
+                {
+                    s->filt_bits = kfilter_bits(params->k, s->ktab_keys);
+                    s->kt.fshift = 2u * params->k - s->filt_bits;
+                    s->kt.filt = dev_alloc<uint32_t>(std::max<uint64_t>(1, (1ull << s->filt_bits) / 32));
+                    CK(launch_kfilter_build(s->kt, s->filt_bits, s->compute));
+                }
             }
         }
         else if (s->algo == SPEQG_ALGO_ROLLING64)
@@ -565,7 +574,8 @@ int speqg_scan_info(speqg_scan * s, uint32_t * algorithm, uint64_t * structure_b
     if (structure_bytes)
     {
         if (s->algo == SPEQG_ALGO_KTABLE) *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1);
-        else if (s->algo == SPEQG_ALGO_KPAIR) *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1) + 32ull * ((uint64_t)s->kp.nbmask + 1);
+        else if (s->algo == SPEQG_ALGO_KPAIR)
+            *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1) + 32ull * ((uint64_t)s->kp.nbmask + 1) + (s->kt.filt ? (1ull << s->filt_bits) / 8 : 0);
         else if (s->algo == SPEQG_ALGO_ROLLING) *structure_bytes = sizeof(FBlock) * (s->idx->host.n / 32 + 1);
         else *structure_bytes = sizeof(KBlock) * s->idx->host.blocks.size();
     }

@@ -88,7 +88,12 @@ struct KTabView
     uint32_t q, rbits, nbmask;    // 2^q buckets of 4 slots; rbits = 2k - q stored key bits; nbmask = 2^q - 1
     uint64_t mask_b, rmask;       // 4^k - 1, 2^rbits - 1
     uint64_t mul, mul_inv;        // invertible multiplicative hash mod 4^k and its inverse
+    uint32_t * filt;              // optional presence filter (pair-table scan): bit (hash >> fshift) is set for every stored k-mer
+    uint32_t fshift;
 };
+// presence filter of the k-mer table for the pair-table scan: 2^fbits bits, L2-resident next to the HBM-resident tables
+uint32_t kfilter_bits(uint32_t k, uint64_t keys);
+cudaError_t launch_kfilter_build(KTabView const & kt, uint32_t fbits, cudaStream_t st);
 bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt);
 cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                 const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,

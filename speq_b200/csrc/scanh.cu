@@ -136,6 +136,22 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(const KTabVie
     }
 }
 
+// presence filter of a built table: the hash of every stored k-mer is rebuilt from its slot (home bucket + remainder)
+__global__ void __launch_bounds__(kBlockH) kfilter_build_kernel(const KTabView kt)
+{
+    const uint64_t n_slots = 4ull * ((uint64_t)kt.nbmask + 1ull);
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const uint64_t w = kt.slots[i];
+        if (w == ~0ull) continue;
+        const uint32_t d = (uint32_t)(w >> kt.rbits) & 7u;
+        const uint32_t home = ((uint32_t)(i >> 2) - d) & kt.nbmask;
+        const uint64_t h = ((uint64_t)home << kt.rbits) | (w & kt.rmask);
+        const uint32_t fi = (uint32_t)(h >> kt.fshift);
+        atomicOr(kt.filt + (fi >> 5), 1u << (fi & 31u));
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // scan
 // ---------------------------------------------------------------------------------------------------------------
@@ -445,6 +461,49 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
 // the k-mer table, exactly as scanh_kernel does.  Windows that cannot be paired (odd one at the end of a read, next to an
 // N) take the same single-window path.
 // ---------------------------------------------------------------------------------------------------------------
+// L2 eviction hints (pair-table scan): evict_first for the table probes (each sector is used once), evict_last for the filter
+#ifndef SPEQB_L2HINT
+#define SPEQB_L2HINT 1
+#endif
+__device__ __forceinline__ uint64_t l2_policy_keep()
+{
+    uint64_t p = 0ull;
+#if SPEQB_L2HINT
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+#endif
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_stream()
+{
+    uint64_t p = 0ull;
+#if SPEQB_L2HINT
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+#endif
+    return p;
+}
+__device__ __forceinline__ void ldg256_stream(uint32_t (&w)[8], const void * ptr, uint64_t pol)
+{
+#if SPEQB_L2HINT
+    asm volatile("ld.global.nc.L2::cache_hint.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(ptr), "l"(pol));
+#else
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(ptr));
+#endif
+}
+__device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t pol)
+{
+    uint32_t v;
+#if SPEQB_L2HINT
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
+#else
+    asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(ptr));
+#endif
+    return v;
+}
+
 constexpr uint32_t kAbsent = 0x10000u;
 
 // value of `key` in a table (synchronous probe sequence), kAbsent when it is not stored; bucket / j = where it is stored
@@ -569,6 +628,9 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     const uint32_t pmask_lo = (uint32_t)pmask, pmask_hi = (uint32_t)(pmask >> 32);
     const uint64_t tmask = (kt.rmask << 3) | 7ull;
     const uint32_t tmask_lo = (uint32_t)tmask, tmask_hi = (uint32_t)(tmask >> 32);
+
+    // the tables stream from HBM and must not push the presence filter out of L2
+    const uint64_t pol_keep = l2_policy_keep(), pol_stream = l2_policy_stream();
 
     uint32_t phase = H_FETCH;
     bool mate2 = false;
@@ -700,24 +762,51 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     mode[j] |= run >= k ? 2u : 0u;
                 }
                 key_b[j] = key;
-                if (mode[j] == 3u)
-                {
-                    const uint64_t h = (key * kp.mul) & kp.mask_b;
-                    pb[j] = (uint32_t)(h >> kp.rbits);
-                    const uint64_t want = h & kp.rmask;
-                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                 : "l"(kp.slots + 4ull * pb[j]));
-                }
             }
             t += nbase;
             if (o + nbase >= 32u) next_group();
+            // ---- presence filter (L2): a window whose k-mer is not in the index -- a sequencing error -- is answered here and
+            //      costs no HBM sector; a pair is probed only when both of its k-mers may exist
+            if (kt.filt != nullptr)
+            {
+                uint32_t fw[2 * kPair], fb[2 * kPair];
+#pragma unroll
+                for (int i = 0; i < 2 * kPair; ++i)
+                {
+                    if (!((mode[i >> 1] >> (i & 1)) & 1u)) continue;
+                    const uint64_t h = (((i & 1) ? key_b[i >> 1] : key_a[i >> 1]) * kt.mul) & kt.mask_b;
+                    fb[i] = (uint32_t)(h >> kt.fshift);
+                    fw[i] = ldg32_keep(kt.filt + (fb[i] >> 5), pol_keep);
+                }
+#pragma unroll
+                for (int i = 0; i < 2 * kPair; ++i)
+                {
+                    if (!((mode[i >> 1] >> (i & 1)) & 1u)) continue;
+                    c_total += 1u;                                // ++total_kmers (src/fm_scanner.cpp:164)
+                    if (!((fw[i] >> (fb[i] & 31u)) & 1u)) mode[i >> 1] &= ~(1u << (i & 1));
+                }
+            }
+            else
+            {
+#pragma unroll
+                for (int j = 0; j < kPair; ++j) c_total += (mode[j] & 1u) + (mode[j] >> 1);
+            }
+#pragma unroll
+            for (int j = 0; j < kPair; ++j)
+            {
+                if (mode[j] == 3u)
+                {
+                    const uint64_t h = (key_b[j] * kp.mul) & kp.mask_b;
+                    pb[j] = (uint32_t)(h >> kp.rbits);
+                    const uint64_t want = h & kp.rmask;
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    ldg256_stream(w[j], kp.slots + 4ull * pb[j], pol_stream);
+                }
+            }
             // ---- pairs: one probe answers both windows
 #pragma unroll
             for (int j = 0; j < kPair; ++j)
             {
-                c_total += (mode[j] & 1u) + (mode[j] >> 1);       // ++total_kmers (src/fm_scanner.cpp:164)
                 if (mode[j] != 3u) continue;
                 n_probe += 1u;
                 uint32_t d = 0u;
@@ -743,9 +832,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     pb[j] = (pb[j] + 1u) & kp.nbmask;
                     const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kp.rbits);
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                 : "l"(kp.slots + 4ull * pb[j]));
+                    ldg256_stream(w[j], kp.slots + 4ull * pb[j], pol_stream);
                 }
             }
             // ---- what is left: unpaired windows and the halves of missed pairs go through the k-mer table, all first probes
@@ -761,9 +848,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     sb[i] = (uint32_t)(h >> kt.rbits);
                     const uint64_t want = h & kt.rmask;
                     sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
-                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                 : "=r"(sw[i][0]), "=r"(sw[i][1]), "=r"(sw[i][2]), "=r"(sw[i][3]), "=r"(sw[i][4]), "=r"(sw[i][5]), "=r"(sw[i][6]), "=r"(sw[i][7])
-                                 : "l"(kt.slots + 4ull * sb[i]));
+                    ldg256_stream(sw[i], kt.slots + 4ull * sb[i], pol_stream);
                 }
 #pragma unroll
                 for (int i = 0; i < 2 * kPair; ++i)
@@ -790,9 +875,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         sb[i] = (sb[i] + 1u) & kt.nbmask;
                         const uint64_t want = u64of(sl[i], sh_[i]) + (1ull << kt.rbits);
                         sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
-                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                     : "=r"(sw[i][0]), "=r"(sw[i][1]), "=r"(sw[i][2]), "=r"(sw[i][3]), "=r"(sw[i][4]), "=r"(sw[i][5]), "=r"(sw[i][6]), "=r"(sw[i][7])
-                                     : "l"(kt.slots + 4ull * sb[i]));
+                        ldg256_stream(sw[i], kt.slots + 4ull * sb[i], pol_stream);
                     }
                 }
             }
@@ -906,7 +989,29 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
     uint64_t x = kt->mul;                                         // Newton: the inverse mod 2^64 (and so mod 2^B)
     for (int i = 0; i < 6; ++i) x *= 2ull - kt->mul * x;
     kt->mul_inv = x;
+    kt->filt = nullptr;
+    kt->fshift = 0u;
     return true;
+}
+
+// Presence filter: one bit per value of the top fbits bits of the k-mer hash, about 4 bits per stored k-mer, at most
+// 2^SPEQB_FBITS_MAX bits (32 MB: it has to stay in L2 while the tables stream from HBM).
+#ifndef SPEQB_FBITS_MAX
+#define SPEQB_FBITS_MAX 28
+#endif
+uint32_t kfilter_bits(uint32_t k, uint64_t keys)
+{
+    uint32_t f = 10u;
+    while (f < (uint32_t)SPEQB_FBITS_MAX && (1ull << f) < keys * 4ull) ++f;
+    return std::min(f, 2u * k);
+}
+
+cudaError_t launch_kfilter_build(KTabView const & kt, uint32_t fbits, cudaStream_t st)
+{
+    cudaError_t e = cudaMemsetAsync(kt.filt, 0, std::max<uint64_t>(4, (1ull << fbits) / 8), st);
+    if (e != cudaSuccess) return e;
+    kfilter_build_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
