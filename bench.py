@@ -344,25 +344,27 @@ def main() -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def allreduce_tallies(r):
-        t = torch.from_numpy(np.concatenate([r.unique, np.array([r.total_kmers, r.ambiguous, r.lookups, r.reads], np.uint64)]).astype(np.int64))
+    # N > 1: the counters are summed across ranks where they live -- one NCCL all-reduce in place on the scan's stream behind
+    # the last kernel -- so a step has a single host sync (finish), which then returns the global tallies
+    cnt_i64 = scan.device_counters()[0] if world > 1 else None
+
+    def finish_global():
         if world > 1:
-            t = t.to(dev)
-            dist.all_reduce(t)
-            t = t.cpu()
-        return t.numpy()
+            dist.all_reduce(cnt_i64)
+        r = scan.finish()
+        return np.concatenate([r.unique, np.array([r.total_kmers, r.ambiguous, r.lookups, r.reads], np.uint64)]).astype(np.int64)
 
     def step_resident():
         scan.reset()
         scan.submit_device(db)
-        return allreduce_tallies(scan.finish())
+        return finish_global()
 
     def step_e2e():
         scan.reset()
         for s in range(0, R, args.batch_reads):
             e = min(R, s + args.batch_reads)
             scan.submit_raw(seq_np, qual_np, offs_np[s:e + 1], e - s)
-        return allreduce_tallies(scan.finish())
+        return finish_global()
 
     # ---- value: resident inputs, CUDA events ----
     for _ in range(args.warmup):
@@ -476,7 +478,7 @@ def main() -> None:
             scan.reset()
             for pb_ in pbs:
                 scan.submit_packed(pb_)
-            return allreduce_tallies(scan.finish())
+            return finish_global()
         for _ in range(min(args.warmup, 3)):
             tall_p = step_packed()
         barrier()

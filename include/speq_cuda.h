@@ -177,6 +177,12 @@ int speqg_scan_stats(speqg_scan * scan, const speqg_batch * device_batch, speqg_
 /* What the handle resolved SPEQG_ALGO_AUTO to, and the size of its per-(index, k) structure: the k-mer table
  * (algorithm == SPEQG_ALGO_KTABLE: bytes, distinct k-mers stored) or the rank blocks of the rolling search (keys = 0). */
 int speqg_scan_info(speqg_scan * scan, uint32_t * algorithm, uint64_t * structure_bytes, uint64_t * keys);
+/* Multi-GPU (replaces the sum over the per-thread vectors after future.get(), src/fm_scanner.cpp:224-233, across devices):
+ * the handle's counters in device memory, for a sum-all-reduce in place on the scan's stream between the last submit and
+ * speqg_scan_finish, which then returns the global tallies.  u64_counters: unique[n_groups], back-check totals[n_groups],
+ * then total_kmers, ambiguous_reads, lookups, steps_executed, kmers_hit, occurrences, occ_sectors, reads (*n_u64 entries);
+ * f64_counters: the local-mode tallies (*n_f64 = n_groups entries).  Any output pointer may be NULL. */
+int speqg_scan_device_counters(speqg_scan * scan, uint64_t ** u64_counters, uint64_t * n_u64, double ** f64_counters, uint64_t * n_f64);
 void speqg_scan_close(speqg_scan * scan);
 
 /* page-locked host memory for read batches (replaces the heap vectors seqan3's record buffer holds,

@@ -84,7 +84,9 @@ struct speqg_scan
     cudaStream_t compute = nullptr, copy = nullptr;
     bool own_compute = false;
     // the scan's counters live in one device block (one memset per reset, one copy per finish):
-    // unique[V] total_g[V] unique_w[V] scalars[SC_COUNT] bad[1] work[1]; h_state is its pinned host mirror
+    // unique[V] total_g[V] scalars[SC_COUNT] unique_w[V] bad[1] work[1]; h_state is its pinned host mirror.  The integer
+    // counters come first so that a multi-GPU driver sums them across ranks in place with one all-reduce
+    // (speqg_scan_device_counters)
     unsigned long long * d_state = nullptr, * h_state = nullptr;
     size_t state_words = 0;
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
@@ -251,9 +253,9 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         CK(cudaMallocHost(&s->h_state, s->state_words * 8));
         s->d_unique = s->d_state;
         s->d_total_g = s->d_unique + V;
-        s->d_unique_w = reinterpret_cast<double *>(s->d_total_g + V);
-        s->d_scalars = s->d_total_g + 2 * (size_t)V;
-        s->d_bad = s->d_scalars + SC_COUNT;
+        s->d_scalars = s->d_total_g + V;
+        s->d_unique_w = reinterpret_cast<double *>(s->d_scalars + SC_COUNT);
+        s->d_bad = s->d_scalars + SC_COUNT + V;
         s->d_work = s->d_bad + 1;
         s->d_percent = dev_alloc<double>(V);
         s->d_tkpg = dev_alloc<double>(V);
@@ -511,14 +513,14 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
     CK(cudaStreamSynchronize(s->compute));
     for (auto & sl : s->slots) sl.busy = false;
     const unsigned long long * hs = s->h_state;
-    const unsigned long long bad = hs[2 * (size_t)V + V + SC_COUNT];
+    const unsigned long long bad = hs[3 * (size_t)V + SC_COUNT];
     if (bad & 2ull) throw api_error(SPEQG_EINVAL, "read longer than 2^32 bases");
     if (bad) throw api_error(SPEQG_EINVAL, "parse_error: illegal (non-IUPAC) sequence character in a read");
     if (unique_u64) memcpy(unique_u64, hs, V * 8);
-    if (unique_f64) memcpy(unique_f64, hs + 2 * (size_t)V, V * 8);
+    if (unique_f64) memcpy(unique_f64, hs + 2 * (size_t)V + SC_COUNT, V * 8);
     if (counts)
     {
-        const unsigned long long * sc = hs + 3 * (size_t)V;
+        const unsigned long long * sc = hs + 2 * (size_t)V;
         memset(counts, 0, sizeof *counts);
         counts->total_kmers = sc[SC_TOTAL];
         counts->ambiguous_reads = sc[SC_AMBIG];
@@ -527,6 +529,18 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
         counts->kernel_launches = s->launches;
         counts->steps_executed = sc[SC_STEPS];   // table algorithms: 32-byte table probes issued (0 otherwise)
     }
+    SPEQG_CATCH
+}
+
+int speqg_scan_device_counters(speqg_scan * s, uint64_t ** u64_counters, uint64_t * n_u64, double ** f64_counters, uint64_t * n_f64)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    uint32_t V = s->idx->host.V;
+    if (u64_counters) *u64_counters = reinterpret_cast<uint64_t *>(s->d_state);
+    if (n_u64) *n_u64 = 2 * (uint64_t)V + SC_COUNT;
+    if (f64_counters) *f64_counters = s->d_unique_w;
+    if (n_f64) *n_f64 = V;
     SPEQG_CATCH
 }
 

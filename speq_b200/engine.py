@@ -204,6 +204,7 @@ class Scan:
         self.index = index
         self.V = index.n_groups
         self.mode = mode
+        self.device = device
         self.params = capi.Params(k, phred_cutoff, mode, int(paired), int(record), algorithm, stream)
         self.h = C.c_void_p()
         capi.check(capi.lib().speqg_scan_open(index.h, device, C.byref(self.params), C.byref(self.h)))
@@ -242,6 +243,20 @@ class Scan:
         a, nb, nk = C.c_uint32(), C.c_uint64(), C.c_uint64()
         capi.check(capi.lib().speqg_scan_info(self.h, C.byref(a), C.byref(nb), C.byref(nk)))
         return {"algorithm": int(a.value), "structure_bytes": int(nb.value), "keys": int(nk.value)}
+
+    def device_counters(self):
+        """The handle's counters as torch tensors over its device memory (int64 view of the u64 counters, float64 local-mode
+        tallies): a multi-GPU driver all-reduces them in place on the scan's stream before finish()."""
+        import torch
+        pu, pf, nu, nf = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint64()
+        capi.check(capi.lib().speqg_scan_device_counters(self.h, C.byref(pu), C.byref(nu), C.byref(pf), C.byref(nf)))
+
+        class _View:
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+        dev = torch.device("cuda", self.device)
+        return (torch.as_tensor(_View(pu.value, nu.value, "<i8"), device=dev), torch.as_tensor(_View(pf.value, nf.value, "<f8"), device=dev))
 
     def refine(self, percent: np.ndarray, group_counts: np.ndarray) -> np.ndarray:
         p = np.ascontiguousarray(percent, np.float64)

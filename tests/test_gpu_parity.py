@@ -398,6 +398,32 @@ def test_long_reads_warp_per_read(lib, mode):
     idx.close()
 
 
+def test_device_counters_reduce_in_place(lib):
+    """speqg_scan_device_counters: the counters a multi-GPU driver sums across ranks in place before finish().  One GPU: the
+    views hold what finish() returns, and an in-place update on the scan's stream (here: doubling, what an all-reduce over two
+    identical ranks yields) is what finish() then reports."""
+    import torch
+    fx = helpers.load_golden("global_single")
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    V = len(counts)
+    idx = engine.Index.from_scaffolds(scaff, gs, V)
+    seq, qual, offs = helpers.flat_reads(seqs, quals)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        sc = engine.Scan(idx, k=fx["run"]["k"], phred_cutoff=fx["run"].get("phred_cutoff", 30), stream=st.cuda_stream)
+        sc.submit_raw(seq, qual, offs, offs.size - 1)
+        ci, cf = sc.device_counters()
+        assert ci.dtype == torch.int64 and ci.numel() == 2 * V + 8 and cf.dtype == torch.float64 and cf.numel() == V
+        ci.mul_(2)
+        r = sc.finish()
+    exp = fx["expected"]
+    assert [int(x) for x in r.unique] == [2 * x for x in exp["unique"]]
+    assert r.total_kmers == 2 * exp["total_kmers"] and r.ambiguous == 2 * exp["ambiguous"] and r.lookups == 2 * exp["lookups"]
+    assert [int(x) for x in ci[:V].cpu()] == [2 * x for x in exp["unique"]]
+    sc.close()
+    idx.close()
+
+
 @pytest.mark.parametrize("case", ["random", "repeats", "collection"])
 def test_device_suffix_array_matches_host(lib, case, tmp_path):
     """SPEQG_BUILD_DEVICE_SA: prefix doubling on the GPU yields the suffix array SA-IS builds on the host (it is unique), hence
