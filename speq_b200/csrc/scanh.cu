@@ -34,6 +34,16 @@ namespace
 constexpr int kBlockH = 256;
 constexpr uint32_t kFullH = 0xFFFFFFFFu;
 constexpr uint32_t kClaimChunk = 64;
+#if defined(__CUDACC__)
+// units a warp claims at a time: kClaimChunk, or for batches of fewer than kClaimChunk units per warp their even share (lanes
+// at and above a share below 32 stay idle, so at most `chunk` lanes claim at once)
+__device__ __forceinline__ uint32_t claim_chunk(uint32_t units)
+{
+    const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
+    const uint32_t per_warp = (units + nwarps - 1u) / nwarps;
+    return per_warp >= kClaimChunk ? kClaimChunk : (per_warp ? per_warp : 1u);
+}
+#endif
 constexpr uint64_t kSlotFree = ~0ull;
 constexpr uint32_t kValMulti = 0xFFFFu;            // a group is < 65535
 constexpr uint32_t kMaxDisp = 6;
@@ -185,8 +195,12 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     const uint64_t kmask = (kt.rmask << 3) | 7ull;
     const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
 
+    // A small batch is spread over all warps -- ceil(units / warps) lanes of each take one unit -- instead of filling the first
+    // warps' lanes twice: the kernel then lasts one read, not two, and every SM takes part.
+    const uint32_t chunk = claim_chunk(units);
+
     // lane state
-    uint32_t phase = H_FETCH;
+    uint32_t phase = (!WPR && lane >= chunk) ? H_DONE : H_FETCH;
     bool mate2 = false;
     uint32_t u = 0u;                             // unit (read or pair)
     uint64_t g0 = 0ull;                          // first 32-base group of the current read
@@ -253,12 +267,12 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 uint32_t nbase = 0u;
                 if (cnt > left)
                 {
-                    if (lane == 0u) nbase = (uint32_t)atomicAdd(a.work, (unsigned long long)kClaimChunk);
+                    if (lane == 0u) nbase = (uint32_t)atomicAdd(a.work, (unsigned long long)chunk);
                     nbase = __shfl_sync(kFullH, nbase, 0);
                 }
                 const uint32_t r = (uint32_t)__popc(mc & ((1u << lane) - 1u));
                 if (claim) u = r < left ? wcur + r : nbase + (r - left);
-                if (cnt > left) { wcur = nbase + (cnt - left); wend = nbase + kClaimChunk; }
+                if (cnt > left) { wcur = nbase + (cnt - left); wend = nbase + chunk; }
                 else wcur += cnt;
             }
             if (ph == H_FETCH)
@@ -631,8 +645,9 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
 
     // the tables stream from HBM and must not push the presence filter out of L2
     const uint64_t pol_keep = l2_policy_keep(), pol_stream = l2_policy_stream();
+    const uint32_t chunk = claim_chunk(units);                    // see scanh_kernel
 
-    uint32_t phase = H_FETCH;
+    uint32_t phase = lane >= chunk ? H_DONE : H_FETCH;
     bool mate2 = false;
     uint32_t u = 0u;
     uint64_t g0 = 0ull;
@@ -690,12 +705,12 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                 uint32_t cbase = 0u;
                 if (cnt > left)
                 {
-                    if (lane == 0u) cbase = (uint32_t)atomicAdd(a.work, (unsigned long long)kClaimChunk);
+                    if (lane == 0u) cbase = (uint32_t)atomicAdd(a.work, (unsigned long long)chunk);
                     cbase = __shfl_sync(kFullH, cbase, 0);
                 }
                 const uint32_t r = (uint32_t)__popc(mc & ((1u << lane) - 1u));
                 if (claim) u = r < left ? wcur + r : cbase + (r - left);
-                if (cnt > left) { wcur = cbase + (cnt - left); wend = cbase + kClaimChunk; }
+                if (cnt > left) { wcur = cbase + (cnt - left); wend = cbase + chunk; }
                 else wcur += cnt;
             }
             if (ph == H_FETCH)
