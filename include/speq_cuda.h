@@ -182,6 +182,11 @@ int speqg_scan_info(speqg_scan * scan, uint32_t * algorithm, uint64_t * structur
  * speqg_scan_finish, which then returns the global tallies.  u64_counters: unique[n_groups], back-check totals[n_groups],
  * then total_kmers, ambiguous_reads, lookups, steps_executed, kmers_hit, occurrences, occ_sectors, reads (*n_u64 entries);
  * f64_counters: the local-mode tallies (*n_f64 = n_groups entries).  Any output pointer may be NULL. */
+/* Ambiguous reads / pairs by the variants that met in them (fix-forward of the reference's fusion_totals map, whose key is
+ * always the empty set because set_groups is passed by value, src/fm_scanner.cpp:915-916,983-995,1033): counts[a * n_groups
+ * + b] = units whose smallest unique variant is a and largest is b (a < b); the entries sum to ambiguous_reads.  Syncs the
+ * scan.  Kept for indexes of at most 1024 variants; not filled by SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64. */
+int speqg_scan_fusion_counts(speqg_scan * scan, uint64_t * counts);
 int speqg_scan_device_counters(speqg_scan * scan, uint64_t ** u64_counters, uint64_t * n_u64, double ** f64_counters, uint64_t * n_f64);
 void speqg_scan_close(speqg_scan * scan);
 

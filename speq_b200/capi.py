@@ -79,6 +79,7 @@ SIGNATURES = {
     "speqg_scan_reset": (C.c_int, [C.c_void_p]),
     "speqg_scan_stats": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Counts)]),
     "speqg_scan_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "speqg_scan_fusion_counts": (C.c_int, [C.c_void_p, C.c_void_p]),
     "speqg_scan_device_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p),
                                              C.POINTER(C.c_uint64)]),
     "speqg_scan_close": (None, [C.c_void_p]),

@@ -87,6 +87,7 @@ struct speqg_scan
     // unique[V] total_g[V] scalars[SC_COUNT] unique_w[V] bad[1] work[1]; h_state is its pinned host mirror.  The integer
     // counters come first so that a multi-GPU driver sums them across ranks in place with one all-reduce
     // (speqg_scan_device_counters)
+    unsigned long long * d_fusion = nullptr;   // [V * V] ambiguous units by (smallest, largest) unique variant; V <= kMaxFusionGroups
     unsigned long long * d_state = nullptr, * h_state = nullptr;
     size_t state_words = 0;
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
@@ -132,7 +133,7 @@ namespace
 {
 void scan_release(speqg_scan * s)
 {
-    cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_mult);
+    cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_fusion); cudaFree(s->d_mult);
     cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
     cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
@@ -156,6 +157,7 @@ ScanArgs scan_args(speqg_scan * s)
     a.segs = nullptr;
     a.n_segs = 0;
     a.work = s->d_work;
+    a.fusion = s->d_fusion;
 
     return a;
 }
@@ -170,6 +172,8 @@ void check_batch(speqg_scan * s, speqg_batch const * b)
     need(b->n_reads < (uint64_t(1) << 32), "more than 2^32 reads in one batch");
 }
 
+// the (smallest, largest variant) matrix of ambiguous units is kept for indexes of at most this many variants (8 MB)
+constexpr uint32_t kMaxFusionGroups = 1024;
 // reads at least this long on average are scanned by a warp each (scanh.cu, WPR) instead of by a lane each
 constexpr uint64_t kWarpPerReadBases = 1024;
 
@@ -257,6 +261,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->d_unique_w = reinterpret_cast<double *>(s->d_scalars + SC_COUNT);
         s->d_bad = s->d_scalars + SC_COUNT + V;
         s->d_work = s->d_bad + 1;
+        if (V <= kMaxFusionGroups) s->d_fusion = dev_alloc<unsigned long long>((size_t)V * V);
         s->d_percent = dev_alloc<double>(V);
         s->d_tkpg = dev_alloc<double>(V);
         s->d_gc = dev_alloc<int32_t>(V);
@@ -390,6 +395,7 @@ int speqg_scan_reset(speqg_scan * s)
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
     CK(cudaMemsetAsync(s->d_state, 0, s->state_words * 8, s->compute));
+    if (s->d_fusion) CK(cudaMemsetAsync(s->d_fusion, 0, (size_t)s->idx->host.V * s->idx->host.V * 8, s->compute));
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
     if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
     if (s->d_pair_mult) CK(cudaMemsetAsync(s->d_pair_mult, 0, 4ull * ((uint64_t)s->kp.nbmask + 1) * 8, s->compute));
@@ -541,6 +547,19 @@ int speqg_scan_device_counters(speqg_scan * s, uint64_t ** u64_counters, uint64_
     if (n_u64) *n_u64 = 2 * (uint64_t)V + SC_COUNT;
     if (f64_counters) *f64_counters = s->d_unique_w;
     if (n_f64) *n_f64 = V;
+    SPEQG_CATCH
+}
+
+int speqg_scan_fusion_counts(speqg_scan * s, uint64_t * counts)
+{
+    SPEQG_TRY
+    need(s != nullptr && counts != nullptr, "NULL argument");
+    need(s->d_fusion != nullptr, "the scan keeps no fusion counts (more than 1024 variants)");
+    need(s->algo != SPEQG_ALGO_DIRECT && s->algo != SPEQG_ALGO_ROLLING64, "fusion counts are kept by the product kernels only");
+    device_guard guard(s->device);
+    uint32_t V = s->idx->host.V;
+    CK(cudaMemcpyAsync(counts, s->d_fusion, (size_t)V * V * 8, cudaMemcpyDeviceToHost, s->compute));
+    CK(cudaStreamSynchronize(s->compute));
     SPEQG_CATCH
 }
 

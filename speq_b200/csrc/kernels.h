@@ -41,6 +41,7 @@ struct ScanArgs
     const SegmentX * segs;             // optional segment table (back-check); null: one segment per read / pair
     uint64_t n_segs;
     unsigned long long * work;        // scan32: next unclaimed unit minus the number of threads (zero at launch)
+    unsigned long long * fusion;      // [V * V] or null: ambiguous units by (smallest, largest) unique variant
 };
 
 struct LaunchCfg

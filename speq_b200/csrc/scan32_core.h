@@ -72,6 +72,7 @@ SPEQB_HD void lane32_init(Lane32 & s, uint64_t first_unit, uint32_t n)
 //   void     env.record(lb)                one more valid window whose k-mer interval starts at lb
 //   void     env.count_fetch(nwin)         a read with nwin windows was presented
 //   void     env.count_unit(total, amb)    a unit ended with `total` valid windows; amb: it was ambiguous
+//   void     env.fusion(gmin, gmax)        an ambiguous unit ended: its smallest and largest unique variant
 template <class Env>
 SPEQB_HD void lane32_flush_agg(Lane32 & s, Env & env)
 {
@@ -147,7 +148,9 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
         else
         {
             // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
-            env.count_unit(s.c_total, s.gmin != kNoGroup && s.gmin != s.gmax);
+            const bool amb = s.gmin != kNoGroup && s.gmin != s.gmax;
+            env.count_unit(s.c_total, amb);
+            if (amb) env.fusion(s.gmin, s.gmax);
             s.c_total = 0u;
             s.gmin = kNoGroup; s.gmax = 0u;
             s.flags &= ~F_MATE2;

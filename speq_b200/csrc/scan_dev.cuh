@@ -88,6 +88,12 @@ template <int MODE> struct Tally32
         if (total) add64(0, total);
         if (amb) add64(1, 1u);
     }
+    // an ambiguous unit (is_ambiguous, src/fm_scanner.cpp:183-190): which variants met -- the key of the reference's
+    // fusion_totals map (src/fm_scanner.cpp:983-995), reduced to the smallest and largest variant of the unit
+    __device__ __forceinline__ void fusion(uint32_t gmin, uint32_t gmax) const
+    {
+        if (a.fusion) atomicAdd(a.fusion + (uint64_t)gmin * a.V + gmax, 1ull);
+    }
 };
 
 __device__ __forceinline__ void smem32_clear(Smem32 const & sm, uint32_t V)

@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                     gmin = __reduce_min_sync(kFullH, gmin);
                     gmax = __reduce_max_sync(kFullH, gmax);
                     n_total += c_total;
-                    if (lane == 0u) n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
+                    if (lane == 0u && gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
                     c_total = 0u; gmin = kNoGroup; gmax = 0u;
                     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                     agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
@@ -440,7 +440,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
             {
                 // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
                 n_total += c_total;
-                n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
+                if (gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
                 c_total = 0u; gmin = kNoGroup; gmax = 0u;
                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                 agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
@@ -902,7 +902,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
             {
                 // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
                 n_total += c_total;
-                n_amb += (gmin != kNoGroup && gmin != gmax) ? 1u : 0u;
+                if (gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
                 c_total = 0u; gmin = kNoGroup; gmax = 0u;
                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                 agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;

@@ -244,6 +244,12 @@ class Scan:
         capi.check(capi.lib().speqg_scan_info(self.h, C.byref(a), C.byref(nb), C.byref(nk)))
         return {"algorithm": int(a.value), "structure_bytes": int(nb.value), "keys": int(nk.value)}
 
+    def fusion_counts(self) -> np.ndarray:
+        """u64[V, V]: ambiguous reads / pairs by (smallest, largest) unique variant; sums to ScanResult.ambiguous."""
+        out = np.zeros((self.V, self.V), np.uint64)
+        capi.check(capi.lib().speqg_scan_fusion_counts(self.h, out.ctypes.data))
+        return out
+
     def device_counters(self):
         """The handle's counters as torch tensors over its device memory (int64 view of the u64 counters, float64 local-mode
         tallies): a multi-GPU driver all-reduces them in place on the scan's stream before finish()."""

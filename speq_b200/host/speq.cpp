@@ -367,7 +367,7 @@ std::vector<double> unique_to_percent(std::vector<double> const & unique_in_read
 // --write-output: the per-variant result table as tab-separated text in -o/--output.  The reference declares the option
 // (src/arg_parse.cpp:20) and reports on stderr only; this is the fix-forward of SURVEY.md 8f-4, off by default.
 void write_table(fs::path const & p, idx_meta const & meta, scan_out const & so, std::vector<double> const & unique_totals,
-                 std::vector<double> const & initial, std::vector<double> const & fin)
+                 std::vector<double> const & initial, std::vector<double> const & fin, std::vector<uint64_t> const & fusion)
 {
     FILE * f = fopen(p.c_str(), "w");
     if (!f) throw std::runtime_error("cannot write " + p.string());
@@ -376,6 +376,18 @@ void write_table(fs::path const & p, idx_meta const & meta, scan_out const & so,
     fprintf(f, "group\tisolates\tunique_kmers\tpercent_initial\tpercent_final\n");
     for (size_t g = 0; g < fin.size(); ++g)
         fprintf(f, "%s\t%d\t%.17g\t%.17g\t%.17g\n", meta.group_names[g].c_str(), meta.group_counts[g], unique_totals[g], initial[g], fin[g]);
+    // the fix-forward of the reference's fusion_totals report (src/fm_scanner.cpp:983-995,1033): ambiguous reads / pairs by
+    // the smallest and largest variant whose unique k-mers they hold
+    const size_t V = fin.size();
+    if (fusion.size() == V * V)
+    {
+        fprintf(f, "# ambiguous reads / pairs by the variants that met in them\nfusion\tgroup_a\tgroup_b\tcount\n");
+        for (size_t a = 0; a < V; ++a)
+            for (size_t b = 0; b < V; ++b)
+                if (fusion[a * V + b])
+                    fprintf(f, "fusion\t%s\t%s\t%llu\n", meta.group_names[a].c_str(), meta.group_names[b].c_str(),
+                            static_cast<unsigned long long>(fusion[a * V + b]));
+    }
     fclose(f);
 }
 
@@ -528,7 +540,22 @@ int do_scan(cmd_arguments & args)
             ++iters;
         }
         double t_refine = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-        if (args.write_output) write_table(args.out_file_path, meta, so, unique_totals, initial, percent);
+        if (args.write_output)
+        {
+            // ambiguous reads / pairs by the variants that met in them, summed over the devices
+            std::vector<uint64_t> fusion;
+            if (V <= 1024)
+            {
+                fusion.assign(static_cast<size_t>(V) * V, 0);
+                std::vector<uint64_t> part(fusion.size());
+                for (auto & L : lanes)
+                {
+                    ck(speqg_scan_fusion_counts(L.scan, part.data()), "speqg_scan_fusion_counts");
+                    for (size_t i = 0; i < part.size(); ++i) fusion[i] += part[i];
+                }
+            }
+            write_table(args.out_file_path, meta, so, unique_totals, initial, percent, fusion);
+        }
         if (!args.json_path.empty())
             write_json(args.json_path, args, local, paired, unique_ref, total_ref, so, unique_totals, initial, percent, iters, t_backcheck, t_refine);
     }

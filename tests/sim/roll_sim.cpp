@@ -108,6 +108,7 @@ struct HostEnv32
     void record(uint32_t lb) const { if (mult) ++mult[lb]; }
     void count_fetch(uint32_t nwin) const { look += nwin; }
     void count_unit(uint32_t t, bool a) const { total += t; amb += a ? 1 : 0; }
+    void fusion(uint32_t, uint32_t) const {}
 };
 
 struct HostEnv

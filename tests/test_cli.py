@@ -140,8 +140,12 @@ def test_speq_all_matches_golden(speq_bin, tmp_path, name):
     rows = [ln.split("\t") for ln in (tmp_path / "table.tsv").read_text().strip().split("\n")]
     assert rows[0] == ["# total_kmers", str(exp["total_kmers"])] and rows[1] == ["# ambiguous_reads", str(exp["ambiguous"])]
     assert rows[2] == ["group", "isolates", "unique_kmers", "percent_initial", "percent_final"]
-    assert [float(r[4]) for r in rows[3:]] == out2["percent_final"]
-    assert [float(r[3]) for r in rows[3:]] == out2["percent_initial"]
+    nv = len(out2["percent_final"])
+    assert [float(r[4]) for r in rows[3:3 + nv]] == out2["percent_final"]
+    assert [float(r[3]) for r in rows[3:3 + nv]] == out2["percent_initial"]
+    # then the fusion report: ambiguous reads / pairs by the variants that met in them; the counts sum to ambiguous_reads
+    assert rows[3 + nv][0].startswith("# ambiguous") and rows[4 + nv] == ["fusion", "group_a", "group_b", "count"]
+    assert sum(int(r[3]) for r in rows[5 + nv:]) == exp["ambiguous"]
 
 
 def _write_fq(path, recs, newline="\n", trailing=True):

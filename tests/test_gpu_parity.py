@@ -398,6 +398,51 @@ def test_long_reads_warp_per_read(lib, mode):
     idx.close()
 
 
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR])
+@pytest.mark.parametrize("paired", [False, True])
+def test_fusion_counts(lib, algorithm, paired):
+    """speqg_scan_fusion_counts: ambiguous units by (smallest, largest) unique variant.  Checked against the same scan run on
+    every unit alone (the variants with a non-zero unique tally are the unit's set); long reads take the warp-per-read form."""
+    rng = np.random.default_rng(5)
+    V, G, k = 4, 6000, 15
+    scaff = [np.where((s := rng.integers(0, 4, G)) == 3, 4, s).astype(np.uint8) for _ in range(V)]   # unrelated variants
+    idx = engine.Index.from_scaffolds(scaff, list(range(V)), V)
+    letters = np.frombuffer(b"ACGNT", np.uint8)
+    for L, R in ((120, 240), (3000, 40)):
+        parts = []
+        for i in range(R):
+            a, b, c = rng.integers(0, V, 3)
+            p = int(rng.integers(0, G - L))
+            r = scaff[int(a)][p:p + L].copy()
+            if i % 3 == 1:                                            # chimera of two variants
+                r[L // 2:] = scaff[int(b)][p + L // 2:p + L]
+            if i % 3 == 2:                                            # three variants
+                r[L // 3:2 * L // 3] = scaff[int(b)][p + L // 3:p + 2 * L // 3]
+                r[2 * L // 3:] = scaff[int(c)][p + 2 * L // 3:p + L]
+            parts.append(letters[r])
+        seq = np.concatenate(parts)
+        qual = np.full(seq.size, ord("I"), np.uint8)
+        offs = np.arange(R + 1, dtype=np.uint64) * L
+        sc = engine.Scan(idx, k=k, algorithm=algorithm, paired=paired)
+        sc.submit_raw(seq, qual, offs, R)
+        r = sc.finish()
+        fus = sc.fusion_counts()
+        assert int(fus.sum()) == r.ambiguous > 0
+        assert np.all(np.tril(fus) == 0)                              # smallest < largest
+        exp = np.zeros((V, V), np.uint64)
+        step = 2 if paired else 1
+        for u in range(0, R, step):
+            sc.reset()
+            sc.submit_raw(seq, qual, offs[u:u + step + 1], step)
+            ru = sc.finish()
+            nz = np.nonzero(ru.unique)[0]
+            if nz.size > 1:
+                exp[nz[0], nz[-1]] += 1
+        assert np.array_equal(fus, exp)
+        sc.close()
+    idx.close()
+
+
 def test_device_counters_reduce_in_place(lib):
     """speqg_scan_device_counters: the counters a multi-GPU driver sums across ranks in place before finish().  One GPU: the
     views hold what finish() returns, and an in-place update on the scan's stream (here: doubling, what an all-reduce over two
