@@ -182,17 +182,17 @@ void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
 {
     if (v.n_reads == 0) return;
     ScanArgs a = scan_args(s);
+    static const uint64_t wpr_bases = getenv("SPEQB_WPR_BASES") ? strtoull(getenv("SPEQB_WPR_BASES"), nullptr, 10) : kWarpPerReadBases;
+    const int wpr = groups * 32u >= v.n_reads * wpr_bases;   // table scans: a warp per read for batches of long reads
     if (s->algo == SPEQG_ALGO_DIRECT) CK(launch_scan_direct(s->view, v, a, s->mode, 0, s->cfg_direct, s->compute));
     else if (s->algo == SPEQG_ALGO_ROLLING64) CK(launch_scan_roll(s->view, v, a, s->mode, s->cfg64, s->compute));
     else if (s->algo == SPEQG_ALGO_KPAIR)
     {
-        CK(launch_scanp(s->kt, s->kp, s->d_slot_mult, s->d_pair_mult, v, a, s->mode, s->cfg_p, s->compute));
+        CK(launch_scanp(s->kt, s->kp, s->d_slot_mult, s->d_pair_mult, v, a, s->mode, wpr, s->cfg_p, s->compute));
         if (s->mode & M_RECORD) s->slot_mult_dirty = true;
     }
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
-        static const uint64_t wpr_bases = getenv("SPEQB_WPR_BASES") ? strtoull(getenv("SPEQB_WPR_BASES"), nullptr, 10) : kWarpPerReadBases;
-        const int wpr = groups * 32u >= v.n_reads * wpr_bases;
         CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, wpr, s->cfg_h, s->compute));
         if (s->mode & M_RECORD) s->slot_mult_dirty = true;
     }

@@ -112,7 +112,7 @@ cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv,
 cudaError_t launch_kpair_fold_mult(KTabView const & kp, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,
                                    unsigned long long * mult, cudaStream_t st);
 cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long long * slot_mult, unsigned long long * pair_mult,
-                         BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg, cudaStream_t st);
+                         BatchView const & b, ScanArgs const & a, int mode, int warp_per_read, LaunchCfg cfg, cudaStream_t st);
 cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

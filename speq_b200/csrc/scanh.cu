@@ -623,7 +623,8 @@ __global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(const KTabView
 #endif
 constexpr int kPair = SPEQB_PWIN;     // pairs of windows per lane and loop trip
 
-template <int MODE>
+// WPR: a warp per read, as in scanh_kernel (long reads)
+template <int MODE, bool WPR>
 __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) scanp_kernel(const KTabView kt, const KTabView kp, unsigned long long * __restrict__ slot_mult,
                                                                                   unsigned long long * __restrict__ pair_mult, const BatchView b, const ScanArgs a,
                                                                                   const int paired)
@@ -647,7 +648,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     const uint64_t pol_keep = l2_policy_keep(), pol_stream = l2_policy_stream();
     const uint32_t chunk = claim_chunk(units);                    // see scanh_kernel
 
-    uint32_t phase = lane >= chunk ? H_DONE : H_FETCH;
+    uint32_t phase = (!WPR && lane >= chunk) ? H_DONE : H_FETCH;
     bool mate2 = false;
     uint32_t u = 0u;
     uint64_t g0 = 0ull;
@@ -699,7 +700,22 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
         {
             const bool claim = ph == H_FETCH && !mate2;
             const uint32_t mc = __ballot_sync(kFullH, claim);
-            if (mc)
+            if (WPR)
+            {
+                if (mc)
+                {
+                    if (wcur == wend)
+                    {
+                        uint32_t nb0 = 0u;
+                        if (lane == 0u) nb0 = (uint32_t)atomicAdd(a.work, (unsigned long long)kClaimChunkW);
+                        wcur = __shfl_sync(kFullH, nb0, 0);
+                        wend = wcur + kClaimChunkW;
+                    }
+                    u = wcur;
+                    wcur += 1u;
+                }
+            }
+            else if (mc)
             {
                 const uint32_t cnt = (uint32_t)__popc(mc), left = wend - wcur;
                 uint32_t cbase = 0u;
@@ -728,18 +744,30 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
         if (ph == H_FIRST)
         {
             const uint32_t L = pend;
-            pend = L >= k ? L : 0u;                               // L < k: the sliding view is empty (sliding.hpp:129-142)
-            n_look += L >= k ? L - k + 1u : 0u;
-            n_reads += 1u;
-            t = 0u; run = 0u; key = 0ull;
-            if (pend)
+            run = 0u; key = 0ull;
+            if (WPR)
             {
-                cb = load_ro(b.bases + g0);
-                ci = load_ro(b.inv + g0);
-                if (pend > 32u)
+                const uint32_t nwin = L >= k ? L - k + 1u : 0u, per = (nwin + 31u) >> 5;
+                const uint32_t s0 = lane * per < nwin ? lane * per : nwin, s1 = nwin - s0 < per ? nwin : s0 + per;
+                if (lane == 0u) { n_look += nwin; n_reads += 1u; }
+                t = s0;
+                pend = s1 > s0 ? s1 + k - 1u : s0;                // this lane's bases: its windows and the k-1 bases before
+            }
+            else
+            {
+                pend = L >= k ? L : 0u;                           // L < k: the sliding view is empty (sliding.hpp:129-142)
+                n_look += L >= k ? L - k + 1u : 0u;
+                n_reads += 1u;
+                t = 0u;
+            }
+            if (t < pend)
+            {
+                cb = load_ro(b.bases + g0 + (t >> 5));
+                ci = load_ro(b.inv + g0 + (t >> 5));
+                if (((t >> 5) + 1u) * 32u < pend)
                 {
-                    nb = load_ro(b.bases + g0 + 1u);
-                    ni = load_ro(b.inv + g0 + 1u);
+                    nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
+                    ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
                 }
             }
             phase = H_RUN;
@@ -895,7 +923,33 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                 }
             }
         }
-        if (phase == H_RUN && t >= pend)
+        if (WPR)
+        {
+            // the lane's share of the read is finished: wait for the warp, then merge the read's ambiguity state
+            if (phase == H_RUN && t >= pend) phase = H_WAIT;
+            if (__all_sync(kFullH, phase == H_WAIT))
+            {
+                if (paired && !mate2) mate2 = true;
+                else
+                {
+                    gmin = __reduce_min_sync(kFullH, gmin);
+                    gmax = __reduce_max_sync(kFullH, gmax);
+                    n_total += c_total;
+                    if (lane == 0u && gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
+                    c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                    if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+                    agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
+                    mate2 = false;
+                    if ((n_total | n_look) & 0x80000000u)
+                    {
+                        env.add64(0, n_total); env.add64(2, n_look);
+                        n_total = 0u; n_look = 0u;
+                    }
+                }
+                phase = H_FETCH;
+            }
+        }
+        else if (phase == H_RUN && t >= pend)
         {
             if (paired && !mate2) mate2 = true;
             else
@@ -1044,10 +1098,14 @@ cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, Ba
 #define SPEQB_SCANP_DISPATCH(M, EXPR)                                                   \
     switch (M)                                                                          \
     {                                                                                   \
-        case 0: { auto kern = scanp_kernel<0>; EXPR; break; }                           \
-        case M_RECORD: { auto kern = scanp_kernel<M_RECORD>; EXPR; break; }             \
-        case M_LOCAL: { auto kern = scanp_kernel<M_LOCAL>; EXPR; break; }               \
-        case M_LOCAL | M_RECORD: { auto kern = scanp_kernel<M_LOCAL | M_RECORD>; EXPR; break; } \
+        case 0: { auto kern = scanp_kernel<0, false>; EXPR; break; }                    \
+        case M_RECORD: { auto kern = scanp_kernel<M_RECORD, false>; EXPR; break; }      \
+        case M_LOCAL: { auto kern = scanp_kernel<M_LOCAL, false>; EXPR; break; }        \
+        case M_LOCAL | M_RECORD: { auto kern = scanp_kernel<M_LOCAL | M_RECORD, false>; EXPR; break; } \
+        case kWprBit: { auto kern = scanp_kernel<0, true>; EXPR; break; }               \
+        case kWprBit | M_RECORD: { auto kern = scanp_kernel<M_RECORD, true>; EXPR; break; } \
+        case kWprBit | M_LOCAL: { auto kern = scanp_kernel<M_LOCAL, true>; EXPR; break; } \
+        case kWprBit | M_LOCAL | M_RECORD: { auto kern = scanp_kernel<M_LOCAL | M_RECORD, true>; EXPR; break; } \
         default: return cudaErrorInvalidValue;                                          \
     }
 
@@ -1056,24 +1114,29 @@ cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     const size_t smem = scan32_smem_bytes(V);
     int bps = 0;
     cudaError_t e = cudaSuccess;
-    const int m = mode & (M_LOCAL | M_RECORD);
-    SPEQB_SCANP_DISPATCH(m, {
-        if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlockH, smem);
-    })
-    if (e != cudaSuccess) return e;
-    if (bps <= 0) return cudaErrorLaunchOutOfResources;
+    for (int wpr = 0; wpr <= kWprBit; wpr += kWprBit)
+    {
+        const int m = (mode & (M_LOCAL | M_RECORD)) | wpr;
+        int bw = 0;
+        SPEQB_SCANP_DISPATCH(m, {
+            if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, kern, kBlockH, smem);
+        })
+        if (e != cudaSuccess) return e;
+        if (bw <= 0) return cudaErrorLaunchOutOfResources;
+        bps = wpr == 0 || bw < bps ? bw : bps;
+    }
     cfg->block = kBlockH;
     cfg->grid = sm_count_h() * bps;
     return cudaSuccess;
 }
 
 cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long long * slot_mult, unsigned long long * pair_mult,
-                         BatchView const & b, ScanArgs const & a, int mode, LaunchCfg cfg, cudaStream_t st)
+                         BatchView const & b, ScanArgs const & a, int mode, int warp_per_read, LaunchCfg cfg, cudaStream_t st)
 {
     const size_t smem = scan32_smem_bytes(a.V);
     const int paired = (mode & M_PAIRED) ? 1 : 0;
-    const int m = mode & (M_LOCAL | M_RECORD);
+    const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     SPEQB_SCANP_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, kp, slot_mult, pair_mult, b, a, paired)))

@@ -383,18 +383,19 @@ def test_long_reads_warp_per_read(lib, mode):
         return r, extra
 
     for paired in (False, True):
-        a, ea = run(capi.ALGO_KTABLE, paired)
         b, eb = run(capi.ALGO_ROLLING, paired)
-        assert a.total_kmers > 0 and 0 < a.ambiguous < (R // 2 if paired else R)
-        assert a.total_kmers == b.total_kmers and a.ambiguous == b.ambiguous and a.lookups == b.lookups
-        assert a.reads == b.reads
-        if mode == "local":
-            assert helpers.rel_close(a.unique_w, b.unique_w, 1e-12)
-        else:
-            assert np.array_equal(a.unique, b.unique)
-        if mode == "record":
-            assert ea[0] == eb[0]
-            assert helpers.rel_close(ea[1], eb[1], 1e-11)
+        for alg in (capi.ALGO_KTABLE, capi.ALGO_KPAIR):                 # both table kernels have the warp-per-read form
+            a, ea = run(alg, paired)
+            assert a.total_kmers > 0 and 0 < a.ambiguous < (R // 2 if paired else R)
+            assert a.total_kmers == b.total_kmers and a.ambiguous == b.ambiguous and a.lookups == b.lookups
+            assert a.reads == b.reads
+            if mode == "local":
+                assert helpers.rel_close(a.unique_w, b.unique_w, 1e-12)
+            else:
+                assert np.array_equal(a.unique, b.unique)
+            if mode == "record":
+                assert ea[0] == eb[0]
+                assert helpers.rel_close(ea[1], eb[1], 1e-11)
     idx.close()
 
 
