@@ -121,7 +121,7 @@ int speqg_pack_reads(const uint8_t * seq, const uint8_t * qual, const uint64_t *
 #define SPEQG_MODE_GLOBAL 0   /* --fixed-accuracy != 0: integer unique tallies (src/fm_scanner.cpp:180) */
 #define SPEQG_MODE_LOCAL 1    /* fp64 tallies weighted by prod 1/(1-10^(-q/10)) (src/fm_scanner.cpp:454-455) */
 
-#define SPEQG_ALGO_ROLLING 0  /* one pass per read: consecutive windows share their search state (default) */
+#define SPEQG_ALGO_ROLLING 0  /* one pass per read: consecutive windows share their search state (any k) */
 #define SPEQG_ALGO_DIRECT 1   /* every window searched from the root, k steps, like seqan3's search_trivial (global mode) */
 #define SPEQG_ALGO_ROLLING64 2 /* the rolling search on the generic 64-byte blocks (the back-check's kernel); cross-checks */
 #define SPEQG_ALGO_KTABLE 3   /* k <= 31: the search memoised per (index, k) as a k-mer table built from the index's own texts;
@@ -129,7 +129,8 @@ int speqg_pack_reads(const uint8_t * seq, const uint8_t * qual, const uint64_t *
 #define SPEQG_ALGO_AUTO 4     /* k <= 31: KTABLE, or KPAIR when the k-mer table is larger than 3/4 of L2 and the index has <= 254
                                  variants; else ROLLING */
 #define SPEQG_ALGO_KPAIR 5    /* KTABLE plus a table over the (k+1)-mers of the texts: one probe answers two consecutive
-                                 windows; a miss falls back to two k-mer probes.  k <= 31, <= 254 variants */
+                                 windows; a miss falls back to two k-mer probes; a presence filter of the k-mers (kept in L2)
+                                 answers absent k-mers before either table is touched.  k <= 31, <= 254 variants */
 
 typedef struct speqg_params
 {
