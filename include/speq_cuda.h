@@ -186,10 +186,34 @@ int speqg_scan_info(speqg_scan * scan, uint32_t * algorithm, uint64_t * structur
 /* Ambiguous reads / pairs by the variants that met in them (fix-forward of the reference's fusion_totals map, whose key is
  * always the empty set because set_groups is passed by value, src/fm_scanner.cpp:915-916,983-995,1033): counts[a * n_groups
  * + b] = units whose smallest unique variant is a and largest is b (a < b); the entries sum to ambiguous_reads.  Syncs the
- * scan.  Kept for indexes of at most 1024 variants; not filled by SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64. */
+ * scan.  Derived from the set map below; not filled by SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64. */
 int speqg_scan_fusion_counts(speqg_scan * scan, uint64_t * counts);
+/* The same by the full SET of variants: the key std::map<std::set<int>,int> fusion_totals of the reference was meant to hold
+ * (src/fm_scanner.cpp:915, 947-952 inserts both sides of every change of variant, :983-995 counts the unit under its set).
+ * keys[i] / counts[i], i < min(*n_sets, capacity): for indexes of at most 64 variants keys[i] has bit g set for every variant g
+ * with a unique k-mer in the unit; above 64 variants keys[i] = 1 << 63 | more << 32 | largest << 16 | smallest, `more` = further
+ * variants lie between the two.  *n_sets = distinct sets seen (call with capacity 0 to size the arrays).  The device map holds
+ * 2^20 sets; units that found no place are counted in *unkeyed_units (0 in practice; they are still part of ambiguous_reads).
+ * Syncs the scan.  Not filled by SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64. */
+int speqg_scan_fusion_sets(speqg_scan * scan, uint64_t * keys, uint64_t * counts, uint64_t capacity, uint64_t * n_sets,
+                           uint64_t * unkeyed_units);
 int speqg_scan_device_counters(speqg_scan * scan, uint64_t ** u64_counters, uint64_t * n_u64, double ** f64_counters, uint64_t * n_f64);
 void speqg_scan_close(speqg_scan * scan);
+
+/* The device packer as an entry point of its own: raw reads that already live in device memory -> a packed batch in device
+ * memory (what speqg_scan_submit_raw runs behind its host-to-device copy; same rules as speqg_pack_reads).  d_seq / d_qual /
+ * d_offsets: device pointers (read i = bytes [d_offsets[i], d_offsets[i+1]) of d_seq; d_qual may be NULL).  device_batch: device
+ * pointers of preallocated arrays; grp_off[0..n_reads] is an INPUT (first 32-base group of every read, e.g. a running sum of
+ * ceil(len / 32)), bases / inv / len (and qual when not NULL) are written.  Several calls may fill disjoint read ranges of one
+ * large batch.  Asynchronous on `stream` (NULL: the default stream) except for the final check: an illegal (non-IUPAC) letter
+ * -> SPEQG_EINVAL, like the reference's seqan3::parse_error. */
+int speqg_pack_device(int device, const uint8_t * d_seq, const uint8_t * d_qual, const uint64_t * d_offsets, uint64_t n_reads,
+                      int encoding, uint32_t phred_cutoff, int n_only, const speqg_batch * device_batch, void * stream);
+
+/* Measurement aid (not on the scan path): giga (1e9) INDEPENDENT random 32-byte sector loads per second this device serves
+ * from a table of table_bytes -- the roofline of kernels whose every access is one data-dependent sector (k-mer table probes,
+ * rank steps of the FM search).  Allocates and frees the table; takes the best of a few launch shapes. */
+int speqg_probe_random_sectors(int device, uint64_t table_bytes, double * gsectors_per_s);
 
 /* page-locked host memory for read batches (replaces the heap vectors seqan3's record buffer holds,
  * deps/seqan3/include/seqan3/range/views/async_input_buffer.hpp:89-116). */

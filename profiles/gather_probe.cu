@@ -48,11 +48,99 @@ __global__ void __launch_bounds__(256) gather(const uint8_t * __restrict__ base,
     if (acc == 0x12345678u) out[0] = acc;
 }
 
-template <int BYTES, int ILP> void run(const char * name, const uint8_t * d, uint64_t bytes, uint32_t stride, uint32_t * out)
+
+// ---- round 2: what decides the HBM-resident (C4) rate?  (VERDICT r1 "weak #5")
+// LINE4: lanes 4i..4i+3 of a warp load the four sectors of ONE random 128-byte line with one instruction
+// SEQ4 : one lane loads the four sectors of a random 128-byte line with four back-to-back v8 loads
+// PF128: a 32-byte load with the L2::128B prefetch-size qualifier
+// PAGES: random sectors confined to the first `window` bytes of every 2 MB page of the table -- an L2-sized footprint spread
+//        over as many pages as the whole table has: separates TLB reach from DRAM access
+enum { V_LINE4 = 0, V_SEQ4 = 1, V_PF128 = 2, V_PAGES = 3 };
+template <int VAR, int ILP>
+__global__ void __launch_bounds__(256) gather2(const uint8_t * __restrict__ base, uint64_t units, uint64_t window, int iters, uint32_t * out)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    uint64_t x = (blockIdx.x * 256ull + (VAR == V_LINE4 ? (threadIdx.x & ~3u) : threadIdx.x)) * 0x9E3779B97F4A7C15ull + 12345;
+    uint32_t acc = 0;
+    for (int it = 0; it < iters; ++it)
+    {
+        uint32_t v[ILP];
+#pragma unroll
+        for (int j = 0; j < ILP; ++j)
+        {
+            x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+            uint32_t w[8];
+            if (VAR == V_LINE4)
+            {
+                const uint8_t * p = base + (x % units) * 128ull + (lane & 3u) * 32u;      // units = lines
+                asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p));
+                v[j] = w[0] ^ w[7];
+            }
+            else if (VAR == V_SEQ4)
+            {
+                const uint8_t * p = base + (x % units) * 128ull;
+                uint32_t a = 0;
+#pragma unroll
+                for (int s = 0; s < 4; ++s)
+                {
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p + 32 * s));
+                    a ^= w[0] ^ w[7];
+                }
+                v[j] = a;
+            }
+            else if (VAR == V_PF128)
+            {
+                const uint8_t * p = base + (x % units) * 32ull;
+                asm volatile("ld.global.nc.L2::128B.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p));
+                v[j] = w[0] ^ w[7];
+            }
+            else
+            {
+                // units = pages of 2 MB; window bytes used at the start of each
+                const uint64_t r = x % (units * (window / 32ull));
+                const uint8_t * p = base + (r / (window / 32ull)) * (2ull << 20) + (r % (window / 32ull)) * 32ull;
+                asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p));
+                v[j] = w[0] ^ w[7];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < ILP; ++j) acc ^= v[j];
+    }
+    if (acc == 0x12345678u) out[0] = acc;
+}
+
+template <int VAR, int ILP> void run2(const char * name, const uint8_t * d, uint64_t bytes, uint64_t window, uint32_t * out, int ctas_per_sm = 8)
 {
     int sms = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-    const int grid = sms * 8, iters = 512 / ILP * 4;
+    const int grid = sms * ctas_per_sm, iters = 512 / ILP * 4;
+    const uint64_t units = VAR == V_PAGES ? bytes / (2ull << 20) : VAR == V_PF128 ? bytes / 32 : bytes / 128;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    gather2<VAR, ILP><<<grid, 256>>>(d, units, window, iters / 4, out);
+    cudaEventRecord(e0);
+    gather2<VAR, ILP><<<grid, 256>>>(d, units, window, iters, out);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    // sectors requested: LINE4 one per lane and load; SEQ4 four per lane and j; PF128 / PAGES one
+    const double loads = (double)grid * 256 * iters * ILP;
+    const double sectors = VAR == V_SEQ4 ? loads * 4 : loads;
+    const double lines = VAR == V_LINE4 ? loads / 4 : loads;
+    printf("%-44s table %5.2f GB: %7.2f G sectors/s  %7.2f G lines/s  %8.1f GB/s useful  (%.2f ms)\n", name, bytes / 1e9, sectors / ms / 1e6,
+           lines / ms / 1e6, sectors * 32 / ms / 1e6, ms);
+}
+
+template <int BYTES, int ILP> void run(const char * name, const uint8_t * d, uint64_t bytes, uint32_t stride, uint32_t * out, int ctas_per_sm = 8)
+{
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    const int grid = sms * ctas_per_sm, iters = 512 / ILP * 4;
     const uint64_t units = bytes / stride;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -86,6 +174,23 @@ int main()
     for (uint64_t sz = 256ull << 20; sz <= big; sz <<= 1) run<64, 4>("64 B burst, table size sweep", d, sz, 64, out);
     run<32, 8>("32 B sector, L2-resident table", d, small, 32, out);
     run<64, 4>("64 B burst, L2-resident table", d, small, 64, out);
+
+    // ---- round 2 probes
+    run2<V_LINE4, 8>("128 B line by 4 lanes (one instruction)", d, big, 0, out);
+    run2<V_SEQ4, 2>("128 B line by one lane (4 loads), ILP 2", d, big, 0, out);
+    run2<V_SEQ4, 4>("128 B line by one lane (4 loads), ILP 4", d, big, 0, out);
+    run2<V_PF128, 8>("32 B sector, L2::128B prefetch", d, big, 0, out);
+    run2<V_LINE4, 8>("128 B line by 4 lanes, 1 GB table", d, 1ull << 30, 0, out);
+    for (uint64_t win = 16ull << 10; win <= (2ull << 20); win <<= 1)
+        run2<V_PAGES, 8>("random sectors in a window of every 2 MB page", d, big, win, out);
+    run2<V_PAGES, 8>("window 32 KB of every page of a 1 GB table", d, 1ull << 30, 32ull << 10, out);
+    run2<V_PAGES, 8>("window 128 KB of every page of a 256 MB table", d, 256ull << 20, 128ull << 10, out);
+    // is the L2-resident figure a ceiling?  more loads in flight per lane, fewer / more CTAs per SM
+    run<32, 12>("32 B sector, L2-resident, ILP 12", d, small, 32, out);
+    run<32, 16>("32 B sector, L2-resident, ILP 16", d, small, 32, out);
+    run<32, 16>("32 B sector, L2-resident, ILP 16, 4 CTAs/SM", d, small, 32, out, 4);
+    run<32, 8>("32 B sector, L2-resident 32 MB, ILP 8", d, 32ull << 20, 32, out);
+    run<32, 16>("32 B sector, L2-resident 32 MB, ILP 16", d, 32ull << 20, 32, out);
     cudaError_t e = cudaDeviceSynchronize();
     printf("status: %s\n", cudaGetErrorString(e));
     return e == cudaSuccess ? 0 : 1;

@@ -80,6 +80,9 @@ SIGNATURES = {
     "speqg_scan_stats": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Counts)]),
     "speqg_scan_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "speqg_scan_fusion_counts": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "speqg_scan_fusion_sets": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, u64p, u64p]),
+    "speqg_pack_device": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.c_int, C.POINTER(Batch), C.c_void_p]),
+    "speqg_probe_random_sectors": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(C.c_double)]),
     "speqg_scan_device_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p),
                                              C.POINTER(C.c_uint64)]),
     "speqg_scan_close": (None, [C.c_void_p]),

@@ -20,6 +20,7 @@ struct scan_refine_view
     DevIndex view;
     cudaStream_t stream;
     unsigned long long * mult;
+    const unsigned long long * unique_n;   // closed form of the unrecorded windows (product kernels), else null
     double * d_percent, * d_tkpg, * d_partial;
     int32_t * d_gc;
     int refine_grid;
@@ -123,7 +124,7 @@ int speqg_refine(speqg_scan * scan, const double * percent, const int32_t * grou
     CK(cudaMemcpyAsync(r.d_percent, percent, r.V * 8, cudaMemcpyHostToDevice, r.stream));
     CK(cudaMemcpyAsync(r.d_gc, group_counts, r.V * 4, cudaMemcpyHostToDevice, r.stream));
     CK(launch_refine(r.view, r.k, r.mult, r.d_percent, r.d_gc, r.V, r.d_partial, r.refine_grid, 256, r.stream));
-    CK(launch_refine_reduce(r.d_partial, r.refine_grid, r.V, r.d_tkpg, r.stream));
+    CK(launch_refine_reduce(r.d_partial, r.refine_grid, r.V, r.d_tkpg, r.unique_n, r.d_percent, r.stream));
     CK(cudaMemcpyAsync(tkpg, r.d_tkpg, r.V * 8, cudaMemcpyDeviceToHost, r.stream));
     CK(cudaStreamSynchronize(r.stream));
     SPEQG_CATCH

@@ -17,6 +17,10 @@ using namespace speqb;
 namespace
 {
 constexpr int kSlots = 3;
+// slots of the fusion map (variant set of an ambiguous unit -> units): 16 MB of device memory per scan handle
+constexpr uint32_t kFusionCap = 1u << 20;
+// a k-mer table slot keeps a variant below 2^15 next to the "several variants" bit
+constexpr uint32_t kMaxGroupsTable = 32767;
 
 template <class T> struct dev_buf
 {
@@ -87,7 +91,16 @@ struct speqg_scan
     // unique[V] total_g[V] scalars[SC_COUNT] unique_w[V] bad[1] work[1]; h_state is its pinned host mirror.  The integer
     // counters come first so that a multi-GPU driver sums them across ranks in place with one all-reduce
     // (speqg_scan_device_counters)
-    unsigned long long * d_fusion = nullptr;   // [V * V] ambiguous units by (smallest, largest) unique variant; V <= kMaxFusionGroups
+    // ambiguous units by the set of variants that met in them: open-addressing map in device memory (ScanArgs::fkeys)
+    unsigned long long * d_fkeys = nullptr, * d_fvals = nullptr;
+    // windows whose k-mer lies in one variant are not recorded for the refinement: their count per variant (closed form)
+    unsigned long long * d_unique_n = nullptr;
+    // k-mer table with positions: recorded runs as a difference array over the packed-text positions
+    unsigned long long * d_diff = nullptr;
+    void * d_scan_tmp = nullptr;
+    size_t scan_tmp_bytes = 0;
+    uint64_t npos = 0;
+    bool diff_dirty = false;
     unsigned long long * d_state = nullptr, * h_state = nullptr;
     size_t state_words = 0;
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
@@ -110,6 +123,7 @@ struct scan_refine_view
     DevIndex view;
     cudaStream_t stream;
     unsigned long long * mult;
+    const unsigned long long * unique_n;
     double * d_percent, * d_tkpg, * d_partial;
     int32_t * d_gc;
     int refine_grid;
@@ -120,11 +134,18 @@ scan_refine_view refine_view(speqg_scan * s)
     if (s->slot_mult_dirty && s->d_mult)
     {
         device_guard guard(s->device);
-        CK(launch_ktable_fold_mult(s->kt, s->view, s->p.k, s->d_slot_mult, s->d_mult, s->compute));
+        if (s->d_slot_mult) CK(launch_ktable_fold_mult(s->kt, s->view, s->p.k, s->d_slot_mult, s->d_mult, s->compute));
         if (s->d_pair_mult) CK(launch_kpair_fold_mult(s->kp, s->view, s->p.k, s->d_pair_mult, s->d_mult, s->compute));
         s->slot_mult_dirty = false;
     }
-    return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult,
+    // k-mer table with positions: recorded runs -> counts per text position -> mult[lb]
+    if (s->diff_dirty && s->d_mult)
+    {
+        device_guard guard(s->device);
+        CK(launch_kpos_fold(s->di->t_bases, s->view, s->p.k, s->d_diff, s->npos, s->d_scan_tmp, s->scan_tmp_bytes, s->d_mult, s->compute));
+        s->diff_dirty = false;
+    }
+    return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult, s->d_unique_n,
                             s->d_percent, s->d_tkpg, s->d_partial, s->d_gc, s->refine_grid};
 }
 }   // namespace speqb
@@ -133,7 +154,8 @@ namespace
 {
 void scan_release(speqg_scan * s)
 {
-    cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_fusion); cudaFree(s->d_mult);
+    cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_fkeys); cudaFree(s->d_fvals); cudaFree(s->d_mult);
+    cudaFree(s->d_unique_n); cudaFree(s->d_diff); cudaFree(s->d_scan_tmp);
     cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
     cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
@@ -157,7 +179,11 @@ ScanArgs scan_args(speqg_scan * s)
     a.segs = nullptr;
     a.n_segs = 0;
     a.work = s->d_work;
-    a.fusion = s->d_fusion;
+    a.fkeys = s->d_fkeys;
+    a.fvals = s->d_fvals;
+    a.fcap_mask = kFusionCap - 1u;
+    a.unique_n = s->d_unique_n;
+    a.diff = s->d_diff;
 
     return a;
 }
@@ -172,8 +198,7 @@ void check_batch(speqg_scan * s, speqg_batch const * b)
     need(b->n_reads < (uint64_t(1) << 32), "more than 2^32 reads in one batch");
 }
 
-// the (smallest, largest variant) matrix of ambiguous units is kept for indexes of at most this many variants (8 MB)
-constexpr uint32_t kMaxFusionGroups = 1024;
+
 // reads at least this long on average are scanned by a warp each (scanh.cu, WPR) instead of by a lane each
 constexpr uint64_t kWarpPerReadBases = 1024;
 
@@ -194,7 +219,7 @@ void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
         CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, wpr, s->cfg_h, s->compute));
-        if (s->mode & M_RECORD) s->slot_mult_dirty = true;
+        if (s->mode & M_RECORD) (s->kt.pshift ? s->diff_dirty : s->slot_mult_dirty) = true;
     }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
     ++s->launches;
@@ -227,6 +252,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
     need(!(params->algorithm == SPEQG_ALGO_KPAIR && (params->k > kMaxKTable || idx->host.V > kMaxGroupsPair)),
          "the pair-table algorithm needs k <= 31 and at most 254 variants");
     need(!(params->algorithm == SPEQG_ALGO_KTABLE && params->k > kMaxKTable), "the k-mer table algorithm needs k <= 31");
+    need(!(params->algorithm == SPEQG_ALGO_KTABLE && idx->host.V > kMaxGroupsTable), "the k-mer table algorithm needs at most 32767 variants");
     need(idx->host.n <= kMaxN32, "index too large: the indexed text must be shorter than 2^31 symbols");
     need(!(params->algorithm == SPEQG_ALGO_DIRECT && params->mode == SPEQG_MODE_LOCAL), "the direct algorithm covers global mode only");
     DeviceIndex & di = device_index(idx, device);
@@ -239,7 +265,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->device = device;
         s->p = *params;
         s->algo = params->algorithm != SPEQG_ALGO_AUTO ? params->algorithm
-                  : params->k > kMaxKTable             ? SPEQG_ALGO_ROLLING
+                  : params->k > kMaxKTable || idx->host.V > kMaxGroupsTable ? SPEQG_ALGO_ROLLING
                                                        : SPEQG_ALGO_KTABLE;   // upgraded to KPAIR below when the table misses L2
         const bool auto_algo = params->algorithm == SPEQG_ALGO_AUTO;
         s->mode = (params->mode == SPEQG_MODE_LOCAL ? M_LOCAL : 0) | (params->record_multiplicity ? M_RECORD : 0) |
@@ -261,7 +287,13 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->d_unique_w = reinterpret_cast<double *>(s->d_scalars + SC_COUNT);
         s->d_bad = s->d_scalars + SC_COUNT + V;
         s->d_work = s->d_bad + 1;
-        if (V <= kMaxFusionGroups) s->d_fusion = dev_alloc<unsigned long long>((size_t)V * V);
+        if (s->algo != SPEQG_ALGO_DIRECT && s->algo != SPEQG_ALGO_ROLLING64)
+        {
+            s->d_fkeys = dev_alloc<unsigned long long>(kFusionCap);
+            s->d_fvals = dev_alloc<unsigned long long>(kFusionCap + 1);
+            // the product kernels record multiplicities only for k-mers held by several variants; the rest is this count
+            if (params->record_multiplicity) s->d_unique_n = dev_alloc<unsigned long long>(V);
+        }
         s->d_percent = dev_alloc<double>(V);
         s->d_tkpg = dev_alloc<double>(V);
         s->d_gc = dev_alloc<int32_t>(V);
@@ -300,12 +332,6 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 CK(cudaFree(s->kt.slots));
                 s->kt.slots = nullptr;
             }
-            if (params->record_multiplicity)
-            {
-                const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
-                s->d_slot_mult = dev_alloc<unsigned long long>(n_slots);
-                CK(cudaMemsetAsync(s->d_slot_mult, 0, n_slots * 8, s->compute));
-            }
             CK(scanh_launch_cfg(s->mode, V, &s->cfg_h));
             if (auto_algo && idx->host.V <= kMaxGroupsPair)
             {
@@ -314,6 +340,27 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 int l2 = 0;
                 CK(cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device));
                 if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3) s->algo = SPEQG_ALGO_KPAIR;
+            }
+            if (params->record_multiplicity)
+            {
+                // Single-window table scan: hits on k-mers held by several variants are recorded as runs over the positions of
+                // the packed texts (two atomics per run of consecutive hits) when a position fits into the slot next to the
+                // remainder; else, and for the pair-table scan, one atomic per hit on a per-slot counter.
+                s->npos = 32ull * h.t_bases.size();
+                if (s->algo == SPEQG_ALGO_KTABLE && !getenv("SPEQB_NO_RUNS") && ktable_positions_fit(s->kt, s->npos))
+                {
+                    s->kt.pshift = s->kt.rbits + 3u;
+                    CK(launch_ktable_canon(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, h.S, max_len, s->kt, params->k, s->compute));
+                    s->d_diff = dev_alloc<unsigned long long>(s->npos + 2);
+                    s->scan_tmp_bytes = kpos_fold_tmp_bytes(s->npos);
+                    CK(cudaMalloc(&s->d_scan_tmp, s->scan_tmp_bytes));
+                }
+                else
+                {
+                    const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
+                    s->d_slot_mult = dev_alloc<unsigned long long>(n_slots);
+                    CK(cudaMemsetAsync(s->d_slot_mult, 0, n_slots * 8, s->compute));
+                }
             }
             if (s->algo == SPEQG_ALGO_KPAIR)
             {
@@ -395,7 +442,14 @@ int speqg_scan_reset(speqg_scan * s)
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
     CK(cudaMemsetAsync(s->d_state, 0, s->state_words * 8, s->compute));
-    if (s->d_fusion) CK(cudaMemsetAsync(s->d_fusion, 0, (size_t)s->idx->host.V * s->idx->host.V * 8, s->compute));
+    if (s->d_fkeys)
+    {
+        CK(cudaMemsetAsync(s->d_fkeys, 0, (size_t)kFusionCap * 8, s->compute));
+        CK(cudaMemsetAsync(s->d_fvals, 0, ((size_t)kFusionCap + 1) * 8, s->compute));
+    }
+    if (s->d_unique_n) CK(cudaMemsetAsync(s->d_unique_n, 0, (size_t)s->idx->host.V * 8, s->compute));
+    if (s->d_diff) CK(cudaMemsetAsync(s->d_diff, 0, (s->npos + 2) * 8, s->compute));
+    s->diff_dirty = false;
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
     if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
     if (s->d_pair_mult) CK(cudaMemsetAsync(s->d_pair_mult, 0, 4ull * ((uint64_t)s->kp.nbmask + 1) * 8, s->compute));
@@ -550,16 +604,51 @@ int speqg_scan_device_counters(speqg_scan * s, uint64_t ** u64_counters, uint64_
     SPEQG_CATCH
 }
 
+int speqg_scan_fusion_sets(speqg_scan * s, uint64_t * keys, uint64_t * counts, uint64_t capacity, uint64_t * n_sets,
+                           uint64_t * unkeyed_units)
+{
+    SPEQG_TRY
+    need(s != nullptr && n_sets != nullptr, "NULL argument");
+    need(s->d_fkeys != nullptr, "fusion sets are kept by the product kernels only (not SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64)");
+    need(capacity == 0 || (keys != nullptr && counts != nullptr), "keys / counts are NULL");
+    device_guard guard(s->device);
+    std::vector<unsigned long long> hk(kFusionCap), hv((size_t)kFusionCap + 1);
+    CK(cudaMemcpyAsync(hk.data(), s->d_fkeys, (size_t)kFusionCap * 8, cudaMemcpyDeviceToHost, s->compute));
+    CK(cudaMemcpyAsync(hv.data(), s->d_fvals, ((size_t)kFusionCap + 1) * 8, cudaMemcpyDeviceToHost, s->compute));
+    CK(cudaStreamSynchronize(s->compute));
+    uint64_t n = 0;
+    for (uint32_t i = 0; i < kFusionCap; ++i)
+    {
+        if (hk[i] == 0ull) continue;
+        if (n < capacity) { keys[n] = hk[i]; counts[n] = hv[i]; }
+        ++n;
+    }
+    *n_sets = n;
+    if (unkeyed_units) *unkeyed_units = hv[kFusionCap];
+    SPEQG_CATCH
+}
+
 int speqg_scan_fusion_counts(speqg_scan * s, uint64_t * counts)
 {
     SPEQG_TRY
     need(s != nullptr && counts != nullptr, "NULL argument");
-    need(s->d_fusion != nullptr, "the scan keeps no fusion counts (more than 1024 variants)");
-    need(s->algo != SPEQG_ALGO_DIRECT && s->algo != SPEQG_ALGO_ROLLING64, "fusion counts are kept by the product kernels only");
-    device_guard guard(s->device);
-    uint32_t V = s->idx->host.V;
-    CK(cudaMemcpyAsync(counts, s->d_fusion, (size_t)V * V * 8, cudaMemcpyDeviceToHost, s->compute));
-    CK(cudaStreamSynchronize(s->compute));
+    need(s->d_fkeys != nullptr, "fusion counts are kept by the product kernels only (not SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64)");
+    uint64_t n = 0, lost = 0;
+    int rc = speqg_scan_fusion_sets(s, nullptr, nullptr, 0, &n, &lost);
+    if (rc != SPEQG_OK) return rc;
+    need(lost == 0, "the fusion map overflowed: some ambiguous units were counted without their variant set");
+    std::vector<uint64_t> k(n), c(n);
+    rc = speqg_scan_fusion_sets(s, k.data(), c.data(), n, &n, &lost);
+    if (rc != SPEQG_OK) return rc;
+    const uint32_t V = s->idx->host.V;
+    memset(counts, 0, (size_t)V * V * 8);
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        uint32_t a, b;
+        if (V <= kMaxGroupsMask) { a = (uint32_t)__builtin_ctzll(k[i]); b = 63u - (uint32_t)__builtin_clzll(k[i]); }
+        else { a = (uint32_t)(k[i] & 0xFFFFu); b = (uint32_t)((k[i] >> 16) & 0xFFFFu); }
+        counts[(size_t)a * V + b] += c[i];
+    }
     SPEQG_CATCH
 }
 
@@ -653,6 +742,32 @@ int speqg_batch_to_device(int device, const speqg_batch * hb, speqg_batch * db)
     }
     db->n_reads = R;
     db->n_groups32 = G;
+    SPEQG_CATCH
+}
+
+int speqg_pack_device(int device, const uint8_t * d_seq, const uint8_t * d_qual, const uint64_t * d_offsets, uint64_t n_reads,
+                      int encoding, uint32_t phred_cutoff, int n_only, const speqg_batch * db, void * stream)
+{
+    SPEQG_TRY
+    need(db != nullptr && d_offsets != nullptr, "NULL argument");
+    if (n_reads == 0) return SPEQG_OK;
+    need(d_seq != nullptr, "d_seq is NULL");
+    need(db->bases && db->inv && db->grp_off && db->len, "batch arrays must not be NULL");
+    need(encoding == SPEQG_ENC_ASCII || encoding == SPEQG_ENC_RANK, "unknown encoding");
+    device_guard guard(device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned long long * d_bad = dev_alloc<unsigned long long>(1);
+    unsigned long long bad = 0;
+    cudaError_t e = cudaMemsetAsync(d_bad, 0, 8, st);
+    if (e == cudaSuccess)
+        e = launch_pack(d_seq, d_qual, 0, d_offsets, n_reads, encoding, phred_cutoff, n_only, db->bases, db->inv, db->qual, db->grp_off, 0,
+                        db->len, d_bad, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_bad);
+    CK(e);
+    if (bad & 2ull) throw api_error(SPEQG_EINVAL, "read longer than 2^32 bases");
+    if (bad) throw api_error(SPEQG_EINVAL, "parse_error: illegal (non-IUPAC) sequence character in a read");
     SPEQG_CATCH
 }
 

@@ -106,6 +106,13 @@ constexpr uint64_t kMaxN32 = 0x7FFFFFFFull;   // cnt[0] keeps bit 31 for the exc
 
 constexpr uint32_t kCtabEnd = 8;
 
+// Key of an ambiguous unit in the fusion map when the index has more variants than a 64-bit mask holds: smallest and largest
+// variant with a unique k-mer in the unit, and whether further variants lie between them.
+SPEQB_HD uint64_t fusion_key_minmax(uint32_t gmin, uint32_t gmax, bool more)
+{
+    return (1ull << 63) | (more ? 1ull << 32 : 0ull) | ((uint64_t)gmax << 16) | (uint64_t)gmin;
+}
+
 // Device view of the index (passed to kernels by value).
 struct DevIndex
 {

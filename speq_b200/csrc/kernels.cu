@@ -402,12 +402,15 @@ __global__ void __launch_bounds__(kBlock) fill_e_kernel(const KBlock * __restric
     }
 }
 
-__global__ void refine_reduce_kernel(const double * __restrict__ partial, int nparts, uint32_t V, double * __restrict__ tkpg)
+__global__ void refine_reduce_kernel(const double * __restrict__ partial, int nparts, uint32_t V, double * __restrict__ tkpg,
+                                     const unsigned long long * __restrict__ unique_n, const double * __restrict__ percent)
 {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= V) return;
     double acc = 0.0;
     for (int p = 0; p < nparts; ++p) acc += partial[(size_t)p * V + g];
+    // windows whose k-mer lies in variant g only were not recorded: each adds a[g] / a[g] = 1 while a[g] > 0, i.e. percent[g] > 0
+    if (unique_n != nullptr && percent[g] > 0.0) acc += (double)unique_n[g];
     tkpg[g] = acc;
 }
 
@@ -584,9 +587,10 @@ cudaError_t launch_refine(DevIndex const & ix, uint32_t k, const unsigned long l
     return cudaGetLastError();
 }
 
-cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V, double * tkpg, cudaStream_t st)
+cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V, double * tkpg, const unsigned long long * unique_n,
+                                 const double * percent, cudaStream_t st)
 {
-    refine_reduce_kernel<<<(V + 127) / 128, 128, 0, st>>>(partial, nparts, V, tkpg);
+    refine_reduce_kernel<<<(V + 127) / 128, 128, 0, st>>>(partial, nparts, V, tkpg, unique_n, percent);
     return cudaGetLastError();
 }
 

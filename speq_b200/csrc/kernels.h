@@ -36,13 +36,27 @@ struct ScanArgs
     unsigned long long * total_g;     // [V] back-check: total_ref
     double * unique_w;                // [V] local mode
     unsigned long long * scalars;     // [SC_COUNT]
-    unsigned long long * mult;        // [n] multiplicity of the valid k-mer windows whose interval starts at lb
+    unsigned long long * mult;        // [n] multiplicity of the valid k-mer windows whose interval starts at lb (k-mers held by
+                                      //     several variants only: see unique_n)
+    unsigned long long * unique_n;    // [V] or null: valid windows whose k-mer lies in variant g only.  Such a window adds
+                                      //     a[g] / a[g] = 1 to the refinement estimate (src/fm_scanner.cpp:1099-1119), so the
+                                      //     product kernels record no multiplicity for it and the estimate adds this count
+    unsigned long long * diff;        // k-mer table with positions: difference array over the packed-text positions; a run of
+                                      //     hits at consecutive positions [s, e] is recorded as diff[s] += 1, diff[e + 1] -= 1
     const double * qden;              // [42] 1 - 1/pow(10, q/10), host libm values   (local mode)
     const SegmentX * segs;             // optional segment table (back-check); null: one segment per read / pair
     uint64_t n_segs;
     unsigned long long * work;        // scan32: next unclaimed unit minus the number of threads (zero at launch)
-    unsigned long long * fusion;      // [V * V] or null: ambiguous units by (smallest, largest) unique variant
+    // ambiguous units by the SET of variants that met in them (the key the reference's fusion_totals map was meant to hold,
+    // src/fm_scanner.cpp:915,983-995): an open-addressing map in device memory, fkeys[i] = 0 when free.  Key of a unit:
+    // V <= kMaxGroupsMask: bit g set for every variant g with a unique k-mer in the unit; else fusion_key_minmax().
+    // fvals[fcap] counts the units that found no place within kFusionMaxProbe slots.
+    unsigned long long * fkeys;       // [fcap] or null
+    unsigned long long * fvals;       // [fcap + 1]
+    uint32_t fcap_mask;               // fcap - 1 (fcap is a power of two)
 };
+constexpr uint32_t kMaxGroupsMask = 64;        // variant sets of indexes with at most this many variants are kept as bit masks
+constexpr uint32_t kFusionMaxProbe = 128;
 
 struct LaunchCfg
 {
@@ -61,7 +75,9 @@ size_t scan_smem_bytes(uint32_t V);
 // refinement estimate: tkpg[g] = sum over recorded k-mers of mult * a[g] / sum(a), a[g] = h[g] * percent[g] / group_counts[g]
 cudaError_t launch_refine(DevIndex const & ix, uint32_t k, const unsigned long long * mult, const double * percent,
                           const int32_t * group_counts, uint32_t V, double * partial, int grid, int block, cudaStream_t st);
-cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V, double * tkpg, cudaStream_t st);
+// unique_n != null: tkpg[g] += unique_n[g] where percent[g] > 0 (the closed form of the windows that were not recorded)
+cudaError_t launch_refine_reduce(const double * partial, int nparts, uint32_t V, double * tkpg, const unsigned long long * unique_n,
+                                 const double * percent, cudaStream_t st);
 // device packer: raw reads (ASCII or dna5 ranks) already in device memory -> packed batch.  make_grp_off != 0: the kernel
 // lays read r out at 32-base group floor((offsets[r] - off0) / 32) + r and writes grp_off[r] itself (the batch then needs
 // (offsets[n_reads] - off0) / 32 + n_reads + 1 groups); else grp_off is an input.
@@ -91,7 +107,15 @@ struct KTabView
     uint64_t mul, mul_inv;        // invertible multiplicative hash mod 4^k and its inverse
     uint32_t * filt;              // optional presence filter (pair-table scan): bit (hash >> fshift) is set for every stored k-mer
     uint32_t fshift;
+    uint32_t pshift;              // != 0: slots of k-mers held by several variants carry, from this bit up to bit 62, the
+                                  // smallest position (32 * group + offset in the packed texts) where the k-mer starts
 };
+bool ktable_positions_fit(KTabView const & kt, uint64_t npos);
+cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
+                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k, cudaStream_t st);
+size_t kpos_fold_tmp_bytes(uint64_t npos);
+cudaError_t launch_kpos_fold(const uint64_t * t_bases, DevIndex const & ix, uint32_t k, unsigned long long * diff, uint64_t npos,
+                             void * tmp, size_t tmp_bytes, unsigned long long * mult, cudaStream_t st);
 // presence filter of the k-mer table for the pair-table scan: 2^fbits bits, L2-resident next to the HBM-resident tables
 uint32_t kfilter_bits(uint32_t k, uint64_t keys);
 cudaError_t launch_kfilter_build(KTabView const & kt, uint32_t fbits, cudaStream_t st);

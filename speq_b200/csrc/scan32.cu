@@ -42,7 +42,7 @@ template <int MODE, bool G8> struct Env32 : Tally32<MODE>
     __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(this->a.mult + lb, 1ull); }
 };
 
-template <int MODE, bool G8>
+template <int MODE, bool G8, bool MASK>
 __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __restrict__ fblk, const DevIndex ix, const BatchView b,
                                                              const ScanArgs a, const int paired)
 {
@@ -59,6 +59,8 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
     cfg.paired = paired;
     cfg.local = LOCAL;
     cfg.record = RECORD;
+    cfg.mask64 = MASK;
+    cfg.skip_unique = 1;
     Env32<MODE, G8> env(fblk, ix, b, a, sm);
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
@@ -206,18 +208,23 @@ int sm_count32()
 
 size_t scan32_smem_bytes(uint32_t V) { return 32 + (size_t)V * 12; }
 
-#define SPEQB_SCAN32_CASE(M, G, EXPR) { auto kern = scan32_kernel<M, G>; EXPR; break; }
-#define SPEQB_SCAN32_DISPATCH(M, G8, EXPR)                                                        \
-    switch ((M) | ((G8) ? 16 : 0))                                                                \
+// G8: variants as bytes inside the blocks (V <= 255); MASK (implies G8): the unit's variants as a 64-bit mask (V <= 64)
+#define SPEQB_SCAN32_CASE(M, G, MK, EXPR) { auto kern = scan32_kernel<M, G, MK>; EXPR; break; }
+#define SPEQB_SCAN32_DISPATCH(M, V_, EXPR)                                                        \
+    switch ((M) | ((V_) <= kMaxGroups8 ? 16 : 0) | ((V_) <= kMaxGroupsMask ? 32 : 0))             \
     {                                                                                             \
-        case 0: SPEQB_SCAN32_CASE(0, false, EXPR)                                                 \
-        case M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, false, EXPR)                                   \
-        case M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, false, EXPR)                                     \
-        case M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, false, EXPR)               \
-        case 16: SPEQB_SCAN32_CASE(0, true, EXPR)                                                 \
-        case 16 | M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, true, EXPR)                               \
-        case 16 | M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, true, EXPR)                                 \
-        case 16 | M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, true, EXPR)           \
+        case 0: SPEQB_SCAN32_CASE(0, false, false, EXPR)                                          \
+        case M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, false, false, EXPR)                            \
+        case M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, false, false, EXPR)                              \
+        case M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, false, false, EXPR)        \
+        case 16: SPEQB_SCAN32_CASE(0, true, false, EXPR)                                          \
+        case 16 | M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, true, false, EXPR)                        \
+        case 16 | M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, true, false, EXPR)                          \
+        case 16 | M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, true, false, EXPR)    \
+        case 48: SPEQB_SCAN32_CASE(0, true, true, EXPR)                                           \
+        case 48 | M_RECORD: SPEQB_SCAN32_CASE(M_RECORD, true, true, EXPR)                         \
+        case 48 | M_LOCAL: SPEQB_SCAN32_CASE(M_LOCAL, true, true, EXPR)                           \
+        case 48 | M_LOCAL | M_RECORD: SPEQB_SCAN32_CASE(M_LOCAL | M_RECORD, true, true, EXPR)     \
         default: return cudaErrorInvalidValue;                                                    \
     }
 
@@ -227,8 +234,7 @@ cudaError_t scan32_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     int bps = 0;
     cudaError_t e = cudaSuccess;
     const int m = mode & (M_LOCAL | M_RECORD);
-    const bool g8 = V <= kMaxGroups8;
-    SPEQB_SCAN32_DISPATCH(m, g8, {
+    SPEQB_SCAN32_DISPATCH(m, V, {
         if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kBlock32, smem);
     })
@@ -247,8 +253,7 @@ cudaError_t launch_scan32(const FBlock * fblk, DevIndex const & ix, BatchView co
     const int m = mode & (M_LOCAL | M_RECORD);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
-    const bool g8 = a.V <= kMaxGroups8;
-    SPEQB_SCAN32_DISPATCH(m, g8, (kern<<<cfg.grid, cfg.block, smem, st>>>(fblk, ix, b, a, paired)))
+    SPEQB_SCAN32_DISPATCH(m, a.V, (kern<<<cfg.grid, cfg.block, smem, st>>>(fblk, ix, b, a, paired)))
     return cudaGetLastError();
 }
 

@@ -35,7 +35,9 @@ struct Lane32
     uint64_t g0;                  // first 32-base group of the read
     uint64_t u, unext;            // unit being scanned / claimed for afterwards
     uint32_t gval, gt;            // group of the last unique hit and the window end it belongs to
-    uint32_t gmin, gmax;          // unit-level ambiguity state
+    uint32_t gmin, gmax;          // unit-level ambiguity state: smallest / largest variant with a unique k-mer in the unit,
+    uint32_t gmore;               //   whether further variants lie between them (Cfg32::mask64 == 0),
+    uint64_t gset;                //   or one bit per variant (Cfg32::mask64 != 0: at most 64 variants)
     uint32_t agg_g, agg_n;        // run-length aggregation of the lane's unique tallies
     double agg_w;
     uint32_t c_total;             // valid windows of the current unit
@@ -55,12 +57,15 @@ struct Cfg32
     uint32_t k, n;
     uint64_t units;
     int paired, local, record;
+    int mask64;                   // the unit's variants are kept as a bit mask (V <= 64), else as (smallest, largest, more)
+    int skip_unique;              // record only windows whose k-mer is held by several variants: the others add exactly 1 to
+                                  // their variant's refinement estimate (src/fm_scanner.cpp:1099-1119), i.e. the unique tally
 };
 
 SPEQB_HD void lane32_init(Lane32 & s, uint64_t first_unit, uint32_t n)
 {
     s.phase = P_FETCH; s.flags = 0; s.lb = 0; s.rb1 = n; s.d = 0; s.run = 0; s.t = 0; s.pend = 0; s.wlo = s.whi = s.winv = 0;
-    s.g0 = 0; s.u = first_unit; s.unext = first_unit; s.gval = 0; s.gt = 0; s.gmin = kNoGroup; s.gmax = 0;
+    s.g0 = 0; s.u = first_unit; s.unext = first_unit; s.gval = 0; s.gt = 0; s.gmin = kNoGroup; s.gmax = 0; s.gmore = 0; s.gset = 0;
     s.agg_g = kNoGroup; s.agg_n = 0; s.agg_w = 0.0; s.c_total = 0;
 }
 
@@ -72,7 +77,7 @@ SPEQB_HD void lane32_init(Lane32 & s, uint64_t first_unit, uint32_t n)
 //   void     env.record(lb)                one more valid window whose k-mer interval starts at lb
 //   void     env.count_fetch(nwin)         a read with nwin windows was presented
 //   void     env.count_unit(total, amb)    a unit ended with `total` valid windows; amb: it was ambiguous
-//   void     env.fusion(gmin, gmax)        an ambiguous unit ended: its smallest and largest unique variant
+//   void     env.fusion(key)               an ambiguous unit ended: key of the set of its unique variants (kernels.h)
 template <class Env>
 SPEQB_HD void lane32_flush_agg(Lane32 & s, Env & env)
 {
@@ -88,15 +93,21 @@ SPEQB_HD void lane32_take_group(Lane32 & s, Cfg32 const & cfg, Env & env)
     // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191)
     const uint32_t g = s.gval;
     s.flags &= ~F_HAVE_G;
-    s.gmin = g < s.gmin ? g : s.gmin;
-    s.gmax = g > s.gmax ? g : s.gmax;
+    if (cfg.mask64) s.gset |= 1ull << g;
+    else
+    {
+        if (s.gmin == kNoGroup) { s.gmin = g; s.gmax = g; }
+        else if (g < s.gmin) { s.gmore |= s.gmin != s.gmax ? 1u : 0u; s.gmin = g; }
+        else if (g > s.gmax) { s.gmore |= s.gmin != s.gmax ? 1u : 0u; s.gmax = g; }
+        else s.gmore |= (g != s.gmin && g != s.gmax) ? 1u : 0u;
+    }
     if (g != s.agg_g)
     {
         lane32_flush_agg(s, env);
         s.agg_g = g;
     }
     if (cfg.local) s.agg_w += env.weight(s.g0, s.gt, cfg.k);
-    else s.agg_n += 1u;
+    s.agg_n += 1u;
 }
 
 #if defined(__CUDA_ARCH__)
@@ -139,6 +150,7 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
             s.gt = s.t;
             s.flags |= F_HAVE_G;
         }
+        else if (cfg.record && cfg.skip_unique) env.record(s.lb);
     }
     if (s.t >= s.pend)
     {
@@ -148,11 +160,11 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
         else
         {
             // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
-            const bool amb = s.gmin != kNoGroup && s.gmin != s.gmax;
+            const bool amb = cfg.mask64 ? (s.gset & (s.gset - 1ull)) != 0ull : (s.gmin != kNoGroup && s.gmin != s.gmax);
             env.count_unit(s.c_total, amb);
-            if (amb) env.fusion(s.gmin, s.gmax);
+            if (amb) env.fusion(cfg.mask64 ? s.gset : fusion_key_minmax(s.gmin, s.gmax, s.gmore != 0u));
             s.c_total = 0u;
-            s.gmin = kNoGroup; s.gmax = 0u;
+            s.gmin = kNoGroup; s.gmax = 0u; s.gmore = 0u; s.gset = 0ull;
             s.flags &= ~F_MATE2;
             s.u = s.unext;
         }
@@ -220,7 +232,7 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
         if (s.d == k)
         {
             s.flags |= F_PENDING;
-            if (cfg.record) env.record(s.lb);
+            if (cfg.record && !cfg.skip_unique) env.record(s.lb);
         }
     }
 }

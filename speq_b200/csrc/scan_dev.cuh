@@ -66,10 +66,11 @@ template <int MODE> struct Tally32
         for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
         return w;
     }
+    // n windows whose k-mer lies in variant g only; w: the sum of their phred weights (local mode)
     __device__ __forceinline__ void unique(uint32_t g, uint32_t n, double w) const
     {
         if (LOCAL) atomicAdd(&sm.w[g], w);
-        else atomicAdd(&sm.cnt[g], n);
+        atomicAdd(&sm.cnt[g], n);
     }
     // 64-bit shared counters as two native 32-bit atomics (a 64-bit shared atomicAdd is a CAS loop)
     __device__ __forceinline__ void add64(int i, uint32_t v) const
@@ -89,10 +90,65 @@ template <int MODE> struct Tally32
         if (amb) add64(1, 1u);
     }
     // an ambiguous unit (is_ambiguous, src/fm_scanner.cpp:183-190): which variants met -- the key of the reference's
-    // fusion_totals map (src/fm_scanner.cpp:983-995), reduced to the smallest and largest variant of the unit
-    __device__ __forceinline__ void fusion(uint32_t gmin, uint32_t gmax) const
+    // fusion_totals map (src/fm_scanner.cpp:983-995); one insert-or-increment in the device map per ambiguous unit
+    __device__ __forceinline__ void fusion(unsigned long long key) const
     {
-        if (a.fusion) atomicAdd(a.fusion + (uint64_t)gmin * a.V + gmax, 1ull);
+        if (a.fkeys == nullptr) return;
+        uint64_t x = key * 0x9E3779B97F4A7C15ull;
+        uint32_t h = (uint32_t)(x >> 32) & a.fcap_mask;
+        for (uint32_t probe = 0; probe < kFusionMaxProbe; ++probe)
+        {
+            unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(a.fkeys + h);
+            if (old == 0ull) old = atomicCAS(a.fkeys + h, 0ull, key);
+            if (old == 0ull || old == key)
+            {
+                atomicAdd(a.fvals + h, 1ull);
+                return;
+            }
+            h = (h + 1u) & a.fcap_mask;
+        }
+        atomicAdd(a.fvals + a.fcap_mask + 1u, 1ull);      // the map is full around this key: counted, not keyed
+    }
+};
+
+// The variants with a unique k-mer in the current unit (read / pair): the ambiguity state of do_a_count
+// (src/fm_scanner.cpp:183-190) and the key of the fusion map.  MASK: one bit per variant (V <= 64); else smallest / largest
+// variant and a "more in between" flag.
+template <bool MASK> struct UnitSet;
+template <> struct UnitSet<true>
+{
+    uint64_t m = 0ull;
+    __device__ __forceinline__ void add(uint32_t g) { m |= 1ull << g; }
+    __device__ __forceinline__ bool ambiguous() const { return (m & (m - 1ull)) != 0ull; }
+    __device__ __forceinline__ unsigned long long key() const { return m; }
+    __device__ __forceinline__ void reset() { m = 0ull; }
+    __device__ __forceinline__ void warp_merge()
+    {
+        const uint32_t lo = __reduce_or_sync(0xFFFFFFFFu, (uint32_t)m), hi = __reduce_or_sync(0xFFFFFFFFu, (uint32_t)(m >> 32));
+        m = ((uint64_t)hi << 32) | lo;
+    }
+};
+template <> struct UnitSet<false>
+{
+    uint32_t gmin = kNoGroup, gmax = 0u;
+    bool more = false;
+    __device__ __forceinline__ void add(uint32_t g)
+    {
+        if (gmin == kNoGroup) { gmin = g; gmax = g; }
+        else if (g < gmin) { more = more || gmin != gmax; gmin = g; }
+        else if (g > gmax) { more = more || gmin != gmax; gmax = g; }
+        else more = more || (g != gmin && g != gmax);
+    }
+    __device__ __forceinline__ bool ambiguous() const { return gmin != kNoGroup && gmin != gmax; }
+    __device__ __forceinline__ unsigned long long key() const { return fusion_key_minmax(gmin, gmax, more); }
+    __device__ __forceinline__ void reset() { gmin = kNoGroup; gmax = 0u; more = false; }
+    __device__ __forceinline__ void warp_merge()
+    {
+        const uint32_t lo = __reduce_min_sync(0xFFFFFFFFu, gmin), hi = __reduce_max_sync(0xFFFFFFFFu, gmax);
+        // a variant other than the warp's smallest / largest: inside one lane's range (its flag) or one of a lane's ends
+        const bool in = more || (gmin != kNoGroup && ((gmin != lo && gmin != hi) || (gmax != lo && gmax != hi)));
+        more = __any_sync(0xFFFFFFFFu, in);
+        gmin = lo; gmax = hi;
     }
 };
 
@@ -122,6 +178,7 @@ __device__ __forceinline__ void smem32_flush(Smem32 const & sm, ScanArgs const &
     {
         if (LOCAL) { if (sm.w[g] != 0.0) atomicAdd(a.unique_w + g, sm.w[g]); }
         else if (sm.cnt[g]) atomicAdd(a.unique + g, (unsigned long long)sm.cnt[g]);
+        if (a.unique_n && sm.cnt[g]) atomicAdd(a.unique_n + g, (unsigned long long)sm.cnt[g]);
     }
 }
 }   // namespace

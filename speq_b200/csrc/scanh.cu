@@ -24,6 +24,8 @@
 // counters of scan_dev.cuh, per-read scalars through per-lane registers.
 #include <algorithm>
 
+#include <cub/device/device_scan.cuh>
+
 #include "kernels.h"
 #include "scan_dev.cuh"
 
@@ -45,8 +47,14 @@ __device__ __forceinline__ uint32_t claim_chunk(uint32_t units)
 }
 #endif
 constexpr uint64_t kSlotFree = ~0ull;
-constexpr uint32_t kValMulti = 0xFFFFu;            // a group is < 65535
+constexpr uint32_t kValMulti = 0xFFFFu;            // value of a k-mer held by texts of several variants; a variant is < 0x8000
 constexpr uint32_t kMaxDisp = 6;
+constexpr uint32_t kNoRun = 0xFFFFFFFFu;
+// bit 63 of a slot = "several variants".  In a table with positions (KTabView::pshift != 0, record_multiplicity) such a slot
+// holds, above the displacement, the smallest position in the packed texts where its k-mer starts (ktable_canon_kernel):
+// consecutive windows of a read that hit a conserved stretch then have consecutive positions, and the scan records a RUN of
+// hits with two atomics on a difference array (ScanArgs::diff) instead of one atomic per window.
+__device__ __forceinline__ bool slot_multi(uint32_t hi) { return (hi >> 31) != 0u; }
 
 // ---------------------------------------------------------------------------------------------------------------
 // build: one thread per 32-base group of a text; the 32 windows that start in the group
@@ -146,6 +154,88 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(const KTabVie
     }
 }
 
+// where `key` is stored: slot index, or ~0 when it is not in the table
+__device__ __forceinline__ uint64_t ktable_slot_of(KTabView const & kt, uint64_t key)
+{
+    const uint64_t h = (key * kt.mul) & kt.mask_b;
+    uint32_t bk = (uint32_t)(h >> kt.rbits);
+    uint64_t want = h & kt.rmask;
+    const uint64_t kmask = (kt.rmask << 3) | 7ull;
+    for (uint32_t d = 0; d <= kMaxDisp; ++d)
+    {
+        bool last_free = false;
+        for (int j = 0; j < 4; ++j)
+        {
+            const uint64_t w = *reinterpret_cast<const volatile uint64_t *>(kt.slots + 4ull * bk + j);
+            if (((w ^ want) & kmask) == 0ull) return 4ull * bk + j;
+            if (j == 3) last_free = w == kSlotFree;
+        }
+        if (last_free) break;
+        bk = (bk + 1u) & kt.nbmask;
+        want += 1ull << kt.rbits;
+    }
+    return ~0ull;
+}
+
+// Second pass of the build for a table with positions: every N-free window of the texts whose k-mer is held by several
+// variants lowers the slot's position field to its own start in the packed texts (32 * group + offset).  The first pass left
+// the field of such slots at a value above every position (variant field 0x7FFF, rest 0), so atomicMin on the whole word works.
+__global__ void __launch_bounds__(kBlockH) ktable_canon_kernel(const uint64_t * __restrict__ bases, const uint32_t * __restrict__ inv,
+                                                               const uint64_t * __restrict__ grp_off, const uint32_t * __restrict__ len,
+                                                               const KTabView kt, const uint32_t k)
+{
+    const uint32_t text = blockIdx.y;
+    const uint32_t L = len[text];
+    if (L < k) return;
+    const uint32_t nwin = L - k + 1u;
+    const uint64_t g0 = grp_off[text];
+    const uint64_t low_mask = (1ull << kt.pshift) - 1ull;
+    for (uint32_t gi = blockIdx.x * blockDim.x + threadIdx.x; (uint64_t)gi * 32u < nwin + k - 1u; gi += gridDim.x * blockDim.x)
+    {
+        // windows that END in bases [32 gi, 32 gi + 32): the k-1 bases before the group are rolled in first
+        const uint32_t first = gi * 32u >= k - 1u ? gi * 32u - (k - 1u) : 0u;
+        uint64_t key = 0ull;
+        uint32_t run = 0u;
+        for (uint32_t pos = first; pos < L && pos < gi * 32u + 32u; ++pos)
+        {
+            const uint64_t bw = bases[g0 + (pos >> 5)];
+            const uint32_t iw = inv[g0 + (pos >> 5)];
+            key = (key << 2) | ((bw >> (2u * (pos & 31u))) & 3ull);
+            run = ((iw >> (pos & 31u)) & 1u) ? 0u : run + 1u;
+            if (pos < gi * 32u || run < k) continue;
+            const uint64_t si = ktable_slot_of(kt, key & kt.mask_b);
+            if (si == ~0ull) continue;
+            const uint64_t w = kt.slots[si];
+            if (!(w >> 63)) continue;
+            const uint64_t start = 32ull * g0 + (pos + 1u - k);
+            atomicMin(reinterpret_cast<unsigned long long *>(kt.slots + si), (1ull << 63) | (start << kt.pshift) | (w & low_mask));
+        }
+    }
+}
+
+// Recorded runs -> multiplicities.  cnt[p] (the inclusive prefix sum of the difference array) = valid windows whose k-mer has
+// its smallest text position at p.  The k-mer is read back from the packed texts, k rank steps from the root give the start of
+// its SA interval, and the count moves to mult[lb] -- what the rolling scan records.  Only positions that were hit pay.
+__global__ void __launch_bounds__(kBlockH) kpos_fold_kernel(const uint64_t * __restrict__ t_bases, const DevIndex ix, const uint32_t k,
+                                                            unsigned long long * __restrict__ cnt, const uint64_t npos,
+                                                            unsigned long long * __restrict__ mult)
+{
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < npos; p += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const unsigned long long m = cnt[p];
+        cnt[p] = 0ull;
+        if (m == 0ull) continue;
+        uint32_t lb = 0u, rb = ix.n - 1u;
+        bool ok = true;
+        for (uint32_t j = 0; j < k && ok; ++j)
+        {
+            const uint64_t q = p + j;
+            ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(t_bases[q >> 5] >> (2u * (q & 31u))) & 3u);
+        }
+        if (ok) atomicAdd(mult + lb, m);
+    }
+}
+
 // presence filter of a built table: the hash of every stored k-mer is rebuilt from its slot (home bucket + remainder)
 __global__ void __launch_bounds__(kBlockH) kfilter_build_kernel(const KTabView kt)
 {
@@ -178,7 +268,7 @@ constexpr int kWin = SPEQB_KWIN;
 
 // WPR (long reads): the 32 lanes of a warp share one read -- lane l takes windows [l * per, (l + 1) * per), per = ceil(nwin / 32),
 // pre-rolling the k-1 bases before its first window; the ambiguity state of the read is the warp's min / max variant.
-template <int MODE, bool WPR>
+template <int MODE, bool WPR, bool MASK>
 __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
                                                                                   const BatchView b, const ScanArgs a, const int paired)
 {
@@ -209,9 +299,18 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                                                  // the bits above are stale bases -- the hash is taken mod 4^k, which ignores them
     uint64_t cb = 0ull, nb = 0ull;               // the 32-base group that holds base t, and the following one (prefetched)
     uint32_t ci = 0u, ni = 0u;                   // their invalid-base bits
-    uint32_t gmin = kNoGroup, gmax = 0u, c_total = 0u;
+    UnitSet<MASK> uset;                          // variants with a unique k-mer in the current unit
+    uint32_t c_total = 0u;
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
+    uint32_t rs = kNoRun, rl = 0xFFFFFFFDu;      // RECORD with positions: the open run [rs, rl] of consecutive text positions
+    auto run_flush = [&]() {
+        if (rs != kNoRun)
+        {
+            atomicAdd(a.diff + rs, 1ull);
+            atomicAdd(a.diff + rl + 1u, ~0ull);                   // -1
+        }
+    };
     // per-lane scalars (flushed at the end, or before they could wrap)
     uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
     // warp-uniform chunk of claimed units
@@ -373,22 +472,34 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                     const bool h3 = (((w[j][6] ^ want_lo[j]) & kmask_lo) | ((w[j][7] ^ want_hi[j]) & kmask_hi)) == 0u;
                     if (h0 || h1 || h2 || h3)
                     {
-                        const uint32_t g = (h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7]) >> 16;
-                        if (RECORD) atomicAdd(slot_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
-                        if (g != kValMulti)
+                        const uint32_t hi = h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7];
+                        if (!slot_multi(hi))
                         {
                             // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191).  The
                             // run-length tally is closed at the end of every unit, so the variant of an open run is already
-                            // inside [gmin, gmax] of this unit.
+                            // in the unit's set.  Nothing is recorded for the refinement: a k-mer of one variant contributes
+                            // a[g] / a[g] = 1 per window (src/fm_scanner.cpp:1099-1119), i.e. the variant's unique count.
+                            const uint32_t g = hi >> 16;
                             if (g != agg_g)
                             {
                                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                                 agg_g = g; agg_n = 0u; agg_w = 0.0;
-                                gmin = g < gmin ? g : gmin;
-                                gmax = g > gmax ? g : gmax;
+                                uset.add(g);
                             }
                             if (LOCAL) agg_w += env.weight(g0, t0 + (uint32_t)j + 1u, k);
-                            else agg_n += 1u;
+                            agg_n += 1u;
+                        }
+                        else if (RECORD)
+                        {
+                            if (kt.pshift != 0u)
+                            {
+                                // the k-mer's smallest text position: extends the open run or starts a new one
+                                const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
+                                const uint32_t p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
+                                if (p == rl + 1u) rl = p;
+                                else { run_flush(); rs = p; rl = p; }
+                            }
+                            else atomicAdd(slot_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
                         }
                         break;
                     }
@@ -415,11 +526,10 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 if (paired && !mate2) mate2 = true;
                 else
                 {
-                    gmin = __reduce_min_sync(kFullH, gmin);
-                    gmax = __reduce_max_sync(kFullH, gmax);
+                    uset.warp_merge();
                     n_total += c_total;
-                    if (lane == 0u && gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
-                    c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                    if (lane == 0u && uset.ambiguous()) { n_amb += 1u; env.fusion(uset.key()); }
+                    c_total = 0u; uset.reset();
                     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                     agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
                     mate2 = false;
@@ -440,8 +550,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
             {
                 // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
                 n_total += c_total;
-                if (gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
-                c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                if (uset.ambiguous()) { n_amb += 1u; env.fusion(uset.key()); }
+                c_total = 0u; uset.reset();
                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                 agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
                 mate2 = false;
@@ -455,6 +565,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
         }
     }
     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
+    if (RECORD) run_flush();
     if (n_total) env.add64(0, n_total);
     if (n_amb) env.add64(1, n_amb);
     if (n_look) env.add64(2, n_look);
@@ -605,8 +716,10 @@ __global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(const KTabView
         const uint32_t home = ((uint32_t)(i >> 2) - d) & kp.nbmask;
         const uint64_t h = ((uint64_t)home << kp.rbits) | (w & kp.rmask);
         const uint64_t key = (h * kp.mul_inv) & kp.mask_b;          // k+1 bases, the first in the highest digit
+        const uint32_t vv = (uint32_t)(w >> 48);                    // value bytes of the two k-mers: variant, or 0xFF
         for (uint32_t which = 0; which < 2u; ++which)
         {
+            if (((vv >> (8u * which)) & 0xFFu) != 0xFFu) continue;  // held by one variant: not recorded (closed form)
             uint32_t lb = 0u, rb = ix.n - 1u;
             bool ok = true;
             for (uint32_t j = 0; j < k && ok; ++j) ok = fm_step(ix, ix.ctab, lb, rb, (uint32_t)(key >> (2u * (k - (j + which)))) & 3u);
@@ -624,7 +737,7 @@ __global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(const KTabView
 constexpr int kPair = SPEQB_PWIN;     // pairs of windows per lane and loop trip
 
 // WPR: a warp per read, as in scanh_kernel (long reads)
-template <int MODE, bool WPR>
+template <int MODE, bool WPR, bool MASK>
 __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) scanp_kernel(const KTabView kt, const KTabView kp, unsigned long long * __restrict__ slot_mult,
                                                                                   unsigned long long * __restrict__ pair_mult, const BatchView b, const ScanArgs a,
                                                                                   const int paired)
@@ -656,7 +769,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     uint64_t key = 0ull;                         // key << 2 | base per base (see scanh_kernel)
     uint64_t cb = 0ull, nb = 0ull;
     uint32_t ci = 0u, ni = 0u;
-    uint32_t gmin = kNoGroup, gmax = 0u, c_total = 0u;
+    UnitSet<MASK> uset;
+    uint32_t c_total = 0u;
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
     uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
@@ -684,11 +798,10 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
         {
             if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
             agg_g = g; agg_n = 0u; agg_w = 0.0;
-            gmin = g < gmin ? g : gmin;
-            gmax = g > gmax ? g : gmax;
+            uset.add(g);
         }
         if (LOCAL) agg_w += env.weight(g0, t_end, k);
-        else agg_n += 1u;
+        agg_n += 1u;
     };
     while (true)
     {
@@ -862,8 +975,9 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     if (h0 || h1 || h2 || h3)
                     {
                         const uint32_t vv = (h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7]) >> 16;
-                        if (RECORD) atomicAdd(pair_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
                         const uint32_t v1 = vv & 0xFFu, v2 = vv >> 8;
+                        // a k-mer of one variant needs no record (see scanh_kernel); the fold skips that half of the pair
+                        if (RECORD && (v1 == 0xFFu || v2 == 0xFFu)) atomicAdd(pair_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
                         if (v1 != 0xFFu) tally(v1, t0 + 2u * (uint32_t)j + 1u);
                         if (v2 != 0xFFu) tally(v2, t0 + 2u * (uint32_t)j + 2u);
                         mode[j] = 0u;                             // answered
@@ -907,9 +1021,9 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         const bool h3 = (((sw[i][6] ^ sl[i]) & tmask_lo) | ((sw[i][7] ^ sh_[i]) & tmask_hi)) == 0u;
                         if (h0 || h1 || h2 || h3)
                         {
-                            const uint32_t g = (h0 ? sw[i][1] : h1 ? sw[i][3] : h2 ? sw[i][5] : sw[i][7]) >> 16;
-                            if (RECORD) atomicAdd(slot_mult + 4ull * sb[i] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
-                            if (g != kValMulti) tally(g, t0 + (uint32_t)i + 1u);
+                            const uint32_t hi = h0 ? sw[i][1] : h1 ? sw[i][3] : h2 ? sw[i][5] : sw[i][7];
+                            if (!slot_multi(hi)) tally(hi >> 16, t0 + (uint32_t)i + 1u);
+                            else if (RECORD) atomicAdd(slot_mult + 4ull * sb[i] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
                             break;
                         }
                         if ((sw[i][6] & sw[i][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;   // the k-mer does not occur in the index
@@ -932,11 +1046,10 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                 if (paired && !mate2) mate2 = true;
                 else
                 {
-                    gmin = __reduce_min_sync(kFullH, gmin);
-                    gmax = __reduce_max_sync(kFullH, gmax);
+                    uset.warp_merge();
                     n_total += c_total;
-                    if (lane == 0u && gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
-                    c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                    if (lane == 0u && uset.ambiguous()) { n_amb += 1u; env.fusion(uset.key()); }
+                    c_total = 0u; uset.reset();
                     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                     agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
                     mate2 = false;
@@ -956,8 +1069,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
             {
                 // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
                 n_total += c_total;
-                if (gmin != kNoGroup && gmin != gmax) { n_amb += 1u; env.fusion(gmin, gmax); }
-                c_total = 0u; gmin = kNoGroup; gmax = 0u;
+                if (uset.ambiguous()) { n_amb += 1u; env.fusion(uset.key()); }
+                c_total = 0u; uset.reset();
                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
                 agg_g = kNoGroup; agg_n = 0u; agg_w = 0.0;
                 mate2 = false;
@@ -998,17 +1111,21 @@ int sm_count_h()
 }   // namespace
 
 constexpr int kWprBit = 16;   // dispatch selector: the warp-per-read instantiation
+constexpr int kMaskBit = 32;  // dispatch selector: the unit's variants as a 64-bit mask (V <= kMaxGroupsMask)
+#define SPEQB_SCANH_CASES(K, B, MK, EXPR)                                               \
+        case (B): { auto kern = K<0, false, MK>; EXPR; break; }                         \
+        case (B) | M_RECORD: { auto kern = K<M_RECORD, false, MK>; EXPR; break; }       \
+        case (B) | M_LOCAL: { auto kern = K<M_LOCAL, false, MK>; EXPR; break; }         \
+        case (B) | M_LOCAL | M_RECORD: { auto kern = K<M_LOCAL | M_RECORD, false, MK>; EXPR; break; } \
+        case (B) | kWprBit: { auto kern = K<0, true, MK>; EXPR; break; }                \
+        case (B) | kWprBit | M_RECORD: { auto kern = K<M_RECORD, true, MK>; EXPR; break; } \
+        case (B) | kWprBit | M_LOCAL: { auto kern = K<M_LOCAL, true, MK>; EXPR; break; } \
+        case (B) | kWprBit | M_LOCAL | M_RECORD: { auto kern = K<M_LOCAL | M_RECORD, true, MK>; EXPR; break; }
 #define SPEQB_SCANH_DISPATCH(M, EXPR)                                                   \
     switch (M)                                                                          \
     {                                                                                   \
-        case 0: { auto kern = scanh_kernel<0, false>; EXPR; break; }                    \
-        case M_RECORD: { auto kern = scanh_kernel<M_RECORD, false>; EXPR; break; }      \
-        case M_LOCAL: { auto kern = scanh_kernel<M_LOCAL, false>; EXPR; break; }        \
-        case M_LOCAL | M_RECORD: { auto kern = scanh_kernel<M_LOCAL | M_RECORD, false>; EXPR; break; } \
-        case kWprBit: { auto kern = scanh_kernel<0, true>; EXPR; break; }               \
-        case kWprBit | M_RECORD: { auto kern = scanh_kernel<M_RECORD, true>; EXPR; break; } \
-        case kWprBit | M_LOCAL: { auto kern = scanh_kernel<M_LOCAL, true>; EXPR; break; } \
-        case kWprBit | M_LOCAL | M_RECORD: { auto kern = scanh_kernel<M_LOCAL | M_RECORD, true>; EXPR; break; } \
+        SPEQB_SCANH_CASES(scanh_kernel, 0, false, EXPR)                                 \
+        SPEQB_SCANH_CASES(scanh_kernel, kMaskBit, true, EXPR)                           \
         default: return cudaErrorInvalidValue;                                          \
     }
 
@@ -1020,7 +1137,7 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     // both instantiations (lane per read, warp per read) are launched with one grid: the smaller occupancy
     for (int wpr = 0; wpr <= kWprBit; wpr += kWprBit)
     {
-        const int m = (mode & (M_LOCAL | M_RECORD)) | wpr;
+        const int m = (mode & (M_LOCAL | M_RECORD)) | wpr | (V <= kMaxGroupsMask ? kMaskBit : 0);
         int bw = 0;
         SPEQB_SCANH_DISPATCH(m, {
             if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1060,6 +1177,7 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
     kt->mul_inv = x;
     kt->filt = nullptr;
     kt->fshift = 0u;
+    kt->pshift = 0u;
     return true;
 }
 
@@ -1088,7 +1206,7 @@ cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, Ba
 {
     const size_t smem = scan32_smem_bytes(a.V);
     const int paired = (mode & M_PAIRED) ? 1 : 0;
-    const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0);
+    const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0) | (a.V <= kMaxGroupsMask ? kMaskBit : 0);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, slot_mult, b, a, paired)))
@@ -1098,14 +1216,8 @@ cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, Ba
 #define SPEQB_SCANP_DISPATCH(M, EXPR)                                                   \
     switch (M)                                                                          \
     {                                                                                   \
-        case 0: { auto kern = scanp_kernel<0, false>; EXPR; break; }                    \
-        case M_RECORD: { auto kern = scanp_kernel<M_RECORD, false>; EXPR; break; }      \
-        case M_LOCAL: { auto kern = scanp_kernel<M_LOCAL, false>; EXPR; break; }        \
-        case M_LOCAL | M_RECORD: { auto kern = scanp_kernel<M_LOCAL | M_RECORD, false>; EXPR; break; } \
-        case kWprBit: { auto kern = scanp_kernel<0, true>; EXPR; break; }               \
-        case kWprBit | M_RECORD: { auto kern = scanp_kernel<M_RECORD, true>; EXPR; break; } \
-        case kWprBit | M_LOCAL: { auto kern = scanp_kernel<M_LOCAL, true>; EXPR; break; } \
-        case kWprBit | M_LOCAL | M_RECORD: { auto kern = scanp_kernel<M_LOCAL | M_RECORD, true>; EXPR; break; } \
+        SPEQB_SCANH_CASES(scanp_kernel, 0, false, EXPR)                                 \
+        SPEQB_SCANH_CASES(scanp_kernel, kMaskBit, true, EXPR)                           \
         default: return cudaErrorInvalidValue;                                          \
     }
 
@@ -1116,7 +1228,7 @@ cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
     cudaError_t e = cudaSuccess;
     for (int wpr = 0; wpr <= kWprBit; wpr += kWprBit)
     {
-        const int m = (mode & (M_LOCAL | M_RECORD)) | wpr;
+        const int m = (mode & (M_LOCAL | M_RECORD)) | wpr | (V <= kMaxGroupsMask ? kMaskBit : 0);
         int bw = 0;
         SPEQB_SCANP_DISPATCH(m, {
             if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1136,7 +1248,7 @@ cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long
 {
     const size_t smem = scan32_smem_bytes(a.V);
     const int paired = (mode & M_PAIRED) ? 1 : 0;
-    const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0);
+    const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0) | (a.V <= kMaxGroupsMask ? kMaskBit : 0);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     SPEQB_SCANP_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, kp, slot_mult, pair_mult, b, a, paired)))
@@ -1187,6 +1299,50 @@ cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv
         ktable_build_kernel<<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, t_group + t0, kt, k, n_keys);
     }
     return cudaGetLastError();
+}
+
+// positions fit above the displacement (and below the variant field's all-ones pattern the first pass leaves in such slots)
+bool ktable_positions_fit(KTabView const & kt, uint64_t npos)
+{
+    uint32_t bits = 1u;
+    while (bits < 63u && (1ull << bits) < npos + 2ull) ++bits;
+    return kt.rbits + bits <= 59u && npos < 0xFFFFFFF0ull;
+}
+
+cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
+                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k, cudaStream_t st)
+{
+    if (n_texts == 0 || max_len < k) return cudaSuccess;
+    const uint32_t groups = (max_len + 31u) / 32u;
+    const uint32_t gx = std::min<uint32_t>((groups + kBlockH - 1) / kBlockH, (uint32_t)sm_count_h() * 8u);
+    for (uint32_t t0 = 0; t0 < n_texts; t0 += 65535u)
+    {
+        const uint32_t nt = std::min<uint32_t>(65535u, n_texts - t0);
+        ktable_canon_kernel<<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, kt, k);
+    }
+    return cudaGetLastError();
+}
+
+// diff -> inclusive prefix sum in place (cub) -> multiplicities at the interval starts; diff is left zeroed
+cudaError_t launch_kpos_fold(const uint64_t * t_bases, DevIndex const & ix, uint32_t k, unsigned long long * diff, uint64_t npos,
+                             void * tmp, size_t tmp_bytes, unsigned long long * mult, cudaStream_t st)
+{
+    size_t need_bytes = 0;
+    cudaError_t e = cub::DeviceScan::InclusiveSum(nullptr, need_bytes, diff, diff, (int64_t)(npos + 2), st);
+    if (e != cudaSuccess) return e;
+    if (need_bytes > tmp_bytes) return cudaErrorInvalidValue;
+    e = cub::DeviceScan::InclusiveSum(tmp, tmp_bytes, diff, diff, (int64_t)(npos + 2), st);
+    if (e != cudaSuccess) return e;
+    kpos_fold_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(t_bases, ix, k, diff, npos + 2, mult);
+    return cudaGetLastError();
+}
+
+size_t kpos_fold_tmp_bytes(uint64_t npos)
+{
+    size_t need_bytes = 0;
+    unsigned long long * d = nullptr;
+    cub::DeviceScan::InclusiveSum(nullptr, need_bytes, d, d, (int64_t)(npos + 2), (cudaStream_t)0);
+    return need_bytes + 256;
 }
 
 cudaError_t launch_ktable_fold_mult(KTabView const & kt, DevIndex const & ix, uint32_t k, unsigned long long * slot_mult,

@@ -250,6 +250,25 @@ class Scan:
         capi.check(capi.lib().speqg_scan_fusion_counts(self.h, out.ctypes.data))
         return out
 
+    def fusion_sets(self) -> dict:
+        """{tuple of variants: ambiguous reads / pairs}: the fix-forward of the reference's fusion_totals map
+        (src/fm_scanner.cpp:915,947-952,983-995).  At most 64 variants: the full set of variants with a unique k-mer in the unit;
+        above: (smallest, largest) with a trailing "+" entry when further variants lie between them."""
+        n, lost = C.c_uint64(), C.c_uint64()
+        capi.check(capi.lib().speqg_scan_fusion_sets(self.h, None, None, 0, C.byref(n), C.byref(lost)))
+        keys, cnts = np.zeros(max(1, n.value), np.uint64), np.zeros(max(1, n.value), np.uint64)
+        capi.check(capi.lib().speqg_scan_fusion_sets(self.h, keys.ctypes.data, cnts.ctypes.data, n.value, C.byref(n), C.byref(lost)))
+        if lost.value:
+            raise capi.SpeqError(capi.ESTATE, f"fusion map overflowed: {lost.value} ambiguous units without a set")
+        out = {}
+        for key, c in zip(keys[:n.value].tolist(), cnts[:n.value].tolist()):
+            if self.V <= 64:
+                t = tuple(g for g in range(64) if (key >> g) & 1)
+            else:
+                t = (key & 0xFFFF, (key >> 16) & 0xFFFF) + (("+",) if (key >> 32) & 1 else ())
+            out[t] = out.get(t, 0) + int(c)
+        return out
+
     def device_counters(self):
         """The handle's counters as torch tensors over its device memory (int64 view of the u64 counters, float64 local-mode
         tallies): a multi-GPU driver all-reduces them in place on the scan's stream before finish()."""

@@ -15,6 +15,7 @@
 #include <cstring>
 #include <fstream>
 #include <iostream>
+#include <map>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -367,7 +368,8 @@ std::vector<double> unique_to_percent(std::vector<double> const & unique_in_read
 // --write-output: the per-variant result table as tab-separated text in -o/--output.  The reference declares the option
 // (src/arg_parse.cpp:20) and reports on stderr only; this is the fix-forward of SURVEY.md 8f-4, off by default.
 void write_table(fs::path const & p, idx_meta const & meta, scan_out const & so, std::vector<double> const & unique_totals,
-                 std::vector<double> const & initial, std::vector<double> const & fin, std::vector<uint64_t> const & fusion)
+                 std::vector<double> const & initial, std::vector<double> const & fin, std::map<uint64_t, uint64_t> const & fusion,
+                 uint64_t fusion_unkeyed)
 {
     FILE * f = fopen(p.c_str(), "w");
     if (!f) throw std::runtime_error("cannot write " + p.string());
@@ -376,18 +378,28 @@ void write_table(fs::path const & p, idx_meta const & meta, scan_out const & so,
     fprintf(f, "group\tisolates\tunique_kmers\tpercent_initial\tpercent_final\n");
     for (size_t g = 0; g < fin.size(); ++g)
         fprintf(f, "%s\t%d\t%.17g\t%.17g\t%.17g\n", meta.group_names[g].c_str(), meta.group_counts[g], unique_totals[g], initial[g], fin[g]);
-    // the fix-forward of the reference's fusion_totals report (src/fm_scanner.cpp:983-995,1033): ambiguous reads / pairs by
-    // the smallest and largest variant whose unique k-mers they hold
+    // the fix-forward of the reference's fusion_totals report (std::map<std::set<int>,int>, src/fm_scanner.cpp:915,947-952,
+    // 983-995,1033): ambiguous reads / pairs by the SET of variants whose unique k-mers they hold.  Up to 64 variants the key is
+    // the full set; above, the smallest and largest variant, with "..." between them when further variants met in the unit.
     const size_t V = fin.size();
-    if (fusion.size() == V * V)
+    fprintf(f, "# ambiguous reads / pairs by the set of variants that met in them\nfusion\tgroups\tcount\n");
+    for (auto const & kv : fusion)
     {
-        fprintf(f, "# ambiguous reads / pairs by the variants that met in them\nfusion\tgroup_a\tgroup_b\tcount\n");
-        for (size_t a = 0; a < V; ++a)
-            for (size_t b = 0; b < V; ++b)
-                if (fusion[a * V + b])
-                    fprintf(f, "fusion\t%s\t%s\t%llu\n", meta.group_names[a].c_str(), meta.group_names[b].c_str(),
-                            static_cast<unsigned long long>(fusion[a * V + b]));
+        std::string names;
+        if (V <= 64)
+        {
+            for (size_t g = 0; g < V; ++g)
+                if ((kv.first >> g) & 1ull) names += (names.empty() ? "" : ",") + meta.group_names[g];
+        }
+        else
+        {
+            names = meta.group_names[kv.first & 0xFFFFull];
+            names += ((kv.first >> 32) & 1ull) ? ",...," : ",";
+            names += meta.group_names[(kv.first >> 16) & 0xFFFFull];
+        }
+        fprintf(f, "fusion\t%s\t%llu\n", names.c_str(), static_cast<unsigned long long>(kv.second));
     }
+    if (fusion_unkeyed) fprintf(f, "fusion\t(not keyed: device map full)\t%llu\n", static_cast<unsigned long long>(fusion_unkeyed));
     fclose(f);
 }
 
@@ -543,18 +555,18 @@ int do_scan(cmd_arguments & args)
         if (args.write_output)
         {
             // ambiguous reads / pairs by the variants that met in them, summed over the devices
-            std::vector<uint64_t> fusion;
-            if (V <= 1024)
+            std::map<uint64_t, uint64_t> fusion;
+            uint64_t unkeyed = 0;
+            for (auto & L : lanes)
             {
-                fusion.assign(static_cast<size_t>(V) * V, 0);
-                std::vector<uint64_t> part(fusion.size());
-                for (auto & L : lanes)
-                {
-                    ck(speqg_scan_fusion_counts(L.scan, part.data()), "speqg_scan_fusion_counts");
-                    for (size_t i = 0; i < part.size(); ++i) fusion[i] += part[i];
-                }
+                uint64_t n = 0, lost = 0;
+                ck(speqg_scan_fusion_sets(L.scan, nullptr, nullptr, 0, &n, &lost), "speqg_scan_fusion_sets");
+                std::vector<uint64_t> keys(n), cnts(n);
+                ck(speqg_scan_fusion_sets(L.scan, keys.data(), cnts.data(), n, &n, &lost), "speqg_scan_fusion_sets");
+                for (uint64_t i = 0; i < n; ++i) fusion[keys[i]] += cnts[i];
+                unkeyed += lost;
             }
-            write_table(args.out_file_path, meta, so, unique_totals, initial, percent, fusion);
+            write_table(args.out_file_path, meta, so, unique_totals, initial, percent, fusion, unkeyed);
         }
         if (!args.json_path.empty())
             write_json(args.json_path, args, local, paired, unique_ref, total_ref, so, unique_totals, initial, percent, iters, t_backcheck, t_refine);

@@ -30,13 +30,30 @@ CASES = {
                     dict(k=9, fixed_accuracy=0.99, paired=False)),
     "short_k": (dict(seed=16, V=5, I=1, G=300, R=150, L=40, e=0.03, d_var=0.15),
                 dict(k=5, fixed_accuracy=0.97, paired=False)),
+    # k > 31 (round 2): reads long enough to hold windows, N / IUPAC letters and low-quality bases so that restarts and parent
+    # jumps at depths up to k-1 trigger; ragged lengths give reads below k.  k = 70 + local mode + --phred-cutoff 30 is the
+    # reference's default invocation (include/arg_parse.h:20-23)
+    "k70_global_single": (dict(seed=21, V=3, I=2, G=2500, R=120, L=180, e=0.004, d_var=0.03, n_rate_read=0.002, lowq_rate=0.003, ragged=True, iupac=True),
+                          dict(k=70, fixed_accuracy=0.996, paired=False)),
+    "k70_local_single": (dict(seed=22, V=3, I=2, G=2500, R=120, L=180, e=0.004, d_var=0.03, n_rate_read=0.002, lowq_rate=0.003, local_quals="high"),
+                         dict(k=70, fixed_accuracy=0.0, paired=False)),
+    "k70_global_paired": (dict(seed=23, V=4, I=2, G=2000, R=120, L=160, e=0.004, d_var=0.03, n_rate_read=0.002, lowq_rate=0.003, ragged=True),
+                          dict(k=70, fixed_accuracy=0.996, paired=True)),
+    "k70_local_paired": (dict(seed=24, V=3, I=2, G=2500, R=120, L=180, e=0.004, d_var=0.03, n_rate_read=0.002, lowq_rate=0.003, local_quals="high"),
+                         dict(k=70, fixed_accuracy=0.0, paired=True)),
+    "k127_local_single": (dict(seed=25, V=3, I=2, G=2500, R=100, L=240, e=0.002, d_var=0.03, n_rate_read=0.001, lowq_rate=0.002, local_quals="high"),
+                          dict(k=127, fixed_accuracy=0.0, paired=False)),
+    "k33_global_paired": (dict(seed=26, V=4, I=2, G=1500, R=120, L=100, e=0.01, d_var=0.04, n_rate_read=0.003, lowq_rate=0.005, ragged=True),
+                          dict(k=33, fixed_accuracy=0.99, paired=True)),
 }
 
 
-def main() -> None:
+def main(only: list[str] | None = None) -> None:
     ref = helpers.ref_binary()
     assert ref is not None, "needs /root/reference to build oracle/_ref/speq_ref"
     for name, (ckw, rkw) in CASES.items():
+        if only and name not in only:
+            continue
         case = helpers.random_case(**ckw)
         rkw = dict(rkw)
         paired = rkw.pop("paired")
@@ -55,4 +72,4 @@ def main() -> None:
 
 
 if __name__ == "__main__":
-    main()
+    main(sys.argv[1:])     # names of the fixtures to (re)generate; none = all

@@ -62,6 +62,38 @@ def run_oracle(binary: Path, refs: Path, groups: Path, reads1: Path, *, k: int, 
     return json.loads(r.stdout)
 
 
+def run_oracle_jobs(binary: Path, refs: Path, groups: Path, jobs: list[dict], *, threads: int = 4, backcheck: bool = True) -> list[dict]:
+    """Several scan jobs against ONE index build of the oracle (`--next` between them; a job inherits the settings of the one
+    before it).  Job keys: reads1, reads2, k, phred_cutoff, fixed_accuracy, precision, max_reads, refine (bool), max_iters,
+    unique_ref / total_ref (lists: injected back-check counts)."""
+    cmd = [str(binary), "run", "--refs", str(refs), "--groups", str(groups), "--threads", str(threads)]
+    if not backcheck:
+        cmd.append("--no-backcheck")
+    for i, j in enumerate(jobs):
+        if i:
+            cmd.append("--next")
+        if "reads1" in j:
+            cmd += ["--reads1", str(j["reads1"])]
+        if j.get("reads2") is not None:
+            cmd += ["--reads2", str(j["reads2"])]
+        for key, flag in (("k", "-k"), ("phred_cutoff", "--phred-cutoff"), ("max_reads", "--max-reads"), ("max_iters", "--max-iters")):
+            if key in j:
+                cmd += [flag, str(int(j[key]))]
+        for key, flag in (("fixed_accuracy", "--fixed-accuracy"), ("precision", "--precision")):
+            if key in j:
+                cmd += [flag, repr(float(j[key]))]
+        if "refine" in j:
+            cmd.append("--refine" if j["refine"] else "--no-refine")
+        for key, flag in (("unique_ref", "--unique-ref"), ("total_ref", "--total-ref")):
+            if key in j:
+                cmd += [flag, ",".join(str(int(x)) for x in j[key])]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"oracle failed: {r.stderr}")
+    out = json.loads(r.stdout)
+    return out if isinstance(out, list) else [out]
+
+
 def run_oracle_search(binary: Path, sigma: int, texts: list[str], queries: list[list[str]], want_size: bool = False) -> list[dict]:
     s = f"sigma {sigma}\n" + "".join(f"text {t}\n" for t in texts)
     if want_size:
@@ -148,7 +180,12 @@ def random_case(seed: int, *, V: int = 3, I: int = 2, G: int = 400, R: int = 200
             low = rng.random(Lr) < 0.1
             s = np.where(low, np.char.lower(s), s)
             s = np.where((s == "T") & (rng.random(Lr) < 0.1), "U", s)
-        if local_quals:
+        if local_quals == "high":
+            # the reference's default invocation (no --fixed-accuracy, --phred-cutoff 30): qualities above the cutoff that
+            # still differ per base, so the phred-weighted tallies are not a constant times the counts
+            u = rng.random(Lr)
+            q = np.where(u < 0.10, 33, np.where(u < 0.40, 37, 40))
+        elif local_quals:
             u = rng.random(Lr)
             q = np.where(u < 0.05, 20, np.where(u < 0.20, 30, 37))
         else:
@@ -173,6 +210,18 @@ def case_files(tmp: Path, case: dict, paired: bool = False):
         return tmp / "refs.fa", tmp / "groups.txt", tmp / "r1.fq", tmp / "r2.fq"
     write_fastq(tmp / "r1.fq", case["seqs"], case["quals"])
     return tmp / "refs.fa", tmp / "groups.txt", tmp / "r1.fq", None
+
+
+def write_fastq_fixed(path: Path, seq: np.ndarray, qual: np.ndarray) -> None:
+    """4-line FASTQ of equal-length reads ([n, L] ASCII arrays), written as one fixed-width byte matrix."""
+    n, L = seq.shape
+    rec = np.empty((n, 3 + L + 3 + L + 1), np.uint8)
+    rec[:, 0:3] = np.frombuffer(b"@r\n", np.uint8)
+    rec[:, 3:3 + L] = seq
+    rec[:, 3 + L:6 + L] = np.frombuffer(b"\n+\n", np.uint8)
+    rec[:, 6 + L:6 + 2 * L] = qual
+    rec[:, 6 + 2 * L] = 10
+    rec.tofile(str(path))
 
 
 def flat_reads(seqs: list[str], quals: list[str] | None):
@@ -237,6 +286,9 @@ def load_golden(name: str) -> dict:
 
 
 GOLDEN_NAMES = ["global_single", "local_single", "global_paired", "local_paired", "refs_with_n", "short_k"]
+# k > 31: the rolling FM search is the product path (the k-mer table covers k <= 31).  k = 70 in local-error mode with the
+# default --phred-cutoff is the reference's default invocation (include/arg_parse.h:20-23)
+GOLDEN_LONG_K = ["k70_global_single", "k70_local_single", "k70_global_paired", "k70_local_paired", "k127_local_single", "k33_global_paired"]
 
 
 def golden_files(tmp: Path, fx: dict):

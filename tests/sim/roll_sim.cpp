@@ -108,7 +108,7 @@ struct HostEnv32
     void record(uint32_t lb) const { if (mult) ++mult[lb]; }
     void count_fetch(uint32_t nwin) const { look += nwin; }
     void count_unit(uint32_t t, bool a) const { total += t; amb += a ? 1 : 0; }
-    void fusion(uint32_t, uint32_t) const {}
+    void fusion(uint64_t) const {}
 };
 
 struct HostEnv
@@ -251,6 +251,8 @@ int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, c
             Cfg32 cfg;
             cfg.k = k; cfg.n = (uint32_t)h.n; cfg.units = paired ? n_reads / 2 : n_reads;
             cfg.paired = paired; cfg.local = local; cfg.record = mult != nullptr;
+            cfg.mask64 = V <= 64 ? 1 : 0;
+            cfg.skip_unique = 0;      // the tests compare the recorded multiplicities with the from-the-root search's
             HostEnv32 env{h, qual, qden, uniq, uniq_w, mult, local != 0, total, amb, look};
             std::vector<Lane32> lanes(nlanes);
             std::vector<Loads32> loads(nlanes);

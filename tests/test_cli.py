@@ -96,7 +96,7 @@ def test_scan_needs_gpu(speq_bin, tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES + ["k70_global_paired", "k127_local_single"])
 def test_speq_all_matches_golden(speq_bin, tmp_path, name):
     fx = helpers.load_golden(name)
     exp, runp = fx["expected"], fx["run"]
@@ -144,8 +144,36 @@ def test_speq_all_matches_golden(speq_bin, tmp_path, name):
     assert [float(r[4]) for r in rows[3:3 + nv]] == out2["percent_final"]
     assert [float(r[3]) for r in rows[3:3 + nv]] == out2["percent_initial"]
     # then the fusion report: ambiguous reads / pairs by the variants that met in them; the counts sum to ambiguous_reads
-    assert rows[3 + nv][0].startswith("# ambiguous") and rows[4 + nv] == ["fusion", "group_a", "group_b", "count"]
-    assert sum(int(r[3]) for r in rows[5 + nv:]) == exp["ambiguous"]
+    assert rows[3 + nv][0].startswith("# ambiguous") and rows[4 + nv] == ["fusion", "groups", "count"]
+    assert sum(int(r[2]) for r in rows[5 + nv:]) == exp["ambiguous"]
+    # the sets are the oracle's fix-forward map: variant names V0, V1, ... joined by commas
+    names, _, _ = helpers.parse_groups(fx["groups_txt"])
+    got = {",".join(str(names.index(x)) for x in r[1].split(",")): int(r[2]) for r in rows[5 + nv:]}
+    assert got == exp["fusion"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["k70_local_single", "k70_local_paired"])
+def test_speq_all_default_invocation(speq_bin, tmp_path, name):
+    """`speq all` with NO -k, NO --fixed-accuracy and NO --phred-cutoff: the reference's defaults kmer{70}, fixed_accuracy{0.0}
+    (= local-error mode, src/fm_scanner.cpp:8-17) and phred_cutoff{30} (include/arg_parse.h:20-23).  The fixtures were generated
+    with exactly those values by oracle/_ref."""
+    fx = helpers.load_golden(name)
+    exp, runp = fx["expected"], fx["run"]
+    assert runp["k"] == 70 and runp["fixed_accuracy"] == 0.0 and runp.get("phred_cutoff", 30) == 30
+    refs, groups, r1, r2 = helpers.golden_files(tmp_path, fx)
+    cmd = ["all", "-r", refs, "-g", groups, "-1", r1, "-x", tmp_path / "i.idx", "--json", tmp_path / "out.json"]
+    if r2 is not None:
+        cmd += ["-2", r2]
+    r = run(speq_bin, *cmd, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    out = json.loads((tmp_path / "out.json").read_text())
+    assert out["unique_ref"] == exp["unique_ref"] and out["total_ref"] == exp["total_ref"]
+    assert out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"] and out["lookups"] == exp["lookups"]
+    assert helpers.rel_close(out["unique_w"], exp["unique_w"], 1e-12)
+    assert out["iterations"] == exp["iterations"]
+    assert helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
+    assert (tmp_path / "i_70mer.dat").exists()            # <stem>_<k>mer.dat with the default k (src/fm_scanner.cpp:81-82)
 
 
 def _write_fq(path, recs, newline="\n", trailing=True):

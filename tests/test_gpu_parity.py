@@ -38,10 +38,12 @@ def _compare(out: dict, exp: dict, V: int):
         assert helpers.rel_close(a, b, 1e-11)
 
 
-@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES + helpers.GOLDEN_LONG_K)
 @pytest.mark.parametrize("raw", [True, False])
 def test_golden(lib, name, raw):
-    """The rolling FM search (the path for every k) against the fixtures."""
+    """The rolling FM search (the path for every k) against the fixtures; the k > 31 fixtures (k = 33, 70, 127; k = 70 in local
+    mode with the default phred cutoff is the reference's default invocation) exercise e-bit contraction and parent jumps at
+    depths up to 126."""
     fx = helpers.load_golden(name)
     exp, run = fx["expected"], fx["run"]
     scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
@@ -66,7 +68,25 @@ def test_golden_ktable_algorithm(lib, name, raw, algorithm):
     _compare(out, exp, len(counts))
 
 
-@pytest.mark.parametrize("name", ["global_single", "global_paired", "refs_with_n", "short_k"])
+@pytest.mark.parametrize("name", helpers.GOLDEN_LONG_K)
+def test_golden_long_k_auto(lib, name):
+    """SPEQG_ALGO_AUTO at k > 31 resolves to the rolling FM search (scan32_kernel): the product path of the reference's
+    default k = 70.  Same fixtures through AUTO, raw submits in small batches."""
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    idx = engine.Index.from_scaffolds(scaff, gs, len(counts))
+    probe = engine.Scan(idx, k=run["k"])
+    assert probe.info()["algorithm"] == capi.ALGO_ROLLING
+    probe.close()
+    out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
+                         fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], raw=True, batch_reads=32,
+                         algorithm=capi.ALGO_AUTO, index=idx)
+    _compare(out, exp, len(counts))
+    idx.close()
+
+
+@pytest.mark.parametrize("name", ["global_single", "global_paired", "refs_with_n", "short_k", "k70_global_single", "k33_global_paired"])
 def test_golden_direct_algorithm(lib, name):
     fx = helpers.load_golden(name)
     exp, run = fx["expected"], fx["run"]
@@ -430,7 +450,10 @@ def test_fusion_counts(lib, algorithm, paired):
         fus = sc.fusion_counts()
         assert int(fus.sum()) == r.ambiguous > 0
         assert np.all(np.tril(fus) == 0)                              # smallest < largest
+        sets = sc.fusion_sets()
+        assert sum(sets.values()) == r.ambiguous and any(len(t) >= 3 for t in sets)      # units with three variants keep all three
         exp = np.zeros((V, V), np.uint64)
+        exp_sets = {}
         step = 2 if paired else 1
         for u in range(0, R, step):
             sc.reset()
@@ -439,7 +462,10 @@ def test_fusion_counts(lib, algorithm, paired):
             nz = np.nonzero(ru.unique)[0]
             if nz.size > 1:
                 exp[nz[0], nz[-1]] += 1
+                t = tuple(int(g) for g in nz)
+                exp_sets[t] = exp_sets.get(t, 0) + 1
         assert np.array_equal(fus, exp)
+        assert sets == exp_sets
         sc.close()
     idx.close()
 

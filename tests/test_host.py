@@ -160,7 +160,7 @@ def _sim_scan(sim, scaff, gs, V, seqs, quals, k, cutoff, paired, algo, backcheck
     return out, out_w, mult
 
 
-@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES + helpers.GOLDEN_LONG_K)
 @pytest.mark.parametrize("algo", [0, 1, 2])
 def test_lane_arithmetic_vs_golden(lib, sim, name, algo):
     fx = helpers.load_golden(name)

@@ -44,9 +44,10 @@ def _same(a: dict, b: dict):
     for key in ("unique_w", "unique_totals", "percent_initial", "percent_final"):
         assert a[key] == b[key], key
     assert a["iter_tkpg"] == b["iter_tkpg"]
+    assert a["fusion"] == b["fusion"]
 
 
-@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES)
+@pytest.mark.parametrize("name", helpers.GOLDEN_NAMES + helpers.GOLDEN_LONG_K)
 def test_golden_fixtures(oracle_bin, tmp_path, name):
     fx = helpers.load_golden(name)
     refs, groups, r1, r2 = helpers.golden_files(tmp_path, fx)
