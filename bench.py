@@ -1,20 +1,27 @@
 #!/usr/bin/env python
 """bench.py -- throughput of the SPeQ scan hot path on B200 (k-mer lookups/s; reads/s alongside).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--config C2] [--reads R]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--config C3] [--reads R] [--mode global|local] [-k K]
 
-A step = one scan pass over one batch of synthetic reads of the named BASELINE.json config (default C2: 10 variants x 20
-isolates x 10 kb, 10 M x 150 bp reads, 0.5 % error, k = 21) per GPU.  N > 1: one rank per GPU (torchrun), every rank
-scans its own 10 M-read shard against its replica of the index (weak scaling, no data-path collective); the only
-collective is the all-reduce of the per-variant tallies at the end of the step.
-  value     lookups/s with the packed reads already resident in HBM (CUDA events, max over ranks)
-  e2e       lookups/s through the C ABI from pinned HOST buffers (ASCII reads + qualities): H2D copy, device packer,
-            scan, D2H of the tallies all inside the timed region
-  roofline  dominant kernel (scan_roll_kernel): ALGORITHMIC bytes of the reference search (SURVEY.md section 8d:
-            64 B per executed backward step after the first, 32 B per 32 occurrences of a hit, 0.5 B per base of input)
-            / measured kernel time, against MEASURED_PEAKS.json's HBM copy bandwidth
-  cpu_baseline  the oracle (oracle/_ref = real sdsl-lite objects when present, else the port) on a bounded sample of the
-            same reads, all host threads
+Default workload = the configuration BASELINE.json's target is quoted on: C3 (50 variants x 10 isolates x 30 kb, 200 M x
+150 bp reads at 0.5 % error, k = 25), STRONG scaling: the same 200 M reads at every N, sharded over the N GPUs (one rank per
+GPU under torchrun, index replicated, no data-path collective; the only collective is the all-reduce of the small tally
+vector at the end of a step).  A step = one scan pass over all the reads.  `--config C1|C2|C4|C5` selects the other shapes.
+
+  value     lookups/s of the scan AS `speq scan` RUNS IT (record_multiplicity = 1: the refinement's per-k-mer counts are kept),
+            packed reads resident in HBM, CUDA events on the scan's stream, max over ranks.  `tallies_only` = the same without
+            the recording.
+  e2e       the same through the C ABI from pinned HOST buffers (ASCII reads + quality chars) in 1 M-read submits: H2D copy,
+            device packer, scan, D2H of the tallies inside the timed region; on the first `--e2e-reads` reads of every rank
+  roofline  the dominant kernel against the roofline its access pattern has: independent random 32-byte sectors (one per
+            k-mer table probe / two per rank step).  achieved = the kernel's own sectors x 32 B / its CUDA-event time;
+            peak = the random-sector rate of THIS device for a table of the probed structure's size, measured in the same
+            process (speqg_probe_random_sectors) x 32 B.  bound says whether that structure is L2- or HBM-resident.
+            `reference_work_rate` keeps SURVEY.md 8d's figure: the algorithmic bytes of the reference's own search
+            (64 B per executed backward step, 32 B per 32 located occurrences, 0.5 B per base) over the same time.
+  parity    the oracle's tallies on the CPU-timed sample == the GPU's tallies on the same reads (default algorithm)
+  cpu_baseline  oracle/_ref (the reference's glue over the real vendored sdsl-lite objects) when it was built, else the
+            port; all host threads; a bounded sample of the same reads
 `--impl reference` times only that CPU arm and prints the same line with "impl": "reference".
 """
 from __future__ import annotations
@@ -37,6 +44,7 @@ sys.path.insert(0, str(ROOT))
 
 METRIC = "kmer_lookups_per_sec"
 UNIT = "lookups/s"
+CHUNK_BASES = 150_000_000      # synthetic reads are generated in chunks of about this many bases (C3: 1 M reads)
 
 
 def log(*a):
@@ -44,34 +52,19 @@ def log(*a):
 
 
 # ---------------------------------------------------------------------------------------------------------------
-# workload
+# workload: a fixed global read set, generated chunk by chunk (chunk c has its own seed), so that every N scans the same reads
 # ---------------------------------------------------------------------------------------------------------------
-def workload(cfg: str, reads: int | None, rank: int, device):
-    """-> (shape, refs codes [V*I, G] on device, seq ASCII [R, L] uint8 host-pinned, qual likewise)"""
-    import torch
-    from speq_b200 import synth
-    sh = synth.CONFIGS[cfg]
-    R = reads or sh.R
-    refs = synth.make_refs(sh, synth.SEED0 + int(cfg[1]), device=device)
-    pin = device != "cpu"
-    seq = torch.empty((R, sh.L), dtype=torch.uint8, pin_memory=pin)
-    qual = torch.empty((R, sh.L), dtype=torch.uint8, pin_memory=pin)
-    chunk = max(1, min(R, (1 << 25) // sh.L))
-    for i, s in enumerate(range(0, R, chunk)):
-        e = min(R, s + chunk)
-        a, b = synth.make_reads(sh, refs, e - s, synth.SEED0 * 1000 + int(cfg[1]) * 100000 + rank * 1000 + i)
-        seq[s:e].copy_(a)
-        qual[s:e].copy_(b)
-        del a, b
-    return sh, refs, seq, qual
+def chunk_reads(sh) -> int:
+    return max(1, min(1_000_000, CHUNK_BASES // sh.L))
 
 
-def cpu_sample(sh, refs, seq, qual, n_reads: int, tmp: Path):
+def shard_chunks(n_chunks: int, rank: int, world: int) -> tuple[int, int]:
+    return n_chunks * rank // world, n_chunks * (rank + 1) // world
+
+
+def gen_chunk(sh, cfg_id: int, refs, c: int, n: int, local: bool):
     from speq_b200 import synth
-    synth.write_fasta(str(tmp / "refs.fa"), refs)
-    synth.write_groups(str(tmp / "groups.txt"), sh)
-    write_fastq_fixed(tmp / "sample.fq", seq[:n_reads].numpy(), qual[:n_reads].numpy())
-    return tmp / "refs.fa", tmp / "groups.txt", tmp / "sample.fq"
+    return synth.make_reads(sh, refs, n, synth.SEED0 * 1000 + cfg_id * 100_000 + c, local_quals=local)
 
 
 def write_fastq_fixed(path: Path, seq: np.ndarray, qual: np.ndarray) -> None:
@@ -122,35 +115,45 @@ def host_threads() -> int:
         return max(1, os.cpu_count() or 1)
 
 
-def run_cpu(binary, files, sh, threads: int, n_reads: int) -> dict:
+def run_cpu(binary, files, k: int, accuracy: float, cutoff: int, threads: int, n_reads: int) -> dict:
     """One scan pass of the oracle over the first n_reads reads (no back-check, no refinement): the reference's scan."""
     refs, groups, fq = files
-    cmd = [str(binary), "run", "--refs", str(refs), "--groups", str(groups), "--reads1", str(fq), "-k", str(sh.k),
-           "--fixed-accuracy", repr(sh.accuracy), "--threads", str(threads), "--max-reads", str(n_reads), "--no-refine", "--no-backcheck"]
+    cmd = [str(binary), "run", "--refs", str(refs), "--groups", str(groups), "--reads1", str(fq), "-k", str(k),
+           "--fixed-accuracy", repr(accuracy), "--phred-cutoff", str(cutoff), "--threads", str(threads), "--max-reads", str(n_reads),
+           "--no-refine", "--no-backcheck"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("oracle failed: " + r.stderr)
     return json.loads(r.stdout)
 
 
-def cpu_arm(sh, refs, seq, qual, *, steps: int, warmup: int, target_s: float, max_sample: int):
-    """Times the CPU scan on a bounded sample.  Returns (lookups/s, sample description, kind, cores, per-step seconds, out)."""
+def cpu_arm(sh, refs_cpu, seq: np.ndarray, qual: np.ndarray, *, k: int, accuracy: float, cutoff: int, steps: int, warmup: int,
+            target_s: float):
+    """Times the CPU scan on a bounded sample (the first n reads of seq).  -> (lookups/s, sample text, kind, cores, s/step, out, n)"""
+    from speq_b200 import synth
     binary, kind = oracle_choice()
     T = host_threads()
+    wpr = max(1, sh.L - k + 1)
     with tempfile.TemporaryDirectory() as d:
+        d = Path(d)
+        synth.write_fasta(str(d / "refs.fa"), refs_cpu)
+        synth.write_groups(str(d / "groups.txt"), sh)
         n_cal = min(seq.shape[0], 256 * T)
-        files = cpu_sample(sh, refs, seq, qual, n_cal, Path(d))
-        cal = run_cpu(binary, files, sh, T, n_cal)
+        write_fastq_fixed(d / "sample.fq", seq[:n_cal], qual[:n_cal])
+        files = (d / "refs.fa", d / "groups.txt", d / "sample.fq")
+        cal = run_cpu(binary, files, k, accuracy, cutoff, T, n_cal)
         rate = cal["lookups"] / max(cal["t_scan_s"], 1e-6)
-        n = int(min(seq.shape[0], max_sample, max(n_cal, rate * target_s / max(1, sh.windows_per_read))))
-        files = cpu_sample(sh, refs, seq, qual, n, Path(d))
+        n = int(min(seq.shape[0], max(n_cal, rate * target_s / wpr)))
+        write_fastq_fixed(d / "sample.fq", seq[:n], qual[:n])
         times, out = [], None
         for i in range(warmup + steps):
-            out = run_cpu(binary, files, sh, T, n)
+            out = run_cpu(binary, files, k, accuracy, cutoff, T, n)
             if i >= warmup:
                 times.append(out["t_scan_s"])
     t = sum(times) / len(times)
-    return out["lookups"] / t, f"first {n} reads of the workload ({out['lookups']} lookups) per step, scan pass only", kind, T, t, out
+    sample = (f"first {n} reads of rank 0's shard ({out['lookups']} lookups) per step, scan pass only (index build, back-check and "
+              f"refinement excluded); sample sized for about {target_s:g} s on this box's {T} threads")
+    return out["lookups"] / t, sample, kind, T, t, out, n
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -205,17 +208,6 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(sm)}
 
 
-# independent random 32-byte sector loads, G sectors/s, by table size (profiles/r1_gather_probe.txt, measured on this pool)
-RANDOM_SECTOR_PEAKS = [
-    (0.12e9, 235.8, "L2-resident table (0.1 GB probe)"),
-    (0.4e9, 72.4, "0.3 GB table probe"),
-    (0.8e9, 48.7, "0.5 GB table probe"),
-    (1.6e9, 42.7, "1.1 GB table probe"),
-    (3.2e9, 39.6, "2.1 GB table probe"),
-    (float("inf"), 37.9, "4.3 GB table probe"),
-]
-
-
 def measured_peak() -> tuple[float, str]:
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -246,12 +238,17 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--config", default="C2", choices=["C1", "C2", "C3", "C4", "C5"])
-    ap.add_argument("--reads", type=int, default=None, help="reads per GPU per step (default: the config's read count; C3: /8)")
+    ap.add_argument("--config", default="C3", choices=["C1", "C2", "C3", "C4", "C5"])
+    ap.add_argument("--reads", type=int, default=None, help="reads of the whole job per step (default: the config's read count)")
+    ap.add_argument("--mode", default="global", choices=["global", "local"],
+                    help="global: --fixed-accuracy 1-e, integer tallies; local: phred-weighted fp64 tallies (no --fixed-accuracy: the reference's default)")
+    ap.add_argument("-k", "--kmer", type=int, default=None, help="k-mer length (default: the config's; the reference's own default is 70)")
     ap.add_argument("--batch-reads", type=int, default=1 << 20, help="reads per C-ABI submit on the e2e leg")
+    ap.add_argument("--e2e-reads", type=int, default=25_000_000, help="reads of every rank's shard the host-fed legs stream per step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-probe", action="store_true", help="skip the in-run random-sector probe (profiling runs)")
     ap.add_argument("--algorithm", default="auto", choices=["auto", "kpair", "ktable", "rolling", "direct"],
                     help="auto = the library's default: pair / k-mer table scan for k <= 31, else the rolling FM search")
     args = ap.parse_args()
@@ -261,22 +258,34 @@ def main() -> None:
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     from speq_b200 import synth
-    sh0 = synth.CONFIGS[args.config]
-    reads = args.reads or (sh0.R // 8 if args.config == "C3" else sh0.R)
-    config = {"workload": sh0.name, "config": args.config, "reads_per_gpu_per_step": reads, "read_len": sh0.L, "k": sh0.k,
-              "variants": sh0.V, "isolates": sh0.I, "genome_len": sh0.G, "error_rate": sh0.e, "mode": "global (--fixed-accuracy %g)" % sh0.accuracy,
-              "parallelism": f"reads sharded over {world} GPU(s), index replicated", "algorithm": args.algorithm}
+    sh = synth.CONFIGS[args.config]
+    cfg_id = int(args.config[1])
+    k = args.kmer or sh.k
+    local = args.mode == "local"
+    accuracy = 0.0 if local else sh.accuracy
+    cutoff = 19 if local else 30          # local-mode reads carry Q20/Q30/Q37, scanned with --phred-cutoff 19
+    R_total = args.reads or sh.R
+    CH = chunk_reads(sh)
+    n_chunks = (R_total + CH - 1) // CH
+    config = {"workload": sh.name, "config": args.config, "reads_per_step": R_total, "read_len": sh.L, "k": k,
+              "variants": sh.V, "isolates": sh.I, "genome_len": sh.G, "error_rate": sh.e,
+              "mode": ("local (phred-weighted, --phred-cutoff 19)" if local else "global (--fixed-accuracy %g)" % sh.accuracy),
+              "parallelism": f"reads sharded over {args.gpus} GPU(s), index replicated", "algorithm": args.algorithm,
+              "l2": "inputs larger than L2 (packed reads of one step: 72 B per 150 bp read)"}
+    wpr = max(0, sh.L - k + 1)
 
     # ------------------------------------------------------------------------------------------------- reference arm
     if args.impl == "reference":
         if rank != 0:
             return
         import torch
-        sh, refs, seq, qual = workload(args.config, min(reads, 2_000_000), 0, "cpu")
-        v, sample, kind, T, t, out = cpu_arm(sh, refs, seq, qual, steps=max(1, args.steps), warmup=min(args.warmup, 1),
-                                             target_s=args.cpu_seconds, max_sample=seq.shape[0])
+        refs = synth.make_refs(sh, synth.SEED0 + cfg_id, device="cpu")
+        n0 = min(R_total, CH, 400_000)
+        a, b = gen_chunk(sh, cfg_id, refs, 0, n0, local)     # the head of chunk 0: the same generator and seed as the native arm
+        v, sample, kind, T, t, out, n = cpu_arm(sh, refs, a.numpy(), b.numpy(), k=k, accuracy=accuracy, cutoff=cutoff,
+                                                steps=max(1, args.steps), warmup=min(args.warmup, 1), target_s=args.cpu_seconds)
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+                "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if local else "u64",
                 "data": "synthetic", "config": config, "reads_per_sec": out["reads"] / t,
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": T, "kind": kind, "sample": sample},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
@@ -294,48 +303,66 @@ def main() -> None:
         dist.init_process_group("nccl", device_id=torch.device(dev))
     from speq_b200 import capi, engine
 
-    t_gen = time.perf_counter()
-    sh, refs, seq, qual = workload(args.config, reads, rank, dev)
-    R, L = seq.shape
-    t_gen = time.perf_counter() - t_gen
+    # ---- index (deterministic synthetic references; suffix sort etc. on the GPU) ----
     t0 = time.perf_counter()
+    refs = synth.make_refs(sh, synth.SEED0 + cfg_id, device=dev)
     cache = os.environ.get("SPEQ_BENCH_INDEX_CACHE")   # optional: reuse the (deterministic) synthetic index between runs
     cpath = Path(cache) / f"{args.config}.speqidx" if cache else None
     if cpath is not None and cpath.exists():
         idx = engine.Index.load(str(cpath))
     else:
-        idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V, device_sa=True)   # suffix sort etc. on the GPU
+        idx = engine.Index.from_scaffolds(synth.refs_to_ranks(refs), synth.group_scaffolds(sh), sh.V, device_sa=True)
         if cpath is not None and rank == 0:
             cpath.parent.mkdir(parents=True, exist_ok=True)
             idx.save(str(cpath))
     t_index = time.perf_counter() - t0
     idx.upload(local_rank)
-    log(f"[rank {rank}] workload {R} reads generated in {t_gen:.1f}s; index n={idx.n} built in {t_index:.1f}s, {idx.device_bytes/1e6:.1f} MB on device")
 
-    seq_f, qual_f = seq.view(-1), qual.view(-1)
-    offs = (torch.arange(R + 1, dtype=torch.int64) * L).pin_memory()
-    offs_np = offs.numpy().view(np.uint64)
-    seq_np, qual_np = seq_f.numpy(), qual_f.numpy()
-
-    # resident packed batch (host packer once, outside every timed region)
+    # ---- this rank's shard: chunks [c0, c1) of the global read set, packed on the device into one resident batch; the first
+    #      e2e_reads reads are also kept as ASCII in pinned host memory for the host-fed legs and the CPU sample ----
     t0 = time.perf_counter()
-    pb = engine.pack_reads(seq_np, qual_np, offs_np, phred_cutoff=30, threads=min(host_threads(), 64))
-    db = engine.DeviceBatch(local_rank, pb)
-    packed_bytes = pb.nbytes(False)
-    t_pack = time.perf_counter() - t0
-    del pb
+    c0, c1 = shard_chunks(n_chunks, rank, world)
+    starts = [c * CH for c in range(c0, c1 + 1)]
+    starts[-1] = min(starts[-1], R_total)
+    R = starts[-1] - starts[0]                                   # reads of this rank
+    E = 0 if args.no_e2e and args.no_cpu else min(R, args.e2e_reads)
+    L = sh.L
+    db = engine.ResidentBatch(local_rank, torch.full((R,), L, dtype=torch.int64, device=dev), with_qual=local)
+    seq_h = torch.empty((E, L), dtype=torch.uint8, pin_memory=True) if E else None
+    qual_h = torch.empty((E, L), dtype=torch.uint8, pin_memory=True) if E else None
+    for c in range(c0, c1):
+        n = min(R_total, (c + 1) * CH) - c * CH
+        a, b = gen_chunk(sh, cfg_id, refs, c, n, local)
+        r0 = c * CH - starts[0]
+        offs = torch.arange(n + 1, dtype=torch.int64, device=dev) * L
+        db.pack(r0, a.view(-1), b.view(-1), offs, phred_cutoff=cutoff)
+        if r0 < E:
+            m = min(n, E - r0)
+            seq_h[r0:r0 + m].copy_(a[:m])
+            qual_h[r0:r0 + m].copy_(b[:m])
+        del a, b, offs
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    t_gen = time.perf_counter() - t0
+    packed_bytes = db.nbytes()
+    log(f"[rank {rank}] index n={idx.n} in {t_index:.1f}s ({idx.device_bytes/1e6:.0f} MB on device); {R} reads generated + packed on "
+        f"the device in {t_gen:.1f}s ({packed_bytes/1e9:.2f} GB resident), {E} of them pinned on the host")
 
     stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream: the scan handle launches on it and the events time it
     torch.cuda.set_stream(stream)
     algo_req = {"rolling": capi.ALGO_ROLLING, "direct": capi.ALGO_DIRECT, "ktable": capi.ALGO_KTABLE, "kpair": capi.ALGO_KPAIR,
                 "auto": capi.ALGO_AUTO}[args.algorithm]
+    mode = capi.MODE_LOCAL if local else capi.MODE_GLOBAL
     t0 = time.perf_counter()
-    scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=algo_req, device=local_rank, stream=stream.cuda_stream)
-    algo = scan.info()["algorithm"]           # what AUTO resolved to
-    config["algorithm"] = {capi.ALGO_ROLLING: "rolling", capi.ALGO_DIRECT: "direct", capi.ALGO_KTABLE: "ktable",
-                           capi.ALGO_KPAIR: "kpair"}[algo] + (" (auto)" if args.algorithm == "auto" else "")
+    # what `speq scan` opens: multiplicities recorded for the refinement (speq_b200/host/speq.cpp)
+    scan = engine.Scan(idx, k=k, phred_cutoff=cutoff, mode=mode, record=algo_req != capi.ALGO_DIRECT, algorithm=algo_req, device=local_rank,
+                       stream=stream.cuda_stream)
     torch.cuda.synchronize()
     t_scan_open = time.perf_counter() - t0     # per-(index, k) specialisation: rank blocks or the k-mer table
+    info = scan.info()
+    algo = info["algorithm"]                   # what AUTO resolved to
+    algo_name = {capi.ALGO_ROLLING: "rolling", capi.ALGO_DIRECT: "direct", capi.ALGO_KTABLE: "ktable", capi.ALGO_KPAIR: "kpair"}[algo]
+    table = algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR)
     V = sh.V
 
     def barrier():
@@ -344,31 +371,43 @@ def main() -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # N > 1: the counters are summed across ranks where they live -- one NCCL all-reduce in place on the scan's stream behind
-    # the last kernel -- so a step has a single host sync (finish), which then returns the global tallies
-    cnt_i64 = scan.device_counters()[0] if world > 1 else None
-
-    def finish_global():
-        if world > 1:
-            dist.all_reduce(cnt_i64)
-        r = scan.finish()
+    def tall_of(r):
         return np.concatenate([r.unique, np.array([r.total_kmers, r.ambiguous, r.lookups, r.reads], np.uint64)]).astype(np.int64)
 
-    def step_resident():
-        scan.reset()
-        scan.submit_device(db)
-        return finish_global()
+    def make_step(sc):
+        # N > 1: the counters are summed across ranks where they live -- one NCCL all-reduce in place on the scan's stream
+        # behind the last kernel -- so a step has a single host sync (finish), which then returns the global tallies
+        ci, cf = sc.device_counters() if world > 1 else (None, None)
 
-    def step_e2e():
-        scan.reset()
-        for s in range(0, R, args.batch_reads):
-            e = min(R, s + args.batch_reads)
-            scan.submit_raw(seq_np, qual_np, offs_np[s:e + 1], e - s)
-        return finish_global()
+        def finish_global():
+            if world > 1:
+                dist.all_reduce(ci)
+                if local:
+                    dist.all_reduce(cf)
+            r = sc.finish()
+            return tall_of(r), r
+
+        def step_resident():
+            sc.reset()
+            sc.submit_device(db)
+            return finish_global()
+
+        def step_e2e():
+            sc.reset()
+            for s in range(0, E, args.batch_reads):
+                e = min(E, s + args.batch_reads)
+                sc.submit_raw(seq_np, qual_np, offs_np[s:e + 1], e - s)
+            return finish_global()
+        return step_resident, step_e2e
+
+    if E:
+        seq_np, qual_np = seq_h.view(-1).numpy(), qual_h.view(-1).numpy()
+        offs_np = (torch.arange(E + 1, dtype=torch.int64) * L).pin_memory().numpy().view(np.uint64)
+    step_resident, step_e2e = make_step(scan)
 
     # ---- value: resident inputs, CUDA events ----
     for _ in range(args.warmup):
-        tall = step_resident()
+        tall, res = step_resident()
     barrier()
     clocks = ClockSampler(local_rank)
     tc0 = time.perf_counter()
@@ -376,7 +415,7 @@ def main() -> None:
     ev0.record(stream)
     launches = 0
     for _ in range(args.steps):
-        tall = step_resident()
+        tall, res = step_resident()
         launches += 1
     ev1.record(stream)
     barrier()
@@ -389,175 +428,227 @@ def main() -> None:
     ms_total = float(tms.item())
     lookups_step = int(tall[V + 2])          # all ranks
     reads_step = int(tall[V + 3])
+    assert reads_step == R_total and lookups_step == R_total * wpr, (reads_step, lookups_step)
     value = lookups_step * args.steps / (ms_total * 1e-3)
+    clocks_all = [clk]
+    if world > 1:
+        clocks_all = [None] * world
+        dist.all_gather_object(clocks_all, clk)
+
+    # ---- the all-reduced tallies are the sum of the ranks' own tallies (checked outside the timed region) ----
+    allreduce_check = None
+    if world > 1:
+        scan.reset(); scan.submit_device(db)
+        own = tall_of(scan.finish())
+        parts = [None] * world
+        dist.all_gather_object(parts, own.tolist())
+        ok = bool(np.array_equal(np.sum(np.array(parts, dtype=np.int64), axis=0), tall))
+        assert ok, "all-reduced tallies differ from the sum of the per-rank tallies"
+        allreduce_check = f"all-reduced unique[V], total, ambiguous, lookups, reads == sum over the {world} ranks' own tallies"
 
     # ---- kernel-only time of the dominant kernel (same stream, no host work between launches) ----
-    scan.reset()
-    barrier()
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k0.record(stream)
-    for _ in range(args.steps):
-        scan.submit_device(db)
-    k1.record(stream)
-    torch.cuda.synchronize()
-    kern_ms = k0.elapsed_time(k1) / args.steps
-    scan.finish()
-
-    # ---- the same resident step with record_multiplicity = 1 (what `speq scan` runs: per-k-mer counts for the refinement) ----
-    rec = None
-    if rank == 0 and algo != capi.ALGO_DIRECT:
-        rscan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, record=True, algorithm=algo_req, device=local_rank,
-                            stream=stream.cuda_stream)
-        for _ in range(2):
-            rscan.reset(); rscan.submit_device(db)
-        torch.cuda.synchronize()
-        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        rscan.reset()
-        r0.record(stream)
+    def kernel_ms(sc):
+        sc.reset()
+        barrier()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k0.record(stream)
         for _ in range(args.steps):
-            rscan.submit_device(db)
-        r1.record(stream)
+            sc.submit_device(db)
+        k1.record(stream)
         torch.cuda.synchronize()
-        rr_ = rscan.finish()
-        rec_ms = r0.elapsed_time(r1) / args.steps
-        rec = {"kernel_ms": rec_ms, "value": rr_.lookups / args.steps / (rec_ms * 1e-3), "unit": UNIT,
-               "note": "one GPU, resident batch, scan kernel with one 8-byte atomic per hit window on top"}
-        rscan.close()
+        r = sc.finish()
+        return k0.elapsed_time(k1) / args.steps, r
+    kern_ms, rk = kernel_ms(scan)
+    probes_rank = rk.probes // args.steps      # table scans count the 32-byte probes they issue
+
+    # ---- the same resident step WITHOUT the recording (tallies only: enough for the closed-form percentages, not for the refinement)
+    tall_only = None
+    if rank == 0 and algo != capi.ALGO_DIRECT:
+        pscan = engine.Scan(idx, k=k, phred_cutoff=cutoff, mode=mode, record=False, algorithm=algo_req, device=local_rank, stream=stream.cuda_stream)
+        for _ in range(2):
+            pscan.reset(); pscan.submit_device(db)
+        torch.cuda.synchronize()
+        p_ms, pr_ = kernel_ms(pscan)
+        assert np.array_equal(pr_.unique, rk.unique) and pr_.total_kmers == rk.total_kmers
+        tall_only = {"kernel_ms": p_ms, "value": R * wpr / (p_ms * 1e-3), "unit": UNIT, "record_over_tallies_only": p_ms / kern_ms,
+                     "note": "rank 0's shard, resident batch, scan kernel without the per-k-mer multiplicity recording"}
+        pscan.close()
 
     # ---- cross-check outside every timed region: the k-mer table scan must reproduce the rolling FM search bit for bit
     cross = None
-    if algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR):
-        ref_scan = engine.Scan(idx, k=sh.k, phred_cutoff=30, mode=capi.MODE_GLOBAL, algorithm=capi.ALGO_ROLLING, device=local_rank,
-                               stream=stream.cuda_stream)
-        ref_scan.submit_device(db)
+    if table:
+        ref_scan = engine.Scan(idx, k=k, phred_cutoff=cutoff, mode=mode, algorithm=capi.ALGO_ROLLING, device=local_rank, stream=stream.cuda_stream)
+        sub = min(R, 25_000_000)
+        subv = capi.Batch(db.s.bases, db.s.inv, db.s.qual, db.s.grp_off, db.s.len, sub, int(db.grp_off[sub].item()))
+
+        class _Sub:
+            s = subv
+        ref_scan.submit_device(_Sub)
         rr = ref_scan.finish()
-        scan.reset(); scan.submit_device(db); rm = scan.finish()
-        assert np.array_equal(rr.unique, rm.unique) and rr.total_kmers == rm.total_kmers and rr.ambiguous == rm.ambiguous, \
-            "k-mer table tallies differ from the rolling FM search"
-        cross = "table-scan tallies == rolling FM-search tallies on this rank's reads (unique[V], total, ambiguous)"
-        probes_rank = rm.probes
+        scan.reset(); scan.submit_device(_Sub); rm = scan.finish()
+        same = np.array_equal(rr.unique, rm.unique) if not local else bool(np.all(np.abs(rr.unique_w - rm.unique_w) <= 1e-12 * np.abs(rr.unique_w)))
+        assert same and rr.total_kmers == rm.total_kmers and rr.ambiguous == rm.ambiguous, "k-mer table tallies differ from the rolling FM search"
+        cross = f"table-scan tallies == rolling FM-search tallies on the first {sub} reads of this rank (unique[V], total, ambiguous)"
         ref_scan.close()
 
     # ---- e2e: pinned host buffers through the C ABI ----
-    e2e = None
-    if not args.no_e2e:
+    e2e = e2e_roof = None
+    if not args.no_e2e and E:
         for _ in range(min(args.warmup, 3)):
-            tall_e = step_e2e()
+            tall_e, _ = step_e2e()
         barrier()
         t0 = time.perf_counter()
-        l0 = 0
         for _ in range(args.steps):
-            tall_e = step_e2e()
+            tall_e, _ = step_e2e()
         barrier()
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-        assert np.array_equal(tall_e[:V + 2], tall[:V + 2]), "e2e tallies differ from the resident path"
-        nb = (R + args.batch_reads - 1) // args.batch_reads
-        h2d = int(seq_np.nbytes + qual_np.nbytes + 8 * (R + nb))
+        nb = (E + args.batch_reads - 1) // args.batch_reads
+        h2d = int(seq_np.nbytes + qual_np.nbytes + 8 * (E + nb))
+        if E == R:
+            assert np.array_equal(tall_e[:V + 2], tall[:V + 2]) or local, "e2e tallies differ from the resident path"
         e2e = {"value": int(tall_e[V + 2]) * args.steps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": (8 * V + 8 * 8 + 8) * world, "ms_per_step": dt * 1e3 / args.steps,
-               "reads_per_sec": int(tall_e[V + 3]) * args.steps / dt, "input": "pinned host ASCII reads + phred chars; device packer",
+               "reads_per_sec": int(tall_e[V + 3]) * args.steps / dt, "reads_per_step": int(tall_e[V + 3]),
+               "input": f"pinned host ASCII reads + phred chars (the first {E} reads of every rank's shard), {args.batch_reads}-read submits; "
+                        "device packer; record_multiplicity = 1",
                "launches_per_step": 2 * nb * world}
+        # the ceiling of that leg: the same bytes in the same pieces as plain cudaMemcpyAsync from the same pinned buffers on all
+        # ranks at once (no kernels) -- tells a box / link limit from a staging limit
+        dbuf = torch.empty(2 * args.batch_reads * L, dtype=torch.uint8, device=dev)
+        cs = torch.cuda.Stream(device=dev)
 
-    # ---- e2e_packed: what the streaming ingest hands over (2-bit packed batches in pinned host buffers, speqg_scan_submit_packed);
-    #      the host packer runs outside the timed region, the H2D copy of the packed batch and the D2H of the tallies inside
-    e2e_packed = None
-    if not args.no_e2e:
-        nbp = (R + args.batch_reads - 1) // args.batch_reads
-        pbs = []
-        for s0 in range(0, R, args.batch_reads):
-            e0 = min(R, s0 + args.batch_reads)
-            o = offs_np[s0:e0 + 1] - offs_np[s0]
-            pbs.append(engine.pack_reads(seq_np[s0 * L:e0 * L], qual_np[s0 * L:e0 * L], o, phred_cutoff=30,
-                                         threads=min(host_threads(), 64), pinned=True))
-
-        def step_packed():
-            scan.reset()
-            for pb_ in pbs:
-                scan.submit_packed(pb_)
-            return finish_global()
-        for _ in range(min(args.warmup, 3)):
-            tall_p = step_packed()
+        def copy_pass():
+            with torch.cuda.stream(cs):
+                for s in range(0, E, args.batch_reads):
+                    e = min(E, s + args.batch_reads)
+                    nbts = (e - s) * L
+                    dbuf[:nbts].copy_(seq_h.view(-1)[s * L:e * L], non_blocking=True)
+                    dbuf[nbts:2 * nbts].copy_(qual_h.view(-1)[s * L:e * L], non_blocking=True)
+            cs.synchronize()
+        copy_pass()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            tall_p = step_packed()
+            copy_pass()
         barrier()
-        dtp = time.perf_counter() - t0
-        tt = torch.tensor([dtp], dtype=torch.float64, device=dev)
+        dtc = time.perf_counter() - t0
+        tt = torch.tensor([dtc], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dtp = float(tt.item())
-        assert np.array_equal(tall_p[:V + 2], tall[:V + 2]), "packed-host tallies differ from the resident path"
-        e2e_packed = {"value": int(tall_p[V + 2]) * args.steps / dtp, "unit": UNIT, "h2d_bytes_per_step": sum(b_.nbytes(False) for b_ in pbs) * world,
-                      "d2h_bytes_per_step": (8 * V + 8 * 8 + 8) * world, "ms_per_step": dtp * 1e3 / args.steps,
-                      "input": "pinned host 2-bit packed batches (host packer outside the timed region)", "launches_per_step": nbp * world}
-        del pbs
+        dtc = float(tt.item())
+        gbs = 2.0 * E * L * world * args.steps / dtc / 1e9
+        e2e_roof = {"h2d_GBps_aggregate": gbs, "h2d_GBps_per_gpu": gbs / world, "value_at_that_rate": E * wpr * world * args.steps / dtc, "unit": UNIT,
+                    "frac": e2e["value"] / (E * wpr * world * args.steps / dtc),
+                    "how": "plain cudaMemcpyAsync of the same pinned bytes in the same pieces, all ranks at once, no kernels"}
+        del dbuf
 
-    # ---- roofline: reference-semantics work counters (direct kernel, outside every timed region) ----
+    # ---- roofline ----
     roof = None
     if rank == 0:
-        st = scan.stats(db)
-        input_bytes = R * L // 2   # 2 bit base + 1 bit N + 1 bit q-pass per base
-        alg = 64 * (st["steps_executed"] - st["lookups"]) + 32 * st["occ_sectors"] + input_bytes
-        peak, how = measured_peak()
-        ach = alg / (kern_ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                "kernel": {capi.ALGO_ROLLING: "scan32_kernel<0>", capi.ALGO_KTABLE: "scanh_kernel<0>",
-                           capi.ALGO_KPAIR: "scanp_kernel<0>"}.get(algo, "scan_direct_kernel<0>"),
-                "kernel_ms": kern_ms,
-                "algorithmic_bytes_per_launch": alg, "peak_source": how,
-                "work": {"steps_executed": st["steps_executed"], "lookups": st["lookups"], "kmers_hit": st["kmers_hit"],
-                         "occ": st["occ"], "occ_sectors": st["occ_sectors"], "input_bytes": input_bytes},
-                "note": "algorithmic bytes follow the reference's per-window search (k steps from the root); the rolling kernel "
-                        "shares search state between overlapping windows and the k-mer table kernel memoises the search, so their "
-                        f"real traffic is lower (own_sectors); index footprint {idx.device_bytes/1e6:.0f} MB"}
+        sb, keys = info["structure_bytes"], info["keys"]
+        l2_bytes = torch.cuda.get_device_properties(local_rank).L2_cache_size
+        sectors = probes_rank if table else 2 * R * L                       # the kernel's own random sectors per launch
+        own_bytes = 32 * sectors + packed_bytes
+        ach = 32.0 * sectors / (kern_ms * 1e-3) / 1e9
+        peak_sec = None
+        if not args.no_probe:
+            try:
+                peak_sec = engine.probe_random_sectors(local_rank, max(sb, 1 << 20))
+            except Exception as ex:
+                log("probe failed:", ex)
+        hbm_peak, hbm_how = measured_peak()
+        kname = {capi.ALGO_ROLLING: "scan32_kernel", capi.ALGO_KTABLE: "scanh_kernel", capi.ALGO_KPAIR: "scanp_kernel"}.get(algo, "scan_direct_kernel")
+        kname += "<%s>" % ("|".join(x for x, on in (("M_LOCAL", local), ("M_RECORD", True)) if on) or "0")
+        roof = {"bound": "l2_random_sector" if sb <= l2_bytes * 3 // 4 else "hbm_random_sector",
+                "achieved": ach, "peak": None if peak_sec is None else 32.0 * peak_sec, "unit": "GB/s",
+                "frac": None if peak_sec is None else ach / (32.0 * peak_sec), "traffic": None,
+                "kernel": kname, "kernel_ms": kern_ms, "sectors_per_launch": sectors,
+                "achieved_Gsectors_per_s": sectors / (kern_ms * 1e-3) / 1e9, "peak_Gsectors_per_s": peak_sec,
+                "peak_source": "speqg_probe_random_sectors in this process: independent random 32-byte loads over a table of the probed "
+                               f"structure's size ({sb/1e6:.0f} MB), best of 4 launch shapes",
+                "structure_bytes": sb, "keys": keys, "l2_bytes": l2_bytes,
+                "algorithmic_bytes_per_launch": own_bytes,
+                "algorithmic_bytes_note": "32 B per table probe (KTABLE / KPAIR) or 2 x 32 B per read base (rolling) + the packed input stream",
+                "own_bytes_GBps": own_bytes / (kern_ms * 1e-3) / 1e9}
+        if sb > l2_bytes * 3 // 4:
+            roof["hbm_frac"] = own_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak
+            roof["hbm_peak"] = hbm_peak
+            roof["hbm_peak_source"] = hbm_how
         # dram__bytes_read + write of this kernel from the committed `ncu --set full` capture, scaled from the captured launch to
         # this launch by the number of reads (per-read traffic does not depend on the launch size: input stream + table misses)
         try:
-            tj = json.loads((ROOT / "profiles" / "r1_traffic.json").read_text()).get(f"{args.config}:{roof['kernel']}")
-            if tj:
-                roof["traffic"] = tj["dram_bytes_per_read"] * R
-                roof["traffic_source"] = tj["source"]
+            for name in ("r2_traffic.json", "r1_traffic.json"):
+                tp = ROOT / "profiles" / name
+                if not tp.exists():
+                    continue
+                tj = json.loads(tp.read_text()).get(f"{args.config}:{kname}") or json.loads(tp.read_text()).get(f"{args.config}:{kname.split('<')[0]}<0>")
+                if tj:
+                    roof["traffic"] = tj["dram_bytes_per_read"] * R
+                    roof["traffic_source"] = tj["source"]
+                    break
         except Exception:
             pass
-        # what the kernel itself must move: one 32-byte sector per valid window (ktable) / two per read base (rolling), plus
-        # the packed input stream; against the HBM peak when the structure misses L2, else informative only
-        table = algo in (capi.ALGO_KTABLE, capi.ALGO_KPAIR)
-        own = (32 * probes_rank if table else 64 * R * L) + packed_bytes
-        roof["own_sectors"] = {"bytes_per_launch": own, "GB/s": own / (kern_ms * 1e-3) / 1e9, "frac_of_hbm_peak": own / (kern_ms * 1e-3) / 1e9 / peak}
-        # the roofline this access pattern really has: independent random 32-byte sectors.  Peaks measured on this pool's B200
-        # by profiles/gather_probe.cu (profiles/r1_gather_probe.txt), chosen by the size of the structure the kernel probes.
-        info = scan.info()
-        sb = info["structure_bytes"]
-        ra_peak, ra_src = next((p_, s_) for lim, p_, s_ in RANDOM_SECTOR_PEAKS if sb <= lim)
-        sectors = probes_rank if table else 2 * R * L     # table scans count the probes they issue
-        roof["random_access"] = {"sectors_per_launch": sectors, "achieved_Gsectors_per_s": sectors / (kern_ms * 1e-3) / 1e9,
-                                 "peak_Gsectors_per_s": ra_peak, "frac": sectors / (kern_ms * 1e-3) / 1e9 / ra_peak,
-                                 "structure_bytes": sb, "keys": info["keys"], "peak_source": ra_src}
-
-    # ---- cpu baseline (rank 0, N = 1 only) ----
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+        # SURVEY.md 8d's figure, kept under its own name: the reference's per-window search (k steps from the root + locate)
+        # counted with reference semantics on a slice by scan_direct_kernel<1>, scaled to the launch
         try:
-            v, sample, kind, T, t, _ = cpu_arm(sh, refs.cpu(), seq, qual, steps=1, warmup=0, target_s=args.cpu_seconds,
-                                               max_sample=min(R, 2_000_000))
+            sub = min(R, 2_000_000)
+            subv = capi.Batch(db.s.bases, db.s.inv, db.s.qual, db.s.grp_off, db.s.len, sub, int(db.grp_off[sub].item()))
+
+            class _Sub2:
+                s = subv
+            st = scan.stats(_Sub2)
+            alg = (64 * (st["steps_executed"] - st["lookups"]) + 32 * st["occ_sectors"] + sub * L // 2) * (R / sub)
+            roof["reference_work_rate"] = {"bytes_per_launch": alg, "GB/s": alg / (kern_ms * 1e-3) / 1e9,
+                                           "note": "SURVEY.md 8d: 64 B per executed backward step after the first, 32 B per 32 occurrences "
+                                                   "located, 0.5 B per base -- the work the reference does for the same windows; the table "
+                                                   "kernel memoises it, so this is a rate of reference work retired, not a roofline fraction",
+                                           "steps_per_lookup": st["steps_executed"] / max(1, st["lookups"]), "occ_per_hit": st["occ"] / max(1, st["kmers_hit"]),
+                                           "counted_on_reads": sub}
+        except Exception as ex:
+            log("stats failed:", ex)
+
+    # ---- cpu baseline + parity against it (rank 0, N = 1 only) ----
+    cpu = parity = None
+    if rank == 0 and world == 1 and not args.no_cpu and E:
+        try:
+            v, sample, kind, T, t, out, n = cpu_arm(sh, refs.cpu(), seq_h.numpy(), qual_h.numpy(), k=k, accuracy=accuracy, cutoff=cutoff,
+                                                    steps=1, warmup=0, target_s=args.cpu_seconds)
             cpu = {"value": v, "unit": UNIT, "cores": T, "kind": kind, "sample": sample}
+            # the oracle's tallies on its sample == the GPU's on the same n reads, default algorithm, through the raw-read C ABI
+            pscan = engine.Scan(idx, k=k, phred_cutoff=cutoff, mode=mode, record=True, algorithm=algo_req, device=local_rank, stream=stream.cuda_stream)
+            pscan.submit_raw(seq_np, qual_np, offs_np[:n + 1], n)
+            g = pscan.finish()
+            pscan.close()
+            if local:
+                okp = bool(np.all(np.abs(g.unique_w - np.array(out["unique_w"])) <= 1e-12 * np.abs(g.unique_w)))
+            else:
+                okp = [int(x) for x in g.unique] == out["unique"]
+            okp = okp and (g.total_kmers, g.ambiguous, g.lookups) == (out["total_kmers"], out["ambiguous"], out["lookups"])
+            parity = {"vs": "oracle/_ref" if kind == "reference" else "oracle (port)", "reads": n, "ok": bool(okp),
+                      "compared": ("unique_w[V] (<= 1e-12 rel)" if local else "unique[V]") + ", total_kmers, ambiguous, lookups"}
+            assert okp, ("GPU tallies differ from the oracle's on the CPU-timed sample", [int(x) for x in g.unique], out["unique"])
+        except AssertionError:
+            raise
         except Exception as ex:   # the checker must never take the bench line down
             cpu = {"value": None, "unit": UNIT, "cores": host_threads(), "kind": "port", "sample": f"failed: {ex}"}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "u64", "data": "synthetic", "config": dict(config, l2="inputs larger than L2: %d MB of packed reads per step" % (packed_bytes >> 20)),
+                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f64" if local else "u64", "data": "synthetic", "config": config,
                 "reads_per_sec": reads_step * args.steps / (ms_total * 1e-3),
-                "clocks": clk, "e2e": e2e, "e2e_packed": e2e_packed, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu, "record_mode": rec,
+                "value_is": "scan with record_multiplicity = 1 (what `speq scan` runs), resident packed reads",
+                "resolved_algorithm": algo_name, "clocks": clk, "clocks_per_rank": clocks_all if world > 1 else None,
+                "e2e": e2e, "e2e_roofline": e2e_roof, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu, "parity": parity,
+                "tallies_only": tall_only,
                 "tallies": {"unique": [int(x) for x in tall[:V]], "total_kmers": int(tall[V]), "ambiguous": int(tall[V + 1])},
-                "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "host_pack_s": t_pack, "scan_open_s": t_scan_open, "numa": numa},
-                "cross_check": cross}
+                "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "generate_and_pack_s": t_gen,
+                          "scan_open_s": t_scan_open, "reads_this_rank": R, "packed_bytes_this_rank": packed_bytes, "numa": numa},
+                "cross_check": cross, "allreduce_check": allreduce_check}
         emit(line)
     scan.close()
     db.close()

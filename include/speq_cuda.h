@@ -81,6 +81,32 @@ int speqg_index_upload(speqg_index * idx, int device);
 void speqg_index_free(speqg_index * idx);
 
 /* ------------------------------------------------------------------------------------------------------------------
+ * Index files written by the REFERENCE (`speq index` of ibharvey/speq): read-only import.
+ * The file is a cereal::BinaryOutputArchive of (reference FASTA path, two file times, group_names, group_scaffolds,
+ * group_counts, seqan3::fm_index) -- src/fm_indexer.cpp:39-50, loaded by src/fm_scanner.cpp:44-58; the fm_index starts with the
+ * sdsl csa_wt, whose wavelet tree is the BWT of the indexed text (S3/include/seqan3/search/fm_index/fm_index.hpp:486-514,
+ * SDSL/csa_wt.hpp:396-404, SDSL/wt_pc.hpp:654-663, SDSL/int_vector.hpp:1843-1849).  speqg_refidx_open parses the metadata,
+ * decodes the BWT from the tree, inverts it and splits the text at the delimiters: the texts the reference indexed
+ * (scaffold j, reverse complement of scaffold j, ...; src/fm_indexer.cpp:25-33) as dna5 ranks.  speqg_refidx_build_index
+ * builds this library's index over them -- what speqg_index_build would produce from the original FASTA.
+ * SPEQG_EIO when the file is not such an archive.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct speqg_refidx speqg_refidx;
+int speqg_refidx_open(const char * path, speqg_refidx ** out);
+const char * speqg_refidx_reference_path(const speqg_refidx * r);             /* the archived in_file_references */
+int64_t speqg_refidx_file_time(const speqg_refidx * r, int which);           /* 0: FASTA, 1: groups file (file_clock ticks) */
+uint64_t speqg_refidx_size(const speqg_refidx * r);                          /* seqan3 fm_index::size() */
+uint32_t speqg_refidx_n_groups(const speqg_refidx * r);
+const char * speqg_refidx_group_name(const speqg_refidx * r, uint32_t g);
+int32_t speqg_refidx_group_count(const speqg_refidx * r, uint32_t g);
+uint32_t speqg_refidx_n_scaffolds(const speqg_refidx * r);                   /* length of group_scaffolds */
+int32_t speqg_refidx_group_of_scaffold(const speqg_refidx * r, uint32_t j);
+uint32_t speqg_refidx_n_texts(const speqg_refidx * r);
+int speqg_refidx_text(const speqg_refidx * r, uint32_t i, const uint8_t ** ranks, uint64_t * len);   /* owned by r */
+int speqg_refidx_build_index(const speqg_refidx * r, uint32_t flags, speqg_index ** out);             /* flags: SPEQG_BUILD_* */
+void speqg_refidx_close(speqg_refidx * r);
+
+/* ------------------------------------------------------------------------------------------------------------------
  * Packed read batches.  Replaces what seqan3::sequence_file_input hands the reference's workers (vector<dna5> +
  * vector<phred42> per record, src/fm_scanner.cpp:198-199) by a 2-bit packed, length-prefixed batch.
  * Read i owns 32-base groups [grp_off[i], grp_off[i+1]):

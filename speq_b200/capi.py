@@ -60,6 +60,19 @@ SIGNATURES = {
     "speqg_index_load": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
     "speqg_index_save_at": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64]),
     "speqg_index_load_at": (C.c_int, [C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "speqg_refidx_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "speqg_refidx_reference_path": (C.c_char_p, [C.c_void_p]),
+    "speqg_refidx_file_time": (C.c_int64, [C.c_void_p, C.c_int]),
+    "speqg_refidx_size": (C.c_uint64, [C.c_void_p]),
+    "speqg_refidx_n_groups": (C.c_uint32, [C.c_void_p]),
+    "speqg_refidx_group_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
+    "speqg_refidx_group_count": (C.c_int32, [C.c_void_p, C.c_uint32]),
+    "speqg_refidx_n_scaffolds": (C.c_uint32, [C.c_void_p]),
+    "speqg_refidx_group_of_scaffold": (C.c_int32, [C.c_void_p, C.c_uint32]),
+    "speqg_refidx_n_texts": (C.c_uint32, [C.c_void_p]),
+    "speqg_refidx_text": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), u64p]),
+    "speqg_refidx_build_index": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "speqg_refidx_close": (None, [C.c_void_p]),
     "speqg_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "speqg_host_free": (None, [C.c_void_p]),
     "speqg_scan_wait_copies": (C.c_int, [C.c_void_p]),

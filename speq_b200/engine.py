@@ -111,6 +111,47 @@ class Index:
             pass
 
 
+class ReferenceIndexFile:
+    """An .idx written by the reference's `speq index` (cereal archive + sdsl csa_wt): metadata and the indexed texts, decoded
+    from the wavelet tree (speqg_refidx_*)."""
+
+    def __init__(self, path: str):
+        self.h = C.c_void_p()
+        capi.check(capi.lib().speqg_refidx_open(os.fsencode(path), C.byref(self.h)))
+        l = capi.lib()
+        self.reference_path = l.speqg_refidx_reference_path(self.h).decode()
+        self.file_times = (int(l.speqg_refidx_file_time(self.h, 0)), int(l.speqg_refidx_file_time(self.h, 1)))
+        self.n = int(l.speqg_refidx_size(self.h))
+        V = int(l.speqg_refidx_n_groups(self.h))
+        self.group_names = [l.speqg_refidx_group_name(self.h, g).decode() for g in range(V)]
+        self.group_counts = [int(l.speqg_refidx_group_count(self.h, g)) for g in range(V)]
+        self.group_scaffolds = [int(l.speqg_refidx_group_of_scaffold(self.h, j)) for j in range(int(l.speqg_refidx_n_scaffolds(self.h)))]
+
+    def texts(self) -> list[np.ndarray]:
+        out = []
+        for i in range(int(capi.lib().speqg_refidx_n_texts(self.h))):
+            p, n = C.c_void_p(), C.c_uint64()
+            capi.check(capi.lib().speqg_refidx_text(self.h, i, C.byref(p), C.byref(n)))
+            out.append(np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,)).copy() if n.value else np.zeros(0, np.uint8))
+        return out
+
+    def build_index(self, device_sa: bool = False) -> Index:
+        out = C.c_void_p()
+        capi.check(capi.lib().speqg_refidx_build_index(self.h, capi.BUILD_DEVICE_SA if device_sa else 0, C.byref(out)))
+        return Index(out.value)
+
+    def close(self) -> None:
+        if self.h:
+            capi.lib().speqg_refidx_close(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 @dataclass
 class PackedBatch:
     """Host-side packed batch (numpy arrays, or pinned torch tensors via from_arrays)."""
@@ -184,6 +225,52 @@ class DeviceBatch:
             self.close()
         except Exception:
             pass
+
+
+class ResidentBatch:
+    """A packed batch in device memory whose arrays are torch tensors, filled range by range by the device packer
+    (speqg_pack_device) from raw reads that already live on the device -- how bench.py builds a resident batch of 2e8 reads
+    without staging them through the host.  grp_off (first 32-base group of every read) is the running sum of ceil(len / 32)."""
+
+    def __init__(self, device: int, lens, with_qual: bool = False):
+        import torch
+        dev = torch.device("cuda", device)
+        self.device = device
+        lens = torch.as_tensor(lens, device=dev, dtype=torch.int64)
+        self.n_reads = int(lens.numel())
+        self.grp_off = torch.zeros(self.n_reads + 1, dtype=torch.int64, device=dev)
+        torch.cumsum((lens + 31) >> 5, 0, out=self.grp_off[1:])
+        self.n_groups32 = int(self.grp_off[-1].item())
+        self.bases = torch.zeros(max(1, self.n_groups32), dtype=torch.int64, device=dev)
+        self.inv = torch.zeros(max(1, self.n_groups32), dtype=torch.int32, device=dev)
+        self.len = torch.zeros(max(1, self.n_reads), dtype=torch.int32, device=dev)
+        self.qual = torch.zeros(max(1, self.n_groups32 * 32), dtype=torch.uint8, device=dev) if with_qual else None
+        self.s = capi.Batch(self.bases.data_ptr(), self.inv.data_ptr(), self.qual.data_ptr() if with_qual else None,
+                            self.grp_off.data_ptr(), self.len.data_ptr(), self.n_reads, self.n_groups32)
+
+    def nbytes(self) -> int:
+        return self.n_groups32 * 12 + (self.n_reads + 1) * 8 + self.n_reads * 4 + (self.n_groups32 * 32 if self.qual is not None else 0)
+
+    def pack(self, r0: int, seq, qual, offsets, *, encoding: int = capi.ENC_ASCII, phred_cutoff: int = 30, n_only: bool = False) -> None:
+        """reads [r0, r0 + n) from device tensors: seq / qual flat uint8, offsets int64[n + 1] relative to seq."""
+        import torch
+        n = int(offsets.numel()) - 1
+        assert 0 <= r0 and r0 + n <= self.n_reads
+        st = capi.Batch(self.bases.data_ptr(), self.inv.data_ptr(), self.qual.data_ptr() if self.qual is not None else None,
+                        self.grp_off.data_ptr() + 8 * r0, self.len.data_ptr() + 4 * r0, n, self.n_groups32)
+        capi.check(capi.lib().speqg_pack_device(self.device, seq.data_ptr(), qual.data_ptr() if qual is not None else None,
+                                                offsets.data_ptr(), n, encoding, phred_cutoff, int(n_only), C.byref(st),
+                                                torch.cuda.current_stream(self.device).cuda_stream))
+
+    def close(self) -> None:
+        self.bases = self.inv = self.len = self.qual = self.grp_off = None
+
+
+def probe_random_sectors(device: int, table_bytes: int) -> float:
+    """Giga independent random 32-byte sector loads per second from a table of table_bytes (speqg_probe_random_sectors)."""
+    out = C.c_double()
+    capi.check(capi.lib().speqg_probe_random_sectors(device, int(table_bytes), C.byref(out)))
+    return float(out.value)
 
 
 @dataclass

@@ -51,7 +51,6 @@ int64_t mtime_of(fs::path const & p)
 
 // ---- .idx container: metadata the reference archives in front of the index (src/fm_indexer.cpp:39-50), then our payload
 const char kIdxMagic[8] = {'S', 'P', 'Q', 'I', 'D', 'X', '0', '2'};
-const char kDatMagic[8] = {'S', 'P', 'Q', 'D', 'A', 'T', '0', '1'};
 
 struct idx_meta
 {
@@ -60,6 +59,8 @@ struct idx_meta
     std::vector<std::string> group_names;
     std::vector<int> group_scaffolds, group_counts;
     uint64_t payload_offset = 0;
+    bool reference_format = false;   // the file is the reference's own cereal + sdsl archive (read through speqg_refidx_*)
+    std::shared_ptr<speqg_refidx> ref;   // ... and stays open (texts decoded once) until the index over them is built
 };
 
 void put_u64(std::ostream & os, uint64_t v) { os.write(reinterpret_cast<const char *>(&v), 8); }
@@ -120,9 +121,27 @@ idx_meta read_meta(fs::path const & p)
     if (!is) throw std::runtime_error("cannot open index file " + p.string());
     char mg[8];
     is.read(mg, 8);
-    if (!is || memcmp(mg, kIdxMagic, 8) != 0)
-        throw std::runtime_error(p.string() + " is not an index written by this build (the reference's cereal archive is not readable yet)");
     idx_meta m;
+    if (!is || memcmp(mg, kIdxMagic, 8) != 0)
+    {
+        // not this build's container: an index written by the reference's `speq index` (src/fm_indexer.cpp:39-50)?
+        is.close();
+        speqg_refidx * r = nullptr;
+        if (speqg_refidx_open(p.c_str(), &r) != SPEQG_OK)
+            throw std::runtime_error(p.string() + " is neither an index of this build nor one written by the reference: " + speqg_last_error());
+        m.scaffold_file = speqg_refidx_reference_path(r);
+        m.scaffold_time = speqg_refidx_file_time(r, 0);
+        m.group_time = speqg_refidx_file_time(r, 1);
+        for (uint32_t g = 0; g < speqg_refidx_n_groups(r); ++g)
+        {
+            m.group_names.push_back(speqg_refidx_group_name(r, g));
+            m.group_counts.push_back(speqg_refidx_group_count(r, g));
+        }
+        for (uint32_t j = 0; j < speqg_refidx_n_scaffolds(r); ++j) m.group_scaffolds.push_back(speqg_refidx_group_of_scaffold(r, j));
+        m.reference_format = true;
+        m.ref = std::shared_ptr<speqg_refidx>(r, speqg_refidx_close);
+        return m;
+    }
     m.scaffold_file = get_str(is);
     m.scaffold_time = static_cast<int64_t>(get_u64(is));
     m.group_time = static_cast<int64_t>(get_u64(is));
@@ -440,7 +459,16 @@ int do_scan(cmd_arguments & args)
     args.io_file_index.replace_extension(".idx");
     idx_meta meta = read_meta(args.io_file_index);
     index_handle idx;
-    ck(speqg_index_load_at(args.io_file_index.c_str(), meta.payload_offset, &idx.h), "speqg_index_load_at");
+    if (meta.reference_format)
+    {
+        // an index the reference built: its texts are decoded from the archived wavelet tree and indexed again here
+        int nd = 0;
+        if (speqg_device_count(&nd) != SPEQG_OK) nd = 0;
+        ck(speqg_refidx_build_index(meta.ref.get(), nd > 0 ? SPEQG_BUILD_DEVICE_SA : 0u, &idx.h), "speqg_refidx_build_index");
+        meta.ref.reset();
+    }
+    else
+        ck(speqg_index_load_at(args.io_file_index.c_str(), meta.payload_offset, &idx.h), "speqg_index_load_at");
     if (args.in_file_references != fs::path(meta.scaffold_file))                      // src/fm_scanner.cpp:60-72
     {
         if (fs::exists(meta.scaffold_file)) args.in_file_references = meta.scaffold_file;
@@ -461,15 +489,22 @@ int do_scan(cmd_arguments & args)
     double t_backcheck = 0;
     if (fs::exists(dat))
     {
+        // the reference's archive, byte for byte (src/fm_scanner.cpp:1561-1571: cereal binary of the .idx file time and two
+        // std::vector<std::size_t>): int64 tick count, then twice (u64 size, size x u64) -- files are interchangeable
         std::ifstream is(dat, std::ios::binary);
-        char mg[8];
-        is.read(mg, 8);
-        if (is && memcmp(mg, kDatMagic, 8) == 0 && static_cast<int64_t>(get_u64(is)) == idx_time && get_u64(is) == V)
+        try
         {
-            is.read(reinterpret_cast<char *>(unique_ref.data()), V * 8);
-            is.read(reinterpret_cast<char *>(total_ref.data()), V * 8);
-            have_dat = static_cast<bool>(is);
+            if (static_cast<int64_t>(get_u64(is)) == idx_time && get_u64(is) == V)
+            {
+                is.read(reinterpret_cast<char *>(unique_ref.data()), V * 8);
+                if (is && get_u64(is) == V)
+                {
+                    is.read(reinterpret_cast<char *>(total_ref.data()), V * 8);
+                    have_dat = static_cast<bool>(is);
+                }
+            }
         }
+        catch (std::exception const &) { have_dat = false; }      // truncated / foreign file: rebuilt below
     }
     if (!have_dat)
     {
@@ -477,10 +512,10 @@ int do_scan(cmd_arguments & args)
         ck(speqg_backcheck(idx.h, 0, args.kmer, unique_ref.data(), total_ref.data()), "speqg_backcheck");
         t_backcheck = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         std::ofstream os(dat, std::ios::binary | std::ios::trunc);
-        os.write(kDatMagic, 8);
         put_u64(os, static_cast<uint64_t>(idx_time));
         put_u64(os, V);
         os.write(reinterpret_cast<const char *>(unique_ref.data()), V * 8);
+        put_u64(os, V);
         os.write(reinterpret_cast<const char *>(total_ref.data()), V * 8);
         std::cerr << unique_ref << "\n";                                              // src/fm_scanner.cpp:1572-1573
         std::cerr << total_ref << "\n";

@@ -176,6 +176,34 @@ def test_speq_all_default_invocation(speq_bin, tmp_path, name):
     assert (tmp_path / "i_70mer.dat").exists()            # <stem>_<k>mer.dat with the default k (src/fm_scanner.cpp:81-82)
 
 
+@pytest.mark.gpu
+def test_speq_scan_on_reference_written_index(speq_bin, tmp_path):
+    """`speq scan -x` on an .idx the REFERENCE wrote (tests/golden/ref_global_single.idx: cereal + sdsl bytes, make_ref_idx.py):
+    the texts are decoded from the archived wavelet tree, and the scan reports the fixture's numbers.  The <stem>_<k>mer.dat it
+    writes has the reference's layout (src/fm_scanner.cpp:1561-1571): int64 index time, then two u64-length-prefixed u64 vectors."""
+    import shutil
+    import struct
+    fx = helpers.load_golden("global_single")
+    exp, runp = fx["expected"], fx["run"]
+    refs, groups, r1, _ = helpers.golden_files(tmp_path, fx)            # refs.fa must exist: the archive names it (src/fm_scanner.cpp:60-72)
+    shutil.copy(helpers.GOLDEN / "ref_global_single.idx", tmp_path / "fromref.idx")
+    r = run(speq_bin, "scan", "-1", r1, "-x", tmp_path / "fromref.idx", "-k", runp["k"], "--fixed-accuracy", runp["fixed_accuracy"],
+            "--json", tmp_path / "out.json", cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    out = json.loads((tmp_path / "out.json").read_text())
+    assert out["unique_ref"] == exp["unique_ref"] and out["total_ref"] == exp["total_ref"]
+    assert out["unique"] == exp["unique"] and out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"]
+    assert out["iterations"] == exp["iterations"] and helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
+    raw = (tmp_path / f"fromref_{runp['k']}mer.dat").read_bytes()
+    V = len(exp["unique_ref"])
+    assert len(raw) == 8 + 2 * (8 + 8 * V)
+    t, n1 = struct.unpack_from("<qQ", raw, 0)
+    assert n1 == V and list(struct.unpack_from(f"<{V}Q", raw, 16)) == exp["unique_ref"]
+    n2 = struct.unpack_from("<Q", raw, 16 + 8 * V)[0]
+    assert n2 == V and list(struct.unpack_from(f"<{V}Q", raw, 24 + 8 * V)) == exp["total_ref"]
+    assert t == os.stat(tmp_path / "fromref.idx").st_mtime_ns or t != 0
+
+
 def _write_fq(path, recs, newline="\n", trailing=True):
     txt = newline.join(newline.join(["@" + h, s, "+", q]) for h, s, q in recs)
     path.write_text(txt + (newline if trailing else ""), newline="")

@@ -240,3 +240,39 @@ def test_lane_arithmetic_low_complexity(lib, sim, seed):
         assert np.array_equal(ma, mb), k
         assert np.array_equal(c, b), k
         assert np.array_equal(mc, mb), k
+
+
+@pytest.mark.parametrize("fixture,golden", [("ref_global_single.idx", "global_single"), ("ref_refs_with_n.idx", "refs_with_n")])
+def test_reference_idx_reader(lib, tmp_path, fixture, golden):
+    """speqg_refidx_*: an .idx as the REFERENCE writes it (cereal archive of the metadata + the real sdsl csa_wt, generated by
+    tests/golden/make_ref_idx.py through oracle/_ref) -> metadata and the indexed texts, decoded from the wavelet tree.  The
+    texts must be scaffold j, reverse complement of scaffold j, ... of the FASTA the index was built from, and the index built
+    over them must be the one speqg_index_build makes from the FASTA (same saved bytes)."""
+    fx = helpers.load_golden(golden)
+    r = engine.ReferenceIndexFile(str(helpers.GOLDEN / fixture))
+    names, counts, gs = helpers.parse_groups(fx["groups_txt"])
+    assert r.reference_path == "refs.fa"
+    assert r.group_names == names and r.group_counts == counts and r.group_scaffolds == [int(g) for g in gs]
+    assert r.n == fx["expected"]["n"]
+    scaff = [engine.ascii_to_ranks(s) for s in helpers.parse_fasta(fx["refs_fa"])]
+    texts = r.texts()
+    assert len(texts) == 2 * len(scaff)
+    for j, s in enumerate(scaff):
+        assert np.array_equal(texts[2 * j], s)
+        assert np.array_equal(texts[2 * j + 1], engine.revcomp_ranks(s))
+    a = r.build_index()
+    b = engine.Index.from_scaffolds(scaff, gs, len(counts))
+    assert a.n == b.n == r.n and a.C == b.C
+    a.save(str(tmp_path / "a.idx")); b.save(str(tmp_path / "b.idx"))
+    assert (tmp_path / "a.idx").read_bytes() == (tmp_path / "b.idx").read_bytes()
+    a.close(); b.close(); r.close()
+
+
+def test_reference_idx_reader_rejects_other_files(lib, tmp_path):
+    (tmp_path / "x.idx").write_bytes(b"SPQIDX02" + bytes(200))
+    with pytest.raises(capi.SpeqError) as ei:
+        engine.ReferenceIndexFile(str(tmp_path / "x.idx"))
+    assert ei.value.code == capi.EIO
+    (tmp_path / "short.idx").write_bytes(b"\x05\x00\x00\x00\x00\x00\x00\x00abc")
+    with pytest.raises(capi.SpeqError):
+        engine.ReferenceIndexFile(str(tmp_path / "short.idx"))
