@@ -190,6 +190,22 @@ int speqg_scan_submit_packed(speqg_scan * scan, const speqg_batch * host_batch);
 /* host raw reads (ASCII or ranks): H2D copy of the bytes + device packer + kernel, asynchronous. */
 int speqg_scan_submit_raw(speqg_scan * scan, const uint8_t * seq, const uint8_t * qual, const uint64_t * offsets,
                           uint64_t n_reads, int encoding);
+/* Raw FASTQ bytes: a region of a (plain, uncompressed) FASTQ file that starts at a record start and ends behind a record,
+ * single-end.  H2D copy of the bytes, then the record grammar of seqan3 (S3/include/seqan3/io/sequence_file/format_fastq.hpp:
+ * 93-205) for the STRICT form -- four lines per record ('@' id, sequence, '+' line, |sequence| quality characters), LF or CRLF --
+ * runs as kernels: line starts, record checks, the packer reading sequence and quality where they lie, the scan.  Asynchronous;
+ * the host does nothing per record.  *region (may be NULL) = the number of this region within the scan, from 0.  A region that is
+ * not in the strict form (multi-line records, blank lines, blanks inside a sequence line, letters outside the IUPAC set, length
+ * mismatch) is NOT scanned: speqg_scan_fastq_rejected names it, and the caller reads that region again with the full grammar on
+ * the host and submits it with speqg_scan_submit_raw (tallies add up, the order of regions does not matter).
+ * *ticket (may be NULL): pass to speqg_scan_wait_ticket before `bytes` is overwritten. */
+int speqg_scan_submit_fastq(speqg_scan * scan, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket);
+/* wait for the host->device copy of ONE earlier submit_fastq (its host buffer may then be refilled; later copies and all kernels
+ * keep running) */
+int speqg_scan_wait_ticket(speqg_scan * scan, uint64_t ticket);
+/* regions submitted since open / reset that were not scanned because they are not strict 4-line FASTQ.  Syncs the scan.
+ * regions[i], i < min(*n_rejected, capacity). */
+int speqg_scan_fastq_rejected(speqg_scan * scan, uint64_t * regions, uint64_t capacity, uint64_t * n_rejected);
 /* batch whose arrays already live in device memory of the scan's device (pointers are device pointers). */
 int speqg_scan_submit_device(speqg_scan * scan, const speqg_batch * device_batch);
 int speqg_scan_sync(speqg_scan * scan);

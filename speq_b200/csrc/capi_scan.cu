@@ -49,17 +49,32 @@ struct Slot
     dev_buf<uint64_t> bases, grp_off, raw_off;
     dev_buf<uint32_t> inv, len;
     dev_buf<uint8_t> qual, raw_seq, raw_qual;
+    // FASTQ regions parsed on the device (speqg_scan_submit_fastq)
+    dev_buf<uint32_t> fq_chunk;                   // newlines per 4 KB chunk -> exclusive prefix sum
+    dev_buf<uint64_t> fq_lines, fq_soff, fq_qoff;
+    dev_buf<unsigned long long> fq_small;         // [0] newline count, [1] reads published for the scan kernel, [2] reject flag
+    unsigned long long * h_total = nullptr;       // pinned: the newline count, read by the host between the two phases
+    cudaEvent_t counted = nullptr;
+    uint64_t fq_bytes = 0, fq_region = 0;
+    bool fq_terminated = true;
     cudaEvent_t copied = nullptr, done = nullptr;
+    uint64_t ticket = 0;
     bool busy = false;
     void release()
     {
         bases.release(); grp_off.release(); raw_off.release(); inv.release(); len.release();
         qual.release(); raw_seq.release(); raw_qual.release();
+        fq_chunk.release(); fq_lines.release(); fq_soff.release(); fq_qoff.release(); fq_small.release();
+        if (h_total) cudaFreeHost(h_total);
+        h_total = nullptr;
+        if (counted) cudaEventDestroy(counted);
         if (copied) cudaEventDestroy(copied);
         if (done) cudaEventDestroy(done);
-        copied = done = nullptr;
+        copied = done = counted = nullptr;
     }
 };
+// regions of one scan whose irregularity can be reported (speqg_scan_fastq_rejected); further regions are refused
+constexpr uint32_t kMaxFastqRegions = 1u << 20;
 }   // namespace
 
 struct speqg_scan
@@ -111,10 +126,16 @@ struct speqg_scan
     Slot slots[kSlots];
     int next_slot = 0;
     uint64_t launches = 0;
+    uint64_t tickets = 0;                  // submits that copied host memory, numbered from 1
+    // FASTQ regions: the second phase of the last submitted region (lines, records, pack, scan) is issued by the next call
+    int fq_pending = -1;
+    uint64_t fq_regions = 0;
+    unsigned int * d_fq_flags = nullptr;   // [kMaxFastqRegions] 1 = the region was not in the strict form and was not scanned
 };
 
 namespace speqb
 {
+void fastq_phase2(speqg_scan * s);   // the deferred second phase of the last FASTQ region (below)
 struct scan_refine_view
 {
     int device;
@@ -130,6 +151,10 @@ struct scan_refine_view
 };
 scan_refine_view refine_view(speqg_scan * s)
 {
+    {
+        device_guard guard(s->device);
+        fastq_phase2(s);
+    }
     // k-mer table scan: multiplicities were recorded per table slot; move them to mult[lb] (what the rolling scan records)
     if (s->slot_mult_dirty && s->d_mult)
     {
@@ -159,7 +184,7 @@ void scan_release(speqg_scan * s)
     cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
     cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
-    cudaFree(s->kp.slots); cudaFree(s->d_pair_mult);
+    cudaFree(s->kp.slots); cudaFree(s->d_pair_mult); cudaFree(s->d_fq_flags);
     for (auto & sl : s->slots) sl.release();
     if (s->copy) cudaStreamDestroy(s->copy);
     if (s->own_compute && s->compute) cudaStreamDestroy(s->compute);
@@ -228,6 +253,7 @@ void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
 Slot & acquire_slot(speqg_scan * s)
 {
     Slot & sl = s->slots[s->next_slot];
+    sl.ticket = ++s->tickets;
     s->next_slot = (s->next_slot + 1) % kSlots;
     if (!sl.copied)
     {
@@ -239,6 +265,49 @@ Slot & acquire_slot(speqg_scan * s)
     return sl;
 }
 }   // namespace
+
+// Second phase of a FASTQ region: the newline count is on the host by now (or as soon as its event has fired), so the line /
+// record arrays can be sized and the rest -- lines, records, pack, scan -- is queued behind the count kernels.
+void speqb::fastq_phase2(speqg_scan * s)
+{
+    if (s->fq_pending < 0) return;
+    Slot & sl = s->slots[s->fq_pending];
+    s->fq_pending = -1;
+    CK(cudaEventSynchronize(sl.counted));
+    const uint64_t n = sl.fq_bytes, n_nl = *sl.h_total;
+    const uint64_t n_lines = n_nl + (sl.fq_terminated ? 0u : 1u);
+    unsigned int * d_reject = reinterpret_cast<unsigned int *>(sl.fq_small.p + 2);
+    unsigned long long * d_nreads = sl.fq_small.p + 1;
+    if (n_lines % 4 != 0 || n_lines / 4 >= (uint64_t(1) << 32))
+    {
+        // not a whole number of 4-line records: nothing of the region is scanned; the caller reads it with the host grammar
+        unsigned int one = 1u;
+        CK(cudaMemcpyAsync(s->d_fq_flags + sl.fq_region, &one, 4, cudaMemcpyHostToDevice, s->compute));
+        CK(cudaEventRecord(sl.done, s->compute));
+        sl.busy = true;
+        return;
+    }
+    const uint64_t n_rec = n_lines / 4;
+    const uint64_t G = (n >> 5) + n_rec + 2;
+    sl.fq_lines.reserve(n_lines + 2); sl.fq_soff.reserve(n_rec + 1); sl.fq_qoff.reserve(n_rec + 1);
+    sl.len.reserve(n_rec + 1); sl.grp_off.reserve(n_rec + 2); sl.bases.reserve(G); sl.inv.reserve(G);
+    const bool local = (s->mode & M_LOCAL) != 0;
+    if (local) sl.qual.reserve(G * 32 + 32);
+    CK(launch_fastq_records(sl.raw_seq.p, n, sl.fq_chunk.p, n_nl, n_rec, sl.fq_lines.p, sl.fq_soff.p, sl.fq_qoff.p, sl.len.p, sl.grp_off.p,
+                            s->p.phred_cutoff, sl.bases.p, sl.inv.p, local ? sl.qual.p : nullptr, d_reject, d_nreads,
+                            s->d_fq_flags + sl.fq_region, s->compute));
+    s->launches += 4;
+    if (n_rec)
+    {
+        BatchView v{};
+        v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = local ? sl.qual.p : nullptr;
+        v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = n_rec; v.n_reads_dev = d_nreads;
+        // a warp per read for long reads: the sequences are at most half of the region's bytes
+        launch_on_view(s, v, (n / 2) / 32 + 1);
+    }
+    CK(cudaEventRecord(sl.done, s->compute));
+    sl.busy = true;
+}
 
 extern "C" {
 
@@ -441,6 +510,9 @@ int speqg_scan_reset(speqg_scan * s)
     SPEQG_TRY
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
+    fastq_phase2(s);
+    s->fq_regions = 0;
+    if (s->d_fq_flags) CK(cudaMemsetAsync(s->d_fq_flags, 0, (size_t)kMaxFastqRegions * 4, s->compute));
     CK(cudaMemsetAsync(s->d_state, 0, s->state_words * 8, s->compute));
     if (s->d_fkeys)
     {
@@ -465,6 +537,7 @@ int speqg_scan_submit_packed(speqg_scan * s, const speqg_batch * hb)
     check_batch(s, hb);
     if (hb->n_reads == 0) return SPEQG_OK;
     device_guard guard(s->device);
+    fastq_phase2(s);
     Slot & sl = acquire_slot(s);
     uint64_t R = hb->n_reads, G = hb->n_groups32;
     need(G == hb->grp_off[R], "n_groups32 != grp_off[n_reads]");
@@ -505,6 +578,7 @@ int speqg_scan_submit_raw(speqg_scan * s, const uint8_t * seq, const uint8_t * q
     need(offsets[R] >= base, "offsets must be non-decreasing");
     // the device packer lays the reads out itself (group floor(o / 32) + r): no pass over the reads on the host
     uint64_t G = (bytes >> 5) + R + 1;
+    fastq_phase2(s);
     Slot & sl = acquire_slot(s);
     sl.bases.reserve(G + 1); sl.inv.reserve(G + 1); sl.grp_off.reserve(R + 1); sl.len.reserve(R); sl.raw_off.reserve(R + 1);
     sl.raw_seq.reserve(bytes + 1);
@@ -528,6 +602,89 @@ int speqg_scan_submit_raw(speqg_scan * s, const uint8_t * seq, const uint8_t * q
     SPEQG_CATCH
 }
 
+int speqg_scan_submit_fastq(speqg_scan * s, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    need(!(s->mode & M_PAIRED), "speqg_scan_submit_fastq takes single-end input (mates of a pair live in two files)");
+    need(s->algo != SPEQG_ALGO_DIRECT && s->algo != SPEQG_ALGO_ROLLING64, "speqg_scan_submit_fastq runs the product kernels only");
+    need(s->fq_regions < kMaxFastqRegions, "too many FASTQ regions in one scan (2^20)");
+    need(n_bytes < (uint64_t(1) << 40), "FASTQ region too large");
+    device_guard guard(s->device);
+    if (!s->d_fq_flags)
+    {
+        s->d_fq_flags = dev_alloc<unsigned int>(kMaxFastqRegions);
+        CK(cudaMemsetAsync(s->d_fq_flags, 0, (size_t)kMaxFastqRegions * 4, s->compute));
+    }
+    const uint64_t id = s->fq_regions++;
+    if (region) *region = id;
+    if (n_bytes == 0)
+    {
+        if (ticket) *ticket = 0;
+        return SPEQG_OK;
+    }
+    need(bytes != nullptr, "bytes is NULL");
+    // the slot after the pending one: its copy is queued first, so it overlaps the pending region's second phase
+    Slot & sl = acquire_slot(s);
+    if (!sl.counted)
+    {
+        CK(cudaEventCreateWithFlags(&sl.counted, cudaEventDisableTiming));
+        CK(cudaMallocHost(reinterpret_cast<void **>(&sl.h_total), 8));
+    }
+    if (ticket) *ticket = sl.ticket;
+    sl.raw_seq.reserve(n_bytes + 64);
+    sl.fq_chunk.reserve(fastq_chunks(n_bytes) + 1);
+    sl.fq_small.reserve(8);
+    CK(cudaMemcpyAsync(sl.raw_seq.p, bytes, n_bytes, cudaMemcpyHostToDevice, s->copy));
+    CK(cudaEventRecord(sl.copied, s->copy));
+    sl.fq_bytes = n_bytes;
+    sl.fq_region = id;
+    sl.fq_terminated = bytes[n_bytes - 1] == '\n';
+    fastq_phase2(s);                                   // the region submitted before this one
+    CK(cudaStreamWaitEvent(s->compute, sl.copied, 0));
+    CK(launch_fastq_count(sl.raw_seq.p, n_bytes, sl.fq_chunk.p, sl.fq_small.p, s->compute));
+    s->launches += 2;
+    CK(cudaMemcpyAsync(sl.h_total, sl.fq_small.p, 8, cudaMemcpyDeviceToHost, s->compute));
+    CK(cudaEventRecord(sl.counted, s->compute));
+    s->fq_pending = (int)(&sl - s->slots);
+    SPEQG_CATCH
+}
+
+int speqg_scan_wait_ticket(speqg_scan * s, uint64_t ticket)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    if (ticket == 0) return SPEQG_OK;
+    device_guard guard(s->device);
+    // the staging ring reuses a slot only after the copy of its previous occupant: an evicted ticket has completed
+    for (auto & sl : s->slots)
+        if (sl.ticket == ticket && sl.copied) CK(cudaEventSynchronize(sl.copied));
+    SPEQG_CATCH
+}
+
+int speqg_scan_fastq_rejected(speqg_scan * s, uint64_t * regions, uint64_t capacity, uint64_t * n_rejected)
+{
+    SPEQG_TRY
+    need(s != nullptr && n_rejected != nullptr, "NULL argument");
+    need(capacity == 0 || regions != nullptr, "regions is NULL");
+    *n_rejected = 0;
+    if (!s->d_fq_flags || s->fq_regions == 0) return SPEQG_OK;
+    device_guard guard(s->device);
+    fastq_phase2(s);
+    std::vector<unsigned int> flags(s->fq_regions);
+    CK(cudaMemcpyAsync(flags.data(), s->d_fq_flags, s->fq_regions * 4, cudaMemcpyDeviceToHost, s->compute));
+    CK(cudaStreamSynchronize(s->compute));
+    uint64_t n = 0;
+    for (uint64_t i = 0; i < s->fq_regions; ++i)
+        if (flags[i])
+        {
+            if (n < capacity) regions[n] = i;
+            ++n;
+        }
+    *n_rejected = n;
+    SPEQG_CATCH
+}
+
 int speqg_scan_submit_device(speqg_scan * s, const speqg_batch * db)
 {
     SPEQG_TRY
@@ -535,6 +692,7 @@ int speqg_scan_submit_device(speqg_scan * s, const speqg_batch * db)
     check_batch(s, db);
     if (db->n_reads == 0) return SPEQG_OK;
     device_guard guard(s->device);
+    fastq_phase2(s);
     BatchView v{};
     v.bases = db->bases; v.inv = db->inv; v.qual = (s->mode & M_LOCAL) ? db->qual : nullptr;
     v.grp_off = db->grp_off; v.len = db->len; v.read_group = nullptr; v.n_reads = db->n_reads;
@@ -547,6 +705,7 @@ int speqg_scan_sync(speqg_scan * s)
     SPEQG_TRY
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
+    fastq_phase2(s);
     CK(cudaStreamSynchronize(s->copy));
     CK(cudaStreamSynchronize(s->compute));
     for (auto & sl : s->slots) sl.busy = false;
@@ -567,6 +726,7 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
     SPEQG_TRY
     need(s != nullptr, "NULL argument");
     device_guard guard(s->device);
+    fastq_phase2(s);
     // every kernel of the scan runs on the compute stream, behind the copies it waits for: one copy + one sync ends the job
     uint32_t V = s->idx->host.V;
     CK(cudaMemcpyAsync(s->h_state, s->d_state, s->state_words * 8, cudaMemcpyDeviceToHost, s->compute));
@@ -612,6 +772,7 @@ int speqg_scan_fusion_sets(speqg_scan * s, uint64_t * keys, uint64_t * counts, u
     need(s->d_fkeys != nullptr, "fusion sets are kept by the product kernels only (not SPEQG_ALGO_DIRECT / SPEQG_ALGO_ROLLING64)");
     need(capacity == 0 || (keys != nullptr && counts != nullptr), "keys / counts are NULL");
     device_guard guard(s->device);
+    fastq_phase2(s);
     std::vector<unsigned long long> hk(kFusionCap), hv((size_t)kFusionCap + 1);
     CK(cudaMemcpyAsync(hk.data(), s->d_fkeys, (size_t)kFusionCap * 8, cudaMemcpyDeviceToHost, s->compute));
     CK(cudaMemcpyAsync(hv.data(), s->d_fvals, ((size_t)kFusionCap + 1) * 8, cudaMemcpyDeviceToHost, s->compute));

@@ -140,6 +140,8 @@ struct BatchView
     const uint32_t * len;         // n_reads
     const int32_t * read_group;   // back-check only: group of the scaffold the read came from
     uint64_t n_reads;
+    const unsigned long long * n_reads_dev;   // optional: the number of reads, decided on the device (FASTQ regions parsed there);
+                                              // n_reads is then an upper bound
 };
 
 // One unit of lane work in the back-check: windows [start, start + nwin) of text `read`.

@@ -138,5 +138,14 @@ cudaError_t launch_kpair_fold_mult(KTabView const & kp, DevIndex const & ix, uin
 cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long long * slot_mult, unsigned long long * pair_mult,
                          BatchView const & b, ScanArgs const & a, int mode, int warp_per_read, LaunchCfg cfg, cudaStream_t st);
 cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
+// FASTQ record grammar on the device (fastq.cu): phase 1 counts the newlines of a raw region (chunk_cnt becomes the exclusive
+// prefix sum per 4 KB chunk, *total the count); phase 2, once the host knows the count, finds the lines and records, packs the
+// reads and publishes the number of reads (0 and *region_flag = 1 when the region is not in the strict 4-line form)
+uint32_t fastq_chunks(uint64_t n_bytes);
+cudaError_t launch_fastq_count(const uint8_t * raw, uint64_t n_bytes, uint32_t * chunk_cnt, unsigned long long * total, cudaStream_t st);
+cudaError_t launch_fastq_records(const uint8_t * raw, uint64_t n_bytes, const uint32_t * chunk_off, uint64_t n_newlines, uint64_t n_rec,
+                                 uint64_t * line_start, uint64_t * soff, uint64_t * qoff, uint32_t * len, uint64_t * grp_off, uint32_t cutoff,
+                                 uint64_t * bases, uint32_t * inv, uint8_t * qual_out, unsigned int * reject, unsigned long long * n_reads_dev,
+                                 unsigned int * region_flag, cudaStream_t st);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

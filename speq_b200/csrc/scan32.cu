@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
     Cfg32 cfg;
     cfg.k = a.k;
     cfg.n = ix.n;
-    cfg.units = paired ? b.n_reads / 2 : b.n_reads;
+    const uint64_t n_reads_b = b.n_reads_dev ? *b.n_reads_dev : b.n_reads;
+    cfg.units = paired ? n_reads_b / 2 : n_reads_b;
     cfg.paired = paired;
     cfg.local = LOCAL;
     cfg.record = RECORD;

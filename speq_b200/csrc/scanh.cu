@@ -280,7 +280,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     Tally32<MODE> env{b, a, sm};
 
     const uint32_t k = a.k;
-    const uint32_t units = (uint32_t)(paired ? b.n_reads / 2 : b.n_reads);
+    const uint64_t n_reads_b = b.n_reads_dev ? *b.n_reads_dev : b.n_reads;
+    const uint32_t units = (uint32_t)(paired ? n_reads_b / 2 : n_reads_b);
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t kmask = (kt.rmask << 3) | 7ull;
     const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
@@ -750,7 +751,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     Tally32<MODE> env{b, a, sm};
 
     const uint32_t k = a.k;
-    const uint32_t units = (uint32_t)(paired ? b.n_reads / 2 : b.n_reads);
+    const uint64_t n_reads_b = b.n_reads_dev ? *b.n_reads_dev : b.n_reads;
+    const uint32_t units = (uint32_t)(paired ? n_reads_b / 2 : n_reads_b);
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t pmask = (kp.rmask << 3) | 7ull;
     const uint32_t pmask_lo = (uint32_t)pmask, pmask_hi = (uint32_t)(pmask >> 32);

@@ -303,6 +303,26 @@ class Scan:
     def submit_raw(self, seq, qual, offsets, n_reads: int, encoding: int = capi.ENC_ASCII) -> None:
         capi.check(capi.lib().speqg_scan_submit_raw(self.h, capi.ptr(seq), capi.ptr(qual), capi.ptr(offsets), n_reads, encoding))
 
+    def submit_fastq(self, raw, n_bytes: int | None = None) -> tuple[int, int]:
+        """raw: bytes / numpy uint8 array / pinned torch tensor holding whole 4-line FASTQ records.  -> (region, ticket)"""
+        if isinstance(raw, (bytes, bytearray)):
+            raw = np.frombuffer(raw, np.uint8)
+        n = int(n_bytes if n_bytes is not None else raw.size if isinstance(raw, np.ndarray) else raw.numel())
+        reg, tick = C.c_uint64(), C.c_uint64()
+        capi.check(capi.lib().speqg_scan_submit_fastq(self.h, capi.ptr(raw) if n else None, n, C.byref(reg), C.byref(tick)))
+        self._keep = raw          # pageable host memory: the copy is staged before the call returns; pinned: caller waits the ticket
+        return int(reg.value), int(tick.value)
+
+    def wait_ticket(self, ticket: int) -> None:
+        capi.check(capi.lib().speqg_scan_wait_ticket(self.h, ticket))
+
+    def fastq_rejected(self) -> list[int]:
+        n = C.c_uint64()
+        capi.check(capi.lib().speqg_scan_fastq_rejected(self.h, None, 0, C.byref(n)))
+        out = np.zeros(max(1, n.value), np.uint64)
+        capi.check(capi.lib().speqg_scan_fastq_rejected(self.h, out.ctypes.data, n.value, C.byref(n)))
+        return [int(x) for x in out[:n.value]]
+
     def submit_device(self, b: DeviceBatch) -> None:
         capi.check(capi.lib().speqg_scan_submit_device(self.h, C.byref(b.s)))
 

@@ -522,3 +522,79 @@ def test_device_suffix_array_matches_host(lib, case, tmp_path):
     a.save(str(tmp_path / "host.idx")); b.save(str(tmp_path / "device.idx"))
     assert (tmp_path / "host.idx").read_bytes() == (tmp_path / "device.idx").read_bytes()
     a.close(); b.close()
+
+
+def _fastq_text(seqs, quals, nl="\n", trailing=True):
+    recs = [nl.join([f"@r{i} some id", s, "+", q]) for i, (s, q) in enumerate(zip(seqs, quals))]
+    return (nl.join(recs) + (nl if trailing else "")).encode("latin-1")
+
+
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR])
+@pytest.mark.parametrize("name", ["global_single", "local_single", "refs_with_n"])
+def test_submit_fastq_device_parser(lib, name, algorithm):
+    """speqg_scan_submit_fastq: the raw FASTQ bytes go to the device, where the 4-line record grammar runs as kernels (line
+    starts, record checks, packer reading in place).  Same tallies as the fixture (oracle/_ref) for LF, CRLF, no trailing
+    newline and several regions; irregular regions (multi-line record, blank line, length mismatch, illegal letter) are
+    reported and not scanned, and scanning them through the raw-read path afterwards completes the tallies."""
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    local = exp["mode"] == "local"
+    idx = engine.Index.from_scaffolds(scaff, gs, len(counts))
+    sc = engine.Scan(idx, k=run["k"], phred_cutoff=run.get("phred_cutoff", 30), mode=capi.MODE_LOCAL if local else capi.MODE_GLOBAL,
+                     algorithm=algorithm, record=True)
+
+    def check(r):
+        assert (r.total_kmers, r.ambiguous, r.lookups, r.reads) == (exp["total_kmers"], exp["ambiguous"], exp["lookups"], len(seqs))
+        if local:
+            assert helpers.rel_close(r.unique_w, exp["unique_w"], TOL)
+        else:
+            assert [int(x) for x in r.unique] == exp["unique"]
+
+    for nl, trailing, pieces in (("\n", True, 1), ("\r\n", True, 1), ("\n", False, 1), ("\n", True, 5), ("\r\n", False, 3)):
+        sc.reset()
+        n = len(seqs)
+        cuts = [n * i // pieces for i in range(pieces + 1)]
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            reg, _ = sc.submit_fastq(_fastq_text(seqs[a:b], quals[a:b], nl, trailing))
+        assert reg == pieces - 1
+        assert sc.fastq_rejected() == []
+        check(sc.finish())
+    # the refinement runs on what the device-parsed regions recorded
+    pct, cnt = np.full(len(counts), 100.0 / len(counts)), np.asarray(counts, np.int32)
+    tk = sc.refine(pct, cnt)
+    sc.reset()
+    seq, q, offs = helpers.flat_reads(seqs, quals)
+    sc.submit_raw(seq, q, offs, len(seqs))
+    sc.finish()
+    assert helpers.rel_close(sc.refine(pct, cnt), tk, 1e-11)
+    # irregular regions: region 1 of 3 is damaged in four different ways; it is reported, the other two are scanned
+    third = len(seqs) // 3
+    parts = [(0, third), (third, 2 * third), (2 * third, len(seqs))]
+    good = [_fastq_text(seqs[a:b], quals[a:b]) for a, b in parts]
+    a, b = parts[1]
+    s_mid, q_mid = seqs[a:b], quals[a:b]
+    j = next(i for i, s in enumerate(s_mid) if len(s) >= 8)
+    multi = _fastq_text(s_mid[:j], q_mid[:j]) + f"@m\n{s_mid[j][:4]}\n{s_mid[j][4:]}\n+\n{q_mid[j][:4]}\n{q_mid[j][4:]}\n".encode("latin-1") + \
+        _fastq_text(s_mid[j + 1:], q_mid[j + 1:])
+    blank = _fastq_text(s_mid[:j], q_mid[:j]) + b"\n" + _fastq_text(s_mid[j:], q_mid[j:])
+    mism = _fastq_text(s_mid[:j] + [s_mid[j] + "A"] + s_mid[j + 1:], q_mid)
+    illegal = _fastq_text(s_mid[:j] + ["X" + s_mid[j][1:]] + s_mid[j + 1:], q_mid)
+    for bad in (multi, blank, mism, illegal):
+        sc.reset()
+        for piece in (good[0], bad, good[2]):
+            sc.submit_fastq(piece)
+        assert sc.fastq_rejected() == [1]
+        # the caller's part: the rejected region again through the host grammar (here: the clean records) and the raw-read path
+        seq, q, offs = helpers.flat_reads(s_mid, q_mid)
+        sc.submit_raw(seq, q, offs, len(s_mid))
+        check(sc.finish())
+    # an empty region and a region of empty reads
+    sc.reset()
+    sc.submit_fastq(b"")
+    sc.submit_fastq(b"@a\n\n+\n\n@b\n\n+\n\n")
+    assert sc.fastq_rejected() == []
+    r = sc.finish()
+    assert r.reads == 2 and r.lookups == 0
+    sc.close()
+    idx.close()
