@@ -244,7 +244,7 @@ def main() -> None:
                     help="global: --fixed-accuracy 1-e, integer tallies; local: phred-weighted fp64 tallies (no --fixed-accuracy: the reference's default)")
     ap.add_argument("-k", "--kmer", type=int, default=None, help="k-mer length (default: the config's; the reference's own default is 70)")
     ap.add_argument("--batch-reads", type=int, default=1 << 20, help="reads per C-ABI submit on the e2e leg")
-    ap.add_argument("--e2e-reads", type=int, default=25_000_000, help="reads of every rank's shard the host-fed legs stream per step")
+    ap.add_argument("--e2e-reads", type=int, default=10_000_000, help="reads of every rank's shard the host-fed legs stream per step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -330,6 +330,9 @@ def main() -> None:
     db = engine.ResidentBatch(local_rank, torch.full((R,), L, dtype=torch.int64, device=dev), with_qual=local)
     seq_h = torch.empty((E, L), dtype=torch.uint8, pin_memory=True) if E else None
     qual_h = torch.empty((E, L), dtype=torch.uint8, pin_memory=True) if E else None
+    # the same reads as 4-line FASTQ text ("@r\n" seq "\n+\n" qual "\n"): what the file of `speq scan -1 reads.fq` holds
+    FQ = 2 * L + 7
+    fq_h = torch.empty((E, FQ), dtype=torch.uint8, pin_memory=True) if E and not args.no_e2e else None
     for c in range(c0, c1):
         n = min(R_total, (c + 1) * CH) - c * CH
         a, b = gen_chunk(sh, cfg_id, refs, c, n, local)
@@ -340,6 +343,15 @@ def main() -> None:
             m = min(n, E - r0)
             seq_h[r0:r0 + m].copy_(a[:m])
             qual_h[r0:r0 + m].copy_(b[:m])
+            if fq_h is not None:
+                rec = torch.empty((m, FQ), dtype=torch.uint8, device=dev)
+                rec[:, 0:3] = torch.tensor(list(b"@r\n"), dtype=torch.uint8, device=dev)
+                rec[:, 3:3 + L] = a[:m]
+                rec[:, 3 + L:6 + L] = torch.tensor(list(b"\n+\n"), dtype=torch.uint8, device=dev)
+                rec[:, 6 + L:6 + 2 * L] = b[:m]
+                rec[:, 6 + 2 * L] = 10
+                fq_h[r0:r0 + m].copy_(rec)
+                del rec
         del a, b, offs
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
@@ -398,12 +410,21 @@ def main() -> None:
                 e = min(E, s + args.batch_reads)
                 sc.submit_raw(seq_np, qual_np, offs_np[s:e + 1], e - s)
             return finish_global()
-        return step_resident, step_e2e
+
+        def step_fastq():
+            # raw FASTQ bytes, region by region; the record grammar runs on the device (speqg_scan_submit_fastq)
+            sc.reset()
+            for s in range(0, E, args.batch_reads):
+                e = min(E, s + args.batch_reads)
+                sc.submit_fastq(fq_np[s * FQ:e * FQ])
+            return finish_global()
+        return step_resident, step_e2e, step_fastq
 
     if E:
         seq_np, qual_np = seq_h.view(-1).numpy(), qual_h.view(-1).numpy()
         offs_np = (torch.arange(E + 1, dtype=torch.int64) * L).pin_memory().numpy().view(np.uint64)
-    step_resident, step_e2e = make_step(scan)
+        fq_np = fq_h.view(-1).numpy() if fq_h is not None else None
+    step_resident, step_e2e, step_fastq = make_step(scan)
 
     # ---- value: resident inputs, CUDA events ----
     for _ in range(args.warmup):
@@ -492,7 +513,7 @@ def main() -> None:
         ref_scan.close()
 
     # ---- e2e: pinned host buffers through the C ABI ----
-    e2e = e2e_roof = None
+    e2e = e2e_roof = e2e_fastq = None
     if not args.no_e2e and E:
         for _ in range(min(args.warmup, 3)):
             tall_e, _ = step_e2e()
@@ -516,6 +537,27 @@ def main() -> None:
                "input": f"pinned host ASCII reads + phred chars (the first {E} reads of every rank's shard), {args.batch_reads}-read submits; "
                         "device packer; record_multiplicity = 1",
                "launches_per_step": 2 * nb * world}
+        # ---- e2e_fastq: the bytes of a FASTQ file from pinned host memory, parsed on the device
+        for _ in range(min(args.warmup, 3)):
+            tall_f, _ = step_fastq()
+        assert scan.fastq_rejected() == []
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            tall_f, _ = step_fastq()
+        barrier()
+        dtf = time.perf_counter() - t0
+        tt = torch.tensor([dtf], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dtf = float(tt.item())
+        assert np.array_equal(tall_f[:V + 4], tall_e[:V + 4]) or local, "device-parsed FASTQ tallies differ from the raw-read path"
+        e2e_fastq = {"value": int(tall_f[V + 2]) * args.steps / dtf, "unit": UNIT, "h2d_bytes_per_step": int(E) * FQ * world,
+                     "d2h_bytes_per_step": (8 * V + 8 * 8 + 8) * world, "ms_per_step": dtf * 1e3 / args.steps,
+                     "reads_per_sec": int(tall_f[V + 3]) * args.steps / dtf,
+                     "input": f"pinned host FASTQ text ({FQ} B per record, the first {E} reads of every rank's shard), {args.batch_reads}-record "
+                              "regions; line starts, record checks and packing on the device",
+                     "launches_per_step": 7 * nb * world}
         # the ceiling of that leg: the same bytes in the same pieces as plain cudaMemcpyAsync from the same pinned buffers on all
         # ranks at once (no kernels) -- tells a box / link limit from a staging limit
         dbuf = torch.empty(2 * args.batch_reads * L, dtype=torch.uint8, device=dev)
@@ -643,7 +685,7 @@ def main() -> None:
                 "reads_per_sec": reads_step * args.steps / (ms_total * 1e-3),
                 "value_is": "scan with record_multiplicity = 1 (what `speq scan` runs), resident packed reads",
                 "resolved_algorithm": algo_name, "clocks": clk, "clocks_per_rank": clocks_all if world > 1 else None,
-                "e2e": e2e, "e2e_roofline": e2e_roof, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu, "parity": parity,
+                "e2e": e2e, "e2e_fastq": e2e_fastq, "e2e_roofline": e2e_roof, "gpu_launches": launches * world, "roofline": roof, "cpu_baseline": cpu, "parity": parity,
                 "tallies_only": tall_only,
                 "tallies": {"unique": [int(x) for x in tall[:V]], "total_kmers": int(tall[V]), "ambiguous": int(tall[V + 1])},
                 "setup": {"index_build_s": t_index, "index_n": idx.n, "index_device_mb": idx.device_bytes / 1e6, "generate_and_pack_s": t_gen,

@@ -21,6 +21,8 @@ constexpr int kSlots = 3;
 constexpr uint32_t kFusionCap = 1u << 20;
 // a k-mer table slot keeps a variant below 2^15 next to the "several variants" bit
 constexpr uint32_t kMaxGroupsTable = 32767;
+// per-CTA shared-memory tallies: 32 + 12 V bytes in the scan kernels, 24 V bytes in refine_kernel (227 KB per CTA)
+constexpr uint32_t kMaxGroupsScan = 8192;
 
 template <class T> struct dev_buf
 {
@@ -323,6 +325,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
     need(!(params->algorithm == SPEQG_ALGO_KTABLE && params->k > kMaxKTable), "the k-mer table algorithm needs k <= 31");
     need(!(params->algorithm == SPEQG_ALGO_KTABLE && idx->host.V > kMaxGroupsTable), "the k-mer table algorithm needs at most 32767 variants");
     need(idx->host.n <= kMaxN32, "index too large: the indexed text must be shorter than 2^31 symbols");
+    need(idx->host.V <= kMaxGroupsScan, "too many variants for the scan kernels: the per-CTA tallies (12 B per variant, 24 B in the "
+                                       "refinement) live in shared memory; at most 8192 variants");
     need(!(params->algorithm == SPEQG_ALGO_DIRECT && params->mode == SPEQG_MODE_LOCAL), "the direct algorithm covers global mode only");
     DeviceIndex & di = device_index(idx, device);
     device_guard guard(device);
@@ -378,6 +382,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         // rank blocks specialised for this k: one pass over the index, once per scan handle
         s->view = di.view;
         if (s->algo == SPEQG_ALGO_KTABLE || s->algo == SPEQG_ALGO_KPAIR)
+        try
         {
             // distinct k-mers of the index <= suffixes that start a depth-k lcp interval; load factor in (0.2, 0.4]
             HostIndex const & h = idx->host;
@@ -467,6 +472,22 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 }
             }
         }
+        catch (api_error const & e)
+        {
+            // SPEQG_ALGO_AUTO: a table that cannot be built here (geometry beyond 2^31 buckets, not enough device memory for the
+            // tables and their counters) is no reason to fail -- the rolling FM search works from the 1 + 2 bytes per suffix the
+            // index already holds.  An explicitly requested table algorithm reports the error.
+            if (!auto_algo || (e.code != SPEQG_ENOMEM && e.code != SPEQG_EINVAL)) throw;
+            cudaGetLastError();
+            cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->kp.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_pair_mult);
+            cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_kstat);
+            s->kt = KTabView{}; s->kp = KTabView{};
+            s->d_slot_mult = s->d_pair_mult = s->d_diff = s->d_kstat = nullptr;
+            s->d_scan_tmp = nullptr;
+            s->ktab_keys = s->kpair_keys = 0;
+            s->algo = SPEQG_ALGO_ROLLING;
+        }
+        if (s->algo == SPEQG_ALGO_KTABLE || s->algo == SPEQG_ALGO_KPAIR) {}
         else if (s->algo == SPEQG_ALGO_ROLLING64)
         {
             s->d_blocks_k = dev_alloc<KBlock>(idx->host.blocks.size());

@@ -91,7 +91,14 @@ template <int MODE> struct Tally32
     }
     // an ambiguous unit (is_ambiguous, src/fm_scanner.cpp:183-190): which variants met -- the key of the reference's
     // fusion_totals map (src/fm_scanner.cpp:983-995); one insert-or-increment in the device map per ambiguous unit
+#ifndef SPEQB_FUSION_NOINLINE
+#define SPEQB_FUSION_NOINLINE 0
+#endif
+#if SPEQB_FUSION_NOINLINE
+    __device__ __noinline__ void fusion(unsigned long long key) const
+#else
     __device__ __forceinline__ void fusion(unsigned long long key) const
+#endif
     {
         if (a.fkeys == nullptr) return;
         uint64_t x = key * 0x9E3779B97F4A7C15ull;

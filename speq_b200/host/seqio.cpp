@@ -42,6 +42,11 @@ sequence_reader::sequence_reader(std::filesystem::path const & p, uint64_t start
         throw std::runtime_error("Could not seek in " + path_);
 }
 
+sequence_reader::sequence_reader(const char * data, uint64_t begin, uint64_t end, std::string const & name)
+    : fastq_(true), mem_(data), mpos_(begin), mend_(end), path_(name)
+{
+}
+
 sequence_reader::~sequence_reader()
 {
     if (gz_) gzclose(static_cast<gzFile>(gz_));
@@ -51,6 +56,17 @@ bool sequence_reader::getline(std::string & out)
 {
     out.clear();
     if (have_peek_) { out.swap(peek_); have_peek_ = false; return true; }
+    if (mem_)
+    {
+        if (mpos_ >= mend_) return false;
+        const char * b = mem_ + mpos_;
+        const char * nl = static_cast<const char *>(memchr(b, '\n', mend_ - mpos_));
+        const uint64_t len = nl ? static_cast<uint64_t>(nl - b) : mend_ - mpos_;
+        out.assign(b, len);
+        mpos_ += len + (nl ? 1 : 0);
+        if (!out.empty() && out.back() == '\r') out.pop_back();
+        return true;
+    }
     bool got = false;
     while (true)
     {
@@ -183,6 +199,47 @@ uint64_t fastq_map::find_start(uint64_t p) const
         q = e0 + 1;
     }
     return size_;
+}
+
+uint64_t fastq_map::region_end(uint64_t pos, uint64_t max_bytes) const
+{
+    if (pos >= size_ || size_ - pos <= max_bytes) return size_;
+    const uint64_t limit = pos + max_bytes;
+    // walk record starts forward from a point shortly before the limit; widen the window when no start lies in it
+    for (uint64_t back = 1ull << 16; ; back <<= 3)
+    {
+        const uint64_t from = limit > pos + back ? limit - back : pos;
+        uint64_t s = from == pos ? pos : find_start(from);
+        if (s <= limit && (s > pos || from == pos))
+        {
+            while (true)
+            {
+                const uint64_t nx = find_start(s + 1);
+                if (nx > limit) break;
+                s = nx;
+            }
+            return s;                  // == pos: the record at pos alone is larger than max_bytes
+        }
+        if (from == pos) return pos;
+    }
+}
+
+void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads)
+{
+    threads = std::max(1, threads);
+    if (threads == 1 || bytes < (8u << 20))
+    {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (int i = 0; i < threads; ++i)
+    {
+        const uint64_t a = bytes * static_cast<uint64_t>(i) / static_cast<uint64_t>(threads) & ~uint64_t(4095);
+        const uint64_t b = i + 1 == threads ? bytes : (bytes * (static_cast<uint64_t>(i) + 1) / static_cast<uint64_t>(threads) & ~uint64_t(4095));
+        th.emplace_back([=]() { memcpy(static_cast<char *>(dst) + a, static_cast<const char *>(src) + a, b - a); });
+    }
+    for (auto & t : th) t.join();
 }
 
 bool fastq_map::index(uint64_t pos, uint64_t max_bytes, int threads, std::vector<fq_rec> & out) const

@@ -27,6 +27,8 @@ class sequence_reader
 public:
     // start_offset: byte offset of a record start (plain files; used when the parallel FASTQ indexer hands over)
     explicit sequence_reader(std::filesystem::path const & p, uint64_t start_offset = 0);
+    // FASTQ records held in memory: bytes [begin, end) of a mapped file (a region the device parser handed back)
+    sequence_reader(const char * data, uint64_t begin, uint64_t end, std::string const & name);
     ~sequence_reader();
     sequence_reader(sequence_reader const &) = delete;
     // next record: returns false at end of file.  qual is filled with 'J' (phred 41) for FASTA records.
@@ -39,6 +41,8 @@ private:
     std::vector<char> buf_;
     size_t pos_ = 0, len_ = 0;
     bool eof_ = false, fastq_ = false, have_peek_ = false;
+    const char * mem_ = nullptr;       // memory source: [mpos_, mend_)
+    uint64_t mpos_ = 0, mend_ = 0;
     std::string peek_;
     std::string path_;
 };
@@ -71,6 +75,11 @@ public:
     bool index(uint64_t pos, uint64_t max_bytes, int threads, std::vector<fq_rec> & out) const;
     const char * data() const { return data_; }
     uint64_t size() const { return size_; }
+    // first record start at or after p (a line that begins with '@' whose second successor begins with '+'); size() if none
+    uint64_t record_start_from(uint64_t p) const { return find_start(p); }
+    // end of a region that starts at the record start `pos` and holds at most max_bytes: the last record start <= pos + max_bytes
+    // (size() when the rest of the file fits); pos itself when not even one record fits
+    uint64_t region_end(uint64_t pos, uint64_t max_bytes) const;
 
 private:
     uint64_t find_start(uint64_t p) const;
@@ -81,6 +90,8 @@ private:
 
 // copy records [r0, r1) of `recs` (step `stride`, slot offset `slot`: mates of a pair interleave with stride 2) into the
 // flat arrays; dst offsets come from `offsets` (already filled for every slot)
+// plain copy by `threads` threads (page cache -> pinned staging buffer)
+void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads);
 void copy_records(const char * data, std::vector<fq_rec> const & recs, uint64_t n, uint8_t * seq, uint8_t * qual,
                   uint64_t const * offsets, uint64_t stride, uint64_t slot, int threads);
 

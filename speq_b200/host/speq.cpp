@@ -12,6 +12,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <iostream>
@@ -249,6 +250,9 @@ struct device_lane
     speqg_scan * scan = nullptr;
     host_batch buf[2];
     int cur = 0;
+    // raw FASTQ regions parsed on the device: copy ticket of each staging buffer, and where every submitted region lies in the file
+    uint64_t ticket[2] = {0, 0};
+    std::vector<std::pair<uint64_t, uint64_t>> regions;
 };
 
 struct scan_out
@@ -278,7 +282,65 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
     //      irregular hands over to the serial reader (full seqan3 grammar) at the offset of the first irregular record
     uint64_t off1 = 0, off2 = 0;
     bool serial = true;
-    if (speq::io::fastq_map::eligible(args.in_file_reads_path_1) && (!paired || speq::io::fastq_map::eligible(args.in_file_reads_path_2)))
+    // ---- single-end plain FASTQ: the file's bytes go to the device region by region (cut at record starts) and the record
+    //      grammar runs there (speqg_scan_submit_fastq); the host only copies page cache -> pinned staging.  Regions the device
+    //      finds irregular (multi-line records, blanks, ...) are read again below with the full grammar; the rest of the file
+    //      goes through the host paths when a single record exceeds the staging buffer.  SPEQ_HOST_FASTQ=1 keeps the host indexer.
+    if (!paired && !getenv("SPEQ_HOST_FASTQ") && speq::io::fastq_map::eligible(args.in_file_reads_path_1))
+    {
+        const int T = std::max(1, static_cast<int>(args.threads) - 1);
+        speq::io::fastq_map m1(args.in_file_reads_path_1);
+        while (off1 < m1.size())
+        {
+            device_lane & L = lanes[dev];
+            host_batch & b = L.buf[L.cur];
+            const uint64_t end = m1.region_end(off1, b.cap_bytes);
+            if (end == off1) break;                                   // a record larger than the staging buffer: host paths
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[L.cur]), "speqg_scan_wait_ticket");   // this buffer's previous copy
+            speq::io::parallel_copy(b.seq, m1.data() + off1, end - off1, T);
+            uint64_t region = 0;
+            ck(speqg_scan_submit_fastq(L.scan, b.seq, end - off1, &region, &L.ticket[L.cur]), "speqg_scan_submit_fastq");
+            if (region != L.regions.size()) throw std::runtime_error("internal error: FASTQ region numbering");
+            L.regions.emplace_back(off1, end - off1);
+            L.cur ^= 1;
+            off1 = end;
+            dev = (dev + 1) % lanes.size();
+        }
+        // regions the device handed back: the serial grammar over the mapped bytes, through the raw-read path
+        for (auto & L : lanes)
+        {
+            uint64_t n_rej = 0;
+            ck(speqg_scan_fastq_rejected(L.scan, nullptr, 0, &n_rej), "speqg_scan_fastq_rejected");
+            if (n_rej == 0) continue;
+            std::vector<uint64_t> rej(n_rej);
+            ck(speqg_scan_fastq_rejected(L.scan, rej.data(), n_rej, &n_rej), "speqg_scan_fastq_rejected");
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[0]), "speqg_scan_wait_ticket");
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[1]), "speqg_scan_wait_ticket");
+            L.buf[0].clear(); L.buf[1].clear();
+            for (uint64_t id : rej)
+            {
+                auto const & rg = L.regions.at(id);
+                speq::io::sequence_reader rd(m1.data(), rg.first, rg.first + rg.second, args.in_file_reads_path_1.string());
+                std::string sq, ql;
+                while (rd.next(sq, ql))
+                {
+                    if (!L.buf[L.cur].fits(sq.size(), 1))
+                    {
+                        flush(L);
+                        if (sq.size() > L.buf[L.cur].cap_bytes)
+                        {
+                            ck(speqg_scan_sync(L.scan), "speqg_scan_sync");
+                            L.buf[L.cur].alloc(sq.size() * 2, L.buf[L.cur].cap_reads);
+                        }
+                    }
+                    L.buf[L.cur].push(sq, ql);
+                }
+            }
+            flush(L);
+        }
+        serial = off1 < m1.size();
+    }
+    else if (speq::io::fastq_map::eligible(args.in_file_reads_path_1) && (!paired || speq::io::fastq_map::eligible(args.in_file_reads_path_2)))
     {
         serial = false;
         const int T = std::max(1, static_cast<int>(args.threads) - 1);

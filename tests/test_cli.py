@@ -204,6 +204,41 @@ def test_speq_scan_on_reference_written_index(speq_bin, tmp_path):
     assert t == os.stat(tmp_path / "fromref.idx").st_mtime_ns or t != 0
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("damage", ["none", "multiline", "crlf_blank"])
+def test_speq_scan_device_fastq_path(speq_bin, tmp_path, damage):
+    """Single-end plain FASTQ takes the device parser (speqg_scan_submit_fastq) in regions of one staging buffer; with
+    --batch-reads 64 the file spans several regions.  A multi-line record / blank lines make their region irregular: it is handed
+    back and read with the host grammar.  Same numbers as with SPEQ_HOST_FASTQ=1 (the host indexer) and as the fixture."""
+    fx = helpers.load_golden("global_single")
+    exp, runp = fx["expected"], fx["run"]
+    refs, groups, r1, _ = helpers.golden_files(tmp_path, fx)
+    seqs, quals = helpers.parse_fastq(fx["reads1_fq"])
+    j = next(i for i, s in enumerate(seqs) if len(s) >= 10 and i > 100)
+    lines = []
+    for i, (sq, ql) in enumerate(zip(seqs, quals)):
+        if damage == "multiline" and i == j:
+            lines += [f"@read_{i}", sq[:5], sq[5:], "+", ql[:5], ql[5:]]
+        else:
+            lines += [f"@read_{i}", sq, "+", ql]
+        if damage == "crlf_blank" and i == j:
+            lines.append("")
+    nl = "\r\n" if damage == "crlf_blank" else "\n"
+    (tmp_path / "x.fq").write_bytes((nl.join(lines) + nl).encode("latin-1"))
+    outs = []
+    for env_host in (False, True):
+        env = dict(os.environ, SPEQ_HOST_FASTQ="1") if env_host else dict(os.environ)
+        r = subprocess.run([str(speq_bin), "all", "-r", str(refs), "-g", str(groups), "-1", str(tmp_path / "x.fq"), "-x", str(tmp_path / "i.idx"),
+                            "-k", str(runp["k"]), "--fixed-accuracy", str(runp["fixed_accuracy"]), "--json", str(tmp_path / "o.json"),
+                            "--batch-reads", "64", "-f"], capture_output=True, text=True, cwd=tmp_path, env=env)
+        assert r.returncode == 0, r.stderr
+        outs.append(json.loads((tmp_path / "o.json").read_text()))
+    for out in outs:
+        assert out["unique"] == exp["unique"] and out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"]
+        assert out["lookups"] == exp["lookups"] and out["iterations"] == exp["iterations"]
+        assert helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
+
+
 def _write_fq(path, recs, newline="\n", trailing=True):
     txt = newline.join(newline.join(["@" + h, s, "+", q]) for h, s, q in recs)
     path.write_text(txt + (newline if trailing else ""), newline="")
