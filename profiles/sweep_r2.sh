@@ -2,7 +2,8 @@
 # Round-2 A/B builds of the table scan on the GPU box: each variant rebuilds the library with SPEQB_NVCC_EXTRA and prints the
 # record-mode (value) and tallies-only kernel times of `bench.py --config C2` and C3 at 25 M reads.
 O=${1:-gpurun_out}; mkdir -p $O
-for v in "${SWEEP[@]:-base}"; do
+IFS=";" read -ra VS <<< "${SWEEP:-base}"
+for v in "${VS[@]}"; do
   extra=""; [ "$v" != "base" ] && extra="$v"
   SPEQB_NVCC_EXTRA="$extra" python -m speq_b200.build --force > /dev/null 2>&1 || { echo "build failed: $v" | tee -a $O/r2_sweep.txt; continue; }
   for c in "C2 10000000" "C3 25000000"; do
