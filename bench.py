@@ -248,6 +248,7 @@ def main() -> None:
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the cross-checks (measurement builds whose results are meaningless)")
     ap.add_argument("--no-probe", action="store_true", help="skip the in-run random-sector probe (profiling runs)")
     ap.add_argument("--algorithm", default="auto", choices=["auto", "kpair", "ktable", "rolling", "direct"],
                     help="auto = the library's default: pair / k-mer table scan for k <= 31, else the rolling FM search")
@@ -490,14 +491,14 @@ def main() -> None:
             pscan.reset(); pscan.submit_device(db)
         torch.cuda.synchronize()
         p_ms, pr_ = kernel_ms(pscan)
-        assert np.array_equal(pr_.unique, rk.unique) and pr_.total_kmers == rk.total_kmers
+        assert args.no_check or (np.array_equal(pr_.unique, rk.unique) and pr_.total_kmers == rk.total_kmers)
         tall_only = {"kernel_ms": p_ms, "value": R * wpr / (p_ms * 1e-3), "unit": UNIT, "record_over_tallies_only": p_ms / kern_ms,
                      "note": "rank 0's shard, resident batch, scan kernel without the per-k-mer multiplicity recording"}
         pscan.close()
 
     # ---- cross-check outside every timed region: the k-mer table scan must reproduce the rolling FM search bit for bit
     cross = None
-    if table:
+    if table and not args.no_check:
         ref_scan = engine.Scan(idx, k=k, phred_cutoff=cutoff, mode=mode, algorithm=capi.ALGO_ROLLING, device=local_rank, stream=stream.cuda_stream)
         sub = min(R, 25_000_000)
         subv = capi.Batch(db.s.bases, db.s.inv, db.s.qual, db.s.grp_off, db.s.len, sub, int(db.grp_off[sub].item()))

@@ -1,6 +1,6 @@
 """Wall-clock of the host CLI (`speq all`, then `speq scan` on the cached index) on a synthetic C2-shaped FASTQ file:
 index build, back-check, parallel FASTQ ingest, scan and refinement through the C ABI.  Usage: python profiles/cli_e2e.py [reads]"""
-import json, subprocess, sys, time, tempfile
+import json, os, subprocess, sys, time, tempfile
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np
@@ -21,9 +21,10 @@ with tempfile.TemporaryDirectory(dir="/dev/shm") as d:
     for name, cmd in (("all", ["all", "-r", "refs.fa", "-g", "groups.txt"]), ("scan", ["scan"])):
         for t in (16,) if name == "all" else (2, 16):
             c = [str(exe), *cmd, "-1", "reads.fq", "-x", "i.idx", "-k", str(sh.k), "--fixed-accuracy", "0.995", "-t", str(t), "--json", "o.json"]
-            t0 = time.time(); r = subprocess.run(c, cwd=d, capture_output=True, text=True); dt = time.time() - t0
+            t0 = time.time(); r = subprocess.run(c, cwd=d, capture_output=True, text=True, env=dict(os.environ, SPEQ_TIMING="1")); dt = time.time() - t0
             assert r.returncode == 0, r.stderr[-2000:]
             o = json.loads((d / "o.json").read_text())
             out[f"{name}_t{t}"] = {"wall_s": dt, "reads_per_s_wall": R / dt, "scan_s": o.get("t_scan_s"), "backcheck_s": o.get("t_backcheck_s"), "refine_s": o.get("t_refine_s"), "total_kmers": o["total_kmers"],
-                                   "iterations": o["iterations"]}
+                                   "iterations": o["iterations"],
+                                   "phases": [ln.split("]", 1)[1].split() for ln in r.stderr.splitlines() if ln.startswith("[timing]")]}
 print(json.dumps(out))

@@ -264,6 +264,9 @@ constexpr uint32_t kClaimChunkW = 4;   // reads a warp claims at a time when it 
 #ifndef SPEQB_HMINB
 #define SPEQB_HMINB 4
 #endif
+#ifndef SPEQB_EXP_FREE_INPUT
+#define SPEQB_EXP_FREE_INPUT 0
+#endif
 constexpr int kWin = SPEQB_KWIN;
 
 // WPR (long reads): the 32 lanes of a warp share one read -- lane l takes windows [l * per, (l + 1) * per), per = ceil(nwin / 32),
@@ -381,7 +384,14 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 else
                 {
                     // issued now, consumed by H_FIRST in the next iteration
+#if SPEQB_EXP_FREE_INPUT
+                    // measurement only (profiles/): every lane of a warp reads the SAME read, so the input loads of a warp are one
+                    // broadcast wavefront each -- the upper bound of what staging the reads in shared memory could save; the
+                    // probes stay spread because the hash below is salted per lane.  Results are meaningless in this build.
+                    const uint64_t fr = (paired ? 2ull * u + (mate2 ? 1u : 0u) : (uint64_t)u) & ~31ull;
+#else
                     const uint64_t fr = paired ? 2ull * u + (mate2 ? 1u : 0u) : (uint64_t)u;
+#endif
                     pend = load_ro(b.len + fr);
                     g0 = load_ro(b.grp_off + fr);
                     phase = H_FIRST;
@@ -447,7 +457,11 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 }
                 if (due[j])
                 {
+#if SPEQB_EXP_FREE_INPUT
+                    const uint64_t h = ((key ^ ((uint64_t)lane * 0x9E3779B1ull)) * kt.mul) & kt.mask_b;
+#else
                     const uint64_t h = (key * kt.mul) & kt.mask_b;
+#endif
                     pb[j] = (uint32_t)(h >> kt.rbits);
                     const uint64_t want = h & kt.rmask;
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);

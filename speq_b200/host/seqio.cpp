@@ -224,6 +224,31 @@ uint64_t fastq_map::region_end(uint64_t pos, uint64_t max_bytes) const
     }
 }
 
+void fastq_map::read_into(void * dst, uint64_t pos, uint64_t len, int threads) const
+{
+    threads = std::max(1, std::min<int>(threads, static_cast<int>(len >> 20) + 1));
+    std::vector<char> failed(static_cast<size_t>(threads), 0);
+    auto work = [&](int i)
+    {
+        uint64_t a = len * static_cast<uint64_t>(i) / static_cast<uint64_t>(threads), b = len * (static_cast<uint64_t>(i) + 1) / static_cast<uint64_t>(threads);
+        while (a < b)
+        {
+            ssize_t r = pread(fd_, static_cast<char *>(dst) + a, b - a, static_cast<off_t>(pos + a));
+            if (r <= 0) { failed[static_cast<size_t>(i)] = 1; return; }
+            a += static_cast<uint64_t>(r);
+        }
+    };
+    if (threads == 1) work(0);
+    else
+    {
+        std::vector<std::thread> th;
+        for (int i = 0; i < threads; ++i) th.emplace_back(work, i);
+        for (auto & t : th) t.join();
+    }
+    for (char f : failed)
+        if (f) throw std::runtime_error("read error in the FASTQ file");
+}
+
 void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads)
 {
     threads = std::max(1, threads);

@@ -80,6 +80,9 @@ public:
     // end of a region that starts at the record start `pos` and holds at most max_bytes: the last record start <= pos + max_bytes
     // (size() when the rest of the file fits); pos itself when not even one record fits
     uint64_t region_end(uint64_t pos, uint64_t max_bytes) const;
+    // bytes [pos, pos + len) of the file into dst with `threads` concurrent pread()s: a plain kernel copy out of the page cache
+    // (no page faults, unlike touching the mapping for the first time)
+    void read_into(void * dst, uint64_t pos, uint64_t len, int threads) const;
 
 private:
     uint64_t find_start(uint64_t p) const;

@@ -20,6 +20,7 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/speq_cuda.h"
@@ -297,7 +298,7 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
             const uint64_t end = m1.region_end(off1, b.cap_bytes);
             if (end == off1) break;                                   // a record larger than the staging buffer: host paths
             ck(speqg_scan_wait_ticket(L.scan, L.ticket[L.cur]), "speqg_scan_wait_ticket");   // this buffer's previous copy
-            speq::io::parallel_copy(b.seq, m1.data() + off1, end - off1, T);
+            m1.read_into(b.seq, off1, end - off1, T);
             uint64_t region = 0;
             ck(speqg_scan_submit_fastq(L.scan, b.seq, end - off1, &region, &L.ticket[L.cur]), "speqg_scan_submit_fastq");
             if (region != L.regions.size()) throw std::runtime_error("internal error: FASTQ region numbering");
@@ -517,6 +518,36 @@ int do_scan(cmd_arguments & args)
     const bool paired = !args.in_file_reads_path_2.empty();
     const bool local = (args.fixed_accuracy == 0.0);                                 // src/fm_scanner.cpp:8-17
     const double percent_perfect = local ? 0.0 : pow(args.fixed_accuracy, args.kmer);
+    // SPEQ_TIMING=1: wall-clock stamps of the phases on stderr (profiles/cli_e2e.py)
+    const auto T0 = std::chrono::steady_clock::now();
+    const bool timing = getenv("SPEQ_TIMING") != nullptr;
+    auto stamp = [&](const char * what)
+    {
+        if (timing) fprintf(stderr, "[timing] %-34s %.3f s\n", what, std::chrono::duration<double>(std::chrono::steady_clock::now() - T0).count());
+    };
+    // Start-up overlap: the CUDA context and the pinned staging buffers do not depend on the index, so a helper thread creates
+    // them while this thread reads the .idx from disk.
+    int ndev = 0;
+    ck(speqg_device_count(&ndev), "speqg_device_count");
+    if (ndev <= 0) throw std::runtime_error("no CUDA device: speq scan has no CPU path");
+    const unsigned gpus = std::min<unsigned>(args.gpus, static_cast<unsigned>(ndev));
+    std::vector<device_lane> lanes(gpus);
+    const uint64_t cap_reads = std::max<uint64_t>(2, args.batch_reads & ~1u);
+    const uint64_t cap_bytes = std::min<uint64_t>(cap_reads * 320, uint64_t(512) << 20);
+    std::string prep_error;
+    std::thread prep([&]()
+    {
+        try
+        {
+            for (unsigned d = 0; d < gpus; ++d)
+            {
+                lanes[d].buf[0].alloc(cap_bytes, cap_reads);
+                lanes[d].buf[1].alloc(cap_bytes, cap_reads);
+            }
+        }
+        catch (std::exception const & e) { prep_error = e.what(); }
+    });
+    struct joiner { std::thread & t; ~joiner() { if (t.joinable()) t.join(); } } prep_join{prep};
     // import the index (src/fm_scanner.cpp:37-58)
     args.io_file_index.replace_extension(".idx");
     idx_meta meta = read_meta(args.io_file_index);
@@ -537,10 +568,7 @@ int do_scan(cmd_arguments & args)
         else throw std::logic_error{"SPeQ could not find the sequence file used to make the specified index file."};
     }
     const uint32_t V = static_cast<uint32_t>(meta.group_names.size());
-    int ndev = 0;
-    ck(speqg_device_count(&ndev), "speqg_device_count");
-    if (ndev <= 0) throw std::runtime_error("no CUDA device: speq scan has no CPU path");
-    const unsigned gpus = std::min<unsigned>(args.gpus, static_cast<unsigned>(ndev));
+    stamp("index file read");
 
     // <stem>_<k>mer.dat: back-check counts, cached per k, keyed by the .idx mtime (src/fm_scanner.cpp:79-135)
     int64_t idx_time = mtime_of(args.io_file_index);
@@ -583,8 +611,8 @@ int do_scan(cmd_arguments & args)
         std::cerr << total_ref << "\n";
     }
 
+    stamp("back-check / .dat");
     // one scan handle per device, index replicated
-    std::vector<device_lane> lanes(gpus);
     speqg_params prm{};
     prm.k = args.kmer;
     prm.phred_cutoff = args.phred_cutoff;
@@ -592,18 +620,16 @@ int do_scan(cmd_arguments & args)
     prm.paired = paired ? 1 : 0;
     prm.record_multiplicity = 1;
     prm.algorithm = SPEQG_ALGO_AUTO;   // k <= 31: k-mer table scan; else the rolling FM search
-    uint64_t cap_reads = std::max<uint64_t>(2, args.batch_reads & ~1u);
-    uint64_t cap_bytes = std::min<uint64_t>(cap_reads * 320, uint64_t(512) << 20);
-    for (unsigned d = 0; d < gpus; ++d)
-    {
-        ck(speqg_scan_open(idx.h, static_cast<int>(d), &prm, &lanes[d].scan), "speqg_scan_open");
-        lanes[d].buf[0].alloc(cap_bytes, cap_reads);
-        lanes[d].buf[1].alloc(cap_bytes, cap_reads);
-    }
+    for (unsigned d = 0; d < gpus; ++d) ck(speqg_scan_open(idx.h, static_cast<int>(d), &prm, &lanes[d].scan), "speqg_scan_open");
+    stamp("scan handles open");
+    prep.join();
+    if (!prep_error.empty()) throw std::runtime_error(prep_error);
+    stamp("pinned staging ready");
     int rc = 1;
     try
     {
         scan_out so = run_scan(args, lanes, V, paired);
+        stamp("scan done");
         std::vector<double> unique_totals(V, 0.0);
         if (local) unique_totals = so.unique_w;
         else for (uint32_t i = 0; i < V; ++i) unique_totals[i] += static_cast<double>(so.unique_int[i]) / percent_perfect;   // :234-236
@@ -649,6 +675,7 @@ int do_scan(cmd_arguments & args)
             ++iters;
         }
         double t_refine = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        stamp("refinement done");
         if (args.write_output)
         {
             // ambiguous reads / pairs by the variants that met in them, summed over the devices
