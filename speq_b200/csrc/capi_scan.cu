@@ -203,6 +203,7 @@ ScanArgs scan_args(speqg_scan * s)
     a.scalars = s->d_scalars;
     a.mult = s->d_mult;
     a.qden = s->d_qden;
+    a.qrden = s->d_qden + 42;
     a.segs = nullptr;
     a.n_segs = 0;
     a.work = s->d_work;
@@ -372,13 +373,14 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
         s->d_gc = dev_alloc<int32_t>(V);
         if (params->record_multiplicity) s->d_mult = dev_alloc<unsigned long long>(idx->host.n);
         // local-mode denominators with the host's libm, exactly the reference's expression (src/fm_scanner.cpp:454)
-        double qden[42];
+        double qden[84];                     // [0, 42): the denominators; [42, 84): their reciprocals (rolling window weight)
         for (int q = 0; q < 42; ++q)
         {
             double b = q;
             qden[q] = 1.0 - 1.0 / pow(10.0, b / 10.0);
+            qden[42 + q] = 1.0 / qden[q];
         }
-        s->d_qden = dev_upload(qden, 42);
+        s->d_qden = dev_upload(qden, 84);
         // rank blocks specialised for this k: one pass over the index, once per scan handle
         s->view = di.view;
         if (s->algo == SPEQG_ALGO_KTABLE || s->algo == SPEQG_ALGO_KPAIR)

@@ -44,6 +44,7 @@ struct ScanArgs
     unsigned long long * diff;        // k-mer table with positions: difference array over the packed-text positions; a run of
                                       //     hits at consecutive positions [s, e] is recorded as diff[s] += 1, diff[e + 1] -= 1
     const double * qden;              // [42] 1 - 1/pow(10, q/10), host libm values   (local mode)
+    const double * qrden;             // [42] 1 / qden (inf for q = 0: never inside a valid window, phred > cutoff >= 0)
     const SegmentX * segs;             // optional segment table (back-check); null: one segment per read / pair
     uint64_t n_segs;
     unsigned long long * work;        // scan32: next unclaimed unit minus the number of threads (zero at launch)

@@ -39,11 +39,21 @@ template <int MODE, bool G8> struct Env32 : Tally32<MODE>
         return v;
     }
     __device__ __forceinline__ uint32_t exc_word(uint32_t blk) const { return load_ro(&ix.blocks[blk >> 1].exc[blk & 1u]); }
+    __device__ __forceinline__ uint64_t qual8(uint64_t g0, uint32_t pos) const
+    {
+        return load_ro(reinterpret_cast<const uint64_t *>(this->b.qual + 32ull * g0 + pos));
+    }
+    __device__ __forceinline__ uint32_t qual1(uint64_t g0, uint32_t pos) const { return load_ro(this->b.qual + 32ull * g0 + pos); }
+    __device__ __forceinline__ double den(uint32_t q) const { return this->sm.den[q]; }
+    __device__ __forceinline__ double rden(uint32_t q) const { return this->sm.rden[q]; }
     __device__ __forceinline__ void record(uint32_t lb) const { atomicAdd(this->a.mult + lb, 1ull); }
 };
 
+#ifndef SPEQB_RMINB_LOCAL
+#define SPEQB_RMINB_LOCAL 3
+#endif
 template <int MODE, bool G8, bool MASK>
-__global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __restrict__ fblk, const DevIndex ix, const BatchView b,
+__global__ void __launch_bounds__(kBlock32, (MODE & M_LOCAL) ? SPEQB_RMINB_LOCAL : 4) scan32_kernel(const FBlock * __restrict__ fblk, const DevIndex ix, const BatchView b,
                                                              const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
@@ -51,6 +61,7 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem32 sm = smem32_view(smem_raw, a.V);
     smem32_clear(sm, a.V);
+    smem32_tables(sm, a, LOCAL);
 
     Cfg32 cfg;
     cfg.k = a.k;
@@ -88,6 +99,7 @@ __global__ void __launch_bounds__(kBlock32, 4) scan32_kernel(const FBlock * __re
             const bool needw = stp && s.t < s.pend && (s.t & 31u) == 0u;
             ld32x2_if(s.wlo, s.whi, b.bases + s.g0 + (s.t >> 5), needw);
             ld32_if(s.winv, b.inv + s.g0 + (s.t >> 5), needw);
+            if (LOCAL && stp) lane32_load_qual(s, cfg, env);
         }
         if (m_up)
         {
@@ -207,7 +219,7 @@ int sm_count32()
 }
 }   // namespace
 
-size_t scan32_smem_bytes(uint32_t V) { return 32 + (size_t)V * 12; }
+size_t scan32_smem_bytes(uint32_t V) { return 32 + (size_t)V * 12 + 2 * 42 * 8; }
 
 // G8: variants as bytes inside the blocks (V <= 255); MASK (implies G8): the unit's variants as a 64-bit mask (V <= 64)
 #define SPEQB_SCAN32_CASE(M, G, MK, EXPR) { auto kern = scan32_kernel<M, G, MK>; EXPR; break; }

@@ -41,6 +41,11 @@ struct Lane32
     uint32_t agg_g, agg_n;        // run-length aggregation of the lane's unique tallies
     double agg_w;
     uint32_t c_total;             // valid windows of the current unit
+    // local-error mode: the phred weight of the window that ends at the cursor, as a rolling product (times 1/den[q] for the
+    // base that enters, times den[q] for the base that leaves, 1 behind an invalid base; see QRoll in scan_dev.cuh for the
+    // error bound), the weights of the hit being resolved / taken, and the 8 quality bytes around base t and base t - k
+    double P, pw0, pw1;
+    uint64_t qn, qo;
 };
 
 // What one iteration loads.  A lane is in exactly one phase, so the phases share registers:
@@ -67,12 +72,15 @@ SPEQB_HD void lane32_init(Lane32 & s, uint64_t first_unit, uint32_t n)
     s.phase = P_FETCH; s.flags = 0; s.lb = 0; s.rb1 = n; s.d = 0; s.run = 0; s.t = 0; s.pend = 0; s.wlo = s.whi = s.winv = 0;
     s.g0 = 0; s.u = first_unit; s.unext = first_unit; s.gval = 0; s.gt = 0; s.gmin = kNoGroup; s.gmax = 0; s.gmore = 0; s.gset = 0;
     s.agg_g = kNoGroup; s.agg_n = 0; s.agg_w = 0.0; s.c_total = 0;
+    s.P = 1.0; s.pw0 = s.pw1 = 0.0; s.qn = s.qo = 0;
 }
 
 // Env supplies the side effects:
 //   uint32_t env.load_grp(i)               group of suffix i
 //   uint32_t env.exc_word(blk)             exception mask of SBlock blk (slow path)
-//   double   env.weight(g0, t_end, k)      local-mode weight of the window ending (exclusive) at t_end
+//   uint64_t env.qual8(g0, pos)            local mode: the 8 phred bytes of the read at positions [pos, pos + 8), pos % 8 == 0
+//   uint32_t env.qual1(g0, pos)            ... one phred byte (periodic exact restart of the rolling weight)
+//   double   env.den(q) / env.rden(q)      1 - 10^(-q/10) and its reciprocal (host libm tables)
 //   void     env.unique(group, n, w)       add n (global) or w (local) to the variant's tally
 //   void     env.record(lb)                one more valid window whose k-mer interval starts at lb
 //   void     env.count_fetch(nwin)         a read with nwin windows was presented
@@ -106,7 +114,7 @@ SPEQB_HD void lane32_take_group(Lane32 & s, Cfg32 const & cfg, Env & env)
         lane32_flush_agg(s, env);
         s.agg_g = g;
     }
-    if (cfg.local) s.agg_w += env.weight(s.g0, s.gt, cfg.k);
+    if (cfg.local) s.agg_w += s.pw1;
     s.agg_n += 1u;
 }
 
@@ -133,6 +141,17 @@ SPEQB_HD void lane32_advance(Lane32 & s)
     s.winv >>= 1;
 }
 
+// Loads of a P_STEP iteration in local mode: the quality bytes around the base about to be consumed (t) and around the base
+// that leaves the window with it (t - k), one aligned 8-byte load per stream every 8 bases.  Idempotent: an iteration that
+// does not consume its base (parent jump, failed extension) loads the same bytes again.
+template <class Env>
+SPEQB_HD void lane32_load_qual(Lane32 & s, Cfg32 const & cfg, Env & env)
+{
+    if (!cfg.local || s.t >= s.pend) return;
+    if ((s.t & 7u) == 0u) s.qn = env.qual8(s.g0, s.t);
+    if (s.t >= cfg.k && ((s.t - cfg.k) & 7u) == 0u) s.qo = env.qual8(s.g0, s.t - cfg.k);
+}
+
 // P_STEP.  ld.A / ld.B: the SBlocks at lb / rb1.  The read group of base t has been loaded into s.wlo / s.whi / s.winv by
 // the caller when t is a multiple of 32.  Written select-style so that the common case is one straight run of code.
 template <class Env>
@@ -148,6 +167,7 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
         {
             s.gval = env.load_grp(s.lb);
             s.gt = s.t;
+            s.pw1 = s.pw0;
             s.flags |= F_HAVE_G;
         }
         else if (cfg.record && cfg.skip_unique) env.record(s.lb);
@@ -225,6 +245,22 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
     s.rb1 = keep ? nr : cfg.n;
     s.d = keep ? dd + 1u : 0u;
     s.run = inv ? 0u : s.run + 1u;
+    if (cfg.local)
+    {
+        // the base at position t enters the window; once more than k valid bases are behind the cursor, base t - k leaves
+        if (inv) s.P = 1.0;
+        else
+        {
+            s.P *= env.rden((uint32_t)(s.qn >> (8u * (s.t & 7u))) & 0xFFu);
+            if (s.run > k) s.P *= env.den((uint32_t)(s.qo >> (8u * ((s.t - k) & 7u))) & 0xFFu);
+            if ((s.t & 255u) == 255u && s.run >= k)
+            {
+                double e = 1.0;                                       // periodic exact restart (long reads)
+                for (uint32_t i = s.t + 1u - k; i <= s.t; ++i) e *= env.rden(env.qual1(s.g0, i));
+                s.P = e;
+            }
+        }
+    }
     lane32_advance(s);
     if (s.run >= k)
     {
@@ -232,6 +268,7 @@ SPEQB_HD void lane32_step(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, Env
         if (s.d == k)
         {
             s.flags |= F_PENDING;
+            s.pw0 = s.P;
             if (cfg.record && !cfg.skip_unique) env.record(s.lb);
         }
     }
@@ -264,7 +301,7 @@ SPEQB_HD void lane32_fetch(Lane32 & s, Loads32 const & ld, Cfg32 const & cfg, En
     }
     const uint32_t L = ld.B[4];
     s.g0 = u64of(ld.B[5], ld.B[6]);
-    s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; s.run = 0u; s.t = 0u;
+    s.lb = 0u; s.rb1 = cfg.n; s.d = 0u; s.run = 0u; s.t = 0u; s.P = 1.0;
     s.pend = L >= cfg.k ? L : 0u;                  // L < k: the sliding view is empty
     env.count_fetch(L >= cfg.k ? L - cfg.k + 1u : 0u);
     s.phase = P_STEP;

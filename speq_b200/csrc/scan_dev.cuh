@@ -37,17 +37,78 @@ __device__ __forceinline__ void ld128_if(uint32_t * w, const void * p, bool pred
 struct Smem32
 {
     double * w;                   // [V] local-mode weighted unique tallies
-    uint32_t * cnt;               // [V] unique tallies (global mode)
+    uint32_t * cnt;               // [V] unique tallies (global mode; local mode: windows behind the weights)
     unsigned long long * scal;    // [4] total, ambiguous, lookups, reads
+    double * den;                 // [kQTab] 1 - 10^(-q/10) and
+    double * rden;                // [kQTab] its reciprocal, by phred value (local mode)
 };
+constexpr uint32_t kQTab = 42;    // phred42: 0..41
 __device__ __forceinline__ Smem32 smem32_view(unsigned char * raw, uint32_t V)
 {
     Smem32 s;
     s.scal = reinterpret_cast<unsigned long long *>(raw);
     s.w = reinterpret_cast<double *>(raw + 32);
-    s.cnt = reinterpret_cast<uint32_t *>(raw + 32 + (size_t)V * 8);
+    s.den = s.w + V;
+    s.rden = s.den + kQTab;
+    s.cnt = reinterpret_cast<uint32_t *>(s.rden + kQTab);
     return s;
 }
+
+// Local-error mode: the weight of a window is the product over its k bases of 1 / (1 - 10^(-q/10)) (the reference folds the
+// divisions left to right from 1.0, src/fm_scanner.cpp:454).  Recomputing it per unique hit costs k dependent fp64 divisions
+// and k byte loads; here it is a ROLLING product along the read: times 1/den[q] for the base that enters, times den[q] for the
+// base that leaves (both tabulated by the host's libm), reset behind an invalid base, and recomputed from scratch every 256
+// bases so that the rounding of at most ~2 * 256 + k multiplications separates it from the reference's k divisions: below
+// 1e-13 relative per window, an order of magnitude inside the 1e-12 the local-mode tallies are held to.  The quality bytes of
+// the entering and the leaving base come from two 8-byte streams (one aligned load per 8 bases each, prefetched one ahead).
+struct QRoll
+{
+    double P = 1.0;
+    uint64_t qn = 0ull, qnn = 0ull, qo = 0ull, qon = 0ull;
+    const uint8_t * qb = nullptr;     // quality bytes of the read (32-byte aligned: reads start at 32-base groups)
+    uint32_t lim = 0u;                // loadable bytes: the read's length rounded up to its last 32-base group
+    __device__ __forceinline__ uint64_t ld8(uint32_t pos8) const
+    {
+        uint64_t v = 0ull;
+        if (pos8 < lim) v = load_ro(reinterpret_cast<const uint64_t *>(qb + pos8));
+        return v;
+    }
+    // the lane starts consuming bases of a read of L bases at position t
+    __device__ __forceinline__ void start(const uint8_t * q, uint32_t L, uint32_t t, uint32_t k)
+    {
+        qb = q;
+        lim = (L + 31u) & ~31u;
+        P = 1.0;
+        const uint32_t u = (t > k ? t : k) - k;        // first position of the leaving stream (read when t' = u + k)
+        qn = ld8(t & ~7u);  qnn = ld8((t & ~7u) + 8u);
+        qo = ld8(u & ~7u);  qon = ld8((u & ~7u) + 8u);
+    }
+    // the base at position t has been consumed; run_after = valid bases ending at t (0: the base itself is invalid)
+    __device__ __forceinline__ void step(uint32_t t, uint32_t k, uint32_t run_after, const double * den, const double * rden)
+    {
+        const uint32_t q = (uint32_t)(qn >> (8u * (t & 7u))) & 0xFFu;
+        if ((t & 7u) == 7u) { qn = qnn; qnn = ld8((t & ~7u) + 16u); }
+        uint32_t qold = 1u;
+        if (t >= k)
+        {
+            const uint32_t u = t - k;
+            qold = (uint32_t)(qo >> (8u * (u & 7u))) & 0xFFu;
+            if ((u & 7u) == 7u) { qo = qon; qon = ld8((u & ~7u) + 16u); }
+        }
+        if (run_after == 0u) P = 1.0;
+        else
+        {
+            P *= rden[q];
+            if (run_after > k) P *= den[qold];
+            if ((t & 255u) == 255u && run_after >= k)
+            {
+                double e = 1.0;                                       // periodic exact restart (long reads)
+                for (uint32_t i = t + 1u - k; i <= t; ++i) e *= rden[load_ro(qb + i)];
+                P = e;
+            }
+        }
+    }
+};
 
 
 // The tally side of a scan kernel's Env: weighted / counted unique hits per variant, total / ambiguous / lookups / reads.
@@ -167,6 +228,16 @@ __device__ __forceinline__ void smem32_clear(Smem32 const & sm, uint32_t V)
         sm.w[g] = 0.0;
         sm.cnt[g] = 0u;
     }
+}
+// ... and the phred tables of local mode (host libm values, ScanArgs::qden / qrden)
+__device__ __forceinline__ void smem32_tables(Smem32 const & sm, ScanArgs const & a, bool local)
+{
+    if (local)
+        for (uint32_t q = threadIdx.x; q < kQTab; q += blockDim.x)
+        {
+            sm.den[q] = a.qden[q];
+            sm.rden[q] = a.qrden[q];
+        }
     __syncthreads();
 }
 

@@ -264,6 +264,9 @@ constexpr uint32_t kClaimChunkW = 4;   // reads a warp claims at a time when it 
 #ifndef SPEQB_HMINB
 #define SPEQB_HMINB 4
 #endif
+#ifndef SPEQB_HMINB_LOCAL
+#define SPEQB_HMINB_LOCAL 2
+#endif
 #ifndef SPEQB_EXP_FREE_INPUT
 #define SPEQB_EXP_FREE_INPUT 0
 #endif
@@ -272,7 +275,7 @@ constexpr int kWin = SPEQB_KWIN;
 // WPR (long reads): the 32 lanes of a warp share one read -- lane l takes windows [l * per, (l + 1) * per), per = ceil(nwin / 32),
 // pre-rolling the k-1 bases before its first window; the ambiguity state of the read is the warp's min / max variant.
 template <int MODE, bool WPR, bool MASK>
-__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
+__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
                                                                                   const BatchView b, const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
@@ -280,6 +283,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem32 sm = smem32_view(smem_raw, a.V);
     smem32_clear(sm, a.V);
+    smem32_tables(sm, a, LOCAL);
     Tally32<MODE> env{b, a, sm};
 
     const uint32_t k = a.k;
@@ -307,6 +311,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
     uint32_t c_total = 0u;
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
+    QRoll qr;                                    // LOCAL: the rolling phred weight of the window that ends at the cursor
     uint32_t rs = kNoRun, rl = 0xFFFFFFFDu;      // RECORD with positions: the open run [rs, rl] of consecutive text positions
     auto run_flush = [&]() {
         if (rs != kNoRun)
@@ -334,6 +339,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
         const uint32_t o = t & 31u;
         key = (key << 2) | ((uint32_t)(cb >> (2u * o)) & 3u);
         run = ((ci >> o) & 1u) ? 0u : run + 1u;                   // N / low quality: no window may contain this base
+        if (LOCAL) qr.step(t, k, run, sm.den, sm.rden);
         t += 1u;
         if ((t & 31u) == 0u) next_group();
     };
@@ -426,6 +432,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                     nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
                     ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
                 }
+                if (LOCAL) qr.start(b.qual + 32ull * g0, L, t, k);
             }
             phase = H_RUN;
         }
@@ -436,6 +443,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
             uint32_t w[kWin][8];
             uint32_t pb[kWin], want_lo[kWin], want_hi[kWin];
             bool due[kWin];
+            double pw[kWin];                                      // LOCAL: weight of the window that ends with base j
             const uint32_t t0 = t, o = t & 31u;
             const uint32_t nbase = pend - t < (uint32_t)kWin ? pend - t : (uint32_t)kWin;
             // the next kWin bases in one register each (they may straddle into the prefetched group)
@@ -453,6 +461,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                 {
                     key = (key << 2) | ((bits >> (2 * j)) & 3u);
                     run = ((ibits >> j) & 1u) ? 0u : run + 1u;    // N / low quality: no window may contain this base
+                    if (LOCAL) { qr.step(t0 + (uint32_t)j, k, run, sm.den, sm.rden); pw[j] = qr.P; }
                     due[j] = run >= k;
                 }
                 if (due[j])
@@ -501,7 +510,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_HMINB) s
                                 agg_g = g; agg_n = 0u; agg_w = 0.0;
                                 uset.add(g);
                             }
-                            if (LOCAL) agg_w += env.weight(g0, t0 + (uint32_t)j + 1u, k);
+                            if (LOCAL) agg_w += pw[j];
                             agg_n += 1u;
                         }
                         else if (RECORD)
@@ -762,6 +771,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem32 sm = smem32_view(smem_raw, a.V);
     smem32_clear(sm, a.V);
+    smem32_tables(sm, a, LOCAL);
     Tally32<MODE> env{b, a, sm};
 
     const uint32_t k = a.k;

@@ -93,6 +93,15 @@ struct HostEnv32
     uint64_t & total, & amb, & look;
     uint32_t load_grp(uint32_t i) const { return h.grp[i]; }
     uint32_t exc_word(uint32_t blk) const { return h.blocks[blk >> 1].exc[blk & 1u]; }
+    uint64_t qual8(uint64_t g0, uint32_t pos) const
+    {
+        uint64_t v;
+        memcpy(&v, qual + 32u * g0 + pos, 8);
+        return v;
+    }
+    uint32_t qual1(uint64_t g0, uint32_t pos) const { return qual[32u * g0 + pos]; }
+    double den(uint32_t q) const { return qden[q]; }
+    double rden(uint32_t q) const { return 1.0 / qden[q]; }
     double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
     {
         const uint8_t * q = qual + 32u * g0 + (t_end - k);
@@ -280,6 +289,7 @@ int sim_scan(const uint8_t * const * texts, const uint64_t * lens, uint32_t S, c
                             s.wlo = (uint32_t)w; s.whi = (uint32_t)(w >> 32);
                             s.winv = inv[s.g0 + (s.t >> 5)];
                         }
+                        lane32_load_qual(s, cfg, env);
                         lane32_step(s, ld, cfg, env);
                     }
                     else if (s.phase == P_UP)
