@@ -6,7 +6,7 @@ IFS=";" read -ra VS <<< "${SWEEP:-base}"
 for v in "${VS[@]}"; do
   extra=""; [ "$v" != "base" ] && extra="$v"
   SPEQB_NVCC_EXTRA="$extra" python -m speq_b200.build --force > /dev/null 2>&1 || { echo "build failed: $v" | tee -a $O/r2_sweep.txt; continue; }
-  for c in ${CONFIGS:-"C2:10000000 C3:25000000"}; do
+  for c in ${CONFIGS:-C2:10000000 C3:25000000}; do
     set -- ${c/:/ }
     timeout 300 python bench.py --config $1 --reads $2 --no-cpu --no-e2e --no-probe --steps 10 $BENCH_ARGS 2>/dev/null | python -c "
 import json,sys
