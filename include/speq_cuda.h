@@ -200,7 +200,9 @@ int speqg_scan_submit_raw(speqg_scan * scan, const uint8_t * seq, const uint8_t 
  * the host and submits it with speqg_scan_submit_raw (tallies add up, the order of regions does not matter).
  * *ticket (may be NULL): pass to speqg_scan_wait_ticket before `bytes` is overwritten. */
 int speqg_scan_submit_fastq(speqg_scan * scan, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket);
-/* wait for the host->device copy of ONE earlier submit_fastq (its host buffer may then be refilled; later copies and all kernels
+/* ticket of the most recent submit that copied host memory (submit_packed / submit_raw / submit_fastq); 0 before the first */
+int speqg_scan_last_ticket(speqg_scan * scan, uint64_t * ticket);
+/* wait for the host->device copy of ONE earlier submit (its host buffer may then be refilled; later copies and all kernels
  * keep running) */
 int speqg_scan_wait_ticket(speqg_scan * scan, uint64_t ticket);
 /* regions submitted since open / reset that were not scanned because they are not strict 4-line FASTQ.  Syncs the scan.

@@ -673,6 +673,14 @@ int speqg_scan_submit_fastq(speqg_scan * s, const uint8_t * bytes, uint64_t n_by
     SPEQG_CATCH
 }
 
+int speqg_scan_last_ticket(speqg_scan * s, uint64_t * ticket)
+{
+    SPEQG_TRY
+    need(s != nullptr && ticket != nullptr, "NULL argument");
+    *ticket = s->tickets;
+    SPEQG_CATCH
+}
+
 int speqg_scan_wait_ticket(speqg_scan * s, uint64_t ticket)
 {
     SPEQG_TRY

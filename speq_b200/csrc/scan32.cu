@@ -50,7 +50,7 @@ template <int MODE, bool G8> struct Env32 : Tally32<MODE>
 };
 
 #ifndef SPEQB_RMINB_LOCAL
-#define SPEQB_RMINB_LOCAL 3
+#define SPEQB_RMINB_LOCAL 4
 #endif
 template <int MODE, bool G8, bool MASK>
 __global__ void __launch_bounds__(kBlock32, (MODE & M_LOCAL) ? SPEQB_RMINB_LOCAL : 4) scan32_kernel(const FBlock * __restrict__ fblk, const DevIndex ix, const BatchView b,

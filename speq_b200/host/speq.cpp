@@ -13,6 +13,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <unistd.h>
 #include <cstring>
 #include <fstream>
 #include <iostream>
@@ -221,14 +222,23 @@ struct host_batch
     uint8_t * qual = nullptr;
     uint64_t * offsets = nullptr;
     uint64_t cap_bytes = 0, cap_reads = 0, n_reads = 0, n_bytes = 0;
-    void alloc(uint64_t bytes, uint64_t reads)
+    // with_records = false: only the byte buffer (raw FASTQ regions for the device parser); the quality and offset arrays of
+    // the record paths are pinned on first use (ensure_records) -- pinning is a large part of a short run's start-up
+    void alloc(uint64_t bytes, uint64_t reads, bool with_records = true)
     {
         release();
         void * p = nullptr;
         ck(speqg_host_alloc(bytes, &p), "speqg_host_alloc"); seq = static_cast<uint8_t *>(p);
-        ck(speqg_host_alloc(bytes, &p), "speqg_host_alloc"); qual = static_cast<uint8_t *>(p);
-        ck(speqg_host_alloc((reads + 1) * 8, &p), "speqg_host_alloc"); offsets = static_cast<uint64_t *>(p);
-        cap_bytes = bytes; cap_reads = reads; n_reads = 0; n_bytes = 0; offsets[0] = 0;
+        cap_bytes = bytes; cap_reads = reads; n_reads = 0; n_bytes = 0;
+        if (with_records) ensure_records();
+    }
+    void ensure_records()
+    {
+        if (qual) return;
+        void * p = nullptr;
+        ck(speqg_host_alloc(cap_bytes, &p), "speqg_host_alloc"); qual = static_cast<uint8_t *>(p);
+        ck(speqg_host_alloc((cap_reads + 1) * 8, &p), "speqg_host_alloc"); offsets = static_cast<uint64_t *>(p);
+        offsets[0] = 0;
     }
     void release()
     {
@@ -243,7 +253,7 @@ struct host_batch
         n_bytes += s.size();
         offsets[++n_reads] = n_bytes;
     }
-    void clear() { n_reads = 0; n_bytes = 0; offsets[0] = 0; }
+    void clear() { n_reads = 0; n_bytes = 0; if (offsets) offsets[0] = 0; }
 };
 
 struct device_lane
@@ -275,8 +285,11 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
         host_batch & b = L.buf[L.cur];
         if (b.n_reads == 0) return;
         ck(speqg_scan_submit_raw(L.scan, b.seq, b.qual, b.offsets, b.n_reads, SPEQG_ENC_ASCII), "speqg_scan_submit_raw");
+        ck(speqg_scan_last_ticket(L.scan, &L.ticket[L.cur]), "speqg_scan_last_ticket");
         L.cur ^= 1;
-        ck(speqg_scan_wait_copies(L.scan), "speqg_scan_wait_copies");   // the other buffer's copy (submitted earlier) is done
+        // only the copy that last read the buffer about to be refilled has to be over; the one just queued keeps running
+        // while the host parses the next batch
+        ck(speqg_scan_wait_ticket(L.scan, L.ticket[L.cur]), "speqg_scan_wait_ticket");
         L.buf[L.cur].clear();
     };
     // ---- plain 4-line FASTQ: mapped file, indexed and copied into the pinned batches by the parser pool (-t); anything
@@ -317,6 +330,7 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
             ck(speqg_scan_fastq_rejected(L.scan, rej.data(), n_rej, &n_rej), "speqg_scan_fastq_rejected");
             ck(speqg_scan_wait_ticket(L.scan, L.ticket[0]), "speqg_scan_wait_ticket");
             ck(speqg_scan_wait_ticket(L.scan, L.ticket[1]), "speqg_scan_wait_ticket");
+            L.buf[0].ensure_records(); L.buf[1].ensure_records();
             L.buf[0].clear(); L.buf[1].clear();
             for (uint64_t id : rej)
             {
@@ -341,6 +355,9 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
         }
         serial = off1 < m1.size();
     }
+    if (serial || paired || getenv("SPEQ_HOST_FASTQ") || !speq::io::fastq_map::eligible(args.in_file_reads_path_1))
+        for (auto & L : lanes) { L.buf[0].ensure_records(); L.buf[1].ensure_records(); }
+    if (!paired && !getenv("SPEQ_HOST_FASTQ") && speq::io::fastq_map::eligible(args.in_file_reads_path_1)) {}
     else if (speq::io::fastq_map::eligible(args.in_file_reads_path_1) && (!paired || speq::io::fastq_map::eligible(args.in_file_reads_path_2)))
     {
         serial = false;
@@ -541,8 +558,8 @@ int do_scan(cmd_arguments & args)
         {
             for (unsigned d = 0; d < gpus; ++d)
             {
-                lanes[d].buf[0].alloc(cap_bytes, cap_reads);
-                lanes[d].buf[1].alloc(cap_bytes, cap_reads);
+                lanes[d].buf[0].alloc(cap_bytes, cap_reads, false);
+                lanes[d].buf[1].alloc(cap_bytes, cap_reads, false);
             }
         }
         catch (std::exception const & e) { prep_error = e.what(); }
@@ -779,5 +796,9 @@ int main(int argc, char ** argv)
         std::cerr << "terminate called after throwing an instance of an exception\n  what():  " << e.what() << "\n";
         return 134;
     }
-    return 0;
+    // every result is written: leave without tearing the CUDA context down handle by handle (about 0.3 s of a 1.5 s run)
+    std::cout.flush();
+    std::cerr.flush();
+    fflush(nullptr);
+    _exit(0);
 }
