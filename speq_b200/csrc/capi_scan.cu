@@ -161,8 +161,8 @@ scan_refine_view refine_view(speqg_scan * s)
     if (s->slot_mult_dirty && s->d_mult)
     {
         device_guard guard(s->device);
-        if (s->d_slot_mult) CK(launch_ktable_fold_mult(s->kt, s->view, s->p.k, s->d_slot_mult, s->d_mult, s->compute));
-        if (s->d_pair_mult) CK(launch_kpair_fold_mult(s->kp, s->view, s->p.k, s->d_pair_mult, s->d_mult, s->compute));
+        if (s->d_slot_mult || s->kt.wide) CK(launch_ktable_fold_mult(s->kt, s->view, s->p.k, s->d_slot_mult, s->d_mult, s->compute));
+        if (s->d_pair_mult || s->kp.wide) CK(launch_kpair_fold_mult(s->kp, s->view, s->p.k, s->d_pair_mult, s->d_mult, s->compute));
         s->slot_mult_dirty = false;
     }
     // k-mer table with positions: recorded runs -> counts per text position -> mult[lb]
@@ -393,10 +393,18 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             uint32_t max_len = 0;
             for (uint32_t L : h.t_len) max_len = L > max_len ? L : max_len;
             s->d_kstat = dev_alloc<unsigned long long>(2);
+            int l2 = 0;
+            CK(cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device));
+            s->npos = 32ull * h.t_bases.size();
+            const bool record = params->record_multiplicity != 0, no_wide = getenv("SPEQB_NO_WIDE") != nullptr;
             for (uint32_t grow = 0;; ++grow)
             {
                 need(grow < 4 && ktable_geometry(params->k, ub, grow, &s->kt), "k-mer table too large");
-                s->kt.slots = dev_alloc<uint64_t>(4ull * ((uint64_t)s->kt.nbmask + 1));
+                // a table beyond L2 that has to count hits per slot keeps the counters inside its (then 64-byte) buckets
+                const bool big = 32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 || getenv("SPEQB_FORCE_WIDE");
+                const bool pair = s->algo == SPEQG_ALGO_KPAIR || (auto_algo && idx->host.V <= kMaxGroupsPair && big);
+                s->kt.wide = record && big && !no_wide && (pair || getenv("SPEQB_NO_RUNS") || !ktable_positions_fit(s->kt, s->npos)) ? 1u : 0u;
+                s->kt.slots = dev_alloc<uint64_t>((4ull << s->kt.wide) * ((uint64_t)s->kt.nbmask + 1));
                 CK(launch_ktable_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, di.t_group, h.S, max_len, s->kt, params->k,
                                        s->d_kstat, s->compute));
                 unsigned long long st[2] = {0, 0};
@@ -413,8 +421,6 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             {
                 // A table that does not stay in L2 is bound by the HBM random-sector rate: halving the probes (two windows
                 // per probe) pays there (C4: +43 %), while on an L2-resident table the single-window kernel is faster.
-                int l2 = 0;
-                CK(cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device));
                 if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3) s->algo = SPEQG_ALGO_KPAIR;
             }
             if (params->record_multiplicity)
@@ -422,8 +428,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 // Single-window table scan: hits on k-mers held by several variants are recorded as runs over the positions of
                 // the packed texts (two atomics per run of consecutive hits) when a position fits into the slot next to the
                 // remainder; else, and for the pair-table scan, one atomic per hit on a per-slot counter.
-                s->npos = 32ull * h.t_bases.size();
-                if (s->algo == SPEQG_ALGO_KTABLE && !getenv("SPEQB_NO_RUNS") && ktable_positions_fit(s->kt, s->npos))
+                if (s->algo == SPEQG_ALGO_KTABLE && !s->kt.wide && !getenv("SPEQB_NO_RUNS") && ktable_positions_fit(s->kt, s->npos))
                 {
                     s->kt.pshift = s->kt.rbits + 3u;
                     CK(launch_ktable_canon(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, h.S, max_len, s->kt, params->k, s->compute));
@@ -431,7 +436,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                     s->scan_tmp_bytes = kpos_fold_tmp_bytes(s->npos);
                     CK(cudaMalloc(&s->d_scan_tmp, s->scan_tmp_bytes));
                 }
-                else
+                else if (!s->kt.wide)
                 {
                     const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
                     s->d_slot_mult = dev_alloc<unsigned long long>(n_slots);
@@ -445,7 +450,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 for (uint32_t grow = 0;; ++grow)
                 {
                     need(grow < 4 && ktable_geometry(params->k + 1, ub2, grow, &s->kp), "pair table too large");
-                    s->kp.slots = dev_alloc<uint64_t>(4ull * ((uint64_t)s->kp.nbmask + 1));
+                    s->kp.wide = record && !no_wide && (32ull * ((uint64_t)s->kp.nbmask + 1) > (uint64_t)l2 / 4 * 3 || getenv("SPEQB_FORCE_WIDE")) ? 1u : 0u;
+                    s->kp.slots = dev_alloc<uint64_t>((4ull << s->kp.wide) * ((uint64_t)s->kp.nbmask + 1));
                     CK(launch_kpair_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, h.S, max_len, s->kt, s->kp, params->k,
                                           s->d_kstat, s->compute));
                     unsigned long long st[2] = {0, 0};
@@ -457,7 +463,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                     CK(cudaFree(s->kp.slots));
                     s->kp.slots = nullptr;
                 }
-                if (params->record_multiplicity)
+                if (params->record_multiplicity && !s->kp.wide)
                 {
                     const uint64_t n_slots = 4ull * ((uint64_t)s->kp.nbmask + 1);
                     s->d_pair_mult = dev_alloc<unsigned long long>(n_slots);
@@ -548,6 +554,8 @@ int speqg_scan_reset(speqg_scan * s)
     if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
     if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
     if (s->d_pair_mult) CK(cudaMemsetAsync(s->d_pair_mult, 0, 4ull * ((uint64_t)s->kp.nbmask + 1) * 8, s->compute));
+    if (s->kt.slots && s->kt.wide) CK(launch_ktable_zero_counters(s->kt, s->compute));
+    if (s->kp.slots && s->kp.wide) CK(launch_ktable_zero_counters(s->kp, s->compute));
     s->slot_mult_dirty = false;
     s->launches = 0;
     SPEQG_CATCH
@@ -887,9 +895,10 @@ int speqg_scan_info(speqg_scan * s, uint32_t * algorithm, uint64_t * structure_b
     if (algorithm) *algorithm = s->algo;
     if (structure_bytes)
     {
-        if (s->algo == SPEQG_ALGO_KTABLE) *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1);
+        if (s->algo == SPEQG_ALGO_KTABLE) *structure_bytes = (32ull << s->kt.wide) * ((uint64_t)s->kt.nbmask + 1);
         else if (s->algo == SPEQG_ALGO_KPAIR)
-            *structure_bytes = 32ull * ((uint64_t)s->kt.nbmask + 1) + 32ull * ((uint64_t)s->kp.nbmask + 1) + (s->kt.filt ? (1ull << s->filt_bits) / 8 : 0);
+            *structure_bytes = (32ull << s->kt.wide) * ((uint64_t)s->kt.nbmask + 1) + (32ull << s->kp.wide) * ((uint64_t)s->kp.nbmask + 1) +
+                               (s->kt.filt ? (1ull << s->filt_bits) / 8 : 0);
         else if (s->algo == SPEQG_ALGO_ROLLING) *structure_bytes = sizeof(FBlock) * (s->idx->host.n / 32 + 1);
         else *structure_bytes = sizeof(KBlock) * s->idx->host.blocks.size();
     }

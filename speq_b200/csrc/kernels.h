@@ -108,10 +108,13 @@ struct KTabView
     uint64_t mul, mul_inv;        // invertible multiplicative hash mod 4^k and its inverse
     uint32_t * filt;              // optional presence filter (pair-table scan): bit (hash >> fshift) is set for every stored k-mer
     uint32_t fshift;
+    uint32_t wide;                // 1: 64-byte buckets = four slots + their four record-mode counters (tables beyond L2)
     uint32_t pshift;              // != 0: slots of k-mers held by several variants carry, from this bit up to bit 62, the
                                   // smallest position (32 * group + offset in the packed texts) where the k-mer starts
 };
 bool ktable_positions_fit(KTabView const & kt, uint64_t npos);
+cudaError_t launch_ktable_clear(KTabView const & kt, cudaStream_t st);
+cudaError_t launch_ktable_zero_counters(KTabView const & kt, cudaStream_t st);
 cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                 uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k, cudaStream_t st);
 size_t kpos_fold_tmp_bytes(uint64_t npos);

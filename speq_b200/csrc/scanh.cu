@@ -55,6 +55,16 @@ constexpr uint32_t kNoRun = 0xFFFFFFFFu;
 // consecutive windows of a read that hit a conserved stretch then have consecutive positions, and the scan records a RUN of
 // hits with two atomics on a difference array (ScanArgs::diff) instead of one atomic per window.
 __device__ __forceinline__ bool slot_multi(uint32_t hi) { return (hi >> 31) != 0u; }
+// Addressing.  Narrow table (wide = 0): bucket b = slots[4b, 4b + 4), one 32-byte sector; the record-mode counters live in a
+// side array.  Wide table (wide = 1, tables beyond L2 with record_multiplicity): bucket b = a 64-byte record, slots in its first
+// sector and the four counters of those slots in its second -- the counter atomic of a hit then goes to the line (and page)
+// the probe has just brought in, instead of paying a second address translation and DRAM access somewhere else (section 8).
+__device__ __forceinline__ const uint64_t * kt_bucket(KTabView const & kt, uint32_t bk) { return kt.slots + ((uint64_t)bk << (2u + kt.wide)); }
+__device__ __forceinline__ uint64_t * kt_slot(KTabView const & kt, uint64_t i) { return kt.slots + ((i >> 2) << (2u + kt.wide)) + (i & 3ull); }
+__device__ __forceinline__ unsigned long long * kt_counter(KTabView const & kt, unsigned long long * side, uint64_t i)
+{
+    return kt.wide ? reinterpret_cast<unsigned long long *>(kt_slot(kt, i) + 4) : side + i;
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // build: one thread per 32-base group of a text; the 32 windows that start in the group
@@ -71,7 +81,7 @@ __device__ __forceinline__ bool ktable_insert(KTabView const & kt, uint64_t key,
         const uint64_t want = r | ((uint64_t)d << kt.rbits);
         for (int j = 0; j < 4; ++j)
         {
-            unsigned long long * p = reinterpret_cast<unsigned long long *>(kt.slots + 4ull * bk + j);
+            unsigned long long * p = reinterpret_cast<unsigned long long *>(kt_slot(kt, 4ull * bk + j));
             unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(p);
             while (true)
             {
@@ -139,10 +149,11 @@ __global__ void __launch_bounds__(kBlockH) ktable_fold_mult_kernel(const KTabVie
     const uint64_t n_slots = 4ull * ((uint64_t)kt.nbmask + 1ull);
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
     {
-        const unsigned long long m = slot_mult[i];
+        unsigned long long * cnt = kt_counter(kt, slot_mult, i);
+        const unsigned long long m = *cnt;
         if (m == 0ull) continue;
-        slot_mult[i] = 0ull;
-        const uint64_t w = kt.slots[i];
+        *cnt = 0ull;
+        const uint64_t w = *kt_slot(kt, i);
         const uint32_t d = (uint32_t)(w >> kt.rbits) & 7u;
         const uint32_t home = ((uint32_t)(i >> 2) - d) & kt.nbmask;
         const uint64_t h = ((uint64_t)home << kt.rbits) | (w & kt.rmask);
@@ -166,7 +177,7 @@ __device__ __forceinline__ uint64_t ktable_slot_of(KTabView const & kt, uint64_t
         bool last_free = false;
         for (int j = 0; j < 4; ++j)
         {
-            const uint64_t w = *reinterpret_cast<const volatile uint64_t *>(kt.slots + 4ull * bk + j);
+            const uint64_t w = *reinterpret_cast<const volatile uint64_t *>(kt_slot(kt, 4ull * bk + j));
             if (((w ^ want) & kmask) == 0ull) return 4ull * bk + j;
             if (j == 3) last_free = w == kSlotFree;
         }
@@ -205,10 +216,10 @@ __global__ void __launch_bounds__(kBlockH) ktable_canon_kernel(const uint64_t * 
             if (pos < gi * 32u || run < k) continue;
             const uint64_t si = ktable_slot_of(kt, key & kt.mask_b);
             if (si == ~0ull) continue;
-            const uint64_t w = kt.slots[si];
+            const uint64_t w = *kt_slot(kt, si);
             if (!(w >> 63)) continue;
             const uint64_t start = 32ull * g0 + (pos + 1u - k);
-            atomicMin(reinterpret_cast<unsigned long long *>(kt.slots + si), (1ull << 63) | (start << kt.pshift) | (w & low_mask));
+            atomicMin(reinterpret_cast<unsigned long long *>(kt_slot(kt, si)), (1ull << 63) | (start << kt.pshift) | (w & low_mask));
         }
     }
 }
@@ -242,7 +253,7 @@ __global__ void __launch_bounds__(kBlockH) kfilter_build_kernel(const KTabView k
     const uint64_t n_slots = 4ull * ((uint64_t)kt.nbmask + 1ull);
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
     {
-        const uint64_t w = kt.slots[i];
+        const uint64_t w = *kt_slot(kt, i);
         if (w == ~0ull) continue;
         const uint32_t d = (uint32_t)(w >> kt.rbits) & 7u;
         const uint32_t home = ((uint32_t)(i >> 2) - d) & kt.nbmask;
@@ -476,7 +487,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
                     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                                  : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                 : "l"(kt.slots + 4ull * pb[j]));
+                                 : "l"(kt_bucket(kt, pb[j])));
                 }
             }
             t += nbase;
@@ -523,7 +534,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                                 if (p == rl + 1u) rl = p;
                                 else { run_flush(); rs = p; rl = p; }
                             }
-                            else atomicAdd(slot_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
+                            else atomicAdd(kt_counter(kt, slot_mult, 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
                         }
                         break;
                     }
@@ -537,7 +548,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
                     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                                  : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                 : "l"(kt.slots + 4ull * pb[j]));
+                                 : "l"(kt_bucket(kt, pb[j])));
                 }
             }
         }
@@ -673,7 +684,7 @@ __device__ __forceinline__ KFound ktable_find(KTabView const & kt, uint64_t key)
         uint32_t w[8];
         asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                     : "l"(kt.slots + 4ull * bk));
+                     : "l"(kt_bucket(kt, bk)));
         f.probes += 1u;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -732,10 +743,11 @@ __global__ void __launch_bounds__(kBlockH) kpair_fold_mult_kernel(const KTabView
     const uint64_t n_slots = 4ull * ((uint64_t)kp.nbmask + 1ull);
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
     {
-        const unsigned long long m = slot_mult[i];
+        unsigned long long * cnt = kt_counter(kp, slot_mult, i);
+        const unsigned long long m = *cnt;
         if (m == 0ull) continue;
-        slot_mult[i] = 0ull;
-        const uint64_t w = kp.slots[i];
+        *cnt = 0ull;
+        const uint64_t w = *kt_slot(kp, i);
         const uint32_t d = (uint32_t)(w >> kp.rbits) & 7u;
         const uint32_t home = ((uint32_t)(i >> 2) - d) & kp.nbmask;
         const uint64_t h = ((uint64_t)home << kp.rbits) | (w & kp.rmask);
@@ -982,7 +994,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     pb[j] = (uint32_t)(h >> kp.rbits);
                     const uint64_t want = h & kp.rmask;
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                    ldg256_stream(w[j], kp.slots + 4ull * pb[j], pol_stream);
+                    ldg256_stream(w[j], kt_bucket(kp, pb[j]), pol_stream);
                 }
             }
             // ---- pairs: one probe answers both windows
@@ -1003,7 +1015,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         const uint32_t vv = (h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7]) >> 16;
                         const uint32_t v1 = vv & 0xFFu, v2 = vv >> 8;
                         // a k-mer of one variant needs no record (see scanh_kernel); the fold skips that half of the pair
-                        if (RECORD && (v1 == 0xFFu || v2 == 0xFFu)) atomicAdd(pair_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
+                        if (RECORD && (v1 == 0xFFu || v2 == 0xFFu)) atomicAdd(kt_counter(kp, pair_mult, 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
                         if (v1 != 0xFFu) tally(v1, t0 + 2u * (uint32_t)j + 1u);
                         if (v2 != 0xFFu) tally(v2, t0 + 2u * (uint32_t)j + 2u);
                         mode[j] = 0u;                             // answered
@@ -1015,7 +1027,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     pb[j] = (pb[j] + 1u) & kp.nbmask;
                     const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kp.rbits);
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                    ldg256_stream(w[j], kp.slots + 4ull * pb[j], pol_stream);
+                    ldg256_stream(w[j], kt_bucket(kp, pb[j]), pol_stream);
                 }
             }
             // ---- what is left: unpaired windows and the halves of missed pairs go through the k-mer table, all first probes
@@ -1031,7 +1043,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     sb[i] = (uint32_t)(h >> kt.rbits);
                     const uint64_t want = h & kt.rmask;
                     sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
-                    ldg256_stream(sw[i], kt.slots + 4ull * sb[i], pol_stream);
+                    ldg256_stream(sw[i], kt_bucket(kt, sb[i]), pol_stream);
                 }
 #pragma unroll
                 for (int i = 0; i < 2 * kPair; ++i)
@@ -1049,7 +1061,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         {
                             const uint32_t hi = h0 ? sw[i][1] : h1 ? sw[i][3] : h2 ? sw[i][5] : sw[i][7];
                             if (!slot_multi(hi)) tally(hi >> 16, t0 + (uint32_t)i + 1u);
-                            else if (RECORD) atomicAdd(slot_mult + 4ull * sb[i] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);
+                            else if (RECORD) atomicAdd(kt_counter(kt, slot_mult, 4ull * sb[i] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
                             break;
                         }
                         if ((sw[i][6] & sw[i][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;   // the k-mer does not occur in the index
@@ -1058,7 +1070,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         sb[i] = (sb[i] + 1u) & kt.nbmask;
                         const uint64_t want = u64of(sl[i], sh_[i]) + (1ull << kt.rbits);
                         sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
-                        ldg256_stream(sw[i], kt.slots + 4ull * sb[i], pol_stream);
+                        ldg256_stream(sw[i], kt_bucket(kt, sb[i]), pol_stream);
                     }
                 }
             }
@@ -1204,6 +1216,7 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
     kt->filt = nullptr;
     kt->fshift = 0u;
     kt->pshift = 0u;
+    kt->wide = 0u;
     return true;
 }
 
@@ -1281,12 +1294,40 @@ cudaError_t launch_scanp(KTabView const & kt, KTabView const & kp, unsigned long
     return cudaGetLastError();
 }
 
+// wide tables: slots_too != 0: all slots free (all ones) and the counters zero; else only the counters back to zero
+__global__ void __launch_bounds__(kBlockH) ktable_wide_clear_kernel(uint64_t * __restrict__ slots, const uint64_t buckets, const int slots_too)
+{
+    // one 16-byte store per thread: 4 threads per 64-byte record
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < buckets * 4ull; i += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const uint32_t part = (uint32_t)(i & 3ull);
+        if (part < 2u && !slots_too) continue;
+        const uint32_t v = part < 2u ? 0xFFFFFFFFu : 0u;
+        reinterpret_cast<uint4 *>(slots)[i] = make_uint4(v, v, v, v);
+    }
+}
+// all slots free; wide tables: their counters zero
+cudaError_t launch_ktable_clear(KTabView const & kt, cudaStream_t st)
+{
+    const size_t buckets = (size_t)kt.nbmask + 1;
+    if (!kt.wide) return cudaMemsetAsync(kt.slots, 0xFF, buckets * 32, st);
+    ktable_wide_clear_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt.slots, buckets, 1);
+    return cudaGetLastError();
+}
+// wide tables: the counters back to zero (speqg_scan_reset)
+cudaError_t launch_ktable_zero_counters(KTabView const & kt, cudaStream_t st)
+{
+    if (!kt.wide) return cudaSuccess;
+    ktable_wide_clear_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt.slots, (size_t)kt.nbmask + 1, 0);
+    return cudaGetLastError();
+}
+
 // the pair table: every N-free (k+1)-mer of the texts -> the values of its two k-mers (looked up in the k-mer table kt)
 cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, KTabView const & kp, uint32_t k,
                                unsigned long long * n_keys, cudaStream_t st)
 {
-    cudaError_t e = cudaMemsetAsync(kp.slots, 0xFF, ((size_t)kp.nbmask + 1) * 32, st);
+    cudaError_t e = launch_ktable_clear(kp, st);
     if (e == cudaSuccess) e = cudaMemsetAsync(n_keys, 0, 16, st);
     if (e != cudaSuccess) return e;
     if (n_texts == 0 || max_len < k + 1) return cudaSuccess;
@@ -1312,7 +1353,7 @@ cudaError_t launch_ktable_build(const uint64_t * t_bases, const uint32_t * t_inv
                                 const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
                                 unsigned long long * n_keys, cudaStream_t st)
 {
-    cudaError_t e = cudaMemsetAsync(kt.slots, 0xFF, ((size_t)kt.nbmask + 1) * 32, st);
+    cudaError_t e = launch_ktable_clear(kt, st);
     if (e == cudaSuccess) e = cudaMemsetAsync(n_keys, 0, 16, st);
     if (e != cudaSuccess) return e;
     if (n_texts == 0 || max_len < k) return cudaSuccess;

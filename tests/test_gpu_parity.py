@@ -598,3 +598,21 @@ def test_submit_fastq_device_parser(lib, name, algorithm):
     assert r.reads == 2 and r.lookups == 0
     sc.close()
     idx.close()
+
+
+@pytest.mark.parametrize("name", ["global_single", "local_paired", "refs_with_n"])
+@pytest.mark.parametrize("variant", ["wide", "slot_counters"])
+def test_record_mode_variants(lib, name, variant, monkeypatch):
+    """The record-mode layouts a small index never picks by itself, forced through the library's measurement switches:
+    `wide` = 64-byte buckets with the per-slot counters inside (tables beyond L2), `slot_counters` = the per-slot side array
+    instead of runs over text positions.  Same refinement as the fixture (oracle/_ref) for the k-mer table and the pair table."""
+    monkeypatch.setenv("SPEQB_NO_RUNS", "1")
+    if variant == "wide":
+        monkeypatch.setenv("SPEQB_FORCE_WIDE", "1")
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)
+    for algorithm in (capi.ALGO_KTABLE, capi.ALGO_KPAIR):
+        out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
+                             fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], batch_reads=64, algorithm=algorithm)
+        _compare(out, exp, len(counts))
