@@ -616,3 +616,44 @@ def test_record_mode_variants(lib, name, variant, monkeypatch):
         out = driver.run_all(scaff, gs, counts, _reads(seqs, quals), k=run["k"], phred_cutoff=run.get("phred_cutoff", 30),
                              fixed_accuracy=run["fixed_accuracy"], paired=run["paired"], batch_reads=64, algorithm=algorithm)
         _compare(out, exp, len(counts))
+
+
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR])
+def test_fusion_sets_many_variants(lib, algorithm):
+    """More than 64 variants: the key of an ambiguous unit is (smallest, largest, further variants in between) instead of a bit
+    mask.  Checked against the same scan run on every unit alone, lane-per-read and warp-per-read forms."""
+    rng = np.random.default_rng(9)
+    V, G, k = 70, 2500, 15
+    scaff = [np.where((s := rng.integers(0, 4, G)) == 3, 4, s).astype(np.uint8) for _ in range(V)]   # unrelated variants
+    idx = engine.Index.from_scaffolds(scaff, list(range(V)), V)
+    letters = np.frombuffer(b"ACGNT", np.uint8)
+    for L, R in ((150, 180), (2400, 24)):
+        parts = []
+        for i in range(R):
+            a, b, c = rng.choice(V, 3, replace=False)
+            p = int(rng.integers(0, G - L + 1))
+            r = scaff[int(a)][p:p + L].copy()
+            if i % 3 >= 1:
+                r[L // 3:2 * L // 3] = scaff[int(b)][p + L // 3:p + 2 * L // 3]
+            if i % 3 == 2:
+                r[2 * L // 3:] = scaff[int(c)][p + 2 * L // 3:p + L]
+            parts.append(letters[r])
+        seq = np.concatenate(parts)
+        qual = np.full(seq.size, ord("I"), np.uint8)
+        offs = np.arange(R + 1, dtype=np.uint64) * L
+        sc = engine.Scan(idx, k=k, algorithm=algorithm)
+        sc.submit_raw(seq, qual, offs, R)
+        r = sc.finish()
+        sets = sc.fusion_sets()
+        assert sum(sets.values()) == r.ambiguous > 0
+        exp = {}
+        for u in range(R):
+            sc.reset()
+            sc.submit_raw(seq, qual, offs[u:u + 2], 1)
+            nz = np.nonzero(sc.finish().unique)[0]
+            if nz.size > 1:
+                t = (int(nz[0]), int(nz[-1])) + (("+",) if nz.size > 2 else ())
+                exp[t] = exp.get(t, 0) + 1
+        assert sets == exp and any(len(t) == 3 for t in sets)
+        sc.close()
+    idx.close()
