@@ -485,7 +485,7 @@ def main() -> None:
 
     # ---- the same resident step WITHOUT the recording (tallies only: enough for the closed-form percentages, not for the refinement)
     tall_only = None
-    if rank == 0 and algo != capi.ALGO_DIRECT:
+    if algo != capi.ALGO_DIRECT:      # every rank (kernel_ms holds a barrier); rank 0 reports its own shard
         pscan = engine.Scan(idx, k=k, phred_cutoff=cutoff, mode=mode, record=False, algorithm=algo_req, device=local_rank, stream=stream.cuda_stream)
         for _ in range(2):
             pscan.reset(); pscan.submit_device(db)
