@@ -78,3 +78,19 @@ def test_gloo_world2_reduction():
         assert np.array_equal(r[2], want_i) and r[2].dtype == np.uint64      # integer tallies: exact, rank-count independent
         assert np.allclose(r[4], want_f, rtol=1e-15)
         assert np.allclose(r[5], want_e, rtol=1e-15)
+
+
+def test_bench_strong_scaling_shards_partition_the_read_set():
+    """bench.py shards the chunks of ONE global read set over the ranks (strong scaling): at every N the ranks' chunk ranges are
+    disjoint, ordered and cover all chunks, so the all-reduced tallies do not depend on N."""
+    import importlib.util
+    from pathlib import Path
+    spec = importlib.util.spec_from_file_location("bench", Path(__file__).resolve().parent.parent / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    for n_chunks in (1, 7, 200, 201):
+        for world in (1, 2, 4, 8):
+            parts = [bench.shard_chunks(n_chunks, r, world) for r in range(world)]
+            assert parts[0][0] == 0 and parts[-1][1] == n_chunks
+            assert all(a[1] == b[0] for a, b in zip(parts[:-1], parts[1:]))
+            assert max(b - a for a, b in parts) - min(b - a for a, b in parts) <= 1
