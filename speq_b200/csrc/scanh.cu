@@ -323,13 +323,13 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
     uint32_t agg_g = kNoGroup, agg_n = 0u;
     double agg_w = 0.0;
     QRoll qr;                                    // LOCAL: the rolling phred weight of the window that ends at the cursor
-    uint32_t rs = kNoRun, rl = 0xFFFFFFFDu;      // RECORD with positions: the open run [rs, rl] of consecutive text positions
-    auto run_flush = [&]() {
-        if (rs != kNoRun)
-        {
-            atomicAdd(a.diff + rs, 1ull);
-            atomicAdd(a.diff + rl + 1u, ~0ull);                   // -1
-        }
+    // RECORD with positions: the open run [rs, rl] of consecutive text positions, and one closed run [cs, cl] waiting for the
+    // single place per loop trip where runs are written (two atomics on the difference array) -- the windows of a trip only
+    // compare and move registers, so the divergent atomic code exists once, not once per unrolled window
+    uint32_t rs = kNoRun, rl = 0xFFFFFFFDu, cs = kNoRun, cl = 0u;
+    auto run_write = [&](uint32_t s0, uint32_t s1) {
+        atomicAdd(a.diff + s0, 1ull);
+        atomicAdd(a.diff + s1 + 1u, ~0ull);                       // -1
     };
     // per-lane scalars (flushed at the end, or before they could wrap)
     uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
@@ -532,7 +532,12 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                                 const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
                                 const uint32_t p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
                                 if (p == rl + 1u) rl = p;
-                                else { run_flush(); rs = p; rl = p; }
+                                else
+                                {
+                                    if (cs != kNoRun) run_write(cs, cl);      // a second run closed within one trip (rare)
+                                    cs = rs; cl = rl;
+                                    rs = p; rl = p;
+                                }
                             }
                             else atomicAdd(kt_counter(kt, slot_mult, 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
                         }
@@ -550,6 +555,11 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                                  : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
                                  : "l"(kt_bucket(kt, pb[j])));
                 }
+            }
+            if (RECORD && cs != kNoRun)
+            {
+                run_write(cs, cl);
+                cs = kNoRun;
             }
         }
         if (WPR)
@@ -600,7 +610,11 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
         }
     }
     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
-    if (RECORD) run_flush();
+    if (RECORD)
+    {
+        if (cs != kNoRun) run_write(cs, cl);
+        if (rs != kNoRun) run_write(rs, rl);
+    }
     if (n_total) env.add64(0, n_total);
     if (n_amb) env.add64(1, n_amb);
     if (n_look) env.add64(2, n_look);
@@ -652,6 +666,17 @@ __device__ __forceinline__ void ldg256_stream(uint32_t (&w)[8], const void * ptr
                  : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
                  : "l"(ptr));
 #endif
+}
+// measurement switch: record-mode probes of the pair-table scan ask L2 to fetch 64 bytes (the bucket's counter sector rides
+// along with its slots, so that the counter atomic that follows finds its sector in L2)
+#ifndef SPEQB_WIDE_PF
+#define SPEQB_WIDE_PF 0
+#endif
+__device__ __forceinline__ void ldg256_stream_pf64(uint32_t (&w)[8], const void * ptr, uint64_t pol)
+{
+    asm volatile("ld.global.nc.L2::cache_hint.L2::64B.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(ptr), "l"(pol));
 }
 __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t pol)
 {
@@ -798,6 +823,10 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     // the tables stream from HBM and must not push the presence filter out of L2
     const uint64_t pol_keep = l2_policy_keep(), pol_stream = l2_policy_stream();
     const uint32_t chunk = claim_chunk(units);                    // see scanh_kernel
+    auto probe256 = [&](uint32_t (&dst)[8], const void * ptr, uint64_t pol) {
+        if (SPEQB_WIDE_PF && RECORD) ldg256_stream_pf64(dst, ptr, pol);
+        else ldg256_stream(dst, ptr, pol);
+    };
 
     uint32_t phase = (!WPR && lane >= chunk) ? H_DONE : H_FETCH;
     bool mate2 = false;
@@ -994,7 +1023,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     pb[j] = (uint32_t)(h >> kp.rbits);
                     const uint64_t want = h & kp.rmask;
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                    ldg256_stream(w[j], kt_bucket(kp, pb[j]), pol_stream);
+                    probe256(w[j], kt_bucket(kp, pb[j]), pol_stream);
                 }
             }
             // ---- pairs: one probe answers both windows
@@ -1027,7 +1056,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     pb[j] = (pb[j] + 1u) & kp.nbmask;
                     const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kp.rbits);
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                    ldg256_stream(w[j], kt_bucket(kp, pb[j]), pol_stream);
+                    probe256(w[j], kt_bucket(kp, pb[j]), pol_stream);
                 }
             }
             // ---- what is left: unpaired windows and the halves of missed pairs go through the k-mer table, all first probes
@@ -1043,7 +1072,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     sb[i] = (uint32_t)(h >> kt.rbits);
                     const uint64_t want = h & kt.rmask;
                     sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
-                    ldg256_stream(sw[i], kt_bucket(kt, sb[i]), pol_stream);
+                    probe256(sw[i], kt_bucket(kt, sb[i]), pol_stream);
                 }
 #pragma unroll
                 for (int i = 0; i < 2 * kPair; ++i)
@@ -1070,7 +1099,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         sb[i] = (sb[i] + 1u) & kt.nbmask;
                         const uint64_t want = u64of(sl[i], sh_[i]) + (1ull << kt.rbits);
                         sl[i] = (uint32_t)want; sh_[i] = (uint32_t)(want >> 32);
-                        ldg256_stream(sw[i], kt_bucket(kt, sb[i]), pol_stream);
+                        probe256(sw[i], kt_bucket(kt, sb[i]), pol_stream);
                     }
                 }
             }
