@@ -403,7 +403,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 // a table beyond L2 that has to count hits per slot keeps the counters inside its (then 64-byte) buckets
                 const bool big = 32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 || getenv("SPEQB_FORCE_WIDE");
                 const bool pair = s->algo == SPEQG_ALGO_KPAIR || (auto_algo && idx->host.V <= kMaxGroupsPair && big);
-                s->kt.wide = record && big && !no_wide && (pair || getenv("SPEQB_NO_RUNS") || !ktable_positions_fit(s->kt, s->npos)) ? 1u : 0u;
+                // (only the pair-table scan reads wide tables: the single-window kernel's hot loop addresses 32-byte buckets)
+                s->kt.wide = record && big && !no_wide && pair ? 1u : 0u;
                 s->kt.slots = dev_alloc<uint64_t>((4ull << s->kt.wide) * ((uint64_t)s->kt.nbmask + 1));
                 CK(launch_ktable_build(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, di.t_group, h.S, max_len, s->kt, params->k,
                                        s->d_kstat, s->compute));

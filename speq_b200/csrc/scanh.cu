@@ -275,6 +275,12 @@ constexpr uint32_t kClaimChunkW = 4;   // reads a warp claims at a time when it 
 #ifndef SPEQB_HMINB
 #define SPEQB_HMINB 4
 #endif
+#ifndef SPEQB_HMINB_REC
+#define SPEQB_HMINB_REC SPEQB_HMINB
+#endif
+#ifndef SPEQB_RUN_DEFER
+#define SPEQB_RUN_DEFER 1
+#endif
 #ifndef SPEQB_HMINB_LOCAL
 #define SPEQB_HMINB_LOCAL 2
 #endif
@@ -286,7 +292,7 @@ constexpr int kWin = SPEQB_KWIN;
 // WPR (long reads): the 32 lanes of a warp share one read -- lane l takes windows [l * per, (l + 1) * per), per = ceil(nwin / 32),
 // pre-rolling the k-1 bases before its first window; the ambiguity state of the read is the warp's min / max variant.
 template <int MODE, bool WPR, bool MASK>
-__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
+__global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL : (MODE & M_RECORD) ? SPEQB_HMINB_REC : SPEQB_HMINB) scanh_kernel(const KTabView kt, unsigned long long * __restrict__ slot_mult,
                                                                                   const BatchView b, const ScanArgs a, const int paired)
 {
     constexpr bool LOCAL = (MODE & M_LOCAL) != 0;
@@ -487,7 +493,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
                     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                                  : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                 : "l"(kt_bucket(kt, pb[j])));
+                                 : "l"(kt.slots + 4ull * pb[j]));
                 }
             }
             t += nbase;
@@ -534,12 +540,16 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                                 if (p == rl + 1u) rl = p;
                                 else
                                 {
+#if SPEQB_RUN_DEFER
                                     if (cs != kNoRun) run_write(cs, cl);      // a second run closed within one trip (rare)
                                     cs = rs; cl = rl;
+#else
+                                    if (rs != kNoRun) run_write(rs, rl);
+#endif
                                     rs = p; rl = p;
                                 }
                             }
-                            else atomicAdd(kt_counter(kt, slot_mult, 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
+                            else atomicAdd(slot_mult + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u), 1ull);   // (this kernel never runs on a wide table)
                         }
                         break;
                     }
@@ -553,7 +563,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                     want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
                     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                                  : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                 : "l"(kt_bucket(kt, pb[j])));
+                                 : "l"(kt.slots + 4ull * pb[j]));
                 }
             }
             if (RECORD && cs != kNoRun)
