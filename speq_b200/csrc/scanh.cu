@@ -275,11 +275,14 @@ constexpr uint32_t kClaimChunkW = 4;   // reads a warp claims at a time when it 
 #ifndef SPEQB_HMINB
 #define SPEQB_HMINB 4
 #endif
+// record-mode instantiations: 3 CTAs per SM (85 registers: no spills; C3 19.04 -> 18.70 ms per 25 M reads, C2 unchanged).
+// SPEQB_RUN_DEFER = 1 parks a closed run in two more registers and writes it at one place per loop trip instead of where it
+// closes: measured slower at 4 CTAs/SM (C2 7.96 vs 6.80 ms, spills) and equal at 3 (profiles/r2_sweep.txt) -- off.
 #ifndef SPEQB_HMINB_REC
-#define SPEQB_HMINB_REC SPEQB_HMINB
+#define SPEQB_HMINB_REC 3
 #endif
 #ifndef SPEQB_RUN_DEFER
-#define SPEQB_RUN_DEFER 1
+#define SPEQB_RUN_DEFER 0
 #endif
 #ifndef SPEQB_HMINB_LOCAL
 #define SPEQB_HMINB_LOCAL 2
