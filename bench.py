@@ -628,7 +628,7 @@ def main() -> None:
                 tp = ROOT / "profiles" / name
                 if not tp.exists():
                     continue
-                tj = json.loads(tp.read_text()).get(f"{args.config}:{kname}") or json.loads(tp.read_text()).get(f"{args.config}:{kname.split('<')[0]}<0>")
+                tj = json.loads(tp.read_text()).get(f"{args.config}:{kname}" + ("" if k == sh.k else f"@k{k}"))
                 if tj:
                     roof["traffic"] = tj["dram_bytes_per_read"] * R
                     roof["traffic_source"] = tj["source"]
