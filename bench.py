@@ -394,6 +394,7 @@ def main() -> None:
 
         def finish_global():
             if world > 1:
+                sc.flush()                 # the last FASTQ region's kernels are queued before the reduction, not by finish()
                 dist.all_reduce(ci)
                 if local:
                     dist.all_reduce(cf)

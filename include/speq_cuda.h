@@ -200,6 +200,10 @@ int speqg_scan_submit_raw(speqg_scan * scan, const uint8_t * seq, const uint8_t 
  * the host and submits it with speqg_scan_submit_raw (tallies add up, the order of regions does not matter).
  * *ticket (may be NULL): pass to speqg_scan_wait_ticket before `bytes` is overwritten. */
 int speqg_scan_submit_fastq(speqg_scan * scan, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket);
+/* Queue everything submitted so far on the scan's stream without waiting for it: the second phase of the last FASTQ region
+ * (lines, records, pack, scan) is otherwise issued by the next call.  Call it before work of your own that must run BEHIND the
+ * scan on that stream -- e.g. the in-place all-reduce of speqg_scan_device_counters. */
+int speqg_scan_flush(speqg_scan * scan);
 /* ticket of the most recent submit that copied host memory (submit_packed / submit_raw / submit_fastq); 0 before the first */
 int speqg_scan_last_ticket(speqg_scan * scan, uint64_t * ticket);
 /* wait for the host->device copy of ONE earlier submit (its host buffer may then be refilled; later copies and all kernels
@@ -226,7 +230,8 @@ int speqg_scan_info(speqg_scan * scan, uint32_t * algorithm, uint64_t * structur
  * the handle's counters in device memory, for a sum-all-reduce in place on the scan's stream between the last submit and
  * speqg_scan_finish, which then returns the global tallies.  u64_counters: unique[n_groups], back-check totals[n_groups],
  * then total_kmers, ambiguous_reads, lookups, steps_executed, kmers_hit, occurrences, occ_sectors, reads (*n_u64 entries);
- * f64_counters: the local-mode tallies (*n_f64 = n_groups entries).  Any output pointer may be NULL. */
+ * f64_counters: the local-mode tallies (*n_f64 = n_groups entries).  Any output pointer may be NULL.  After
+ * speqg_scan_submit_fastq, call speqg_scan_flush before the reduction (the last region's kernels are queued lazily). */
 /* Ambiguous reads / pairs by the variants that met in them (fix-forward of the reference's fusion_totals map, whose key is
  * always the empty set because set_groups is passed by value, src/fm_scanner.cpp:915-916,983-995,1033): counts[a * n_groups
  * + b] = units whose smallest unique variant is a and largest is b (a < b); the entries sum to ambiguous_reads.  Syncs the

@@ -682,6 +682,15 @@ int speqg_scan_submit_fastq(speqg_scan * s, const uint8_t * bytes, uint64_t n_by
     SPEQG_CATCH
 }
 
+int speqg_scan_flush(speqg_scan * s)
+{
+    SPEQG_TRY
+    need(s != nullptr, "NULL argument");
+    device_guard guard(s->device);
+    fastq_phase2(s);
+    SPEQG_CATCH
+}
+
 int speqg_scan_last_ticket(speqg_scan * s, uint64_t * ticket)
 {
     SPEQG_TRY

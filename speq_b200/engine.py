@@ -313,6 +313,10 @@ class Scan:
         self._keep = raw          # pageable host memory: the copy is staged before the call returns; pinned: caller waits the ticket
         return int(reg.value), int(tick.value)
 
+    def flush(self) -> None:
+        """Everything submitted so far is queued on the scan's stream (needed before an in-place all-reduce of device_counters)."""
+        capi.check(capi.lib().speqg_scan_flush(self.h))
+
     def wait_ticket(self, ticket: int) -> None:
         capi.check(capi.lib().speqg_scan_wait_ticket(self.h, ticket))
 
