@@ -680,10 +680,10 @@ __device__ __forceinline__ void ldg256_stream(uint32_t (&w)[8], const void * ptr
                  : "l"(ptr));
 #endif
 }
-// measurement switch: record-mode probes of the pair-table scan ask L2 to fetch 64 bytes (the bucket's counter sector rides
-// along with its slots, so that the counter atomic that follows finds its sector in L2)
+// record-mode probes of the pair-table scan ask L2 to fetch 64 bytes: the bucket's counter sector rides along with its slots,
+// so the counter atomic that follows finds its sector in L2 (C4, 20 M reads: 56.0 -> 52.1 ms, profiles/r2_sweep.txt)
 #ifndef SPEQB_WIDE_PF
-#define SPEQB_WIDE_PF 0
+#define SPEQB_WIDE_PF 1
 #endif
 __device__ __forceinline__ void ldg256_stream_pf64(uint32_t (&w)[8], const void * ptr, uint64_t pol)
 {
