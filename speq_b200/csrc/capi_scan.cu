@@ -118,6 +118,7 @@ struct speqg_scan
     size_t scan_tmp_bytes = 0;
     uint64_t npos = 0;
     bool diff_dirty = false;
+    bool mult_dirty = true;         // mult[] holds counts (or was never cleared): reset has to zero it
     unsigned long long * d_state = nullptr, * h_state = nullptr;
     size_t state_words = 0;
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
@@ -158,6 +159,7 @@ scan_refine_view refine_view(speqg_scan * s)
         fastq_phase2(s);
     }
     // k-mer table scan: multiplicities were recorded per table slot; move them to mult[lb] (what the rolling scan records)
+    if ((s->slot_mult_dirty || s->diff_dirty) && s->d_mult) s->mult_dirty = true;
     if (s->slot_mult_dirty && s->d_mult)
     {
         device_guard guard(s->device);
@@ -250,6 +252,7 @@ void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
         if (s->mode & M_RECORD) (s->kt.pshift ? s->diff_dirty : s->slot_mult_dirty) = true;
     }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
+    if ((s->mode & M_RECORD) && s->algo != SPEQG_ALGO_KTABLE && s->algo != SPEQG_ALGO_KPAIR) s->mult_dirty = true;   // these record into mult[] directly
     ++s->launches;
 }
 
@@ -552,7 +555,13 @@ int speqg_scan_reset(speqg_scan * s)
     if (s->d_unique_n) CK(cudaMemsetAsync(s->d_unique_n, 0, (size_t)s->idx->host.V * 8, s->compute));
     if (s->d_diff) CK(cudaMemsetAsync(s->d_diff, 0, (s->npos + 2) * 8, s->compute));
     s->diff_dirty = false;
-    if (s->d_mult) CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
+    // the table scans write mult[] only when the refinement folds their counters into it; a scan that was never refined
+    // leaves it clean (8 bytes per suffix not rewritten per step)
+    if (s->d_mult && s->mult_dirty)
+    {
+        CK(cudaMemsetAsync(s->d_mult, 0, s->idx->host.n * 8, s->compute));
+        s->mult_dirty = false;
+    }
     if (s->d_slot_mult) CK(cudaMemsetAsync(s->d_slot_mult, 0, 4ull * ((uint64_t)s->kt.nbmask + 1) * 8, s->compute));
     if (s->d_pair_mult) CK(cudaMemsetAsync(s->d_pair_mult, 0, 4ull * ((uint64_t)s->kp.nbmask + 1) * 8, s->compute));
     if (s->kt.slots && s->kt.wide) CK(launch_ktable_zero_counters(s->kt, s->compute));
