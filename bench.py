@@ -283,8 +283,11 @@ def main() -> None:
         refs = synth.make_refs(sh, synth.SEED0 + cfg_id, device="cpu")
         n0 = min(R_total, CH, 400_000)
         a, b = gen_chunk(sh, cfg_id, refs, 0, n0, local)     # the head of chunk 0: the same generator and seed as the native arm
+        # every step scans the same bounded sample; the sample is sized so that the whole run stays around 100 s of CPU work
+        n_runs = max(1, args.steps) + min(args.warmup, 1)
         v, sample, kind, T, t, out, n = cpu_arm(sh, refs, a.numpy(), b.numpy(), k=k, accuracy=accuracy, cutoff=cutoff,
-                                                steps=max(1, args.steps), warmup=min(args.warmup, 1), target_s=args.cpu_seconds)
+                                                steps=max(1, args.steps), warmup=min(args.warmup, 1),
+                                                target_s=min(args.cpu_seconds, 100.0 / n_runs))
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if local else "u64",
                 "data": "synthetic", "config": config, "reads_per_sec": out["reads"] / t,

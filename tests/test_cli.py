@@ -274,3 +274,25 @@ def test_parallel_fastq_indexer_matches_serial_reader(speq_bin, tmp_path, thread
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.split("\n")[0].split()[1] == "601"
     assert int(r.stdout.split("handover")[1]) > 0
+
+
+@pytest.mark.gpu
+def test_speq_scan_two_gpus_same_result(speq_bin, tmp_path):
+    """`--gpus 2`: the batches / FASTQ regions go round-robin to two devices with the index replicated, the per-device tallies and
+    the per-iteration refinement estimates are summed on the host (the reference sums its futures, src/fm_scanner.cpp:224-233).
+    Same numbers as on one device.  Needs two visible GPUs (skipped on the one-GPU box)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    fx = helpers.load_golden("global_single")
+    exp, runp = fx["expected"], fx["run"]
+    refs, groups, r1, _ = helpers.golden_files(tmp_path, fx)
+    for env_host in (False, True):
+        env = dict(os.environ, SPEQ_HOST_FASTQ="1") if env_host else dict(os.environ)
+        r = subprocess.run([str(speq_bin), "all", "-r", str(refs), "-g", str(groups), "-1", str(r1), "-x", str(tmp_path / "i.idx"), "-k", str(runp["k"]),
+                            "--fixed-accuracy", str(runp["fixed_accuracy"]), "--json", str(tmp_path / "o.json"), "--batch-reads", "32", "--gpus", "2",
+                            "-f", "--write-output", "-o", str(tmp_path / "t.tsv")], capture_output=True, text=True, cwd=tmp_path, env=env)
+        assert r.returncode == 0, r.stderr
+        out = json.loads((tmp_path / "o.json").read_text())
+        assert out["unique"] == exp["unique"] and out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"]
+        assert out["iterations"] == exp["iterations"] and helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
