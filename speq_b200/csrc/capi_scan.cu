@@ -434,7 +434,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 // remainder; else, and for the pair-table scan, one atomic per hit on a per-slot counter.
                 if (s->algo == SPEQG_ALGO_KTABLE && !s->kt.wide && !getenv("SPEQB_NO_RUNS") && ktable_positions_fit(s->kt, s->npos))
                 {
-                    s->kt.pshift = s->kt.rbits + 3u;
+                    // the position starts at bit 32 when remainder + displacement fit the low word (one AND extracts it)
+                    s->kt.pshift = (s->kt.rbits + 3u <= 32u && s->npos < 0x7FFF0000ull) ? 32u : s->kt.rbits + 3u;   // (below the 0x7FFF.. pattern pass 1 leaves)
                     CK(launch_ktable_canon(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, h.S, max_len, s->kt, params->k, s->compute));
                     s->d_diff = dev_alloc<unsigned long long>(s->npos + 2);
                     s->scan_tmp_bytes = kpos_fold_tmp_bytes(s->npos);

@@ -538,8 +538,14 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                             if (kt.pshift != 0u)
                             {
                                 // the k-mer's smallest text position: extends the open run or starts a new one
-                                const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
-                                const uint32_t p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
+                                // (pshift == 32 whenever remainder + displacement fit the low word: the position is the high
+                                //  word without its top bit)
+                                uint32_t p = hi & 0x7FFFFFFFu;
+                                if (kt.pshift != 32u)
+                                {
+                                    const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
+                                    p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
+                                }
                                 if (p == rl + 1u) rl = p;
                                 else
                                 {
