@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define SPEQG_ABI_VERSION 1
+#define SPEQG_ABI_VERSION 2   /* 2: fusion sets, FASTQ regions, copy tickets, reference .idx import, device packer, probe */
 
 enum
 {

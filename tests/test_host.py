@@ -27,7 +27,7 @@ def test_header_symbols_exported(lib):
     assert declared == set(capi.SIGNATURES), declared ^ set(capi.SIGNATURES)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.speqg_abi_version() == 1
+    assert lib.speqg_abi_version() == 2
     # the product library must not contain the oracle
     nm = subprocess.run(["nm", "-D", "--defined-only", str(capi.LIB_PATH)], capture_output=True, text=True).stdout
     assert "oracle" not in nm.lower()
