@@ -12,7 +12,8 @@ cap() {   # name, kernel regex, skip, count, bench args...
   ls -la /tmp/$name.ncu-rep $O/${name}_raw.csv $O/${name}_source.csv | awk '{print $5, $9}'
 }
 B="python bench.py --config C3 --reads 20000000 --steps 2 --warmup 1 --no-cpu"
-$B > $O/r2_plain_C3.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file $O/r2_launches_C3.csv $B > $O/r2_ncu_launches.log 2>&1
+# launch list of the library's own kernels in one bench run (torch's generator kernels of the synthetic workload are filtered out)
+$B > $O/r2_plain_C3.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"scan|pack|fq_|kpos|ktable|kpair|kfilter|fill|refine|probe|build_up|sa_|count_nonzero" -c 3000 --csv --log-file $O/r2_launches_C3.csv $B > $O/r2_ncu_launches.log 2>&1
 cap r2_scanh_C3 scanh_kernel 4 2 --config C3 --reads 2000000
 cap r2_scanh_C2 scanh_kernel 4 2 --config C2 --reads 1000000
 cap r2_scan32_local_k70 scan32_kernel 2 1 --config C2 --reads 1000000 --mode local -k 70
