@@ -118,15 +118,6 @@ template <int MODE> struct Tally32
     BatchView const & b;
     ScanArgs const & a;
     Smem32 sm;
-    __device__ __forceinline__ double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
-    {
-        // window = positions [t_end-k, t_end); the left fold of src/fm_scanner.cpp:454, a / (1 - 1/pow(10, q/10)), with
-        // the denominators tabulated by the host's libm: IEEE division keeps every weight bit-exact
-        const uint8_t * q = b.qual + 32u * g0 + (t_end - k);
-        double w = 1.0;
-        for (uint32_t i = 0; i < k; ++i) w = w / a.qden[load_ro(q + i)];
-        return w;
-    }
     // n windows whose k-mer lies in variant g only; w: the sum of their phred weights (local mode)
     __device__ __forceinline__ void unique(uint32_t g, uint32_t n, double w) const
     {

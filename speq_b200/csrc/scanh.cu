@@ -861,6 +861,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
     double agg_w = 0.0;
     uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
     uint32_t wcur = 0u, wend = 0u;
+    QRoll qr;                                    // LOCAL: the rolling phred weight of the window that ends at the cursor
 
     auto next_group = [&]() {
         cb = nb; ci = ni;
@@ -874,19 +875,21 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
         const uint32_t o = t & 31u;
         key = (key << 2) | ((uint32_t)(cb >> (2u * o)) & 3u);
         run = ((ci >> o) & 1u) ? 0u : run + 1u;
+        if (LOCAL) qr.step(t, k, run, sm.den, sm.rden);
         t += 1u;
         if ((t & 31u) == 0u) next_group();
     };
     // ++unique_kmers[which_hit] and the read-level ambiguity state (src/fm_scanner.cpp:178-191) for a window whose k-mer
     // lies in variant g only; t_end: end of the window (local mode weight)
-    auto tally = [&](uint32_t g, uint32_t t_end) {
+    // wgt: the window's phred weight (local mode; the rolling product of scanh_kernel, QRoll)
+    auto tally = [&](uint32_t g, double wgt) {
         if (g != agg_g)
         {
             if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
             agg_g = g; agg_n = 0u; agg_w = 0.0;
             uset.add(g);
         }
-        if (LOCAL) agg_w += env.weight(g0, t_end, k);
+        if (LOCAL) agg_w += wgt;
         agg_n += 1u;
     };
     while (true)
@@ -968,6 +971,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                     nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
                     ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
                 }
+                if (LOCAL) qr.start(b.qual + 32ull * g0, L, t, k);
             }
             phase = H_RUN;
         }
@@ -978,6 +982,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
             uint32_t pb[kPair], want_lo[kPair], want_hi[kPair];
             uint64_t key_a[kPair], key_b[kPair];                  // the k-mer register after the first / second base of each pair
             uint32_t mode[kPair];                                 // bit 0: first window due, bit 1: second window due
+            double pw[2 * kPair];                                 // LOCAL: weight of the window that ends with base i of the trip
             const uint32_t t0 = t, o = t & 31u;
             const uint32_t nbase = pend - t < 2u * (uint32_t)kPair ? pend - t : 2u * (uint32_t)kPair;
             uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
@@ -994,6 +999,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                 {
                     key = (key << 2) | ((bits >> (4 * j)) & 3u);
                     run = ((ibits >> (2 * j)) & 1u) ? 0u : run + 1u;
+                    if (LOCAL) { qr.step(t0 + 2u * (uint32_t)j, k, run, sm.den, sm.rden); pw[2 * j] = qr.P; }
                     mode[j] = run >= k ? 1u : 0u;
                 }
                 key_a[j] = key;
@@ -1001,6 +1007,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                 {
                     key = (key << 2) | ((bits >> (4 * j + 2)) & 3u);
                     run = ((ibits >> (2 * j + 1)) & 1u) ? 0u : run + 1u;
+                    if (LOCAL) { qr.step(t0 + 2u * (uint32_t)j + 1u, k, run, sm.den, sm.rden); pw[2 * j + 1] = qr.P; }
                     mode[j] |= run >= k ? 2u : 0u;
                 }
                 key_b[j] = key;
@@ -1064,8 +1071,8 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         const uint32_t v1 = vv & 0xFFu, v2 = vv >> 8;
                         // a k-mer of one variant needs no record (see scanh_kernel); the fold skips that half of the pair
                         if (RECORD && (v1 == 0xFFu || v2 == 0xFFu)) atomicAdd(kt_counter(kp, pair_mult, 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
-                        if (v1 != 0xFFu) tally(v1, t0 + 2u * (uint32_t)j + 1u);
-                        if (v2 != 0xFFu) tally(v2, t0 + 2u * (uint32_t)j + 2u);
+                        if (v1 != 0xFFu) tally(v1, LOCAL ? pw[2 * j] : 0.0);
+                        if (v2 != 0xFFu) tally(v2, LOCAL ? pw[2 * j + 1] : 0.0);
                         mode[j] = 0u;                             // answered
                         break;
                     }
@@ -1108,7 +1115,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? 2 : SPEQB_PMINB) s
                         if (h0 || h1 || h2 || h3)
                         {
                             const uint32_t hi = h0 ? sw[i][1] : h1 ? sw[i][3] : h2 ? sw[i][5] : sw[i][7];
-                            if (!slot_multi(hi)) tally(hi >> 16, t0 + (uint32_t)i + 1u);
+                            if (!slot_multi(hi)) tally(hi >> 16, LOCAL ? pw[i] : 0.0);
                             else if (RECORD) atomicAdd(kt_counter(kt, slot_mult, 4ull * sb[i] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)), 1ull);
                             break;
                         }

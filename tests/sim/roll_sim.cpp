@@ -102,13 +102,6 @@ struct HostEnv32
     uint32_t qual1(uint64_t g0, uint32_t pos) const { return qual[32u * g0 + pos]; }
     double den(uint32_t q) const { return qden[q]; }
     double rden(uint32_t q) const { return 1.0 / qden[q]; }
-    double weight(uint64_t g0, uint32_t t_end, uint32_t k) const
-    {
-        const uint8_t * q = qual + 32u * g0 + (t_end - k);
-        double w = 1.0;
-        for (uint32_t i = 0; i < k; ++i) w = w / qden[q[i]];
-        return w;
-    }
     void unique(uint32_t g, uint32_t n, double w) const
     {
         if (local) uniq_w[g] += w;
