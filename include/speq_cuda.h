@@ -200,6 +200,12 @@ int speqg_scan_submit_raw(speqg_scan * scan, const uint8_t * seq, const uint8_t 
  * the host and submits it with speqg_scan_submit_raw (tallies add up, the order of regions does not matter).
  * *ticket (may be NULL): pass to speqg_scan_wait_ticket before `bytes` is overwritten. */
 int speqg_scan_submit_fastq(speqg_scan * scan, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket);
+/* The same for paired input (scan opened with paired = 1): a region of the first mates' file and a region of the second mates'
+ * file that hold the SAME number of whole records (record i of one pairs with record i of the other, what views::zip of the two
+ * files yields, src/fm_scanner.cpp:651); the device interleaves them.  Regions whose record counts differ are rejected like
+ * irregular ones. */
+int speqg_scan_submit_fastq_pair(speqg_scan * scan, const uint8_t * bytes1, uint64_t n_bytes1, const uint8_t * bytes2,
+                                 uint64_t n_bytes2, uint64_t * region, uint64_t * ticket);
 /* Queue everything submitted so far on the scan's stream without waiting for it: the second phase of the last FASTQ region
  * (lines, records, pack, scan) is otherwise issued by the next call.  Call it before work of your own that must run BEHIND the
  * scan on that stream -- e.g. the in-place all-reduce of speqg_scan_device_counters. */

@@ -87,6 +87,7 @@ SIGNATURES = {
     "speqg_scan_submit_packed": (C.c_int, [C.c_void_p, C.POINTER(Batch)]),
     "speqg_scan_submit_raw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]),
     "speqg_scan_submit_fastq": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, u64p, u64p]),
+    "speqg_scan_submit_fastq_pair": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, u64p, u64p]),
     "speqg_scan_wait_ticket": (C.c_int, [C.c_void_p, C.c_uint64]),
     "speqg_scan_last_ticket": (C.c_int, [C.c_void_p, u64p]),
     "speqg_scan_flush": (C.c_int, [C.c_void_p]),

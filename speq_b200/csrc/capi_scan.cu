@@ -52,13 +52,14 @@ struct Slot
     dev_buf<uint32_t> inv, len;
     dev_buf<uint8_t> qual, raw_seq, raw_qual;
     // FASTQ regions parsed on the device (speqg_scan_submit_fastq)
-    dev_buf<uint32_t> fq_chunk;                   // newlines per 4 KB chunk -> exclusive prefix sum
-    dev_buf<uint64_t> fq_lines, fq_soff, fq_qoff;
-    dev_buf<unsigned long long> fq_small;         // [0] newline count, [1] reads published for the scan kernel, [2] reject flag
-    unsigned long long * h_total = nullptr;       // pinned: the newline count, read by the host between the two phases
+    dev_buf<uint32_t> fq_chunk, fq_chunk2;        // newlines per 4 KB chunk -> exclusive prefix sum (2: the second mate's file)
+    dev_buf<uint64_t> fq_lines, fq_lines2, fq_soff, fq_qoff;
+    dev_buf<unsigned long long> fq_small;         // [0] newline count, [1] reads published for the scan kernel, [2] reject flag,
+                                                  // [3] newline count of the second file
+    unsigned long long * h_total = nullptr;       // pinned [2]: the newline counts, read by the host between the two phases
     cudaEvent_t counted = nullptr;
-    uint64_t fq_bytes = 0, fq_region = 0;
-    bool fq_terminated = true;
+    uint64_t fq_bytes = 0, fq_bytes2 = 0, fq_region = 0;
+    bool fq_terminated = true, fq_terminated2 = true, fq_pair = false;
     cudaEvent_t copied = nullptr, done = nullptr;
     uint64_t ticket = 0;
     bool busy = false;
@@ -66,7 +67,7 @@ struct Slot
     {
         bases.release(); grp_off.release(); raw_off.release(); inv.release(); len.release();
         qual.release(); raw_seq.release(); raw_qual.release();
-        fq_chunk.release(); fq_lines.release(); fq_soff.release(); fq_qoff.release(); fq_small.release();
+        fq_chunk.release(); fq_chunk2.release(); fq_lines.release(); fq_lines2.release(); fq_soff.release(); fq_qoff.release(); fq_small.release();
         if (h_total) cudaFreeHost(h_total);
         h_total = nullptr;
         if (counted) cudaEventDestroy(counted);
@@ -280,36 +281,49 @@ void speqb::fastq_phase2(speqg_scan * s)
     Slot & sl = s->slots[s->fq_pending];
     s->fq_pending = -1;
     CK(cudaEventSynchronize(sl.counted));
-    const uint64_t n = sl.fq_bytes, n_nl = *sl.h_total;
-    const uint64_t n_lines = n_nl + (sl.fq_terminated ? 0u : 1u);
+    const uint32_t files = sl.fq_pair ? 2u : 1u;
+    const uint64_t n[2] = {sl.fq_bytes, sl.fq_bytes2}, n_nl[2] = {sl.h_total[0], sl.h_total[1]};
+    const uint64_t n_lines[2] = {n_nl[0] + (sl.fq_terminated ? 0u : 1u), n_nl[1] + (sl.fq_terminated2 ? 0u : 1u)};
     unsigned int * d_reject = reinterpret_cast<unsigned int *>(sl.fq_small.p + 2);
     unsigned long long * d_nreads = sl.fq_small.p + 1;
-    if (n_lines % 4 != 0 || n_lines / 4 >= (uint64_t(1) << 32))
+    bool whole = n_lines[0] % 4 == 0 && n_lines[0] / 4 < (uint64_t(1) << 31);
+    if (sl.fq_pair) whole = whole && n_lines[1] == n_lines[0];          // mate i of file 1 pairs with record i of file 2
+    if (!whole)
     {
-        // not a whole number of 4-line records: nothing of the region is scanned; the caller reads it with the host grammar
+        // not a whole number of 4-line records (or not as many mates as reads): nothing of the region is scanned; the caller
+        // reads it with the host grammar
         unsigned int one = 1u;
         CK(cudaMemcpyAsync(s->d_fq_flags + sl.fq_region, &one, 4, cudaMemcpyHostToDevice, s->compute));
         CK(cudaEventRecord(sl.done, s->compute));
         sl.busy = true;
         return;
     }
-    const uint64_t n_rec = n_lines / 4;
-    const uint64_t G = (n >> 5) + n_rec + 2;
-    sl.fq_lines.reserve(n_lines + 2); sl.fq_soff.reserve(n_rec + 1); sl.fq_qoff.reserve(n_rec + 1);
-    sl.len.reserve(n_rec + 1); sl.grp_off.reserve(n_rec + 2); sl.bases.reserve(G); sl.inv.reserve(G);
+    const uint64_t n_rec = n_lines[0] / 4, n_reads = n_rec * files;
+    // first 32-base group of each file's reads: read r of a file sits at group base + floor(sequence offset / 32) + r
+    const uint64_t gbase[2] = {0, (n[0] >> 5) + n_rec + 1};
+    const uint64_t G = gbase[1] + (sl.fq_pair ? (n[1] >> 5) + n_rec + 1 : 0) + 1;
+    sl.fq_lines.reserve(n_lines[0] + 2);
+    if (sl.fq_pair) sl.fq_lines2.reserve(n_lines[1] + 2);
+    sl.fq_soff.reserve(n_reads + 1); sl.fq_qoff.reserve(n_reads + 1);
+    sl.len.reserve(n_reads + 1); sl.grp_off.reserve(n_reads + 2); sl.bases.reserve(G); sl.inv.reserve(G);
     const bool local = (s->mode & M_LOCAL) != 0;
     if (local) sl.qual.reserve(G * 32 + 32);
-    CK(launch_fastq_records(sl.raw_seq.p, n, sl.fq_chunk.p, n_nl, n_rec, sl.fq_lines.p, sl.fq_soff.p, sl.fq_qoff.p, sl.len.p, sl.grp_off.p,
-                            s->p.phred_cutoff, sl.bases.p, sl.inv.p, local ? sl.qual.p : nullptr, d_reject, d_nreads,
-                            s->d_fq_flags + sl.fq_region, s->compute));
-    s->launches += 4;
+    CK(launch_fastq_begin(d_reject, s->compute));
+    CK(launch_fastq_records(sl.raw_seq.p, n[0], sl.fq_chunk.p, n_nl[0], n_rec, sl.fq_lines.p, sl.fq_soff.p, sl.fq_qoff.p, sl.len.p, sl.grp_off.p,
+                            files, 0u, gbase[0], s->p.phred_cutoff, sl.bases.p, sl.inv.p, local ? sl.qual.p : nullptr, d_reject, s->compute));
+    if (sl.fq_pair)
+        CK(launch_fastq_records(sl.raw_qual.p, n[1], sl.fq_chunk2.p, n_nl[1], n_rec, sl.fq_lines2.p, sl.fq_soff.p, sl.fq_qoff.p, sl.len.p,
+                                sl.grp_off.p, files, 1u, gbase[1], s->p.phred_cutoff, sl.bases.p, sl.inv.p, local ? sl.qual.p : nullptr, d_reject,
+                                s->compute));
+    CK(launch_fastq_finalize(d_reject, n_reads, d_nreads, s->d_fq_flags + sl.fq_region, s->compute));
+    s->launches += 1 + 3 * files;
     if (n_rec)
     {
         BatchView v{};
         v.bases = sl.bases.p; v.inv = sl.inv.p; v.qual = local ? sl.qual.p : nullptr;
-        v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = n_rec; v.n_reads_dev = d_nreads;
-        // a warp per read for long reads: the sequences are at most half of the region's bytes
-        launch_on_view(s, v, (n / 2) / 32 + 1);
+        v.grp_off = sl.grp_off.p; v.len = sl.len.p; v.read_group = nullptr; v.n_reads = n_reads; v.n_reads_dev = d_nreads;
+        // a warp per read for long reads: the sequences are at most half of the regions' bytes
+        launch_on_view(s, v, ((n[0] + n[1]) / 2) / 32 + 1);
     }
     CK(cudaEventRecord(sl.done, s->compute));
     sl.busy = true;
@@ -644,14 +658,17 @@ int speqg_scan_submit_raw(speqg_scan * s, const uint8_t * seq, const uint8_t * q
     SPEQG_CATCH
 }
 
-int speqg_scan_submit_fastq(speqg_scan * s, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket)
+static int submit_fastq_impl(speqg_scan * s, const uint8_t * bytes, uint64_t n_bytes, const uint8_t * bytes2, uint64_t n_bytes2, bool pair,
+                             uint64_t * region, uint64_t * ticket)
 {
     SPEQG_TRY
     need(s != nullptr, "NULL argument");
-    need(!(s->mode & M_PAIRED), "speqg_scan_submit_fastq takes single-end input (mates of a pair live in two files)");
+    need(pair == ((s->mode & M_PAIRED) != 0), pair ? "speqg_scan_submit_fastq_pair needs a scan opened with paired = 1"
+                                                   : "speqg_scan_submit_fastq takes single-end input (mates of a pair live in two files: "
+                                                     "speqg_scan_submit_fastq_pair)");
     need(s->algo != SPEQG_ALGO_DIRECT && s->algo != SPEQG_ALGO_ROLLING64, "speqg_scan_submit_fastq runs the product kernels only");
     need(s->fq_regions < kMaxFastqRegions, "too many FASTQ regions in one scan (2^20)");
-    need(n_bytes < (uint64_t(1) << 40), "FASTQ region too large");
+    need(n_bytes < (uint64_t(1) << 40) && n_bytes2 < (uint64_t(1) << 40), "FASTQ region too large");
     device_guard guard(s->device);
     if (!s->d_fq_flags)
     {
@@ -660,36 +677,63 @@ int speqg_scan_submit_fastq(speqg_scan * s, const uint8_t * bytes, uint64_t n_by
     }
     const uint64_t id = s->fq_regions++;
     if (region) *region = id;
-    if (n_bytes == 0)
+    if (n_bytes == 0 && n_bytes2 == 0)
     {
         if (ticket) *ticket = 0;
         return SPEQG_OK;
     }
-    need(bytes != nullptr, "bytes is NULL");
+    need((n_bytes == 0 || bytes != nullptr) && (n_bytes2 == 0 || bytes2 != nullptr), "bytes is NULL");
     // the slot after the pending one: its copy is queued first, so it overlaps the pending region's second phase
     Slot & sl = acquire_slot(s);
     if (!sl.counted)
     {
         CK(cudaEventCreateWithFlags(&sl.counted, cudaEventDisableTiming));
-        CK(cudaMallocHost(reinterpret_cast<void **>(&sl.h_total), 8));
+        CK(cudaMallocHost(reinterpret_cast<void **>(&sl.h_total), 16));
     }
     if (ticket) *ticket = sl.ticket;
     sl.raw_seq.reserve(n_bytes + 64);
     sl.fq_chunk.reserve(fastq_chunks(n_bytes) + 1);
     sl.fq_small.reserve(8);
-    CK(cudaMemcpyAsync(sl.raw_seq.p, bytes, n_bytes, cudaMemcpyHostToDevice, s->copy));
+    if (n_bytes) CK(cudaMemcpyAsync(sl.raw_seq.p, bytes, n_bytes, cudaMemcpyHostToDevice, s->copy));
+    if (pair)
+    {
+        sl.raw_qual.reserve(n_bytes2 + 64);                 // (the second file's bytes use the raw-read path's quality staging)
+        sl.fq_chunk2.reserve(fastq_chunks(n_bytes2) + 1);
+        if (n_bytes2) CK(cudaMemcpyAsync(sl.raw_qual.p, bytes2, n_bytes2, cudaMemcpyHostToDevice, s->copy));
+    }
     CK(cudaEventRecord(sl.copied, s->copy));
+    sl.fq_pair = pair;
     sl.fq_bytes = n_bytes;
+    sl.fq_bytes2 = pair ? n_bytes2 : 0;
     sl.fq_region = id;
-    sl.fq_terminated = bytes[n_bytes - 1] == '\n';
+    sl.fq_terminated = n_bytes == 0 || bytes[n_bytes - 1] == '\n';
+    sl.fq_terminated2 = !pair || n_bytes2 == 0 || bytes2[n_bytes2 - 1] == '\n';
+    sl.h_total[1] = 0;
     fastq_phase2(s);                                   // the region submitted before this one
     CK(cudaStreamWaitEvent(s->compute, sl.copied, 0));
     CK(launch_fastq_count(sl.raw_seq.p, n_bytes, sl.fq_chunk.p, sl.fq_small.p, s->compute));
     s->launches += 2;
     CK(cudaMemcpyAsync(sl.h_total, sl.fq_small.p, 8, cudaMemcpyDeviceToHost, s->compute));
+    if (pair)
+    {
+        CK(launch_fastq_count(sl.raw_qual.p, n_bytes2, sl.fq_chunk2.p, sl.fq_small.p + 3, s->compute));
+        s->launches += 2;
+        CK(cudaMemcpyAsync(sl.h_total + 1, sl.fq_small.p + 3, 8, cudaMemcpyDeviceToHost, s->compute));
+    }
     CK(cudaEventRecord(sl.counted, s->compute));
     s->fq_pending = (int)(&sl - s->slots);
     SPEQG_CATCH
+}
+
+int speqg_scan_submit_fastq(speqg_scan * s, const uint8_t * bytes, uint64_t n_bytes, uint64_t * region, uint64_t * ticket)
+{
+    return submit_fastq_impl(s, bytes, n_bytes, nullptr, 0, false, region, ticket);
+}
+
+int speqg_scan_submit_fastq_pair(speqg_scan * s, const uint8_t * bytes1, uint64_t n_bytes1, const uint8_t * bytes2, uint64_t n_bytes2,
+                                 uint64_t * region, uint64_t * ticket)
+{
+    return submit_fastq_impl(s, bytes1, n_bytes1, bytes2, n_bytes2, true, region, ticket);
 }
 
 int speqg_scan_flush(speqg_scan * s)

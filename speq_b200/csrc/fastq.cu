@@ -144,8 +144,11 @@ __global__ void __launch_bounds__(kFqBlock) fq_lines_kernel(const uint8_t * __re
 __global__ void __launch_bounds__(kFqBlock) fq_records_kernel(const uint8_t * __restrict__ raw, const uint64_t n, const uint64_t * __restrict__ line_start,
                                                               const uint64_t n_newlines, const uint64_t n_rec, uint64_t * __restrict__ soff,
                                                               uint64_t * __restrict__ qoff, uint32_t * __restrict__ len, uint64_t * __restrict__ grp_off,
+                                                              const uint32_t stride, const uint32_t slot, const uint64_t gbase,
                                                               unsigned int * __restrict__ reject)
 {
+    // stride / slot: record r becomes read r * stride + slot of the batch (mates of a pair interleave: stride 2, slot = mate);
+    // gbase: first 32-base group this file's reads may use (the second mate's groups lie behind all of the first's)
     for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rec; r += (uint64_t)gridDim.x * blockDim.x)
     {
         const uint64_t s0 = line_start[4 * r], s1 = line_start[4 * r + 1], s2 = line_start[4 * r + 2], s3 = line_start[4 * r + 3];
@@ -156,17 +159,19 @@ __global__ void __launch_bounds__(kFqBlock) fq_records_kernel(const uint8_t * __
         // '@' opens the id line, '+' the separator line (format_fastq.hpp:112-125,172-186); equal lengths (:196-202)
         const bool ok = raw[s0] == '@' && raw[s2] == '+' && ls == lq && ls <= 0xFFFFFFFFull;    // (an empty line holds its newline there)
         if (!ok) atomicOr(reject, 1u);
-        soff[r] = s1;
-        qoff[r] = s3;
-        len[r] = ok ? (uint32_t)ls : 0u;
-        grp_off[r] = (s1 >> 5) + r;              // monotone, never overlapping: consecutive sequence lines are >= len bytes apart
-        if (r + 1 == n_rec) grp_off[n_rec] = (n >> 5) + n_rec + 1ull;
+        const uint64_t o = r * stride + slot;
+        soff[o] = s1;
+        qoff[o] = s3;
+        len[o] = ok ? (uint32_t)ls : 0u;
+        grp_off[o] = gbase + (s1 >> 5) + r;      // monotone, never overlapping: consecutive sequence lines are >= len bytes apart
+        if (r + 1 == n_rec && slot + 1u == stride) grp_off[n_rec * stride] = gbase + (n >> 5) + n_rec + 1ull;
     }
 }
 
 __global__ void __launch_bounds__(kFqBlock) fq_pack_kernel(const uint8_t * __restrict__ raw, const uint64_t * __restrict__ soff,
                                                            const uint64_t * __restrict__ qoff, const uint32_t * __restrict__ len,
-                                                           const uint64_t * __restrict__ grp_off, const uint64_t n_rec, const uint32_t cutoff,
+                                                           const uint64_t * __restrict__ grp_off, const uint64_t n_rec, const uint32_t stride,
+                                                           const uint32_t slot, const uint32_t cutoff,
                                                            uint64_t * __restrict__ bases, uint32_t * __restrict__ inv, uint8_t * __restrict__ qual_out,
                                                            unsigned int * __restrict__ reject)
 {
@@ -196,8 +201,9 @@ __global__ void __launch_bounds__(kFqBlock) fq_pack_kernel(const uint8_t * __res
     bool any_bad = false;
     for (uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n_rec; r += nwarps)
     {
-        const uint64_t so = soff[r], qo = qoff[r], g0 = grp_off[r];
-        const uint32_t L = len[r];
+        const uint64_t o = r * stride + slot;
+        const uint64_t so = soff[o], qo = qoff[o], g0 = grp_off[o];
+        const uint32_t L = len[o];
         const uint32_t ng = (L + 31u) >> 5;
         for (uint32_t g = lane; g < ng; g += 32u)
         {
@@ -259,25 +265,34 @@ cudaError_t launch_fastq_count(const uint8_t * raw, uint64_t n_bytes, uint32_t *
     return cudaGetLastError();
 }
 
+// lines, records and packing of ONE raw region into reads r * stride + slot of the batch; *reject is set when the region is not
+// in the strict form (it must have been zeroed before the first region of the batch: launch_fastq_begin)
 cudaError_t launch_fastq_records(const uint8_t * raw, uint64_t n_bytes, const uint32_t * chunk_off, uint64_t n_newlines, uint64_t n_rec,
-                                 uint64_t * line_start, uint64_t * soff, uint64_t * qoff, uint32_t * len, uint64_t * grp_off, uint32_t cutoff,
-                                 uint64_t * bases, uint32_t * inv, uint8_t * qual_out, unsigned int * reject, unsigned long long * n_reads_dev,
-                                 unsigned int * region_flag, cudaStream_t st)
+                                 uint64_t * line_start, uint64_t * soff, uint64_t * qoff, uint32_t * len, uint64_t * grp_off, uint32_t stride,
+                                 uint32_t slot, uint64_t gbase, uint32_t cutoff, uint64_t * bases, uint32_t * inv, uint8_t * qual_out,
+                                 unsigned int * reject, cudaStream_t st)
 {
     const uint32_t nc = fastq_chunks(n_bytes);
-    cudaError_t e = cudaMemsetAsync(reject, 0, 4, st);
-    if (e != cudaSuccess) return e;
     if (nc && n_rec)
     {
         fq_lines_kernel<<<std::min<uint32_t>(nc, (uint32_t)fq_sms() * 16u), kFqBlock, 0, st>>>(raw, n_bytes, chunk_off, nc, line_start);
         const uint64_t want = (n_rec + kFqBlock - 1) / kFqBlock;
         fq_records_kernel<<<(int)std::min<uint64_t>(want, (uint64_t)fq_sms() * 16), kFqBlock, 0, st>>>(raw, n_bytes, line_start, n_newlines, n_rec, soff, qoff,
-                                                                                                      len, grp_off, reject);
+                                                                                                      len, grp_off, stride, slot, gbase, reject);
         const uint64_t wantp = (n_rec * 32 + kFqBlock - 1) / kFqBlock;
-        fq_pack_kernel<<<(int)std::min<uint64_t>(wantp, (uint64_t)fq_sms() * 16), kFqBlock, 0, st>>>(raw, soff, qoff, len, grp_off, n_rec, cutoff, bases, inv,
-                                                                                                    qual_out, reject);
+        fq_pack_kernel<<<(int)std::min<uint64_t>(wantp, (uint64_t)fq_sms() * 16), kFqBlock, 0, st>>>(raw, soff, qoff, len, grp_off, n_rec, stride, slot, cutoff,
+                                                                                                    bases, inv, qual_out, reject);
     }
-    fq_finalize_kernel<<<1, 1, 0, st>>>(reject, n_rec, n_reads_dev, region_flag);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fastq_begin(unsigned int * reject, cudaStream_t st) { return cudaMemsetAsync(reject, 0, 4, st); }
+
+// n_reads: reads of the batch when the region(s) were regular
+cudaError_t launch_fastq_finalize(const unsigned int * reject, uint64_t n_reads, unsigned long long * n_reads_dev, unsigned int * region_flag,
+                                  cudaStream_t st)
+{
+    fq_finalize_kernel<<<1, 1, 0, st>>>(reject, n_reads, n_reads_dev, region_flag);
     return cudaGetLastError();
 }
 }   // namespace speqb

@@ -147,9 +147,12 @@ cudaError_t scanp_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
 // reads and publishes the number of reads (0 and *region_flag = 1 when the region is not in the strict 4-line form)
 uint32_t fastq_chunks(uint64_t n_bytes);
 cudaError_t launch_fastq_count(const uint8_t * raw, uint64_t n_bytes, uint32_t * chunk_cnt, unsigned long long * total, cudaStream_t st);
+cudaError_t launch_fastq_begin(unsigned int * reject, cudaStream_t st);
 cudaError_t launch_fastq_records(const uint8_t * raw, uint64_t n_bytes, const uint32_t * chunk_off, uint64_t n_newlines, uint64_t n_rec,
-                                 uint64_t * line_start, uint64_t * soff, uint64_t * qoff, uint32_t * len, uint64_t * grp_off, uint32_t cutoff,
-                                 uint64_t * bases, uint32_t * inv, uint8_t * qual_out, unsigned int * reject, unsigned long long * n_reads_dev,
-                                 unsigned int * region_flag, cudaStream_t st);
+                                 uint64_t * line_start, uint64_t * soff, uint64_t * qoff, uint32_t * len, uint64_t * grp_off, uint32_t stride,
+                                 uint32_t slot, uint64_t gbase, uint32_t cutoff, uint64_t * bases, uint32_t * inv, uint8_t * qual_out,
+                                 unsigned int * reject, cudaStream_t st);
+cudaError_t launch_fastq_finalize(const unsigned int * reject, uint64_t n_reads, unsigned long long * n_reads_dev, unsigned int * region_flag,
+                                  cudaStream_t st);
 cudaError_t launch_count_nonzero(const unsigned long long * mult, uint32_t n, unsigned long long * out, cudaStream_t st);
 }   // namespace speqb

@@ -313,6 +313,16 @@ class Scan:
         self._keep = raw          # pageable host memory: the copy is staged before the call returns; pinned: caller waits the ticket
         return int(reg.value), int(tick.value)
 
+    def submit_fastq_pair(self, raw1, raw2) -> tuple[int, int]:
+        """Two raw FASTQ regions with the same number of records: first mates, second mates.  -> (region, ticket)"""
+        a = np.frombuffer(raw1, np.uint8) if isinstance(raw1, (bytes, bytearray)) else raw1
+        b = np.frombuffer(raw2, np.uint8) if isinstance(raw2, (bytes, bytearray)) else raw2
+        reg, tick = C.c_uint64(), C.c_uint64()
+        capi.check(capi.lib().speqg_scan_submit_fastq_pair(self.h, capi.ptr(a) if a.size else None, a.size, capi.ptr(b) if b.size else None, b.size,
+                                                           C.byref(reg), C.byref(tick)))
+        self._keep = (a, b)
+        return int(reg.value), int(tick.value)
+
     def flush(self) -> None:
         """Everything submitted so far is queued on the scan's stream (needed before an in-place all-reduce of device_counters)."""
         capi.check(capi.lib().speqg_scan_flush(self.h))

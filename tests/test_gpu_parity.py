@@ -657,3 +657,50 @@ def test_fusion_sets_many_variants(lib, algorithm):
         assert sets == exp and any(len(t) == 3 for t in sets)
         sc.close()
     idx.close()
+
+
+@pytest.mark.parametrize("algorithm", [capi.ALGO_ROLLING, capi.ALGO_KTABLE, capi.ALGO_KPAIR])
+@pytest.mark.parametrize("name", ["global_paired", "local_paired"])
+def test_submit_fastq_pair_device_parser(lib, name, algorithm):
+    """speqg_scan_submit_fastq_pair: a region of each mate file, same number of records, parsed and interleaved on the device.
+    Same tallies as the fixture (oracle/_ref) in one and in several region pairs, LF and CRLF; a pair of regions whose record
+    counts differ, or with an irregular record in either file, is reported and not scanned."""
+    fx = helpers.load_golden(name)
+    exp, run = fx["expected"], fx["run"]
+    scaff, gs, counts, seqs, quals = helpers.golden_inputs(fx)            # interleaved mates
+    s1, q1, s2, q2 = seqs[0::2], quals[0::2], seqs[1::2], quals[1::2]
+    local = exp["mode"] == "local"
+    idx = engine.Index.from_scaffolds(scaff, gs, len(counts))
+    sc = engine.Scan(idx, k=run["k"], phred_cutoff=run.get("phred_cutoff", 30), mode=capi.MODE_LOCAL if local else capi.MODE_GLOBAL,
+                     algorithm=algorithm, paired=True, record=True)
+
+    def check(r):
+        assert (r.total_kmers, r.ambiguous, r.lookups, r.reads) == (exp["total_kmers"], exp["ambiguous"], exp["lookups"], len(seqs))
+        if local:
+            assert helpers.rel_close(r.unique_w, exp["unique_w"], TOL)
+        else:
+            assert [int(x) for x in r.unique] == exp["unique"]
+
+    n = len(s1)
+    for nl, trailing, pieces in (("\n", True, 1), ("\r\n", False, 1), ("\n", True, 4)):
+        sc.reset()
+        cuts = [n * i // pieces for i in range(pieces + 1)]
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            sc.submit_fastq_pair(_fastq_text(s1[a:b], q1[a:b], nl, trailing), _fastq_text(s2[a:b], q2[a:b], nl, trailing))
+        assert sc.fastq_rejected() == []
+        check(sc.finish())
+    assert {",".join(map(str, key)): c for key, c in sc.fusion_sets().items()} == exp["fusion"]
+    # record counts differ / an irregular record in the second file: the pair of regions is handed back
+    h = n // 2
+    for bad2 in (_fastq_text(s2[h:n - 1], q2[h:n - 1]), _fastq_text(s2[h:], q2[h:]).replace(b"\n+\n", b"\n+\n\n", 1)):
+        sc.reset()
+        sc.submit_fastq_pair(_fastq_text(s1[:h], q1[:h]), _fastq_text(s2[:h], q2[:h]))
+        sc.submit_fastq_pair(_fastq_text(s1[h:], q1[h:]), bad2)
+        assert sc.fastq_rejected() == [1]
+        seq, q, offs = helpers.flat_reads(seqs[2 * h:], quals[2 * h:])
+        sc.submit_raw(seq, q, offs, len(seqs) - 2 * h)
+        check(sc.finish())
+    with pytest.raises(capi.SpeqError):
+        sc.submit_fastq(_fastq_text(s1, q1))                  # a paired scan takes pairs of regions
+    sc.close()
+    idx.close()
