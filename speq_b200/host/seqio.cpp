@@ -249,6 +249,70 @@ void fastq_map::read_into(void * dst, uint64_t pos, uint64_t len, int threads) c
         if (f) throw std::runtime_error("read error in the FASTQ file");
 }
 
+namespace
+{
+uint64_t count_nl_serial(const char * p, uint64_t n)
+{
+    uint64_t c = 0;
+    const char * e = p + n;
+    while (p < e)
+    {
+        const char * q = static_cast<const char *>(memchr(p, '\n', static_cast<size_t>(e - p)));
+        if (!q) break;
+        ++c;
+        p = q + 1;
+    }
+    return c;
+}
+std::vector<uint64_t> piece_counts(const char * p, uint64_t n, int threads, std::vector<uint64_t> & cut)
+{
+    threads = std::max(1, std::min<int>(threads, static_cast<int>(n >> 20) + 1));
+    cut.assign(static_cast<size_t>(threads) + 1, 0);
+    for (int i = 0; i <= threads; ++i) cut[static_cast<size_t>(i)] = n * static_cast<uint64_t>(i) / static_cast<uint64_t>(threads);
+    std::vector<uint64_t> cnt(static_cast<size_t>(threads), 0);
+    if (threads == 1) cnt[0] = count_nl_serial(p, n);
+    else
+    {
+        std::vector<std::thread> th;
+        for (int i = 0; i < threads; ++i)
+            th.emplace_back([&, i]() { cnt[static_cast<size_t>(i)] = count_nl_serial(p + cut[static_cast<size_t>(i)], cut[static_cast<size_t>(i) + 1] - cut[static_cast<size_t>(i)]); });
+        for (auto & t : th) t.join();
+    }
+    return cnt;
+}
+}   // namespace
+
+uint64_t count_newlines(const char * p, uint64_t n, int threads)
+{
+    std::vector<uint64_t> cut;
+    uint64_t total = 0;
+    for (uint64_t c : piece_counts(p, n, threads, cut)) total += c;
+    return total;
+}
+
+uint64_t offset_after_newline(const char * p, uint64_t n, uint64_t nth, int threads)
+{
+    std::vector<uint64_t> cut;
+    std::vector<uint64_t> cnt = piece_counts(p, n, threads, cut);
+    uint64_t before = 0;
+    for (size_t i = 0; i < cnt.size(); ++i)
+    {
+        if (before + cnt[i] >= nth)
+        {
+            const char * q = p + cut[i];
+            const char * e = p + cut[i + 1];
+            for (uint64_t left = nth - before; left; --left)
+            {
+                q = static_cast<const char *>(memchr(q, '\n', static_cast<size_t>(e - q)));
+                ++q;
+            }
+            return static_cast<uint64_t>(q - p);
+        }
+        before += cnt[i];
+    }
+    return n;
+}
+
 void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads)
 {
     threads = std::max(1, threads);

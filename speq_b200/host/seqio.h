@@ -93,6 +93,9 @@ private:
 
 // copy records [r0, r1) of `recs` (step `stride`, slot offset `slot`: mates of a pair interleave with stride 2) into the
 // flat arrays; dst offsets come from `offsets` (already filled for every slot)
+// newlines in [p, p + n), counted by `threads` threads; and the offset just behind the nth (>= 1) of them (n when there are fewer)
+uint64_t count_newlines(const char * p, uint64_t n, int threads);
+uint64_t offset_after_newline(const char * p, uint64_t n, uint64_t nth, int threads);
 // plain copy by `threads` threads (page cache -> pinned staging buffer)
 void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads);
 void copy_records(const char * data, std::vector<fq_rec> const & recs, uint64_t n, uint8_t * seq, uint8_t * qual,

@@ -264,6 +264,7 @@ struct device_lane
     // raw FASTQ regions parsed on the device: copy ticket of each staging buffer, and where every submitted region lies in the file
     uint64_t ticket[2] = {0, 0};
     std::vector<std::pair<uint64_t, uint64_t>> regions;
+    std::vector<std::pair<uint64_t, uint64_t>> regions2;     // paired input: the region of the second mates' file
 };
 
 struct scan_out
@@ -355,9 +356,96 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
         }
         serial = off1 < m1.size();
     }
-    if (serial || paired || getenv("SPEQ_HOST_FASTQ") || !speq::io::fastq_map::eligible(args.in_file_reads_path_1))
+    // ---- paired plain FASTQ: a region of each file with the same number of records (cut by line count, verified to end at
+    //      record starts) goes to the device, which parses and interleaves the mates (speqg_scan_submit_fastq_pair)
+    bool paired_device = false;
+    if (paired && !getenv("SPEQ_HOST_FASTQ") && speq::io::fastq_map::eligible(args.in_file_reads_path_1) &&
+        speq::io::fastq_map::eligible(args.in_file_reads_path_2))
+    {
+        paired_device = true;
+        const int T = std::max(1, static_cast<int>(args.threads) - 1);
+        speq::io::fastq_map m1(args.in_file_reads_path_1), m2(args.in_file_reads_path_2);
+        for (auto & L : lanes) { L.buf[0].ensure_records(); L.buf[1].ensure_records(); }   // the quality staging holds file 2's bytes
+        while (off1 < m1.size() && off2 < m2.size())
+        {
+            device_lane & L = lanes[dev];
+            host_batch & b = L.buf[L.cur];
+            uint64_t n1 = m1.region_end(off1, b.cap_bytes) - off1, n2 = m2.region_end(off2, b.cap_bytes) - off2;
+            if (n1 == 0 || n2 == 0) break;                            // a record larger than the staging buffer: host paths
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[L.cur]), "speqg_scan_wait_ticket");
+            m1.read_into(b.seq, off1, n1, T);
+            m2.read_into(b.qual, off2, n2, T);
+            const char * p1 = reinterpret_cast<const char *>(b.seq), * p2 = reinterpret_cast<const char *>(b.qual);
+            const uint64_t l1 = speq::io::count_newlines(p1, n1, T) + (p1[n1 - 1] != '\n'), l2 = speq::io::count_newlines(p2, n2, T) + (p2[n2 - 1] != '\n');
+            const uint64_t recs = std::min(l1, l2) / 4;
+            if (recs == 0) break;
+            if (l1 != 4 * recs) n1 = speq::io::offset_after_newline(p1, n1, 4 * recs, T);
+            if (l2 != 4 * recs) n2 = speq::io::offset_after_newline(p2, n2, 4 * recs, T);
+            // both cuts must be record starts (4-line records all the way): else the files are not in the strict form here
+            if ((off1 + n1 < m1.size() && m1.record_start_from(off1 + n1) != off1 + n1) ||
+                (off2 + n2 < m2.size() && m2.record_start_from(off2 + n2) != off2 + n2))
+                break;
+            uint64_t region = 0;
+            ck(speqg_scan_submit_fastq_pair(L.scan, b.seq, n1, b.qual, n2, &region, &L.ticket[L.cur]), "speqg_scan_submit_fastq_pair");
+            if (region != L.regions.size()) throw std::runtime_error("internal error: FASTQ region numbering");
+            L.regions.emplace_back(off1, n1);
+            L.regions2.emplace_back(off2, n2);
+            L.cur ^= 1;
+            off1 += n1;
+            off2 += n2;
+            dev = (dev + 1) % lanes.size();
+        }
+        // region pairs the device handed back: both regions again with the serial grammar, zipped
+        for (auto & L : lanes)
+        {
+            uint64_t n_rej = 0;
+            ck(speqg_scan_fastq_rejected(L.scan, nullptr, 0, &n_rej), "speqg_scan_fastq_rejected");
+            if (n_rej == 0) continue;
+            std::vector<uint64_t> rej(n_rej);
+            ck(speqg_scan_fastq_rejected(L.scan, rej.data(), n_rej, &n_rej), "speqg_scan_fastq_rejected");
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[0]), "speqg_scan_wait_ticket");
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[1]), "speqg_scan_wait_ticket");
+            L.buf[0].clear(); L.buf[1].clear();
+            for (uint64_t id : rej)
+            {
+                auto const & r1 = L.regions.at(id);
+                auto const & r2 = L.regions2.at(id);
+                speq::io::sequence_reader rd1(m1.data(), r1.first, r1.first + r1.second, args.in_file_reads_path_1.string());
+                speq::io::sequence_reader rd2(m2.data(), r2.first, r2.first + r2.second, args.in_file_reads_path_2.string());
+                std::string sa, qa, sb, qb;
+                while (true)
+                {
+                    const bool g1 = rd1.next(sa, qa), g2 = rd2.next(sb, qb);
+                    if (g1 != g2)
+                        throw std::runtime_error("the paired FASTQ files lose step inside a region that is not in the 4-line form; "
+                                                 "run again with SPEQ_HOST_FASTQ=1 (serial reader over both files)");
+                    if (!g1) break;
+                    if (!L.buf[L.cur].fits(sa.size() + sb.size(), 2))
+                    {
+                        flush(L);
+                        if (sa.size() + sb.size() > L.buf[L.cur].cap_bytes)
+                        {
+                            ck(speqg_scan_sync(L.scan), "speqg_scan_sync");
+                            L.buf[L.cur].alloc((sa.size() + sb.size()) * 2, L.buf[L.cur].cap_reads);
+                        }
+                    }
+                    L.buf[L.cur].push(sa, qa);
+                    L.buf[L.cur].push(sb, qb);
+                }
+            }
+            flush(L);
+        }
+        for (auto & L : lanes)
+        {
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[0]), "speqg_scan_wait_ticket");
+            ck(speqg_scan_wait_ticket(L.scan, L.ticket[1]), "speqg_scan_wait_ticket");
+            L.buf[0].clear(); L.buf[1].clear();
+        }
+        serial = off1 < m1.size() && off2 < m2.size();
+    }
+    if (serial || (paired && !paired_device) || getenv("SPEQ_HOST_FASTQ") || !speq::io::fastq_map::eligible(args.in_file_reads_path_1))
         for (auto & L : lanes) { L.buf[0].ensure_records(); L.buf[1].ensure_records(); }
-    if (!paired && !getenv("SPEQ_HOST_FASTQ") && speq::io::fastq_map::eligible(args.in_file_reads_path_1)) {}
+    if (paired_device || (!paired && !getenv("SPEQ_HOST_FASTQ") && speq::io::fastq_map::eligible(args.in_file_reads_path_1))) {}
     else if (speq::io::fastq_map::eligible(args.in_file_reads_path_1) && (!paired || speq::io::fastq_map::eligible(args.in_file_reads_path_2)))
     {
         serial = false;

@@ -296,3 +296,32 @@ def test_speq_scan_two_gpus_same_result(speq_bin, tmp_path):
         out = json.loads((tmp_path / "o.json").read_text())
         assert out["unique"] == exp["unique"] and out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"]
         assert out["iterations"] == exp["iterations"] and helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("damage", ["none", "multiline_in_mate2", "crlf"])
+def test_speq_scan_device_fastq_paired(speq_bin, tmp_path, damage):
+    """Paired plain FASTQ: regions of both files with equal record counts go to the device (speqg_scan_submit_fastq_pair); a
+    multi-line record in the second file ends the device path in front of its region (the cut is no record start) or gets its
+    region pair handed back, and the host readers take over.  Same numbers as SPEQ_HOST_FASTQ=1 and as the fixture."""
+    fx = helpers.load_golden("global_paired")
+    exp, runp = fx["expected"], fx["run"]
+    refs, groups, _, _ = helpers.golden_files(tmp_path, fx)
+    nl = "\r\n" if damage == "crlf" else "\n"
+    for name, text, dmg in (("a_1.fq", fx["reads1_fq"], False), ("a_2.fq", fx["reads2_fq"], damage == "multiline_in_mate2")):
+        seqs, quals = helpers.parse_fastq(text)
+        j = next(i for i, s in enumerate(seqs) if len(s) >= 10 and i > 40)
+        lines = []
+        for i, (sq, ql) in enumerate(zip(seqs, quals)):
+            lines += [f"@read_{i}", sq[:5], sq[5:], "+", ql[:5], ql[5:]] if dmg and i == j else [f"@read_{i}", sq, "+", ql]
+        (tmp_path / name).write_bytes((nl.join(lines) + nl).encode("latin-1"))
+    for env_host in (False, True):
+        env = dict(os.environ, SPEQ_HOST_FASTQ="1") if env_host else dict(os.environ)
+        r = subprocess.run([str(speq_bin), "all", "-r", str(refs), "-g", str(groups), "-1", str(tmp_path / "a_1.fq"), "-2", str(tmp_path / "a_2.fq"),
+                            "-x", str(tmp_path / "i.idx"), "-k", str(runp["k"]), "--fixed-accuracy", str(runp["fixed_accuracy"]),
+                            "--json", str(tmp_path / "o.json"), "--batch-reads", "32", "-f"], capture_output=True, text=True, cwd=tmp_path, env=env)
+        assert r.returncode == 0, r.stderr
+        out = json.loads((tmp_path / "o.json").read_text())
+        assert out["unique"] == exp["unique"] and out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"]
+        assert out["lookups"] == exp["lookups"] and out["iterations"] == exp["iterations"]
+        assert helpers.rel_close(out["percent_final"], exp["percent_final"], 1e-12)
