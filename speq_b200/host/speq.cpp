@@ -395,9 +395,14 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
             off2 += n2;
             dev = (dev + 1) % lanes.size();
         }
-        // region pairs the device handed back: both regions again with the serial grammar, zipped
+        // region pairs the device handed back: both regions again with the serial grammar, zipped.  Regions were cut by LINE
+        // count; where a region is not in the 4-line form the two files may hold different numbers of records in it, and then
+        // every later region paired the wrong mates: the tallies are dropped and both files go through the serial reader from
+        // the start (views::zip over two record streams, src/fm_scanner.cpp:651)
+        bool lost_step = false;
         for (auto & L : lanes)
         {
+            if (lost_step) break;
             uint64_t n_rej = 0;
             ck(speqg_scan_fastq_rejected(L.scan, nullptr, 0, &n_rej), "speqg_scan_fastq_rejected");
             if (n_rej == 0) continue;
@@ -408,6 +413,7 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
             L.buf[0].clear(); L.buf[1].clear();
             for (uint64_t id : rej)
             {
+                if (lost_step) break;
                 auto const & r1 = L.regions.at(id);
                 auto const & r2 = L.regions2.at(id);
                 speq::io::sequence_reader rd1(m1.data(), r1.first, r1.first + r1.second, args.in_file_reads_path_1.string());
@@ -416,9 +422,7 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
                 while (true)
                 {
                     const bool g1 = rd1.next(sa, qa), g2 = rd2.next(sb, qb);
-                    if (g1 != g2)
-                        throw std::runtime_error("the paired FASTQ files lose step inside a region that is not in the 4-line form; "
-                                                 "run again with SPEQ_HOST_FASTQ=1 (serial reader over both files)");
+                    if (g1 != g2) { lost_step = true; break; }
                     if (!g1) break;
                     if (!L.buf[L.cur].fits(sa.size() + sb.size(), 2))
                     {
@@ -442,6 +446,22 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
             L.buf[0].clear(); L.buf[1].clear();
         }
         serial = off1 < m1.size() && off2 < m2.size();
+        if (lost_step)
+        {
+            std::cerr << "speq: the paired FASTQ files lose step inside a region that is not in the 4-line form; reading both "
+                         "files again with the serial grammar\n";
+            for (auto & L : lanes)
+            {
+                ck(speqg_scan_sync(L.scan), "speqg_scan_sync");
+                ck(speqg_scan_reset(L.scan), "speqg_scan_reset");
+                L.regions.clear(); L.regions2.clear();
+                L.cur = 0;
+            }
+            off1 = off2 = 0;
+            dev = 0;
+            serial = true;
+            paired_device = false;
+        }
     }
     if (serial || (paired && !paired_device) || getenv("SPEQ_HOST_FASTQ") || !speq::io::fastq_map::eligible(args.in_file_reads_path_1))
         for (auto & L : lanes) { L.buf[0].ensure_records(); L.buf[1].ensure_records(); }

@@ -299,21 +299,25 @@ def test_speq_scan_two_gpus_same_result(speq_bin, tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("damage", ["none", "multiline_in_mate2", "crlf"])
+@pytest.mark.parametrize("damage", ["none", "multiline_in_mate2", "two_multiline_in_mate2", "crlf"])
 def test_speq_scan_device_fastq_paired(speq_bin, tmp_path, damage):
     """Paired plain FASTQ: regions of both files with equal record counts go to the device (speqg_scan_submit_fastq_pair); a
     multi-line record in the second file ends the device path in front of its region (the cut is no record start) or gets its
-    region pair handed back, and the host readers take over.  Same numbers as SPEQ_HOST_FASTQ=1 and as the fixture."""
+    region pair handed back, and the host readers take over.  Two 6-line records next to each other keep the LINE count a
+    multiple of four while the region holds one record less than its mate region: the files lose step there, the device tallies
+    are dropped (speqg_scan_reset) and both files are read again by the host readers.  Same numbers as SPEQ_HOST_FASTQ=1 and
+    as the fixture."""
     fx = helpers.load_golden("global_paired")
     exp, runp = fx["expected"], fx["run"]
     refs, groups, _, _ = helpers.golden_files(tmp_path, fx)
     nl = "\r\n" if damage == "crlf" else "\n"
-    for name, text, dmg in (("a_1.fq", fx["reads1_fq"], False), ("a_2.fq", fx["reads2_fq"], damage == "multiline_in_mate2")):
+    for name, text, dmg in (("a_1.fq", fx["reads1_fq"], False), ("a_2.fq", fx["reads2_fq"], "multiline_in_mate2" in damage)):
         seqs, quals = helpers.parse_fastq(text)
-        j = next(i for i, s in enumerate(seqs) if len(s) >= 10 and i > 40)
+        j = next(i for i, s in enumerate(seqs[:-1]) if len(s) >= 10 and len(seqs[i + 1]) >= 10 and i > 40)
+        hit = (j, j + 1) if damage.startswith("two_") else (j,)
         lines = []
         for i, (sq, ql) in enumerate(zip(seqs, quals)):
-            lines += [f"@read_{i}", sq[:5], sq[5:], "+", ql[:5], ql[5:]] if dmg and i == j else [f"@read_{i}", sq, "+", ql]
+            lines += [f"@read_{i}", sq[:5], sq[5:], "+", ql[:5], ql[5:]] if dmg and i in hit else [f"@read_{i}", sq, "+", ql]
         (tmp_path / name).write_bytes((nl.join(lines) + nl).encode("latin-1"))
     for env_host in (False, True):
         env = dict(os.environ, SPEQ_HOST_FASTQ="1") if env_host else dict(os.environ)
@@ -321,6 +325,7 @@ def test_speq_scan_device_fastq_paired(speq_bin, tmp_path, damage):
                             "-x", str(tmp_path / "i.idx"), "-k", str(runp["k"]), "--fixed-accuracy", str(runp["fixed_accuracy"]),
                             "--json", str(tmp_path / "o.json"), "--batch-reads", "32", "-f"], capture_output=True, text=True, cwd=tmp_path, env=env)
         assert r.returncode == 0, r.stderr
+        assert ("lose step" in r.stderr) == (damage.startswith("two_") and not env_host), r.stderr
         out = json.loads((tmp_path / "o.json").read_text())
         assert out["unique"] == exp["unique"] and out["total_kmers"] == exp["total_kmers"] and out["ambiguous"] == exp["ambiguous"]
         assert out["lookups"] == exp["lookups"] and out["iterations"] == exp["iterations"]
