@@ -115,6 +115,8 @@ struct speqg_scan
     unsigned long long * d_unique_n = nullptr;
     // k-mer table with positions: recorded runs as a difference array over the packed-text positions
     unsigned long long * d_diff = nullptr;
+    uint64_t * d_tflags = nullptr;           // walk form of the k-mer table: per-group window flags and variants (KTabView)
+    uint16_t * d_gvar = nullptr;
     void * d_scan_tmp = nullptr;
     size_t scan_tmp_bytes = 0;
     uint64_t npos = 0;
@@ -172,7 +174,7 @@ scan_refine_view refine_view(speqg_scan * s)
     if (s->diff_dirty && s->d_mult)
     {
         device_guard guard(s->device);
-        CK(launch_kpos_fold(s->di->t_bases, s->view, s->p.k, s->d_diff, s->npos, s->d_scan_tmp, s->scan_tmp_bytes, s->d_mult, s->compute));
+        CK(launch_kpos_fold(s->di->t_bases, s->view, s->p.k, s->d_diff, s->npos, s->d_scan_tmp, s->scan_tmp_bytes, s->d_mult, s->kt, s->compute));
         s->diff_dirty = false;
     }
     return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult, s->d_unique_n,
@@ -185,7 +187,7 @@ namespace
 void scan_release(speqg_scan * s)
 {
     cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_fkeys); cudaFree(s->d_fvals); cudaFree(s->d_mult);
-    cudaFree(s->d_unique_n); cudaFree(s->d_diff); cudaFree(s->d_scan_tmp);
+    cudaFree(s->d_unique_n); cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_tflags); cudaFree(s->d_gvar);
     cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
     cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
@@ -441,7 +443,33 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 // per probe) pays there (C4: +43 %), while on an L2-resident table the single-window kernel is faster.
                 if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3) s->algo = SPEQG_ALGO_KPAIR;
             }
-            if (params->record_multiplicity)
+            // Global mode, single-window table scan: when a text position fits into every slot the table is put into walk form
+            // (KTabView::walk, scanw_kernel) -- the scan then answers most windows from the packed texts and two flag bits per
+            // text position instead of a probe.  SPEQB_NO_WALK=1 keeps the probing scan (measurements).
+            const bool walk = s->algo == SPEQG_ALGO_KTABLE && !s->kt.wide && !(s->mode & M_LOCAL) && !getenv("SPEQB_NO_WALK") &&
+                              !getenv("SPEQB_NO_RUNS") && ktable_walk_fits(s->kt, s->npos) && h.t_bases.size() < 0x7FFFFFFFull;
+            if (walk)
+            {
+                s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
+                s->kt.tgroups = (uint32_t)h.t_bases.size();
+                s->d_tflags = dev_alloc<uint64_t>((size_t)s->kt.tgroups + 2);
+                s->d_gvar = dev_alloc<uint16_t>((size_t)s->kt.tgroups + 2);
+                CK(cudaMemsetAsync(s->d_tflags, 0, ((size_t)s->kt.tgroups + 2) * 8, s->compute));
+                CK(cudaMemsetAsync(s->d_gvar, 0, ((size_t)s->kt.tgroups + 2) * 2, s->compute));
+                CK(launch_ktable_canon(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, di.t_group, h.S, max_len, s->kt, params->k,
+                                       s->d_tflags, s->d_gvar, s->compute));
+                s->kt.walk = 1u;
+                s->kt.tbases = di.t_bases;
+                s->kt.tflags = s->d_tflags;
+                s->kt.gvar = s->d_gvar;
+                if (params->record_multiplicity)
+                {
+                    s->d_diff = dev_alloc<unsigned long long>(s->npos + 2);
+                    s->scan_tmp_bytes = kpos_fold_tmp_bytes(s->npos);
+                    CK(cudaMalloc(&s->d_scan_tmp, s->scan_tmp_bytes));
+                }
+            }
+            else if (params->record_multiplicity)
             {
                 // Single-window table scan: hits on k-mers held by several variants are recorded as runs over the positions of
                 // the packed texts (two atomics per run of consecutive hits) when a position fits into the slot next to the
@@ -450,7 +478,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 {
                     // the position starts at bit 32 when remainder + displacement fit the low word (one AND extracts it)
                     s->kt.pshift = (s->kt.rbits + 3u <= 32u && s->npos < 0x7FFF0000ull) ? 32u : s->kt.rbits + 3u;   // (below the 0x7FFF.. pattern pass 1 leaves)
-                    CK(launch_ktable_canon(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, h.S, max_len, s->kt, params->k, s->compute));
+                    CK(launch_ktable_canon(di.t_bases, di.t_inv, di.t_grp_off, di.t_len, nullptr, h.S, max_len, s->kt, params->k,
+                                           nullptr, nullptr, s->compute));
                     s->d_diff = dev_alloc<unsigned long long>(s->npos + 2);
                     s->scan_tmp_bytes = kpos_fold_tmp_bytes(s->npos);
                     CK(cudaMalloc(&s->d_scan_tmp, s->scan_tmp_bytes));
@@ -507,9 +536,10 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             if (!auto_algo || (e.code != SPEQG_ENOMEM && e.code != SPEQG_EINVAL)) throw;
             cudaGetLastError();
             cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->kp.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_pair_mult);
-            cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_kstat);
+            cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_kstat); cudaFree(s->d_tflags); cudaFree(s->d_gvar);
             s->kt = KTabView{}; s->kp = KTabView{};
             s->d_slot_mult = s->d_pair_mult = s->d_diff = s->d_kstat = nullptr;
+            s->d_tflags = nullptr; s->d_gvar = nullptr;
             s->d_scan_tmp = nullptr;
             s->ktab_keys = s->kpair_keys = 0;
             s->algo = SPEQG_ALGO_ROLLING;

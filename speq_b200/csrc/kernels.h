@@ -111,15 +111,27 @@ struct KTabView
     uint32_t wide;                // 1: 64-byte buckets = four slots + their four record-mode counters (tables beyond L2)
     uint32_t pshift;              // != 0: slots of k-mers held by several variants carry, from this bit up to bit 62, the
                                   // smallest position (32 * group + offset in the packed texts) where the k-mer starts
+    // walk != 0 (global mode, positions fit): EVERY slot carries its k-mer's smallest text position (bit 63 still says "several
+    // variants"; the variant of a single-variant k-mer is that of the text the position lies in, gvar[position >> 5]), and the
+    // scan follows the packed texts from a hit instead of probing the table for every window (scanw_kernel, scanh.cu)
+    uint32_t walk;
+    uint32_t tgroups;             // 32-base groups of the packed texts
+    const uint64_t * tbases;      // the packed texts (2 bits per base, 32 per word)
+    const uint64_t * tflags;      // per group: low word = bit j set when the window that ENDS at base 32 g + j is an N-free k-mer of
+                                  // one text; high word = ... and texts of several variants hold that k-mer
+    const uint16_t * gvar;        // variant of the text a group belongs to
 };
 bool ktable_positions_fit(KTabView const & kt, uint64_t npos);
 cudaError_t launch_ktable_clear(KTabView const & kt, cudaStream_t st);
 cudaError_t launch_ktable_zero_counters(KTabView const & kt, cudaStream_t st);
+// t_group / tflags / gvar != NULL: the walk form (every slot gets its position; the per-group flags and variants are written)
 cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
-                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k, cudaStream_t st);
+                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
+                                uint64_t * tflags, uint16_t * gvar, cudaStream_t st);
+bool ktable_walk_fits(KTabView const & kt, uint64_t npos);
 size_t kpos_fold_tmp_bytes(uint64_t npos);
 cudaError_t launch_kpos_fold(const uint64_t * t_bases, DevIndex const & ix, uint32_t k, unsigned long long * diff, uint64_t npos,
-                             void * tmp, size_t tmp_bytes, unsigned long long * mult, cudaStream_t st);
+                             void * tmp, size_t tmp_bytes, unsigned long long * mult, KTabView const & kt, cudaStream_t st);
 // presence filter of the k-mer table for the pair-table scan: 2^fbits bits, L2-resident next to the HBM-resident tables
 uint32_t kfilter_bits(uint32_t k, uint64_t keys);
 cudaError_t launch_kfilter_build(KTabView const & kt, uint32_t fbits, cudaStream_t st);

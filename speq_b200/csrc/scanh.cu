@@ -191,9 +191,15 @@ __device__ __forceinline__ uint64_t ktable_slot_of(KTabView const & kt, uint64_t
 // Second pass of the build for a table with positions: every N-free window of the texts whose k-mer is held by several
 // variants lowers the slot's position field to its own start in the packed texts (32 * group + offset).  The first pass left
 // the field of such slots at a value above every position (variant field 0x7FFF, rest 0), so atomicMin on the whole word works.
+//
+// Walk form (tflags != NULL; the slots were prepared by ktable_prep_pos_kernel): EVERY window lowers its slot's position, and the
+// thread writes what the walking scan reads per 32-base group of the texts: which windows that end in the group are k-mers of
+// one text, which of those are held by several variants, and the variant of the text.
+template <bool WALK>
 __global__ void __launch_bounds__(kBlockH) ktable_canon_kernel(const uint64_t * __restrict__ bases, const uint32_t * __restrict__ inv,
                                                                const uint64_t * __restrict__ grp_off, const uint32_t * __restrict__ len,
-                                                               const KTabView kt, const uint32_t k)
+                                                               const int32_t * __restrict__ text_group, const KTabView kt, const uint32_t k,
+                                                               uint64_t * __restrict__ tflags, uint16_t * __restrict__ gvar)
 {
     const uint32_t text = blockIdx.y;
     const uint32_t L = len[text];
@@ -206,7 +212,7 @@ __global__ void __launch_bounds__(kBlockH) ktable_canon_kernel(const uint64_t * 
         // windows that END in bases [32 gi, 32 gi + 32): the k-1 bases before the group are rolled in first
         const uint32_t first = gi * 32u >= k - 1u ? gi * 32u - (k - 1u) : 0u;
         uint64_t key = 0ull;
-        uint32_t run = 0u;
+        uint32_t run = 0u, vbits = 0u, mbits = 0u;
         for (uint32_t pos = first; pos < L && pos < gi * 32u + 32u; ++pos)
         {
             const uint64_t bw = bases[g0 + (pos >> 5)];
@@ -217,9 +223,68 @@ __global__ void __launch_bounds__(kBlockH) ktable_canon_kernel(const uint64_t * 
             const uint64_t si = ktable_slot_of(kt, key & kt.mask_b);
             if (si == ~0ull) continue;
             const uint64_t w = *kt_slot(kt, si);
-            if (!(w >> 63)) continue;
+            if (WALK)
+            {
+                vbits |= 1u << (pos & 31u);
+                if (w >> 63) mbits |= 1u << (pos & 31u);
+            }
+            else if (!(w >> 63)) continue;
             const uint64_t start = 32ull * g0 + (pos + 1u - k);
-            atomicMin(reinterpret_cast<unsigned long long *>(kt_slot(kt, si)), (1ull << 63) | (start << kt.pshift) | (w & low_mask));
+            atomicMin(reinterpret_cast<unsigned long long *>(kt_slot(kt, si)), (w & (1ull << 63)) | (start << kt.pshift) | (w & low_mask));
+        }
+        if (WALK)
+        {
+            tflags[g0 + gi] = (uint64_t)vbits | ((uint64_t)mbits << 32);
+            gvar[g0 + gi] = (uint16_t)text_group[text];
+        }
+    }
+}
+
+// walk form, between the build and the canon pass: the variant leaves every stored slot -- bit 63 = held by several variants,
+// the position field = all ones (above every position), remainder and displacement stay
+__global__ void __launch_bounds__(kBlockH) ktable_prep_pos_kernel(const KTabView kt)
+{
+    const uint64_t n_slots = 4ull * ((uint64_t)kt.nbmask + 1ull);
+    const uint64_t low_mask = (1ull << kt.pshift) - 1ull;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const uint64_t w = *kt_slot(kt, i);
+        if (w == kSlotFree) continue;
+        const uint64_t multi = (w >> 48) == kValMulti ? 1ull << 63 : 0ull;
+        *kt_slot(kt, i) = multi | (((1ull << 63) - 1ull) & ~low_mask) | (w & low_mask);
+    }
+}
+
+// Walk form of the fold, after the prefix sum: the walking scan records whole stretches of text positions, whatever their k-mers.
+// A position whose k-mer belongs to one variant drops its count (the refinement takes those from the per-variant counts); one
+// whose k-mer has its smallest position elsewhere moves its count there, so that kpos_fold_kernel searches every k-mer once.
+__global__ void __launch_bounds__(kBlockH) kpos_canon_counts_kernel(const KTabView kt, const uint32_t k, unsigned long long * __restrict__ cnt,
+                                                                    const uint64_t npos)
+{
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < npos; p += (uint64_t)gridDim.x * blockDim.x)
+    {
+        const unsigned long long m = cnt[p];
+        if (m == 0ull) continue;
+        const uint64_t e = p + k - 1u;
+        const uint64_t fl = e < 32ull * kt.tgroups ? kt.tflags[e >> 5] : 0ull;
+        if (!((fl >> (32u + (uint32_t)(e & 31ull))) & 1ull))
+        {
+            cnt[p] = 0ull;
+            continue;
+        }
+        uint64_t key = 0ull;
+        for (uint32_t j = 0; j < k; ++j)
+        {
+            const uint64_t q = p + j;
+            key = (key << 2) | ((kt.tbases[q >> 5] >> (2u * (uint32_t)(q & 31ull))) & 3ull);
+        }
+        const uint64_t si = ktable_slot_of(kt, key & kt.mask_b);
+        if (si == ~0ull) continue;
+        const uint64_t c = (*kt_slot(kt, si) & ~(1ull << 63)) >> kt.pshift;
+        if (c != p)
+        {
+            atomicAdd(cnt + c, m);
+            cnt[p] = 0ull;
         }
     }
 }
@@ -523,7 +588,18 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                             // run-length tally is closed at the end of every unit, so the variant of an open run is already
                             // in the unit's set.  Nothing is recorded for the refinement: a k-mer of one variant contributes
                             // a[g] / a[g] = 1 per window (src/fm_scanner.cpp:1099-1119), i.e. the variant's unique count.
-                            const uint32_t g = hi >> 16;
+                            uint32_t g = hi >> 16;
+                            if (kt.walk)
+                            {
+                                // table in walk form: the slot holds the k-mer's position, the variant is that of its text
+                                uint32_t p = hi & 0x7FFFFFFFu;
+                                if (kt.pshift != 32u)
+                                {
+                                    const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
+                                    p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
+                                }
+                                g = kt.gvar[p >> 5];
+                            }
                             if (g != agg_g)
                             {
                                 if (agg_g != kNoGroup) env.unique(agg_g, agg_n, agg_w);
@@ -644,6 +720,341 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
         if (lane == 0u && wp) atomicAdd(a.scalars + SC_STEPS, (unsigned long long)wp);
     }
     smem32_flush<LOCAL>(sm, a);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// The walking scan (global mode, one lane per read; table in walk form).  Two facts make most probes unnecessary:
+//   * a window of a read that was found at text position p, followed by a read base that equals the text's next base, IS the
+//     k-mer at p + 1 -- whose answer (a k-mer of one text? held by several variants?) was computed when the table was built
+//     and lies in two bits of KTabView::tflags; its variant, when it has one, is that of the text;
+//   * reads follow some text for most of their length: a sequencing error or a variant site ends a stretch, k windows later
+//     the next one begins.
+// So a lane alternates between two steps.  PROBE: exactly scanh_kernel's trip (kWin windows, one bucket each); when the last
+// window of the trip was found, its slot gives a text position and the lane starts to WALK: up to 32 read bases are compared
+// with the text in one XOR, the flag words say how many of the windows count for the variant of the text and how many are held
+// by several variants (two popcounts), and the whole stretch is recorded as one run of text positions (the fold drops the
+// positions of single-variant k-mers and moves the others to their k-mer's smallest position, kpos_canon_counts_kernel).
+// Tallies are the same integers as scanh_kernel's: the answer per window is the same function of the window's k-mer.
+// ---------------------------------------------------------------------------------------------------------------
+#ifndef SPEQB_WMINB
+#define SPEQB_WMINB 3
+#endif
+// the 32 bases in front of the cursor, as a key (digit i = base t-1-i): 2-bit digits reversed
+__device__ __forceinline__ uint64_t rev_digits(uint64_t s)
+{
+    const uint64_t r = __brevll(s);
+    return ((r & 0x5555555555555555ull) << 1) | ((r >> 1) & 0x5555555555555555ull);
+}
+
+template <bool RECORD, bool MASK>
+__global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabView kt, const BatchView b, const ScanArgs a, const int paired)
+{
+    constexpr int MODE = RECORD ? M_RECORD : 0;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem32 sm = smem32_view(smem_raw, a.V);
+    smem32_clear(sm, a.V);
+    smem32_tables(sm, a, false);
+    Tally32<MODE> env{b, a, sm};
+
+    const uint32_t k = a.k;
+    const uint64_t n_reads_b = b.n_reads_dev ? *b.n_reads_dev : b.n_reads;
+    const uint32_t units = (uint32_t)(paired ? n_reads_b / 2 : n_reads_b);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t kmask = (kt.rmask << 3) | 7ull;
+    const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
+    const uint32_t chunk = claim_chunk(units);
+
+    uint32_t phase = lane >= chunk ? H_DONE : H_FETCH;
+    bool mate2 = false;
+    uint32_t u = 0u;
+    uint64_t g0 = 0ull;
+    uint32_t t = 0u, pend = 0u, run = 0u;
+    uint64_t key = 0ull;
+    uint64_t cb = 0ull, nb = 0ull, pvb = 0ull;   // the 32-base group that holds base t, the following one, the one before
+    uint32_t ci = 0u, ni = 0u;
+    UnitSet<MASK> uset;
+    uint32_t c_total = 0u;
+    uint32_t agg_g = kNoGroup, agg_n = 0u;
+    // the walk: text position of the LAST base of the window that ends at read base t - 1, when that window was found there
+    uint32_t we = kNoRun, cur_g = 0u;
+    uint32_t rs = kNoRun, rl = 0xFFFFFFFDu;
+    auto run_write = [&](uint32_t s0, uint32_t s1) {
+        atomicAdd(a.diff + s0, 1ull);
+        atomicAdd(a.diff + s1 + 1u, ~0ull);
+    };
+    uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
+    uint32_t wcur = 0u, wend = 0u;
+
+    auto next_group = [&]() {
+        pvb = cb;
+        cb = nb; ci = ni;
+        if (((t >> 5) + 1u) * 32u < pend)
+        {
+            nb = load_ro(b.bases + g0 + (t >> 5) + 1u);
+            ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
+        }
+    };
+    auto roll1 = [&]() {
+        const uint32_t o = t & 31u;
+        key = (key << 2) | ((uint32_t)(cb >> (2u * o)) & 3u);
+        run = ((ci >> o) & 1u) ? 0u : run + 1u;
+        t += 1u;
+        if ((t & 31u) == 0u) next_group();
+    };
+
+    while (true)
+    {
+        __syncwarp();
+        const uint32_t ph = phase;
+        if (!__any_sync(kFullH, ph != H_DONE)) break;
+        const uint32_t m_fe = __ballot_sync(kFullH, ph == H_FETCH);
+        if (m_fe)
+        {
+            const bool claim = ph == H_FETCH && !mate2;
+            const uint32_t mc = __ballot_sync(kFullH, claim);
+            if (mc)
+            {
+                const uint32_t cnt = (uint32_t)__popc(mc), left = wend - wcur;
+                uint32_t nbase = 0u;
+                if (cnt > left)
+                {
+                    if (lane == 0u) nbase = (uint32_t)atomicAdd(a.work, (unsigned long long)chunk);
+                    nbase = __shfl_sync(kFullH, nbase, 0);
+                }
+                const uint32_t r = (uint32_t)__popc(mc & ((1u << lane) - 1u));
+                if (claim) u = r < left ? wcur + r : nbase + (r - left);
+                if (cnt > left) { wcur = nbase + (cnt - left); wend = nbase + chunk; }
+                else wcur += cnt;
+            }
+            if (ph == H_FETCH)
+            {
+                if (u >= units) phase = H_DONE;
+                else
+                {
+                    const uint64_t fr = paired ? 2ull * u + (mate2 ? 1u : 0u) : (uint64_t)u;
+                    pend = load_ro(b.len + fr);
+                    g0 = load_ro(b.grp_off + fr);
+                    phase = H_FIRST;
+                }
+            }
+        }
+        if (ph == H_FIRST)
+        {
+            const uint32_t L = pend;
+            run = 0u; key = 0ull; we = kNoRun; pvb = 0ull;
+            pend = L >= k ? L : 0u;
+            n_look += L >= k ? L - k + 1u : 0u;
+            n_reads += 1u;
+            t = 0u;
+            if (t < pend)
+            {
+                cb = load_ro(b.bases + g0);
+                ci = load_ro(b.inv + g0);
+                if (32u < pend)
+                {
+                    nb = load_ro(b.bases + g0 + 1u);
+                    ni = load_ro(b.inv + g0 + 1u);
+                }
+            }
+            phase = H_RUN;
+        }
+        else if (ph == H_RUN)
+        {
+            if (we != kNoRun)
+            {
+                // ---- walk: the read bases from t on against the text bases from we + 1 on
+                // (tflags ends with two zero words: behind the last text no window is valid, whatever the clamped base words hold)
+                const uint32_t e1 = we + 1u, ot = e1 & 31u, gt = e1 >> 5, glast = kt.tgroups - 1u;
+                const uint64_t T0 = load_ro(kt.tbases + (gt < glast ? gt : glast)), T1 = load_ro(kt.tbases + (gt + 1u < glast ? gt + 1u : glast));
+                const uint64_t F0 = load_ro(kt.tflags + gt), F1 = load_ro(kt.tflags + gt + 1u);
+                const uint32_t o = t & 31u;
+                const uint64_t TB = ot ? (T0 >> (2u * ot)) | (T1 << (64u - 2u * ot)) : T0;
+                const uint64_t RB = o ? (cb >> (2u * o)) | (nb << (64u - 2u * o)) : cb;
+                const uint32_t TV = __funnelshift_r((uint32_t)F0, (uint32_t)F1, ot);          // windows that end at e1 + j: k-mers of one text
+                const uint32_t TM = __funnelshift_r((uint32_t)(F0 >> 32), (uint32_t)(F1 >> 32), ot);   // ... held by several variants
+                const uint32_t RI = __funnelshift_r(ci, ni, o);                                 // read bases that are no ACGT
+                uint64_t x = RB ^ TB;
+                x = (x | (x >> 1)) & 0x5555555555555555ull;
+                const uint32_t lim = pend - t < 32u ? pend - t : 32u;
+                uint32_t m = x ? ((uint32_t)__ffsll((long long)x) - 1u) >> 1 : 32u;             // bases that agree
+                const uint32_t stop = RI | ~TV;
+                const uint32_t m2 = stop ? (uint32_t)__ffs((int)stop) - 1u : 32u;
+                m = m < m2 ? m : m2;
+                m = m < lim ? m : lim;
+                if (m != 0u)
+                {
+                    const uint32_t mm = m == 32u ? 0xFFFFFFFFu : (1u << m) - 1u;
+                    const uint32_t nm = (uint32_t)__popc(TM & mm), nu = m - nm;
+                    c_total += m;                                 // every one of the m windows is a k-mer of the index
+                    if (nu)
+                    {
+                        if (cur_g != agg_g)
+                        {
+                            if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
+                            agg_g = cur_g; agg_n = 0u;
+                            uset.add(cur_g);
+                        }
+                        agg_n += nu;
+                    }
+                    if (RECORD && nm)
+                    {
+                        const uint32_t s0 = e1 - (k - 1u), s1 = s0 + m - 1u;   // where the m windows START in the texts
+                        if (s0 == rl + 1u) rl = s1;
+                        else
+                        {
+                            if (rs != kNoRun) run_write(rs, rl);
+                            rs = s0; rl = s1;
+                        }
+                    }
+                    we += m;
+                    t += m;
+                    if (o + m >= 32u) next_group();
+                }
+                if (m < lim)
+                {
+                    // the stretch ends in front of base t (a base that differs, an N, the end of the text): the table again.
+                    // The key of the k-1 bases before t is rebuilt from the two groups that hold them.
+                    we = kNoRun;
+                    const uint32_t o2 = t & 31u;
+                    key = rev_digits(o2 ? (pvb >> (2u * o2)) | (cb << (64u - 2u * o2)) : pvb);
+                    run = k;
+                }
+            }
+            if (we == kNoRun && t < pend)
+            {
+                // ---- probe: up to kWin windows, every probe issued, then consumed in window order (as scanh_kernel)
+                while (run + 1u < k && t < pend) roll1();
+                uint32_t w[kWin][8];
+                uint32_t pb[kWin], want_lo[kWin], want_hi[kWin];
+                bool due[kWin];
+                const uint32_t o = t & 31u;
+                const uint32_t nbase = pend - t < (uint32_t)kWin ? pend - t : (uint32_t)kWin;
+                uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
+                if (o + (uint32_t)kWin > 32u)
+                {
+                    bits |= (uint32_t)nb << (2u * (32u - o));
+                    ibits |= ni << (32u - o);
+                }
+#pragma unroll
+                for (int j = 0; j < kWin; ++j)
+                {
+                    due[j] = false;
+                    if ((uint32_t)j < nbase)
+                    {
+                        key = (key << 2) | ((bits >> (2 * j)) & 3u);
+                        run = ((ibits >> j) & 1u) ? 0u : run + 1u;
+                        due[j] = run >= k;
+                    }
+                    if (due[j])
+                    {
+                        const uint64_t h = (key * kt.mul) & kt.mask_b;
+                        pb[j] = (uint32_t)(h >> kt.rbits);
+                        const uint64_t want = h & kt.rmask;
+                        want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                     : "l"(kt.slots + 4ull * pb[j]));
+                    }
+                }
+                t += nbase;
+                if (o + nbase >= 32u) next_group();
+                uint32_t lastp = 0u;
+                int lasthit = -1;
+#pragma unroll
+                for (int j = 0; j < kWin; ++j)
+                {
+                    if (!due[j]) continue;
+                    c_total += 1u;
+                    n_probe += 1u;
+                    uint32_t d = 0u;
+                    while (true)
+                    {
+                        const bool h0 = (((w[j][0] ^ want_lo[j]) & kmask_lo) | ((w[j][1] ^ want_hi[j]) & kmask_hi)) == 0u;
+                        const bool h1 = (((w[j][2] ^ want_lo[j]) & kmask_lo) | ((w[j][3] ^ want_hi[j]) & kmask_hi)) == 0u;
+                        const bool h2 = (((w[j][4] ^ want_lo[j]) & kmask_lo) | ((w[j][5] ^ want_hi[j]) & kmask_hi)) == 0u;
+                        const bool h3 = (((w[j][6] ^ want_lo[j]) & kmask_lo) | ((w[j][7] ^ want_hi[j]) & kmask_hi)) == 0u;
+                        if (h0 || h1 || h2 || h3)
+                        {
+                            const uint32_t hi = h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7];
+                            uint32_t p = hi & 0x7FFFFFFFu;        // where the k-mer starts in the texts (its smallest position)
+                            if (kt.pshift != 32u)
+                            {
+                                const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
+                                p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
+                            }
+                            lastp = p; lasthit = j;
+                            if (!slot_multi(hi))
+                            {
+                                const uint32_t g = load_ro(kt.gvar + (p >> 5));
+                                if (g != agg_g)
+                                {
+                                    if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
+                                    agg_g = g; agg_n = 0u;
+                                    uset.add(g);
+                                }
+                                agg_n += 1u;
+                            }
+                            else if (RECORD)
+                            {
+                                if (p == rl + 1u) rl = p;
+                                else
+                                {
+                                    if (rs != kNoRun) run_write(rs, rl);
+                                    rs = p; rl = p;
+                                }
+                            }
+                            break;
+                        }
+                        if ((w[j][6] & w[j][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;
+                        d += 1u;
+                        n_probe += 1u;
+                        pb[j] = (pb[j] + 1u) & kt.nbmask;
+                        const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kt.rbits);
+                        want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                     : "l"(kt.slots + 4ull * pb[j]));
+                    }
+                }
+                // the window that ends at base t - 1 was found: the next windows are looked for in the text behind it
+                if (lasthit >= 0 && (uint32_t)lasthit + 1u == nbase && t < pend)
+                {
+                    we = lastp + k - 1u;
+                    cur_g = load_ro(kt.gvar + (we >> 5));
+                }
+            }
+        }
+        if (phase == H_RUN && t >= pend)
+        {
+            if (paired && !mate2) mate2 = true;
+            else
+            {
+                n_total += c_total;
+                if (uset.ambiguous()) { n_amb += 1u; env.fusion(uset.key()); }
+                c_total = 0u; uset.reset();
+                if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
+                agg_g = kNoGroup; agg_n = 0u;
+                mate2 = false;
+                if ((n_total | n_look) & 0x80000000u)
+                {
+                    env.add64(0, n_total); env.add64(2, n_look);
+                    n_total = 0u; n_look = 0u;
+                }
+            }
+            phase = H_FETCH;
+        }
+    }
+    if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
+    if (RECORD && rs != kNoRun) run_write(rs, rl);
+    if (n_total) env.add64(0, n_total);
+    if (n_amb) env.add64(1, n_amb);
+    if (n_look) env.add64(2, n_look);
+    if (n_reads) env.add64(3, n_reads);
+    {
+        const uint32_t wp = __reduce_add_sync(kFullH, n_probe);
+        if (lane == 0u && wp) atomicAdd(a.scalars + SC_STEPS, (unsigned long long)wp);
+    }
+    smem32_flush<false>(sm, a);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1240,6 +1651,23 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
         if (bw <= 0) return cudaErrorLaunchOutOfResources;
         bps = wpr == 0 || bw < bps ? bw : bps;
     }
+    if (!(mode & M_LOCAL))
+    {
+        // the walking scan shares the grid
+        int bw = 0;
+        const bool rec = (mode & M_RECORD) != 0, mask = V <= kMaxGroupsMask;
+        auto occ = [&](auto kern) {
+            if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, kern, kBlockH, smem);
+        };
+        if (rec && mask) occ(scanw_kernel<true, true>);
+        else if (rec) occ(scanw_kernel<true, false>);
+        else if (mask) occ(scanw_kernel<false, true>);
+        else occ(scanw_kernel<false, false>);
+        if (e != cudaSuccess) return e;
+        if (bw <= 0) return cudaErrorLaunchOutOfResources;
+        bps = bw < bps ? bw : bps;
+    }
     cfg->block = kBlockH;
     cfg->grid = sm_count_h() * bps;
     return cudaSuccess;
@@ -1272,6 +1700,11 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
     kt->fshift = 0u;
     kt->pshift = 0u;
     kt->wide = 0u;
+    kt->walk = 0u;
+    kt->tgroups = 0u;
+    kt->tbases = nullptr;
+    kt->tflags = nullptr;
+    kt->gvar = nullptr;
     return true;
 }
 
@@ -1303,6 +1736,16 @@ cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, Ba
     const int m = (mode & (M_LOCAL | M_RECORD)) | (warp_per_read ? kWprBit : 0) | (a.V <= kMaxGroupsMask ? kMaskBit : 0);
     cudaError_t e = cudaMemsetAsync(a.work, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
+    if (kt.walk && !warp_per_read && !(mode & M_LOCAL))
+    {
+        // global mode, one lane per read, table in walk form: the walking scan
+        const bool rec = (mode & M_RECORD) != 0, mask = a.V <= kMaxGroupsMask;
+        if (rec && mask) scanw_kernel<true, true><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
+        else if (rec) scanw_kernel<true, false><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
+        else if (mask) scanw_kernel<false, true><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
+        else scanw_kernel<false, false><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
+        return cudaGetLastError();
+    }
     SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, slot_mult, b, a, paired)))
     return cudaGetLastError();
 }
@@ -1431,23 +1874,32 @@ bool ktable_positions_fit(KTabView const & kt, uint64_t npos)
     return kt.rbits + bits <= 59u && npos < 0xFFFFFFF0ull;
 }
 
+// every slot can hold a position next to its remainder, displacement and the "several variants" bit, and a position fits the
+// 32-bit cursor of the walking scan
+bool ktable_walk_fits(KTabView const & kt, uint64_t npos) { return ktable_positions_fit(kt, npos) && npos < 0x7FFF0000ull; }
+
 cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
-                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k, cudaStream_t st)
+                                const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
+                                uint64_t * tflags, uint16_t * gvar, cudaStream_t st)
 {
     if (n_texts == 0 || max_len < k) return cudaSuccess;
     const uint32_t groups = (max_len + 31u) / 32u;
     const uint32_t gx = std::min<uint32_t>((groups + kBlockH - 1) / kBlockH, (uint32_t)sm_count_h() * 8u);
+    if (tflags) ktable_prep_pos_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt);
     for (uint32_t t0 = 0; t0 < n_texts; t0 += 65535u)
     {
         const uint32_t nt = std::min<uint32_t>(65535u, n_texts - t0);
-        ktable_canon_kernel<<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, kt, k);
+        if (tflags)
+            ktable_canon_kernel<true><<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, t_group + t0, kt, k, tflags, gvar);
+        else
+            ktable_canon_kernel<false><<<dim3(gx, nt), kBlockH, 0, st>>>(t_bases, t_inv, t_grp_off + t0, t_len + t0, nullptr, kt, k, nullptr, nullptr);
     }
     return cudaGetLastError();
 }
 
 // diff -> inclusive prefix sum in place (cub) -> multiplicities at the interval starts; diff is left zeroed
 cudaError_t launch_kpos_fold(const uint64_t * t_bases, DevIndex const & ix, uint32_t k, unsigned long long * diff, uint64_t npos,
-                             void * tmp, size_t tmp_bytes, unsigned long long * mult, cudaStream_t st)
+                             void * tmp, size_t tmp_bytes, unsigned long long * mult, KTabView const & kt, cudaStream_t st)
 {
     size_t need_bytes = 0;
     cudaError_t e = cub::DeviceScan::InclusiveSum(nullptr, need_bytes, diff, diff, (int64_t)(npos + 2), st);
@@ -1455,6 +1907,7 @@ cudaError_t launch_kpos_fold(const uint64_t * t_bases, DevIndex const & ix, uint
     if (need_bytes > tmp_bytes) return cudaErrorInvalidValue;
     e = cub::DeviceScan::InclusiveSum(tmp, tmp_bytes, diff, diff, (int64_t)(npos + 2), st);
     if (e != cudaSuccess) return e;
+    if (kt.walk) kpos_canon_counts_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt, k, diff, npos);
     kpos_fold_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(t_bases, ix, k, diff, npos + 2, mult);
     return cudaGetLastError();
 }
