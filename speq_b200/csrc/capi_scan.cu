@@ -117,6 +117,7 @@ struct speqg_scan
     unsigned long long * d_diff = nullptr;
     uint64_t * d_tflags = nullptr;           // walk form of the k-mer table: per-group window flags and variants (KTabView)
     uint16_t * d_gvar = nullptr;
+    uint32_t * d_pos_side = nullptr;
     void * d_scan_tmp = nullptr;
     size_t scan_tmp_bytes = 0;
     uint64_t npos = 0;
@@ -187,7 +188,7 @@ namespace
 void scan_release(speqg_scan * s)
 {
     cudaFree(s->d_state); cudaFreeHost(s->h_state); cudaFree(s->d_fkeys); cudaFree(s->d_fvals); cudaFree(s->d_mult);
-    cudaFree(s->d_unique_n); cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_tflags); cudaFree(s->d_gvar);
+    cudaFree(s->d_unique_n); cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_tflags); cudaFree(s->d_gvar); cudaFree(s->d_pos_side);
     cudaFree(s->d_qden); cudaFree(s->d_percent); cudaFree(s->d_tkpg); cudaFree(s->d_partial);
     cudaFree(s->d_gc); cudaFree(s->d_blocks_k); cudaFree(s->d_sblk);
     cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->d_slot_mult); cudaFree(s->d_kstat);
@@ -416,12 +417,16 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             CK(cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device));
             s->npos = 32ull * h.t_bases.size();
             const bool record = params->record_multiplicity != 0, no_wide = getenv("SPEQB_NO_WIDE") != nullptr;
+            // Global mode: the single-window table in walk form (KTabView::walk, scanw_kernel) -- the scan answers most windows
+            // from the packed texts and two flag bits per text position instead of a probe, so it is also what AUTO picks for
+            // tables beyond L2 (where the pair table used to halve the probes).  SPEQB_NO_WALK=1 keeps the probing scans.
+            const bool walk_ok = !(s->mode & M_LOCAL) && !getenv("SPEQB_NO_WALK") && !getenv("SPEQB_NO_RUNS") && s->npos < 0x7FFF0000ull;
             for (uint32_t grow = 0;; ++grow)
             {
                 need(grow < 4 && ktable_geometry(params->k, ub, grow, &s->kt), "k-mer table too large");
                 // a table beyond L2 that has to count hits per slot keeps the counters inside its (then 64-byte) buckets
                 const bool big = 32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 || getenv("SPEQB_FORCE_WIDE");
-                const bool pair = s->algo == SPEQG_ALGO_KPAIR || (auto_algo && idx->host.V <= kMaxGroupsPair && big);
+                const bool pair = s->algo == SPEQG_ALGO_KPAIR || (auto_algo && idx->host.V <= kMaxGroupsPair && big && !walk_ok);
                 // (only the pair-table scan reads wide tables: the single-window kernel's hot loop addresses 32-byte buckets)
                 s->kt.wide = record && big && !no_wide && pair ? 1u : 0u;
                 s->kt.slots = dev_alloc<uint64_t>((4ull << s->kt.wide) * ((uint64_t)s->kt.nbmask + 1));
@@ -436,21 +441,25 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 CK(cudaFree(s->kt.slots));
                 s->kt.slots = nullptr;
             }
-            CK(scanh_launch_cfg(s->mode, V, &s->cfg_h));
             if (auto_algo && idx->host.V <= kMaxGroupsPair)
             {
                 // A table that does not stay in L2 is bound by the HBM random-sector rate: halving the probes (two windows
                 // per probe) pays there (C4: +43 %), while on an L2-resident table the single-window kernel is faster.
-                if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3) s->algo = SPEQG_ALGO_KPAIR;
+                if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 && !walk_ok) s->algo = SPEQG_ALGO_KPAIR;
             }
-            // Global mode, single-window table scan: when a text position fits into every slot the table is put into walk form
-            // (KTabView::walk, scanw_kernel) -- the scan then answers most windows from the packed texts and two flag bits per
-            // text position instead of a probe.  SPEQB_NO_WALK=1 keeps the probing scan (measurements).
-            const bool walk = s->algo == SPEQG_ALGO_KTABLE && !s->kt.wide && !(s->mode & M_LOCAL) && !getenv("SPEQB_NO_WALK") &&
-                              !getenv("SPEQB_NO_RUNS") && ktable_walk_fits(s->kt, s->npos) && h.t_bases.size() < 0x7FFFFFFFull;
+            const bool walk = s->algo == SPEQG_ALGO_KTABLE && !s->kt.wide && walk_ok;
+            CK(scanh_launch_cfg(s->mode, V, walk ? 1 : 0, &s->cfg_h));
             if (walk)
             {
-                s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
+                // the position goes into the slot when it fits next to remainder and displacement (from bit 32 when those fit the
+                // low word: one AND extracts it); else into a side array, one 32-bit position per slot
+                const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
+                if (ktable_positions_fit(s->kt, s->npos)) s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
+                else
+                {
+                    s->d_pos_side = dev_alloc<uint32_t>(n_slots);
+                    s->kt.pos_side = s->d_pos_side;
+                }
                 s->kt.tgroups = (uint32_t)h.t_bases.size();
                 s->d_tflags = dev_alloc<uint64_t>((size_t)s->kt.tgroups + 2);
                 s->d_gvar = dev_alloc<uint16_t>((size_t)s->kt.tgroups + 2);
@@ -467,6 +476,14 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                     s->d_diff = dev_alloc<unsigned long long>(s->npos + 2);
                     s->scan_tmp_bytes = kpos_fold_tmp_bytes(s->npos);
                     CK(cudaMalloc(&s->d_scan_tmp, s->scan_tmp_bytes));
+                }
+                // a table beyond L2: the presence filter answers the windows with a sequencing error out of L2
+                if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 && !getenv("SPEQB_NO_FILTER"))
+                {
+                    s->filt_bits = kfilter_bits(params->k, s->ktab_keys);
+                    s->kt.fshift = 2u * params->k - s->filt_bits;
+                    s->kt.filt = dev_alloc<uint32_t>(std::max<uint64_t>(1, (1ull << s->filt_bits) / 32));
+                    CK(launch_kfilter_build(s->kt, s->filt_bits, s->compute));
                 }
             }
             else if (params->record_multiplicity)
@@ -536,10 +553,10 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
             if (!auto_algo || (e.code != SPEQG_ENOMEM && e.code != SPEQG_EINVAL)) throw;
             cudaGetLastError();
             cudaFree(s->kt.slots); cudaFree(s->kt.filt); cudaFree(s->kp.slots); cudaFree(s->d_slot_mult); cudaFree(s->d_pair_mult);
-            cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_kstat); cudaFree(s->d_tflags); cudaFree(s->d_gvar);
+            cudaFree(s->d_diff); cudaFree(s->d_scan_tmp); cudaFree(s->d_kstat); cudaFree(s->d_tflags); cudaFree(s->d_gvar); cudaFree(s->d_pos_side);
             s->kt = KTabView{}; s->kp = KTabView{};
             s->d_slot_mult = s->d_pair_mult = s->d_diff = s->d_kstat = nullptr;
-            s->d_tflags = nullptr; s->d_gvar = nullptr;
+            s->d_tflags = nullptr; s->d_gvar = nullptr; s->d_pos_side = nullptr;
             s->d_scan_tmp = nullptr;
             s->ktab_keys = s->kpair_keys = 0;
             s->algo = SPEQG_ALGO_ROLLING;

@@ -120,6 +120,9 @@ struct KTabView
     const uint64_t * tflags;      // per group: low word = bit j set when the window that ENDS at base 32 g + j is an N-free k-mer of
                                   // one text; high word = ... and texts of several variants hold that k-mer
     const uint16_t * gvar;        // variant of the text a group belongs to
+    // walk != 0 with pshift == 0 (a position does not fit next to the remainder: large tables): the slots keep their variant
+    // and the positions live in a side array, one per slot -- read only where the walk starts and where a hit is recorded
+    uint32_t * pos_side;
 };
 bool ktable_positions_fit(KTabView const & kt, uint64_t npos);
 cudaError_t launch_ktable_clear(KTabView const & kt, cudaStream_t st);
@@ -128,7 +131,6 @@ cudaError_t launch_ktable_zero_counters(KTabView const & kt, cudaStream_t st);
 cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                 const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
                                 uint64_t * tflags, uint16_t * gvar, cudaStream_t st);
-bool ktable_walk_fits(KTabView const & kt, uint64_t npos);
 size_t kpos_fold_tmp_bytes(uint64_t npos);
 cudaError_t launch_kpos_fold(const uint64_t * t_bases, DevIndex const & ix, uint32_t k, unsigned long long * diff, uint64_t npos,
                              void * tmp, size_t tmp_bytes, unsigned long long * mult, KTabView const & kt, cudaStream_t st);
@@ -144,7 +146,7 @@ cudaError_t launch_ktable_fold_mult(KTabView const & kt, DevIndex const & ix, ui
 // warp_per_read != 0: the 32 lanes of a warp split the windows of one read (long reads); else one read / pair per lane
 cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
                          int warp_per_read, LaunchCfg cfg, cudaStream_t st);
-cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg);
+cudaError_t scanh_launch_cfg(int mode, uint32_t V, int walk, LaunchCfg * cfg);   // walk: the table is in walk form (scanw_kernel shares the grid)
 // two windows per probe (SPEQG_ALGO_KPAIR): a second table over the (k+1)-mers of the texts, values = one byte per k-mer
 cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, KTabView const & kp, uint32_t k,

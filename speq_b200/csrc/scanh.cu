@@ -230,7 +230,8 @@ __global__ void __launch_bounds__(kBlockH) ktable_canon_kernel(const uint64_t * 
             }
             else if (!(w >> 63)) continue;
             const uint64_t start = 32ull * g0 + (pos + 1u - k);
-            atomicMin(reinterpret_cast<unsigned long long *>(kt_slot(kt, si)), (w & (1ull << 63)) | (start << kt.pshift) | (w & low_mask));
+            if (WALK && kt.pshift == 0u) atomicMin(kt.pos_side + si, (uint32_t)start);
+            else atomicMin(reinterpret_cast<unsigned long long *>(kt_slot(kt, si)), (w & (1ull << 63)) | (start << kt.pshift) | (w & low_mask));
         }
         if (WALK)
         {
@@ -280,7 +281,7 @@ __global__ void __launch_bounds__(kBlockH) kpos_canon_counts_kernel(const KTabVi
         }
         const uint64_t si = ktable_slot_of(kt, key & kt.mask_b);
         if (si == ~0ull) continue;
-        const uint64_t c = (*kt_slot(kt, si) & ~(1ull << 63)) >> kt.pshift;
+        const uint64_t c = kt.pshift ? (*kt_slot(kt, si) & ~(1ull << 63)) >> kt.pshift : (uint64_t)kt.pos_side[si];
         if (c != p)
         {
             atomicAdd(cnt + c, m);
@@ -589,7 +590,7 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                             // in the unit's set.  Nothing is recorded for the refinement: a k-mer of one variant contributes
                             // a[g] / a[g] = 1 per window (src/fm_scanner.cpp:1099-1119), i.e. the variant's unique count.
                             uint32_t g = hi >> 16;
-                            if (kt.walk)
+                            if (kt.walk && kt.pshift != 0u)
                             {
                                 // table in walk form: the slot holds the k-mer's position, the variant is that of its text
                                 uint32_t p = hi & 0x7FFFFFFFu;
@@ -611,13 +612,14 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                         }
                         else if (RECORD)
                         {
-                            if (kt.pshift != 0u)
+                            if (kt.pshift != 0u || kt.walk)
                             {
                                 // the k-mer's smallest text position: extends the open run or starts a new one
                                 // (pshift == 32 whenever remainder + displacement fit the low word: the position is the high
-                                //  word without its top bit)
+                                //  word without its top bit; pshift == 0 in walk form: the side array)
                                 uint32_t p = hi & 0x7FFFFFFFu;
-                                if (kt.pshift != 32u)
+                                if (kt.pshift == 0u) p = kt.pos_side[4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u)];
+                                else if (kt.pshift != 32u)
                                 {
                                     const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
                                     p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
@@ -722,6 +724,60 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
     smem32_flush<LOCAL>(sm, a);
 }
 
+// L2 eviction hints (pair-table scan): evict_first for the table probes (each sector is used once), evict_last for the filter
+#ifndef SPEQB_L2HINT
+#define SPEQB_L2HINT 1
+#endif
+__device__ __forceinline__ uint64_t l2_policy_keep()
+{
+    uint64_t p = 0ull;
+#if SPEQB_L2HINT
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+#endif
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_stream()
+{
+    uint64_t p = 0ull;
+#if SPEQB_L2HINT
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+#endif
+    return p;
+}
+__device__ __forceinline__ void ldg256_stream(uint32_t (&w)[8], const void * ptr, uint64_t pol)
+{
+#if SPEQB_L2HINT
+    asm volatile("ld.global.nc.L2::cache_hint.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(ptr), "l"(pol));
+#else
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(ptr));
+#endif
+}
+// record-mode probes of the pair-table scan ask L2 to fetch 64 bytes: the bucket's counter sector rides along with its slots,
+// so the counter atomic that follows finds its sector in L2 (C4, 20 M reads: 56.0 -> 52.1 ms, profiles/r2_sweep.txt)
+#ifndef SPEQB_WIDE_PF
+#define SPEQB_WIDE_PF 1
+#endif
+__device__ __forceinline__ void ldg256_stream_pf64(uint32_t (&w)[8], const void * ptr, uint64_t pol)
+{
+    asm volatile("ld.global.nc.L2::cache_hint.L2::64B.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(ptr), "l"(pol));
+}
+__device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t pol)
+{
+    uint32_t v;
+#if SPEQB_L2HINT
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
+#else
+    asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(ptr));
+#endif
+    return v;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // The walking scan (global mode, one lane per read; table in walk form).  Two facts make most probes unnecessary:
 //   * a window of a read that was found at text position p, followed by a read base that equals the text's next base, IS the
@@ -771,7 +827,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     uint32_t t = 0u, pend = 0u, run = 0u;
     uint64_t key = 0ull;
     uint64_t cb = 0ull, nb = 0ull, pvb = 0ull;   // the 32-base group that holds base t, the following one, the one before
-    uint32_t ci = 0u, ni = 0u;
+    uint32_t ci = 0u, ni = 0u, pvi = 0u;
     UnitSet<MASK> uset;
     uint32_t c_total = 0u;
     uint32_t agg_g = kNoGroup, agg_n = 0u;
@@ -786,7 +842,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     uint32_t wcur = 0u, wend = 0u;
 
     auto next_group = [&]() {
-        pvb = cb;
+        pvb = cb; pvi = ci;
         cb = nb; ci = ni;
         if (((t >> 5) + 1u) * 32u < pend)
         {
@@ -794,12 +850,14 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
             ni = load_ro(b.inv + g0 + (t >> 5) + 1u);
         }
     };
-    auto roll1 = [&]() {
-        const uint32_t o = t & 31u;
-        key = (key << 2) | ((uint32_t)(cb >> (2u * o)) & 3u);
-        run = ((ci >> o) & 1u) ? 0u : run + 1u;
-        t += 1u;
-        if ((t & 31u) == 0u) next_group();
+    // key and run of the cursor from the 32 bases in front of it (the two groups that hold them), instead of rolling them in
+    // one by one: lanes start their reads at different times here, and a per-base loop would run for one lane at a time
+    auto seek = [&]() {
+        const uint32_t o2 = t & 31u;
+        key = rev_digits(o2 ? (pvb >> (2u * o2)) | (cb << (64u - 2u * o2)) : pvb);
+        const uint32_t iv = __funnelshift_r(pvi, ci, o2);         // bit 31 = base t - 1
+        const uint32_t z = (uint32_t)__clz((int)iv);
+        run = z < t ? z : t;
     };
 
     while (true)
@@ -841,7 +899,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
         if (ph == H_FIRST)
         {
             const uint32_t L = pend;
-            run = 0u; key = 0ull; we = kNoRun; pvb = 0ull;
+            run = 0u; key = 0ull; we = kNoRun; pvb = 0ull; pvi = 0u;
             pend = L >= k ? L : 0u;
             n_look += L >= k ? L - k + 1u : 0u;
             n_reads += 1u;
@@ -855,6 +913,8 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                     nb = load_ro(b.bases + g0 + 1u);
                     ni = load_ro(b.inv + g0 + 1u);
                 }
+                t = k - 1u;                                       // (k <= 31: inside the first group) the first window ends here
+                seek();
             }
             phase = H_RUN;
         }
@@ -915,18 +975,23 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                     // the stretch ends in front of base t (a base that differs, an N, the end of the text): the table again.
                     // The key of the k-1 bases before t is rebuilt from the two groups that hold them.
                     we = kNoRun;
-                    const uint32_t o2 = t & 31u;
-                    key = rev_digits(o2 ? (pvb >> (2u * o2)) | (cb << (64u - 2u * o2)) : pvb);
-                    run = k;
+                    seek();
                 }
             }
             if (we == kNoRun && t < pend)
             {
                 // ---- probe: up to kWin windows, every probe issued, then consumed in window order (as scanh_kernel)
-                while (run + 1u < k && t < pend) roll1();
+                // behind an N: the next window that can be valid ends k - 1 - run bases further on
+                while (run + 1u < k && t < pend)
+                {
+                    const uint32_t o3 = t & 31u, skip = k - 1u - run < pend - t ? k - 1u - run : pend - t;
+                    t += skip;
+                    if (o3 + skip >= 32u) next_group();
+                    seek();
+                }
                 uint32_t w[kWin][8];
                 uint32_t pb[kWin], want_lo[kWin], want_hi[kWin];
-                bool due[kWin];
+                bool due[kWin], ask[kWin];                        // a valid window; one whose bucket is read
                 const uint32_t o = t & 31u;
                 const uint32_t nbase = pend - t < (uint32_t)kWin ? pend - t : (uint32_t)kWin;
                 uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
@@ -945,19 +1010,39 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                         run = ((ibits >> j) & 1u) ? 0u : run + 1u;
                         due[j] = run >= k;
                     }
+                    ask[j] = due[j];
                     if (due[j])
                     {
                         const uint64_t h = (key * kt.mul) & kt.mask_b;
                         pb[j] = (uint32_t)(h >> kt.rbits);
                         const uint64_t want = h & kt.rmask;
                         want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                     : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                     : "l"(kt.slots + 4ull * pb[j]));
+                        if (kt.filt)
+                        {
+                            // table beyond L2: the presence filter (L2-resident) answers most windows that hold a sequencing
+                            // error; its word is parked in w[j][0] until the bucket is asked for
+                            const uint32_t fi = (uint32_t)(h >> kt.fshift);
+                            w[j][0] = ldg32_keep(kt.filt + (fi >> 5), l2_policy_keep());
+                            w[j][1] = fi & 31u;
+                        }
+                        else
+                            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                         : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                         : "l"(kt.slots + 4ull * pb[j]));
                     }
                 }
                 t += nbase;
                 if (o + nbase >= 32u) next_group();
+                if (kt.filt)
+                {
+#pragma unroll
+                    for (int j = 0; j < kWin; ++j)
+                    {
+                        if (!due[j]) continue;
+                        ask[j] = ((w[j][0] >> w[j][1]) & 1u) != 0u;
+                        if (ask[j]) ldg256_stream(w[j], kt.slots + 4ull * pb[j], l2_policy_stream());
+                    }
+                }
                 uint32_t lastp = 0u;
                 int lasthit = -1;
 #pragma unroll
@@ -965,6 +1050,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                 {
                     if (!due[j]) continue;
                     c_total += 1u;
+                    if (!ask[j]) continue;                        // not in the filter: not in the index
                     n_probe += 1u;
                     uint32_t d = 0u;
                     while (true)
@@ -977,7 +1063,8 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                         {
                             const uint32_t hi = h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7];
                             uint32_t p = hi & 0x7FFFFFFFu;        // where the k-mer starts in the texts (its smallest position)
-                            if (kt.pshift != 32u)
+                            if (kt.pshift == 0u) p = load_ro(kt.pos_side + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u));
+                            else if (kt.pshift != 32u)
                             {
                                 const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
                                 p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
@@ -985,7 +1072,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                             lastp = p; lasthit = j;
                             if (!slot_multi(hi))
                             {
-                                const uint32_t g = load_ro(kt.gvar + (p >> 5));
+                                const uint32_t g = kt.pshift == 0u ? hi >> 16 : (uint32_t)load_ro(kt.gvar + (p >> 5));
                                 if (g != agg_g)
                                 {
                                     if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
@@ -1065,60 +1152,6 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
 // the k-mer table, exactly as scanh_kernel does.  Windows that cannot be paired (odd one at the end of a read, next to an
 // N) take the same single-window path.
 // ---------------------------------------------------------------------------------------------------------------
-// L2 eviction hints (pair-table scan): evict_first for the table probes (each sector is used once), evict_last for the filter
-#ifndef SPEQB_L2HINT
-#define SPEQB_L2HINT 1
-#endif
-__device__ __forceinline__ uint64_t l2_policy_keep()
-{
-    uint64_t p = 0ull;
-#if SPEQB_L2HINT
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-#endif
-    return p;
-}
-__device__ __forceinline__ uint64_t l2_policy_stream()
-{
-    uint64_t p = 0ull;
-#if SPEQB_L2HINT
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-#endif
-    return p;
-}
-__device__ __forceinline__ void ldg256_stream(uint32_t (&w)[8], const void * ptr, uint64_t pol)
-{
-#if SPEQB_L2HINT
-    asm volatile("ld.global.nc.L2::cache_hint.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                 : "l"(ptr), "l"(pol));
-#else
-    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                 : "l"(ptr));
-#endif
-}
-// record-mode probes of the pair-table scan ask L2 to fetch 64 bytes: the bucket's counter sector rides along with its slots,
-// so the counter atomic that follows finds its sector in L2 (C4, 20 M reads: 56.0 -> 52.1 ms, profiles/r2_sweep.txt)
-#ifndef SPEQB_WIDE_PF
-#define SPEQB_WIDE_PF 1
-#endif
-__device__ __forceinline__ void ldg256_stream_pf64(uint32_t (&w)[8], const void * ptr, uint64_t pol)
-{
-    asm volatile("ld.global.nc.L2::cache_hint.L2::64B.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                 : "l"(ptr), "l"(pol));
-}
-__device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t pol)
-{
-    uint32_t v;
-#if SPEQB_L2HINT
-    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
-#else
-    asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(ptr));
-#endif
-    return v;
-}
-
 constexpr uint32_t kAbsent = 0x10000u;
 
 // value of `key` in a table (synchronous probe sequence), kAbsent when it is not stored; bucket / j = where it is stored
@@ -1633,7 +1666,7 @@ constexpr int kMaskBit = 32;  // dispatch selector: the unit's variants as a 64-
         default: return cudaErrorInvalidValue;                                          \
     }
 
-cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
+cudaError_t scanh_launch_cfg(int mode, uint32_t V, int walk, LaunchCfg * cfg)
 {
     const size_t smem = scan32_smem_bytes(V);
     int bps = 0;
@@ -1651,7 +1684,7 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, LaunchCfg * cfg)
         if (bw <= 0) return cudaErrorLaunchOutOfResources;
         bps = wpr == 0 || bw < bps ? bw : bps;
     }
-    if (!(mode & M_LOCAL))
+    if (walk && !(mode & M_LOCAL))
     {
         // the walking scan shares the grid
         int bw = 0;
@@ -1705,6 +1738,7 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
     kt->tbases = nullptr;
     kt->tflags = nullptr;
     kt->gvar = nullptr;
+    kt->pos_side = nullptr;
     return true;
 }
 
@@ -1874,10 +1908,6 @@ bool ktable_positions_fit(KTabView const & kt, uint64_t npos)
     return kt.rbits + bits <= 59u && npos < 0xFFFFFFF0ull;
 }
 
-// every slot can hold a position next to its remainder, displacement and the "several variants" bit, and a position fits the
-// 32-bit cursor of the walking scan
-bool ktable_walk_fits(KTabView const & kt, uint64_t npos) { return ktable_positions_fit(kt, npos) && npos < 0x7FFF0000ull; }
-
 cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                 const int32_t * t_group, uint32_t n_texts, uint32_t max_len, KTabView const & kt, uint32_t k,
                                 uint64_t * tflags, uint16_t * gvar, cudaStream_t st)
@@ -1885,7 +1915,12 @@ cudaError_t launch_ktable_canon(const uint64_t * t_bases, const uint32_t * t_inv
     if (n_texts == 0 || max_len < k) return cudaSuccess;
     const uint32_t groups = (max_len + 31u) / 32u;
     const uint32_t gx = std::min<uint32_t>((groups + kBlockH - 1) / kBlockH, (uint32_t)sm_count_h() * 8u);
-    if (tflags) ktable_prep_pos_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt);
+    if (tflags && kt.pshift != 0u) ktable_prep_pos_kernel<<<sm_count_h() * 8, kBlockH, 0, st>>>(kt);
+    if (tflags && kt.pshift == 0u)
+    {
+        cudaError_t e = cudaMemsetAsync(kt.pos_side, 0xFF, 16ull * ((uint64_t)kt.nbmask + 1ull), st);
+        if (e != cudaSuccess) return e;
+    }
     for (uint32_t t0 = 0; t0 < n_texts; t0 += 65535u)
     {
         const uint32_t nt = std::min<uint32_t>(65535u, n_texts - t0);
