@@ -179,9 +179,11 @@ typedef struct speqg_counts
     /* filled by speqg_scan_stats only (reference-semantics work counters for the roofline): */
     uint64_t steps_executed;    /* backward_search calls incl. the failing one (fm_index_cursor.hpp:316-324); from
                                    speqg_scan_finish with a table algorithm: 32-byte table probes issued */
-    uint64_t kmers_hit;         /* k-mers with a non-empty final interval */
+    uint64_t kmers_hit;         /* k-mers with a non-empty final interval; from speqg_scan_finish with the walking table scan
+                                   (global mode): windows answered from the packed texts, without a table probe */
     uint64_t occurrences;       /* sum of final interval sizes */
-    uint64_t occ_sectors;       /* sum ceil(occ/32) */
+    uint64_t occ_sectors;       /* sum ceil(occ/32); from speqg_scan_finish with the walking table scan: walk steps (<= 32
+                                   windows each) */
 } speqg_counts;
 
 int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, speqg_scan ** out);

@@ -253,7 +253,7 @@ void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
         CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, wpr, s->cfg_h, s->compute));
-        if (s->mode & M_RECORD) (s->kt.pshift ? s->diff_dirty : s->slot_mult_dirty) = true;
+        if (s->mode & M_RECORD) (s->d_diff ? s->diff_dirty : s->slot_mult_dirty) = true;
     }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
     if ((s->mode & M_RECORD) && s->algo != SPEQG_ALGO_KTABLE && s->algo != SPEQG_ALGO_KPAIR) s->mult_dirty = true;   // these record into mult[] directly
@@ -454,7 +454,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 // the position goes into the slot when it fits next to remainder and displacement (from bit 32 when those fit the
                 // low word: one AND extracts it); else into a side array, one 32-bit position per slot
                 const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
-                if (ktable_positions_fit(s->kt, s->npos)) s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
+                if (ktable_positions_fit(s->kt, s->npos) && !getenv("SPEQB_FORCE_SIDE")) s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
                 else
                 {
                     s->d_pos_side = dev_alloc<uint32_t>(n_slots);
@@ -478,7 +478,7 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                     CK(cudaMalloc(&s->d_scan_tmp, s->scan_tmp_bytes));
                 }
                 // a table beyond L2: the presence filter answers the windows with a sequencing error out of L2
-                if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 && !getenv("SPEQB_NO_FILTER"))
+                if ((32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 || getenv("SPEQB_FORCE_FILTER")) && !getenv("SPEQB_NO_FILTER"))
                 {
                     s->filt_bits = kfilter_bits(params->k, s->ktab_keys);
                     s->kt.fshift = 2u * params->k - s->filt_bits;
@@ -898,6 +898,11 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
         counts->reads = sc[SC_READS];
         counts->kernel_launches = s->launches;
         counts->steps_executed = sc[SC_STEPS];   // table algorithms: 32-byte table probes issued (0 otherwise)
+        if (s->kt.walk)
+        {
+            counts->kmers_hit = sc[SC_HIT];      // the walking scan: windows answered from the texts, without a probe ...
+            counts->occ_sectors = sc[SC_OCCSEC]; // ... and the steps (<= 32 windows each) that answered them
+        }
     }
     SPEQG_CATCH
 }

@@ -839,6 +839,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
         atomicAdd(a.diff + s1 + 1u, ~0ull);
     };
     uint32_t n_total = 0u, n_amb = 0u, n_look = 0u, n_reads = 0u, n_probe = 0u;
+    uint32_t n_wwin = 0u, n_wstep = 0u;          // windows answered by the walk, and the steps (<= 32 windows each) that did it
     uint32_t wcur = 0u, wend = 0u;
 
     auto next_group = [&]() {
@@ -946,6 +947,8 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                     const uint32_t mm = m == 32u ? 0xFFFFFFFFu : (1u << m) - 1u;
                     const uint32_t nm = (uint32_t)__popc(TM & mm), nu = m - nm;
                     c_total += m;                                 // every one of the m windows is a k-mer of the index
+                    n_wwin += m;
+                    n_wstep += 1u;
                     if (nu)
                     {
                         if (cur_g != agg_g)
@@ -1140,6 +1143,10 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     {
         const uint32_t wp = __reduce_add_sync(kFullH, n_probe);
         if (lane == 0u && wp) atomicAdd(a.scalars + SC_STEPS, (unsigned long long)wp);
+        // (per-lane counts stay far below 2^32 / 32 for any batch that fits a device: the warp sums do not wrap)
+        const uint32_t ww = __reduce_add_sync(kFullH, n_wwin), ws = __reduce_add_sync(kFullH, n_wstep);
+        if (lane == 0u && ww) atomicAdd(a.scalars + SC_HIT, (unsigned long long)ww);
+        if (lane == 0u && ws) atomicAdd(a.scalars + SC_OCCSEC, (unsigned long long)ws);
     }
     smem32_flush<false>(sm, a);
 }

@@ -283,6 +283,8 @@ class ScanResult:
     reads: int
     kernel_launches: int
     probes: int = 0           # table algorithms: 32-byte table probes issued
+    walked: int = 0           # walking table scan: windows answered from the packed texts, without a probe
+    walk_steps: int = 0       # ... and the steps (<= 32 windows each) that answered them
 
 
 class Scan:
@@ -351,7 +353,8 @@ class Scan:
         w = np.zeros(self.V, np.float64)
         c = capi.Counts()
         capi.check(capi.lib().speqg_scan_finish(self.h, u.ctypes.data, w.ctypes.data, C.byref(c)))
-        return ScanResult(u, w, int(c.total_kmers), int(c.ambiguous_reads), int(c.lookups), int(c.reads), int(c.kernel_launches), int(c.steps_executed))
+        return ScanResult(u, w, int(c.total_kmers), int(c.ambiguous_reads), int(c.lookups), int(c.reads), int(c.kernel_launches), int(c.steps_executed),
+                          int(c.kmers_hit), int(c.occ_sectors))
 
     def stats(self, b: DeviceBatch) -> dict:
         c = capi.Counts()

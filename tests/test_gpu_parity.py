@@ -769,8 +769,14 @@ def test_walking_scan_matches_rolling(lib, k, paired, monkeypatch):
     probing = run(capi.ALGO_KTABLE)
     monkeypatch.delenv("SPEQB_NO_WALK")
     walking = run(capi.ALGO_KTABLE)
+    assert walking[0].walked > 0 and walking[0].probes < probing[0].probes
+    # the form tables beyond L2 take: positions in a side array, the presence filter in front of the probes
+    monkeypatch.setenv("SPEQB_FORCE_SIDE", "1")
+    monkeypatch.setenv("SPEQB_FORCE_FILTER", "1")
+    walking_big = run(capi.ALGO_KTABLE)
+    assert walking_big[0].walked > 0
     assert ref[0].total_kmers > 0 and ref[0].unique.sum() > 0
-    for got in (probing, walking):
+    for got in (probing, walking, walking_big):
         assert np.array_equal(got[0].unique, ref[0].unique)
         assert got[0].total_kmers == ref[0].total_kmers and got[0].ambiguous == ref[0].ambiguous
         assert got[0].lookups == ref[0].lookups and got[0].reads == ref[0].reads
