@@ -486,6 +486,7 @@ def main() -> None:
         return k0.elapsed_time(k1) / args.steps, r
     kern_ms, rk = kernel_ms(scan)
     probes_rank = rk.probes // args.steps      # table scans count the 32-byte probes they issue
+    walked_rank, wsteps_rank = rk.walked // args.steps, rk.walk_steps // args.steps   # walking table scan (global mode)
 
     # ---- the same resident step WITHOUT the recording (tallies only: enough for the closed-form percentages, not for the refinement)
     tall_only = None
@@ -598,7 +599,9 @@ def main() -> None:
     if rank == 0:
         sb, keys = info["structure_bytes"], info["keys"]
         l2_bytes = torch.cuda.get_device_properties(local_rank).L2_cache_size
-        sectors = probes_rank if table else 2 * R * L                       # the kernel's own random sectors per launch
+        # the kernel's own random sectors per launch.  A walk step reads two adjacent words of the packed texts and two of the
+        # per-position flags: 1.25 sectors each on average (a pair of 8-byte words straddles a 32-byte sector one time in four)
+        sectors = (probes_rank + (5 * wsteps_rank) // 2) if table else 2 * R * L
         own_bytes = 32 * sectors + packed_bytes
         ach = 32.0 * sectors / (kern_ms * 1e-3) / 1e9
         peak_sec = None
@@ -609,6 +612,8 @@ def main() -> None:
                 log("probe failed:", ex)
         hbm_peak, hbm_how = measured_peak()
         kname = {capi.ALGO_ROLLING: "scan32_kernel", capi.ALGO_KTABLE: "scanh_kernel", capi.ALGO_KPAIR: "scanp_kernel"}.get(algo, "scan_direct_kernel")
+        if wsteps_rank:
+            kname = "scanw_kernel"
         kname += "<%s>" % ("|".join(x for x, on in (("M_LOCAL", local), ("M_RECORD", True)) if on) or "0")
         roof = {"bound": "l2_random_sector" if sb <= l2_bytes * 3 // 4 else "hbm_random_sector",
                 "achieved": ach, "peak": None if peak_sec is None else 32.0 * peak_sec, "unit": "GB/s",
@@ -621,6 +626,17 @@ def main() -> None:
                 "algorithmic_bytes_per_launch": own_bytes,
                 "algorithmic_bytes_note": "32 B per table probe (KTABLE / KPAIR) or 2 x 32 B per read base (rolling) + the packed input stream",
                 "own_bytes_GBps": own_bytes / (kern_ms * 1e-3) / 1e9}
+        if wsteps_rank:
+            # The walking scan answers most windows from the packed texts (32 per step), so it needs a fraction of the sectors
+            # the probing scan needs and is no longer bound by them (issue slots: profiles/r2c_ncu.md).  Next to its own sectors:
+            # what one sector per valid window -- the probing scan's roofline, rounds 1-2 -- would have to sustain to match it.
+            roof.update({"table_probes_per_launch": probes_rank, "walk_steps_per_launch": wsteps_rank,
+                         "windows_answered_by_the_walk": walked_rank, "windows_per_sector": R * wpr / max(1, sectors),
+                         "algorithmic_bytes_note": "32 B per table probe + 2.5 x 32 B per walk step (<= 32 windows) + the packed input stream",
+                         "probing_scan_equivalent": {"Gsectors_per_s": R * wpr / (kern_ms * 1e-3) / 1e9,
+                                                     "frac_of_peak": None if peak_sec is None else R * wpr / (kern_ms * 1e-3) / 1e9 / peak_sec,
+                                                     "note": "one 32-byte sector per window, as scanh_kernel issues them: > 1 means no probing "
+                                                             "scan can reach this rate on this device"}})
         if sb > l2_bytes * 3 // 4:
             roof["hbm_frac"] = own_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak
             roof["hbm_peak"] = hbm_peak

@@ -795,6 +795,9 @@ __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t po
 #ifndef SPEQB_WMINB
 #define SPEQB_WMINB 3
 #endif
+#ifndef SPEQB_WKWIN
+#define SPEQB_WKWIN 3
+#endif
 // the 32 bases in front of the cursor, as a key (digit i = base t-1-i): 2-bit digits reversed
 __device__ __forceinline__ uint64_t rev_digits(uint64_t s)
 {
@@ -806,6 +809,7 @@ template <bool RECORD, bool MASK>
 __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabView kt, const BatchView b, const ScanArgs a, const int paired)
 {
     constexpr int MODE = RECORD ? M_RECORD : 0;
+    constexpr int kW = SPEQB_WKWIN;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem32 sm = smem32_view(smem_raw, a.V);
     smem32_clear(sm, a.V);
@@ -820,6 +824,9 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
     const uint32_t chunk = claim_chunk(units);
 
+    // A lane is in one of three states: it needs a read (H_FETCH), it walks (H_RUN with a text position), it probes (H_RUN
+    // without).  Lanes change state at different times, so each loop trip runs ONE of the three steps -- the one most lanes
+    // wait for -- and the others wait a trip: every step then runs with most of the warp instead of a third of it.
     uint32_t phase = lane >= chunk ? H_DONE : H_FETCH;
     bool mate2 = false;
     uint32_t u = 0u;
@@ -860,16 +867,28 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
         const uint32_t z = (uint32_t)__clz((int)iv);
         run = z < t ? z : t;
     };
+    // a unique hit of variant g (n windows)
+    auto count_unique = [&](uint32_t g, uint32_t n) {
+        if (g != agg_g)
+        {
+            if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
+            agg_g = g; agg_n = 0u;
+            uset.add(g);
+        }
+        agg_n += n;
+    };
 
     while (true)
     {
         __syncwarp();
-        const uint32_t ph = phase;
-        if (!__any_sync(kFullH, ph != H_DONE)) break;
-        const uint32_t m_fe = __ballot_sync(kFullH, ph == H_FETCH);
-        if (m_fe)
+        const bool is_f = phase == H_FETCH, is_w = phase == H_RUN && we != kNoRun, is_p = phase == H_RUN && we == kNoRun;
+        const uint32_t m_f = __ballot_sync(kFullH, is_f), m_w = __ballot_sync(kFullH, is_w), m_p = __ballot_sync(kFullH, is_p);
+        if (!(m_f | m_w | m_p)) break;
+        const int c_f = __popc(m_f), c_w = __popc(m_w), c_p = __popc(m_p);
+        if (c_f >= c_w && c_f >= c_p)
         {
-            const bool claim = ph == H_FETCH && !mate2;
+            // ---- next read: claim (first mate only), length + first group, the first groups of bases, the cursor at base k - 1
+            const bool claim = is_f && !mate2;
             const uint32_t mc = __ballot_sync(kFullH, claim);
             if (mc)
             {
@@ -885,43 +904,38 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                 if (cnt > left) { wcur = nbase + (cnt - left); wend = nbase + chunk; }
                 else wcur += cnt;
             }
-            if (ph == H_FETCH)
+            if (is_f)
             {
                 if (u >= units) phase = H_DONE;
                 else
                 {
                     const uint64_t fr = paired ? 2ull * u + (mate2 ? 1u : 0u) : (uint64_t)u;
-                    pend = load_ro(b.len + fr);
+                    const uint32_t L = load_ro(b.len + fr);
                     g0 = load_ro(b.grp_off + fr);
-                    phase = H_FIRST;
+                    run = 0u; key = 0ull; we = kNoRun; pvb = 0ull; pvi = 0u;
+                    pend = L >= k ? L : 0u;                       // L < k: the sliding view is empty (sliding.hpp:129-142)
+                    n_look += L >= k ? L - k + 1u : 0u;
+                    n_reads += 1u;
+                    t = 0u;
+                    if (pend)
+                    {
+                        cb = load_ro(b.bases + g0);
+                        ci = load_ro(b.inv + g0);
+                        if (32u < pend)
+                        {
+                            nb = load_ro(b.bases + g0 + 1u);
+                            ni = load_ro(b.inv + g0 + 1u);
+                        }
+                        t = k - 1u;                               // (k <= 31: inside the first group) the first window ends here
+                        seek();
+                    }
+                    phase = H_RUN;
                 }
             }
         }
-        if (ph == H_FIRST)
+        else if (c_w >= c_p)
         {
-            const uint32_t L = pend;
-            run = 0u; key = 0ull; we = kNoRun; pvb = 0ull; pvi = 0u;
-            pend = L >= k ? L : 0u;
-            n_look += L >= k ? L - k + 1u : 0u;
-            n_reads += 1u;
-            t = 0u;
-            if (t < pend)
-            {
-                cb = load_ro(b.bases + g0);
-                ci = load_ro(b.inv + g0);
-                if (32u < pend)
-                {
-                    nb = load_ro(b.bases + g0 + 1u);
-                    ni = load_ro(b.inv + g0 + 1u);
-                }
-                t = k - 1u;                                       // (k <= 31: inside the first group) the first window ends here
-                seek();
-            }
-            phase = H_RUN;
-        }
-        else if (ph == H_RUN)
-        {
-            if (we != kNoRun)
+            if (is_w)
             {
                 // ---- walk: the read bases from t on against the text bases from we + 1 on
                 // (tflags ends with two zero words: behind the last text no window is valid, whatever the clamped base words hold)
@@ -949,16 +963,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                     c_total += m;                                 // every one of the m windows is a k-mer of the index
                     n_wwin += m;
                     n_wstep += 1u;
-                    if (nu)
-                    {
-                        if (cur_g != agg_g)
-                        {
-                            if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
-                            agg_g = cur_g; agg_n = 0u;
-                            uset.add(cur_g);
-                        }
-                        agg_n += nu;
-                    }
+                    if (nu) count_unique(cur_g, nu);
                     if (RECORD && nm)
                     {
                         const uint32_t s0 = e1 - (k - 1u), s1 = s0 + m - 1u;   // where the m windows START in the texts
@@ -976,149 +981,143 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                 if (m < lim)
                 {
                     // the stretch ends in front of base t (a base that differs, an N, the end of the text): the table again.
-                    // The key of the k-1 bases before t is rebuilt from the two groups that hold them.
+                    // Key and run of the cursor are rebuilt from the two groups that hold the bases before t.
                     we = kNoRun;
                     seek();
                 }
             }
-            if (we == kNoRun && t < pend)
+        }
+        else if (is_p)
+        {
+            // ---- probe: up to kW windows, every probe issued, then consumed in window order up to the FIRST window that is
+            //      found -- its slot gives a text position, the walk goes on from there and answers the windows behind it
+            // (behind an N: the next window that can be valid ends k - 1 - run bases further on)
+            while (run + 1u < k && t < pend)
             {
-                // ---- probe: up to kWin windows, every probe issued, then consumed in window order (as scanh_kernel)
-                // behind an N: the next window that can be valid ends k - 1 - run bases further on
-                while (run + 1u < k && t < pend)
-                {
-                    const uint32_t o3 = t & 31u, skip = k - 1u - run < pend - t ? k - 1u - run : pend - t;
-                    t += skip;
-                    if (o3 + skip >= 32u) next_group();
-                    seek();
-                }
-                uint32_t w[kWin][8];
-                uint32_t pb[kWin], want_lo[kWin], want_hi[kWin];
-                bool due[kWin], ask[kWin];                        // a valid window; one whose bucket is read
-                const uint32_t o = t & 31u;
-                const uint32_t nbase = pend - t < (uint32_t)kWin ? pend - t : (uint32_t)kWin;
-                uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
-                if (o + (uint32_t)kWin > 32u)
-                {
-                    bits |= (uint32_t)nb << (2u * (32u - o));
-                    ibits |= ni << (32u - o);
-                }
+                const uint32_t o3 = t & 31u, skip = k - 1u - run < pend - t ? k - 1u - run : pend - t;
+                t += skip;
+                if (o3 + skip >= 32u) next_group();
+                seek();
+            }
+            uint32_t w[kW][8];
+            uint32_t pb[kW], want_lo[kW], want_hi[kW];
+            bool due[kW], ask[kW];                                // a valid window; one whose bucket is read
+            const uint32_t o = t & 31u;
+            const uint32_t nbase = pend - t < (uint32_t)kW ? pend - t : (uint32_t)kW;
+            uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
+            if (o + (uint32_t)kW > 32u)
+            {
+                bits |= (uint32_t)nb << (2u * (32u - o));
+                ibits |= ni << (32u - o);
+            }
 #pragma unroll
-                for (int j = 0; j < kWin; ++j)
+            for (int j = 0; j < kW; ++j)
+            {
+                due[j] = false;
+                if ((uint32_t)j < nbase)
                 {
-                    due[j] = false;
-                    if ((uint32_t)j < nbase)
-                    {
-                        key = (key << 2) | ((bits >> (2 * j)) & 3u);
-                        run = ((ibits >> j) & 1u) ? 0u : run + 1u;
-                        due[j] = run >= k;
-                    }
-                    ask[j] = due[j];
-                    if (due[j])
-                    {
-                        const uint64_t h = (key * kt.mul) & kt.mask_b;
-                        pb[j] = (uint32_t)(h >> kt.rbits);
-                        const uint64_t want = h & kt.rmask;
-                        want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
-                        if (kt.filt)
-                        {
-                            // table beyond L2: the presence filter (L2-resident) answers most windows that hold a sequencing
-                            // error; its word is parked in w[j][0] until the bucket is asked for
-                            const uint32_t fi = (uint32_t)(h >> kt.fshift);
-                            w[j][0] = ldg32_keep(kt.filt + (fi >> 5), l2_policy_keep());
-                            w[j][1] = fi & 31u;
-                        }
-                        else
-                            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                         : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
-                                         : "l"(kt.slots + 4ull * pb[j]));
-                    }
+                    key = (key << 2) | ((bits >> (2 * j)) & 3u);
+                    run = ((ibits >> j) & 1u) ? 0u : run + 1u;
+                    due[j] = run >= k;
                 }
-                t += nbase;
-                if (o + nbase >= 32u) next_group();
-                if (kt.filt)
+                ask[j] = due[j];
+                if (due[j])
                 {
-#pragma unroll
-                    for (int j = 0; j < kWin; ++j)
+                    const uint64_t h = (key * kt.mul) & kt.mask_b;
+                    pb[j] = (uint32_t)(h >> kt.rbits);
+                    const uint64_t want = h & kt.rmask;
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    if (kt.filt)
                     {
-                        if (!due[j]) continue;
-                        ask[j] = ((w[j][0] >> w[j][1]) & 1u) != 0u;
-                        if (ask[j]) ldg256_stream(w[j], kt.slots + 4ull * pb[j], l2_policy_stream());
+                        // table beyond L2: the presence filter (L2-resident) answers most windows that hold a sequencing
+                        // error; its word is parked in w[j][0] until the bucket is asked for
+                        const uint32_t fi = (uint32_t)(h >> kt.fshift);
+                        w[j][0] = ldg32_keep(kt.filt + (fi >> 5), l2_policy_keep());
+                        w[j][1] = fi & 31u;
                     }
-                }
-                uint32_t lastp = 0u;
-                int lasthit = -1;
-#pragma unroll
-                for (int j = 0; j < kWin; ++j)
-                {
-                    if (!due[j]) continue;
-                    c_total += 1u;
-                    if (!ask[j]) continue;                        // not in the filter: not in the index
-                    n_probe += 1u;
-                    uint32_t d = 0u;
-                    while (true)
-                    {
-                        const bool h0 = (((w[j][0] ^ want_lo[j]) & kmask_lo) | ((w[j][1] ^ want_hi[j]) & kmask_hi)) == 0u;
-                        const bool h1 = (((w[j][2] ^ want_lo[j]) & kmask_lo) | ((w[j][3] ^ want_hi[j]) & kmask_hi)) == 0u;
-                        const bool h2 = (((w[j][4] ^ want_lo[j]) & kmask_lo) | ((w[j][5] ^ want_hi[j]) & kmask_hi)) == 0u;
-                        const bool h3 = (((w[j][6] ^ want_lo[j]) & kmask_lo) | ((w[j][7] ^ want_hi[j]) & kmask_hi)) == 0u;
-                        if (h0 || h1 || h2 || h3)
-                        {
-                            const uint32_t hi = h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7];
-                            uint32_t p = hi & 0x7FFFFFFFu;        // where the k-mer starts in the texts (its smallest position)
-                            if (kt.pshift == 0u) p = load_ro(kt.pos_side + 4ull * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u));
-                            else if (kt.pshift != 32u)
-                            {
-                                const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
-                                p = (uint32_t)((u64of(lo, hi) & ~(1ull << 63)) >> kt.pshift);
-                            }
-                            lastp = p; lasthit = j;
-                            if (!slot_multi(hi))
-                            {
-                                const uint32_t g = kt.pshift == 0u ? hi >> 16 : (uint32_t)load_ro(kt.gvar + (p >> 5));
-                                if (g != agg_g)
-                                {
-                                    if (agg_g != kNoGroup) env.unique(agg_g, agg_n, 0.0);
-                                    agg_g = g; agg_n = 0u;
-                                    uset.add(g);
-                                }
-                                agg_n += 1u;
-                            }
-                            else if (RECORD)
-                            {
-                                if (p == rl + 1u) rl = p;
-                                else
-                                {
-                                    if (rs != kNoRun) run_write(rs, rl);
-                                    rs = p; rl = p;
-                                }
-                            }
-                            break;
-                        }
-                        if ((w[j][6] & w[j][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;
-                        d += 1u;
-                        n_probe += 1u;
-                        pb[j] = (pb[j] + 1u) & kt.nbmask;
-                        const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kt.rbits);
-                        want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    else
                         asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                                      : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
                                      : "l"(kt.slots + 4ull * pb[j]));
-                    }
                 }
-                // the window that ends at base t - 1 was found: the next windows are looked for in the text behind it
-                if (lasthit >= 0 && (uint32_t)lasthit + 1u == nbase && t < pend)
+            }
+            if (kt.filt)
+            {
+#pragma unroll
+                for (int j = 0; j < kW; ++j)
                 {
-                    we = lastp + k - 1u;
-                    cur_g = load_ro(kt.gvar + (we >> 5));
+                    if (!due[j]) continue;
+                    ask[j] = ((w[j][0] >> w[j][1]) & 1u) != 0u;
+                    if (ask[j]) ldg256_stream(w[j], kt.slots + 4ull * pb[j], l2_policy_stream());
+                }
+            }
+            int jh = -1;                                          // the first window of the trip that was found
+            uint32_t h_hi = 0u, h_lo = 0u;                        // its slot (h_lo: the low word, or with side positions the slot's index)
+#pragma unroll
+            for (int j = 0; j < kW; ++j)
+            {
+                if (!due[j] || jh >= 0) continue;
+                c_total += 1u;                                    // ++total_kmers (src/fm_scanner.cpp:164)
+                if (!ask[j]) continue;                            // not in the filter: not in the index
+                n_probe += 1u;
+                uint32_t d = 0u;
+                while (true)
+                {
+                    const bool h0 = (((w[j][0] ^ want_lo[j]) & kmask_lo) | ((w[j][1] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    const bool h1 = (((w[j][2] ^ want_lo[j]) & kmask_lo) | ((w[j][3] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    const bool h2 = (((w[j][4] ^ want_lo[j]) & kmask_lo) | ((w[j][5] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    const bool h3 = (((w[j][6] ^ want_lo[j]) & kmask_lo) | ((w[j][7] ^ want_hi[j]) & kmask_hi)) == 0u;
+                    if (h0 || h1 || h2 || h3)
+                    {
+                        jh = j;
+                        h_hi = h0 ? w[j][1] : h1 ? w[j][3] : h2 ? w[j][5] : w[j][7];
+                        h_lo = kt.pshift == 0u ? 4u * pb[j] + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u) : h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
+                        break;
+                    }
+                    // a free last slot ends the probe sequence: the k-mer does not occur in the index
+                    if ((w[j][6] & w[j][7]) == 0xFFFFFFFFu || d == kMaxDisp) break;
+                    // rare: the home bucket is full of other k-mers; the k-mer may sit in the next bucket
+                    d += 1u;
+                    n_probe += 1u;
+                    pb[j] = (pb[j] + 1u) & kt.nbmask;
+                    const uint64_t want = u64of(want_lo[j], want_hi[j]) + (1ull << kt.rbits);
+                    want_lo[j] = (uint32_t)want; want_hi[j] = (uint32_t)(want >> 32);
+                    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]), "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7])
+                                 : "l"(kt.slots + 4ull * pb[j]));
+                }
+            }
+            // the cursor moves behind the window that was found, or over the whole trip
+            const uint32_t adv = jh >= 0 ? (uint32_t)jh + 1u : nbase;
+            t += adv;
+            if (o + adv >= 32u) next_group();
+            if (jh >= 0)
+            {
+                // where the k-mer starts in the texts (its smallest position): in the slot, or in the side array
+                uint32_t p = h_hi & 0x7FFFFFFFu;
+                if (kt.pshift == 0u) p = load_ro(kt.pos_side + h_lo);
+                else if (kt.pshift != 32u) p = (uint32_t)((u64of(h_lo, h_hi) & ~(1ull << 63)) >> kt.pshift);
+                we = p + k - 1u;
+                cur_g = kt.pshift == 0u && !slot_multi(h_hi) ? h_hi >> 16 : (uint32_t)load_ro(kt.gvar + (p >> 5));
+                if (!slot_multi(h_hi)) count_unique(cur_g, 1u);   // ++unique_kmers[which_hit] (src/fm_scanner.cpp:178-191)
+                else if (RECORD)
+                {
+                    if (p == rl + 1u) rl = p;
+                    else
+                    {
+                        if (rs != kNoRun) run_write(rs, rl);
+                        rs = p; rl = p;
+                    }
                 }
             }
         }
         if (phase == H_RUN && t >= pend)
         {
+            // the read is finished
             if (paired && !mate2) mate2 = true;
             else
             {
+                // is_ambiguous: unique k-mers of two different variants in one read / pair (src/fm_scanner.cpp:183-190,213)
                 n_total += c_total;
                 if (uset.ambiguous()) { n_amb += 1u; env.fusion(uset.key()); }
                 c_total = 0u; uset.reset();
@@ -1131,6 +1130,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                     n_total = 0u; n_look = 0u;
                 }
             }
+            we = kNoRun;
             phase = H_FETCH;
         }
     }
@@ -1141,6 +1141,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     if (n_look) env.add64(2, n_look);
     if (n_reads) env.add64(3, n_reads);
     {
+        // sectors probed (table loads issued): one global atomic per warp
         const uint32_t wp = __reduce_add_sync(kFullH, n_probe);
         if (lane == 0u && wp) atomicAdd(a.scalars + SC_STEPS, (unsigned long long)wp);
         // (per-lane counts stay far below 2^32 / 32 for any batch that fits a device: the warp sums do not wrap)

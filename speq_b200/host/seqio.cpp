@@ -224,17 +224,27 @@ uint64_t fastq_map::region_end(uint64_t pos, uint64_t max_bytes) const
     }
 }
 
-void fastq_map::read_into(void * dst, uint64_t pos, uint64_t len, int threads) const
+void fastq_map::read_into(void * dst, uint64_t pos, uint64_t len, int threads, uint64_t * newlines) const
 {
     threads = std::max(1, std::min<int>(threads, static_cast<int>(len >> 20) + 1));
     std::vector<char> failed(static_cast<size_t>(threads), 0);
+    std::vector<uint64_t> nl(static_cast<size_t>(threads), 0);
     auto work = [&](int i)
     {
         uint64_t a = len * static_cast<uint64_t>(i) / static_cast<uint64_t>(threads), b = len * (static_cast<uint64_t>(i) + 1) / static_cast<uint64_t>(threads);
+        // with a line count wanted: blocks small enough to still be in this core's cache when they are counted
+        const uint64_t block = newlines ? (256u << 10) : ~uint64_t(0);
         while (a < b)
         {
-            ssize_t r = pread(fd_, static_cast<char *>(dst) + a, b - a, static_cast<off_t>(pos + a));
+            ssize_t r = pread(fd_, static_cast<char *>(dst) + a, std::min(b - a, block), static_cast<off_t>(pos + a));
             if (r <= 0) { failed[static_cast<size_t>(i)] = 1; return; }
+            if (newlines)
+            {
+                const char * q = static_cast<const char *>(dst) + a, * e = q + r;
+                uint64_t c = 0;
+                while (q < e && (q = static_cast<const char *>(memchr(q, '\n', static_cast<size_t>(e - q)))) != nullptr) { ++c; ++q; }
+                nl[static_cast<size_t>(i)] += c;
+            }
             a += static_cast<uint64_t>(r);
         }
     };
@@ -247,6 +257,11 @@ void fastq_map::read_into(void * dst, uint64_t pos, uint64_t len, int threads) c
     }
     for (char f : failed)
         if (f) throw std::runtime_error("read error in the FASTQ file");
+    if (newlines)
+    {
+        *newlines = 0;
+        for (uint64_t c : nl) *newlines += c;
+    }
 }
 
 namespace
@@ -311,6 +326,18 @@ uint64_t offset_after_newline(const char * p, uint64_t n, uint64_t nth, int thre
         before += cnt[i];
     }
     return n;
+}
+
+uint64_t offset_without_last_lines(const char * p, uint64_t n, uint64_t drop)
+{
+    uint64_t end = n;
+    for (; drop && end; --drop)
+    {
+        const uint64_t upto = p[end - 1] == '\n' ? end - 1 : end;     // the line's own terminator is not the previous line's
+        const void * q = memrchr(p, '\n', static_cast<size_t>(upto));
+        end = q ? static_cast<uint64_t>(static_cast<const char *>(q) - p) + 1 : 0;
+    }
+    return end;
 }
 
 void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads)

@@ -82,7 +82,8 @@ public:
     uint64_t region_end(uint64_t pos, uint64_t max_bytes) const;
     // bytes [pos, pos + len) of the file into dst with `threads` concurrent pread()s: a plain kernel copy out of the page cache
     // (no page faults, unlike touching the mapping for the first time)
-    void read_into(void * dst, uint64_t pos, uint64_t len, int threads) const;
+    // newlines != NULL: also the number of '\n' among the bytes, counted block by block while they are still in cache
+    void read_into(void * dst, uint64_t pos, uint64_t len, int threads, uint64_t * newlines = nullptr) const;
 
 private:
     uint64_t find_start(uint64_t p) const;
@@ -95,6 +96,9 @@ private:
 // flat arrays; dst offsets come from `offsets` (already filled for every slot)
 // newlines in [p, p + n), counted by `threads` threads; and the offset just behind the nth (>= 1) of them (n when there are fewer)
 uint64_t count_newlines(const char * p, uint64_t n, int threads);
+// the length of [p, p + n) without its last `drop` lines (the last one may lack its newline): a backward search, cheap when
+// few lines go
+uint64_t offset_without_last_lines(const char * p, uint64_t n, uint64_t drop);
 uint64_t offset_after_newline(const char * p, uint64_t n, uint64_t nth, int threads);
 // plain copy by `threads` threads (page cache -> pinned staging buffer)
 void parallel_copy(void * dst, const void * src, uint64_t bytes, int threads);

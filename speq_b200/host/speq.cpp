@@ -373,14 +373,15 @@ scan_out run_scan(cmd_arguments const & args, std::vector<device_lane> & lanes, 
             uint64_t n1 = m1.region_end(off1, b.cap_bytes) - off1, n2 = m2.region_end(off2, b.cap_bytes) - off2;
             if (n1 == 0 || n2 == 0) break;                            // a record larger than the staging buffer: host paths
             ck(speqg_scan_wait_ticket(L.scan, L.ticket[L.cur]), "speqg_scan_wait_ticket");
-            m1.read_into(b.seq, off1, n1, T);
-            m2.read_into(b.qual, off2, n2, T);
+            uint64_t nl1 = 0, nl2 = 0;
+            m1.read_into(b.seq, off1, n1, T, &nl1);
+            m2.read_into(b.qual, off2, n2, T, &nl2);
             const char * p1 = reinterpret_cast<const char *>(b.seq), * p2 = reinterpret_cast<const char *>(b.qual);
-            const uint64_t l1 = speq::io::count_newlines(p1, n1, T) + (p1[n1 - 1] != '\n'), l2 = speq::io::count_newlines(p2, n2, T) + (p2[n2 - 1] != '\n');
+            const uint64_t l1 = nl1 + (p1[n1 - 1] != '\n'), l2 = nl2 + (p2[n2 - 1] != '\n');
             const uint64_t recs = std::min(l1, l2) / 4;
             if (recs == 0) break;
-            if (l1 != 4 * recs) n1 = speq::io::offset_after_newline(p1, n1, 4 * recs, T);
-            if (l2 != 4 * recs) n2 = speq::io::offset_after_newline(p2, n2, 4 * recs, T);
+            if (l1 != 4 * recs) n1 = speq::io::offset_without_last_lines(p1, n1, l1 - 4 * recs);
+            if (l2 != 4 * recs) n2 = speq::io::offset_without_last_lines(p2, n2, l2 - 4 * recs);
             // both cuts must be record starts (4-line records all the way): else the files are not in the strict form here
             if ((off1 + n1 < m1.size() && m1.record_start_from(off1 + n1) != off1 + n1) ||
                 (off2 + n2 < m2.size() && m2.record_start_from(off2 + n2) != off2 + n2))
