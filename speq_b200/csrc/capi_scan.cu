@@ -454,7 +454,11 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 // the position goes into the slot when it fits next to remainder and displacement (from bit 32 when those fit the
                 // low word: one AND extracts it); else into a side array, one 32-bit position per slot
                 const uint64_t n_slots = 4ull * ((uint64_t)s->kt.nbmask + 1);
-                if (ktable_positions_fit(s->kt, s->npos) && !getenv("SPEQB_FORCE_SIDE")) s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
+                if (ktable_positions_fit(s->kt, s->npos) && !getenv("SPEQB_FORCE_SIDE"))
+                {
+                    s->kt.pshift = s->kt.rbits + 3u <= 32u ? 32u : s->kt.rbits + 3u;
+                    if (s->kt.rbits + 18u <= 32u) s->kt.vshift = s->kt.rbits + 3u;       // room for the variant too (KTabView::vshift)
+                }
                 else
                 {
                     s->d_pos_side = dev_alloc<uint32_t>(n_slots);

@@ -123,6 +123,9 @@ struct KTabView
     // walk != 0 with pshift == 0 (a position does not fit next to the remainder: large tables): the slots keep their variant
     // and the positions live in a side array, one per slot -- read only where the walk starts and where a hit is recorded
     uint32_t * pos_side;
+    // walk != 0, pshift == 32 and 15 more bits free in the low word (rbits + 18 <= 32: small k): single-variant slots ALSO keep
+    // their variant, from this bit up -- the warp-per-read scan (long reads, scanh_kernel) then needs no gvar load per hit
+    uint32_t vshift;
 };
 bool ktable_positions_fit(KTabView const & kt, uint64_t npos);
 cudaError_t launch_ktable_clear(KTabView const & kt, cudaStream_t st);

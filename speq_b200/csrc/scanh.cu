@@ -252,7 +252,8 @@ __global__ void __launch_bounds__(kBlockH) ktable_prep_pos_kernel(const KTabView
         const uint64_t w = *kt_slot(kt, i);
         if (w == kSlotFree) continue;
         const uint64_t multi = (w >> 48) == kValMulti ? 1ull << 63 : 0ull;
-        *kt_slot(kt, i) = multi | (((1ull << 63) - 1ull) & ~low_mask) | (w & low_mask);
+        const uint64_t var = kt.vshift && !multi ? (w >> 48) << kt.vshift : 0ull;
+        *kt_slot(kt, i) = multi | (((1ull << 63) - 1ull) & ~low_mask) | (w & low_mask) | var;
     }
 }
 
@@ -590,7 +591,13 @@ __global__ void __launch_bounds__(kBlockH, (MODE & M_LOCAL) ? SPEQB_HMINB_LOCAL 
                             // in the unit's set.  Nothing is recorded for the refinement: a k-mer of one variant contributes
                             // a[g] / a[g] = 1 per window (src/fm_scanner.cpp:1099-1119), i.e. the variant's unique count.
                             uint32_t g = hi >> 16;
-                            if (kt.walk && kt.pshift != 0u)
+                            if (kt.vshift != 0u)
+                            {
+                                // table in walk form with room for the variant in the low word
+                                const uint32_t lo = h0 ? w[j][0] : h1 ? w[j][2] : h2 ? w[j][4] : w[j][6];
+                                g = (lo >> kt.vshift) & 0x7FFFu;
+                            }
+                            else if (kt.walk && kt.pshift != 0u)
                             {
                                 // table in walk form: the slot holds the k-mer's position, the variant is that of its text
                                 uint32_t p = hi & 0x7FFFFFFFu;
@@ -798,6 +805,16 @@ __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t po
 #ifndef SPEQB_WKWIN
 #define SPEQB_WKWIN 3
 #endif
+// which step a warp runs next: the one with the largest (lanes waiting for it) x weight
+#ifndef SPEQB_WGT_F
+#define SPEQB_WGT_F 1
+#endif
+#ifndef SPEQB_WGT_W
+#define SPEQB_WGT_W 1
+#endif
+#ifndef SPEQB_WGT_P
+#define SPEQB_WGT_P 1
+#endif
 // the 32 bases in front of the cursor, as a key (digit i = base t-1-i): 2-bit digits reversed
 __device__ __forceinline__ uint64_t rev_digits(uint64_t s)
 {
@@ -884,7 +901,8 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
         const bool is_f = phase == H_FETCH, is_w = phase == H_RUN && we != kNoRun, is_p = phase == H_RUN && we == kNoRun;
         const uint32_t m_f = __ballot_sync(kFullH, is_f), m_w = __ballot_sync(kFullH, is_w), m_p = __ballot_sync(kFullH, is_p);
         if (!(m_f | m_w | m_p)) break;
-        const int c_f = __popc(m_f), c_w = __popc(m_w), c_p = __popc(m_p);
+        // (weights: a probe trip costs about three walk trips, so it pays to let lanes gather in front of it)
+        const int c_f = __popc(m_f) * SPEQB_WGT_F, c_w = __popc(m_w) * SPEQB_WGT_W, c_p = __popc(m_p) * SPEQB_WGT_P;
         if (c_f >= c_w && c_f >= c_p)
         {
             // ---- next read: claim (first mate only), length + first group, the first groups of bases, the cursor at base k - 1
@@ -1747,6 +1765,7 @@ bool ktable_geometry(uint32_t k, uint64_t keys, uint32_t grow, KTabView * kt)
     kt->tflags = nullptr;
     kt->gvar = nullptr;
     kt->pos_side = nullptr;
+    kt->vshift = 0u;
     return true;
 }
 
