@@ -298,6 +298,20 @@ int speqg_backcheck(speqg_index * idx, int device, uint32_t k, uint64_t * unique
 int speqg_refine(speqg_scan * scan, const double * percent, const int32_t * group_counts, double * tkpg);
 /* export / import the recorded multiplicities (lb, rb, count) so several devices or ranks can be merged. */
 int speqg_scan_multiplicity_count(speqg_scan * scan, uint64_t * n_entries);
+/* The same estimate for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Calls no cudaMalloc, cudaFree
+ * or allocating library routine, copies nothing and does not synchronise: it launches speqg_refine's two kernels on the
+ * scan's stream (speqg_params.stream, else the handle's own; speqg_scan_sync waits for it).
+ *   d_percent, d_group_counts: n_groups entries in DEVICE memory of the scan's device; d_tkpg: n_groups entries out, DEVICE.
+ * The per-block partial sums live in one file-scope __device__ array of SPEQG_NOALLOC_MAX_DOUBLES doubles (1 MiB, held by
+ * every GPU that loads the library until the process exits): n_groups x (4 x multiprocessors) must not exceed it -- at most
+ * 221 variants on a 148-SM B200 -- else SPEQG_EINVAL.  All calls (all handles, all streams) of one device share that array,
+ * which keeps the last call's contents (every call overwrites what it reads, nothing has to start at zero): calls that
+ * overlap on the GPU race -- keep them on one stream or order them with events.  SPEQG_ESTATE when work is still due before
+ * the multiplicities can be read (reads submitted since the last speqg_refine / speqg_scan_multiplicity_count, a deferred
+ * FASTQ region): call one of those two once after the last submit, then this as often as needed. */
+#define SPEQG_NOALLOC_MAX_DOUBLES 131072
+int speqg_refine_noalloc(speqg_scan * scan, const double * d_percent, const int32_t * d_group_counts, double * d_tkpg);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * Host-side solve (fp64, exact operation order of the reference).

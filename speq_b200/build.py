@@ -20,7 +20,7 @@ OBJ_DIR = ROOT / "build"
 CLI_SRC = ROOT / "host"
 CLI_BIN = ROOT / "bin" / "speq"
 
-LIB_SOURCES = ["scanh.cu", "scan32.cu", "fastq.cu", "capi.cu", "capi_scan.cu", "capi_refine.cu", "kernels.cu", "sa_device.cu", "probe.cu", "index_build.cpp", "pack.cpp", "refidx.cpp"]
+LIB_SOURCES = ["scanh.cu", "scan32.cu", "fastq.cu", "capi.cu", "capi_scan.cu", "capi_refine.cu", "kernels.cu", "sa_device.cu", "probe.cu", "noalloc.cu", "index_build.cpp", "pack.cpp", "refidx.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall,-pthread"]
 
 

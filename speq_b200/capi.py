@@ -110,6 +110,7 @@ SIGNATURES = {
     "speqg_backcheck": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]),
     "speqg_refine": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "speqg_scan_multiplicity_count": (C.c_int, [C.c_void_p, u64p]),
+    "speqg_refine_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "speqg_unique_to_percent": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
 }
 

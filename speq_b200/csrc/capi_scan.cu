@@ -181,6 +181,15 @@ scan_refine_view refine_view(speqg_scan * s)
     return scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult, s->d_unique_n,
                             s->d_percent, s->d_tkpg, s->d_partial, s->d_gc, s->refine_grid};
 }
+// The same view WITHOUT any work: false when work is still due before the refinement may read mult[] (a deferred FASTQ region,
+// multiplicities not yet folded to the interval starts).  For speqg_refine_noalloc (noalloc.cu), which may only launch kernels.
+bool refine_view_ready(speqg_scan * s, scan_refine_view * out)
+{
+    if (s->fq_pending >= 0 || ((s->slot_mult_dirty || s->diff_dirty) && s->d_mult)) return false;
+    *out = scan_refine_view{s->device, s->p.k, s->idx->host.V, s->idx->host.n, s->view, s->compute, s->d_mult, s->d_unique_n,
+                            s->d_percent, s->d_tkpg, s->d_partial, s->d_gc, s->refine_grid};
+    return true;
+}
 }   // namespace speqb
 
 namespace
