@@ -128,7 +128,7 @@ struct speqg_scan
     unsigned long long * d_unique = nullptr, * d_total_g = nullptr, * d_scalars = nullptr, * d_mult = nullptr, * d_bad = nullptr, * d_work = nullptr;
     double * d_unique_w = nullptr, * d_qden = nullptr, * d_percent = nullptr, * d_tkpg = nullptr, * d_partial = nullptr;
     int32_t * d_gc = nullptr;
-    LaunchCfg cfg{}, cfg64{}, cfg_direct{}, cfg_stats{}, cfg_h{};
+    LaunchCfg cfg{}, cfg64{}, cfg_direct{}, cfg_stats{}, cfg_h{}, cfg_w{};
     int refine_grid = 0;
     Slot slots[kSlots];
     int next_slot = 0;
@@ -261,7 +261,9 @@ void launch_on_view(speqg_scan * s, BatchView const & v, uint64_t groups)
     }
     else if (s->algo == SPEQG_ALGO_KTABLE)
     {
-        CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, wpr, s->cfg_h, s->compute));
+        // (launch_scanh runs the walking scan on a walk-form table in global mode with one lane per read)
+        const bool walks = s->kt.walk && !wpr && !(s->mode & M_LOCAL);
+        CK(launch_scanh(s->kt, s->d_slot_mult, v, a, s->mode, wpr, walks ? s->cfg_w : s->cfg_h, s->compute));
         if (s->mode & M_RECORD) (s->d_diff ? s->diff_dirty : s->slot_mult_dirty) = true;
     }
     else CK(launch_scan32(s->d_sblk, s->view, v, a, s->mode, s->cfg, s->compute));
@@ -457,7 +459,8 @@ int speqg_scan_open(speqg_index * idx, int device, const speqg_params * params, 
                 if (32ull * ((uint64_t)s->kt.nbmask + 1) > (uint64_t)l2 / 4 * 3 && !walk_ok) s->algo = SPEQG_ALGO_KPAIR;
             }
             const bool walk = s->algo == SPEQG_ALGO_KTABLE && !s->kt.wide && walk_ok;
-            CK(scanh_launch_cfg(s->mode, V, walk ? 1 : 0, &s->cfg_h));
+            CK(scanh_launch_cfg(s->mode, V, 0, &s->cfg_h));
+            if (walk) CK(scanh_launch_cfg(s->mode, V, 1, &s->cfg_w));
             if (walk)
             {
                 // the position goes into the slot when it fits next to remainder and displacement (from bit 32 when those fit the

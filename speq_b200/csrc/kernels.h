@@ -149,7 +149,7 @@ cudaError_t launch_ktable_fold_mult(KTabView const & kt, DevIndex const & ix, ui
 // warp_per_read != 0: the 32 lanes of a warp split the windows of one read (long reads); else one read / pair per lane
 cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, BatchView const & b, ScanArgs const & a, int mode,
                          int warp_per_read, LaunchCfg cfg, cudaStream_t st);
-cudaError_t scanh_launch_cfg(int mode, uint32_t V, int walk, LaunchCfg * cfg);   // walk: the table is in walk form (scanw_kernel shares the grid)
+cudaError_t scanh_launch_cfg(int mode, uint32_t V, int walk, LaunchCfg * cfg);   // walk != 0: the configuration of scanw_kernel instead
 // two windows per probe (SPEQG_ALGO_KPAIR): a second table over the (k+1)-mers of the texts, values = one byte per k-mer
 cudaError_t launch_kpair_build(const uint64_t * t_bases, const uint32_t * t_inv, const uint64_t * t_grp_off, const uint32_t * t_len,
                                uint32_t n_texts, uint32_t max_len, KTabView const & kt, KTabView const & kp, uint32_t k,

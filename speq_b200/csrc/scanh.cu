@@ -806,11 +806,12 @@ __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t po
 #define SPEQB_WKWIN 3
 #endif
 // which step a warp runs next: the one with the largest (lanes waiting for it) x weight
+// (3 / 2 / 1 against 1 / 1 / 1: C2 3.62 -> 3.52 ms per 10 M reads, C3 11.64 -> 11.26 ms per 25 M, C4 14.31 -> 13.74 ms per 20 M)
 #ifndef SPEQB_WGT_F
-#define SPEQB_WGT_F 1
+#define SPEQB_WGT_F 3
 #endif
 #ifndef SPEQB_WGT_W
-#define SPEQB_WGT_W 1
+#define SPEQB_WGT_W 2
 #endif
 #ifndef SPEQB_WGT_P
 #define SPEQB_WGT_P 1
@@ -1712,8 +1713,9 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, int walk, LaunchCfg * cfg)
     }
     if (walk && !(mode & M_LOCAL))
     {
-        // the walking scan shares the grid
+        // walk != 0: the grid of the walking scan alone (it has its own launch configuration: the probing kernels keep theirs)
         int bw = 0;
+        bps = 1 << 30;
         const bool rec = (mode & M_RECORD) != 0, mask = V <= kMaxGroupsMask;
         auto occ = [&](auto kern) {
             if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
