@@ -805,6 +805,12 @@ __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t po
 #ifndef SPEQB_WKWIN
 #define SPEQB_WKWIN 3
 #endif
+// 1: the table lookups of a probe trip are spread over all 32 lanes through a queue in shared memory (needs SPEQB_WKWIN <= 3)
+#ifndef SPEQB_WCOOP
+#define SPEQB_WCOOP 1
+#endif
+constexpr size_t kWalkQueueBytes = SPEQB_WCOOP ? (size_t)(kBlockH / 32) * 32u * SPEQB_WKWIN * 8u : 0u;   // per CTA
+__host__ __device__ inline size_t scanw_queue_offset(uint32_t V) { return (32u + (size_t)V * 12u + 2u * 42u * 8u + 7u) & ~(size_t)7u; }
 // which step a warp runs next: the one with the largest (lanes waiting for it) x weight
 // (3 / 2 / 1 against 1 / 1 / 1: C2 3.62 -> 3.52 ms per 10 M reads, C3 11.64 -> 11.26 ms per 25 M, C4 14.31 -> 13.74 ms per 20 M)
 #ifndef SPEQB_WGT_F
@@ -833,6 +839,11 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     smem32_clear(sm, a.V);
     smem32_tables(sm, a, false);
     Tally32<MODE> env{b, a, sm};
+#if SPEQB_WCOOP
+    static_assert(SPEQB_WKWIN <= 3, "the queue offsets are summed from two ballots");
+    // the warp's queue of keys / answers: 32 lanes x kW entries
+    uint64_t * const wq = reinterpret_cast<uint64_t *>(smem_raw + scanw_queue_offset(a.V)) + (threadIdx.x >> 5) * (32u * SPEQB_WKWIN);
+#endif
 
     const uint32_t k = a.k;
     const uint64_t n_reads_b = b.n_reads_dev ? *b.n_reads_dev : b.n_reads;
@@ -1006,6 +1017,150 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                 }
             }
         }
+#if SPEQB_WCOOP
+        else
+        {
+            // ---- probe, the whole warp working: the lanes that wait for a probe roll up to kW windows each and put the keys of
+            //      the valid ones into the warp's queue in shared memory; then ALL 32 lanes look keys up (hash, bucket, four
+            //      compares), whatever step they wait for themselves; then the probing lanes take their answers in window
+            //      order up to the FIRST window that was found -- its slot gives a text position, the walk goes on from there.
+            uint64_t keys[kW];
+            bool due[kW];
+            uint32_t nd = 0u, nbase = 0u, o = 0u;
+            if (is_p)
+            {
+                // (behind an N: the next window that can be valid ends k - 1 - run bases further on)
+                while (run + 1u < k && t < pend)
+                {
+                    const uint32_t o3 = t & 31u, skip = k - 1u - run < pend - t ? k - 1u - run : pend - t;
+                    t += skip;
+                    if (o3 + skip >= 32u) next_group();
+                    seek();
+                }
+                o = t & 31u;
+                nbase = pend - t < (uint32_t)kW ? pend - t : (uint32_t)kW;
+                uint32_t bits = (uint32_t)(cb >> (2u * o)), ibits = ci >> o;
+                if (o + (uint32_t)kW > 32u)
+                {
+                    bits |= (uint32_t)nb << (2u * (32u - o));
+                    ibits |= ni << (32u - o);
+                }
+#pragma unroll
+                for (int j = 0; j < kW; ++j)
+                {
+                    due[j] = false;
+                    if ((uint32_t)j < nbase)
+                    {
+                        key = (key << 2) | ((bits >> (2 * j)) & 3u);
+                        run = ((ibits >> j) & 1u) ? 0u : run + 1u;
+                        due[j] = run >= k;
+                    }
+                    keys[j] = key;
+                    nd += due[j] ? 1u : 0u;
+                }
+            }
+            // where this lane's keys go: the sum of nd (<= 3) over the lanes below, from two ballots
+            const uint32_t b0 = __ballot_sync(kFullH, (nd & 1u) != 0u), b1 = __ballot_sync(kFullH, (nd & 2u) != 0u);
+            const uint32_t below = (1u << lane) - 1u;
+            const uint32_t off = (uint32_t)__popc(b0 & below) + 2u * (uint32_t)__popc(b1 & below);
+            const uint32_t Q = (uint32_t)__popc(b0) + 2u * (uint32_t)__popc(b1);
+            if (nd)
+            {
+                uint32_t qi = off;
+#pragma unroll
+                for (int j = 0; j < kW; ++j)
+                    if (due[j]) wq[qi++] = keys[j];
+            }
+            __syncwarp();
+            for (uint32_t i = lane; i < Q; i += 32u)
+            {
+                const uint64_t h = (wq[i] * kt.mul) & kt.mask_b;
+                uint32_t bk = (uint32_t)(h >> kt.rbits);
+                uint64_t want = h & kt.rmask;
+                uint64_t res = kSlotFree;                         // not in the index
+                bool ask = true;
+                if (kt.filt)
+                {
+                    // table beyond L2: the presence filter (L2-resident) answers most windows that hold a sequencing error
+                    const uint32_t fi = (uint32_t)(h >> kt.fshift);
+                    ask = ((ldg32_keep(kt.filt + (fi >> 5), l2_policy_keep()) >> (fi & 31u)) & 1u) != 0u;
+                }
+                if (ask)
+                {
+                    for (uint32_t d = 0u; d <= kMaxDisp; ++d)
+                    {
+                        uint32_t w[8];
+                        if (kt.filt) ldg256_stream(w, kt.slots + 4ull * bk, l2_policy_stream());
+                        else
+                            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                                         : "l"(kt.slots + 4ull * bk));
+                        n_probe += 1u;
+                        const uint32_t want_lo = (uint32_t)want, want_hi = (uint32_t)(want >> 32);
+                        const bool h0 = (((w[0] ^ want_lo) & kmask_lo) | ((w[1] ^ want_hi) & kmask_hi)) == 0u;
+                        const bool h1 = (((w[2] ^ want_lo) & kmask_lo) | ((w[3] ^ want_hi) & kmask_hi)) == 0u;
+                        const bool h2 = (((w[4] ^ want_lo) & kmask_lo) | ((w[5] ^ want_hi) & kmask_hi)) == 0u;
+                        const bool h3 = (((w[6] ^ want_lo) & kmask_lo) | ((w[7] ^ want_hi) & kmask_hi)) == 0u;
+                        if (h0 || h1 || h2 || h3)
+                        {
+                            const uint32_t hi = h0 ? w[1] : h1 ? w[3] : h2 ? w[5] : w[7];
+                            // positions in a side array: "several variants" + variant on top, the slot's index below
+                            if (kt.pshift == 0u) res = ((uint64_t)(hi >> 16) << 48) | (4ull * bk + (h0 ? 0u : h1 ? 1u : h2 ? 2u : 3u));
+                            else res = u64of(h0 ? w[0] : h1 ? w[2] : h2 ? w[4] : w[6], hi);
+                            break;
+                        }
+                        // a free last slot ends the probe sequence: the k-mer does not occur in the index
+                        if ((w[6] & w[7]) == 0xFFFFFFFFu) break;
+                        // rare: the home bucket is full of other k-mers; the k-mer may sit in the next bucket
+                        bk = (bk + 1u) & kt.nbmask;
+                        want += 1ull << kt.rbits;
+                    }
+                }
+                wq[i] = res;
+            }
+            __syncwarp();
+            if (is_p)
+            {
+                int jh = -1;                                      // the first window of the trip that was found
+                uint64_t rh = 0ull;
+                uint32_t qi = off;
+#pragma unroll
+                for (int j = 0; j < kW; ++j)
+                {
+                    if (!due[j] || jh >= 0) continue;
+                    c_total += 1u;                                // ++total_kmers (src/fm_scanner.cpp:164)
+                    const uint64_t r = wq[qi++];
+                    if (r != kSlotFree) { jh = j; rh = r; }
+                }
+                // the cursor moves behind the window that was found, or over the whole trip
+                const uint32_t adv = jh >= 0 ? (uint32_t)jh + 1u : nbase;
+                // (the windows behind a hit belong to the walk: key and run are rebuilt where it ends)
+                t += adv;
+                if (o + adv >= 32u) next_group();
+                if (jh >= 0)
+                {
+                    const bool multi = (rh >> 63) != 0ull;
+                    uint32_t p;                                   // where the k-mer starts in the texts (its smallest position)
+                    if (kt.pshift == 0u) p = load_ro(kt.pos_side + (rh & 0x3FFFFFFFFull));
+                    else if (kt.pshift == 32u) p = (uint32_t)(rh >> 32) & 0x7FFFFFFFu;
+                    else p = (uint32_t)((rh & ~(1ull << 63)) >> kt.pshift);
+                    we = p + k - 1u;
+                    cur_g = kt.pshift == 0u && !multi ? (uint32_t)(rh >> 48) & 0x7FFFu : (uint32_t)load_ro(kt.gvar + (p >> 5));
+                    if (!multi) count_unique(cur_g, 1u);          // ++unique_kmers[which_hit] (src/fm_scanner.cpp:178-191)
+                    else if (RECORD)
+                    {
+                        if (p == rl + 1u) rl = p;
+                        else
+                        {
+                            if (rs != kNoRun) run_write(rs, rl);
+                            rs = p; rl = p;
+                        }
+                    }
+                }
+            }
+            __syncwarp();                                         // the queue is reused by the next probe trip
+        }
+#else
         else if (is_p)
         {
             // ---- probe: up to kW windows, every probe issued, then consumed in window order up to the FIRST window that is
@@ -1130,6 +1285,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                 }
             }
         }
+#endif
         if (phase == H_RUN && t >= pend)
         {
             // the read is finished
@@ -1717,9 +1873,10 @@ cudaError_t scanh_launch_cfg(int mode, uint32_t V, int walk, LaunchCfg * cfg)
         int bw = 0;
         bps = 1 << 30;
         const bool rec = (mode & M_RECORD) != 0, mask = V <= kMaxGroupsMask;
+        const size_t smem_w = scanw_queue_offset(V) + kWalkQueueBytes;
         auto occ = [&](auto kern) {
-            if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, kern, kBlockH, smem);
+            if (smem_w > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w);
+            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bw, kern, kBlockH, smem_w);
         };
         if (rec && mask) occ(scanw_kernel<true, true>);
         else if (rec) occ(scanw_kernel<true, false>);
@@ -1803,10 +1960,11 @@ cudaError_t launch_scanh(KTabView const & kt, unsigned long long * slot_mult, Ba
     {
         // global mode, one lane per read, table in walk form: the walking scan
         const bool rec = (mode & M_RECORD) != 0, mask = a.V <= kMaxGroupsMask;
-        if (rec && mask) scanw_kernel<true, true><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
-        else if (rec) scanw_kernel<true, false><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
-        else if (mask) scanw_kernel<false, true><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
-        else scanw_kernel<false, false><<<cfg.grid, cfg.block, smem, st>>>(kt, b, a, paired);
+        const size_t smem_w = scanw_queue_offset(a.V) + kWalkQueueBytes;
+        if (rec && mask) scanw_kernel<true, true><<<cfg.grid, cfg.block, smem_w, st>>>(kt, b, a, paired);
+        else if (rec) scanw_kernel<true, false><<<cfg.grid, cfg.block, smem_w, st>>>(kt, b, a, paired);
+        else if (mask) scanw_kernel<false, true><<<cfg.grid, cfg.block, smem_w, st>>>(kt, b, a, paired);
+        else scanw_kernel<false, false><<<cfg.grid, cfg.block, smem_w, st>>>(kt, b, a, paired);
         return cudaGetLastError();
     }
     SPEQB_SCANH_DISPATCH(m, (kern<<<cfg.grid, cfg.block, smem, st>>>(kt, slot_mult, b, a, paired)))
