@@ -805,9 +805,13 @@ __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t po
 #ifndef SPEQB_WKWIN
 #define SPEQB_WKWIN 3
 #endif
-// 1: the table lookups of a probe trip are spread over all 32 lanes through a queue in shared memory (needs SPEQB_WKWIN <= 3)
+// 1: the table lookups of a probe trip are spread over all 32 lanes through a queue in shared memory (needs SPEQB_WKWIN <= 3).
+// Measured SLOWER and therefore off (profiles/r2_sweep_walk_coop.txt: C2 3.53 -> 3.80 ms per 10 M reads, C3 11.28 -> 12.60 ms
+// per 25 M, C4 13.78 -> 16.42 ms per 20 M): every lane works in a probe trip then (75 registers, no bucket arrays), but the
+// queue's two warp syncs, the shared-memory round trip and one lookup in flight per lane instead of three cost more than the
+// idle lanes did.
 #ifndef SPEQB_WCOOP
-#define SPEQB_WCOOP 1
+#define SPEQB_WCOOP 0
 #endif
 constexpr size_t kWalkQueueBytes = SPEQB_WCOOP ? (size_t)(kBlockH / 32) * 32u * SPEQB_WKWIN * 8u : 0u;   // per CTA
 __host__ __device__ inline size_t scanw_queue_offset(uint32_t V) { return (32u + (size_t)V * 12u + 2u * 42u * 8u + 7u) & ~(size_t)7u; }
