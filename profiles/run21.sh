@@ -6,10 +6,6 @@ timeout 1500 python -m pytest tests -q -m gpu --maxfail=4 2>&1 | tail -40 > $O/r
 tail -3 $O/r21_pytest.txt
 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > $O/r21_smoke.txt 2>&1
 t0=$(date +%s); python bench.py --steps 20 --warmup 5 > $O/r2_bench_f_C3_default.json 2> $O/r21_bench_err.txt; echo "wall $(( $(date +%s) - t0 )) s" >> $O/r21_bench_err.txt
-for c in C2:10000000 C4:100000000 C5:1000000 C1:100000; do
-  set -- ${c/:/ }
-  timeout 600 python bench.py --config $1 --reads $2 --steps 10 --warmup 3 > $O/r2_bench_f_$1.json 2> $O/r21_err_$1.txt
-done
 F="--steps 2 --warmup 1 --no-cpu --no-e2e --no-probe"
 cap() {   # name, kernel regex, skip, count, bench args...
   name=$1; rx=$2; skip=$3; cnt=$4; shift 4
