@@ -661,14 +661,17 @@ int do_scan(cmd_arguments & args)
     const uint64_t cap_reads = std::max<uint64_t>(2, args.batch_reads & ~1u);
     const uint64_t cap_bytes = std::min<uint64_t>(cap_reads * 320, uint64_t(512) << 20);
     std::string prep_error;
+    // (paired input always needs the second staging array -- the device parser takes the second file's bytes there, the host
+    //  paths the qualities -- so it is pinned here as well instead of inside the scan phase)
+    const bool records_now = !args.in_file_reads_path_2.empty();
     std::thread prep([&]()
     {
         try
         {
             for (unsigned d = 0; d < gpus; ++d)
             {
-                lanes[d].buf[0].alloc(cap_bytes, cap_reads, false);
-                lanes[d].buf[1].alloc(cap_bytes, cap_reads, false);
+                lanes[d].buf[0].alloc(cap_bytes, cap_reads, records_now);
+                lanes[d].buf[1].alloc(cap_bytes, cap_reads, records_now);
             }
         }
         catch (std::exception const & e) { prep_error = e.what(); }
