@@ -1,3 +1,4 @@
+# (compute-sanitizer turned out to be closed on this pool: the memcheck step below printed the pool's notice and ran nothing.)
 # compute-sanitizer memcheck over the walking scan's differential test, the walk-form table builds and the no-alloc entry point;
 # CLI tests and paired CLI timing after pinning the second staging array at start-up
 set -x
