@@ -902,6 +902,10 @@ int speqg_scan_finish(speqg_scan * s, uint64_t * unique_u64, double * unique_f64
     const unsigned long long bad = hs[3 * (size_t)V + SC_COUNT];
     if (bad & 2ull) throw api_error(SPEQG_EINVAL, "read longer than 2^32 bases");
     if (bad) throw api_error(SPEQG_EINVAL, "parse_error: illegal (non-IUPAC) sequence character in a read");
+#if defined(SPEQB_BOUNDS) && SPEQB_BOUNDS
+    if (s->kt.walk && hs[2 * (size_t)V + SC_OCC])
+        throw api_error(SPEQG_ESTATE, "checking build: " + std::to_string(hs[2 * (size_t)V + SC_OCC]) + " index checks failed in scanw_kernel");
+#endif
     if (unique_u64) memcpy(unique_u64, hs, V * 8);
     if (unique_f64) memcpy(unique_f64, hs + 2 * (size_t)V + SC_COUNT, V * 8);
     if (counts)

@@ -802,6 +802,16 @@ __device__ __forceinline__ uint32_t ldg32_keep(const uint32_t * ptr, uint64_t po
 #ifndef SPEQB_WMINB
 #define SPEQB_WMINB 3
 #endif
+// -DSPEQB_BOUNDS=1: a checking build (compute-sanitizer is not available on the pool) -- every index the walking scan derives
+// from table contents is checked before use; a violation is counted in scalars[SC_OCC] and speqg_scan_finish fails on it
+#ifndef SPEQB_BOUNDS
+#define SPEQB_BOUNDS 0
+#endif
+#if SPEQB_BOUNDS
+#define SPEQB_CHECK(cond) do { if (!(cond)) atomicAdd(a.scalars + SC_OCC, 1ull); } while (0)
+#else
+#define SPEQB_CHECK(cond) do { } while (0)
+#endif
 #ifndef SPEQB_WKWIN
 #define SPEQB_WKWIN 3
 #endif
@@ -875,6 +885,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
     uint32_t we = kNoRun, cur_g = 0u;
     uint32_t rs = kNoRun, rl = 0xFFFFFFFDu;
     auto run_write = [&](uint32_t s0, uint32_t s1) {
+        SPEQB_CHECK(s0 <= s1 && (uint64_t)s1 + 1u < 32ull * kt.tgroups + 2ull);
         atomicAdd(a.diff + s0, 1ull);
         atomicAdd(a.diff + s1 + 1u, ~0ull);
     };
@@ -975,6 +986,7 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
                 // (tflags ends with two zero words: behind the last text no window is valid, whatever the clamped base words hold)
                 const uint32_t e1 = we + 1u, ot = e1 & 31u, gt = e1 >> 5, glast = kt.tgroups - 1u;
                 const uint64_t T0 = load_ro(kt.tbases + (gt < glast ? gt : glast)), T1 = load_ro(kt.tbases + (gt + 1u < glast ? gt + 1u : glast));
+                SPEQB_CHECK(gt + 1u < kt.tgroups + 2u && t < pend);
                 const uint64_t F0 = load_ro(kt.tflags + gt), F1 = load_ro(kt.tflags + gt + 1u);
                 const uint32_t o = t & 31u;
                 const uint64_t TB = ot ? (T0 >> (2u * ot)) | (T1 << (64u - 2u * ot)) : T0;
@@ -1273,8 +1285,10 @@ __global__ void __launch_bounds__(kBlockH, SPEQB_WMINB) scanw_kernel(const KTabV
             {
                 // where the k-mer starts in the texts (its smallest position): in the slot, or in the side array
                 uint32_t p = h_hi & 0x7FFFFFFFu;
+                SPEQB_CHECK(kt.pshift != 0u || h_lo < 4ull * ((uint64_t)kt.nbmask + 1ull));
                 if (kt.pshift == 0u) p = load_ro(kt.pos_side + h_lo);
                 else if (kt.pshift != 32u) p = (uint32_t)((u64of(h_lo, h_hi) & ~(1ull << 63)) >> kt.pshift);
+                SPEQB_CHECK((uint64_t)p + k <= 32ull * kt.tgroups);
                 we = p + k - 1u;
                 cur_g = kt.pshift == 0u && !slot_multi(h_hi) ? h_hi >> 16 : (uint32_t)load_ro(kt.gvar + (p >> 5));
                 if (!slot_multi(h_hi)) count_unique(cur_g, 1u);   // ++unique_kmers[which_hit] (src/fm_scanner.cpp:178-191)
