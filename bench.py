@@ -652,6 +652,8 @@ def main() -> None:
                 if tj:
                     roof["traffic"] = tj["dram_bytes_per_read"] * R
                     roof["traffic_source"] = tj["source"]
+                    if "issue" in tj:      # what the same ncu capture says about instruction issue (the walking scan's real bound)
+                        roof["issue_from_ncu"] = tj["issue"]
                     break
         except Exception:
             pass
